@@ -1,0 +1,185 @@
+/*
+ * ls1g.h — C ABI of the B200 (sm_100a) short-range force + integrate path of ls1-MarDyn.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no C++/torch types.  The C++ shim
+ * classes a maintainer adds to ls1 (GpuLinkedCells : ParticleContainer, GpuLeapfrog : Integrator;
+ * see INTEGRATION.md) forward to exactly these entry points.  Every entry point names the
+ * reference interface it replaces (paths relative to the reference tree).
+ *
+ * Conventions
+ *   - All pointers are caller-owned HOST memory; arrays of vectors are AoS ([n][3], [n][4]).
+ *   - All calls are synchronous on return and return 0 on success, non-zero on error;
+ *     ls1g_last_error() gives the message (the shim maps it to global_log->error + Simulation::exit,
+ *     the reference's own error path: src/particleContainer/LinkedCells.cpp:101,162).
+ *   - One context = one ParticleContainer = one GPU = one rank (src/Simulation.cpp:135-139).
+ *   - There is no CPU fallback: without a CUDA device every compute call fails.
+ */
+#ifndef LS1G_H
+#define LS1G_H
+
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct ls1g_ctx ls1g_ctx;
+
+/* How the cell grid is derived from the cutoff (the reference has two code paths). */
+enum {
+	LS1G_GRID_REBUILD = 0, /* LinkedCells::rebuild, XML path: float rc   (LinkedCells.cpp:136-204) */
+	LS1G_GRID_CTOR    = 1  /* LinkedCells(min,max,rc), test path: double rc (LinkedCells.cpp:42-107) */
+};
+
+typedef struct {
+	int    device;            /* CUDA device ordinal */
+	double box_min[3];        /* bounding box of THIS rank: rebuild(bBoxMin,bBoxMax) (LinkedCells.cpp:136) */
+	double box_max[3];
+	double global_length[3];  /* Domain::getGlobalLength (periodic shift magnitude) */
+	double cutoff;            /* rc   : charge/dipole/quadrupole + cell size (Simulation.cpp:257-267) */
+	double lj_cutoff;         /* rcLJ : LJ sites */
+	double eps_rf;            /* Domain::getepsilonRF (reaction field) */
+	int    grid_mode;         /* LS1G_GRID_* */
+	int    rank_grid[3];      /* DomainDecomposition::_gridSize  (DomainDecomposition.cpp:35) ; {1,1,1} = sequential */
+	int    rank_coords[3];    /* DomainDecomposition::_coords */
+	uint64_t capacity;        /* max molecules incl. halo copies this context may hold; 0 = grow on upload */
+} ls1g_config;
+
+/* One Component (src/molecules/Component.h).  Site tables are row-major doubles:
+ *   lj         [n_lj][7]         x y z m eps sigma shift6     (Site.h:84-141)
+ *   charge     [n_charge][5]     x y z m q                    (Site.h:143-193)
+ *   dipole     [n_dipole][7]     x y z ex ey ez absMy         (Site.h:195-300)
+ *   quadrupole [n_quadrupole][7] x y z ex ey ez absQ
+ */
+typedef struct {
+	double mass;              /* Component::m()  */
+	double inertia[3];        /* I11, I22, I33 (principal axes) */
+	int    rot_dof;           /* Component::getRotationalDegreesOfFreedom() */
+	int    n_lj, n_charge, n_dipole, n_quadrupole;
+	const double* lj;
+	const double* charge;
+	const double* dipole;
+	const double* quadrupole;
+} ls1g_component;
+
+/* Fields for ls1g_download (bit mask). */
+enum {
+	LS1G_F_ID = 1, LS1G_F_CID = 2, LS1G_F_R = 4, LS1G_F_V = 8, LS1G_F_Q = 16, LS1G_F_L = 32,
+	LS1G_F_F = 64, LS1G_F_M = 128, LS1G_F_VI = 256, LS1G_F_CELL = 512
+};
+
+typedef struct {
+	uint64_t* id;     /* [n]    */
+	uint32_t* cid;    /* [n]    */
+	double*   r;      /* [n][3] */
+	double*   v;      /* [n][3] */
+	double*   q;      /* [n][4] (w,x,y,z) */
+	double*   L;      /* [n][3] angular momentum D */
+	double*   F;      /* [n][3] */
+	double*   M;      /* [n][3] */
+	double*   Vi;     /* [n][3] */
+	uint32_t* cell;   /* [n] linear cell index (z*ny+y)*nx+x incl. halo layer */
+} ls1g_fields;
+
+/* Per-step record of ls1g_run (one row per time step). */
+typedef struct {
+	double   upot;      /* Domain::setLocalUpot   value (VectorizedCellProcessor.cpp:156) */
+	double   virial;    /* Domain::setLocalVirial value (VectorizedCellProcessor.cpp:155) */
+	double   summv2;    /* Domain::setLocalSummv2 (Leapfrog.cpp:148) */
+	double   sumIw2;    /* Domain::setLocalSumIw2 */
+	uint64_t n;         /* Domain::setLocalNrotDOF N      */
+	uint64_t rot_dof;   /* Domain::setLocalNrotDOF rotDOF */
+} ls1g_step_record;
+
+const char* ls1g_last_error(void);
+int ls1g_version(void);
+
+/* --- life cycle --------------------------------------------------------------------------
+ * replaces: Simulation::readXML datastructure dispatch + container->rebuild (Simulation.cpp:411-450) */
+int ls1g_create(const ls1g_config* cfg, ls1g_ctx** out);
+int ls1g_destroy(ls1g_ctx* ctx);
+
+/* replaces: VectorizedCellProcessor ctor tables (VectorizedCellProcessor.cpp:21-98),
+ * Comp2Param::initialize (Comp2Param.cpp:10-187), Ensemble::setComponentLookUpIDs (EnsembleBase.cpp:91-103).
+ * mixcoeff = Domain::getmixcoeff(): (xi, eta) per component pair i<j, row-major upper triangle. */
+int ls1g_set_components(ls1g_ctx* ctx, int n_components, const ls1g_component* comps,
+                        const double* mixcoeff, int n_mixcoeff);
+
+/* --- grid queries (host only, no GPU work) ------------------------------------------------
+ * replaces: LinkedCells::rebuild geometry (LinkedCells.cpp:136-204), CellBorderAndFlagManager */
+int ls1g_get_grid(const ls1g_ctx* ctx, int cells_per_dim[3], double cell_length[3]);
+/* replaces: LinkedCells::getCellIndexOfPoint (LinkedCells.cpp:830-882); host evaluation */
+int ls1g_cell_index_of_points_host(const ls1g_ctx* ctx, size_t n, const double* points, uint32_t* out);
+/* same on the device (the kernel the sort uses) */
+int ls1g_cell_index_of_points(ls1g_ctx* ctx, size_t n, const double* points, uint32_t* out);
+/* replaces: C08CellPairTraversal::traverseCellPairs + C08BasedTraversals::processBaseCell
+ * (C08CellPairTraversal.h:50-80, C08BasedTraversals.h:48-102): emits (cell1, cell2, kind) triplets,
+ * kind 0 = processCell, 1 = processCellPair, in colour/base-cell order.  pairs may be NULL to count. */
+int ls1g_debug_cell_pairs(const ls1g_ctx* ctx, uint32_t* triplets, size_t capacity, size_t* n_out);
+
+/* --- particle storage ---------------------------------------------------------------------
+ * replaces: ParticleContainer::addParticles / clear (LinkedCells.cpp:445-520,596-601). Replaces the content. */
+int ls1g_upload(ls1g_ctx* ctx, size_t n, const uint64_t* id, const uint32_t* cid,
+                const double* r, const double* v, const double* q, const double* L);
+/* number of molecules held: owned (non-halo cells) and halo copies */
+int ls1g_count(ls1g_ctx* ctx, uint64_t* n_owned, uint64_t* n_halo);
+/* replaces: ParticleIterator over ALL_CELLS / ONLY_INNER_AND_BOUNDARY + Molecule getters.
+ * Molecules come in cell-sorted order; include_halo selects ALL_CELLS. Returns count in *n_out. */
+int ls1g_download(ls1g_ctx* ctx, int field_mask, int include_halo, size_t capacity,
+                  ls1g_fields* out, size_t* n_out);
+
+/* --- per-step operators ------------------------------------------------------------------- */
+/* replaces: LinkedCells::update (LinkedCells.cpp:243-356): re-bin into cells (device sort) */
+int ls1g_update(ls1g_ctx* ctx);
+/* replaces: DomainDecompBase::exchangeMolecules (DomainDecompBase.cpp:51-86,174-225,293-348) on a
+ * sequential rank grid, DomainDecomposition::balanceAndExchange (DomainDecomposition.cpp:87-103)
+ * otherwise: wrap/send leaving molecules, create/receive halo copies, re-bin. */
+int ls1g_exchange(ls1g_ctx* ctx);
+/* replaces: LinkedCells::updateMoleculeCaches + traverseCells(VectorizedCellProcessor) +
+ * Simulation::updateForces/calcFM (LinkedCells.cpp:564-575,1076-1086; VectorizedCellProcessor.cpp:
+ * 796-2821; FullMolecule.cpp:551-631).  Outputs the values endTraversal hands to Domain. */
+int ls1g_traverse(ls1g_ctx* ctx, double* upot, double* virial);
+/* replaces: LinkedCells::deleteOuterParticles (LinkedCells.cpp:611-628) */
+int ls1g_delete_outer(ls1g_ctx* ctx);
+/* replaces: Leapfrog::eventNewTimestep -> FullMolecule::upd_preF (Leapfrog.cpp:48-68, FullMolecule.cpp:334-364) */
+int ls1g_integrate_pre(ls1g_ctx* ctx, double dt);
+/* replaces: Leapfrog::eventForcesCalculated -> upd_postF + Domain::setLocal* (Leapfrog.cpp:70-155) */
+int ls1g_integrate_post(ls1g_ctx* ctx, double dt_half, double* summv2, double* sumIw2,
+                        uint64_t* n, uint64_t* rot_dof);
+/* replaces: VelocityScalingThermostat::apply (VelocityScalingThermostat.cpp:45-80), global betas */
+int ls1g_scale(ls1g_ctx* ctx, double beta_trans, double beta_rot);
+
+/* Device-resident time loop: n_steps x { integrate_pre, update+exchange, traverse, delete_outer,
+ * integrate_post, [thermostat] } in the order of Simulation::simulate (Simulation.cpp:979-1177).
+ * target_temperature <= 0 : NVE (Domain::thermostatOff); else Domain::calculateGlobalValues betas
+ * (Domain.cpp:226-247) are applied each step.  records may be NULL, else [n_steps].
+ * Requires forces from a previous ls1g_traverse (as prepare_start does, Simulation.cpp:813-844). */
+int ls1g_run(ls1g_ctx* ctx, int n_steps, double dt, double target_temperature, ls1g_step_record* records);
+
+/* --- multi-GPU (one context per rank/GPU) --------------------------------------------------
+ * replaces: DomainDecomposition::getBoundingBoxMin/Max (DomainDecomposition.cpp:116-125); host only */
+int ls1g_decomp_box(const int rank_grid[3], const int rank_coords[3], const double global_length[3],
+                    double box_min[3], double box_max[3]);
+/* replaces: MPI_Dims_create + MPI_Cart_coords (DomainDecomposition.cpp:35-39); host only */
+int ls1g_decomp_grid(int n_ranks, int rank, int rank_grid[3], int rank_coords[3]);
+/* NCCL bootstrap: rank 0 calls ls1g_comm_unique_id, distributes the 128 bytes, all call ls1g_comm_init.
+ * replaces: MPI_Cart_create + CommunicationPartner set-up (DomainDecomposition.cpp:36, DomainDecompMPIBase.cpp:148-170) */
+int ls1g_comm_unique_id(unsigned char id[128]);
+int ls1g_comm_init(ls1g_ctx* ctx, int n_ranks, int rank, const unsigned char id[128]);
+/* replaces: Domain::calculateGlobalValues collComm allreduce (Domain.cpp:170-176,214-224): sums 6 doubles in place */
+int ls1g_allreduce_sum(ls1g_ctx* ctx, double* values, int n);
+
+/* --- measurement -------------------------------------------------------------------------- */
+enum { LS1G_T_FORCE = 0, LS1G_T_SORT = 1, LS1G_T_INTEGRATE = 2, LS1G_T_EXCHANGE = 3, LS1G_T_COUNT = 4 };
+/* accumulated CUDA-event time (ms) and launch count per kernel class since the last reset */
+int ls1g_timers(ls1g_ctx* ctx, double ms[LS1G_T_COUNT], uint64_t launches[LS1G_T_COUNT], int reset);
+/* dependent-free DFMA micro-kernel: measured FP64 FMA peak of this GPU in TFLOP/s (roofline denominator) */
+int ls1g_measure_fp64_peak(int device, double* tflops);
+/* pair statistics of the last traverse: molecule pairs inside the cutoff (counted once) */
+int ls1g_last_pair_count(ls1g_ctx* ctx, uint64_t* pairs_in_cutoff);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LS1G_H */

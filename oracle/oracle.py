@@ -1,0 +1,139 @@
+"""ctypes binding of the CPU oracle (oracle/libls1_oracle.so).  TEST INFRASTRUCTURE ONLY:
+imported by tests/, __graft_entry__.smoke() and bench.py's cpu_baseline leg, never by the product."""
+import ctypes as C
+import os
+import subprocess
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+
+
+class OGrid(C.Structure):
+    _fields_ = [("box_min", C.c_double * 3), ("box_max", C.c_double * 3),
+                ("halo_min", C.c_double * 3), ("halo_max", C.c_double * 3),
+                ("cell_len", C.c_double * 3), ("cell_len_recip", C.c_double * 3),
+                ("box_cells", C.c_int * 3), ("cpd", C.c_int * 3), ("cutoff", C.c_double)]
+
+
+class OParams(C.Structure):
+    _fields_ = [("nc", C.c_int), ("counts", C.c_void_p), ("scal", C.c_void_p), ("lj", C.c_void_p),
+                ("ch", C.c_void_p), ("di", C.c_void_p), ("qu", C.c_void_p), ("mix", C.c_void_p),
+                ("nmix", C.c_int), ("eps_rf", C.c_double), ("rc", C.c_double), ("rc_lj", C.c_double)]
+
+
+def build():
+    subprocess.check_call(["make", "-s", "-C", _HERE])
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        path = os.path.join(_HERE, "libls1_oracle.so")
+        if not os.path.exists(path):
+            build()
+        _LIB = C.CDLL(path)
+        _LIB.o_cell_index.restype = C.c_uint32
+        _LIB.o_c08_pairs.restype = C.c_size_t
+        _LIB.o_exchange.restype = C.c_size_t
+    return _LIB
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class System:
+    """Component tables + cutoffs, in the flattened layout of the ref_driver dump."""
+
+    def __init__(self, counts, scal, lj, ch, di, qu, mix, eps_rf, rc, rc_lj):
+        self.counts = np.ascontiguousarray(counts, dtype=np.int64).reshape(-1, 6)
+        self.scal = np.ascontiguousarray(scal, dtype=np.float64).reshape(-1, 4)
+        self.lj = np.ascontiguousarray(lj, dtype=np.float64).reshape(-1, 7)
+        self.ch = np.ascontiguousarray(ch, dtype=np.float64).reshape(-1, 5)
+        self.di = np.ascontiguousarray(di, dtype=np.float64).reshape(-1, 7)
+        self.qu = np.ascontiguousarray(qu, dtype=np.float64).reshape(-1, 7)
+        self.mix = np.ascontiguousarray(mix, dtype=np.float64).ravel()
+        self.eps_rf, self.rc, self.rc_lj = float(eps_rf), float(rc), float(rc_lj)
+        self.params = OParams(len(self.counts), _p(self.counts), _p(self.scal), _p(self.lj), _p(self.ch),
+                              _p(self.di), _p(self.qu), _p(self.mix), len(self.mix),
+                              self.eps_rf, self.rc, self.rc_lj)
+
+    @classmethod
+    def from_dump(cls, d):
+        return cls(d["comp_counts"], d["comp_scalars"], d["lj_sites"], d["charge_sites"], d["dipole_sites"],
+                   d["quadrupole_sites"], d["mixcoeff"], float(d["epsRF"][0]), float(d["rc"][0]), float(d["rc"][1]))
+
+    @classmethod
+    def single_lj(cls, eps=1.0, sigma=1.0, mass=1.0, rc=2.5, shift6=0.0):
+        return cls([[1, 0, 0, 0, 0, 0]], [[mass, 0, 0, 0]], [[0, 0, 0, mass, eps, sigma, shift6]],
+                   np.zeros((0, 5)), np.zeros((0, 7)), np.zeros((0, 7)), [], 1e10, rc, rc)
+
+
+def grid(box_min, box_max, rc, mode):
+    g = OGrid()
+    bmin = (C.c_double * 3)(*box_min)
+    bmax = (C.c_double * 3)(*box_max)
+    rcode = lib().o_grid_init(C.byref(g), bmin, bmax, C.c_double(rc), int(mode))
+    if rcode:
+        raise ValueError("region too small")
+    return g
+
+
+def cell_indices(g, pts):
+    pts = np.ascontiguousarray(pts, dtype=np.float64).reshape(-1, 3)
+    out = np.empty(len(pts), dtype=np.uint32)
+    lib().o_cell_indices(C.byref(g), C.c_size_t(len(pts)), _p(pts), _p(out))
+    return out
+
+
+def c08_pairs(g):
+    n = lib().o_c08_pairs(C.byref(g), None, C.c_size_t(0))
+    out = np.empty((n, 3), dtype=np.uint32)
+    lib().o_c08_pairs(C.byref(g), _p(out), C.c_size_t(n))
+    return out
+
+
+def lj_tables(sysm):
+    S = int(sysm.counts[:, 0].sum())
+    e = np.zeros((S, S)); s = np.zeros((S, S)); sh = np.zeros((S, S))
+    lib().o_lj_tables(C.byref(sysm.params), _p(e), _p(s), _p(sh), S * S)
+    return e, s, sh
+
+
+def exchange(g, global_len, r):
+    """returns (wrapped r, halo_src, halo_r)"""
+    r = np.array(r, dtype=np.float64).reshape(-1, 3).copy()
+    n = len(r)
+    cap = 27 * n + 64
+    src = np.empty(cap, dtype=np.uint32)
+    hr = np.empty((cap, 3))
+    gl = (C.c_double * 3)(*global_len)
+    h = lib().o_exchange(C.byref(g), gl, C.c_size_t(n), _p(r), C.c_size_t(cap), _p(src), _p(hr))
+    assert h <= cap
+    return r, src[:h].copy(), hr[:h].copy()
+
+
+def forces(sysm, g, cid, r, q):
+    """returns dict(F, M, Vi, upot, virial, q(normalised), n_dist, n_pairs)"""
+    cid = np.ascontiguousarray(cid, dtype=np.uint32)
+    r = np.ascontiguousarray(r, dtype=np.float64).reshape(-1, 3)
+    q = np.array(q, dtype=np.float64).reshape(-1, 4).copy()
+    n = len(cid)
+    F = np.zeros((n, 3)); M = np.zeros((n, 3)); Vi = np.zeros((n, 3))
+    up = C.c_double(); vir = C.c_double()
+    stats = np.zeros(2, dtype=np.uint64)
+    lib().o_forces(C.byref(sysm.params), C.byref(g), C.c_size_t(n), _p(cid), _p(r), _p(q), _p(F), _p(M), _p(Vi),
+                   C.byref(up), C.byref(vir), _p(stats))
+    return dict(F=F, M=M, Vi=Vi, upot=up.value, virial=vir.value, q=q, n_dist=int(stats[0]), n_pairs=int(stats[1]))
+
+
+def run(sysm, g, global_len, cid, r, v, q, L, F, M, steps, dt, target_T=0.0):
+    cid = np.ascontiguousarray(cid, dtype=np.uint32)
+    st = [np.array(a, dtype=np.float64).copy() for a in (r, v, q, L, F, M)]
+    series = np.zeros((steps, 4))
+    gl = (C.c_double * 3)(*global_len)
+    rc = lib().o_run(C.byref(sysm.params), C.byref(g), gl, C.c_size_t(len(cid)), _p(cid), *[_p(a) for a in st],
+                     int(steps), C.c_double(dt), C.c_double(target_T), _p(series))
+    assert rc == 0
+    return dict(r=st[0], v=st[1], q=st[2], L=st[3], F=st[4], M=st[5], series=series)
