@@ -167,8 +167,15 @@ int ls1g_decomp_grid(int n_ranks, int rank, int rank_grid[3], int rank_coords[3]
  * replaces: MPI_Cart_create + CommunicationPartner set-up (DomainDecomposition.cpp:36, DomainDecompMPIBase.cpp:148-170) */
 int ls1g_comm_unique_id(unsigned char id[128]);
 int ls1g_comm_init(ls1g_ctx* ctx, int n_ranks, int rank, const unsigned char id[128]);
-/* replaces: Domain::calculateGlobalValues collComm allreduce (Domain.cpp:170-176,214-224): sums 6 doubles in place */
+/* replaces: Domain::calculateGlobalValues collComm allreduce (Domain.cpp:170-176,214-224): sums up to 8 doubles in place */
 int ls1g_allreduce_sum(ls1g_ctx* ctx, double* values, int n);
+/* In-process transport: all ranks are contexts of THIS process (ordered by rank), records move by device copies.
+ * Exercises the same pack / stage / unpack kernels as the NCCL path on any number of GPUs >= 1 (tests).
+ * replaces: the sequential fall-back of the reference when MPI is absent (DomainDecompBase) only in spirit;
+ * the exchanged regions are those of NeighbourCommunicationScheme.cpp:500-600. */
+int ls1g_comm_init_local(ls1g_ctx** ctxs, int n);
+/* one leaving+halo exchange of all local ranks in lockstep (= ls1g_exchange on every rank) */
+int ls1g_exchange_group(ls1g_ctx** ctxs, int n);
 
 /* --- measurement -------------------------------------------------------------------------- */
 enum { LS1G_T_FORCE = 0, LS1G_T_SORT = 1, LS1G_T_INTEGRATE = 2, LS1G_T_EXCHANGE = 3, LS1G_T_COUNT = 4 };

@@ -1,0 +1,440 @@
+// api.cu — the C ABI declared in include/ls1g.h: context life cycle, parameter tables, storage, the per-step
+// operators and the device-resident time loop.  Kernels are in cells.cu / force*.cu / integrate.cu / comm.cu.
+#include "ls1g_internal.cuh"
+
+#include <math.h>
+#include <string.h>
+#include <algorithm>
+#include <mutex>
+
+static thread_local std::string g_err;
+void ls1g_set_error(const std::string& msg) { g_err = msg; }
+extern "C" const char* ls1g_last_error(void) { return g_err.c_str(); }
+extern "C" int ls1g_version(void) { return 100; }
+
+
+// ------------------------------------------------------------------------------------------------
+// timers: event pairs are queued and resolved lazily (no host sync inside the step)
+// ------------------------------------------------------------------------------------------------
+static std::vector<PendingEvt>& pending(ls1g_ctx* c) { return c->pending; }
+static std::vector<cudaEvent_t>& evpool(ls1g_ctx* c) { return c->evpool; }
+
+static cudaEvent_t get_event(ls1g_ctx* c) {
+	auto& pool = evpool(c);
+	if (!pool.empty()) { cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
+	cudaEvent_t e; cudaEventCreate(&e); return e;
+}
+static void resolve_timers(ls1g_ctx* c) {
+	auto& p = pending(c);
+	for (auto& e : p) {
+		if (!e.b) { evpool(c).push_back(e.a); continue; }
+		cudaEventSynchronize(e.b);
+		float ms = 0.f;
+		if (cudaEventElapsedTime(&ms, e.a, e.b) == cudaSuccess) { c->timers[e.which].ms += ms; c->timers[e.which].launches += e.launches; }
+		evpool(c).push_back(e.a); evpool(c).push_back(e.b);
+	}
+	p.clear();
+}
+void ls1g_resolve_timers(ls1g_ctx* c) { resolve_timers(c); }
+void timer_start(ls1g_ctx* c, int which) {
+	if (pending(c).size() > 8192) resolve_timers(c);
+	PendingEvt e; e.a = get_event(c); e.b = nullptr; e.which = which; e.launches = 0;
+	cudaEventRecord(e.a, c->stream);
+	pending(c).push_back(e);
+}
+void timer_stop(ls1g_ctx* c, int which, int launches) {
+	auto& p = pending(c);
+	for (size_t k = p.size(); k-- > 0;)
+		if (p[k].which == which && !p[k].b) { p[k].b = get_event(c); p[k].launches = launches; cudaEventRecord(p[k].b, c->stream); break; }
+}
+
+// ------------------------------------------------------------------------------------------------
+// grid geometry: LinkedCells::rebuild (LinkedCells.cpp:136-204, float rc) / constructor (:42-107, double rc)
+// ------------------------------------------------------------------------------------------------
+static int grid_init(Grid& g, const ls1g_config& cfg) {
+	memset(&g, 0, sizeof(g));
+	g.cutoff = cfg.cutoff;
+	long ncell = 1;
+	for (int d = 0; d < 3; ++d) {
+		g.box_min[d] = cfg.box_min[d]; g.box_max[d] = cfg.box_max[d];
+		double diff = cfg.box_max[d] - cfg.box_min[d];
+		int n;
+		if (cfg.grid_mode == LS1G_GRID_CTOR) {
+			n = (int)floor(diff / cfg.cutoff);            // LinkedCells.cpp:53-54
+			if (n == 0) n = 1;                            // :56-58
+		} else {
+			float rcf = (float)(cfg.cutoff / 1);          // :152 float rc = _cutoffRadius / _cellsInCutoff
+			n = (int)floor(diff / rcf);                   // :155
+			if (n == 0) LS1G_FAIL("ls1g_create: bounding box too small for the cutoff (LinkedCells.cpp:160-163)");
+		}
+		g.cpd[d] = n + 2;
+		g.cell_len[d] = diff / n;                         // :168
+		g.cell_len_recip[d] = n / diff;                   // :169
+		g.halo_min[d] = cfg.box_min[d] - g.cell_len[d];
+		g.halo_max[d] = cfg.box_max[d] + g.cell_len[d];
+		g.box_len[d] = diff;
+		g.self_periodic[d] = cfg.rank_grid[d] <= 1 ? 1 : 0;
+		ncell *= g.cpd[d];
+	}
+	if (ncell > 0x7fffffffL - 8) LS1G_FAIL("ls1g_create: too many cells");
+	g.n_cells = (int)ncell;
+	return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// life cycle
+// ------------------------------------------------------------------------------------------------
+static void free_molecules(ls1g_ctx* c) {
+	MolBuf* bufs[2] = {&c->cur, &c->alt};
+	for (MolBuf* b : bufs) {
+		cudaFree(b->pos); cudaFree(b->vel); cudaFree(b->q); cudaFree(b->L); cudaFree(b->id); cudaFree(b->cell);
+		memset(b, 0, sizeof(MolBuf));
+	}
+	cudaFree(c->F); cudaFree(c->M); cudaFree(c->Vi); cudaFree(c->F_alt); cudaFree(c->M_alt); cudaFree(c->site_cache);
+	cudaFree(c->slot_src); cudaFree(c->slot_code); cudaFree(c->slot_key); cudaFree(c->slot_cell);
+	c->F = c->M = c->Vi = c->F_alt = c->M_alt = nullptr; c->site_cache = nullptr;
+	c->slot_src = nullptr; c->slot_code = nullptr; c->slot_key = nullptr; c->slot_cell = nullptr;
+	c->cap = 0;
+}
+
+static int alloc_molecules(ls1g_ctx* c, size_t cap) {
+	free_molecules(c);
+	if (cap >= 0x7fffff00ull) LS1G_FAIL("ls1g: more than 2^31 slots per GPU are not supported");
+	MolBuf* bufs[2] = {&c->cur, &c->alt};
+	for (MolBuf* b : bufs) {
+		CUDA_TRY(cudaMalloc((void**)&b->pos, cap * sizeof(double4)));
+		CUDA_TRY(cudaMalloc((void**)&b->vel, cap * 3 * sizeof(double)));
+		CUDA_TRY(cudaMalloc((void**)&b->id, cap * sizeof(uint64_t)));
+		CUDA_TRY(cudaMalloc((void**)&b->cell, cap * sizeof(uint32_t)));
+		if (c->has_rot) {
+			CUDA_TRY(cudaMalloc((void**)&b->q, cap * sizeof(double4)));
+			CUDA_TRY(cudaMalloc((void**)&b->L, cap * 3 * sizeof(double)));
+		}
+	}
+	CUDA_TRY(cudaMalloc((void**)&c->F, cap * 3 * sizeof(double)));
+	CUDA_TRY(cudaMalloc((void**)&c->Vi, cap * 3 * sizeof(double)));
+	CUDA_TRY(cudaMalloc((void**)&c->F_alt, cap * 3 * sizeof(double)));
+	CUDA_TRY(cudaMemset(c->F, 0, cap * 3 * sizeof(double)));
+	CUDA_TRY(cudaMemset(c->Vi, 0, cap * 3 * sizeof(double)));
+	if (c->has_rot) {
+		CUDA_TRY(cudaMalloc((void**)&c->M, cap * 3 * sizeof(double)));
+		CUDA_TRY(cudaMalloc((void**)&c->M_alt, cap * 3 * sizeof(double)));
+		CUDA_TRY(cudaMemset(c->M, 0, cap * 3 * sizeof(double)));
+		CUDA_TRY(cudaMalloc((void**)&c->site_cache, cap * (size_t)c->cache_stride * sizeof(double4)));
+	}
+	CUDA_TRY(cudaMalloc((void**)&c->slot_src, cap * sizeof(uint32_t)));
+	CUDA_TRY(cudaMalloc((void**)&c->slot_code, cap * sizeof(uint8_t)));
+	CUDA_TRY(cudaMalloc((void**)&c->slot_key, cap * sizeof(uint64_t)));
+	CUDA_TRY(cudaMalloc((void**)&c->slot_cell, cap * sizeof(uint32_t)));
+	c->cap = cap;
+	return 0;
+}
+
+extern "C" int ls1g_create(const ls1g_config* cfg, ls1g_ctx** out) {
+	if (!cfg || !out) LS1G_FAIL("ls1g_create: null argument");
+	int ndev = 0;
+	cudaError_t e = cudaGetDeviceCount(&ndev);
+	if (e != cudaSuccess || ndev == 0)
+		LS1G_FAIL(std::string("ls1g_create: no CUDA device available (there is no CPU fallback): ") + cudaGetErrorString(e));
+	if (cfg->device < 0 || cfg->device >= ndev) LS1G_FAIL("ls1g_create: invalid device ordinal");
+	CUDA_TRY(cudaSetDevice(cfg->device));
+	ls1g_ctx* c = new ls1g_ctx();
+	// zero the POD part
+	c->cfg = *cfg;
+	for (int d = 0; d < 3; ++d) if (c->cfg.rank_grid[d] < 1) c->cfg.rank_grid[d] = 1;
+	if (c->cfg.lj_cutoff <= 0) c->cfg.lj_cutoff = c->cfg.cutoff;
+	c->stream = nullptr;
+	c->n_comp = 0; c->n_site_rows = 0; c->S_lj = 0; c->max_sites = 0; c->has_rot = 0; c->simple_1clj = 0;
+	c->comps = nullptr; c->sites = nullptr; c->eps24 = c->sig2 = c->shift6 = nullptr;
+	c->cap = c->n_slots = c->n_owned = c->n_halo = 0; c->sorted = 0; c->forces_valid = 0;
+	memset(&c->cur, 0, sizeof(MolBuf)); memset(&c->alt, 0, sizeof(MolBuf));
+	c->F = c->M = c->Vi = c->F_alt = c->M_alt = nullptr; c->site_cache = nullptr; c->cache_stride = 1;
+	c->cell_count = c->cell_fill = c->cell_start = c->scan_block = nullptr;
+	c->slot_src = nullptr; c->slot_code = nullptr; c->slot_key = nullptr; c->slot_cell = nullptr;
+	c->d_counters = c->h_counters = nullptr;
+	c->partials = nullptr; c->partials_cap = 0; c->d_scalars = c->h_scalars = nullptr; c->d_pairs = nullptr; c->last_pairs = 0;
+	c->nccl_comm = nullptr; c->n_ranks = 1; c->rank = 0; c->comm_mode = 0;
+	c->send_buf[0] = c->send_buf[1] = c->recv_buf[0] = c->recv_buf[1] = nullptr; c->xbuf_cap = 0;
+	memset(c->timers, 0, sizeof(c->timers));
+	if (grid_init(c->grid, c->cfg)) { delete c; return 1; }
+	c->rc2 = c->cfg.cutoff * c->cfg.cutoff;
+	c->rclj2 = c->cfg.lj_cutoff * c->cfg.lj_cutoff;
+	// VectorizedCellProcessor.cpp:24
+	c->epsRFInvrc3 = 2. * (c->cfg.eps_rf - 1.) / ((c->cfg.cutoff * c->cfg.cutoff * c->cfg.cutoff) * (2. * c->cfg.eps_rf + 1.));
+	CUDA_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+	size_t nc = (size_t)c->grid.n_cells + 1;
+	CUDA_TRY(cudaMalloc((void**)&c->cell_count, nc * sizeof(uint32_t)));
+	CUDA_TRY(cudaMalloc((void**)&c->cell_fill, nc * sizeof(uint32_t)));
+	CUDA_TRY(cudaMalloc((void**)&c->cell_start, (nc + 8) * sizeof(uint32_t)));
+	CUDA_TRY(cudaMemset(c->cell_start, 0, (nc + 8) * sizeof(uint32_t)));
+	CUDA_TRY(cudaMalloc((void**)&c->scan_block, (nc / 2048 + 8) * sizeof(uint32_t)));
+	CUDA_TRY(cudaMalloc((void**)&c->d_counters, 8 * sizeof(uint32_t)));
+	CUDA_TRY(cudaMallocHost((void**)&c->h_counters, 8 * sizeof(uint32_t)));
+	CUDA_TRY(cudaMalloc((void**)&c->d_scalars, 16 * sizeof(double)));
+	CUDA_TRY(cudaMemset(c->d_scalars, 0, 16 * sizeof(double)));
+	CUDA_TRY(cudaMallocHost((void**)&c->h_scalars, 16 * sizeof(double)));
+	*out = c;
+	return 0;
+}
+
+extern "C" int ls1g_destroy(ls1g_ctx* c) {
+	if (!c) return 0;
+	cudaSetDevice(c->cfg.device);
+	if (c->stream) cudaStreamSynchronize(c->stream);
+	resolve_timers(c);
+	comm_destroy(c);
+	for (cudaEvent_t e : evpool(c)) cudaEventDestroy(e);
+	free_molecules(c);
+	cudaFree(c->comps); cudaFree(c->sites); cudaFree(c->eps24); cudaFree(c->sig2); cudaFree(c->shift6);
+	cudaFree(c->cell_count); cudaFree(c->cell_fill); cudaFree(c->cell_start); cudaFree(c->scan_block);
+	cudaFree(c->d_counters); cudaFreeHost(c->h_counters); cudaFree(c->partials); cudaFree(c->d_scalars); cudaFreeHost(c->h_scalars);
+	for (int k = 0; k < 2; ++k) { cudaFree(c->send_buf[k]); cudaFree(c->recv_buf[k]); }
+	if (c->stream) cudaStreamDestroy(c->stream);
+	delete c;
+	return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// components + mixing tables (Comp2Param::initialize, Comp2Param.cpp:10-100; VCP ctor :21-98)
+// ------------------------------------------------------------------------------------------------
+extern "C" int ls1g_set_components(ls1g_ctx* c, int nc, const ls1g_component* comps, const double* mix, int n_mix) {
+	if (!c || nc <= 0 || !comps) LS1G_FAIL("ls1g_set_components: bad arguments");
+	if (n_mix < nc * (nc - 1)) LS1G_FAIL("ls1g_set_components: mixcoeff needs (xi,eta) for every component pair i<j");
+	CUDA_TRY(cudaSetDevice(c->cfg.device));
+	c->comps_h.clear(); c->sites_h.clear();
+	int S = 0, max_rows = 1;
+	for (int k = 0; k < nc; ++k) {
+		const ls1g_component& in = comps[k];
+		CompDev cd; memset(&cd, 0, sizeof(cd));
+		cd.mass = in.mass;
+		for (int d = 0; d < 3; ++d) { cd.I[d] = in.inertia[d]; cd.invI[d] = in.inertia[d] != 0. ? 1. / in.inertia[d] : 0.; }  // FullMolecule.h:88-101
+		cd.rot_dof = in.rot_dof;
+		cd.n_lj = in.n_lj; cd.n_ch = in.n_charge; cd.n_di = in.n_dipole; cd.n_qu = in.n_quadrupole;
+		cd.lj_id0 = S; cd.site0 = (int)c->sites_h.size();
+		cd.n_sites = cd.n_lj + cd.n_ch + cd.n_di + cd.n_qu;
+		for (int a = 0; a < in.n_lj; ++a) {
+			SiteDev s; memset(&s, 0, sizeof(s)); const double* r = in.lj + 7 * a;
+			s.d[0] = r[0]; s.d[1] = r[1]; s.d[2] = r[2]; s.type = SITE_LJ; s.ljid = S + a; c->sites_h.push_back(s);
+		}
+		for (int a = 0; a < in.n_charge; ++a) {
+			SiteDev s; memset(&s, 0, sizeof(s)); const double* r = in.charge + 5 * a;
+			s.d[0] = r[0]; s.d[1] = r[1]; s.d[2] = r[2]; s.val = r[4]; s.type = SITE_CH; c->sites_h.push_back(s);
+		}
+		for (int a = 0; a < in.n_dipole; ++a) {
+			SiteDev s; memset(&s, 0, sizeof(s)); const double* r = in.dipole + 7 * a;
+			for (int d = 0; d < 3; ++d) { s.d[d] = r[d]; s.e[d] = r[3 + d]; } s.val = r[6]; s.type = SITE_DI; c->sites_h.push_back(s);
+		}
+		for (int a = 0; a < in.n_quadrupole; ++a) {
+			SiteDev s; memset(&s, 0, sizeof(s)); const double* r = in.quadrupole + 7 * a;
+			for (int d = 0; d < 3; ++d) { s.d[d] = r[d]; s.e[d] = r[3 + d]; } s.val = r[6]; s.type = SITE_QU; c->sites_h.push_back(s);
+		}
+		S += in.n_lj;
+		max_rows = std::max(max_rows, cd.n_lj + cd.n_ch + 2 * cd.n_di + 2 * cd.n_qu);
+		c->comps_h.push_back(cd);
+	}
+	c->n_comp = nc; c->S_lj = S; c->cache_stride = max_rows; c->n_site_rows = (int)c->sites_h.size();
+	// LJ tables indexed by global LJ-site id
+	size_t SS = (size_t)std::max(S, 1) * std::max(S, 1);
+	c->eps24_h.assign(SS, 0.); c->sig2_h.assign(SS, 0.); c->shift6_h.assign(SS, 0.);
+	const double rclj = c->cfg.lj_cutoff;
+	int mixpos = 0;
+	for (int ci = 0; ci < nc; ++ci) {
+		const ls1g_component& A = comps[ci]; int oi = c->comps_h[ci].lj_id0;
+		for (int a = 0; a < A.n_lj; ++a)                                            // Comp2Param.cpp:24-41
+			for (int b = 0; b < A.n_lj; ++b) {
+				const double *si = A.lj + 7 * a, *sj = A.lj + 7 * b;
+				double s2 = .5 * (si[5] + sj[5]); s2 *= s2;
+				size_t k = (size_t)(oi + a) * S + (oi + b);
+				c->eps24_h[k] = 24. * sqrt(si[4] * sj[4]); c->sig2_h[k] = s2; c->shift6_h[k] = si[6];
+			}
+		for (int cj = ci + 1; cj < nc; ++cj) {                                      // :43-98
+			const ls1g_component& B = comps[cj]; int oj = c->comps_h[cj].lj_id0;
+			double xi = mix[mixpos++], eta = mix[mixpos++];
+			for (int a = 0; a < A.n_lj; ++a)
+				for (int b = 0; b < B.n_lj; ++b) {
+					const double *si = A.lj + 7 * a, *sj = B.lj + 7 * b;
+					double e24 = 24. * xi * sqrt(si[4] * sj[4]);
+					double s2 = eta * .5 * (si[5] + sj[5]); s2 *= s2;
+					double sr2 = s2 / (rclj * rclj), sr6 = sr2 * sr2 * sr2;
+					double sh = e24 * (sr6 - sr6 * sr6);
+					size_t k = (size_t)(oi + a) * S + (oj + b), kt = (size_t)(oj + b) * S + (oi + a);
+					c->eps24_h[k] = e24; c->sig2_h[k] = s2; c->shift6_h[k] = sh;
+					c->eps24_h[kt] = e24; c->sig2_h[kt] = s2; c->shift6_h[kt] = sh;
+				}
+		}
+	}
+	const CompDev& c0 = c->comps_h[0];
+	const SiteDev* s0 = c->sites_h.empty() ? nullptr : &c->sites_h[0];
+	c->simple_1clj = (nc == 1 && c0.n_lj == 1 && c0.n_ch == 0 && c0.n_di == 0 && c0.n_qu == 0 && c0.rot_dof == 0 &&
+	                  s0->d[0] == 0. && s0->d[1] == 0. && s0->d[2] == 0.);
+	c->has_rot = !c->simple_1clj;
+	cudaFree(c->comps); cudaFree(c->sites); cudaFree(c->eps24); cudaFree(c->sig2); cudaFree(c->shift6);
+	CUDA_TRY(cudaMalloc((void**)&c->comps, nc * sizeof(CompDev)));
+	CUDA_TRY(cudaMalloc((void**)&c->sites, std::max<size_t>(1, c->sites_h.size()) * sizeof(SiteDev)));
+	CUDA_TRY(cudaMalloc((void**)&c->eps24, SS * sizeof(double)));
+	CUDA_TRY(cudaMalloc((void**)&c->sig2, SS * sizeof(double)));
+	CUDA_TRY(cudaMalloc((void**)&c->shift6, SS * sizeof(double)));
+	CUDA_TRY(cudaMemcpy(c->comps, c->comps_h.data(), nc * sizeof(CompDev), cudaMemcpyHostToDevice));
+	if (!c->sites_h.empty()) CUDA_TRY(cudaMemcpy(c->sites, c->sites_h.data(), c->sites_h.size() * sizeof(SiteDev), cudaMemcpyHostToDevice));
+	CUDA_TRY(cudaMemcpy(c->eps24, c->eps24_h.data(), SS * sizeof(double), cudaMemcpyHostToDevice));
+	CUDA_TRY(cudaMemcpy(c->sig2, c->sig2_h.data(), SS * sizeof(double), cudaMemcpyHostToDevice));
+	CUDA_TRY(cudaMemcpy(c->shift6, c->shift6_h.data(), SS * sizeof(double), cudaMemcpyHostToDevice));
+	free_molecules(c);   // storage layout depends on has_rot / cache_stride
+	c->n_slots = c->n_owned = c->n_halo = 0; c->sorted = 0; c->forces_valid = 0;
+	return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// grid queries
+// ------------------------------------------------------------------------------------------------
+extern "C" int ls1g_get_grid(const ls1g_ctx* c, int cells_per_dim[3], double cell_length[3]) {
+	if (!c) LS1G_FAIL("null context");
+	for (int d = 0; d < 3; ++d) { cells_per_dim[d] = c->grid.cpd[d]; cell_length[d] = c->grid.cell_len[d]; }
+	return 0;
+}
+extern "C" int ls1g_cell_index_of_points_host(const ls1g_ctx* c, size_t n, const double* pts, uint32_t* out) {
+	if (!c) LS1G_FAIL("null context");
+	for (size_t i = 0; i < n; ++i) out[i] = grid_cell_index(c->grid, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2]);
+	return 0;
+}
+extern "C" int ls1g_cell_index_of_points(ls1g_ctx* c, size_t n, const double* pts, uint32_t* out) {
+	if (!c) LS1G_FAIL("null context");
+	if (n == 0) return 0;
+	CUDA_TRY(cudaSetDevice(c->cfg.device));
+	double* d_p = nullptr; uint32_t* d_o = nullptr;
+	CUDA_TRY(cudaMalloc((void**)&d_p, n * 3 * sizeof(double)));
+	CUDA_TRY(cudaMalloc((void**)&d_o, n * sizeof(uint32_t)));
+	int rc = 0;
+	if (cudaMemcpyAsync(d_p, pts, n * 3 * sizeof(double), cudaMemcpyHostToDevice, c->stream) != cudaSuccess) rc = 1;
+	if (!rc) rc = k_cell_index(c, n, d_p, d_o);
+	if (!rc && cudaMemcpyAsync(out, d_o, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess) rc = 1;
+	cudaError_t e = cudaStreamSynchronize(c->stream);
+	cudaFree(d_p); cudaFree(d_o);
+	if (e != cudaSuccess) { ls1g_set_error(std::string("cell index kernel: ") + cudaGetErrorString(e)); return 1; }
+	return rc;
+}
+extern "C" int ls1g_debug_cell_pairs(const ls1g_ctx* c, uint32_t* triplets, size_t capacity, size_t* n_out) {
+	if (!c || !n_out) LS1G_FAIL("null argument");
+	CUDA_TRY(cudaSetDevice(c->cfg.device));
+	return k_debug_cell_pairs(c, triplets, capacity, n_out);
+}
+
+// ------------------------------------------------------------------------------------------------
+// storage
+// ------------------------------------------------------------------------------------------------
+static size_t default_capacity(const ls1g_ctx* c, size_t n) {
+	// halo copies live in the shell of halo cells: N * (cells incl. halo / real cells - 1), with head room
+	double tot = 1., real = 1.;
+	for (int d = 0; d < 3; ++d) { tot *= c->grid.cpd[d]; real *= (c->grid.cpd[d] - 2); }
+	double est = (double)n * (tot / real - 1.) * 1.3 + 4096;
+	double hard = 27.0 * (double)n + 64;
+	return n + (size_t)std::min(est, hard) + (size_t)(0.05 * n);
+}
+
+extern "C" int ls1g_upload(ls1g_ctx* c, size_t n, const uint64_t* id, const uint32_t* cid,
+                           const double* r, const double* v, const double* q, const double* L) {
+	if (!c) LS1G_FAIL("null context");
+	if (c->n_comp == 0) LS1G_FAIL("ls1g_upload: call ls1g_set_components first");
+	if (n && (!id || !cid || !r)) LS1G_FAIL("ls1g_upload: id, cid and r are required");
+	CUDA_TRY(cudaSetDevice(c->cfg.device));
+	size_t want = c->cfg.capacity ? (size_t)c->cfg.capacity : default_capacity(c, n);
+	if (want < n) LS1G_FAIL("ls1g_upload: more molecules than the configured capacity");
+	if (c->cap < want || c->cap == 0) { if (alloc_molecules(c, std::max<size_t>(want, 1))) return 1; }
+	for (size_t i = 0; i < n; ++i) if (cid[i] >= (uint32_t)c->n_comp) LS1G_FAIL("ls1g_upload: component id out of range");
+	// stage through pinned memory in the device layout
+	double4* h_pos = nullptr; double4* h_q = nullptr;
+	CUDA_TRY(cudaMallocHost((void**)&h_pos, std::max<size_t>(n, 1) * sizeof(double4)));
+	for (size_t i = 0; i < n; ++i) {
+		h_pos[i].x = r[3 * i]; h_pos[i].y = r[3 * i + 1]; h_pos[i].z = r[3 * i + 2];
+		long long bits = (long long)cid[i]; memcpy(&h_pos[i].w, &bits, 8);
+	}
+	cudaError_t e = cudaMemcpyAsync(c->cur.pos, h_pos, n * sizeof(double4), cudaMemcpyHostToDevice, c->stream);
+	if (e == cudaSuccess && v) e = cudaMemcpyAsync(c->cur.vel, v, n * 3 * sizeof(double), cudaMemcpyHostToDevice, c->stream);
+	if (e == cudaSuccess && !v) e = cudaMemsetAsync(c->cur.vel, 0, n * 3 * sizeof(double), c->stream);
+	if (e == cudaSuccess) e = cudaMemcpyAsync(c->cur.id, id, n * sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream);
+	if (e == cudaSuccess) e = cudaMemsetAsync(c->cur.cell, 0, n * sizeof(uint32_t), c->stream);
+	if (e == cudaSuccess && c->has_rot) {
+		e = cudaMallocHost((void**)&h_q, std::max<size_t>(n, 1) * sizeof(double4));
+		if (e == cudaSuccess) {
+			for (size_t i = 0; i < n; ++i) {
+				if (q) { h_q[i].x = q[4 * i]; h_q[i].y = q[4 * i + 1]; h_q[i].z = q[4 * i + 2]; h_q[i].w = q[4 * i + 3]; }
+				else { h_q[i].x = 1.; h_q[i].y = h_q[i].z = h_q[i].w = 0.; }
+			}
+			e = cudaMemcpyAsync(c->cur.q, h_q, n * sizeof(double4), cudaMemcpyHostToDevice, c->stream);
+		}
+		if (e == cudaSuccess && L) e = cudaMemcpyAsync(c->cur.L, L, n * 3 * sizeof(double), cudaMemcpyHostToDevice, c->stream);
+		if (e == cudaSuccess && !L) e = cudaMemsetAsync(c->cur.L, 0, n * 3 * sizeof(double), c->stream);
+		if (e == cudaSuccess) e = cudaMemsetAsync(c->M, 0, n * 3 * sizeof(double), c->stream);
+	}
+	if (e == cudaSuccess) e = cudaMemsetAsync(c->F, 0, n * 3 * sizeof(double), c->stream);
+	if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+	cudaFreeHost(h_pos); if (h_q) cudaFreeHost(h_q);
+	if (e != cudaSuccess) LS1G_FAIL(std::string("ls1g_upload: ") + cudaGetErrorString(e));
+	c->n_slots = c->n_owned = n; c->n_halo = 0; c->sorted = 0; c->forces_valid = 0;
+	return 0;
+}
+
+extern "C" int ls1g_count(ls1g_ctx* c, uint64_t* n_owned, uint64_t* n_halo) {
+	if (!c) LS1G_FAIL("null context");
+	if (n_owned) *n_owned = c->n_owned;
+	if (n_halo) *n_halo = c->n_halo;
+	return 0;
+}
+
+extern "C" int ls1g_download(ls1g_ctx* c, int mask, int include_halo, size_t capacity, ls1g_fields* out, size_t* n_out) {
+	if (!c || !out || !n_out) LS1G_FAIL("null argument");
+	CUDA_TRY(cudaSetDevice(c->cfg.device));
+	size_t ns = c->n_slots;
+	bool halo_ok = include_halo && c->n_halo > 0;
+	size_t n_ret = halo_ok ? c->n_owned + c->n_halo : c->n_owned;
+	*n_out = n_ret;
+	if (capacity < n_ret) LS1G_FAIL("ls1g_download: capacity too small");
+	if (ns == 0) return 0;
+	std::vector<uint32_t> cell(ns);
+	std::vector<double4> p4;
+	std::vector<double> tmp;
+	std::vector<uint64_t> tid;
+	CUDA_TRY(cudaStreamSynchronize(c->stream));
+	CUDA_TRY(cudaMemcpy(cell.data(), c->cur.cell, ns * sizeof(uint32_t), cudaMemcpyDeviceToHost));
+	std::vector<uint32_t> keep; keep.reserve(n_ret);
+	for (size_t s = 0; s < ns; ++s) if (halo_ok || !(cell[s] & HALO_FLAG)) keep.push_back((uint32_t)s);
+	if (keep.size() != n_ret) LS1G_FAIL("ls1g_download: internal slot bookkeeping mismatch");
+	if ((mask & (LS1G_F_R | LS1G_F_CID))) {
+		p4.resize(ns);
+		CUDA_TRY(cudaMemcpy(p4.data(), c->cur.pos, ns * sizeof(double4), cudaMemcpyDeviceToHost));
+		for (size_t k = 0; k < n_ret; ++k) {
+			const double4& p = p4[keep[k]];
+			if ((mask & LS1G_F_R) && out->r) { out->r[3 * k] = p.x; out->r[3 * k + 1] = p.y; out->r[3 * k + 2] = p.z; }
+			if ((mask & LS1G_F_CID) && out->cid) { long long b; memcpy(&b, &p.w, 8); out->cid[k] = (uint32_t)b; }
+		}
+	}
+	if ((mask & LS1G_F_ID) && out->id) {
+		tid.resize(ns);
+		CUDA_TRY(cudaMemcpy(tid.data(), c->cur.id, ns * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+		for (size_t k = 0; k < n_ret; ++k) out->id[k] = tid[keep[k]];
+	}
+	if ((mask & LS1G_F_CELL) && out->cell)
+		for (size_t k = 0; k < n_ret; ++k) out->cell[k] = c->sorted ? (cell[keep[k]] & ~HALO_FLAG) : 0u;
+	auto get3 = [&](const double* dev, double* dst) -> int {
+		if (!dst) return 0;
+		if (!dev) { for (size_t k = 0; k < 3 * n_ret; ++k) dst[k] = 0.; return 0; }
+		tmp.resize(ns * 3);
+		CUDA_TRY(cudaMemcpy(tmp.data(), dev, ns * 3 * sizeof(double), cudaMemcpyDeviceToHost));
+		for (size_t k = 0; k < n_ret; ++k) for (int d = 0; d < 3; ++d) dst[3 * k + d] = tmp[3 * (size_t)keep[k] + d];
+		return 0;
+	};
+	if ((mask & LS1G_F_V) && get3(c->cur.vel, out->v)) return 1;
+	if ((mask & LS1G_F_L) && get3(c->has_rot ? c->cur.L : nullptr, out->L)) return 1;
+	if ((mask & LS1G_F_F) && get3(c->F, out->F)) return 1;
+	if ((mask & LS1G_F_M) && get3(c->has_rot ? c->M : nullptr, out->M)) return 1;
+	if ((mask & LS1G_F_VI) && get3(c->Vi, out->Vi)) return 1;
+	if ((mask & LS1G_F_Q) && out->q) {
+		if (c->has_rot) {
+			p4.resize(ns);
+			CUDA_TRY(cudaMemcpy(p4.data(), c->cur.q, ns * sizeof(double4), cudaMemcpyDeviceToHost));
+			for (size_t k = 0; k < n_ret; ++k) { const double4& p = p4[keep[k]]; out->q[4 * k] = p.x; out->q[4 * k + 1] = p.y; out->q[4 * k + 2] = p.z; out->q[4 * k + 3] = p.w; }
+		} else
+			for (size_t k = 0; k < n_ret; ++k) { out->q[4 * k] = 1.; out->q[4 * k + 1] = out->q[4 * k + 2] = out->q[4 * k + 3] = 0.; }
+	}
+	return 0;
+}

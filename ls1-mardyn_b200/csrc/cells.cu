@@ -1,0 +1,373 @@
+// cells.cu — cell assignment, periodic images and the device counting sort.
+//
+// Replaces (reference, src/):
+//   LinkedCells::getCellIndexOfPoint / update            particleContainer/LinkedCells.cpp:243-356,830-882
+//   DomainDecompBase::handleDomainLeavingParticles       parallel/DomainDecompBase.cpp:174-225
+//   DomainDecompBase::populateHaloLayerWithCopies        parallel/DomainDecompBase.cpp:293-348
+//   C08CellPairTraversal / C08BasedTraversals            particleContainer/LinkedCellTraversals/*.h (enumeration dump)
+//
+// Pipeline of one re-sort (k_sort):
+//   bin      per molecule: wrap leavers, cell index (bit-exact), count self + periodic images per cell
+//   scan     exclusive prefix over the cell histogram -> cell_start
+//   scatter  claim a slot in the target cell for self + every image (atomic rank; order fixed later)
+//   gather   per new slot: rank inside the cell by molecule id (deterministic order), copy the payload
+//            from the old buffer, applying the image shift.  cur/alt are swapped afterwards.
+// All four are HBM-bound; algorithmic bytes per molecule are listed in DESIGN.md.
+#include "ls1g_internal.cuh"
+
+#include <algorithm>
+
+// ------------------------------------------------------------------------------------------------
+// periodic image helpers
+// ------------------------------------------------------------------------------------------------
+// option o in {1: lower slab, shift +L ; 2: upper slab, shift -L}; returns true if coordinate x of dimension d
+// lies in that slab (Molecule::inBox on [lo,hi), DomainDecompBase.cpp:300-325).
+__device__ __forceinline__ bool in_slab(const Grid& g, int d, int o, double x) {
+	double lo = o == 1 ? g.box_min[d] : __dsub_rn(g.box_max[d], g.cutoff);
+	double hi = o == 1 ? __dadd_rn(g.box_min[d], g.cutoff) : g.box_max[d];
+	return x >= lo && x < hi;
+}
+// shifted coordinate of the halo copy incl. the "must land outside the box" guards (DomainDecompBase.cpp:326-341)
+__device__ __forceinline__ double image_coord(const Grid& g, int d, int o, double x) {
+	if (o == 1) {
+		double y = __dadd_rn(x, g.box_len[d]);
+		if (y < g.box_max[d]) y = nextafter(g.box_max[d], g.box_max[d] + 1.0);
+		return y;
+	} else {
+		double y = __dsub_rn(x, g.box_len[d]);
+		if (y >= g.box_min[d]) y = nextafter(g.box_min[d], g.box_min[d] - 1.0);
+		return y;
+	}
+}
+// leaving molecules on a self-periodic dimension (DomainDecompBase.cpp:196-221)
+__device__ __forceinline__ double wrap_coord(const Grid& g, int d, double x) {
+	if (x < g.box_min[d]) {
+		x = __dadd_rn(x, g.box_len[d]);
+		if (x >= g.box_max[d]) x = nextafter(g.box_max[d], g.box_max[d] - 1.0);
+	} else if (x >= g.box_max[d]) {
+		x = __dsub_rn(x, g.box_len[d]);
+		if (x <= g.box_min[d]) x = g.box_min[d];
+	}
+	return x;
+}
+
+// Enumerates the periodic images of an owned molecule at p.  f(code, x, y, z) is called for every image;
+// code = o0 + 3*o1 + 9*o2 with o_d in {0 none, 1 +L, 2 -L}; code 0 (the molecule itself) is not visited.
+template <class F>
+__device__ __forceinline__ void for_each_image(const Grid& g, double px, double py, double pz, F f) {
+	double p[3] = {px, py, pz};
+	bool opt[3][3];
+#pragma unroll
+	for (int d = 0; d < 3; ++d) {
+		opt[d][0] = true;
+		opt[d][1] = g.self_periodic[d] && in_slab(g, d, 1, p[d]);
+		opt[d][2] = g.self_periodic[d] && in_slab(g, d, 2, p[d]);
+	}
+	if (!(opt[0][1] | opt[0][2] | opt[1][1] | opt[1][2] | opt[2][1] | opt[2][2])) return;
+	for (int o2 = 0; o2 < 3; ++o2) {
+		if (!opt[2][o2]) continue;
+		double z = o2 ? image_coord(g, 2, o2, p[2]) : p[2];
+		for (int o1 = 0; o1 < 3; ++o1) {
+			if (!opt[1][o1]) continue;
+			double y = o1 ? image_coord(g, 1, o1, p[1]) : p[1];
+			for (int o0 = 0; o0 < 3; ++o0) {
+				if (!opt[0][o0] || (o0 | o1 | o2) == 0) continue;
+				double x = o0 ? image_coord(g, 0, o0, p[0]) : p[0];
+				f(o0 + 3 * o1 + 9 * o2, x, y, z);
+			}
+		}
+	}
+}
+
+__device__ __forceinline__ void image_pos(const Grid& g, int code, double& x, double& y, double& z) {
+	int o0 = code % 3, o1 = (code / 3) % 3, o2 = code / 9;
+	if (o0) x = image_coord(g, 0, o0, x);
+	if (o1) y = image_coord(g, 1, o1, y);
+	if (o2) z = image_coord(g, 2, o2, z);
+}
+
+// ------------------------------------------------------------------------------------------------
+// kernels
+// ------------------------------------------------------------------------------------------------
+__global__ void cell_index_kernel(Grid g, size_t n, const double* __restrict__ pts, uint32_t* __restrict__ out) {
+	size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	out[i] = grid_cell_index(g, pts[3 * i], pts[3 * i + 1], pts[3 * i + 2]);
+}
+
+// bin: cell[] holds HALO_FLAG for stale halo copies (skipped, marked 0xFFFFFFFF).
+__global__ void __launch_bounds__(256) bin_kernel(Grid g, size_t n, double4* __restrict__ pos, uint32_t* __restrict__ cell,
+                                                   uint32_t* __restrict__ count, int make_images) {
+	size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	uint32_t c0 = cell[i];
+	if (c0 & HALO_FLAG) { cell[i] = 0xFFFFFFFFu; return; }
+	double4 p = pos[i];
+	if (make_images) {
+		double x = g.self_periodic[0] ? wrap_coord(g, 0, p.x) : p.x;
+		double y = g.self_periodic[1] ? wrap_coord(g, 1, p.y) : p.y;
+		double z = g.self_periodic[2] ? wrap_coord(g, 2, p.z) : p.z;
+		if (x != p.x || y != p.y || z != p.z) { p.x = x; p.y = y; p.z = z; pos[i] = p; }
+	}
+	uint32_t c = grid_cell_index(g, p.x, p.y, p.z);
+	cell[i] = c;
+	atomicAdd(&count[c], 1u);
+	if (make_images)
+		for_each_image(g, p.x, p.y, p.z, [&](int, double x, double y, double z) {
+			atomicAdd(&count[grid_cell_index(g, x, y, z)], 1u);
+		});
+}
+
+// three-kernel exclusive scan over the cell histogram (SCAN_ITEMS cells per block)
+#define SCAN_THREADS 512
+#define SCAN_ITEMS 2048
+__global__ void __launch_bounds__(SCAN_THREADS) scan_reduce_kernel(const uint32_t* __restrict__ in, int n, uint32_t* __restrict__ block_sums) {
+	__shared__ uint32_t sh[SCAN_THREADS / 32];
+	int base = blockIdx.x * SCAN_ITEMS;
+	uint32_t s = 0;
+	for (int k = threadIdx.x; k < SCAN_ITEMS; k += SCAN_THREADS) { int i = base + k; if (i < n) s += in[i]; }
+	for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+	if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = s;
+	__syncthreads();
+	if (threadIdx.x == 0) { uint32_t t = 0; for (int w = 0; w < SCAN_THREADS / 32; ++w) t += sh[w]; block_sums[blockIdx.x] = t; }
+}
+__global__ void scan_blocks_kernel(uint32_t* block_sums, int nb, uint32_t* total_out) {
+	// single thread block, sequential over chunks of 1024: nb is at most a few thousand
+	__shared__ uint32_t sh[1024];
+	__shared__ uint32_t carry;
+	if (threadIdx.x == 0) carry = 0;
+	__syncthreads();
+	for (int base = 0; base < nb; base += 1024) {
+		int i = base + threadIdx.x;
+		uint32_t v = i < nb ? block_sums[i] : 0;
+		sh[threadIdx.x] = v;
+		__syncthreads();
+		for (int o = 1; o < 1024; o <<= 1) {
+			uint32_t t = threadIdx.x >= o ? sh[threadIdx.x - o] : 0;
+			__syncthreads();
+			sh[threadIdx.x] += t;
+			__syncthreads();
+		}
+		uint32_t incl = sh[threadIdx.x];
+		if (i < nb) block_sums[i] = carry + incl - v;
+		__syncthreads();
+		if (threadIdx.x == 1023) carry += incl;
+		__syncthreads();
+	}
+	if (threadIdx.x == 0) *total_out = carry;
+}
+__global__ void __launch_bounds__(SCAN_THREADS) scan_apply_kernel(const uint32_t* __restrict__ in, int n, const uint32_t* __restrict__ block_sums,
+                                                                   uint32_t* __restrict__ out /* [n+1] */) {
+	// each thread owns SCAN_ITEMS/SCAN_THREADS consecutive items
+	const int PER = SCAN_ITEMS / SCAN_THREADS;
+	__shared__ uint32_t sh[SCAN_THREADS / 32];
+	int base = blockIdx.x * SCAN_ITEMS + threadIdx.x * PER;
+	uint32_t v[PER], s = 0;
+#pragma unroll
+	for (int k = 0; k < PER; ++k) { v[k] = (base + k < n) ? in[base + k] : 0; s += v[k]; }
+	// exclusive scan of s across the block
+	uint32_t incl = s;
+	int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+	for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+	if (lane == 31) sh[warp] = incl;
+	__syncthreads();
+	if (warp == 0) {
+		uint32_t w = lane < SCAN_THREADS / 32 ? sh[lane] : 0, wi = w;
+		for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, wi, o); if (lane >= o) wi += t; }
+		if (lane < SCAN_THREADS / 32) sh[lane] = wi - w;
+	}
+	__syncthreads();
+	uint32_t run = block_sums[blockIdx.x] + sh[warp] + incl - s;
+#pragma unroll
+	for (int k = 0; k < PER; ++k) { if (base + k < n) out[base + k] = run; run += v[k]; }
+	if (base <= n - 1 && n - 1 < base + PER) out[n] = run;   // the thread owning the last item writes the total
+}
+
+__global__ void __launch_bounds__(256) scatter_kernel(Grid g, size_t n, const double4* __restrict__ pos, const uint32_t* __restrict__ cell,
+                                                       const uint64_t* __restrict__ id, const uint32_t* __restrict__ cell_start,
+                                                       uint32_t* __restrict__ fill, uint32_t* __restrict__ slot_src,
+                                                       uint8_t* __restrict__ slot_code, uint64_t* __restrict__ slot_key,
+                                                       uint32_t* __restrict__ slot_cell, int make_images) {
+	size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n) return;
+	uint32_t c = cell[i];
+	if (c == 0xFFFFFFFFu) return;
+	uint64_t key = id[i];
+	uint32_t s = cell_start[c] + atomicAdd(&fill[c], 1u);
+	slot_src[s] = (uint32_t)i; slot_code[s] = 0; slot_key[s] = key; slot_cell[s] = c;
+	if (make_images) {
+		double4 p = pos[i];
+		for_each_image(g, p.x, p.y, p.z, [&](int code, double x, double y, double z) {
+			uint32_t ci = grid_cell_index(g, x, y, z);
+			uint32_t si = cell_start[ci] + atomicAdd(&fill[ci], 1u);
+			slot_src[si] = (uint32_t)i; slot_code[si] = (uint8_t)code; slot_key[si] = key; slot_cell[si] = ci;
+		});
+	}
+}
+
+struct GatherArgs {
+	MolBuf src, dst;
+	const double *F_src, *M_src; double *F_dst, *M_dst;   // carried only when non-null
+	int has_rot;
+};
+
+__global__ void __launch_bounds__(256) gather_kernel(Grid g, size_t n_new, GatherArgs a, const uint32_t* __restrict__ cell_start,
+                                                      const uint32_t* __restrict__ slot_src, const uint8_t* __restrict__ slot_code,
+                                                      const uint64_t* __restrict__ slot_key, const uint32_t* __restrict__ slot_cell) {
+	size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (s >= n_new) return;
+	uint32_t c = slot_cell[s];
+	uint32_t b0 = cell_start[c], b1 = cell_start[c + 1];
+	uint64_t key = slot_key[s];
+	uint32_t rank = 0;
+	for (uint32_t k = b0; k < b1; ++k) {
+		uint64_t kk = slot_key[k];
+		rank += (kk < key) || (kk == key && k < (uint32_t)s);
+	}
+	size_t dst = (size_t)b0 + rank;
+	uint32_t src = slot_src[s];
+	int code = slot_code[s];
+	double4 p = a.src.pos[src];
+	if (code) image_pos(g, code, p.x, p.y, p.z);
+	a.dst.pos[dst] = p;
+	a.dst.id[dst] = key;
+	bool halo = grid_is_halo(g, c);
+	a.dst.cell[dst] = c | (halo ? HALO_FLAG : 0u);
+#pragma unroll
+	for (int d = 0; d < 3; ++d) a.dst.vel[3 * dst + d] = a.src.vel[3 * (size_t)src + d];
+	if (a.has_rot) {
+		a.dst.q[dst] = a.src.q[src];
+#pragma unroll
+		for (int d = 0; d < 3; ++d) a.dst.L[3 * dst + d] = a.src.L[3 * (size_t)src + d];
+	}
+	if (a.F_src) {
+#pragma unroll
+		for (int d = 0; d < 3; ++d) a.F_dst[3 * dst + d] = a.F_src[3 * (size_t)src + d];
+		if (a.M_src)
+#pragma unroll
+			for (int d = 0; d < 3; ++d) a.M_dst[3 * dst + d] = a.M_src[3 * (size_t)src + d];
+	}
+}
+
+// C08 enumeration on the device: one thread per base cell writes its (up to 14) triplets into a
+// fixed-stride table; kind 2 marks an unused row.  Colour-major order is restored on the host.
+__global__ void c08_pairs_kernel(Grid g, uint32_t* __restrict__ out /* [n_cells][14][3] */) {
+	long base = (long)blockIdx.x * blockDim.x + threadIdx.x;
+	if (base >= g.n_cells) return;
+	const long nx = g.cpd[0], ny = g.cpd[1], nz = g.cpd[2];
+	long cx = base % nx, cy = (base / nx) % ny, cz = base / (nx * ny);
+	uint32_t* row = out + (size_t)base * 42;
+	bool is_base = cx < nx - 1 && cy < ny - 1 && cz < nz - 1;
+	const long o = 0, x = 1, y = nx, z = nx * ny, xy = x + y, yz = y + z, xz = x + z, xyz = x + y + z;
+	const long pairs[14][2] = {{o, o}, {o, y}, {y, z}, {o, z}, {o, yz}, {x, yz}, {x, y}, {x, z},
+	                           {o, x}, {o, xy}, {xy, z}, {y, xz}, {o, xz}, {o, xyz}};   // C08BasedTraversals.h:127-142
+	for (int j = 0; j < 14; ++j) {
+		uint32_t k = 2, a = 0, b = 0;
+		if (is_base) {
+			uint32_t c1 = (uint32_t)(base + pairs[j][0]), c2 = (uint32_t)(base + pairs[j][1]);
+			bool h1 = grid_is_halo(g, c1), h2 = grid_is_halo(g, c2);
+			if (!(h1 && h2)) {                       // C08BasedTraversals.h:82-84
+				a = c1; b = c2; k = 1;
+				if (c1 == c2) k = 0;                 // processCell
+				else if (h1) { a = c2; b = c1; }     // non-halo cell first (:90-95)
+			}
+		}
+		row[3 * j] = a; row[3 * j + 1] = b; row[3 * j + 2] = k;
+	}
+}
+
+// ------------------------------------------------------------------------------------------------
+// host launchers
+// ------------------------------------------------------------------------------------------------
+static inline unsigned nblk(size_t n, unsigned t) { return (unsigned)((n + t - 1) / t); }
+
+int k_cell_index(ls1g_ctx* c, size_t n, const double* d_pts, uint32_t* d_out) {
+	if (n == 0) return 0;
+	cell_index_kernel<<<nblk(n, 256), 256, 0, c->stream>>>(c->grid, n, d_pts, d_out);
+	CUDA_TRY(cudaGetLastError());
+	return 0;
+}
+
+int k_sort(ls1g_ctx* c, int make_images) {
+	const Grid& g = c->grid;
+	const int nc = g.n_cells;
+	size_t n = c->n_slots;
+	timer_start(c, LS1G_T_SORT);
+	CUDA_TRY(cudaMemsetAsync(c->cell_count, 0, sizeof(uint32_t) * (nc + 1), c->stream));
+	CUDA_TRY(cudaMemsetAsync(c->cell_fill, 0, sizeof(uint32_t) * (nc + 1), c->stream));
+	int launches = 0;
+	if (n) { bin_kernel<<<nblk(n, 256), 256, 0, c->stream>>>(g, n, c->cur.pos, c->cur.cell, c->cell_count, make_images); ++launches; }
+	int nb = (nc + SCAN_ITEMS - 1) / SCAN_ITEMS;
+	scan_reduce_kernel<<<nb, SCAN_THREADS, 0, c->stream>>>(c->cell_count, nc, c->scan_block);
+	scan_blocks_kernel<<<1, 1024, 0, c->stream>>>(c->scan_block, nb, c->d_counters);
+	scan_apply_kernel<<<nb, SCAN_THREADS, 0, c->stream>>>(c->cell_count, nc, c->scan_block, c->cell_start);
+	launches += 3;
+	CUDA_TRY(cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+	CUDA_TRY(cudaStreamSynchronize(c->stream));
+	size_t n_new = c->h_counters[0];
+	if (n_new > c->cap) {
+		timer_stop(c, LS1G_T_SORT, launches);
+		LS1G_FAIL("ls1g: capacity exceeded by halo copies (" + std::to_string(n_new) + " > " + std::to_string(c->cap) + ")");
+	}
+	if (n) {
+		scatter_kernel<<<nblk(n, 256), 256, 0, c->stream>>>(g, n, c->cur.pos, c->cur.cell, c->cur.id, c->cell_start, c->cell_fill,
+		                                                   c->slot_src, c->slot_code, c->slot_key, c->slot_cell, make_images);
+		++launches;
+	}
+	if (n_new) {
+		GatherArgs a;
+		a.src = c->cur; a.dst = c->alt; a.has_rot = c->has_rot;
+		// forces are carried through a re-sort only when they exist (API use outside ls1g_run); Vi is not carried
+		bool carry = c->forces_valid;
+		a.F_src = carry ? c->F : nullptr; a.F_dst = c->F_alt;
+		a.M_src = (carry && c->has_rot) ? c->M : nullptr; a.M_dst = c->M_alt;
+		gather_kernel<<<nblk(n_new, 256), 256, 0, c->stream>>>(g, n_new, a, c->cell_start, c->slot_src, c->slot_code, c->slot_key, c->slot_cell);
+		++launches;
+		if (carry) { std::swap(c->F, c->F_alt); if (c->has_rot) std::swap(c->M, c->M_alt); }
+	}
+	CUDA_TRY(cudaGetLastError());
+	std::swap(c->cur, c->alt);
+	c->n_slots = n_new;
+	c->n_halo = n_new - c->n_owned;
+	c->sorted = 1;
+	timer_stop(c, LS1G_T_SORT, launches);
+	return 0;
+}
+
+int k_drop_halo(ls1g_ctx* c) {
+	// halo copies keep HALO_FLAG in cell[]: the integrator and the next bin skip them.  Nothing to move.
+	c->n_halo = 0;
+	return 0;
+}
+
+int k_debug_cell_pairs(const ls1g_ctx* c, uint32_t* h_triplets, size_t capacity, size_t* n_out) {
+	const Grid& g = c->grid;
+	size_t rows = (size_t)g.n_cells * 14;
+	uint32_t* d = nullptr;
+	CUDA_TRY(cudaMalloc((void**)&d, rows * 3 * sizeof(uint32_t)));
+	c08_pairs_kernel<<<nblk(g.n_cells, 128), 128, 0, c->stream>>>(g, d);
+	std::vector<uint32_t> h(rows * 3);
+	cudaError_t e = cudaMemcpyAsync(h.data(), d, rows * 3 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream);
+	if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+	cudaFree(d);
+	if (e != cudaSuccess) { ls1g_set_error(std::string("c08 dump: ") + cudaGetErrorString(e)); return 1; }
+	// colour-major order as C08CellPairTraversal::traverseCellPairs (C08CellPairTraversal.h:60-79)
+	size_t cnt = 0;
+	const long nx = g.cpd[0], ny = g.cpd[1], nz = g.cpd[2];
+	for (int col = 0; col < 8; ++col) {
+		long bx = col % 2, by = (col / 2) % 2, bz = col / 4;
+		for (long cz = bz; cz < nz - 1; cz += 2)
+			for (long cy = by; cy < ny - 1; cy += 2)
+				for (long cx = bx; cx < nx - 1; cx += 2) {
+					size_t base = (size_t)((cz * ny + cy) * nx + cx);
+					for (int j = 0; j < 14; ++j) {
+						const uint32_t* r = &h[(base * 14 + j) * 3];
+						if (r[2] == 2) continue;
+						if (h_triplets && cnt < capacity) { h_triplets[3 * cnt] = r[0]; h_triplets[3 * cnt + 1] = r[1]; h_triplets[3 * cnt + 2] = r[2]; }
+						++cnt;
+					}
+				}
+	}
+	*n_out = cnt;
+	return 0;
+}

@@ -1,0 +1,256 @@
+// ls1g_internal.cuh — shared declarations of the B200 (sm_100a) short-range force + integrate path.
+//
+// One ls1g_ctx = one ParticleContainer (reference: src/particleContainer/LinkedCells.h) resident in
+// HBM as a cell-sorted SoA.  Kernels live in the .cu files next to this header; the C ABI
+// (include/ls1g.h) is implemented in api.cu.  No CPU fallback exists anywhere in this directory.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stddef.h>
+#include <string>
+#include <vector>
+
+#include "../../include/ls1g.h"
+
+// ------------------------------------------------------------------------------------------------
+// Grid geometry (LinkedCells::rebuild / constructor, src/particleContainer/LinkedCells.cpp:42-204 and
+// CellBorderAndFlagManager.h:99-157).  Passed BY VALUE to kernels (lives in the kernel-parameter
+// constant bank).
+// ------------------------------------------------------------------------------------------------
+struct Grid {
+	double box_min[3], box_max[3];
+	double halo_min[3], halo_max[3];
+	double cell_len[3], cell_len_recip[3];
+	double box_len[3];        // box_max - box_min : periodic shift magnitude (DomainDecompBase.cpp:175)
+	double cutoff;            // halo slab width (DomainDecompBase.cpp:293-348)
+	int    cpd[3];            // cells per dimension incl. one halo layer on each side
+	int    n_cells;
+	int    self_periodic[3];  // 1: this rank is its own neighbour in that dimension (rank_grid[d]==1)
+};
+
+// Per-component constants (src/molecules/Component.h, FullMolecule::updateMassInertia FullMolecule.h:88-101)
+struct CompDev {
+	double mass, inv_mass_unused;
+	double I[3], invI[3];
+	int    rot_dof;
+	int    n_lj, n_ch, n_di, n_qu;
+	int    lj_id0;            // Component::getLookUpId (EnsembleBase.cpp:91-103): global id of LJ site 0
+	int    site0;             // offset of this component's first site row in the body-frame site table
+	int    n_sites;           // n_lj + n_ch + n_di + n_qu
+};
+
+// Body-frame site row (Site.h:84-300).  type: 0 LJ, 1 charge, 2 dipole, 3 quadrupole.
+struct SiteDev {
+	double d[3];              // body-frame offset
+	double e[3];              // body-frame orientation (dipole / quadrupole)
+	double val;               // q | |mu| | |Q| ; unused for LJ
+	int    type;
+	int    ljid;              // global LJ id (LJ sites)
+};
+
+enum { SITE_LJ = 0, SITE_CH = 1, SITE_DI = 2, SITE_QU = 3 };
+
+// ------------------------------------------------------------------------------------------------
+// Molecule storage.  All arrays have `cap` entries, index = slot in cell-sorted order.
+// pos.w carries the component id (low 32 bits of the bit pattern) so that one 32-byte load gives a
+// neighbour's centre AND its component.
+// ------------------------------------------------------------------------------------------------
+struct MolBuf {
+	double4*  pos;    // x y z | cid bits
+	double*   vel;    // [cap][3]
+	double4*  q;      // w x y z           (only if ctx->has_rot)
+	double*   L;      // [cap][3]          (only if ctx->has_rot)
+	uint64_t* id;
+	uint32_t* cell;   // linear cell index | HALO_FLAG
+};
+
+static const uint32_t HALO_FLAG = 0x80000000u;
+
+struct Timer { double ms; uint64_t launches; };
+struct PendingEvt { cudaEvent_t a, b; int which; int launches; };
+
+struct ls1g_ctx {
+	ls1g_config cfg;
+	Grid grid;
+	cudaStream_t stream;
+
+	// components
+	int n_comp, n_site_rows, S_lj;          // S_lj = total LJ sites over all components
+	int max_sites;                          // max sites of any component (site-cache stride)
+	int has_rot;                            // any component needs q/L (multi-site or rot_dof>0)
+	int simple_1clj;                        // exactly one component: one LJ site at the origin, nothing else
+	std::vector<CompDev> comps_h;
+	std::vector<SiteDev> sites_h;
+	std::vector<double>  eps24_h, sig2_h, shift6_h;
+	CompDev* comps; SiteDev* sites;         // device copies
+	double *eps24, *sig2, *shift6;          // device [S_lj*S_lj]
+	double epsRFInvrc3, rc2, rclj2;
+
+	// molecules
+	size_t cap;                             // allocated slots
+	size_t n_slots;                         // slots in use (owned + halo copies), cell-sorted if sorted
+	size_t n_owned, n_halo;
+	int    sorted;                          // cell[] / cell_start valid
+	int    forces_valid;
+	MolBuf cur, alt;                        // double buffer for the sort
+	double *F, *M, *Vi;                     // [cap][3]; M only if has_rot
+	double *F_alt, *M_alt;                  // targets when forces are carried through a re-sort
+	double4* site_cache;                    // [cap*cache_stride] world-frame site data (multi-site path)
+	int     cache_stride;
+
+	// cells / sort scratch
+	uint32_t *cell_count, *cell_fill, *cell_start;   // [n_cells+1]
+	uint32_t *scan_block;                            // block sums of the scan
+	uint32_t *slot_src;  uint8_t* slot_code; uint64_t* slot_key; uint32_t* slot_cell;   // [cap]
+	uint32_t *d_counters;                            // [8] misc device counters
+	uint32_t *h_counters;                            // pinned mirror
+
+	// reductions
+	double*  partials; size_t partials_cap;          // per-block partial sums
+	double*  d_scalars;                              // [16] reduced results
+	double*  h_scalars;                              // pinned mirror
+	unsigned long long* d_pairs;                     // pair counter
+	uint64_t last_pairs;
+
+	// multi-GPU
+	void* nccl_comm; int n_ranks, rank;
+	int comm_mode;                          // 0 single rank, 1 NCCL, 2 in-process local group (tests)
+	double *send_buf[2], *recv_buf[2]; size_t xbuf_cap;
+
+	Timer timers[LS1G_T_COUNT];
+	std::vector<PendingEvt> pending;        // event pairs not yet resolved into timers[]
+	std::vector<cudaEvent_t> evpool;
+};
+
+// error handling --------------------------------------------------------------------------------
+void ls1g_set_error(const std::string& msg);
+#define CUDA_TRY(expr) do { cudaError_t _e = (expr); if (_e != cudaSuccess) { \
+	ls1g_set_error(std::string(#expr) + ": " + cudaGetErrorString(_e)); return 1; } } while (0)
+#define LS1G_FAIL(msg) do { ls1g_set_error(msg); return 1; } while (0)
+
+// launchers implemented in the kernel files ---------------------------------------------------------
+// cells.cu
+int  k_cell_index(ls1g_ctx* c, size_t n, const double* d_pts, uint32_t* d_out);
+int  k_sort(ls1g_ctx* c, int make_images);      // bin (+periodic images) -> scan -> scatter -> gather, swaps cur/alt
+int  k_drop_halo(ls1g_ctx* c);                  // deleteOuterParticles
+int  k_debug_cell_pairs(const ls1g_ctx* c, uint32_t* h_triplets, size_t capacity, size_t* n_out);
+// integrate.cu
+int  k_scale(ls1g_ctx* c, double bt, double br);
+int  k_post_pre(ls1g_ctx* c, double dt, int do_post, int do_pre, int thermostat, double target_T);
+// force.cu
+int  k_forces(ls1g_ctx* c);                           // results in d_scalars[0..3]; caller syncs
+// peak.cu
+int  k_fp64_peak(int device, double* tflops);
+// comm.cu
+int  comm_exchange(ls1g_ctx* c);
+int  comm_allreduce(ls1g_ctx* c, double* d_vals, int n);
+void comm_destroy(ls1g_ctx* c);
+
+void timer_start(ls1g_ctx* c, int which);
+void timer_stop(ls1g_ctx* c, int which, int launches);
+
+// ------------------------------------------------------------------------------------------------
+// Device helpers shared by kernels
+// ------------------------------------------------------------------------------------------------
+#ifdef __CUDACC__
+
+__device__ __forceinline__ uint32_t pos_cid(const double4& p) { return (uint32_t)__double_as_longlong(p.w); }
+__device__ __forceinline__ double   cid_bits(uint32_t cid) { return __longlong_as_double((long long)cid); }
+
+// CellBorderAndFlagManager::getBorder (CellBorderAndFlagManager.h:134-157).  The general branch is an
+// FMA in the reference's -O3 -mfma build (pinned by tests/golden/cellindex_*.npz).
+__device__ __host__ __forceinline__ double grid_border(const Grid& g, int index, int d) {
+	if (index == 0) return g.halo_min[d];
+	if (index == 1) return g.box_min[d];
+	if (index == g.cpd[d] - 1) return g.box_max[d];
+	if (index == g.cpd[d]) return g.halo_max[d];
+#ifdef __CUDA_ARCH__
+	return __fma_rn((double)index, g.cell_len[d], g.halo_min[d]);
+#else
+	return __builtin_fma((double)index, g.cell_len[d], g.halo_min[d]);
+#endif
+}
+
+// LinkedCells::getCellIndexOfPoint (LinkedCells.cpp:830-882): bit-exact (explicit rounding intrinsics,
+// no contraction).
+__device__ __host__ __forceinline__ uint32_t grid_cell_index(const Grid& g, double px, double py, double pz) {
+	double p[3] = {px, py, pz};
+	int ci[3];
+#pragma unroll
+	for (int d = 0; d < 3; ++d) {
+		if (p[d] <= g.halo_min[d]) p[d] = p[d] + g.cell_len[d] * 0.5;
+		else if (p[d] >= g.halo_max[d]) p[d] = p[d] - g.cell_len[d] * 0.5;
+#ifdef __CUDA_ARCH__
+		double t = __dmul_rn(__dsub_rn(p[d], g.box_min[d]), g.cell_len_recip[d]);
+#else
+		volatile double t0 = p[d] - g.box_min[d];
+		volatile double t = t0 * g.cell_len_recip[d];
+#endif
+		int c = (int)floor(t) + 1;
+		c = c < 0 ? 0 : c;
+		c = c > g.cpd[d] - 1 ? g.cpd[d] - 1 : c;
+		ci[d] = c;
+	}
+	bool in = true;
+#pragma unroll
+	for (int d = 0; d < 3; ++d) in = in && (grid_border(g, ci[d], d) <= p[d]) && (p[d] < grid_border(g, ci[d] + 1, d));
+	if (!in) {
+#pragma unroll
+		for (int d = 0; d < 3; ++d) {
+			int c0 = ci[d];
+			if (p[d] < grid_border(g, c0, d)) ci[d] = c0 - 1;
+			else if (p[d] >= grid_border(g, c0 + 1, d)) ci[d] = c0 + 1;
+		}
+	}
+	return (uint32_t)((ci[2] * g.cpd[1] + ci[1]) * g.cpd[0] + ci[0]);
+}
+
+__device__ __host__ __forceinline__ bool grid_is_halo(const Grid& g, uint32_t cell) {
+	int x = cell % g.cpd[0];
+	int y = (cell / g.cpd[0]) % g.cpd[1];
+	int z = cell / (g.cpd[0] * g.cpd[1]);
+	return x == 0 || y == 0 || z == 0 || x == g.cpd[0] - 1 || y == g.cpd[1] - 1 || z == g.cpd[2] - 1;
+}
+
+// Quaternion::rotate (src/molecules/Quaternion.cpp:43-62)
+__device__ __forceinline__ void quat_rotate(const double4& q, const double d[3], double out[3]) {
+	double ww = q.x*q.x, xx = q.y*q.y, yy = q.z*q.z, zz = q.w*q.w;
+	double wx = q.x*q.y, wy = q.x*q.z, wz = q.x*q.w, xy = q.y*q.z, xz = q.y*q.w, yz = q.z*q.w;
+	out[0] = (ww+xx-yy-zz)*d[0] + 2.*(xy-wz)*d[1] + 2.*(wy+xz)*d[2];
+	out[1] = 2.*(wz+xy)*d[0] + (ww-xx+yy-zz)*d[1] + 2.*(yz-wx)*d[2];
+	out[2] = 2.*(xz-wy)*d[0] + 2.*(wx+yz)*d[1] + (ww-xx-yy+zz)*d[2];
+}
+// Quaternion::rotateinv (Quaternion.cpp:64-83)
+__device__ __forceinline__ void quat_rotateinv(const double4& q, const double d[3], double out[3]) {
+	double ww = q.x*q.x, xx = q.y*q.y, yy = q.z*q.z, zz = q.w*q.w;
+	double wx = q.x*q.y, wy = q.x*q.z, wz = q.x*q.w, xy = q.y*q.z, xz = q.y*q.w, yz = q.z*q.w;
+	out[0] = (ww+xx-yy-zz)*d[0] + 2.*(xy+wz)*d[1] + 2.*(xz-wy)*d[2];
+	out[1] = 2.*(xy-wz)*d[0] + (ww-xx+yy-zz)*d[1] + 2.*(yz+wx)*d[2];
+	out[2] = 2.*(xz+wy)*d[0] + 2.*(yz-wx)*d[1] + (ww-xx-yy+zz)*d[2];
+}
+
+// warp / block sum of `NV` doubles; result valid in thread 0 of the block.  Fixed order -> deterministic.
+template <int NV>
+__device__ __forceinline__ void block_sum(double (&v)[NV], double* smem /* [NV*32] */) {
+#pragma unroll
+	for (int k = 0; k < NV; ++k)
+#pragma unroll
+		for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_down_sync(0xffffffffu, v[k], o);
+	int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+	if (lane == 0)
+#pragma unroll
+		for (int k = 0; k < NV; ++k) smem[k * 32 + warp] = v[k];
+	__syncthreads();
+	if (warp == 0) {
+#pragma unroll
+		for (int k = 0; k < NV; ++k) {
+			double x = lane < nw ? smem[k * 32 + lane] : 0.0;
+#pragma unroll
+			for (int o = 16; o > 0; o >>= 1) x += __shfl_down_sync(0xffffffffu, x, o);
+			v[k] = x;
+		}
+	}
+	__syncthreads();
+}
+#endif  // __CUDACC__

@@ -1,0 +1,173 @@
+// step.cu — per-step operators of the C ABI and the device-resident time loop (Simulation::simulate order,
+// src/Simulation.cpp:979-1177).
+#include "ls1g_internal.cuh"
+
+#include <math.h>
+#include <string.h>
+
+int k_post_pre(ls1g_ctx* c, double dt, int do_post, int do_pre, int thermostat, double target_T);
+void ls1g_resolve_timers(ls1g_ctx* c);
+
+#define NEED(c) do { if (!(c)) LS1G_FAIL("null context"); CUDA_TRY(cudaSetDevice((c)->cfg.device)); } while (0)
+
+static int sync_check(ls1g_ctx* c, const char* what) {
+	cudaError_t e = cudaStreamSynchronize(c->stream);
+	if (e == cudaSuccess) e = cudaGetLastError();
+	if (e != cudaSuccess) LS1G_FAIL(std::string(what) + ": " + cudaGetErrorString(e));
+	return 0;
+}
+
+// LinkedCells::update (LinkedCells.cpp:243-356): re-bin every owned molecule; no wrap, no halo copies
+extern "C" int ls1g_update(ls1g_ctx* c) {
+	NEED(c);
+	if (k_sort(c, 0)) return 1;
+	return sync_check(c, "ls1g_update");
+}
+
+// DomainDecompBase::exchangeMolecules (DomainDecompBase.cpp:51-86) / DomainDecomposition::balanceAndExchange
+extern "C" int ls1g_exchange(ls1g_ctx* c) {
+	NEED(c);
+	if (c->n_ranks > 1) { if (comm_exchange(c)) return 1; }
+	else if (k_sort(c, 1)) return 1;
+	return sync_check(c, "ls1g_exchange");
+}
+
+extern "C" int ls1g_traverse(ls1g_ctx* c, double* upot, double* virial) {
+	NEED(c);
+	if (k_forces(c)) return 1;
+	CUDA_TRY(cudaMemcpyAsync(c->h_scalars, c->d_scalars, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+	if (sync_check(c, "ls1g_traverse")) return 1;
+	c->forces_valid = 1;
+	c->last_pairs = (uint64_t)llround(c->h_scalars[2]);
+	if (upot) *upot = c->h_scalars[0];
+	if (virial) *virial = c->h_scalars[1];
+	return 0;
+}
+
+extern "C" int ls1g_delete_outer(ls1g_ctx* c) {
+	NEED(c);
+	return k_drop_halo(c);
+}
+
+extern "C" int ls1g_integrate_pre(ls1g_ctx* c, double dt) {
+	NEED(c);
+	if (k_post_pre(c, dt, 0, 1, 0, 0.)) return 1;
+	c->sorted = 0;   // positions moved: cell_start is stale until the next update/exchange
+	return sync_check(c, "ls1g_integrate_pre");
+}
+
+extern "C" int ls1g_integrate_post(ls1g_ctx* c, double dt_half, double* summv2, double* sumIw2, uint64_t* n, uint64_t* rot_dof) {
+	NEED(c);
+	if (k_post_pre(c, 2. * dt_half, 1, 0, 0, 0.)) return 1;
+	CUDA_TRY(cudaMemcpyAsync(c->h_scalars + 4, c->d_scalars + 4, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+	if (sync_check(c, "ls1g_integrate_post")) return 1;
+	if (summv2) *summv2 = c->h_scalars[4];
+	if (sumIw2) *sumIw2 = c->h_scalars[5];
+	if (n) *n = (uint64_t)llround(c->h_scalars[6]);
+	if (rot_dof) *rot_dof = (uint64_t)llround(c->h_scalars[7]);
+	return 0;
+}
+
+extern "C" int ls1g_scale(ls1g_ctx* c, double bt, double br) {
+	NEED(c);
+	if (k_scale(c, bt, br)) return 1;
+	return sync_check(c, "ls1g_scale");
+}
+
+// Device-resident loop.  Per step: pre -> exchange (wrap, images, sort) -> forces (+calcFM) -> post -> thermostat.
+// post(n), the thermostat and pre(n+1) run as one kernel between two force passes.
+extern "C" int ls1g_run(ls1g_ctx* c, int n_steps, double dt, double target_T, ls1g_step_record* records) {
+	NEED(c);
+	if (n_steps <= 0) return 0;
+	if (!c->forces_valid) LS1G_FAIL("ls1g_run: forces missing - call ls1g_exchange + ls1g_traverse once (prepare_start, Simulation.cpp:813-844)");
+	const int thermo = target_T > 0.;
+	double* d_rec = nullptr;
+	if (records) CUDA_TRY(cudaMallocAsync((void**)&d_rec, (size_t)n_steps * 8 * sizeof(double), c->stream));
+	int rc = k_post_pre(c, dt, 0, 1, 0, 0.);
+	for (int s = 0; s < n_steps && !rc; ++s) {
+		c->sorted = 0;
+		rc = c->n_ranks > 1 ? comm_exchange(c) : k_sort(c, 1);
+		if (!rc) rc = k_forces(c);
+		if (!rc) rc = k_drop_halo(c);
+		if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s, c->d_scalars, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
+		if (!rc) rc = k_post_pre(c, dt, 1, s + 1 < n_steps, thermo, target_T);
+		if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s + 4, c->d_scalars + 4, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
+	}
+	std::vector<double> h;
+	if (!rc && d_rec) {
+		h.resize((size_t)n_steps * 8);
+		if (cudaMemcpyAsync(h.data(), d_rec, h.size() * sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess) rc = 1;
+	}
+	if (d_rec) cudaFreeAsync(d_rec, c->stream);
+	if (rc) { cudaStreamSynchronize(c->stream); return 1; }
+	if (sync_check(c, "ls1g_run")) return 1;
+	if (records)
+		for (int s = 0; s < n_steps; ++s) {
+			const double* r = &h[(size_t)s * 8];
+			records[s].upot = r[0]; records[s].virial = r[1]; records[s].summv2 = r[4]; records[s].sumIw2 = r[5];
+			records[s].n = (uint64_t)llround(r[6]); records[s].rot_dof = (uint64_t)llround(r[7]);
+			c->last_pairs = (uint64_t)llround(r[2]);
+		}
+	return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// decomposition helpers (host only)
+// ------------------------------------------------------------------------------------------------
+// DomainDecomposition::getBoundingBoxMin/Max (DomainDecomposition.cpp:116-125)
+extern "C" int ls1g_decomp_box(const int grid[3], const int coords[3], const double L[3], double box_min[3], double box_max[3]) {
+	for (int d = 0; d < 3; ++d) {
+		if (grid[d] < 1 || coords[d] < 0 || coords[d] >= grid[d]) LS1G_FAIL("ls1g_decomp_box: bad grid/coords");
+		box_min[d] = coords[d] * L[d] / grid[d];
+		box_max[d] = coords[d] + 1 == grid[d] ? L[d] : (coords[d] + 1) * L[d] / grid[d];
+	}
+	return 0;
+}
+
+// MPI_Dims_create(n, 3, dims) with dims = {0,0,0}: balanced factorisation, non-increasing order; MPI_Cart_coords:
+// row-major, last dimension varies fastest (DomainDecomposition.cpp:35-39).
+extern "C" int ls1g_decomp_grid(int n_ranks, int rank, int grid[3], int coords[3]) {
+	if (n_ranks < 1 || rank < 0 || rank >= n_ranks) LS1G_FAIL("ls1g_decomp_grid: bad rank");
+	int best[3] = {n_ranks, 1, 1};
+	for (int a = 1; a <= n_ranks; ++a) {
+		if (n_ranks % a) continue;
+		int rest = n_ranks / a;
+		for (int b = 1; b <= rest; ++b) {
+			if (rest % b) continue;
+			int cdim = rest / b;
+			if (!(a >= b && b >= cdim)) continue;
+			if (a - cdim < best[0] - best[2] || (a - cdim == best[0] - best[2] && a < best[0])) { best[0] = a; best[1] = b; best[2] = cdim; }
+		}
+	}
+	for (int d = 0; d < 3; ++d) grid[d] = best[d];
+	coords[2] = rank % grid[2];
+	coords[1] = (rank / grid[2]) % grid[1];
+	coords[0] = rank / (grid[2] * grid[1]);
+	return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// measurement
+// ------------------------------------------------------------------------------------------------
+extern "C" int ls1g_timers(ls1g_ctx* c, double ms[LS1G_T_COUNT], uint64_t launches[LS1G_T_COUNT], int reset) {
+	NEED(c);
+	CUDA_TRY(cudaStreamSynchronize(c->stream));
+	ls1g_resolve_timers(c);
+	for (int k = 0; k < LS1G_T_COUNT; ++k) {
+		if (ms) ms[k] = c->timers[k].ms;
+		if (launches) launches[k] = c->timers[k].launches;
+		if (reset) { c->timers[k].ms = 0.; c->timers[k].launches = 0; }
+	}
+	return 0;
+}
+
+extern "C" int ls1g_measure_fp64_peak(int device, double* tflops) {
+	if (!tflops) LS1G_FAIL("null argument");
+	return k_fp64_peak(device, tflops);
+}
+
+extern "C" int ls1g_last_pair_count(ls1g_ctx* c, uint64_t* pairs) {
+	if (!c || !pairs) LS1G_FAIL("null argument");
+	*pairs = c->last_pairs;
+	return 0;
+}
