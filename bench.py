@@ -1,0 +1,480 @@
+#!/usr/bin/env python
+"""bench.py — MMUPS (million molecule-updates/s) of the ls1-MarDyn short-range force + integrate path.
+
+  python bench.py --gpus N --steps K --warmup W            the B200 path (C ABI, libls1g.so)
+  python bench.py --impl reference --steps K --warmup W    the reference's own CPU implementation (oracle/_ref/MarDyn)
+
+Workload (BASELINE.json configs[1], SURVEY.md 8d cfg B): synthetic 1CLJ fcc lattice, eps=sigma=m=1, rho*=0.8442,
+T*=1.44, rc=2.5 sigma, dt*=0.002, NVE, 136^3 unit cells = 10 061 824 molecules PER GPU (weak scaling; the rank grid
+is DomainDecomposition's block grid, halo + leaving exchange over NCCL).  One step = one full time step of the path:
+leapfrog pre -> wrap/halo/sort -> force pass (+calcFM, upot, virial) -> leapfrog post + kinetic sums.
+MUPS is the reference's own definition, N_global * steps / time of the loop (src/MarDyn.cpp:264-266).
+
+Prints ONE JSON line (rank 0).  `value`: device-resident loop, inputs in HBM.  `e2e`: the same step driven through the
+public API with HOST (pinned) buffers: every step uploads id,cid,r,v,F and downloads id,r,v,F."""
+import argparse
+import importlib
+import json
+import os
+import re
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+RHO, TEMP, RC, DT = 0.8442, 1.44, 2.5, 0.002
+CELLS_PER_GPU = 136            # fcc unit cells per dimension per GPU: 4*136^3 = 10 061 824 molecules
+METRIC = "MMUPS (million molecule-updates/s), 1CLJ fcc 10^7 molecules per B200, force+integrate step"
+
+
+def _pkg():
+    return importlib.import_module("ls1-mardyn_b200")
+
+
+def _gen():
+    return importlib.import_module("ls1-mardyn_b200.generators")
+
+
+# ----------------------------------------------------------------------------------------------------------
+# workload
+# ----------------------------------------------------------------------------------------------------------
+def make_shard(n_cells_global, world, rank):
+    """this rank's block of the global fcc system (DomainDecomposition.cpp:116-125 boxes)"""
+    ls1g, gen = _pkg(), _gen()
+    grid, coords = ls1g.decomp_grid(world, rank)
+    _, L = gen.fcc_box(n_cells_global, RHO)
+    bmin, bmax = ls1g.decomp_box(grid, coords, list(L))
+    ids, r, v = gen.fcc_block(n_cells_global, bmin, bmax, RHO, TEMP, seed=1)
+    return dict(id=ids, r=r, v=v, grid=grid, coords=coords, box_min=bmin, box_max=bmax, L=list(L))
+
+
+def global_cells(world, per_gpu):
+    grid, _ = _pkg().decomp_grid(world, 0)
+    return [per_gpu * g for g in grid]
+
+
+def global_mean_velocity(v, dist=None):
+    """IOHelpers::removeMomentum: global mean velocity (all-reduced when distributed)"""
+    import torch
+    t = torch.tensor([v[:, 0].sum(), v[:, 1].sum(), v[:, 2].sum(), float(len(v))], dtype=torch.float64)
+    if dist is not None and dist.is_initialized() and dist.get_world_size() > 1:
+        if dist.get_backend() == "nccl":
+            t = t.cuda()
+        dist.all_reduce(t)
+        t = t.cpu()
+    return (t[:3] / t[3]).numpy()
+
+
+def distance_checks(cell, cpd):
+    """N_dist of the FlopCounter model: molecule-centre distance checks with Newton 3, every unordered pair of molecules
+    in the same or adjacent cells once (halo-halo excluded; a pair with a halo image counts 1/2 from each side)."""
+    nx, ny, nz = cpd
+    cnt = np.bincount(cell.astype(np.int64), minlength=nx * ny * nz).astype(np.float64).reshape(nz, ny, nx)
+    inner = cnt[1:-1, 1:-1, 1:-1]
+    tot = (inner * (inner - 1.0)).sum() * 0.5
+    for dz in (-1, 0, 1):
+        for dy in (-1, 0, 1):
+            for dx in (-1, 0, 1):
+                if dx == 0 and dy == 0 and dz == 0:
+                    continue
+                nb = cnt[1 + dz:nz - 1 + dz, 1 + dy:ny - 1 + dy, 1 + dx:nx - 1 + dx]
+                tot += 0.5 * (inner * nb).sum()
+    return float(tot)
+
+
+def lj_flops(n_dist, n_pairs):
+    """FlopCounter model (adapter/FlopCounter.cpp:19-75, FlopCounter.h:243-269) for one LJ site per molecule:
+    8 per distance check + (8 + 15 + 12) per in-cutoff site pair + (4 + 2) macroscopic"""
+    return 8.0 * n_dist + (8.0 + 15.0 + 12.0 + 4.0 + 2.0) * n_pairs
+
+
+# ----------------------------------------------------------------------------------------------------------
+# clocks
+# ----------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, device):
+        self.device, self.rows, self.proc = device, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for k, n in enumerate(names) if any(len(r) >= 6 and r[2 + k].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------------------------------------
+# the reference's own CPU implementation (oracle/_ref/MarDyn, built from the unmodified sources by oracle/ref/Makefile)
+# ----------------------------------------------------------------------------------------------------------
+MARDYN_XML = """<?xml version='1.0' encoding='UTF-8'?>
+<mardyn version="20100525">
+  <refunits type="SI"><length unit="nm">0.1</length><mass unit="u">1</mass><energy unit="K">1</energy></refunits>
+  <simulation type="MD">
+    <integrator type="Leapfrog"><timestep unit="reduced">{dt}</timestep></integrator>
+    <run><currenttime>0</currenttime><production><steps>{steps}</steps></production></run>
+    <ensemble type="NVT">
+      <temperature unit="reduced">{temp}</temperature>
+      <domain type="box"><lx>{L}</lx><ly>{L}</ly><lz>{L}</lz></domain>
+      <components>
+        <moleculetype id="1" name="1CLJ">
+          <site type="LJ126" id="1" name="LJ"><coords><x>0.0</x><y>0.0</y><z>0.0</z></coords><mass>1.0</mass><sigma>1.0</sigma><epsilon>1.0</epsilon><shifted>false</shifted></site>
+        </moleculetype>
+      </components>
+      <phasespacepoint>
+        <generator name="MultiObjectGenerator">
+          <objectgenerator>
+            <filler type="GridFiller">
+              <lattice system="cubic" centering="face">
+                <vec id="a"><x>1</x><y>0</y><z>0</z></vec><vec id="b"><x>0</x><y>1</y><z>0</z></vec><vec id="c"><x>0</x><y>0</y><z>1</z></vec>
+              </lattice>
+              <basis><site><componentid>0</componentid><coordinate><x>0.25</x><y>0.25</y><z>0.25</z></coordinate></site></basis>
+              <latticeOccupancy>1</latticeOccupancy>
+              <density>{rho}</density>
+            </filler>
+            <object type="Cuboid"><lower><x>0</x><y>0</y><z>0</z></lower><upper><x>{L}</x><y>{L}</y><z>{L}</z></upper></object>
+            <velocityAssigner type="EqualVelocityDistribution"></velocityAssigner>
+          </objectgenerator>
+        </generator>
+      </phasespacepoint>
+    </ensemble>
+    <algorithm>
+      <parallelisation type="DomainDecomposition"></parallelisation>
+      <datastructure type="LinkedCells"><cellsInCutoffRadius>1</cellsInCutoffRadius></datastructure>
+      <cutoffs type="CenterOfMass"><defaultCutoff unit="reduced">{rc}</defaultCutoff><radiusLJ unit="reduced">{rc}</radiusLJ></cutoffs>
+      <electrostatic type="ReactionField"><epsilon>1.0e+10</epsilon></electrostatic>
+    </algorithm>
+    <output></output>
+  </simulation>
+</mardyn>
+"""
+
+
+def host_cores():
+    try:
+        import psutil
+        n = psutil.cpu_count(logical=False) or os.cpu_count()
+    except Exception:
+        n = os.cpu_count()
+    try:
+        n = min(n, len(os.sched_getaffinity(0)))
+    except Exception:
+        pass
+    return max(int(n), 1)
+
+
+def reference_binary():
+    """oracle/_ref/MarDyn (AVX2 build); MarDyn_avx512 when present and the host CPU has avx512f"""
+    ref = os.path.join(ROOT, "oracle", "_ref")
+    cands = []
+    try:
+        flags = open("/proc/cpuinfo").read()
+    except OSError:
+        flags = ""
+    if " avx512f" in flags:
+        cands.append(os.path.join(ref, "MarDyn_avx512"))
+    cands.append(os.path.join(ref, "MarDyn"))
+    for c in cands:
+        if os.path.exists(c) and os.access(c, os.X_OK):
+            return c
+    return None
+
+
+def run_reference_sample(sample_cells, steps, threads):
+    """runs the unmodified reference on a 1CLJ fcc sample of the bench workload (same rho, T, rc, dt; NVT thermostat
+    as every shipped config) with all host threads; returns dict(mmups, n, loop_s, force_s, binary)"""
+    exe = reference_binary()
+    if exe is None:
+        return None
+    a = (4.0 / RHO) ** (1.0 / 3.0)
+    L = sample_cells * a
+    with tempfile.TemporaryDirectory() as td:
+        cfg = os.path.join(td, "cfg.xml")
+        with open(cfg, "w") as f:
+            f.write(MARDYN_XML.format(dt=DT, steps=steps, temp=TEMP, L=repr(L), rho=RHO, rc=RC))
+        env = dict(os.environ, OMP_NUM_THREADS=str(threads), OMP_PROC_BIND="close", OMP_PLACES="cores")
+        t0 = time.time()
+        p = subprocess.run([exe, cfg, "--steps", str(steps)], cwd=td, env=env, capture_output=True, text=True, timeout=3000)
+        wall = time.time() - t0
+    out = p.stdout + p.stderr
+    if p.returncode != 0:
+        raise RuntimeError("reference MarDyn failed (%d): %s" % (p.returncode, out[-2000:]))
+    n = int(re.search(r"globally inserted molecules:\s*(\d+)", out).group(1))
+    loop_s = float(re.search(r"Computation in main loop took:\s*([0-9.eE+-]+)", out).group(1))
+    m = re.search(r"Force calculation took:\s*([0-9.eE+-]+)", out)
+    vec = re.search(r"VectorizedCellProcessor: using (\S+) intrinsics", out)
+    return dict(mmups=n * steps / loop_s / 1e6, n=n, loop_s=loop_s, force_s=float(m.group(1)) if m else None,
+                binary=os.path.basename(exe), simd=vec.group(1) if vec else "?", wall_s=wall)
+
+
+def run_oracle_port_sample(sample_cells, steps):
+    """fallback when oracle/_ref/MarDyn is absent: the scalar C restatement (oracle/ls1_oracle.c), 1 thread"""
+    from oracle import oracle as O
+    gen = _gen()
+    ids, r, v = gen.fcc_block(sample_cells, rho=RHO, temperature=TEMP)
+    _, L = gen.fcc_box(sample_cells, RHO)
+    n = len(ids)
+    sysm = O.System.single_lj(rc=RC)
+    g = O.grid([0, 0, 0], L, RC, 0)
+    cid = np.zeros(n, dtype=np.uint32)
+    q = np.tile([1.0, 0, 0, 0], (n, 1))
+    z = np.zeros((n, 3))
+    t0 = time.time()
+    O.run(sysm, g, L, cid, r, v, q, z, z, z, steps, DT)
+    dt = time.time() - t0
+    return dict(mmups=n * steps / dt / 1e6, n=n, loop_s=dt)
+
+
+def cpu_baseline(sample_cells=64, steps=10):
+    """reported CPU baseline: the reference on a bounded sample (4*64^3 = 1 048 576 molecules, 10 steps)"""
+    threads = host_cores()
+    res = run_reference_sample(sample_cells, steps, threads)
+    if res is not None:
+        return {"value": round(res["mmups"], 4), "unit": "MMUPS", "cores": threads, "kind": "reference",
+                "sample": "%s (%s), 1CLJ fcc %d molecules x %d steps, OpenMP %d threads, loop %.2f s (force %.2f s)"
+                          % (res["binary"], res["simd"], res["n"], steps, threads, res["loop_s"], res["force_s"] or -1)}
+    res = run_oracle_port_sample(16, 3)
+    return {"value": round(res["mmups"], 4), "unit": "MMUPS", "cores": 1, "kind": "port",
+            "sample": "oracle/ls1_oracle.c scalar port, 1CLJ fcc %d molecules x 3 steps" % res["n"]}
+
+
+def main_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    threads = host_cores()
+    steps = max(args.steps, 1)
+    sample_cells = args.ref_cells
+    res = run_reference_sample(sample_cells, steps, threads)
+    kind = "reference"
+    if res is None:
+        res = run_oracle_port_sample(16, min(steps, 3))
+        kind, threads, steps = "port", 1, min(steps, 3)
+    val = res["mmups"]
+    line = {"impl": "reference", "metric": METRIC, "value": round(val, 4), "unit": "MMUPS", "n_gpus": args.gpus, "steps": steps,
+            "warmup": args.warmup, "ms_per_step": round(1e3 * res["loop_s"] / steps, 3), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": "1CLJ fcc rho*=0.8442 T*=1.44 rc=2.5 dt*=0.002, bounded sample of cfg B: %d molecules per step "
+                                   "(reference's own MultiObjectGenerator fcc lattice)" % res["n"],
+                       "warmup_note": "the reference's prepare_start force pass is its warm-up; its loop timer covers all steps"},
+            "cpu_baseline": {"value": round(val, 4), "unit": "MMUPS", "cores": threads, "kind": kind,
+                             "sample": "%s, %d molecules x %d steps" % (res.get("binary", "oracle port"), res["n"], steps)},
+            "e2e": {"value": round(val, 4), "unit": "MMUPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ----------------------------------------------------------------------------------------------------------
+# the B200 arm
+# ----------------------------------------------------------------------------------------------------------
+def main_b200(args):
+    import torch
+    import torch.distributed as dist
+    ls1g = _pkg()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("launch with torch.distributed.run --nproc-per-node %d (one process per GPU)" % args.gpus)
+        raise SystemExit("--gpus %d does not match WORLD_SIZE %d" % (args.gpus, world))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product path has no CPU fallback)")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    cells_global = global_cells(world, args.cells)
+    shard = make_shard(cells_global, world, rank)
+    n_local = len(shard["id"])
+    vmean = global_mean_velocity(shard["v"], dist if world > 1 else None)
+    shard["v"] -= vmean
+    nt = torch.tensor([float(n_local)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(nt)
+    n_global = int(nt.item())
+
+    cap = int(1.35 * n_local) + 200000
+    c = ls1g.Container(shard["box_max"], RC, box_min=shard["box_min"], global_length=shard["L"], rank_grid=shard["grid"],
+                       rank_coords=shard["coords"], device=local, capacity=cap)
+    c.set_components([ls1g.lj_component()])
+    if world > 1:
+        idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+        if rank == 0:
+            idt = torch.tensor(list(ls1g.comm_unique_id()), dtype=torch.uint8, device="cuda")
+        dist.broadcast(idt, 0)
+        c.comm_init(world, rank, bytes(idt.cpu().tolist()))
+
+    # pinned host mirror (the e2e arm moves these every step)
+    def pinned(shape, dtype):
+        return torch.empty(shape, dtype=dtype, pin_memory=True).numpy()
+    host = dict(id=pinned((cap,), torch.int64).view(np.uint64), cid=pinned((cap,), torch.int32).view(np.uint32),
+                r=pinned((cap, 3), torch.float64), v=pinned((cap, 3), torch.float64), F=pinned((cap, 3), torch.float64))
+    host["id"][:n_local] = shard["id"]
+    host["cid"][:] = 0
+    host["r"][:n_local] = shard["r"]
+    host["v"][:n_local] = shard["v"]
+    del shard["r"], shard["v"]
+
+    c.add_particles(host["id"][:n_local], host["cid"][:n_local], host["r"][:n_local], host["v"][:n_local])
+    c.exchange()
+    u0, w0 = c.traverse_cells()
+    stream = torch.cuda.ExternalStream(c.stream(), device=torch.device("cuda", local))
+
+    # ---- device-resident loop ------------------------------------------------------------------------------
+    if args.warmup > 0:
+        c.run(args.warmup, DT)
+    c.timers(reset=True)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    clocks = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        clocks.start()
+    e0.record(stream)
+    rec = c.run(args.steps, DT)
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    clk = clocks.stop() if rank == 0 else None
+    tm = c.timers(reset=True)
+    n_pairs = c.last_pair_count()
+    mt = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(mt, op=dist.ReduceOp.MAX)
+    ms_max = float(mt.item())
+    value = n_global * args.steps / (ms_max * 1e-3) / 1e6
+
+    # energy conservation over the timed steps (NVE): reported, not timed
+    et = torch.tensor(np.concatenate([rec[:, 0], 0.5 * rec[:, 2]]), dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(et)
+    et = et.cpu().numpy()
+    etot = et[:args.steps] + et[args.steps:]
+    drift = float(abs(etot[-1] - etot[0]) / abs(etot[0])) if args.steps > 1 else 0.0
+
+    # ---- roofline of the pair kernel ---------------------------------------------------------------------------
+    cpd, _ = c.get_grid()
+    c.exchange()                                      # halo copies back for the cell census (not timed)
+    cells_all = c.download(("cell",), include_halo=True)["cell"]
+    n_dist = distance_checks(cells_all, cpd)
+    c.traverse_cells()
+    n_pairs = c.last_pair_count()
+    del cells_all
+    flops = lj_flops(n_dist, n_pairs)
+    force_ms = tm["force"]["ms"] / max(tm["force"]["launches"], 1)
+    peak = ls1g.fp64_peak_tflops(local) if rank == 0 else 0.0
+    achieved = flops / (force_ms * 1e-3) / 1e12 if force_ms > 0 else 0.0
+    launches = sum(t["launches"] for t in tm.values())
+
+    # ---- e2e: the same step through the public API with host buffers ---------------------------------------------
+    def e2e_step(n):
+        c.add_particles(host["id"][:n], host["cid"][:n], host["r"][:n], host["v"][:n])
+        c.set_forces(host["F"][:n])
+        c.run(1, DT, records=True)
+        out = c.download(("id", "r", "v", "F"), out=host)
+        return len(out["id"])
+    c.delete_outer_particles()
+    n_cur = len(c.download(("id", "r", "v", "F"), out=host)["id"])
+    for _ in range(max(1, min(args.warmup, 3))):
+        n_cur = e2e_step(n_cur)
+    k_e2e = max(1, min(args.steps, args.e2e_steps))
+    h2d = d2h = 0
+    barrier()
+    t0 = time.perf_counter()
+    e0.record(stream)
+    for _ in range(k_e2e):
+        h2d += n_cur * (8 + 4 + 24 + 24 + 24)
+        n_cur = e2e_step(n_cur)
+        d2h += n_cur * (8 + 24 + 24 + 24) + 48
+    e1.record(stream)
+    barrier()
+    ms_e2e = max(e0.elapsed_time(e1), (time.perf_counter() - t0) * 1e3)   # host-driven: wall clock and device clock agree
+    mt = torch.tensor([ms_e2e], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(mt, op=dist.ReduceOp.MAX)
+    e2e_val = n_global * k_e2e / (float(mt.item()) * 1e-3) / 1e6
+
+    if rank == 0:
+        cb = cpu_baseline() if (world == 1 and not args.no_cpu_baseline) else None
+        line = {"metric": METRIC, "value": round(value, 2), "unit": "MMUPS", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": round(ms_max / args.steps, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f64", "data": "synthetic",
+                "config": {"workload": "cfg B: 1CLJ fcc lattice rho*=0.8442 T*=1.44 rc=2.5sigma dt*=0.002 NVE, %d^3 unit cells = %d molecules per GPU"
+                                       % (args.cells, 4 * args.cells ** 3),
+                           "n_molecules": n_global, "rank_grid": shard["grid"], "cells_per_dim": cpd,
+                           "l2": "inputs larger than L2 (pos+vel+F = %.0f MB per GPU)" % (n_local * 80 / 1e6),
+                           "nve_rel_energy_drift_over_timed_steps": drift, "upot_per_molecule_t0": u0 / max(n_local, 1)},
+                "e2e": {"value": round(e2e_val, 2), "unit": "MMUPS", "h2d_bytes_per_step": h2d // k_e2e, "d2h_bytes_per_step": d2h // k_e2e,
+                        "steps": k_e2e, "what": "per step: add_particles(id,cid,r,v)+set_forces(F) from pinned host, ls1g_run(1), download(id,r,v,F) to pinned host"},
+                "gpu_launches": int(launches),
+                "roofline": {"bound": "fp64", "kernel": "force_1clj", "achieved": round(achieved, 3), "peak": round(peak, 3), "unit": "TFLOP/s",
+                             "frac": round(achieved / peak, 4) if peak > 0 else None, "traffic": None,
+                             "peak_source": "measured here: dependent-free DFMA kernel (ls1g_measure_fp64_peak); MEASURED_PEAKS.json has no FP64 figure",
+                             "flops_per_launch": flops, "n_dist": n_dist, "n_pairs": n_pairs, "kernel_ms": round(force_ms, 4),
+                             "model": "FlopCounter: 8*N_dist + 41*N_pairs (Newton-3 counts)"},
+                "kernel_ms_per_step": {k: round(t["ms"] / args.steps, 4) for k, t in tm.items()},
+                "clocks": clk}
+        if cb is not None:
+            line["cpu_baseline"] = cb
+        print(json.dumps(line), flush=True)
+    c.close()
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--cells", type=int, default=CELLS_PER_GPU, help="fcc unit cells per dimension per GPU")
+    ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--ref-cells", type=int, default=64, help="fcc unit cells per dimension of the reference arm's sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return main_reference(args)
+    return main_b200(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -122,6 +122,10 @@ int ls1g_debug_cell_pairs(const ls1g_ctx* ctx, uint32_t* triplets, size_t capaci
  * replaces: ParticleContainer::addParticles / clear (LinkedCells.cpp:445-520,596-601). Replaces the content. */
 int ls1g_upload(ls1g_ctx* ctx, size_t n, const uint64_t* id, const uint32_t* cid,
                 const double* r, const double* v, const double* q, const double* L);
+/* replaces: Molecule::setF / setM (molecules/FullMolecule.h) for a restart WITH forces: F (and M, may be NULL)
+ * of the molecules of the directly preceding ls1g_upload, same order.  Makes ls1g_run callable without a
+ * fresh ls1g_traverse (the first half-kick of Leapfrog::transition1to2 needs F(t), Leapfrog.cpp:48-68). */
+int ls1g_upload_forces(ls1g_ctx* ctx, size_t n, const double* F, const double* M);
 /* number of molecules held: owned (non-halo cells) and halo copies */
 int ls1g_count(ls1g_ctx* ctx, uint64_t* n_owned, uint64_t* n_halo);
 /* replaces: ParticleIterator over ALL_CELLS / ONLY_INNER_AND_BOUNDARY + Molecule getters.
@@ -178,9 +182,12 @@ int ls1g_comm_init_local(ls1g_ctx** ctxs, int n);
 int ls1g_exchange_group(ls1g_ctx** ctxs, int n);
 
 /* --- measurement -------------------------------------------------------------------------- */
-enum { LS1G_T_FORCE = 0, LS1G_T_SORT = 1, LS1G_T_INTEGRATE = 2, LS1G_T_EXCHANGE = 3, LS1G_T_COUNT = 4 };
+/* LS1G_T_FORCE brackets ONLY the pair kernel (the roofline kernel); its reductions and the site cache are LS1G_T_AUX */
+enum { LS1G_T_FORCE = 0, LS1G_T_SORT = 1, LS1G_T_INTEGRATE = 2, LS1G_T_EXCHANGE = 3, LS1G_T_AUX = 4, LS1G_T_COUNT = 5 };
 /* accumulated CUDA-event time (ms) and launch count per kernel class since the last reset */
 int ls1g_timers(ls1g_ctx* ctx, double ms[LS1G_T_COUNT], uint64_t launches[LS1G_T_COUNT], int reset);
+/* the cudaStream_t all work of this context is issued on (for CUDA-event timing by the caller) */
+int ls1g_stream(ls1g_ctx* ctx, void** stream);
 /* dependent-free DFMA micro-kernel: measured FP64 FMA peak of this GPU in TFLOP/s (roofline denominator) */
 int ls1g_measure_fp64_peak(int device, double* tflops);
 /* pair statistics of the last traverse: molecule pairs inside the cutoff (counted once) */

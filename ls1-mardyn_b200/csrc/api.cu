@@ -92,6 +92,7 @@ static void free_molecules(ls1g_ctx* c) {
 	}
 	cudaFree(c->F); cudaFree(c->M); cudaFree(c->Vi); cudaFree(c->F_alt); cudaFree(c->M_alt); cudaFree(c->site_cache);
 	cudaFree(c->slot_src); cudaFree(c->slot_code); cudaFree(c->slot_key); cudaFree(c->slot_cell);
+	cudaFree(c->stage); c->stage = nullptr; c->stage_bytes = 0;
 	c->F = c->M = c->Vi = c->F_alt = c->M_alt = nullptr; c->site_cache = nullptr;
 	c->slot_src = nullptr; c->slot_code = nullptr; c->slot_key = nullptr; c->slot_cell = nullptr;
 	c->cap = 0;
@@ -149,6 +150,7 @@ extern "C" int ls1g_create(const ls1g_config* cfg, ls1g_ctx** out) {
 	c->cap = c->n_slots = c->n_owned = c->n_halo = 0; c->sorted = 0; c->forces_valid = 0;
 	memset(&c->cur, 0, sizeof(MolBuf)); memset(&c->alt, 0, sizeof(MolBuf));
 	c->F = c->M = c->Vi = c->F_alt = c->M_alt = nullptr; c->site_cache = nullptr; c->cache_stride = 1;
+	c->stage = nullptr; c->stage_bytes = 0;
 	c->cell_count = c->cell_fill = c->cell_start = c->scan_block = nullptr;
 	c->slot_src = nullptr; c->slot_code = nullptr; c->slot_key = nullptr; c->slot_cell = nullptr;
 	c->d_counters = c->h_counters = nullptr;
@@ -340,36 +342,8 @@ extern "C" int ls1g_upload(ls1g_ctx* c, size_t n, const uint64_t* id, const uint
 	size_t want = c->cfg.capacity ? (size_t)c->cfg.capacity : default_capacity(c, n);
 	if (want < n) LS1G_FAIL("ls1g_upload: more molecules than the configured capacity");
 	if (c->cap < want || c->cap == 0) { if (alloc_molecules(c, std::max<size_t>(want, 1))) return 1; }
-	for (size_t i = 0; i < n; ++i) if (cid[i] >= (uint32_t)c->n_comp) LS1G_FAIL("ls1g_upload: component id out of range");
-	// stage through pinned memory in the device layout
-	double4* h_pos = nullptr; double4* h_q = nullptr;
-	CUDA_TRY(cudaMallocHost((void**)&h_pos, std::max<size_t>(n, 1) * sizeof(double4)));
-	for (size_t i = 0; i < n; ++i) {
-		h_pos[i].x = r[3 * i]; h_pos[i].y = r[3 * i + 1]; h_pos[i].z = r[3 * i + 2];
-		long long bits = (long long)cid[i]; memcpy(&h_pos[i].w, &bits, 8);
-	}
-	cudaError_t e = cudaMemcpyAsync(c->cur.pos, h_pos, n * sizeof(double4), cudaMemcpyHostToDevice, c->stream);
-	if (e == cudaSuccess && v) e = cudaMemcpyAsync(c->cur.vel, v, n * 3 * sizeof(double), cudaMemcpyHostToDevice, c->stream);
-	if (e == cudaSuccess && !v) e = cudaMemsetAsync(c->cur.vel, 0, n * 3 * sizeof(double), c->stream);
-	if (e == cudaSuccess) e = cudaMemcpyAsync(c->cur.id, id, n * sizeof(uint64_t), cudaMemcpyHostToDevice, c->stream);
-	if (e == cudaSuccess) e = cudaMemsetAsync(c->cur.cell, 0, n * sizeof(uint32_t), c->stream);
-	if (e == cudaSuccess && c->has_rot) {
-		e = cudaMallocHost((void**)&h_q, std::max<size_t>(n, 1) * sizeof(double4));
-		if (e == cudaSuccess) {
-			for (size_t i = 0; i < n; ++i) {
-				if (q) { h_q[i].x = q[4 * i]; h_q[i].y = q[4 * i + 1]; h_q[i].z = q[4 * i + 2]; h_q[i].w = q[4 * i + 3]; }
-				else { h_q[i].x = 1.; h_q[i].y = h_q[i].z = h_q[i].w = 0.; }
-			}
-			e = cudaMemcpyAsync(c->cur.q, h_q, n * sizeof(double4), cudaMemcpyHostToDevice, c->stream);
-		}
-		if (e == cudaSuccess && L) e = cudaMemcpyAsync(c->cur.L, L, n * 3 * sizeof(double), cudaMemcpyHostToDevice, c->stream);
-		if (e == cudaSuccess && !L) e = cudaMemsetAsync(c->cur.L, 0, n * 3 * sizeof(double), c->stream);
-		if (e == cudaSuccess) e = cudaMemsetAsync(c->M, 0, n * 3 * sizeof(double), c->stream);
-	}
-	if (e == cudaSuccess) e = cudaMemsetAsync(c->F, 0, n * 3 * sizeof(double), c->stream);
-	if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
-	cudaFreeHost(h_pos); if (h_q) cudaFreeHost(h_q);
-	if (e != cudaSuccess) LS1G_FAIL(std::string("ls1g_upload: ") + cudaGetErrorString(e));
+	if (k_upload(c, n, id, cid, r, v, q, L)) return 1;
+	c->n_uploaded = n;
 	c->n_slots = c->n_owned = n; c->n_halo = 0; c->sorted = 0; c->forces_valid = 0;
 	return 0;
 }
@@ -389,52 +363,26 @@ extern "C" int ls1g_download(ls1g_ctx* c, int mask, int include_halo, size_t cap
 	size_t n_ret = halo_ok ? c->n_owned + c->n_halo : c->n_owned;
 	*n_out = n_ret;
 	if (capacity < n_ret) LS1G_FAIL("ls1g_download: capacity too small");
-	if (ns == 0) return 0;
-	std::vector<uint32_t> cell(ns);
-	std::vector<double4> p4;
-	std::vector<double> tmp;
-	std::vector<uint64_t> tid;
+	(void)ns;
 	CUDA_TRY(cudaStreamSynchronize(c->stream));
-	CUDA_TRY(cudaMemcpy(cell.data(), c->cur.cell, ns * sizeof(uint32_t), cudaMemcpyDeviceToHost));
-	std::vector<uint32_t> keep; keep.reserve(n_ret);
-	for (size_t s = 0; s < ns; ++s) if (halo_ok || !(cell[s] & HALO_FLAG)) keep.push_back((uint32_t)s);
-	if (keep.size() != n_ret) LS1G_FAIL("ls1g_download: internal slot bookkeeping mismatch");
-	if ((mask & (LS1G_F_R | LS1G_F_CID))) {
-		p4.resize(ns);
-		CUDA_TRY(cudaMemcpy(p4.data(), c->cur.pos, ns * sizeof(double4), cudaMemcpyDeviceToHost));
-		for (size_t k = 0; k < n_ret; ++k) {
-			const double4& p = p4[keep[k]];
-			if ((mask & LS1G_F_R) && out->r) { out->r[3 * k] = p.x; out->r[3 * k + 1] = p.y; out->r[3 * k + 2] = p.z; }
-			if ((mask & LS1G_F_CID) && out->cid) { long long b; memcpy(&b, &p.w, 8); out->cid[k] = (uint32_t)b; }
-		}
-	}
-	if ((mask & LS1G_F_ID) && out->id) {
-		tid.resize(ns);
-		CUDA_TRY(cudaMemcpy(tid.data(), c->cur.id, ns * sizeof(uint64_t), cudaMemcpyDeviceToHost));
-		for (size_t k = 0; k < n_ret; ++k) out->id[k] = tid[keep[k]];
-	}
-	if ((mask & LS1G_F_CELL) && out->cell)
-		for (size_t k = 0; k < n_ret; ++k) out->cell[k] = c->sorted ? (cell[keep[k]] & ~HALO_FLAG) : 0u;
-	auto get3 = [&](const double* dev, double* dst) -> int {
-		if (!dst) return 0;
-		if (!dev) { for (size_t k = 0; k < 3 * n_ret; ++k) dst[k] = 0.; return 0; }
-		tmp.resize(ns * 3);
-		CUDA_TRY(cudaMemcpy(tmp.data(), dev, ns * 3 * sizeof(double), cudaMemcpyDeviceToHost));
-		for (size_t k = 0; k < n_ret; ++k) for (int d = 0; d < 3; ++d) dst[3 * k + d] = tmp[3 * (size_t)keep[k] + d];
-		return 0;
-	};
-	if ((mask & LS1G_F_V) && get3(c->cur.vel, out->v)) return 1;
-	if ((mask & LS1G_F_L) && get3(c->has_rot ? c->cur.L : nullptr, out->L)) return 1;
-	if ((mask & LS1G_F_F) && get3(c->F, out->F)) return 1;
-	if ((mask & LS1G_F_M) && get3(c->has_rot ? c->M : nullptr, out->M)) return 1;
-	if ((mask & LS1G_F_VI) && get3(c->Vi, out->Vi)) return 1;
-	if ((mask & LS1G_F_Q) && out->q) {
-		if (c->has_rot) {
-			p4.resize(ns);
-			CUDA_TRY(cudaMemcpy(p4.data(), c->cur.q, ns * sizeof(double4), cudaMemcpyDeviceToHost));
-			for (size_t k = 0; k < n_ret; ++k) { const double4& p = p4[keep[k]]; out->q[4 * k] = p.x; out->q[4 * k + 1] = p.y; out->q[4 * k + 2] = p.z; out->q[4 * k + 3] = p.w; }
-		} else
-			for (size_t k = 0; k < n_ret; ++k) { out->q[4 * k] = 1.; out->q[4 * k + 1] = out->q[4 * k + 2] = out->q[4 * k + 3] = 0.; }
-	}
+	return k_download(c, mask, halo_ok ? 1 : 0, n_ret, out);
+}
+
+// Molecule::setF / setM for the molecules of the last ls1g_upload, same order (restart with forces:
+// the leapfrog half-kick of the next step needs F(t), Leapfrog.cpp:48-68)
+extern "C" int ls1g_upload_forces(ls1g_ctx* c, size_t n, const double* F, const double* M) {
+	if (!c) LS1G_FAIL("null context");
+	if (n != c->n_uploaded || c->sorted || c->n_slots != n) LS1G_FAIL("ls1g_upload_forces: call directly after ls1g_upload with the same n");
+	if (n && !F) LS1G_FAIL("ls1g_upload_forces: F is required");
+	CUDA_TRY(cudaSetDevice(c->cfg.device));
+	if (k_upload_forces(c, n, F, M)) return 1;
+	c->forces_valid = 1;
+	return 0;
+}
+
+// the CUDA stream all work of this context is issued on (cudaStream_t), for event timing by the caller
+extern "C" int ls1g_stream(ls1g_ctx* c, void** stream) {
+	if (!c || !stream) LS1G_FAIL("null argument");
+	*stream = (void*)c->stream;
 	return 0;
 }

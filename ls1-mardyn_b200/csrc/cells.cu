@@ -288,6 +288,17 @@ int k_cell_index(ls1g_ctx* c, size_t n, const double* d_pts, uint32_t* d_out) {
 	return 0;
 }
 
+// exclusive scan over the n_cells entries of `in` -> out[0..n_cells]; the total also lands in d_counters[0]
+int ls1g_scan_cells(ls1g_ctx* c, const uint32_t* in, uint32_t* out) {
+	const int nc = c->grid.n_cells;
+	int nb = (nc + SCAN_ITEMS - 1) / SCAN_ITEMS;
+	scan_reduce_kernel<<<nb, SCAN_THREADS, 0, c->stream>>>(in, nc, c->scan_block);
+	scan_blocks_kernel<<<1, 1024, 0, c->stream>>>(c->scan_block, nb, c->d_counters);
+	scan_apply_kernel<<<nb, SCAN_THREADS, 0, c->stream>>>(in, nc, c->scan_block, out);
+	CUDA_TRY(cudaGetLastError());
+	return 0;
+}
+
 int k_sort(ls1g_ctx* c, int make_images) {
 	const Grid& g = c->grid;
 	const int nc = g.n_cells;
@@ -297,10 +308,7 @@ int k_sort(ls1g_ctx* c, int make_images) {
 	CUDA_TRY(cudaMemsetAsync(c->cell_fill, 0, sizeof(uint32_t) * (nc + 1), c->stream));
 	int launches = 0;
 	if (n) { bin_kernel<<<nblk(n, 256), 256, 0, c->stream>>>(g, n, c->cur.pos, c->cur.cell, c->cell_count, make_images); ++launches; }
-	int nb = (nc + SCAN_ITEMS - 1) / SCAN_ITEMS;
-	scan_reduce_kernel<<<nb, SCAN_THREADS, 0, c->stream>>>(c->cell_count, nc, c->scan_block);
-	scan_blocks_kernel<<<1, 1024, 0, c->stream>>>(c->scan_block, nb, c->d_counters);
-	scan_apply_kernel<<<nb, SCAN_THREADS, 0, c->stream>>>(c->cell_count, nc, c->scan_block, c->cell_start);
+	if (ls1g_scan_cells(c, c->cell_count, c->cell_start)) return 1;
 	launches += 3;
 	CUDA_TRY(cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
 	CUDA_TRY(cudaStreamSynchronize(c->stream));

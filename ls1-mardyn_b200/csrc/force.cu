@@ -249,7 +249,9 @@ __global__ void __launch_bounds__(256) force_finalize_kernel(const double* __res
 static inline unsigned nblk(size_t n, unsigned t) { return (unsigned)((n + t - 1) / t); }
 
 int k_force_finalize(ls1g_ctx* c, size_t nb) {
+	timer_start(c, LS1G_T_AUX);
 	force_finalize_kernel<<<1, 256, 0, c->stream>>>(c->partials, nb, c->d_scalars);
+	timer_stop(c, LS1G_T_AUX, 1);
 	CUDA_TRY(cudaGetLastError());
 	return 0;
 }
@@ -260,21 +262,21 @@ int k_forces(ls1g_ctx* c) {
 	size_t n = c->n_slots;
 	unsigned nb = nblk(n, FORCE_THREADS);
 	if (ls1g_ensure_partials(c, nb ? nb : 1, 5)) return 1;
-	timer_start(c, LS1G_T_FORCE);
-	int launches = 1;
 	if (n) {
+		timer_start(c, LS1G_T_AUX);
 		site_cache_kernel<<<nblk(n, 256), 256, 0, c->stream>>>(n, c->cur.pos, c->cur.q, c->comps, c->sites, c->site_cache, c->cache_stride);
+		timer_stop(c, LS1G_T_AUX, 1);
 		ForceArgs a;
 		a.g = c->grid; a.n = n; a.pos = c->cur.pos; a.cell = c->cur.cell; a.cell_start = c->cell_start;
 		a.comps = c->comps; a.cache = c->site_cache; a.stride = c->cache_stride;
 		a.eps24 = c->eps24; a.sig2 = c->sig2; a.shift6 = c->shift6; a.S = c->S_lj;
 		a.rc2 = c->rc2; a.rclj2 = c->rclj2; a.epsRFInvrc3 = c->epsRFInvrc3;
 		a.F = c->F; a.M = c->M; a.Vi = c->Vi; a.partials = c->partials;
+		timer_start(c, LS1G_T_FORCE);
 		force_generic_kernel<<<nb, FORCE_THREADS, 0, c->stream>>>(a);
-		launches += 2;
+		timer_stop(c, LS1G_T_FORCE, 1);
 	}
 	if (k_force_finalize(c, nb)) return 1;
 	CUDA_TRY(cudaGetLastError());
-	timer_stop(c, LS1G_T_FORCE, launches);
 	return 0;
 }

@@ -72,18 +72,16 @@ int k_forces_1clj(ls1g_ctx* c) {
 	size_t n = c->n_slots;
 	unsigned nb = nblk(n, LJ1_THREADS);
 	if (ls1g_ensure_partials(c, nb ? nb : 1, 5)) return 1;
-	timer_start(c, LS1G_T_FORCE);
-	int launches = 1;
 	if (n) {
 		LJ1Args a;
 		a.g = c->grid; a.n = n; a.pos = c->cur.pos; a.cell = c->cur.cell; a.cell_start = c->cell_start;
 		a.eps24 = c->eps24_h[0]; a.sig2 = c->sig2_h[0]; a.shift6 = c->shift6_h[0]; a.rclj2 = c->rclj2;
 		a.F = c->F; a.Vi = c->Vi; a.partials = c->partials;
+		timer_start(c, LS1G_T_FORCE);
 		force_1clj_simple_kernel<<<nb, LJ1_THREADS, 0, c->stream>>>(a);
-		++launches;
+		timer_stop(c, LS1G_T_FORCE, 1);
 	}
 	if (k_force_finalize(c, nb)) return 1;
 	CUDA_TRY(cudaGetLastError());
-	timer_stop(c, LS1G_T_FORCE, launches);
 	return 0;
 }

@@ -91,6 +91,7 @@ struct ls1g_ctx {
 	size_t cap;                             // allocated slots
 	size_t n_slots;                         // slots in use (owned + halo copies), cell-sorted if sorted
 	size_t n_owned, n_halo;
+	size_t n_uploaded;                      // n of the last ls1g_upload (ls1g_upload_forces refers to it)
 	int    sorted;                          // cell[] / cell_start valid
 	int    forces_valid;
 	MolBuf cur, alt;                        // double buffer for the sort
@@ -98,6 +99,7 @@ struct ls1g_ctx {
 	double *F_alt, *M_alt;                  // targets when forces are carried through a re-sort
 	double4* site_cache;                    // [cap*cache_stride] world-frame site data (multi-site path)
 	int     cache_stride;
+	void*   stage; size_t stage_bytes;      // device staging area of the host<->device transfers (transfer.cu)
 
 	// cells / sort scratch
 	uint32_t *cell_count, *cell_fill, *cell_start;   // [n_cells+1]
@@ -135,6 +137,11 @@ int  k_cell_index(ls1g_ctx* c, size_t n, const double* d_pts, uint32_t* d_out);
 int  k_sort(ls1g_ctx* c, int make_images);      // bin (+periodic images) -> scan -> scatter -> gather, swaps cur/alt
 int  k_drop_halo(ls1g_ctx* c);                  // deleteOuterParticles
 int  k_debug_cell_pairs(const ls1g_ctx* c, uint32_t* h_triplets, size_t capacity, size_t* n_out);
+int  ls1g_scan_cells(ls1g_ctx* c, const uint32_t* in, uint32_t* out);   // exclusive scan over n_cells entries -> out[n_cells+1]
+// transfer.cu
+int  k_upload(ls1g_ctx* c, size_t n, const uint64_t* id, const uint32_t* cid, const double* r, const double* v, const double* q, const double* L);
+int  k_upload_forces(ls1g_ctx* c, size_t n, const double* F, const double* M);
+int  k_download(ls1g_ctx* c, int mask, int include_halo, size_t n_ret, ls1g_fields* out);
 // integrate.cu
 int  k_scale(ls1g_ctx* c, double bt, double br);
 int  k_post_pre(ls1g_ctx* c, double dt, int do_post, int do_pre, int thermostat, double target_T);

@@ -1,0 +1,379 @@
+"""GPU parity tests: the CUDA path (through the C ABI, include/ls1g.h) against (a) the golden outputs of the
+unmodified reference (tests/golden/*.npz) and (b) the CPU oracle on seeded inputs.
+
+Bars (BASELINE.json north_star): cell assignment, halo images and cell-pair enumeration bit-exact; per-molecule
+F, M, Vi, upot, virial within 1e-10 relative (double build), stated per case below."""
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+from tests.helpers import golden_cases, load, system_and_grid, vec_rel_err, initial_state
+from tests.gpu_helpers import ls1g, container_of, by_id, fcc_lattice, random_quaternions
+
+pytestmark = pytest.mark.gpu
+
+FORCE_CASES = golden_cases("vcp_") + golden_cases("per_") + golden_cases("ex_")
+# see tests/test_oracle_golden.py: the CO2 charge sites cancel to 1e-4 of their magnitude
+FORCE_TOL = {"ex_CO2": 2e-9}
+
+
+def scalar_close(a, b, tol, floor=0.0):
+    return abs(a - b) <= tol * max(abs(b), floor)
+
+
+@pytest.mark.parametrize("name", golden_cases("cellindex_"))
+def test_cell_index_bit_exact(name):
+    d = load(name)
+    with ls1g.Container(d["box"], float(d["rc"][0]), grid_mode=int(d["mode"][0])) as c:
+        cpd, cl = c.get_grid()
+        assert cpd == list(d["cells_per_dim"])
+        assert np.array_equal(np.array(cl), d["cell_length"])
+        assert np.array_equal(c.cell_index_of_points(d["points"]), d["cell_index"])
+        assert np.array_equal(c.cell_index_of_points(d["points"], host=True), d["cell_index"])
+
+
+@pytest.mark.parametrize("name", FORCE_CASES)
+def test_cell_pairs_bit_exact(name):
+    d = load(name)
+    with container_of(d) as c:
+        cp = c.cell_pairs()
+    cp = cp[np.lexsort((cp[:, 2], cp[:, 1], cp[:, 0]))]
+    assert np.array_equal(cp, d["cellpairs"])
+
+
+def _load_into(c, d, periodic):
+    if periodic:
+        st = initial_state(d)
+        c.add_particles(st["id"], st["cid"], st["r"], st["v"], st["q"], st["L"])
+        c.exchange()
+        return st
+    inorder = np.argsort(d["in_id"])
+    c.add_particles(d["in_id"][inorder], d["in_cid"][inorder], d["in_r"][inorder], d["in_v"][inorder],
+                    d["in_q"][inorder], d["in_L"][inorder])
+    c.update()
+    return None
+
+
+@pytest.mark.parametrize("name", FORCE_CASES)
+def test_forces_match_reference(name):
+    d = load(name)
+    periodic = bool(d["meta"][0])
+    tol = FORCE_TOL.get(name, 1e-10)
+    with container_of(d) as c:
+        _load_into(c, d, periodic)
+        upot, virial = c.traverse_cells()
+        out = by_id(c.download(("id", "cid", "r", "F", "M", "Vi", "cell")))
+        allm = c.download(("id", "r", "cell"), include_halo=True)
+    own = d["f_owned"].astype(bool)
+    order = np.argsort(d["f_id"][own])
+    ref = {k: d["f_" + k][own][order] for k in ("id", "r", "F", "M", "Vi", "cell")}
+    assert np.array_equal(out["id"], ref["id"].astype(np.uint64))
+    assert np.array_equal(out["r"], ref["r"])
+    assert np.array_equal(out["cell"], ref["cell"].astype(np.uint32))          # cell assignment bit-exact
+    if periodic:                                                               # halo images bit-exact (id, r, cell)
+        mine = np.column_stack([allm["id"].astype(np.float64), allm["r"], allm["cell"].astype(np.float64)])
+        refa = np.column_stack([d["f_id"].astype(np.float64), d["f_r"], d["f_cell"].astype(np.float64)])
+        mine = mine[np.lexsort(mine.T[::-1])]
+        refa = refa[np.lexsort(refa.T[::-1])]
+        assert mine.shape == refa.shape and np.array_equal(mine, refa)
+    if name == "vcp_F0":
+        assert np.abs(out["F"] - ref["F"]).max() < 1e-8
+    else:
+        assert vec_rel_err(out["F"], ref["F"]) < tol
+        assert vec_rel_err(out["M"], ref["M"]) < tol
+        assert vec_rel_err(out["Vi"], ref["Vi"]) < tol
+    u, w = d["upot_virial"]
+    assert scalar_close(upot, u, tol, 1.0 if name == "vcp_U0" else 1e-12)
+    assert scalar_close(virial, w, tol, 1e-3 if name == "vcp_F0" else 1e-300)
+
+
+def test_known_answers_u0_f0():
+    """VectorizedCellProcessorTest.cpp:45-134"""
+    d = load("vcp_U0")
+    with container_of(d) as c:
+        _load_into(c, d, False)
+        u, w = c.traverse_cells()
+        F = c.download(("F",))["F"]
+    assert np.allclose(np.abs(F[:, :2]), 24.0, atol=1e-8) and np.allclose(F[:, 2], 0.0)
+    assert abs(u) < 1e-8 and abs(w - 96.0) < 1e-8
+    d = load("vcp_F0")
+    with container_of(d) as c:
+        _load_into(c, d, False)
+        u, w = c.traverse_cells()
+        F = c.download(("F",))["F"]
+    assert np.abs(F).max() < 1e-6 and abs(u + 4.0) < 1e-8 and abs(w) < 1e-6
+
+
+@pytest.mark.parametrize("name", [n for n in FORCE_CASES if int(load(n)["meta"][2]) > 0])
+@pytest.mark.parametrize("fused", [True, False])
+def test_time_loop_matches_reference(name, fused):
+    """Leapfrog + rigid-body rotation + periodic exchange + forces, NVE.  fused: device-resident ls1g_run;
+    otherwise the per-operator calls in Simulation::simulate order."""
+    d = load(name)
+    steps, dt = int(d["meta"][2]), float(d["dt"][0])
+    with container_of(d) as c:
+        _load_into(c, d, True)
+        c.traverse_cells()
+        if fused:
+            series = c.run(steps, dt)[:, :4]
+        else:
+            series = np.zeros((steps, 4))
+            for s in range(steps):
+                c.event_new_timestep(dt)
+                c.exchange()
+                series[s, :2] = c.traverse_cells()
+                c.delete_outer_particles()
+                series[s, 2:] = c.event_forces_calculated(dt)[:2]
+        out = by_id(c.download(("id", "r", "v", "q", "L", "F", "M")))
+    tol = 1e-9 if name == "ex_CO2" else 1e-11
+    assert np.array_equal(out["id"], d["post_id"].astype(np.uint64))
+    for k in ("r", "v", "q", "L"):
+        ref = d["post_" + k]
+        assert np.abs(out[k] - ref).max() <= tol * max(np.abs(ref).max(), 1e-300), k
+    assert vec_rel_err(out["F"], d["post_F"]) < 100 * tol
+    assert vec_rel_err(out["M"], d["post_M"]) < 100 * tol
+    ser = d["series"]
+    assert np.all(np.abs(series - ser) <= 100 * tol * np.maximum(np.abs(ser).max(axis=0), 1e-300))
+
+
+# ------------------------------------------------------------------------------------------------------
+# seeded inputs against the oracle
+# ------------------------------------------------------------------------------------------------------
+def _oracle_forces(sysm, g, box, cid, r, q):
+    r2, src, hr = O.exchange(g, box, r)
+    all_r = np.concatenate([r2, hr])
+    all_cid = np.concatenate([cid, cid[src]])
+    all_q = np.concatenate([q, q[src]])
+    res = O.forces(sysm, g, all_cid, all_r, all_q)
+    n = len(r)
+    return {k: (res[k][:n] if isinstance(res[k], np.ndarray) else res[k]) for k in res}
+
+
+def test_1clj_liquid_vs_oracle():
+    """cfg B in small: perturbed fcc 1CLJ, rho*=0.8442, rc=2.5 (13 molecules per cell): the specialised 1CLJ kernel"""
+    r, v, box = fcc_lattice(12, seed=3)
+    rng = np.random.default_rng(5)
+    r = np.mod(r + rng.normal(scale=0.08, size=r.shape), box)
+    n = len(r)
+    sysm = O.System.single_lj(rc=2.5)
+    g = O.grid([0, 0, 0], box, 2.5, 0)
+    cid = np.zeros(n, dtype=np.uint32)
+    q = np.tile([1.0, 0, 0, 0], (n, 1))
+    ref = _oracle_forces(sysm, g, box, cid, r, q)
+    with ls1g.Container(box, 2.5) as c:
+        c.set_components([ls1g.lj_component()])
+        c.add_particles(np.arange(n), cid, r, v)
+        c.exchange()
+        u, w = c.traverse_cells()
+        out = by_id(c.download(("id", "F", "Vi")))
+        # molecule pairs inside the cutoff, each once (minimum image, brute force)
+        n_in = 0
+        for a in range(0, n, 512):
+            dd = r[a:a + 512, None, :] - r[None, :, :]
+            dd -= box * np.round(dd / box)
+            n_in += int(((dd * dd).sum(axis=2) < 2.5 * 2.5).sum()) - len(dd)
+        assert c.last_pair_count() == n_in // 2
+    assert vec_rel_err(out["F"], ref["F"]) < 1e-10
+    assert vec_rel_err(out["Vi"], ref["Vi"]) < 1e-10
+    assert scalar_close(u, ref["upot"], 1e-10) and scalar_close(w, ref["virial"], 1e-10)
+
+
+def test_mixture_vs_oracle():
+    """two components (2CLJ+quadrupole and 3LJ+dipole+charges) with xi/eta mixing, rc_LJ < rc, random orientations"""
+    rng = np.random.default_rng(11)
+    box = np.array([21.0, 17.5, 19.0])
+    n = 1500
+    # jittered grid so that no two molecules overlap
+    m = int(np.ceil(n ** (1 / 3)))
+    gi = np.stack(np.meshgrid(*[np.arange(m)] * 3, indexing="ij"), axis=-1).reshape(-1, 3)[:n]
+    r = (gi + 0.5 + rng.uniform(-0.2, 0.2, size=(n, 3))) * (box / m)
+    cid = rng.integers(0, 2, size=n).astype(np.uint32)
+    q = random_quaternions(n, rng)
+    counts = [[2, 0, 0, 1, 2, 0], [3, 2, 1, 0, 3, 2]]
+    scal = [[2.0, 0.5, 0.5, 0.0], [3.0, 0.4, 0.6, 0.9]]
+    lj = [[0, 0, -0.3, 1, 1.0, 1.0, 0.0], [0, 0, 0.3, 1, 1.0, 1.0, 0.0],
+          [0.2, 0, 0, 1, 0.8, 0.9, 0.0], [-0.2, 0.1, 0, 1, 1.2, 1.1, 0.0], [0, -0.2, 0.2, 1, 0.5, 0.8, 0.0]]
+    qu = [[0, 0, 0, 0, 0, 1, 1.5]]
+    ch = [[0.25, 0, 0, 0, 0.4], [-0.25, 0, 0, 0, -0.4]]
+    di = [[0, 0.1, 0, 1, 0, 0, 0.7]]
+    mix = [0.95, 1.03]
+    sysm = O.System(counts, scal, lj, ch, di, qu, mix, 1e10, 3.2, 2.6)
+    g = O.grid([0, 0, 0], box, 3.2, 0)
+    ref = _oracle_forces(sysm, g, box, cid, r, q)
+    with ls1g.Container(box, 3.2, lj_cutoff=2.6) as c:
+        c.set_components(ls1g.components_from_tables(counts, scal, lj, ch, di, qu), mix)
+        c.add_particles(np.arange(n), cid, r, None, q, None)
+        c.exchange()
+        u, w = c.traverse_cells()
+        out = by_id(c.download(("id", "F", "M", "Vi")))
+    assert vec_rel_err(out["F"], ref["F"]) < 1e-10
+    assert vec_rel_err(out["M"], ref["M"]) < 1e-10
+    assert vec_rel_err(out["Vi"], ref["Vi"]) < 1e-10
+    assert scalar_close(u, ref["upot"], 1e-10) and scalar_close(w, ref["virial"], 1e-10)
+
+
+def test_empty_and_single_molecule():
+    """edge cases: empty container, one molecule (no partner), ragged cells"""
+    with ls1g.Container([10.0, 10.0, 10.0], 2.5) as c:
+        c.set_components([ls1g.lj_component()])
+        c.add_particles(np.zeros(0, dtype=np.uint64), np.zeros(0, dtype=np.uint32), np.zeros((0, 3)))
+        c.exchange()
+        assert c.traverse_cells() == (0.0, 0.0)
+        assert c.count() == (0, 0)
+        c.add_particles([7], [0], [[0.1, 9.9, 5.0]], [[1.0, 0.0, 0.0]])
+        c.exchange()
+        assert c.count() == (1, 3)          # images across the x and y faces and the xy edge
+        u, w = c.traverse_cells()
+        assert u == 0.0 and w == 0.0
+        rec = c.run(3, 0.5)
+        out = c.download(("id", "r", "v", "F"))
+        assert np.array_equal(out["F"], np.zeros((1, 3)))
+        assert np.allclose(out["r"], [[1.6, 9.9, 5.0]]) and rec[-1, 4] == 1
+
+
+def test_leaving_molecules_wrap():
+    """molecules moved outside the box re-enter on the other side (handleDomainLeavingParticles), ids conserved"""
+    r, v, box = fcc_lattice(6, seed=2)
+    n = len(r)
+    sysm = O.System.single_lj(rc=2.5)
+    g = O.grid([0, 0, 0], box, 2.5, 0)
+    rng = np.random.default_rng(4)
+    r = r + rng.uniform(-1.0, 1.0, size=r.shape)       # some leave through faces, edges and corners
+    r_wrapped, src, hr = O.exchange(g, box, r)
+    with ls1g.Container(box, 2.5) as c:
+        c.set_components([ls1g.lj_component()])
+        c.add_particles(np.arange(n), np.zeros(n, dtype=np.uint32), r, v)
+        c.exchange()
+        out = by_id(c.download(("id", "r", "cell")))
+        allm = c.download(("id", "r"), include_halo=True)
+    assert np.array_equal(out["r"], r_wrapped)
+    assert np.array_equal(out["cell"], O.cell_indices(g, r_wrapped))
+    mine = np.column_stack([allm["id"].astype(np.float64), allm["r"]])
+    ref = np.column_stack([np.concatenate([np.arange(n), src]).astype(np.float64), np.concatenate([r_wrapped, hr])])
+    assert np.array_equal(mine[np.lexsort(mine.T[::-1])], ref[np.lexsort(ref.T[::-1])])
+
+
+# ------------------------------------------------------------------------------------------------------
+# size-independent properties at a larger size
+# ------------------------------------------------------------------------------------------------------
+def test_nve_properties_large():
+    """256k-molecule 1CLJ fcc liquid: Newton 3 (sum F = 0), momentum and molecule count conserved, NVE energy
+    drift small over 200 steps, re-sort idempotent, deterministic (bitwise identical repeat)."""
+    r, v, box = fcc_lattice(40, seed=9)
+    n = len(r)
+    dt = 0.002
+
+    def one():
+        with ls1g.Container(box, 2.5) as c:
+            c.set_components([ls1g.lj_component()])
+            c.add_particles(np.arange(n), np.zeros(n, dtype=np.uint32), r, v)
+            c.exchange()
+            u0, _ = c.traverse_cells()
+            first = c.download(("id", "r", "F"))
+            c.exchange()                                   # idempotent: same order, same content
+            again = c.download(("id", "r"))
+            assert np.array_equal(first["id"], again["id"]) and np.array_equal(first["r"], again["r"])
+            c.traverse_cells()
+            rec = c.run(200, dt)
+            return u0, first, rec, by_id(c.download(("id", "r", "v", "F")))
+
+    u0, first, rec, out = one()
+    fmax = np.abs(first["F"]).max()
+    assert fmax == 0.0 or np.abs(first["F"].sum(axis=0)).max() < 1e-9 * max(fmax, 1.0) * np.sqrt(n)
+    assert np.all(rec[:, 4] == n)
+    e = rec[:, 0] + 0.5 * rec[:, 2]                        # Upot + Ekin (summv2 = sum m v^2)
+    assert abs(e[-1] - e[0]) < 2e-4 * abs(e[0])            # leapfrog, dt*=0.002
+    assert np.abs(out["v"].sum(axis=0)).max() < 1e-8 * n
+    assert np.abs(out["F"].sum(axis=0)).max() < 1e-9 * np.abs(out["F"]).max() * np.sqrt(n)
+    u0b, _, recb, outb = one()
+    assert u0 == u0b and np.array_equal(rec, recb) and np.array_equal(out["r"], outb["r"])
+
+
+def test_thermostat_run_holds_temperature():
+    """NVT: Domain::calculateGlobalValues betas (Domain.cpp:226-247) drive T to the target"""
+    r, v, box = fcc_lattice(10, seed=1, temperature=1.0)
+    n = len(r)
+    with ls1g.Container(box, 2.5) as c:
+        c.set_components([ls1g.lj_component()])
+        c.add_particles(np.arange(n), np.zeros(n, dtype=np.uint32), r, v)
+        c.exchange()
+        c.traverse_cells()
+        rec = c.run(50, 0.002, target_temperature=1.3)
+        T = rec[:, 2] / (3 * rec[:, 4])
+        assert abs(T[-1] - 1.3) < 0.05
+        # oracle with the same thermostat rule
+        sysm = O.System.single_lj(rc=2.5)
+        g = O.grid([0, 0, 0], box, 2.5, 0)
+        q = np.tile([1.0, 0, 0, 0], (n, 1))
+        f0 = _oracle_forces(sysm, g, box, np.zeros(n, dtype=np.uint32), r, q)
+        ref = O.run(sysm, g, box, np.zeros(n, dtype=np.uint32), r, v, q, np.zeros((n, 3)), f0["F"], np.zeros((n, 3)),
+                    50, 0.002, 1.3)
+        assert np.all(np.abs(rec[:, :3] - ref["series"][:, :3]) <= 1e-9 * np.abs(ref["series"][:, :3]).max(axis=0))
+
+
+# ------------------------------------------------------------------------------------------------------
+# block decomposition: several ranks as contexts of this process (same pack/unpack kernels as the NCCL path)
+# ------------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("n_ranks", [2, 4, 8])
+@pytest.mark.parametrize("case", ["1clj", "ex_CO2"])
+def test_decomposed_matches_single_rank(n_ranks, case):
+    if case == "1clj":
+        r, v, box = fcc_lattice(12, seed=6)
+        rng = np.random.default_rng(8)
+        r = np.mod(r + rng.normal(scale=0.05, size=r.shape), box)
+        n = len(r)
+        ids, cid, q, L = np.arange(n), np.zeros(n, dtype=np.uint32), None, None
+        rc, rclj, comps, mix, dt = 2.5, 2.5, [ls1g.lj_component()], (), 0.004
+    else:
+        d = load(case)
+        st = initial_state(d)
+        ids, cid, r, v, q, L = st["id"], st["cid"], st["r"], st["v"], st["q"], st["L"]
+        box, rc, rclj, dt = d["box"], float(d["rc"][0]), float(d["rc"][1]), float(d["dt"][0])
+        from tests.gpu_helpers import components_of
+        comps, mix = components_of(d), d["mixcoeff"]
+        n = len(ids)
+    steps = 4
+    with ls1g.Container(box, rc, lj_cutoff=rclj) as c:
+        c.set_components(comps, mix)
+        c.add_particles(ids, cid, r, v, q, L)
+        c.exchange()
+        c.traverse_cells()
+        ref_rec = c.run(steps, dt)
+        ref = by_id(c.download(("id", "r", "v", "F", "M", "q", "L")))
+    ranks = []
+    try:
+        for rank in range(n_ranks):
+            grid, coords = ls1g.decomp_grid(n_ranks, rank)
+            bmin, bmax = ls1g.decomp_box(grid, coords, box)
+            c = ls1g.Container(bmax, rc, box_min=bmin, lj_cutoff=rclj, global_length=box, rank_grid=grid,
+                               rank_coords=coords, capacity=4 * n + 1024)
+            c.set_components(comps, mix)
+            mine = np.all((r >= np.array(bmin)) & (r < np.array(bmax)), axis=1)
+            c.add_particles(ids[mine], cid[mine], r[mine], v[mine], None if q is None else q[mine], None if L is None else L[mine])
+            ranks.append(c)
+        ls1g.comm_init_local(ranks)
+        ls1g.exchange_group(ranks)
+        rec = np.zeros((steps, 6))
+        for c in ranks:
+            c.traverse_cells()
+        for s in range(steps):
+            for c in ranks:
+                c.event_new_timestep(dt)
+            ls1g.exchange_group(ranks)
+            for c in ranks:
+                u, w = c.traverse_cells()
+                c.delete_outer_particles()
+                a, b, nn, rd = c.event_forces_calculated(dt)
+                rec[s] += [u, w, a, b, nn, rd]
+        parts = [c.download(("id", "r", "v", "F", "M", "q", "L")) for c in ranks]
+    finally:
+        for c in ranks:
+            c.close()
+    out = by_id({k: np.concatenate([p[k] for p in parts]) for k in parts[0]})
+    assert np.array_equal(out["id"], ref["id"])
+    assert np.all(rec[:, 4] == n)
+    tol = 1e-9 if case == "ex_CO2" else 1e-11
+    for k in ("r", "v", "q", "L"):
+        assert np.abs(out[k] - ref[k]).max() <= tol * max(np.abs(ref[k]).max(), 1e-300), k
+    assert vec_rel_err(out["F"], ref["F"]) < 100 * tol
+    assert np.all(np.abs(rec[:, :4] - ref_rec[:, :4]) <= 100 * tol * np.maximum(np.abs(ref_rec[:, :4]).max(axis=0), 1e-300))
