@@ -258,14 +258,18 @@ def test_leaving_molecules_wrap():
 # ------------------------------------------------------------------------------------------------------
 def test_nve_properties_large():
     """256k-molecule 1CLJ fcc liquid: Newton 3 (sum F = 0), momentum and molecule count conserved, NVE energy
-    drift small over 200 steps, re-sort idempotent, deterministic (bitwise identical repeat)."""
+    drift small over 200 steps, re-sort idempotent, deterministic (bitwise identical repeat).  The potential is the
+    SHIFTED LJ here (Component::addLJcenter shift6, Component.cpp:105-117): the unshifted one jumps by U(rc) whenever a
+    pair crosses the cutoff, so its "energy" is not a conserved quantity (see test_nve_drift_matches_oracle)."""
     r, v, box = fcc_lattice(40, seed=9)
     n = len(r)
     dt = 0.002
+    s6 = (1.0 / 2.5) ** 6
+    shift6 = 24.0 * (s6 - s6 * s6)
 
     def one():
         with ls1g.Container(box, 2.5) as c:
-            c.set_components([ls1g.lj_component()])
+            c.set_components([ls1g.lj_component(shift6=shift6)])
             c.add_particles(np.arange(n), np.zeros(n, dtype=np.uint32), r, v)
             c.exchange()
             u0, _ = c.traverse_cells()
@@ -282,11 +286,35 @@ def test_nve_properties_large():
     assert fmax == 0.0 or np.abs(first["F"].sum(axis=0)).max() < 1e-9 * max(fmax, 1.0) * np.sqrt(n)
     assert np.all(rec[:, 4] == n)
     e = rec[:, 0] + 0.5 * rec[:, 2]                        # Upot + Ekin (summv2 = sum m v^2)
-    assert abs(e[-1] - e[0]) < 2e-4 * abs(e[0])            # leapfrog, dt*=0.002
+    assert np.abs(e - e[0]).max() < 1e-4 * abs(e[0])       # leapfrog, dt*=0.002, shifted potential
     assert np.abs(out["v"].sum(axis=0)).max() < 1e-8 * n
     assert np.abs(out["F"].sum(axis=0)).max() < 1e-9 * np.abs(out["F"]).max() * np.sqrt(n)
     u0b, _, recb, outb = one()
     assert u0 == u0b and np.array_equal(rec, recb) and np.array_equal(out["r"], outb["r"])
+
+
+def test_nve_drift_matches_oracle():
+    """NVE over 300 steps (unshifted LJ, as cfg B): the energy series of the device loop follows the oracle's, so the
+    drift is the reference algorithm's own (BASELINE.json: drift no worse than the reference)"""
+    r, v, box = fcc_lattice(8, seed=4)
+    n = len(r)
+    steps, dt = 300, 0.002
+    sysm = O.System.single_lj(rc=2.5)
+    g = O.grid([0, 0, 0], box, 2.5, 0)
+    cid = np.zeros(n, dtype=np.uint32)
+    q = np.tile([1.0, 0, 0, 0], (n, 1))
+    f0 = _oracle_forces(sysm, g, box, cid, r, q)
+    ref = O.run(sysm, g, box, cid, r, v, q, np.zeros((n, 3)), f0["F"], np.zeros((n, 3)), steps, dt)
+    with ls1g.Container(box, 2.5) as c:
+        c.set_components([ls1g.lj_component()])
+        c.add_particles(np.arange(n), cid, r, v)
+        c.exchange()
+        c.traverse_cells()
+        rec = c.run(steps, dt)
+    e_ref = ref["series"][:, 0] + 0.5 * ref["series"][:, 2]
+    e = rec[:, 0] + 0.5 * rec[:, 2]
+    assert np.abs(e - e_ref).max() < 1e-8 * abs(e_ref[0])
+    assert abs((e[-1] - e[0]) - (e_ref[-1] - e_ref[0])) < 1e-8 * abs(e_ref[0])
 
 
 def test_thermostat_run_holds_temperature():
