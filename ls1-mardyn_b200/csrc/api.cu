@@ -4,6 +4,7 @@
 
 #include <math.h>
 #include <string.h>
+#include <stdlib.h>
 #include <algorithm>
 #include <mutex>
 
@@ -158,6 +159,7 @@ extern "C" int ls1g_create(const ls1g_config* cfg, ls1g_ctx** out) {
 	c->nccl_comm = nullptr; c->n_ranks = 1; c->rank = 0; c->comm_mode = 0;
 	c->send_buf[0] = c->send_buf[1] = c->recv_buf[0] = c->recv_buf[1] = nullptr; c->xbuf_cap = 0;
 	memset(c->timers, 0, sizeof(c->timers));
+	{ const char* fk = getenv("LS1G_FORCE_KERNEL"); c->force_variant = (fk && !strcmp(fk, "simple")) ? 1 : 0; }
 	if (grid_init(c->grid, c->cfg)) { delete c; return 1; }
 	c->rc2 = c->cfg.cutoff * c->cfg.cutoff;
 	c->rclj2 = c->cfg.lj_cutoff * c->cfg.lj_cutoff;

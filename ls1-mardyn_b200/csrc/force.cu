@@ -248,10 +248,42 @@ __global__ void __launch_bounds__(256) force_finalize_kernel(const double* __res
 
 static inline unsigned nblk(size_t n, unsigned t) { return (unsigned)((n + t - 1) / t); }
 
+// first level of the deterministic two-level reduction: gridDim.x slices of the per-block partials -> out[gridDim.x][NV]
+template <int NV>
+__global__ void __launch_bounds__(256) reduce_partials_kernel(const double* __restrict__ partials, size_t nb, double* __restrict__ out) {
+	__shared__ double red[NV * 32];
+	const size_t per = (nb + gridDim.x - 1) / gridDim.x;
+	const size_t b0 = (size_t)blockIdx.x * per, b1 = b0 + per < nb ? b0 + per : nb;
+	double s[NV];
+#pragma unroll
+	for (int k = 0; k < NV; ++k) s[k] = 0.;
+	for (size_t b = b0 + threadIdx.x; b < b1; b += blockDim.x)
+#pragma unroll
+		for (int k = 0; k < NV; ++k) s[k] += partials[b * NV + k];
+	block_sum<NV>(s, red);
+	if (threadIdx.x == 0)
+#pragma unroll
+		for (int k = 0; k < NV; ++k) out[(size_t)blockIdx.x * NV + k] = s[k];
+}
+
+// reduces partials[nb][nv] (nv = 4 or 5) to at most 256 rows when nb is large; returns the rows to finalize and their base
+int ls1g_prereduce(ls1g_ctx* c, size_t& nb, int nv, const double*& base) {
+	base = c->partials;
+	if (nb <= 2048) return 0;
+	double* out = c->partials + nb * nv;          // ensure_partials reserves twice the requested size
+	if (nv == 5) reduce_partials_kernel<5><<<256, 256, 0, c->stream>>>(c->partials, nb, out);
+	else reduce_partials_kernel<4><<<256, 256, 0, c->stream>>>(c->partials, nb, out);
+	CUDA_TRY(cudaGetLastError());
+	nb = 256; base = out;
+	return 0;
+}
+
 int k_force_finalize(ls1g_ctx* c, size_t nb) {
 	timer_start(c, LS1G_T_AUX);
-	force_finalize_kernel<<<1, 256, 0, c->stream>>>(c->partials, nb, c->d_scalars);
-	timer_stop(c, LS1G_T_AUX, 1);
+	const double* base; int extra = nb > 2048;
+	if (ls1g_prereduce(c, nb, 5, base)) return 1;
+	force_finalize_kernel<<<1, 256, 0, c->stream>>>(base, nb, c->d_scalars);
+	timer_stop(c, LS1G_T_AUX, 1 + extra);
 	CUDA_TRY(cudaGetLastError());
 	return 0;
 }

@@ -66,21 +66,53 @@ __global__ void __launch_bounds__(LJ1_THREADS) force_1clj_simple_kernel(LJ1Args 
 	}
 }
 
+
+#include "force_1clj_tile.cuh"
+
 static inline unsigned nblk(size_t n, unsigned t) { return (unsigned)((n + t - 1) / t); }
 
 int k_forces_1clj(ls1g_ctx* c) {
 	size_t n = c->n_slots;
-	unsigned nb = nblk(n, LJ1_THREADS);
-	if (ls1g_ensure_partials(c, nb ? nb : 1, 5)) return 1;
-	if (n) {
-		LJ1Args a;
-		a.g = c->grid; a.n = n; a.pos = c->cur.pos; a.cell = c->cur.cell; a.cell_start = c->cell_start;
-		a.eps24 = c->eps24_h[0]; a.sig2 = c->sig2_h[0]; a.shift6 = c->shift6_h[0]; a.rclj2 = c->rclj2;
-		a.F = c->F; a.Vi = c->Vi; a.partials = c->partials;
-		timer_start(c, LS1G_T_FORCE);
-		force_1clj_simple_kernel<<<nb, LJ1_THREADS, 0, c->stream>>>(a);
-		timer_stop(c, LS1G_T_FORCE, 1);
+	const Grid& g = c->grid;
+	if (c->force_variant == 1) {   // v1 (LS1G_FORCE_KERNEL=simple): kept as the in-library cross-check of v2
+		unsigned nb = nblk(n, LJ1_THREADS);
+		if (ls1g_ensure_partials(c, nb ? nb : 1, 5)) return 1;
+		if (n) {
+			LJ1Args a;
+			a.g = c->grid; a.n = n; a.pos = c->cur.pos; a.cell = c->cur.cell; a.cell_start = c->cell_start;
+			a.eps24 = c->eps24_h[0]; a.sig2 = c->sig2_h[0]; a.shift6 = c->shift6_h[0]; a.rclj2 = c->rclj2;
+			a.F = c->F; a.Vi = c->Vi; a.partials = c->partials;
+			timer_start(c, LS1G_T_FORCE);
+			force_1clj_simple_kernel<<<nb, LJ1_THREADS, 0, c->stream>>>(a);
+			timer_stop(c, LS1G_T_FORCE, 1);
+		}
+		if (k_force_finalize(c, nb)) return 1;
+		CUDA_TRY(cudaGetLastError());
+		return 0;
 	}
+	LJ3Args a;
+	a.g = g; a.pos = c->cur.pos; a.cell_start = c->cell_start;
+	a.eps24 = c->eps24_h[0]; a.sig2 = c->sig2_h[0]; a.shift6 = c->shift6_h[0]; a.rclj2 = c->rclj2;
+	// FP32 filter: coordinates relative to the segment centre are < 6 cell lengths, i.e. an absolute error of
+	// ~2^-24 * 6 cells per coordinate and < 1e-5 relative on r^2 near rc^2; the 3e-4 margin is > 30x that bound, so the
+	// filter never rejects a pair the FP64 test accepts
+	a.rc2f = (float)(c->rclj2 * (1.0 + 3e-4));
+	a.F = c->F; a.Vi = c->Vi;
+	a.nxi = g.cpd[0] - 2; a.nyi = g.cpd[1] - 2;
+	a.nbx = (a.nxi + LJ3_GX - 1) / LJ3_GX;
+	unsigned nb = (unsigned)(a.nbx * a.nyi * (g.cpd[2] - 2));
+	if (ls1g_ensure_partials(c, nb ? nb : 1, 5)) return 1;
+	a.partials = c->partials;
+	if (n && nb) {
+		static bool attr_set = false;
+		if (!attr_set) {
+			CUDA_TRY(cudaFuncSetAttribute(force_1clj_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LJ3_SMEM_BYTES));
+			attr_set = true;
+		}
+		timer_start(c, LS1G_T_FORCE);
+		force_1clj_tile_kernel<<<nb, LJ3_W * 32, LJ3_SMEM_BYTES, c->stream>>>(a);
+		timer_stop(c, LS1G_T_FORCE, 1);
+	} else nb = 0;
 	if (k_force_finalize(c, nb)) return 1;
 	CUDA_TRY(cudaGetLastError());
 	return 0;

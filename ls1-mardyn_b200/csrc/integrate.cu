@@ -146,6 +146,8 @@ __global__ void __launch_bounds__(INT_THREADS) scale_kernel(size_t n, const uint
 	for (int d = 0; d < 3; ++d) { vel[3 * i + d] *= bt; if (L) L[3 * i + d] *= br; }
 }
 
+int ls1g_prereduce(ls1g_ctx* c, size_t& nb, int nv, const double*& base);   // force.cu
+
 // ------------------------------------------------------------------------------------------------
 static inline unsigned nblk(size_t n, unsigned t) { return (unsigned)((n + t - 1) / t); }
 
@@ -158,7 +160,7 @@ static IntArgs make_args(ls1g_ctx* c) {
 }
 
 static int ensure_partials(ls1g_ctx* c, size_t blocks, int nv) {
-	size_t need = blocks * nv + 64;
+	size_t need = blocks * nv + 64 + 256 * 8;   // + room for the first-level output of ls1g_prereduce
 	if (need > c->partials_cap) {
 		if (c->partials) cudaFree(c->partials);
 		c->partials = nullptr; c->partials_cap = 0;
@@ -195,12 +197,15 @@ int k_post_pre(ls1g_ctx* c, double dt, int do_post, int do_pre, int thermostat, 
 	timer_start(c, LS1G_T_INTEGRATE);
 	IntArgs a = make_args(c); a.dt = dt; a.dt_half = 0.5 * dt; a.partials = c->partials;
 	int launches = 0;
+	size_t nbr = nb; const double* pbase = c->partials;
 	if (do_post && !thermostat) {
 		if (nb) { if (do_pre) launch_int<true, true>(c, a, nb); else launch_int<true, false>(c, a, nb); ++launches; }
-		finalize_kernel<<<1, 256, 0, c->stream>>>(c->partials, nb, 4, c->d_scalars + 4, 0., nullptr); ++launches;
+		if (ls1g_prereduce(c, nbr, 4, pbase)) return 1;
+		finalize_kernel<<<1, 256, 0, c->stream>>>(pbase, nbr, 4, c->d_scalars + 4, 0., nullptr); launches += 1 + (nbr != nb);
 	} else if (do_post) {
 		if (nb) { launch_int<true, false>(c, a, nb); ++launches; }
-		finalize_kernel<<<1, 256, 0, c->stream>>>(c->partials, nb, 4, c->d_scalars + 4, target_T, c->d_scalars + 8); ++launches;
+		if (ls1g_prereduce(c, nbr, 4, pbase)) return 1;
+		finalize_kernel<<<1, 256, 0, c->stream>>>(pbase, nbr, 4, c->d_scalars + 4, target_T, c->d_scalars + 8); launches += 1 + (nbr != nb);
 		if (c->n_ranks > 1) {
 			// global sums first, then the betas from the reduced values
 			if (comm_allreduce(c, c->d_scalars + 4, 4)) return 1;

@@ -80,6 +80,7 @@ struct ls1g_ctx {
 	int max_sites;                          // max sites of any component (site-cache stride)
 	int has_rot;                            // any component needs q/L (multi-site or rot_dof>0)
 	int simple_1clj;                        // exactly one component: one LJ site at the origin, nothing else
+	int force_variant;                      // 0 = default kernels; 1 = v1 thread-per-molecule kernels (env LS1G_FORCE_KERNEL=simple)
 	std::vector<CompDev> comps_h;
 	std::vector<SiteDev> sites_h;
 	std::vector<double>  eps24_h, sig2_h, shift6_h;

@@ -149,8 +149,11 @@ def _oracle_forces(sysm, g, box, cid, r, q):
     return {k: (res[k][:n] if isinstance(res[k], np.ndarray) else res[k]) for k in res}
 
 
-def test_1clj_liquid_vs_oracle():
-    """cfg B in small: perturbed fcc 1CLJ, rho*=0.8442, rc=2.5 (13 molecules per cell): the specialised 1CLJ kernel"""
+@pytest.mark.parametrize("kernel", ["default", "simple"])
+def test_1clj_liquid_vs_oracle(kernel, monkeypatch):
+    """cfg B in small: perturbed fcc 1CLJ, rho*=0.8442, rc=2.5 (13 molecules per cell): the specialised 1CLJ kernels
+    (default: warp-per-cell with FP32 candidate filter; simple: v1 thread-per-molecule)"""
+    monkeypatch.setenv("LS1G_FORCE_KERNEL", kernel)
     r, v, box = fcc_lattice(12, seed=3)
     rng = np.random.default_rng(5)
     r = np.mod(r + rng.normal(scale=0.08, size=r.shape), box)
