@@ -52,19 +52,20 @@ void timer_stop(ls1g_ctx* c, int which, int launches) {
 // ------------------------------------------------------------------------------------------------
 // grid geometry: LinkedCells::rebuild (LinkedCells.cpp:136-204, float rc) / constructor (:42-107, double rc)
 // ------------------------------------------------------------------------------------------------
-static int grid_init(Grid& g, const ls1g_config& cfg) {
+// cut: cell size bound and halo slab width; mode LS1G_GRID_* or -1 (plain double arithmetic, internal bin grids)
+int grid_init_cut(Grid& g, const ls1g_config& cfg, double cut, int mode) {
 	memset(&g, 0, sizeof(g));
-	g.cutoff = cfg.cutoff;
+	g.cutoff = cut;
 	long ncell = 1;
 	for (int d = 0; d < 3; ++d) {
 		g.box_min[d] = cfg.box_min[d]; g.box_max[d] = cfg.box_max[d];
 		double diff = cfg.box_max[d] - cfg.box_min[d];
 		int n;
-		if (cfg.grid_mode == LS1G_GRID_CTOR) {
-			n = (int)floor(diff / cfg.cutoff);            // LinkedCells.cpp:53-54
+		if (mode == LS1G_GRID_CTOR || mode < 0) {
+			n = (int)floor(diff / cut);                   // LinkedCells.cpp:53-54
 			if (n == 0) n = 1;                            // :56-58
 		} else {
-			float rcf = (float)(cfg.cutoff / 1);          // :152 float rc = _cutoffRadius / _cellsInCutoff
+			float rcf = (float)(cut / 1);                 // :152 float rc = _cutoffRadius / _cellsInCutoff
 			n = (int)floor(diff / rcf);                   // :155
 			if (n == 0) LS1G_FAIL("ls1g_create: bounding box too small for the cutoff (LinkedCells.cpp:160-163)");
 		}
@@ -81,6 +82,7 @@ static int grid_init(Grid& g, const ls1g_config& cfg) {
 	g.n_cells = (int)ncell;
 	return 0;
 }
+static int grid_init(Grid& g, const ls1g_config& cfg) { return grid_init_cut(g, cfg, cfg.cutoff, cfg.grid_mode); }
 
 // ------------------------------------------------------------------------------------------------
 // life cycle
@@ -91,9 +93,13 @@ static void free_molecules(ls1g_ctx* c) {
 		cudaFree(b->pos); cudaFree(b->vel); cudaFree(b->q); cudaFree(b->L); cudaFree(b->id); cudaFree(b->cell);
 		memset(b, 0, sizeof(MolBuf));
 	}
-	cudaFree(c->F); cudaFree(c->M); cudaFree(c->Vi); cudaFree(c->F_alt); cudaFree(c->M_alt); cudaFree(c->site_cache);
+	cudaFree(c->F); cudaFree(c->M); cudaFree(c->Vi); cudaFree(c->F_alt); cudaFree(c->M_alt); cudaFree(c->Vi_alt); cudaFree(c->site_cache);
+	c->Vi_alt = nullptr;
 	cudaFree(c->slot_src); cudaFree(c->slot_code); cudaFree(c->slot_key); cudaFree(c->slot_cell);
 	cudaFree(c->stage); c->stage = nullptr; c->stage_bytes = 0;
+	cudaFree(c->halo_src); cudaFree(c->halo_code); cudaFree(c->slot_dst); cudaFree(c->pos_build); cudaFree(c->lists); cudaFree(c->lcount);
+	c->halo_src = nullptr; c->halo_code = nullptr; c->slot_dst = nullptr; c->pos_build = nullptr; c->lists = nullptr; c->lcount = nullptr;
+	c->lists_cap = c->lcount_cap = 0;
 	c->F = c->M = c->Vi = c->F_alt = c->M_alt = nullptr; c->site_cache = nullptr;
 	c->slot_src = nullptr; c->slot_code = nullptr; c->slot_key = nullptr; c->slot_cell = nullptr;
 	c->cap = 0;
@@ -116,6 +122,7 @@ static int alloc_molecules(ls1g_ctx* c, size_t cap) {
 	CUDA_TRY(cudaMalloc((void**)&c->F, cap * 3 * sizeof(double)));
 	CUDA_TRY(cudaMalloc((void**)&c->Vi, cap * 3 * sizeof(double)));
 	CUDA_TRY(cudaMalloc((void**)&c->F_alt, cap * 3 * sizeof(double)));
+	CUDA_TRY(cudaMalloc((void**)&c->Vi_alt, cap * 3 * sizeof(double)));
 	CUDA_TRY(cudaMemset(c->F, 0, cap * 3 * sizeof(double)));
 	CUDA_TRY(cudaMemset(c->Vi, 0, cap * 3 * sizeof(double)));
 	if (c->has_rot) {
@@ -128,6 +135,9 @@ static int alloc_molecules(ls1g_ctx* c, size_t cap) {
 	CUDA_TRY(cudaMalloc((void**)&c->slot_code, cap * sizeof(uint8_t)));
 	CUDA_TRY(cudaMalloc((void**)&c->slot_key, cap * sizeof(uint64_t)));
 	CUDA_TRY(cudaMalloc((void**)&c->slot_cell, cap * sizeof(uint32_t)));
+	CUDA_TRY(cudaMalloc((void**)&c->slot_dst, cap * sizeof(uint32_t)));
+	CUDA_TRY(cudaMalloc((void**)&c->halo_src, cap * sizeof(uint32_t)));
+	CUDA_TRY(cudaMalloc((void**)&c->halo_code, cap * sizeof(uint8_t)));
 	c->cap = cap;
 	return 0;
 }
@@ -161,6 +171,8 @@ extern "C" int ls1g_create(const ls1g_config* cfg, ls1g_ctx** out) {
 	memset(c->timers, 0, sizeof(c->timers));
 	{ const char* fk = getenv("LS1G_FORCE_KERNEL"); c->force_variant = (fk && !strcmp(fk, "simple")) ? 1 : 0; }
 	if (grid_init(c->grid, c->cfg)) { delete c; return 1; }
+	c->bgrid = c->grid;
+	{ const char* sk = getenv("LS1G_SKIN"); c->skin = sk ? atof(sk) : 0.12 * c->cfg.cutoff; if (c->skin < 0.) c->skin = 0.; }
 	c->rc2 = c->cfg.cutoff * c->cfg.cutoff;
 	c->rclj2 = c->cfg.lj_cutoff * c->cfg.lj_cutoff;
 	// VectorizedCellProcessor.cpp:24
@@ -177,6 +189,9 @@ extern "C" int ls1g_create(const ls1g_config* cfg, ls1g_ctx** out) {
 	CUDA_TRY(cudaMalloc((void**)&c->d_scalars, 16 * sizeof(double)));
 	CUDA_TRY(cudaMemset(c->d_scalars, 0, 16 * sizeof(double)));
 	CUDA_TRY(cudaMallocHost((void**)&c->h_scalars, 16 * sizeof(double)));
+	CUDA_TRY(cudaMalloc((void**)&c->d_flags, 4 * sizeof(unsigned long long)));
+	CUDA_TRY(cudaMemset(c->d_flags, 0, 4 * sizeof(unsigned long long)));
+	CUDA_TRY(cudaMallocHost((void**)&c->h_flags, 4 * sizeof(unsigned long long)));
 	*out = c;
 	return 0;
 }
@@ -191,6 +206,7 @@ extern "C" int ls1g_destroy(ls1g_ctx* c) {
 	free_molecules(c);
 	cudaFree(c->comps); cudaFree(c->sites); cudaFree(c->eps24); cudaFree(c->sig2); cudaFree(c->shift6);
 	cudaFree(c->cell_count); cudaFree(c->cell_fill); cudaFree(c->cell_start); cudaFree(c->scan_block);
+	cudaFree(c->d_flags); cudaFreeHost(c->h_flags);
 	cudaFree(c->d_counters); cudaFreeHost(c->h_counters); cudaFree(c->partials); cudaFree(c->d_scalars); cudaFreeHost(c->h_scalars);
 	for (int k = 0; k < 2; ++k) { cudaFree(c->send_buf[k]); cudaFree(c->recv_buf[k]); }
 	if (c->stream) cudaStreamDestroy(c->stream);

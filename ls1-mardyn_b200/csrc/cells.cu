@@ -207,8 +207,10 @@ __global__ void __launch_bounds__(256) scatter_kernel(Grid g, size_t n, const do
 
 struct GatherArgs {
 	MolBuf src, dst;
-	const double *F_src, *M_src; double *F_dst, *M_dst;   // carried only when non-null
+	const double *F_src, *M_src, *Vi_src; double *F_dst, *M_dst, *Vi_dst;   // carried only when non-null
 	int has_rot;
+	uint32_t* slot_dst;      // [n_new] final slot of scatter entry s
+	uint32_t* new_of_old;    // [n_old] new slot of every surviving (non-image) molecule; aliases src.cell
 };
 
 __global__ void __launch_bounds__(256) gather_kernel(Grid g, size_t n_new, GatherArgs a, const uint32_t* __restrict__ cell_start,
@@ -227,6 +229,8 @@ __global__ void __launch_bounds__(256) gather_kernel(Grid g, size_t n_new, Gathe
 	size_t dst = (size_t)b0 + rank;
 	uint32_t src = slot_src[s];
 	int code = slot_code[s];
+	a.slot_dst[s] = (uint32_t)dst;
+	if (!code) a.new_of_old[src] = (uint32_t)dst;
 	double4 p = a.src.pos[src];
 	if (code) image_pos(g, code, p.x, p.y, p.z);
 	a.dst.pos[dst] = p;
@@ -246,6 +250,8 @@ __global__ void __launch_bounds__(256) gather_kernel(Grid g, size_t n_new, Gathe
 		if (a.M_src)
 #pragma unroll
 			for (int d = 0; d < 3; ++d) a.M_dst[3 * dst + d] = a.M_src[3 * (size_t)src + d];
+#pragma unroll
+		for (int d = 0; d < 3; ++d) a.Vi_dst[3 * dst + d] = a.Vi_src[3 * (size_t)src + d];
 	}
 }
 
@@ -290,7 +296,7 @@ int k_cell_index(ls1g_ctx* c, size_t n, const double* d_pts, uint32_t* d_out) {
 
 // exclusive scan over the n_cells entries of `in` -> out[0..n_cells]; the total also lands in d_counters[0]
 int ls1g_scan_cells(ls1g_ctx* c, const uint32_t* in, uint32_t* out) {
-	const int nc = c->grid.n_cells;
+	const int nc = c->bgrid.n_cells;
 	int nb = (nc + SCAN_ITEMS - 1) / SCAN_ITEMS;
 	scan_reduce_kernel<<<nb, SCAN_THREADS, 0, c->stream>>>(in, nc, c->scan_block);
 	scan_blocks_kernel<<<1, 1024, 0, c->stream>>>(c->scan_block, nb, c->d_counters);
@@ -300,7 +306,7 @@ int ls1g_scan_cells(ls1g_ctx* c, const uint32_t* in, uint32_t* out) {
 }
 
 int k_sort(ls1g_ctx* c, int make_images) {
-	const Grid& g = c->grid;
+	const Grid& g = c->bgrid;
 	const int nc = g.n_cells;
 	size_t n = c->n_slots;
 	timer_start(c, LS1G_T_SORT);
@@ -325,13 +331,15 @@ int k_sort(ls1g_ctx* c, int make_images) {
 	if (n_new) {
 		GatherArgs a;
 		a.src = c->cur; a.dst = c->alt; a.has_rot = c->has_rot;
+		a.slot_dst = c->slot_dst; a.new_of_old = c->cur.cell;
 		// forces are carried through a re-sort only when they exist (API use outside ls1g_run); Vi is not carried
 		bool carry = c->forces_valid;
 		a.F_src = carry ? c->F : nullptr; a.F_dst = c->F_alt;
 		a.M_src = (carry && c->has_rot) ? c->M : nullptr; a.M_dst = c->M_alt;
+		a.Vi_src = c->Vi; a.Vi_dst = c->Vi_alt;
 		gather_kernel<<<nblk(n_new, 256), 256, 0, c->stream>>>(g, n_new, a, c->cell_start, c->slot_src, c->slot_code, c->slot_key, c->slot_cell);
 		++launches;
-		if (carry) { std::swap(c->F, c->F_alt); if (c->has_rot) std::swap(c->M, c->M_alt); }
+		if (carry) { std::swap(c->F, c->F_alt); std::swap(c->Vi, c->Vi_alt); if (c->has_rot) std::swap(c->M, c->M_alt); }
 	}
 	CUDA_TRY(cudaGetLastError());
 	std::swap(c->cur, c->alt);
@@ -339,6 +347,26 @@ int k_sort(ls1g_ctx* c, int make_images) {
 	c->n_halo = n_new - c->n_owned;
 	c->sorted = 1;
 	timer_stop(c, LS1G_T_SORT, launches);
+	return 0;
+}
+
+// halo_src / halo_code for the frozen-layout steps of the neighbour-list loop: every periodic image remembers the slot
+// of the molecule it copies.  Valid directly after k_sort(c, 1) (alt.cell still holds new_of_old).
+__global__ void __launch_bounds__(256) halo_map_kernel(size_t n_new, const uint32_t* __restrict__ slot_src, const uint8_t* __restrict__ slot_code,
+                                                        const uint32_t* __restrict__ slot_dst, const uint32_t* __restrict__ new_of_old,
+                                                        uint32_t* __restrict__ halo_src, uint8_t* __restrict__ halo_code) {
+	size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (s >= n_new) return;
+	const uint8_t code = slot_code[s];
+	const uint32_t dst = slot_dst[s];
+	halo_code[dst] = code;
+	halo_src[dst] = code ? new_of_old[slot_src[s]] : dst;
+}
+
+int k_halo_map(ls1g_ctx* c) {
+	if (c->n_slots == 0) return 0;
+	halo_map_kernel<<<nblk(c->n_slots, 256), 256, 0, c->stream>>>(c->n_slots, c->slot_src, c->slot_code, c->slot_dst, c->alt.cell, c->halo_src, c->halo_code);
+	CUDA_TRY(cudaGetLastError());
 	return 0;
 }
 

@@ -176,7 +176,7 @@ static int stage_pack(ls1g_ctx* c, int d) {
 	if (ensure_xbuf(c)) return 1;
 	CUDA_TRY(cudaMemsetAsync(c->d_counters + 2, 0, 2 * sizeof(uint32_t), c->stream));
 	PackArgs a;
-	a.g = c->grid; a.n = c->n_slots; a.m = c->cur; a.has_rot = c->has_rot; a.dim = d;
+	a.g = c->bgrid; a.n = c->n_slots; a.m = c->cur; a.has_rot = c->has_rot; a.dim = d;
 	a.global_len = c->cfg.global_length[d];
 	a.shift[0] = c->cfg.rank_coords[d] == 0 ? c->cfg.global_length[d] : 0.;
 	a.shift[1] = c->cfg.rank_coords[d] == c->cfg.rank_grid[d] - 1 ? -c->cfg.global_length[d] : 0.;

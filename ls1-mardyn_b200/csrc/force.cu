@@ -299,7 +299,7 @@ int k_forces(ls1g_ctx* c) {
 		site_cache_kernel<<<nblk(n, 256), 256, 0, c->stream>>>(n, c->cur.pos, c->cur.q, c->comps, c->sites, c->site_cache, c->cache_stride);
 		timer_stop(c, LS1G_T_AUX, 1);
 		ForceArgs a;
-		a.g = c->grid; a.n = n; a.pos = c->cur.pos; a.cell = c->cur.cell; a.cell_start = c->cell_start;
+		a.g = c->bgrid; a.n = n; a.pos = c->cur.pos; a.cell = c->cur.cell; a.cell_start = c->cell_start;
 		a.comps = c->comps; a.cache = c->site_cache; a.stride = c->cache_stride;
 		a.eps24 = c->eps24; a.sig2 = c->sig2; a.shift6 = c->shift6; a.S = c->S_lj;
 		a.rc2 = c->rc2; a.rclj2 = c->rclj2; a.epsRFInvrc3 = c->epsRFInvrc3;

@@ -73,13 +73,13 @@ static inline unsigned nblk(size_t n, unsigned t) { return (unsigned)((n + t - 1
 
 int k_forces_1clj(ls1g_ctx* c) {
 	size_t n = c->n_slots;
-	const Grid& g = c->grid;
+	const Grid& g = c->bgrid;
 	if (c->force_variant == 1) {   // v1 (LS1G_FORCE_KERNEL=simple): kept as the in-library cross-check of v2
 		unsigned nb = nblk(n, LJ1_THREADS);
 		if (ls1g_ensure_partials(c, nb ? nb : 1, 5)) return 1;
 		if (n) {
 			LJ1Args a;
-			a.g = c->grid; a.n = n; a.pos = c->cur.pos; a.cell = c->cur.cell; a.cell_start = c->cell_start;
+			a.g = c->bgrid; a.n = n; a.pos = c->cur.pos; a.cell = c->cur.cell; a.cell_start = c->cell_start;
 			a.eps24 = c->eps24_h[0]; a.sig2 = c->sig2_h[0]; a.shift6 = c->shift6_h[0]; a.rclj2 = c->rclj2;
 			a.F = c->F; a.Vi = c->Vi; a.partials = c->partials;
 			timer_start(c, LS1G_T_FORCE);

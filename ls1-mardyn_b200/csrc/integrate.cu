@@ -32,6 +32,8 @@ struct IntArgs {
 	double dt;             // full step (pre)
 	double dt_half;        // post
 	const double* betas;   // device [2] beta_trans, beta_rot; nullptr = no scaling
+	const double4* pos_build;          // neighbour-list mode: positions at the last list build (nullptr = not tracked)
+	unsigned long long* maxdisp;       // max |r - r_build|^2 as double bits (atomicMax)
 	double* partials;      // [gridDim.x][4]
 };
 
@@ -40,6 +42,7 @@ __global__ void __launch_bounds__(INT_THREADS) integrate_kernel(IntArgs a) {
 	__shared__ double red[4 * 32];
 	size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
 	double acc[4] = {0., 0., 0., 0.};   // summv2, sumIw2, N, rotDOF
+	double disp2 = 0.;
 	bool active = i < a.n && !(a.cell[i] & HALO_FLAG);
 	if (active) {
 		double4 p = a.pos[i];
@@ -82,6 +85,7 @@ __global__ void __launch_bounds__(INT_THREADS) integrate_kernel(IntArgs a) {
 			for (int d = 0; d < 3; ++d) { v[d] += dtInv2m * F[d]; r[d] += a.dt * v[d]; }
 			p.x = r[0]; p.y = r[1]; p.z = r[2];
 			a.pos[i] = p;
+			if (a.pos_build) { const double4 b = a.pos_build[i]; const double ex = p.x - b.x, ey = p.y - b.y, ez = p.z - b.z; disp2 = ex * ex + ey * ey + ez * ez; }
 			if (ROT) {
 				double w[3];
 				quat_rotateinv(q, L, w);
@@ -105,6 +109,12 @@ __global__ void __launch_bounds__(INT_THREADS) integrate_kernel(IntArgs a) {
 		}
 		a.vel[3 * i] = v[0]; a.vel[3 * i + 1] = v[1]; a.vel[3 * i + 2] = v[2];
 		if (ROT) { a.L[3 * i] = L[0]; a.L[3 * i + 1] = L[1]; a.L[3 * i + 2] = L[2]; }
+	}
+	if (PRE && a.pos_build) {          // displacement criterion of the neighbour lists (lists.cuh)
+#pragma unroll
+		for (int o = 16; o > 0; o >>= 1) disp2 = fmax(disp2, __shfl_xor_sync(0xffffffffu, disp2, o));
+		const unsigned long long bits = (unsigned long long)__double_as_longlong(disp2);
+		if ((threadIdx.x & 31) == 0 && bits > *(volatile unsigned long long*)a.maxdisp) atomicMax(a.maxdisp, bits);
 	}
 	if (POST) {
 		block_sum<4>(acc, red);
@@ -156,6 +166,7 @@ static IntArgs make_args(ls1g_ctx* c) {
 	a.n = c->n_slots; a.pos = c->cur.pos; a.vel = c->cur.vel; a.q = c->cur.q; a.L = c->cur.L;
 	a.F = c->F; a.M = c->M; a.cell = c->cur.cell; a.comps = c->comps;
 	a.dt = 0.; a.dt_half = 0.; a.betas = nullptr; a.partials = c->partials;
+	a.pos_build = c->track_disp ? c->pos_build : nullptr; a.maxdisp = c->d_flags;
 	return a;
 }
 

@@ -1,0 +1,99 @@
+// lists.cu — host side of the neighbour-list mode of ls1g_run (kernels in lists.cuh).
+#include "ls1g_internal.cuh"
+#include "potentials.cuh"
+#include "lists.cuh"
+
+#include <math.h>
+#include <string.h>
+
+int ls1g_ensure_partials(ls1g_ctx* c, size_t blocks, int nv);
+int k_force_finalize(ls1g_ctx* c, size_t nb);
+
+static inline unsigned nblk(size_t n, unsigned t) { return (unsigned)((n + t - 1) / t); }
+
+// list mode applies to: one rank, single-centre LJ, default kernels, skin > 0, not disabled by an earlier overflow
+int nl_applicable(const ls1g_ctx* c) {
+	return c->simple_1clj && c->n_ranks == 1 && c->force_variant == 0 && c->skin > 0. && !c->list_disabled;
+}
+
+// switch the bin grid: cells >= cutoff + skin (list mode) or the reference grid
+int nl_set_bin_grid(ls1g_ctx* c, int list_mode) {
+	if (!list_mode) { c->bgrid = c->grid; return 0; }
+	Grid g;
+	if (grid_init_cut(g, c->cfg, c->cfg.cutoff + c->skin, -1)) return 1;
+	if (g.n_cells > c->grid.n_cells) LS1G_FAIL("neighbour-list grid larger than the reference grid");
+	c->bgrid = g;
+	return 0;
+}
+
+static NLArgs nl_args(ls1g_ctx* c) {
+	NLArgs a;
+	a.g = c->bgrid; a.pos = c->cur.pos; a.cell = c->cur.cell; a.cell_start = c->cell_start;
+	a.lists = c->lists; a.lcount = c->lcount; a.flags = c->d_flags; a.bpr = c->list_bpr; a.nyi = c->bgrid.cpd[1] - 2;
+	const double rl = c->cfg.lj_cutoff + c->skin;
+	// FP32 filter: coordinates relative to the block centre are < 8 cell lengths: relative error on r^2 near rl^2 < 2e-5;
+	// the 3e-4 margin can only over-accept (the force kernel applies the exact FP64 test)
+	a.rl2f = (float)(rl * rl * (1.0 + 3e-4));
+	a.eps24 = c->eps24_h[0]; a.sig2 = c->sig2_h[0]; a.shift6 = c->shift6_h[0]; a.rclj2 = c->rclj2;
+	a.F = c->F; a.Vi = c->Vi; a.partials = c->partials;
+	return a;
+}
+
+static size_t nl_blocks(const ls1g_ctx* c) { return (size_t)(c->bgrid.cpd[1] - 2) * (c->bgrid.cpd[2] - 2) * (size_t)c->list_bpr; }
+
+// after k_sort on the bin grid: size the block grid, build the lists, remember the build positions.
+// The caller synchronises and reads h_flags[1] (overflow bits).
+int k_list_build(ls1g_ctx* c) {
+	const Grid& g = c->bgrid;
+	const size_t rows = (size_t)(g.cpd[1] - 2) * (g.cpd[2] - 2);
+	const double avg_row = (double)c->n_owned / (double)rows;
+	c->list_bpr = (int)ceil(1.3 * avg_row / NL_BT) + 1;
+	const size_t nb = nl_blocks(c);
+	const size_t want_l = nb * NL_LCAP * NL_BT, want_c = nb * NL_BT;
+	if (want_l > c->lists_cap) {
+		cudaFree(c->lists); c->lists = nullptr; c->lists_cap = 0;
+		CUDA_TRY(cudaMalloc((void**)&c->lists, want_l * sizeof(unsigned short)));
+		c->lists_cap = want_l;
+	}
+	if (want_c > c->lcount_cap) {
+		cudaFree(c->lcount); c->lcount = nullptr; c->lcount_cap = 0;
+		CUDA_TRY(cudaMalloc((void**)&c->lcount, want_c * sizeof(uint32_t)));
+		c->lcount_cap = want_c;
+	}
+	if (!c->pos_build) CUDA_TRY(cudaMalloc((void**)&c->pos_build, c->cap * sizeof(double4)));
+	timer_start(c, LS1G_T_SORT);
+	CUDA_TRY(cudaMemsetAsync(c->d_flags, 0, 2 * sizeof(unsigned long long), c->stream));
+	CUDA_TRY(cudaMemcpyAsync(c->pos_build, c->cur.pos, c->n_slots * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));
+	NLArgs a = nl_args(c);
+	nl_build_kernel<<<(unsigned)nb, NL_BT, 0, c->stream>>>(a);
+	CUDA_TRY(cudaGetLastError());
+	CUDA_TRY(cudaMemcpyAsync(c->h_flags, c->d_flags, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+	timer_stop(c, LS1G_T_SORT, 2);
+	return 0;
+}
+
+int k_forces_list(ls1g_ctx* c) {
+	const size_t nb = nl_blocks(c);
+	if (ls1g_ensure_partials(c, nb ? nb : 1, 5)) return 1;
+	static bool attr_set = false;
+	if (!attr_set) {
+		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, NL_FORCE_SMEM));
+		attr_set = true;
+	}
+	NLArgs a = nl_args(c);
+	timer_start(c, LS1G_T_FORCE);
+	nl_force_kernel<<<(unsigned)nb, NL_BT, NL_FORCE_SMEM, c->stream>>>(a);
+	timer_stop(c, LS1G_T_FORCE, 1);
+	if (k_force_finalize(c, nb)) return 1;
+	CUDA_TRY(cudaGetLastError());
+	return 0;
+}
+
+int k_halo_refresh(ls1g_ctx* c) {
+	if (c->n_slots == 0) return 0;
+	timer_start(c, LS1G_T_SORT);
+	halo_refresh_kernel<<<nblk(c->n_slots, 256), 256, 0, c->stream>>>(c->bgrid, c->n_slots, c->cur.pos, c->cur.cell, c->halo_src, c->halo_code);
+	timer_stop(c, LS1G_T_SORT, 1);
+	CUDA_TRY(cudaGetLastError());
+	return 0;
+}

@@ -72,7 +72,9 @@ struct PendingEvt { cudaEvent_t a, b; int which; int launches; };
 
 struct ls1g_ctx {
 	ls1g_config cfg;
-	Grid grid;
+	Grid grid;                              // the reference's cell grid (LinkedCells::rebuild): cell queries, C08 dump, download
+	Grid bgrid;                             // the grid the device sort bins on: == grid, except inside the neighbour-list loop of
+	                                        // ls1g_run where its cells are >= cutoff + skin (lists.cu)
 	cudaStream_t stream;
 
 	// components
@@ -97,10 +99,22 @@ struct ls1g_ctx {
 	int    forces_valid;
 	MolBuf cur, alt;                        // double buffer for the sort
 	double *F, *M, *Vi;                     // [cap][3]; M only if has_rot
-	double *F_alt, *M_alt;                  // targets when forces are carried through a re-sort
+	double *F_alt, *M_alt, *Vi_alt;                // targets when forces are carried through a re-sort
 	double4* site_cache;                    // [cap*cache_stride] world-frame site data (multi-site path)
 	int     cache_stride;
-	void*   stage; size_t stage_bytes;      // device staging area of the host<->device transfers (transfer.cu)
+	void*   stage; size_t stage_bytes;
+	// neighbour-list mode of ls1g_run (lists.cu): frozen slot layout between rebuilds
+	double   skin;                          // list radius = cutoff + skin; 0 disables the list mode
+	int      list_disabled;                 // set when a buffer limit was hit once: stay on the rebuild-every-step path
+	uint32_t *halo_src; uint8_t* halo_code; // [cap] per halo slot: slot of its source molecule, periodic image code
+	uint32_t *slot_dst;                     // [cap] final slot of scatter entry s (sort scratch)
+	double4* pos_build;                     // [cap] positions when the lists were built (displacement criterion)
+	unsigned short* lists; size_t lists_cap;// [blocks][LCAP][128] tile indices
+	uint32_t* lcount; size_t lcount_cap;    // [blocks*128]
+	int      track_disp;                    // integrate kernels track max |r - pos_build|^2 into d_flags[0]
+	int      list_bpr;                      // blocks per cell row
+	unsigned long long* d_flags;            // [4]: max displacement^2 bits | overflow bits
+	unsigned long long* h_flags;            // pinned mirror      // device staging area of the host<->device transfers (transfer.cu)
 
 	// cells / sort scratch
 	uint32_t *cell_count, *cell_fill, *cell_start;   // [n_cells+1]
@@ -134,6 +148,8 @@ void ls1g_set_error(const std::string& msg);
 
 // launchers implemented in the kernel files ---------------------------------------------------------
 // cells.cu
+int  grid_init_cut(Grid& g, const ls1g_config& cfg, double cut, int mode);   // api.cu
+int  k_halo_map(ls1g_ctx* c);                   // after k_sort(c, 1): halo_src / halo_code of every halo slot
 int  k_cell_index(ls1g_ctx* c, size_t n, const double* d_pts, uint32_t* d_out);
 int  k_sort(ls1g_ctx* c, int make_images);      // bin (+periodic images) -> scan -> scatter -> gather, swaps cur/alt
 int  k_drop_halo(ls1g_ctx* c);                  // deleteOuterParticles

@@ -13,15 +13,13 @@
 //   _loopBodyQuadrupole        :652-794      pot_Q_Q
 #pragma once
 
-// reciprocal of a positive, normal double: hardware seed (MUFU.RCP64H) + two Newton-Raphson steps, then one
-// correction so the result is within 1 ulp.  The reference itself uses NR-refined estimates on AVX2/AVX-512
+// reciprocal of a positive, normal double: hardware seed (MUFU.RCP64H) + two Newton-Raphson steps (within ~1 ulp).  The reference itself uses NR-refined estimates on AVX2/AVX-512
 // (vectorization/RealVecDouble.h:411-541); parity tolerance is 1e-10 relative.
 __device__ __forceinline__ double fast_rcp(double a) {
 	double x;
 	asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(x) : "d"(a));
+	// seed error <= 2^-20 (PTX ISA, rcp.approx.ftz.f64) -> 2^-40 -> 2^-80: two steps reach the rounding level
 	double e = fma(-a, x, 1.0);
-	x = fma(x, e, x);
-	e = fma(-a, x, 1.0);
 	x = fma(x, e, x);
 	e = fma(-a, x, 1.0);
 	x = fma(x, e, x);

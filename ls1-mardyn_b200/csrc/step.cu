@@ -4,6 +4,8 @@
 
 #include <math.h>
 #include <string.h>
+#include <stdio.h>
+#include <stdlib.h>
 
 int k_post_pre(ls1g_ctx* c, double dt, int do_post, int do_pre, int thermostat, double target_T);
 void ls1g_resolve_timers(ls1g_ctx* c);
@@ -74,6 +76,60 @@ extern "C" int ls1g_scale(ls1g_ctx* c, double bt, double br) {
 	return sync_check(c, "ls1g_scale");
 }
 
+int nl_applicable(const ls1g_ctx* c);
+int nl_set_bin_grid(ls1g_ctx* c, int list_mode);
+int k_list_build(ls1g_ctx* c);
+int k_forces_list(ls1g_ctx* c);
+int k_halo_refresh(ls1g_ctx* c);
+
+// Neighbour-list steps of ls1g_run (lists.cuh).  On entry the pre-kick of step 0 is done.  Runs steps [0, n_steps) unless
+// a buffer limit is hit while building lists for step s: then the bin grid is restored and *done = s tells the caller to
+// continue with the rebuild-every-step loop (the state is exactly what that loop expects).
+static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, double target_T, double* d_rec, int* done) {
+	*done = 0;
+	if (nl_set_bin_grid(c, 1)) return 1;
+	bool need_build = true;
+	int rc = 0, s = 0;
+	for (; s < n_steps && !rc; ++s) {
+		if (need_build) {
+			c->sorted = 0; c->track_disp = 0;
+			c->forces_valid = 0;
+			rc = k_sort(c, 1);
+			c->forces_valid = 1;
+			if (!rc) rc = k_halo_map(c);
+			if (!rc) rc = k_list_build(c);
+			if (!rc && sync_check(c, "ls1g_run (list build)")) rc = 1;
+			if (!rc && c->h_flags[1]) {          // tile / list / row capacity exceeded: this system is too dense for the list buffers
+				c->list_disabled = 1;
+				if (getenv("LS1G_DEBUG")) fprintf(stderr, "ls1g: neighbour lists disabled, overflow bits %llu (1 tile, 2 list, 4 row), bpr %d\n", c->h_flags[1], c->list_bpr);
+				nl_set_bin_grid(c, 0);
+				*done = s;
+				return 0;
+			}
+			c->track_disp = 1;
+		} else rc = k_halo_refresh(c);
+		if (!rc) rc = k_forces_list(c);
+		if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s, c->d_scalars, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
+		if (!rc) rc = k_post_pre(c, dt, 1, s + 1 < n_steps, thermo, target_T);
+		if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s + 4, c->d_scalars + 4, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
+		if (!rc && s + 1 < n_steps) {
+			if (cudaMemcpyAsync(c->h_flags, c->d_flags, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess) rc = 1;
+			if (!rc && sync_check(c, "ls1g_run (displacement)")) rc = 1;
+			double d2; memcpy(&d2, c->h_flags, sizeof(double));
+			need_build = 2. * sqrt(d2) > 0.999 * c->skin;       // lists stay exact while no molecule moved more than skin/2
+		}
+	}
+	c->track_disp = 0;
+	if (rc) { nl_set_bin_grid(c, 0); return rc; }
+	// leave the state as the per-step loop does: wrapped positions, sorted on the reference grid, halo copies dropped
+	if (nl_set_bin_grid(c, 0)) return 1;
+	c->sorted = 0;
+	if (k_sort(c, 1)) return 1;
+	if (k_drop_halo(c)) return 1;
+	*done = n_steps;
+	return 0;
+}
+
 // Device-resident loop.  Per step: pre -> exchange (wrap, images, sort) -> forces (+calcFM) -> post -> thermostat.
 // post(n), the thermostat and pre(n+1) run as one kernel between two force passes.
 extern "C" int ls1g_run(ls1g_ctx* c, int n_steps, double dt, double target_T, ls1g_step_record* records) {
@@ -84,9 +140,13 @@ extern "C" int ls1g_run(ls1g_ctx* c, int n_steps, double dt, double target_T, ls
 	double* d_rec = nullptr;
 	if (records) CUDA_TRY(cudaMallocAsync((void**)&d_rec, (size_t)n_steps * 8 * sizeof(double), c->stream));
 	int rc = k_post_pre(c, dt, 0, 1, 0, 0.);
-	for (int s = 0; s < n_steps && !rc; ++s) {
+	int s0 = 0;
+	if (!rc && nl_applicable(c)) rc = run_list_steps(c, n_steps, dt, thermo, target_T, d_rec, &s0);
+	for (int s = s0; s < n_steps && !rc; ++s) {
 		c->sorted = 0;
+		c->forces_valid = 0;     // F is recomputed before its next use: do not carry it through the sort
 		rc = c->n_ranks > 1 ? comm_exchange(c) : k_sort(c, 1);
+		c->forces_valid = 1;
 		if (!rc) rc = k_forces(c);
 		if (!rc) rc = k_drop_halo(c);
 		if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s, c->d_scalars, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;

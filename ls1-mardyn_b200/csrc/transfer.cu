@@ -151,7 +151,7 @@ int k_download(ls1g_ctx* c, int mask, int include_halo, size_t n_ret, ls1g_field
 	const bool identity = (n_ret == ns);
 	const uint32_t* kept = nullptr;
 	if (!identity) {
-		kept_count_kernel<<<nblk(c->grid.n_cells, 256), 256, 0, st>>>(c->grid, c->cell_start, include_halo, c->cell_count);
+		kept_count_kernel<<<nblk(c->bgrid.n_cells, 256), 256, 0, st>>>(c->bgrid, c->cell_start, include_halo, c->cell_count);
 		if (ls1g_scan_cells(c, c->cell_count, c->cell_fill)) return 1;
 		kept = c->cell_fill;
 	}

@@ -320,6 +320,42 @@ def test_nve_drift_matches_oracle():
     assert abs((e[-1] - e[0]) - (e_ref[-1] - e_ref[0])) < 1e-8 * abs(e_ref[0])
 
 
+def test_list_loop_equals_per_step_loop(monkeypatch):
+    """ls1g_run with neighbour lists (rebuild on displacement > skin/2, frozen layout, refreshed images) against the
+    rebuild-every-step loop (LS1G_SKIN=0) on a liquid that crosses the periodic boundary: same pairs, same energies"""
+    r, v, box = fcc_lattice(14, seed=12, temperature=2.0)
+    n = len(r)
+    out = {}
+    for skin in ("0", "0.3", "0.6"):
+        monkeypatch.setenv("LS1G_SKIN", skin)
+        with ls1g.Container(box, 2.5) as c:
+            c.set_components([ls1g.lj_component()])
+            c.add_particles(np.arange(n), np.zeros(n, dtype=np.uint32), r, v)
+            c.exchange()
+            c.traverse_cells()
+            rec = c.run(120, 0.004)
+            pairs = c.last_pair_count()
+            st = by_id(c.download(("id", "r", "v", "F", "Vi", "cell")))
+            # the container is left in the per-step state: a plain exchange + traverse reproduces the forces
+            c.exchange()
+            u, w = c.traverse_cells()
+            st2 = by_id(c.download(("id", "F")))
+            assert vec_rel_err(st2["F"], st["F"]) < 1e-12
+        out[skin] = (rec, st, pairs)
+    ref_rec, ref_st, ref_pairs = out["0"]
+    assert np.all(ref_st["r"] >= 0) and np.all(ref_st["r"] < box)
+    for skin in ("0.3", "0.6"):
+        rec, st, pairs = out[skin]
+        assert pairs == ref_pairs
+        assert np.all(st["r"] >= 0) and np.all(st["r"] < box)
+        assert np.array_equal(st["cell"], ref_st["cell"])
+        assert np.all(np.abs(rec - ref_rec) <= 1e-9 * np.maximum(np.abs(ref_rec).max(axis=0), 1e-300))
+        for k in ("r", "v"):
+            assert np.abs(st[k] - ref_st[k]).max() <= 1e-9 * np.abs(ref_st[k]).max(), k
+        assert vec_rel_err(st["F"], ref_st["F"]) < 1e-7
+        assert vec_rel_err(st["Vi"], ref_st["Vi"]) < 1e-7
+
+
 def test_thermostat_run_holds_temperature():
     """NVT: Domain::calculateGlobalValues betas (Domain.cpp:226-247) drive T to the target"""
     r, v, box = fcc_lattice(10, seed=1, temperature=1.0)
