@@ -116,7 +116,14 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append([x.strip() for x in line.split(",")] + [time.perf_counter()])
+
+    def window(self, t0, t1):
+        """keep only the samples taken inside [t0, t1] (the timed region); the sampler itself is started before the
+        warm-up because the first nvidia-smi query can stall the driver for a few hundred ms"""
+        rows = [r for r in self.rows if t0 <= r[-1] <= t1]
+        if rows:
+            self.rows = rows
 
     def stop(self):
         if self.proc is None:
@@ -127,10 +134,10 @@ class ClockSampler:
             self.proc.wait(5)
         except subprocess.TimeoutExpired:
             self.proc.kill()
-        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for k, n in enumerate(names) if any(len(r) >= 6 and r[2 + k].lower().startswith("active") for r in self.rows)]
+        reasons = [n for k, n in enumerate(names) if any(len(r) >= 7 and r[2 + k].lower().startswith("active") for r in self.rows)]
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "reasons": reasons, "samples": len(sm)}
 
@@ -359,19 +366,26 @@ def main_b200(args):
     stream = torch.cuda.ExternalStream(c.stream(), device=torch.device("cuda", local))
 
     # ---- device-resident loop ------------------------------------------------------------------------------
+    clocks = ClockSampler(local)
+    if rank == 0:
+        clocks.start()
+        t_wait = time.time()
+        while not clocks.rows and time.time() - t_wait < 10.0:     # the first nvidia-smi query is slow on a cold box:
+            time.sleep(0.05)                                       # let it finish before anything is timed
     if args.warmup > 0:
         c.run(args.warmup, DT)
     c.timers(reset=True)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    clocks = ClockSampler(local)
     barrier()
-    if rank == 0:
-        clocks.start()
+    tw0 = time.perf_counter()
     e0.record(stream)
     rec = c.run(args.steps, DT)
     e1.record(stream)
     barrier()
+    tw1 = time.perf_counter()
     ms = e0.elapsed_time(e1)
+    if rank == 0:
+        clocks.window(tw0, tw1)
     clk = clocks.stop() if rank == 0 else None
     tm = c.timers(reset=True)
     n_pairs = c.last_pair_count()
@@ -463,8 +477,8 @@ def main_b200(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cells", type=int, default=CELLS_PER_GPU, help="fcc unit cells per dimension per GPU")
     ap.add_argument("--e2e-steps", type=int, default=5)

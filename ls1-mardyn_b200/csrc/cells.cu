@@ -305,6 +305,19 @@ int ls1g_scan_cells(ls1g_ctx* c, const uint32_t* in, uint32_t* out) {
 	return 0;
 }
 
+// owned molecules of the fullest cell row (y, z): sizes the block grid of the neighbour-list kernels (lists.cuh)
+__global__ void __launch_bounds__(256) row_max_kernel(Grid g, const uint32_t* __restrict__ cell_start, uint32_t* __restrict__ out) {
+	const int nyi = g.cpd[1] - 2, nzi = g.cpd[2] - 2;
+	int row = blockIdx.x * blockDim.x + threadIdx.x;
+	uint32_t n = 0;
+	if (row < nyi * nzi) {
+		const int crow = ((row / nyi + 1) * g.cpd[1] + (row % nyi + 1)) * g.cpd[0];
+		n = cell_start[crow + g.cpd[0] - 1] - cell_start[crow + 1];
+	}
+	n = __reduce_max_sync(0xffffffffu, n);
+	if ((threadIdx.x & 31) == 0 && n) atomicMax(out, n);
+}
+
 int k_sort(ls1g_ctx* c, int make_images) {
 	const Grid& g = c->bgrid;
 	const int nc = g.n_cells;
@@ -315,10 +328,13 @@ int k_sort(ls1g_ctx* c, int make_images) {
 	int launches = 0;
 	if (n) { bin_kernel<<<nblk(n, 256), 256, 0, c->stream>>>(g, n, c->cur.pos, c->cur.cell, c->cell_count, make_images); ++launches; }
 	if (ls1g_scan_cells(c, c->cell_count, c->cell_start)) return 1;
-	launches += 3;
-	CUDA_TRY(cudaMemcpyAsync(c->h_counters, c->d_counters, sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+	CUDA_TRY(cudaMemsetAsync(c->d_counters + 7, 0, sizeof(uint32_t), c->stream));
+	row_max_kernel<<<nblk((size_t)(g.cpd[1] - 2) * (g.cpd[2] - 2), 256), 256, 0, c->stream>>>(g, c->cell_start, c->d_counters + 7);
+	launches += 4;
+	CUDA_TRY(cudaMemcpyAsync(c->h_counters, c->d_counters, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
 	CUDA_TRY(cudaStreamSynchronize(c->stream));
 	size_t n_new = c->h_counters[0];
+	c->max_row = c->h_counters[7];
 	if (n_new > c->cap) {
 		timer_stop(c, LS1G_T_SORT, launches);
 		LS1G_FAIL("ls1g: capacity exceeded by halo copies (" + std::to_string(n_new) + " > " + std::to_string(c->cap) + ")");

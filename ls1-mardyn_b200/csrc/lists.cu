@@ -30,6 +30,7 @@ static NLArgs nl_args(ls1g_ctx* c) {
 	NLArgs a;
 	a.g = c->bgrid; a.pos = c->cur.pos; a.cell = c->cur.cell; a.cell_start = c->cell_start;
 	a.lists = c->lists; a.lcount = c->lcount; a.flags = c->d_flags; a.bpr = c->list_bpr; a.nyi = c->bgrid.cpd[1] - 2;
+	a.tcap = NL_TCAP;
 	const double rl = c->cfg.lj_cutoff + c->skin;
 	// FP32 filter: coordinates relative to the block centre are < 8 cell lengths: relative error on r^2 near rl^2 < 2e-5;
 	// the 3e-4 margin can only over-accept (the force kernel applies the exact FP64 test)
@@ -44,10 +45,8 @@ static size_t nl_blocks(const ls1g_ctx* c) { return (size_t)(c->bgrid.cpd[1] - 2
 // after k_sort on the bin grid: size the block grid, build the lists, remember the build positions.
 // The caller synchronises and reads h_flags[1] (overflow bits).
 int k_list_build(ls1g_ctx* c) {
-	const Grid& g = c->bgrid;
-	const size_t rows = (size_t)(g.cpd[1] - 2) * (g.cpd[2] - 2);
-	const double avg_row = (double)c->n_owned / (double)rows;
-	c->list_bpr = (int)ceil(1.3 * avg_row / NL_BT) + 1;
+	c->list_bpr = (int)((c->max_row + NL_BT - 1) / NL_BT);
+	if (c->list_bpr < 1) c->list_bpr = 1;
 	const size_t nb = nl_blocks(c);
 	const size_t want_l = nb * NL_LCAP * NL_BT, want_c = nb * NL_BT;
 	if (want_l > c->lists_cap) {
@@ -62,12 +61,12 @@ int k_list_build(ls1g_ctx* c) {
 	}
 	if (!c->pos_build) CUDA_TRY(cudaMalloc((void**)&c->pos_build, c->cap * sizeof(double4)));
 	timer_start(c, LS1G_T_SORT);
-	CUDA_TRY(cudaMemsetAsync(c->d_flags, 0, 2 * sizeof(unsigned long long), c->stream));
+	CUDA_TRY(cudaMemsetAsync(c->d_flags, 0, 3 * sizeof(unsigned long long), c->stream));
 	CUDA_TRY(cudaMemcpyAsync(c->pos_build, c->cur.pos, c->n_slots * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));
 	NLArgs a = nl_args(c);
 	nl_build_kernel<<<(unsigned)nb, NL_BT, 0, c->stream>>>(a);
 	CUDA_TRY(cudaGetLastError());
-	CUDA_TRY(cudaMemcpyAsync(c->h_flags, c->d_flags, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+	CUDA_TRY(cudaMemcpyAsync(c->h_flags, c->d_flags, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
 	timer_stop(c, LS1G_T_SORT, 2);
 	return 0;
 }
@@ -77,12 +76,13 @@ int k_forces_list(ls1g_ctx* c) {
 	if (ls1g_ensure_partials(c, nb ? nb : 1, 5)) return 1;
 	static bool attr_set = false;
 	if (!attr_set) {
-		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, NL_FORCE_SMEM));
+		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
 		attr_set = true;
 	}
 	NLArgs a = nl_args(c);
+	a.tcap = c->list_tcap;      // the largest tile of the last build: shared memory sized to what this system needs
 	timer_start(c, LS1G_T_FORCE);
-	nl_force_kernel<<<(unsigned)nb, NL_BT, NL_FORCE_SMEM, c->stream>>>(a);
+	nl_force_kernel<<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
 	timer_stop(c, LS1G_T_FORCE, 1);
 	if (k_force_finalize(c, nb)) return 1;
 	CUDA_TRY(cudaGetLastError());

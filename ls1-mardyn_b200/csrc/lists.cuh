@@ -15,14 +15,22 @@
 //   block (row, b)  = 128 consecutive owned slots [s0, s1) of one cell row (y, z); lane = one molecule
 //   tile            = the 9 neighbouring rows cut to cells [x_first-1, x_last+1] of the block's molecules: 9 contiguous
 //                     slot ranges, staged in shared memory (FP64 originals; the build adds FP32 copies for the filter)
-//   list entry      = 16-bit tile index; lists[((blk*(LCAP/8) + t/8)*128 + thread)*8 + t%8]: one 16-byte load = 8 entries
+//   row groups      = the force kernel stages the tile in three phases of three rows each (a third of the shared memory,
+//                     three times the resident warps).  Each group holds rows that are point-symmetric about the own row
+//                     ({own, two opposite corners}, {two opposite edges + a corner} x 2), so a molecule's neighbours split
+//                     evenly over the groups wherever it sits in its cell and the lanes of a warp stay in step.  A
+//                     molecule's list is grouped accordingly, each group padded to a multiple of 4 entries (sentinel 0xFFFF)
+//   list entry      = 16-bit index into the group's tile; lists[((blk*(LCAP/4) + t/4)*128 + thread)*4 + t%4]: one 8-byte
+//                     load = 4 entries; lcount packs the three cumulative group ends (in units of 4 entries, 8 bits each)
 #pragma once
 
 #define NL_BT 128          // threads per block = molecules per block
-#define NL_TCAP 2560       // tile capacity (candidates), multiple of 4
-#define NL_LCAP 128        // list entries per molecule, multiple of 8
+#define NL_TCAP 3072       // capacity of the build kernel's 9-row FP32 tile (candidates), multiple of 4
+#define NL_LCAP 128        // list entries per molecule, multiple of 4
 
-#define NL_FORCE_SMEM (3 * NL_TCAP * 8)
+// staging / scan order of the 9 neighbour rows (r = 3*(dz+1) + (dy+1)): three point-symmetric groups
+__device__ __constant__ int NL_ORD[9] = {4, 0, 8, 1, 7, 6, 3, 5, 2};
+
 
 enum { NL_OVF_TILE = 1, NL_OVF_LIST = 2, NL_OVF_ROW = 4 };
 
@@ -33,6 +41,7 @@ struct NLArgs {
 	unsigned long long* flags;  // [1] |= NL_OVF_*
 	int bpr;                    // blocks per row
 	int nyi;
+	int tcap;                   // slab tile capacity of the force launch (max slab tile of the last build), multiple of 4
 	float rl2f;                 // (rc + skin)^2 * (1 + margin), FP32 filter
 	double eps24, sig2, shift6, rclj2;
 	double *F, *Vi;
@@ -63,10 +72,10 @@ __device__ __forceinline__ NLBlock nl_plan(const NLArgs& a, uint32_t* s_beg, int
 	x_first = (int)((a.cell[b.s0] & ~HALO_FLAG) % (uint32_t)nx);
 	x_last = (int)((a.cell[b.s1 - 1] & ~HALO_FLAG) % (uint32_t)nx);
 	if (threadIdx.x < 9) {
-		const int r = threadIdx.x;
+		const int r = NL_ORD[threadIdx.x];               // s_beg / s_len / s_off are indexed by POSITION in NL_ORD
 		const int cr = ((cz + r / 3 - 1) * ny + (cy + r % 3 - 1)) * nx;
 		const uint32_t beg = a.cell_start[cr + x_first - 1], end = a.cell_start[cr + x_last + 2];
-		s_beg[r] = beg; s_len[r] = (int)(end - beg);
+		s_beg[threadIdx.x] = beg; s_len[threadIdx.x] = (int)(end - beg);
 	}
 	__syncthreads();
 	if (threadIdx.x == 0) {
@@ -94,6 +103,10 @@ __global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
 	int x_first = 0, x_last = 0;
 	const NLBlock b = nl_plan(a, s_beg, s_off, s_len, x_first, x_last);
 	if (!b.live) return;
+	if (tid == 0) {      // largest slab tile of this build: sizes the force kernel's shared memory
+		const int m = max(max(s_off[3], s_off[6] - s_off[3]), s_off[9] - s_off[6]);
+		if ((unsigned long long)m > *(volatile unsigned long long*)(a.flags + 2)) atomicMax(a.flags + 2, (unsigned long long)m);
+	}
 	const int nx = g.cpd[0], ny = g.cpd[1];
 	const int row = blockIdx.x / a.bpr;
 	const int cy = row % a.nyi + 1, cz = row / a.nyi + 1;
@@ -119,14 +132,17 @@ __global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
 	const bool active = i < w1;
 	float fx = -1e30f, fy = -1e30f, fz = -1e30f;
 	if (active) { const double4 Pi = a.pos[i]; fx = (float)(Pi.x - ox); fy = (float)(Pi.y - oy); fz = (float)(Pi.z - oz); }
-	unsigned short* my = a.lists + ((size_t)blockIdx.x * (NL_LCAP / 8) * NL_BT + tid) * 8;     // entry t at my[(t/8)*NL_BT*8 + t%8]
+	unsigned short* my = a.lists + ((size_t)blockIdx.x * (NL_LCAP / 4) * NL_BT + tid) * 4;     // entry t at my[(t/4)*NL_BT*4 + t%4]
 	int cnt = 0; bool ovf = false;
+	uint32_t ends = 0;
 	const float rl2 = a.rl2f;
-	for (int r = 0; r < 9; ++r) {
+	for (int p = 0; p < 9; ++p) {
+		const int r = NL_ORD[p];
+		const int gbase = s_off[(p / 3) * 3];          // indices are relative to the row group's tile
 		const int cr = ((cz + r / 3 - 1) * ny + (cy + r % 3 - 1)) * nx;
 		const uint32_t lo = a.cell_start[cr + xw_first - 1], hi = a.cell_start[cr + xw_last + 2];
-		const uint32_t beg = s_beg[r];
-		const int k0 = s_off[r] + (int)((lo - beg) & ~3u), k1 = s_off[r] + (int)((hi - beg + 3u) & ~3u);
+		const uint32_t beg = s_beg[p];
+		const int k0 = s_off[p] + (int)((lo - beg) & ~3u), k1 = s_off[p] + (int)((hi - beg + 3u) & ~3u);
 		for (int k = k0; k < k1; k += 4) {
 			const float4 cx4 = *(const float4*)(xs + k), cy4 = *(const float4*)(ys + k), cz4 = *(const float4*)(zs + k);
 			const float cxa[4] = {cx4.x, cx4.y, cx4.z, cx4.w}, cya[4] = {cy4.x, cy4.y, cy4.z, cy4.w}, cza[4] = {cz4.x, cz4.y, cz4.z, cz4.w};
@@ -134,12 +150,17 @@ __global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
 			for (int u = 0; u < 4; ++u) {
 				const float dx = fx - cxa[u], dy = fy - cya[u], dz = fz - cza[u];
 				const float r2 = dx * dx + dy * dy + dz * dz;
-				if (r2 < rl2) { my[(cnt >> 3) * (NL_BT * 8) + (cnt & 7)] = (unsigned short)(k + u); ++cnt; }
+				if (r2 < rl2) { my[(cnt >> 2) * (NL_BT * 4) + (cnt & 3)] = (unsigned short)(k + u - gbase); ++cnt; }
 			}
-			if (cnt > NL_LCAP - 4) { ovf = true; cnt = 0; }
+			if (cnt > NL_LCAP - 12) { ovf = true; cnt = 0; }
+		}
+		if (p % 3 == 2) {                               // end of a row group: pad it to a multiple of 4 with sentinels
+			while (cnt & 3) { my[(cnt >> 2) * (NL_BT * 4) + (cnt & 3)] = 0xFFFFu; ++cnt; }
+			ends |= (uint32_t)(cnt >> 2) << (8 * (p / 3));
+			if (cnt > NL_LCAP - 12) { ovf = true; cnt = 0; }
 		}
 	}
-	if (active) a.lcount[(size_t)blockIdx.x * NL_BT + tid] = (uint32_t)cnt;
+	if (active) a.lcount[(size_t)blockIdx.x * NL_BT + tid] = ends;
 	if (ovf && active) atomicOr(a.flags + 1, (unsigned long long)NL_OVF_LIST);
 }
 
@@ -148,7 +169,7 @@ __global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
 // ---------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 	extern __shared__ __align__(16) double nl_tile[];
-	double* xd = nl_tile; double* yd = xd + NL_TCAP; double* zd = yd + NL_TCAP;
+	double* xd = nl_tile; double* yd = xd + a.tcap; double* zd = yd + a.tcap;
 	__shared__ uint32_t s_beg[9]; __shared__ int s_off[10], s_len[9];
 	__shared__ double red[5 * 32];
 	const int tid = threadIdx.x;
@@ -156,60 +177,70 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 	const NLBlock b = nl_plan(a, s_beg, s_off, s_len, x_first, x_last);
 	double acc[5] = {0., 0., 0., 0., 0.};
 	if (b.live) {
-		for (int r = 0; r < 9; ++r) {
-			const int off = s_off[r], len = s_len[r];
-			const uint32_t beg = s_beg[r];
-			for (int t = tid; t < len; t += NL_BT) { const double4 P = a.pos[beg + t]; xd[off + t] = P.x; yd[off + t] = P.y; zd[off + t] = P.z; }
-		}
-		__syncthreads();
 		const uint32_t i = b.s0 + tid;
-		if (i < b.s1) {
-			const double4 Pi = a.pos[i];
-			const int cnt = (int)a.lcount[(size_t)blockIdx.x * NL_BT + tid];
-			const uint4* my = (const uint4*)(a.lists + ((size_t)blockIdx.x * (NL_LCAP / 8) * NL_BT + tid) * 8);   // 8 entries per load
-			double Fx = 0., Fy = 0., Fz = 0., Vx = 0., Vy = 0., Vz = 0., u6 = 0.;
-			int np_i = 0;
-			// 4 pairs at a time, branch-free (invalid pairs contribute exact zeros) so that the four dependency chains overlap
-			auto quad = [&](uint32_t w0, uint32_t w1, int t) {
-				int k[4] = {(int)(w0 & 0xffffu), (int)(w0 >> 16), (int)(w1 & 0xffffu), (int)(w1 >> 16)};
-				double dx[4], dy[4], dz[4], r2[4], sc[4], e6[4];
-				bool ok[4];
+		const bool active = i < b.s1;
+		double4 Pi = make_double4(0., 0., 0., 0.);
+		uint32_t ends = 0;
+		if (active) { Pi = a.pos[i]; ends = a.lcount[(size_t)blockIdx.x * NL_BT + tid]; }
+		const uint2* my = (const uint2*)(a.lists + ((size_t)blockIdx.x * (NL_LCAP / 4) * NL_BT + tid) * 4);   // 4 entries per load
+		double Fx = 0., Fy = 0., Fz = 0., Vx = 0., Vy = 0., Vz = 0., u6 = 0.;
+		int np_i = 0;
+		// 4 pairs at a time, branch-free (invalid pairs contribute exact zeros) so that the dependency chains overlap.
+		// eps24 and shift6 are constants of the single component: F, V accumulate d * inv*(2 lj12 - lj6) and are scaled by
+		// eps24 once; upot6 = eps24 * sum(lj12 - lj6) + shift6 * pairs.
+		double s6 = 0.;
+		auto quad = [&](const uint2& w) {
+			const uint32_t ww[2] = {w.x, w.y};
+			double dx[4], dy[4], dz[4], r2[4];
+			bool ok[4];
 #pragma unroll
-				for (int u = 0; u < 4; ++u) {
-					if (t + u >= cnt) k[u] = 0;
-					dx[u] = Pi.x - xd[k[u]]; dy[u] = Pi.y - yd[k[u]]; dz[u] = Pi.z - zd[k[u]];
-					r2[u] = dx[u] * dx[u] + dy[u] * dy[u] + dz[u] * dz[u];
-					// r2 == 0: the molecule itself, or a coincident molecule of the same cell (SingleCellPolicy_ mask, Helpers.h:367-376)
-					ok[u] = (t + u < cnt) && r2[u] < a.rclj2 && r2[u] != 0.0;
-					r2[u] = ok[u] ? r2[u] : 1.0;
-				}
+			for (int u = 0; u < 4; ++u) {
+				int k = (int)((u & 1) ? (ww[u >> 1] >> 16) : (ww[u >> 1] & 0xffffu));
+				const bool real = k != 0xFFFF;
+				k = real ? k : 0;
+				dx[u] = Pi.x - xd[k]; dy[u] = Pi.y - yd[k]; dz[u] = Pi.z - zd[k];
+				r2[u] = dx[u] * dx[u] + dy[u] * dy[u] + dz[u] * dz[u];
+				// r2 == 0: the molecule itself, or a coincident molecule of the same cell (SingleCellPolicy_ mask, Helpers.h:367-376)
+				ok[u] = real && r2[u] < a.rclj2 && r2[u] != 0.0;
+				r2[u] = ok[u] ? r2[u] : 1.0;
+			}
 #pragma unroll
-				for (int u = 0; u < 4; ++u) {
-					const double inv = fast_rcp(r2[u]);
-					const double lj2 = a.sig2 * inv, lj4 = lj2 * lj2, lj6 = lj4 * lj2, lj12 = lj6 * lj6, lj12m6 = lj12 - lj6;
-					const double scale = (a.eps24 * inv) * (lj12 + lj12m6);
-					sc[u] = ok[u] ? scale : 0.0;
-					e6[u] = ok[u] ? a.eps24 * lj12m6 + a.shift6 : 0.0;
-				}
-#pragma unroll
-				for (int u = 0; u < 4; ++u) {
-					const double px = dx[u] * sc[u], py = dy[u] * sc[u], pz = dz[u] * sc[u];
-					Fx += px; Fy += py; Fz += pz;
-					Vx += dx[u] * px; Vy += dy[u] * py; Vz += dz[u] * pz;
-					u6 += e6[u];
-					np_i += ok[u] ? 1 : 0;
-				}
-			};
-			if (cnt > 0) {
-				uint4 cur = my[0];
-				for (int t = 0; t < cnt; t += 8) {
-					uint4 nxt = cur;
-					if (t + 8 < cnt) nxt = my[((t >> 3) + 1) * NL_BT];      // prefetch the next 8 entries
-					quad(cur.x, cur.y, t);
-					if (t + 4 < cnt) quad(cur.z, cur.w, t + 4);
+			for (int u = 0; u < 4; ++u) {
+				const double inv = fast_rcp(r2[u]);
+				const double lj2 = a.sig2 * inv, lj4 = lj2 * lj2, lj6 = lj4 * lj2, lj12 = lj6 * lj6, lj12m6 = lj12 - lj6;
+				double sc = inv * (lj12 + lj12m6);
+				sc = ok[u] ? sc : 0.0;
+				s6 += ok[u] ? lj12m6 : 0.0;
+				const double px = dx[u] * sc, py = dy[u] * sc, pz = dz[u] * sc;
+				Fx += px; Fy += py; Fz += pz;
+				Vx += dx[u] * px; Vy += dy[u] * py; Vz += dz[u] * pz;
+				np_i += ok[u] ? 1 : 0;
+			}
+		};
+		int o = 0;                                       // next group of 4 entries of this molecule
+		for (int gz = 0; gz < 3; ++gz) {
+			if (gz) __syncthreads();                     // everyone is done with the previous row group
+			const int gbase = s_off[3 * gz];
+			for (int r = 3 * gz; r < 3 * gz + 3; ++r) {
+				const int off = s_off[r] - gbase, len = s_len[r];
+				const uint32_t beg = s_beg[r];
+				for (int t = tid; t < len; t += NL_BT) { const double4 P = a.pos[beg + t]; xd[off + t] = P.x; yd[off + t] = P.y; zd[off + t] = P.z; }
+			}
+			__syncthreads();
+			const int oend = (int)((ends >> (8 * gz)) & 0xffu);
+			if (o < oend) {
+				uint2 cur = my[o * NL_BT];
+				for (; o < oend; ++o) {
+					uint2 nxt = cur;
+					if (o + 1 < oend) nxt = my[(o + 1) * NL_BT];      // prefetch the next 4 entries
+					quad(cur);
 					cur = nxt;
 				}
 			}
+		}
+		if (active) {
+			Fx *= a.eps24; Fy *= a.eps24; Fz *= a.eps24; Vx *= a.eps24; Vy *= a.eps24; Vz *= a.eps24;
+			u6 = a.eps24 * s6 + a.shift6 * (double)np_i;
 			double* Fp = a.F + 3 * (size_t)i; double* Vp = a.Vi + 3 * (size_t)i;
 			Fp[0] = Fx; Fp[1] = Fy; Fp[2] = Fz; Vp[0] = 0.5 * Vx; Vp[1] = 0.5 * Vy; Vp[2] = 0.5 * Vz;
 			acc[0] = u6; acc[2] = Vx + Vy + Vz; acc[4] = (double)np_i;

@@ -95,6 +95,7 @@ struct ls1g_ctx {
 	size_t n_slots;                         // slots in use (owned + halo copies), cell-sorted if sorted
 	size_t n_owned, n_halo;
 	size_t n_uploaded;                      // n of the last ls1g_upload (ls1g_upload_forces refers to it)
+	uint32_t max_row;                       // owned molecules of the fullest cell row after the last sort
 	int    sorted;                          // cell[] / cell_start valid
 	int    forces_valid;
 	MolBuf cur, alt;                        // double buffer for the sort
@@ -112,6 +113,7 @@ struct ls1g_ctx {
 	unsigned short* lists; size_t lists_cap;// [blocks][LCAP][128] tile indices
 	uint32_t* lcount; size_t lcount_cap;    // [blocks*128]
 	int      track_disp;                    // integrate kernels track max |r - pos_build|^2 into d_flags[0]
+	int      list_tcap;                     // tile capacity used by the list force kernel (max tile of the last build, padded)
 	int      list_bpr;                      // blocks per cell row
 	unsigned long long* d_flags;            // [4]: max displacement^2 bits | overflow bits
 	unsigned long long* h_flags;            // pinned mirror      // device staging area of the host<->device transfers (transfer.cu)

@@ -5,6 +5,7 @@
 #include <math.h>
 #include <string.h>
 #include <stdio.h>
+#include <time.h>
 #include <stdlib.h>
 
 int k_post_pre(ls1g_ctx* c, double dt, int do_post, int do_pre, int thermostat, double target_T);
@@ -107,6 +108,9 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 				return 0;
 			}
 			c->track_disp = 1;
+			c->list_tcap = (int)((c->h_flags[2] + 63) & ~63ull);
+			if (getenv("LS1G_DEBUG")) fprintf(stderr, "ls1g: list build at step %d: max tile %llu, bpr %d, slots %zu, bin grid %d %d %d\n", s, c->h_flags[2], c->list_bpr, c->n_slots, c->bgrid.cpd[0], c->bgrid.cpd[1], c->bgrid.cpd[2]);
+			if (c->list_tcap < 64) c->list_tcap = 64;
 		} else rc = k_halo_refresh(c);
 		if (!rc) rc = k_forces_list(c);
 		if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s, c->d_scalars, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
@@ -117,6 +121,7 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 			if (!rc && sync_check(c, "ls1g_run (displacement)")) rc = 1;
 			double d2; memcpy(&d2, c->h_flags, sizeof(double));
 			need_build = 2. * sqrt(d2) > 0.999 * c->skin;       // lists stay exact while no molecule moved more than skin/2
+			if (getenv("LS1G_DEBUG") && (s < 6 || need_build)) { struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); fprintf(stderr, "ls1g: step %d done at %.3f ms, max displacement %.4f, rebuild %d\n", s, ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6, sqrt(d2), (int)need_build); }
 		}
 	}
 	c->track_disp = 0;
