@@ -25,6 +25,7 @@
 #include <dlfcn.h>
 #include <string.h>
 #include <stdlib.h>
+#include <vector>
 
 // ---- minimal NCCL surface (signatures from nccl.h 2.2x; loaded with dlsym) ------------------------
 typedef struct ncclComm* ncclComm_t;
@@ -73,11 +74,15 @@ struct PackArgs {
 	double shift[2];          // periodic shift applied for direction 0 (lower) / 1 (upper); 0 = none
 	double global_len;
 	double* out[2]; uint32_t* counters; uint32_t cap;
+	int mode;                 // 0: leaving + halo in one pass (the reference's scheme); 1: leaving only, sent molecules are removed
+	                          // here; 2: halo copies only, the source slot of every record is remembered in rec_slot
+	uint32_t* rec_slot[2];
 };
 
 __device__ __forceinline__ void write_record(const PackArgs& a, int dir, size_t i, double4 p) {
 	uint32_t k = atomicAdd(&a.counters[dir], 1u);
 	if (k >= a.cap) return;                     // overflow: detected on the host from the counter
+	if (a.mode == 2) a.rec_slot[dir][k] = (uint32_t)i;
 	const int rec = a.has_rot ? 16 : 8;
 	double* o = a.out[dir] + (size_t)k * rec;
 	o[0] = p.x; o[1] = p.y; o[2] = p.z; o[3] = p.w;
@@ -103,6 +108,8 @@ __global__ void __launch_bounds__(256) pack_kernel(PackArgs a) {
 		double lo = dir == 0 ? g.box_min[d] : __dsub_rn(g.box_max[d], g.cutoff);
 		double hi = dir == 0 ? __dadd_rn(g.box_min[d], g.cutoff) : g.box_max[d];
 		bool slab = x >= lo && x < hi;
+		if (a.mode == 1) slab = false;
+		if (a.mode == 2) leaving = false;
 		if (!(leaving || slab)) continue;
 		double y = x;
 		double sh = a.shift[dir];
@@ -119,7 +126,32 @@ __global__ void __launch_bounds__(256) pack_kernel(PackArgs a) {
 		double4 o = p;
 		if (d == 0) o.x = y; else if (d == 1) o.y = y; else o.z = y;
 		write_record(a, dir, i, o);
+		if (a.mode == 1) a.m.cell[i] = HALO_FLAG;      // migrated: the next sort drops this slot
 	}
+}
+
+// ---- persistent halo lists (neighbour-list loop) --------------------------------------------------
+__global__ void __launch_bounds__(256) translate_slots_kernel(size_t n, const uint32_t* __restrict__ pre, uint32_t base, const uint32_t* __restrict__ new_of_old,
+                                                               uint32_t* __restrict__ post) {
+	size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (k < n) post[k] = new_of_old[pre ? pre[k] : base + (uint32_t)k];
+}
+// positions only: 3 doubles per record, shifted along the stage dimension when the neighbour is across the global boundary
+__global__ void __launch_bounds__(256) pack_pos_list_kernel(size_t n, const uint32_t* __restrict__ slots, const double4* __restrict__ pos, int dim, double shift,
+                                                             double* __restrict__ out) {
+	size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (k >= n) return;
+	double4 p = pos[slots[k]];
+	if (dim == 0) p.x += shift; else if (dim == 1) p.y += shift; else p.z += shift;
+	out[3 * k] = p.x; out[3 * k + 1] = p.y; out[3 * k + 2] = p.z;
+}
+__global__ void __launch_bounds__(256) unpack_pos_list_kernel(size_t n, const uint32_t* __restrict__ slots, const double* __restrict__ in, double4* __restrict__ pos) {
+	size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (k >= n) return;
+	const uint32_t s = slots[k];
+	double4 p = pos[s];
+	p.x = in[3 * k]; p.y = in[3 * k + 1]; p.z = in[3 * k + 2];
+	pos[s] = p;
 }
 
 __global__ void __launch_bounds__(256) unpack_kernel(const double* __restrict__ in, size_t n, size_t base, MolBuf m, int has_rot) {
@@ -166,13 +198,15 @@ static int ensure_xbuf(ls1g_ctx* c) {
 	for (int k = 0; k < 2; ++k) {
 		CUDA_TRY(cudaMalloc((void**)&c->send_buf[k], bytes));
 		CUDA_TRY(cudaMalloc((void**)&c->recv_buf[k], bytes));
+		cudaFree(c->xl_pre[k]); c->xl_pre[k] = nullptr;
+		CUDA_TRY(cudaMalloc((void**)&c->xl_pre[k], want * sizeof(uint32_t)));
 	}
 	c->xbuf_cap = want;
 	return 0;
 }
 
 // phase 1 of stage d: pack both directions; send counts end in h_counters[2], [3]
-static int stage_pack(ls1g_ctx* c, int d) {
+static int stage_pack(ls1g_ctx* c, int d, int mode = 0) {
 	if (ensure_xbuf(c)) return 1;
 	CUDA_TRY(cudaMemsetAsync(c->d_counters + 2, 0, 2 * sizeof(uint32_t), c->stream));
 	PackArgs a;
@@ -181,6 +215,7 @@ static int stage_pack(ls1g_ctx* c, int d) {
 	a.shift[0] = c->cfg.rank_coords[d] == 0 ? c->cfg.global_length[d] : 0.;
 	a.shift[1] = c->cfg.rank_coords[d] == c->cfg.rank_grid[d] - 1 ? -c->cfg.global_length[d] : 0.;
 	a.out[0] = c->send_buf[0]; a.out[1] = c->send_buf[1]; a.counters = c->d_counters + 2; a.cap = (uint32_t)c->xbuf_cap;
+	a.mode = mode; a.rec_slot[0] = c->xl_pre[0]; a.rec_slot[1] = c->xl_pre[1];
 	if (c->n_slots) pack_kernel<<<nblk(c->n_slots, 256), 256, 0, c->stream>>>(a);
 	CUDA_TRY(cudaMemcpyAsync(c->h_counters + 2, c->d_counters + 2, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
 	CUDA_TRY(cudaStreamSynchronize(c->stream));
@@ -222,16 +257,13 @@ static int check_grid_order(const ls1g_ctx* c) {
 }
 
 // ---- NCCL transport --------------------------------------------------------------------------------
-int comm_exchange(ls1g_ctx* c) {
-	if (c->comm_mode != 1) LS1G_FAIL("ls1g_exchange: multi-rank context without NCCL communicator (local groups use ls1g_exchange_group)");
-	if (check_grid_order(c)) return 1;
-	timer_start(c, LS1G_T_EXCHANGE);
+// one stage (dimension d): pack, exchange counts and records with both neighbours, append the received records.
+// n_recv_out[2]: records received from the upper / lower neighbour; *base_out: slot of the first appended record.
+static int nccl_stage(ls1g_ctx* c, int d, int mode, uint32_t n_recv_out[2], uint32_t* base_out) {
 	ncclComm_t comm = (ncclComm_t)c->nccl_comm;
 	const int rec = rec_doubles(c);
-	int launches = 0;
-	for (int d = 0; d < 3; ++d) {
-		if (c->cfg.rank_grid[d] <= 1) continue;
-		if (stage_pack(c, d)) return 1;
+	{
+		if (stage_pack(c, d, mode)) return 1;
 		const int lower = neighbour_rank(c, d, 0), upper = neighbour_rank(c, d, 1);
 		// counts: d_counters[2],[3] = my sends (lower, upper); [4] = from upper, [5] = from lower
 		NCCL_TRY(g_nccl.GroupStart());
@@ -250,11 +282,120 @@ int comm_exchange(ls1g_ctx* c) {
 		if (n_recv[0]) NCCL_TRY(g_nccl.Recv(c->recv_buf[0], (size_t)n_recv[0] * rec, NCCL_DOUBLE, upper, comm, c->stream));
 		if (n_recv[1]) NCCL_TRY(g_nccl.Recv(c->recv_buf[1], (size_t)n_recv[1] * rec, NCCL_DOUBLE, lower, comm, c->stream));
 		NCCL_TRY(g_nccl.GroupEnd());
+		*base_out = (uint32_t)c->n_slots;
 		if (stage_unpack(c, n_recv)) return 1;
+		n_recv_out[0] = n_recv[0]; n_recv_out[1] = n_recv[1];
+	}
+	return 0;
+}
+
+int comm_exchange(ls1g_ctx* c) {
+	if (c->comm_mode != 1) LS1G_FAIL("ls1g_exchange: multi-rank context without NCCL communicator (local groups use ls1g_exchange_group)");
+	if (check_grid_order(c)) return 1;
+	timer_start(c, LS1G_T_EXCHANGE);
+	int launches = 0;
+	for (int d = 0; d < 3; ++d) {
+		if (c->cfg.rank_grid[d] <= 1) continue;
+		uint32_t nr[2], base;
+		if (nccl_stage(c, d, 0, nr, &base)) return 1;
 		launches += 4;
 	}
 	timer_stop(c, LS1G_T_EXCHANGE, launches);
 	return finish_exchange(c);
+}
+
+static int ensure_u32(uint32_t** p, size_t* cap, size_t want) {
+	if (*cap >= want && *p) return 0;
+	cudaFree(*p); *p = nullptr; *cap = 0;
+	CUDA_TRY(cudaMalloc((void**)p, (want + want / 8 + 1024) * sizeof(uint32_t)));
+	*cap = want + want / 8 + 1024;
+	return 0;
+}
+
+// Exchange of a list-build step.  The reference sends leaving molecules together with the halo copies and keeps the
+// leaver's old copy as the sender's halo particle (CommunicationPartner.h:55); with a frozen layout that copy would never be
+// refreshed, so here ownership moves first (pass 1), then the halo copies are created (pass 2) and every stage remembers
+// which slots it sent and where the received copies live: comm_refresh re-sends just their positions on later steps.
+int comm_exchange_build(ls1g_ctx* c) {
+	if (c->comm_mode != 1) LS1G_FAIL("ls1g_run: multi-rank neighbour lists need the NCCL transport");
+	if (check_grid_order(c)) return 1;
+	timer_start(c, LS1G_T_EXCHANGE);
+	int launches = 0;
+	uint32_t nr[2], base;
+	for (int d = 0; d < 3; ++d) {
+		if (c->cfg.rank_grid[d] <= 1) continue;
+		if (nccl_stage(c, d, 1, nr, &base)) return 1;
+		launches += 4;
+	}
+	// pre-sort bookkeeping of pass 2, translated after the sort
+	std::vector<uint32_t*> pre_copy;
+	for (int d = 0; d < 3; ++d) {
+		for (int k = 0; k < 2; ++k) { c->xl_n_send[d][k] = c->xl_n_recv[d][k] = 0; c->xl_recv_base[d][k] = 0; }
+		if (c->cfg.rank_grid[d] <= 1) continue;
+		if (nccl_stage(c, d, 2, nr, &base)) return 1;
+		launches += 4;
+		for (int k = 0; k < 2; ++k) {
+			c->xl_n_send[d][k] = c->h_counters[2 + k];
+			if (ensure_u32(&c->xl_send[d][k], &c->xl_send_cap[d][k], c->xl_n_send[d][k])) return 1;
+			// keep the pre-sort slots in xl_send until they are translated
+			if (c->xl_n_send[d][k]) CUDA_TRY(cudaMemcpyAsync(c->xl_send[d][k], c->xl_pre[k], c->xl_n_send[d][k] * sizeof(uint32_t), cudaMemcpyDeviceToDevice, c->stream));
+		}
+		c->xl_n_recv[d][0] = nr[0]; c->xl_n_recv[d][1] = nr[1];
+		c->xl_recv_base[d][0] = base; c->xl_recv_base[d][1] = base + nr[0];
+		for (int k = 0; k < 2; ++k) if (ensure_u32(&c->xl_recv[d][k], &c->xl_recv_cap[d][k], c->xl_n_recv[d][k])) return 1;
+	}
+	timer_stop(c, LS1G_T_EXCHANGE, launches);
+	if (finish_exchange(c)) return 1;
+	const uint32_t* new_of_old = c->alt.cell;     // valid directly after k_sort (cells.cu: gather_kernel)
+	for (int d = 0; d < 3; ++d)
+		for (int k = 0; k < 2; ++k) {
+			if (c->xl_n_send[d][k])
+				translate_slots_kernel<<<nblk(c->xl_n_send[d][k], 256), 256, 0, c->stream>>>(c->xl_n_send[d][k], c->xl_send[d][k], 0, new_of_old, c->xl_send[d][k]);
+			if (c->xl_n_recv[d][k])
+				translate_slots_kernel<<<nblk(c->xl_n_recv[d][k], 256), 256, 0, c->stream>>>(c->xl_n_recv[d][k], nullptr, c->xl_recv_base[d][k], new_of_old, c->xl_recv[d][k]);
+		}
+	CUDA_TRY(cudaGetLastError());
+	return 0;
+}
+
+// frozen-layout step: positions of the halo copies follow their owners, stage by stage (x, y, z: forwarded copies are
+// refreshed before they are forwarded again)
+int comm_refresh(ls1g_ctx* c) {
+	ncclComm_t comm = (ncclComm_t)c->nccl_comm;
+	timer_start(c, LS1G_T_EXCHANGE);
+	int launches = 0;
+	for (int d = 0; d < 3; ++d) {
+		if (c->cfg.rank_grid[d] <= 1) continue;
+		const int lower = neighbour_rank(c, d, 0), upper = neighbour_rank(c, d, 1);
+		const double shift[2] = {c->cfg.rank_coords[d] == 0 ? c->cfg.global_length[d] : 0.,
+		                         c->cfg.rank_coords[d] == c->cfg.rank_grid[d] - 1 ? -c->cfg.global_length[d] : 0.};
+		for (int k = 0; k < 2; ++k)
+			if (c->xl_n_send[d][k]) {
+				pack_pos_list_kernel<<<nblk(c->xl_n_send[d][k], 256), 256, 0, c->stream>>>(c->xl_n_send[d][k], c->xl_send[d][k], c->cur.pos, d, shift[k], c->send_buf[k]);
+				++launches;
+			}
+		NCCL_TRY(g_nccl.GroupStart());
+		if (c->xl_n_send[d][0]) NCCL_TRY(g_nccl.Send(c->send_buf[0], (size_t)c->xl_n_send[d][0] * 3, NCCL_DOUBLE, lower, comm, c->stream));
+		if (c->xl_n_send[d][1]) NCCL_TRY(g_nccl.Send(c->send_buf[1], (size_t)c->xl_n_send[d][1] * 3, NCCL_DOUBLE, upper, comm, c->stream));
+		if (c->xl_n_recv[d][0]) NCCL_TRY(g_nccl.Recv(c->recv_buf[0], (size_t)c->xl_n_recv[d][0] * 3, NCCL_DOUBLE, upper, comm, c->stream));
+		if (c->xl_n_recv[d][1]) NCCL_TRY(g_nccl.Recv(c->recv_buf[1], (size_t)c->xl_n_recv[d][1] * 3, NCCL_DOUBLE, lower, comm, c->stream));
+		NCCL_TRY(g_nccl.GroupEnd());
+		for (int k = 0; k < 2; ++k)
+			if (c->xl_n_recv[d][k]) {
+				unpack_pos_list_kernel<<<nblk(c->xl_n_recv[d][k], 256), 256, 0, c->stream>>>(c->xl_n_recv[d][k], c->xl_recv[d][k], c->recv_buf[k], c->cur.pos);
+				++launches;
+			}
+	}
+	CUDA_TRY(cudaGetLastError());
+	timer_stop(c, LS1G_T_EXCHANGE, launches);
+	return 0;
+}
+
+int comm_allreduce_max(ls1g_ctx* c, double* d_vals, int n) {
+	if (c->n_ranks <= 1) return 0;
+	if (c->comm_mode != 1) LS1G_FAIL("ls1g: device all-reduce needs the NCCL transport");
+	NCCL_TRY(g_nccl.AllReduce(d_vals, d_vals, (size_t)n, NCCL_DOUBLE, 2 /* ncclMax */, (ncclComm_t)c->nccl_comm, c->stream));
+	return 0;
 }
 
 int comm_allreduce(ls1g_ctx* c, double* d_vals, int n) {

@@ -13,7 +13,7 @@ static inline unsigned nblk(size_t n, unsigned t) { return (unsigned)((n + t - 1
 
 // list mode applies to: one rank, single-centre LJ, default kernels, skin > 0, not disabled by an earlier overflow
 int nl_applicable(const ls1g_ctx* c) {
-	return c->simple_1clj && c->n_ranks == 1 && c->force_variant == 0 && c->skin > 0. && !c->list_disabled;
+	return c->simple_1clj && (c->n_ranks == 1 || c->comm_mode == 1) && c->force_variant == 0 && c->skin > 0. && !c->list_disabled;
 }
 
 // switch the bin grid: cells >= cutoff + skin (list mode) or the reference grid

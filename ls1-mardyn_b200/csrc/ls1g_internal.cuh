@@ -136,6 +136,11 @@ struct ls1g_ctx {
 	void* nccl_comm; int n_ranks, rank;
 	int comm_mode;                          // 0 single rank, 1 NCCL, 2 in-process local group (tests)
 	double *send_buf[2], *recv_buf[2]; size_t xbuf_cap;
+	// persistent halo lists of the neighbour-list loop (comm.cu: comm_exchange_build / comm_refresh), per stage and direction
+	uint32_t *xl_send[3][2], *xl_recv[3][2];   // device: slots to send / slots the received positions go to (post-sort numbering)
+	size_t   xl_send_cap[3][2], xl_recv_cap[3][2];
+	uint32_t xl_n_send[3][2], xl_n_recv[3][2], xl_recv_base[3][2];
+	uint32_t *xl_pre[2];                       // device scratch: pre-sort slot of every packed record (current stage)
 
 	Timer timers[LS1G_T_COUNT];
 	std::vector<PendingEvt> pending;        // event pairs not yet resolved into timers[]
@@ -170,6 +175,9 @@ int  k_forces(ls1g_ctx* c);                           // results in d_scalars[0.
 int  k_fp64_peak(int device, double* tflops);
 // comm.cu
 int  comm_exchange(ls1g_ctx* c);
+int  comm_exchange_build(ls1g_ctx* c);         // list mode: migrate leavers, then halo pass with persistent lists, sort
+int  comm_refresh(ls1g_ctx* c);                // list mode: refresh halo positions along the persistent lists
+int  comm_allreduce_max(ls1g_ctx* c, double* d_vals, int n);
 int  comm_allreduce(ls1g_ctx* c, double* d_vals, int n);
 void comm_destroy(ls1g_ctx* c);
 

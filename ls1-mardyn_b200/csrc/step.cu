@@ -95,11 +95,19 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 		if (need_build) {
 			c->sorted = 0; c->track_disp = 0;
 			c->forces_valid = 0;
-			rc = k_sort(c, 1);
+			rc = c->n_ranks > 1 ? comm_exchange_build(c) : k_sort(c, 1);
 			c->forces_valid = 1;
 			if (!rc) rc = k_halo_map(c);
 			if (!rc) rc = k_list_build(c);
 			if (!rc && sync_check(c, "ls1g_run (list build)")) rc = 1;
+			if (!rc && c->n_ranks > 1) {         // every rank must take the same decision
+				double ovf = c->h_flags[1] ? 1. : 0.;
+				if (cudaMemcpyAsync(c->d_scalars + 12, &ovf, sizeof(double), cudaMemcpyHostToDevice, c->stream) != cudaSuccess) rc = 1;
+				if (!rc) rc = comm_allreduce_max(c, c->d_scalars + 12, 1);
+				if (!rc && cudaMemcpyAsync(&ovf, c->d_scalars + 12, sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess) rc = 1;
+				if (!rc && sync_check(c, "ls1g_run (list build)")) rc = 1;
+				if (ovf != 0. && !c->h_flags[1]) c->h_flags[1] = 8;
+			}
 			if (!rc && c->h_flags[1]) {          // tile / list / row capacity exceeded: this system is too dense for the list buffers
 				c->list_disabled = 1;
 				if (getenv("LS1G_DEBUG")) fprintf(stderr, "ls1g: neighbour lists disabled, overflow bits %llu (1 tile, 2 list, 4 row), bpr %d\n", c->h_flags[1], c->list_bpr);
@@ -111,13 +119,17 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 			c->list_tcap = (int)((c->h_flags[2] + 63) & ~63ull);
 			if (getenv("LS1G_DEBUG")) fprintf(stderr, "ls1g: list build at step %d: max tile %llu, bpr %d, slots %zu, bin grid %d %d %d\n", s, c->h_flags[2], c->list_bpr, c->n_slots, c->bgrid.cpd[0], c->bgrid.cpd[1], c->bgrid.cpd[2]);
 			if (c->list_tcap < 64) c->list_tcap = 64;
-		} else rc = k_halo_refresh(c);
+		} else {
+			if (c->n_ranks > 1) rc = comm_refresh(c);
+			if (!rc) rc = k_halo_refresh(c);
+		}
 		if (!rc) rc = k_forces_list(c);
 		if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s, c->d_scalars, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
 		if (!rc) rc = k_post_pre(c, dt, 1, s + 1 < n_steps, thermo, target_T);
 		if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s + 4, c->d_scalars + 4, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
 		if (!rc && s + 1 < n_steps) {
-			if (cudaMemcpyAsync(c->h_flags, c->d_flags, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess) rc = 1;
+			if (c->n_ranks > 1) rc = comm_allreduce_max(c, (double*)c->d_flags, 1);     // non-negative doubles: bit order == value order
+			if (!rc && cudaMemcpyAsync(c->h_flags, c->d_flags, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess) rc = 1;
 			if (!rc && sync_check(c, "ls1g_run (displacement)")) rc = 1;
 			double d2; memcpy(&d2, c->h_flags, sizeof(double));
 			need_build = 2. * sqrt(d2) > 0.999 * c->skin;       // lists stay exact while no molecule moved more than skin/2
@@ -129,7 +141,7 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 	// leave the state as the per-step loop does: wrapped positions, sorted on the reference grid, halo copies dropped
 	if (nl_set_bin_grid(c, 0)) return 1;
 	c->sorted = 0;
-	if (k_sort(c, 1)) return 1;
+	if (c->n_ranks > 1 ? comm_exchange(c) : k_sort(c, 1)) return 1;
 	if (k_drop_halo(c)) return 1;
 	*done = n_steps;
 	return 0;
