@@ -413,6 +413,16 @@ def main_b200(args):
     del cells_all
     flops = lj_flops(n_dist, n_pairs)
     force_ms = tm["force"]["ms"] / max(tm["force"]["launches"], 1)
+    traffic, traffic_src = None, None
+    prof = os.path.join(ROOT, "profiles", "r01_ncu_nl_force_10M_summary.csv")
+    if os.path.exists(prof) and args.cells == CELLS_PER_GPU:      # dram bytes of ONE launch from the committed ncu --set full capture
+        vals = {}
+        for ln in open(prof):
+            f = ln.strip().split(",")
+            if len(f) >= 3 and f[0].startswith("dram__bytes_"):
+                vals[f[0]] = float(f[1]) * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}.get(f[2], 1.0)
+        if len(vals) == 2:
+            traffic, traffic_src = sum(vals.values()), "profiles/r01_ncu_nl_force_10M_summary.csv (ncu --set full, one launch, same workload)"
     peak = ls1g.fp64_peak_tflops(local) if rank == 0 else 0.0
     achieved = flops / (force_ms * 1e-3) / 1e12 if force_ms > 0 else 0.0
     launches = sum(t["launches"] for t in tm.values())
@@ -458,11 +468,12 @@ def main_b200(args):
                 "e2e": {"value": round(e2e_val, 2), "unit": "MMUPS", "h2d_bytes_per_step": h2d // k_e2e, "d2h_bytes_per_step": d2h // k_e2e,
                         "steps": k_e2e, "what": "per step: add_particles(id,cid,r,v)+set_forces(F) from pinned host, ls1g_run(1), download(id,r,v,F) to pinned host"},
                 "gpu_launches": int(launches),
-                "roofline": {"bound": "fp64", "kernel": "force_1clj", "achieved": round(achieved, 3), "peak": round(peak, 3), "unit": "TFLOP/s",
-                             "frac": round(achieved / peak, 4) if peak > 0 else None, "traffic": None,
+                "roofline": {"bound": "fp64", "kernel": "nl_force_kernel (lists.cuh)", "achieved": round(achieved, 3), "peak": round(peak, 3), "unit": "TFLOP/s",
+                             "frac": round(achieved / peak, 4) if peak > 0 else None, "traffic": traffic, "traffic_source": traffic_src,
                              "peak_source": "measured here: dependent-free DFMA kernel (ls1g_measure_fp64_peak); MEASURED_PEAKS.json has no FP64 figure",
                              "flops_per_launch": flops, "n_dist": n_dist, "n_pairs": n_pairs, "kernel_ms": round(force_ms, 4),
-                             "model": "FlopCounter: 8*N_dist + 41*N_pairs (Newton-3 counts)"},
+                             "model": "FlopCounter: 8*N_dist + 41*N_pairs (Newton-3 counts); the kernel is owner-computes and executes ~2x these",
+                             "note": "bound is the FP64 FMA pipe (SURVEY 8d), not HBM/tensor: ncu sm__pipe_fp64_cycles_active 64 % (profiles/)"},
                 "kernel_ms_per_step": {k: round(t["ms"] / args.steps, 4) for k, t in tm.items()},
                 "clocks": clk}
         if cb is not None:

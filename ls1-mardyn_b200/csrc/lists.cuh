@@ -15,10 +15,10 @@
 //   block (row, b)  = 128 consecutive owned slots [s0, s1) of one cell row (y, z); lane = one molecule
 //   tile            = the 9 neighbouring rows cut to cells [x_first-1, x_last+1] of the block's molecules: 9 contiguous
 //                     slot ranges, staged in shared memory (FP64 originals; the build adds FP32 copies for the filter)
-//   row groups      = the force kernel stages the tile in three phases of three rows each (a third of the shared memory,
-//                     three times the resident warps).  Each group holds rows that are point-symmetric about the own row
-//                     ({own, two opposite corners}, {two opposite edges + a corner} x 2), so a molecule's neighbours split
-//                     evenly over the groups wherever it sits in its cell and the lanes of a warp stay in step.  A
+//   row groups      = the force kernel stages the tile in three phases (less than half the shared memory, twice the
+//                     resident warps).  Every group is point-symmetric about the own row: {own row + 2 opposite corner
+//                     rows}, {the 4 edge rows}, {the other 2 corner rows}; wherever a molecule sits in its cell, what it
+//                     loses in one row of a group it gains in the opposite one, so the lanes of a warp stay in step.  A
 //                     molecule's list is grouped accordingly, each group padded to a multiple of 4 entries (sentinel 0xFFFF)
 //   list entry      = 16-bit index into the group's tile; lists[((blk*(LCAP/4) + t/4)*128 + thread)*4 + t%4]: one 8-byte
 //                     load = 4 entries; lcount packs the three cumulative group ends (in units of 4 entries, 8 bits each)
@@ -29,7 +29,8 @@
 #define NL_LCAP 128        // list entries per molecule, multiple of 4
 
 // staging / scan order of the 9 neighbour rows (r = 3*(dz+1) + (dy+1)): three point-symmetric groups
-__device__ __constant__ int NL_ORD[9] = {4, 0, 8, 1, 7, 6, 3, 5, 2};
+__device__ __constant__ int NL_ORD[9] = {4, 0, 8, 1, 7, 3, 5, 2, 6};
+__device__ __constant__ int NL_GRP[4] = {0, 3, 7, 9};      // group g = positions [NL_GRP[g], NL_GRP[g+1]) of NL_ORD
 
 
 enum { NL_OVF_TILE = 1, NL_OVF_LIST = 2, NL_OVF_ROW = 4 };
@@ -104,7 +105,7 @@ __global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
 	const NLBlock b = nl_plan(a, s_beg, s_off, s_len, x_first, x_last);
 	if (!b.live) return;
 	if (tid == 0) {      // largest slab tile of this build: sizes the force kernel's shared memory
-		const int m = max(max(s_off[3], s_off[6] - s_off[3]), s_off[9] - s_off[6]);
+		const int m = max(max(s_off[3], s_off[7] - s_off[3]), s_off[9] - s_off[7]);
 		if ((unsigned long long)m > *(volatile unsigned long long*)(a.flags + 2)) atomicMax(a.flags + 2, (unsigned long long)m);
 	}
 	const int nx = g.cpd[0], ny = g.cpd[1];
@@ -136,9 +137,10 @@ __global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
 	int cnt = 0; bool ovf = false;
 	uint32_t ends = 0;
 	const float rl2 = a.rl2f;
+	int grp = 0;
 	for (int p = 0; p < 9; ++p) {
 		const int r = NL_ORD[p];
-		const int gbase = s_off[(p / 3) * 3];          // indices are relative to the row group's tile
+		const int gbase = s_off[NL_GRP[grp]];          // indices are relative to the row group's tile
 		const int cr = ((cz + r / 3 - 1) * ny + (cy + r % 3 - 1)) * nx;
 		const uint32_t lo = a.cell_start[cr + xw_first - 1], hi = a.cell_start[cr + xw_last + 2];
 		const uint32_t beg = s_beg[p];
@@ -154,9 +156,10 @@ __global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
 			}
 			if (cnt > NL_LCAP - 12) { ovf = true; cnt = 0; }
 		}
-		if (p % 3 == 2) {                               // end of a row group: pad it to a multiple of 4 with sentinels
+		if (p + 1 == NL_GRP[grp + 1]) {                 // end of a row group: pad it to a multiple of 4 with sentinels
 			while (cnt & 3) { my[(cnt >> 2) * (NL_BT * 4) + (cnt & 3)] = 0xFFFFu; ++cnt; }
-			ends |= (uint32_t)(cnt >> 2) << (8 * (p / 3));
+			ends |= (uint32_t)(cnt >> 2) << (8 * grp);
+			++grp;
 			if (cnt > NL_LCAP - 12) { ovf = true; cnt = 0; }
 		}
 	}
@@ -169,7 +172,7 @@ __global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
 // ---------------------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 	extern __shared__ __align__(16) double nl_tile[];
-	double* xd = nl_tile; double* yd = xd + a.tcap; double* zd = yd + a.tcap;
+	double* tile = nl_tile;                         // [tcap][3]: x y z of candidate k at tile[3k..3k+2]
 	__shared__ uint32_t s_beg[9]; __shared__ int s_off[10], s_len[9];
 	__shared__ double red[5 * 32];
 	const int tid = threadIdx.x;
@@ -189,6 +192,7 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 		// eps24 and shift6 are constants of the single component: F, V accumulate d * inv*(2 lj12 - lj6) and are scaled by
 		// eps24 once; upot6 = eps24 * sum(lj12 - lj6) + shift6 * pairs.
 		double s6 = 0.;
+		const long long rc2b = __double_as_longlong(a.rclj2);
 		auto quad = [&](const uint2& w) {
 			const uint32_t ww[2] = {w.x, w.y};
 			double dx[4], dy[4], dz[4], r2[4];
@@ -198,18 +202,21 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 				int k = (int)((u & 1) ? (ww[u >> 1] >> 16) : (ww[u >> 1] & 0xffffu));
 				const bool real = k != 0xFFFF;
 				k = real ? k : 0;
-				dx[u] = Pi.x - xd[k]; dy[u] = Pi.y - yd[k]; dz[u] = Pi.z - zd[k];
+				const double* pk = tile + 3 * k;
+				dx[u] = Pi.x - pk[0]; dy[u] = Pi.y - pk[1]; dz[u] = Pi.z - pk[2];
 				r2[u] = dx[u] * dx[u] + dy[u] * dy[u] + dz[u] * dz[u];
-				// r2 == 0: the molecule itself, or a coincident molecule of the same cell (SingleCellPolicy_ mask, Helpers.h:367-376)
-				ok[u] = real && r2[u] < a.rclj2 && r2[u] != 0.0;
-				r2[u] = ok[u] ? r2[u] : 1.0;
+				// r2 == 0: the molecule itself, or a coincident molecule of the same cell (SingleCellPolicy_ mask, Helpers.h:367-376).
+				// r2 and rc^2 are non-negative doubles: their order is the order of their bit patterns, so both tests run on
+				// the integer pipe and leave the FP64 pipe to the force arithmetic
+				const long long r2b = __double_as_longlong(r2[u]);
+				ok[u] = real && r2b < rc2b && r2b != 0;
 			}
 #pragma unroll
 			for (int u = 0; u < 4; ++u) {
-				const double inv = fast_rcp(r2[u]);
+				const double inv = fast_rcp3(r2[u]);
 				const double lj2 = a.sig2 * inv, lj4 = lj2 * lj2, lj6 = lj4 * lj2, lj12 = lj6 * lj6, lj12m6 = lj12 - lj6;
 				double sc = inv * (lj12 + lj12m6);
-				sc = ok[u] ? sc : 0.0;
+				sc = ok[u] ? sc : 0.0;                    // (a rejected pair may have produced inf/nan: selected away, never multiplied)
 				s6 += ok[u] ? lj12m6 : 0.0;
 				const double px = dx[u] * sc, py = dy[u] * sc, pz = dz[u] * sc;
 				Fx += px; Fy += py; Fz += pz;
@@ -220,11 +227,11 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 		int o = 0;                                       // next group of 4 entries of this molecule
 		for (int gz = 0; gz < 3; ++gz) {
 			if (gz) __syncthreads();                     // everyone is done with the previous row group
-			const int gbase = s_off[3 * gz];
-			for (int r = 3 * gz; r < 3 * gz + 3; ++r) {
+			const int gbase = s_off[NL_GRP[gz]];
+			for (int r = NL_GRP[gz]; r < NL_GRP[gz + 1]; ++r) {
 				const int off = s_off[r] - gbase, len = s_len[r];
 				const uint32_t beg = s_beg[r];
-				for (int t = tid; t < len; t += NL_BT) { const double4 P = a.pos[beg + t]; xd[off + t] = P.x; yd[off + t] = P.y; zd[off + t] = P.z; }
+				for (int t = tid; t < len; t += NL_BT) { const double4 P = a.pos[beg + t]; double* q = tile + 3 * (off + t); q[0] = P.x; q[1] = P.y; q[2] = P.z; }
 			}
 			__syncthreads();
 			const int oend = (int)((ends >> (8 * gz)) & 0xffu);
