@@ -19,14 +19,16 @@
 //                     resident warps).  Every group is point-symmetric about the own row: {own row + 2 opposite corner
 //                     rows}, {the 4 edge rows}, {the other 2 corner rows}; wherever a molecule sits in its cell, what it
 //                     loses in one row of a group it gains in the opposite one, so the lanes of a warp stay in step.  A
-//                     molecule's list is grouped accordingly, each group padded to a multiple of 4 entries (sentinel 0xFFFF)
-//   list entry      = 16-bit index into the group's tile; lists[((blk*(LCAP/4) + t/4)*128 + thread)*4 + t%4]: one 8-byte
+//                     molecule's list is grouped accordingly, each group padded to a multiple of 4 entries with index 0
+//   list entry      = 16-bit index into the group's tile + NL_DUMMY; tile entries 0..NL_DUMMY-1 hold a far-away dummy
+//                     position (r^2 = inf fails the cutoff test), so padding needs no special case; lists[((blk*(LCAP/4) + t/4)*128 + thread)*4 + t%4]: one 8-byte
 //                     load = 4 entries; lcount packs the three cumulative group ends (in units of 4 entries, 8 bits each)
 #pragma once
 
 #define NL_BT 128          // threads per block = molecules per block
 #define NL_TCAP 3072       // capacity of the build kernel's 9-row FP32 tile (candidates), multiple of 4
 #define NL_LCAP 128        // list entries per molecule, multiple of 4
+#define NL_DUMMY 4         // dummy entries at the start of every group tile (keeps real entries 4-aligned)
 
 // staging / scan order of the 9 neighbour rows (r = 3*(dz+1) + (dy+1)): three point-symmetric groups
 __device__ __constant__ int NL_ORD[9] = {4, 0, 8, 1, 7, 3, 5, 2, 6};
@@ -105,7 +107,7 @@ __global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
 	const NLBlock b = nl_plan(a, s_beg, s_off, s_len, x_first, x_last);
 	if (!b.live) return;
 	if (tid == 0) {      // largest slab tile of this build: sizes the force kernel's shared memory
-		const int m = max(max(s_off[3], s_off[7] - s_off[3]), s_off[9] - s_off[7]);
+		const int m = max(max(s_off[3], s_off[7] - s_off[3]), s_off[9] - s_off[7]) + NL_DUMMY;
 		if ((unsigned long long)m > *(volatile unsigned long long*)(a.flags + 2)) atomicMax(a.flags + 2, (unsigned long long)m);
 	}
 	const int nx = g.cpd[0], ny = g.cpd[1];
@@ -152,12 +154,12 @@ __global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
 			for (int u = 0; u < 4; ++u) {
 				const float dx = fx - cxa[u], dy = fy - cya[u], dz = fz - cza[u];
 				const float r2 = dx * dx + dy * dy + dz * dz;
-				if (r2 < rl2) { my[(cnt >> 2) * (NL_BT * 4) + (cnt & 3)] = (unsigned short)(k + u - gbase); ++cnt; }
+				if (r2 < rl2) { my[(cnt >> 2) * (NL_BT * 4) + (cnt & 3)] = (unsigned short)(k + u - gbase + NL_DUMMY); ++cnt; }
 			}
 			if (cnt > NL_LCAP - 12) { ovf = true; cnt = 0; }
 		}
 		if (p + 1 == NL_GRP[grp + 1]) {                 // end of a row group: pad it to a multiple of 4 with sentinels
-			while (cnt & 3) { my[(cnt >> 2) * (NL_BT * 4) + (cnt & 3)] = 0xFFFFu; ++cnt; }
+			while (cnt & 3) { my[(cnt >> 2) * (NL_BT * 4) + (cnt & 3)] = 0; ++cnt; }        // index 0 = dummy tile entry
 			ends |= (uint32_t)(cnt >> 2) << (8 * grp);
 			++grp;
 			if (cnt > NL_LCAP - 12) { ovf = true; cnt = 0; }
@@ -170,6 +172,7 @@ __global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
 // ---------------------------------------------------------------------------------------------------------------
 // force: exact FP64 test + _loopBodyLJ over the listed pairs
 // ---------------------------------------------------------------------------------------------------------------
+template <bool COUNT>
 __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 	extern __shared__ __align__(16) double nl_tile[];
 	double* tile = nl_tile;                         // [tcap][3]: x y z of candidate k at tile[3k..3k+2]
@@ -199,9 +202,7 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 			bool ok[4];
 #pragma unroll
 			for (int u = 0; u < 4; ++u) {
-				int k = (int)((u & 1) ? (ww[u >> 1] >> 16) : (ww[u >> 1] & 0xffffu));
-				const bool real = k != 0xFFFF;
-				k = real ? k : 0;
+				const int k = (int)((u & 1) ? (ww[u >> 1] >> 16) : (ww[u >> 1] & 0xffffu));
 				const double* pk = tile + 3 * k;
 				dx[u] = Pi.x - pk[0]; dy[u] = Pi.y - pk[1]; dz[u] = Pi.z - pk[2];
 				r2[u] = dx[u] * dx[u] + dy[u] * dy[u] + dz[u] * dz[u];
@@ -209,27 +210,28 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 				// r2 and rc^2 are non-negative doubles: their order is the order of their bit patterns, so both tests run on
 				// the integer pipe and leave the FP64 pipe to the force arithmetic
 				const long long r2b = __double_as_longlong(r2[u]);
-				ok[u] = real && r2b < rc2b && r2b != 0;
+				ok[u] = r2b < rc2b && r2b != 0;
 			}
 #pragma unroll
 			for (int u = 0; u < 4; ++u) {
-				const double inv = fast_rcp3(r2[u]);
+				double inv = fast_rcp3(r2[u]);
+				inv = ok[u] ? inv : 0.0;                  // rejected pair (possibly inf/nan): selected away, everything below is an exact 0
 				const double lj2 = a.sig2 * inv, lj4 = lj2 * lj2, lj6 = lj4 * lj2, lj12 = lj6 * lj6, lj12m6 = lj12 - lj6;
-				double sc = inv * (lj12 + lj12m6);
-				sc = ok[u] ? sc : 0.0;                    // (a rejected pair may have produced inf/nan: selected away, never multiplied)
-				s6 += ok[u] ? lj12m6 : 0.0;
+				const double sc = inv * (lj12 + lj12m6);
+				s6 += lj12m6;
 				const double px = dx[u] * sc, py = dy[u] * sc, pz = dz[u] * sc;
 				Fx += px; Fy += py; Fz += pz;
 				Vx += dx[u] * px; Vy += dy[u] * py; Vz += dz[u] * pz;
-				np_i += ok[u] ? 1 : 0;
+				if (COUNT) np_i += ok[u] ? 1 : 0;
 			}
 		};
 		int o = 0;                                       // next group of 4 entries of this molecule
 		for (int gz = 0; gz < 3; ++gz) {
 			if (gz) __syncthreads();                     // everyone is done with the previous row group
 			const int gbase = s_off[NL_GRP[gz]];
+			if (tid < NL_DUMMY) { double* q = tile + 3 * tid; q[0] = 1e300; q[1] = 1e300; q[2] = 1e300; }
 			for (int r = NL_GRP[gz]; r < NL_GRP[gz + 1]; ++r) {
-				const int off = s_off[r] - gbase, len = s_len[r];
+				const int off = s_off[r] - gbase + NL_DUMMY, len = s_len[r];
 				const uint32_t beg = s_beg[r];
 				for (int t = tid; t < len; t += NL_BT) { const double4 P = a.pos[beg + t]; double* q = tile + 3 * (off + t); q[0] = P.x; q[1] = P.y; q[2] = P.z; }
 			}
@@ -247,7 +249,8 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 		}
 		if (active) {
 			Fx *= a.eps24; Fy *= a.eps24; Fz *= a.eps24; Vx *= a.eps24; Vy *= a.eps24; Vz *= a.eps24;
-			u6 = a.eps24 * s6 + a.shift6 * (double)np_i;
+			u6 = a.eps24 * s6;       // + shift6 * pairs: added by the caller's finalize when the potential is shifted (COUNT)
+			if (COUNT) u6 += a.shift6 * (double)np_i;
 			double* Fp = a.F + 3 * (size_t)i; double* Vp = a.Vi + 3 * (size_t)i;
 			Fp[0] = Fx; Fp[1] = Fy; Fp[2] = Fz; Vp[0] = 0.5 * Vx; Vp[1] = 0.5 * Vy; Vp[2] = 0.5 * Vz;
 			acc[0] = u6; acc[2] = Vx + Vy + Vz; acc[4] = (double)np_i;

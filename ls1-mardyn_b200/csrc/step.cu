@@ -80,7 +80,7 @@ extern "C" int ls1g_scale(ls1g_ctx* c, double bt, double br) {
 int nl_applicable(const ls1g_ctx* c);
 int nl_set_bin_grid(ls1g_ctx* c, int list_mode);
 int k_list_build(ls1g_ctx* c);
-int k_forces_list(ls1g_ctx* c);
+int k_forces_list(ls1g_ctx* c, int count_pairs);
 int k_halo_refresh(ls1g_ctx* c);
 
 // Neighbour-list steps of ls1g_run (lists.cuh).  On entry the pre-kick of step 0 is done.  Runs steps [0, n_steps) unless
@@ -123,7 +123,7 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 			if (c->n_ranks > 1) rc = comm_refresh(c);
 			if (!rc) rc = k_halo_refresh(c);
 		}
-		if (!rc) rc = k_forces_list(c);
+		if (!rc) rc = k_forces_list(c, s + 1 == n_steps);      // pair statistics only for the last step (ls1g_last_pair_count)
 		if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s, c->d_scalars, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
 		if (!rc) rc = k_post_pre(c, dt, 1, s + 1 < n_steps, thermo, target_T);
 		if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s + 4, c->d_scalars + 4, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
