@@ -226,6 +226,12 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 			}
 		};
 		int o = 0;                                       // next group of 4 entries of this molecule
+		// list entries stream from HBM: keep three loads in flight per lane, across the row-group boundaries
+		const int oall = (int)((ends >> 16) & 0xffu);
+		uint2 p0 = make_uint2(0, 0), p1 = p0, p2 = p0;
+		if (0 < oall) p0 = my[0];
+		if (1 < oall) p1 = my[NL_BT];
+		if (2 < oall) p2 = my[2 * NL_BT];
 		for (int gz = 0; gz < 3; ++gz) {
 			if (gz) __syncthreads();                     // everyone is done with the previous row group
 			const int gbase = s_off[NL_GRP[gz]];
@@ -237,14 +243,11 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 			}
 			__syncthreads();
 			const int oend = (int)((ends >> (8 * gz)) & 0xffu);
-			if (o < oend) {
-				uint2 cur = my[o * NL_BT];
-				for (; o < oend; ++o) {
-					uint2 nxt = cur;
-					if (o + 1 < oend) nxt = my[(o + 1) * NL_BT];      // prefetch the next 4 entries
-					quad(cur);
-					cur = nxt;
-				}
+			for (; o < oend; ++o) {
+				const uint2 cur = p0;
+				p0 = p1; p1 = p2;
+				if (o + 3 < oall) p2 = my[(o + 3) * NL_BT];
+				quad(cur);
 			}
 		}
 		if (active) {
