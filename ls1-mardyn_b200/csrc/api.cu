@@ -360,6 +360,7 @@ extern "C" int ls1g_upload(ls1g_ctx* c, size_t n, const uint64_t* id, const uint
 	size_t want = c->cfg.capacity ? (size_t)c->cfg.capacity : default_capacity(c, n);
 	if (want < n) LS1G_FAIL("ls1g_upload: more molecules than the configured capacity");
 	if (c->cap < want || c->cap == 0) { if (alloc_molecules(c, std::max<size_t>(want, 1))) return 1; }
+	if (c->in_list_mode) { c->in_list_mode = 0; c->track_disp = 0; c->bgrid = c->grid; }     // the content is replaced
 	if (k_upload(c, n, id, cid, r, v, q, L)) return 1;
 	c->n_uploaded = n;
 	c->n_slots = c->n_owned = n; c->n_halo = 0; c->sorted = 0; c->forces_valid = 0;
@@ -376,6 +377,7 @@ extern "C" int ls1g_count(ls1g_ctx* c, uint64_t* n_owned, uint64_t* n_halo) {
 extern "C" int ls1g_download(ls1g_ctx* c, int mask, int include_halo, size_t capacity, ls1g_fields* out, size_t* n_out) {
 	if (!c || !out || !n_out) LS1G_FAIL("null argument");
 	CUDA_TRY(cudaSetDevice(c->cfg.device));
+	if (c->in_list_mode && ls1g_nl_leave(c)) return 1;
 	size_t ns = c->n_slots;
 	bool halo_ok = include_halo && c->n_halo > 0;
 	size_t n_ret = halo_ok ? c->n_owned + c->n_halo : c->n_owned;

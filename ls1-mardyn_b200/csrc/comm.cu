@@ -466,6 +466,7 @@ extern "C" int ls1g_comm_init_local(ls1g_ctx** ctxs, int n) {
 extern "C" int ls1g_exchange_group(ls1g_ctx** ctxs, int n) {
 	if (!ctxs || n < 1) LS1G_FAIL("ls1g_exchange_group: bad arguments");
 	if (n == 1) return ls1g_exchange(ctxs[0]);
+	for (int r = 0; r < n; ++r) if (ctxs[r]->in_list_mode && ls1g_nl_leave(ctxs[r])) return 1;
 	for (int r = 0; r < n; ++r) if (ctxs[r]->comm_mode != 2) LS1G_FAIL("ls1g_exchange_group: call ls1g_comm_init_local first");
 	for (int d = 0; d < 3; ++d) {
 		if (ctxs[0]->cfg.rank_grid[d] <= 1) continue;

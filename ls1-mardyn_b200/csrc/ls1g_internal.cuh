@@ -106,6 +106,7 @@ struct ls1g_ctx {
 	void*   stage; size_t stage_bytes;
 	// neighbour-list mode of ls1g_run (lists.cu): frozen slot layout between rebuilds
 	double   skin;                          // list radius = cutoff + skin; 0 disables the list mode
+	int      in_list_mode;                  // the slots are in the frozen neighbour-list layout (bin grid, lists valid or expired)
 	int      list_disabled;                 // set when a buffer limit was hit once: stay on the rebuild-every-step path
 	uint32_t *halo_src; uint8_t* halo_code; // [cap] per halo slot: slot of its source molecule, periodic image code
 	uint32_t *slot_dst;                     // [cap] final slot of scatter entry s (sort scratch)
@@ -166,6 +167,7 @@ int  ls1g_scan_cells(ls1g_ctx* c, const uint32_t* in, uint32_t* out);   // exclu
 int  k_upload(ls1g_ctx* c, size_t n, const uint64_t* id, const uint32_t* cid, const double* r, const double* v, const double* q, const double* L);
 int  k_upload_forces(ls1g_ctx* c, size_t n, const double* F, const double* M);
 int  k_download(ls1g_ctx* c, int mask, int include_halo, size_t n_ret, ls1g_fields* out);
+int  ls1g_nl_leave(ls1g_ctx* c);               // step.cu: back to the reference-grid state (no-op outside list mode)
 // integrate.cu
 int  k_scale(ls1g_ctx* c, double bt, double br);
 int  k_post_pre(ls1g_ctx* c, double dt, int do_post, int do_pre, int thermostat, double target_T);

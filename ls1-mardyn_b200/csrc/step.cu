@@ -12,6 +12,25 @@ int k_post_pre(ls1g_ctx* c, double dt, int do_post, int do_pre, int thermostat, 
 void ls1g_resolve_timers(ls1g_ctx* c);
 
 #define NEED(c) do { if (!(c)) LS1G_FAIL("null context"); CUDA_TRY(cudaSetDevice((c)->cfg.device)); } while (0)
+// per-step operators and transfers work on the reference-grid state: leave the neighbour-list layout first
+#define NEED_REF(c) do { NEED(c); if ((c)->in_list_mode && ls1g_nl_leave(c)) return 1; } while (0)
+
+int nl_set_bin_grid(ls1g_ctx* c, int list_mode);
+static int sync_check(ls1g_ctx* c, const char* what);
+
+// ls1g_run leaves the container in the frozen neighbour-list layout so that the next ls1g_run continues without a
+// rebuild.  Everything else first restores what the per-step loop leaves behind: wrapped positions, molecules sorted on
+// the reference grid, halo copies dropped (one exchange; collective on multi-rank contexts, like the operators themselves).
+int ls1g_nl_leave(ls1g_ctx* c) {
+	if (!c->in_list_mode) return 0;
+	c->in_list_mode = 0; c->track_disp = 0;
+	if (nl_set_bin_grid(c, 0)) return 1;
+	c->sorted = 0;
+	if (c->n_ranks > 1 ? comm_exchange(c) : k_sort(c, 1)) return 1;
+	if (k_drop_halo(c)) return 1;
+	return sync_check(c, "leaving the neighbour-list layout");
+}
+
 
 static int sync_check(ls1g_ctx* c, const char* what) {
 	cudaError_t e = cudaStreamSynchronize(c->stream);
@@ -22,21 +41,21 @@ static int sync_check(ls1g_ctx* c, const char* what) {
 
 // LinkedCells::update (LinkedCells.cpp:243-356): re-bin every owned molecule; no wrap, no halo copies
 extern "C" int ls1g_update(ls1g_ctx* c) {
-	NEED(c);
+	NEED_REF(c);
 	if (k_sort(c, 0)) return 1;
 	return sync_check(c, "ls1g_update");
 }
 
 // DomainDecompBase::exchangeMolecules (DomainDecompBase.cpp:51-86) / DomainDecomposition::balanceAndExchange
 extern "C" int ls1g_exchange(ls1g_ctx* c) {
-	NEED(c);
+	NEED_REF(c);
 	if (c->n_ranks > 1) { if (comm_exchange(c)) return 1; }
 	else if (k_sort(c, 1)) return 1;
 	return sync_check(c, "ls1g_exchange");
 }
 
 extern "C" int ls1g_traverse(ls1g_ctx* c, double* upot, double* virial) {
-	NEED(c);
+	NEED_REF(c);
 	if (k_forces(c)) return 1;
 	CUDA_TRY(cudaMemcpyAsync(c->h_scalars, c->d_scalars, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
 	if (sync_check(c, "ls1g_traverse")) return 1;
@@ -48,19 +67,19 @@ extern "C" int ls1g_traverse(ls1g_ctx* c, double* upot, double* virial) {
 }
 
 extern "C" int ls1g_delete_outer(ls1g_ctx* c) {
-	NEED(c);
+	NEED_REF(c);
 	return k_drop_halo(c);
 }
 
 extern "C" int ls1g_integrate_pre(ls1g_ctx* c, double dt) {
-	NEED(c);
+	NEED_REF(c);
 	if (k_post_pre(c, dt, 0, 1, 0, 0.)) return 1;
 	c->sorted = 0;   // positions moved: cell_start is stale until the next update/exchange
 	return sync_check(c, "ls1g_integrate_pre");
 }
 
 extern "C" int ls1g_integrate_post(ls1g_ctx* c, double dt_half, double* summv2, double* sumIw2, uint64_t* n, uint64_t* rot_dof) {
-	NEED(c);
+	NEED_REF(c);
 	if (k_post_pre(c, 2. * dt_half, 1, 0, 0, 0.)) return 1;
 	CUDA_TRY(cudaMemcpyAsync(c->h_scalars + 4, c->d_scalars + 4, 4 * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
 	if (sync_check(c, "ls1g_integrate_post")) return 1;
@@ -72,7 +91,7 @@ extern "C" int ls1g_integrate_post(ls1g_ctx* c, double dt_half, double* summv2, 
 }
 
 extern "C" int ls1g_scale(ls1g_ctx* c, double bt, double br) {
-	NEED(c);
+	NEED_REF(c);
 	if (k_scale(c, bt, br)) return 1;
 	return sync_check(c, "ls1g_scale");
 }
@@ -88,9 +107,17 @@ int k_halo_refresh(ls1g_ctx* c);
 // continue with the rebuild-every-step loop (the state is exactly what that loop expects).
 static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, double target_T, double* d_rec, int* done) {
 	*done = 0;
-	if (nl_set_bin_grid(c, 1)) return 1;
 	bool need_build = true;
 	int rc = 0, s = 0;
+	if (c->in_list_mode) {       // continuing the previous ls1g_run: the pre-kick above was tracked; rebuild only if the lists expired
+		if (c->n_ranks > 1) rc = comm_allreduce_max(c, (double*)c->d_flags, 1);
+		if (!rc && cudaMemcpyAsync(c->h_flags, c->d_flags, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess) rc = 1;
+		if (!rc && sync_check(c, "ls1g_run (displacement)")) rc = 1;
+		if (rc) return 1;
+		double d2; memcpy(&d2, c->h_flags, sizeof(double));
+		need_build = 2. * sqrt(d2) > 0.999 * c->skin;
+	} else if (nl_set_bin_grid(c, 1)) return 1;
+	c->in_list_mode = 1;
 	for (; s < n_steps && !rc; ++s) {
 		if (need_build) {
 			c->sorted = 0; c->track_disp = 0;
@@ -109,7 +136,7 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 				if (ovf != 0. && !c->h_flags[1]) c->h_flags[1] = 8;
 			}
 			if (!rc && c->h_flags[1]) {          // tile / list / row capacity exceeded: this system is too dense for the list buffers
-				c->list_disabled = 1;
+				c->list_disabled = 1; c->in_list_mode = 0; c->track_disp = 0;
 				if (getenv("LS1G_DEBUG")) fprintf(stderr, "ls1g: neighbour lists disabled, overflow bits %llu (1 tile, 2 list, 4 row), bpr %d\n", c->h_flags[1], c->list_bpr);
 				nl_set_bin_grid(c, 0);
 				*done = s;
@@ -136,12 +163,8 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 			if (getenv("LS1G_DEBUG") && (s < 6 || need_build)) { struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); fprintf(stderr, "ls1g: step %d done at %.3f ms, max displacement %.4f, rebuild %d\n", s, ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6, sqrt(d2), (int)need_build); }
 		}
 	}
-	c->track_disp = 0;
-	if (rc) { nl_set_bin_grid(c, 0); return rc; }
-	// leave the state as the per-step loop does: wrapped positions, sorted on the reference grid, halo copies dropped
-	if (nl_set_bin_grid(c, 0)) return 1;
-	c->sorted = 0;
-	if (c->n_ranks > 1 ? comm_exchange(c) : k_sort(c, 1)) return 1;
+	if (rc) { c->track_disp = 0; c->in_list_mode = 0; nl_set_bin_grid(c, 0); return rc; }
+	// stay in the frozen layout (in_list_mode): the next ls1g_run continues, any other entry point calls ls1g_nl_leave first
 	if (k_drop_halo(c)) return 1;
 	*done = n_steps;
 	return 0;
@@ -152,6 +175,7 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 extern "C" int ls1g_run(ls1g_ctx* c, int n_steps, double dt, double target_T, ls1g_step_record* records) {
 	NEED(c);
 	if (n_steps <= 0) return 0;
+	if (c->in_list_mode && !nl_applicable(c) && ls1g_nl_leave(c)) return 1;
 	if (!c->forces_valid) LS1G_FAIL("ls1g_run: forces missing - call ls1g_exchange + ls1g_traverse once (prepare_start, Simulation.cpp:813-844)");
 	const int thermo = target_T > 0.;
 	double* d_rec = nullptr;
