@@ -106,6 +106,8 @@ class ClockSampler:
         self.device, self.rows, self.proc = device, [], None
 
     def start(self):
+        if os.environ.get("LS1G_BENCH_NO_CLOCKS"):      # diagnosis only: a line without clocks is not a valid bench line
+            return
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.device), "--query-gpu=" + self.Q,
                                           "--format=csv,noheader,nounits", "-lms", "100"],

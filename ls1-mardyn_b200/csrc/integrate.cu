@@ -35,11 +35,13 @@ struct IntArgs {
 	const double4* pos_build;          // neighbour-list mode: positions at the last list build (nullptr = not tracked)
 	unsigned long long* maxdisp;       // max |r - r_build|^2 as double bits (atomicMax)
 	double* partials;      // [gridDim.x][4]
+	const unsigned long long* guard; unsigned long long guard_thr;   // skip when *guard > guard_thr (see run_list_steps)
 };
 
 template <bool POST, bool PRE, bool ROT>
 __global__ void __launch_bounds__(INT_THREADS) integrate_kernel(IntArgs a) {
 	__shared__ double red[4 * 32];
+	if (a.guard && *a.guard > a.guard_thr) return;
 	size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
 	double acc[4] = {0., 0., 0., 0.};   // summv2, sumIw2, N, rotDOF
 	double disp2 = 0.;
@@ -167,6 +169,7 @@ static IntArgs make_args(ls1g_ctx* c) {
 	a.F = c->F; a.M = c->M; a.cell = c->cur.cell; a.comps = c->comps;
 	a.dt = 0.; a.dt_half = 0.; a.betas = nullptr; a.partials = c->partials;
 	a.pos_build = c->track_disp ? c->pos_build : nullptr; a.maxdisp = c->d_flags;
+	a.guard = c->guard_on ? c->d_flags + 3 : nullptr; a.guard_thr = (unsigned long long)host_double_bits(c->disp_thr2);
 	return a;
 }
 

@@ -37,6 +37,7 @@ static NLArgs nl_args(ls1g_ctx* c) {
 	a.rl2f = (float)(rl * rl * (1.0 + 3e-4));
 	a.eps24 = c->eps24_h[0]; a.sig2 = c->sig2_h[0]; a.shift6 = c->shift6_h[0]; a.rclj2 = c->rclj2;
 	a.F = c->F; a.Vi = c->Vi; a.partials = c->partials;
+	a.guard = c->guard_on ? c->d_flags + 3 : nullptr; a.guard_thr = (unsigned long long)host_double_bits(c->disp_thr2);
 	return a;
 }
 

@@ -49,6 +49,7 @@ struct NLArgs {
 	double eps24, sig2, shift6, rclj2;
 	double *F, *Vi;
 	double* partials;           // [blocks][5]
+	const unsigned long long* guard; unsigned long long guard_thr;   // skip the launch when *guard > guard_thr (lists expired)
 };
 
 struct NLBlock {
@@ -179,6 +180,7 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 	__shared__ uint32_t s_beg[9]; __shared__ int s_off[10], s_len[9];
 	__shared__ double red[5 * 32];
 	const int tid = threadIdx.x;
+	if (a.guard && *a.guard > a.guard_thr) return;      // speculatively enqueued step whose lists turned out expired: the host rebuilds and repeats it
 	int x_first = 0, x_last = 0;
 	const NLBlock b = nl_plan(a, s_beg, s_off, s_len, x_first, x_last);
 	double acc[5] = {0., 0., 0., 0., 0.};
@@ -195,7 +197,8 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 		// eps24 and shift6 are constants of the single component: F, V accumulate d * inv*(2 lj12 - lj6) and are scaled by
 		// eps24 once; upot6 = eps24 * sum(lj12 - lj6) + shift6 * pairs.
 		double s6 = 0.;
-		const long long rc2b = __double_as_longlong(a.rclj2);
+		// 0 < r2 < rc^2  <=>  (r2b - 1) <u (rc2b - 1) on the bit patterns (r2b == 0 wraps to the largest unsigned): one predicate
+		const unsigned long long rc2m1 = (unsigned long long)__double_as_longlong(a.rclj2) - 1ull;
 		auto quad = [&](const uint2& w) {
 			const uint32_t ww[2] = {w.x, w.y};
 			double dx[4], dy[4], dz[4], r2[4];
@@ -209,8 +212,7 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 				// r2 == 0: the molecule itself, or a coincident molecule of the same cell (SingleCellPolicy_ mask, Helpers.h:367-376).
 				// r2 and rc^2 are non-negative doubles: their order is the order of their bit patterns, so both tests run on
 				// the integer pipe and leave the FP64 pipe to the force arithmetic
-				const long long r2b = __double_as_longlong(r2[u]);
-				ok[u] = r2b < rc2b && r2b != 0;
+				ok[u] = (unsigned long long)__double_as_longlong(r2[u]) - 1ull < rc2m1;
 			}
 #pragma unroll
 			for (int u = 0; u < 4; ++u) {

@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stddef.h>
+#include <string.h>
 #include <string>
 #include <vector>
 
@@ -18,6 +19,8 @@
 // CellBorderAndFlagManager.h:99-157).  Passed BY VALUE to kernels (lives in the kernel-parameter
 // constant bank).
 // ------------------------------------------------------------------------------------------------
+static inline long long host_double_bits(double x) { long long b; memcpy(&b, &x, sizeof b); return b; }
+
 struct Grid {
 	double box_min[3], box_max[3];
 	double halo_min[3], halo_max[3];
@@ -116,7 +119,10 @@ struct ls1g_ctx {
 	int      track_disp;                    // integrate kernels track max |r - pos_build|^2 into d_flags[0]
 	int      list_tcap;                     // tile capacity used by the list force kernel (max tile of the last build, padded)
 	int      list_bpr;                      // blocks per cell row
-	unsigned long long* d_flags;            // [4]: max displacement^2 bits | overflow bits
+	unsigned long long* d_flags;            // [4]: max displacement^2 bits | overflow bits | max slab tile | snapshot of [0] (kernel guard)
+	int      guard_on;                      // force / integrate kernels return at once when d_flags[3] > disp_thr2 (lists expired)
+	double   disp_thr2;                     // (0.4995 skin)^2: the lists are exact while max |r - r_build|^2 <= this
+	cudaEvent_t disp_ev[2];                 // completion of the per-step copy of d_flags[0] into h_flags[4 + (step & 1)]
 	unsigned long long* h_flags;            // pinned mirror      // device staging area of the host<->device transfers (transfer.cu)
 
 	// cells / sort scratch

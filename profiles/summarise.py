@@ -1,0 +1,21 @@
+"""python profiles/summarise.py X.ncu-rep > profiles/<name>_summary.csv   (key metrics of every captured launch, via `ncu -i ... --page raw --csv`)"""
+import csv, io, subprocess, sys
+KEYS = ["gpu__time_duration.sum", "sm__warps_active.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_fp64.avg.pct_of_peak_sustained_active", "sm__pipe_fp64_cycles_active.avg.pct_of_peak_sustained_active",
+        "smsp__inst_executed.sum", "smsp__issue_active.avg.pct_of_peak_sustained_active", "dram__bytes_read.sum", "dram__bytes_write.sum",
+        "dram__throughput.avg.pct_of_peak_sustained_elapsed", "lts__t_sector_hit_rate.pct",
+        "launch__registers_per_thread", "launch__occupancy_limit_shared_mem", "launch__occupancy_limit_registers",
+        "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "smsp__thread_inst_executed_per_inst_executed.ratio",
+        "launch__grid_size", "launch__block_size", "launch__shared_mem_per_block_dynamic", "launch__shared_mem_per_block_static"]
+STALL = "smsp__average_warps_issue_stalled_"
+out = subprocess.run(["ncu", "-i", sys.argv[1], "--page", "raw", "--csv"], capture_output=True, text=True, check=True).stdout
+rows = list(csv.reader(io.StringIO(out)))
+hdr, units = rows[0], rows[1]
+for r in rows[2:]:
+    print("Kernel Name,%s," % r[hdr.index("Kernel Name")])
+    for k in KEYS:
+        if k in hdr:
+            print("%s,%s,%s" % (k, r[hdr.index(k)], units[hdr.index(k)]))
+    st = [(float(r[i].replace(",", "")), h) for i, h in enumerate(hdr) if h.startswith(STALL) and h.endswith("_per_issue_active.ratio") and r[i]]
+    for v, h in sorted(st, reverse=True)[:6]:
+        print("%s,%.3f,warps/issue" % (h, v))
