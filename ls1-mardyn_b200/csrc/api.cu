@@ -192,7 +192,7 @@ extern "C" int ls1g_create(const ls1g_config* cfg, ls1g_ctx** out) {
 	CUDA_TRY(cudaMalloc((void**)&c->d_flags, 4 * sizeof(unsigned long long)));
 	CUDA_TRY(cudaMemset(c->d_flags, 0, 4 * sizeof(unsigned long long)));
 	CUDA_TRY(cudaMallocHost((void**)&c->h_flags, 8 * sizeof(unsigned long long)));
-	for (int k = 0; k < 2; ++k) CUDA_TRY(cudaEventCreateWithFlags(&c->disp_ev[k], cudaEventDisableTiming));
+	for (int k = 0; k < 4; ++k) CUDA_TRY(cudaEventCreateWithFlags(&c->disp_ev[k], cudaEventDisableTiming));
 	*out = c;
 	return 0;
 }
@@ -208,7 +208,7 @@ extern "C" int ls1g_destroy(ls1g_ctx* c) {
 	cudaFree(c->comps); cudaFree(c->sites); cudaFree(c->eps24); cudaFree(c->sig2); cudaFree(c->shift6);
 	cudaFree(c->cell_count); cudaFree(c->cell_fill); cudaFree(c->cell_start); cudaFree(c->scan_block);
 	cudaFree(c->d_flags); cudaFreeHost(c->h_flags);
-	for (int k = 0; k < 2; ++k) if (c->disp_ev[k]) cudaEventDestroy(c->disp_ev[k]);
+	for (int k = 0; k < 4; ++k) if (c->disp_ev[k]) cudaEventDestroy(c->disp_ev[k]);
 	cudaFree(c->d_counters); cudaFreeHost(c->h_counters); cudaFree(c->partials); cudaFree(c->d_scalars); cudaFreeHost(c->h_scalars);
 	for (int k = 0; k < 2; ++k) { cudaFree(c->send_buf[k]); cudaFree(c->recv_buf[k]); }
 	if (c->stream) cudaStreamDestroy(c->stream);

@@ -73,20 +73,23 @@ int k_list_build(ls1g_ctx* c) {
 }
 
 // count_pairs: also count the pairs inside the cutoff (ls1g_last_pair_count); always on when the potential is shifted
-int k_forces_list(ls1g_ctx* c, int count_pairs) {
+int k_forces_list(ls1g_ctx* c, int last_step) {
 	const size_t nb = nl_blocks(c);
 	if (ls1g_ensure_partials(c, nb ? nb : 1, 5)) return 1;
 	static bool attr_set = false;
 	if (!attr_set) {
-		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
-		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
+		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
+		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
+		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
 		attr_set = true;
 	}
 	NLArgs a = nl_args(c);
 	a.tcap = c->list_tcap;      // the largest tile of the last build: shared memory sized to what this system needs
 	timer_start(c, LS1G_T_FORCE);
-	if (count_pairs || c->shift6_h[0] != 0.) nl_force_kernel<true><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
-	else nl_force_kernel<false><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
+	// last step of a run: pair statistics + per-molecule virial; other steps: forces + the scalar sums of the step record
+	if (last_step) nl_force_kernel<true, true><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
+	else if (c->shift6_h[0] != 0.) nl_force_kernel<true, false><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
+	else nl_force_kernel<false, false><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
 	timer_stop(c, LS1G_T_FORCE, 1);
 	if (k_force_finalize(c, nb)) return 1;
 	CUDA_TRY(cudaGetLastError());

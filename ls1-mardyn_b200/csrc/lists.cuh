@@ -21,7 +21,7 @@
 //                     loses in one row of a group it gains in the opposite one, so the lanes of a warp stay in step.  A
 //                     molecule's list is grouped accordingly, each group padded to a multiple of 4 entries with index 0
 //   list entry      = 16-bit index into the group's tile + NL_DUMMY; tile entries 0..NL_DUMMY-1 hold a far-away dummy
-//                     position (r^2 = inf fails the cutoff test), so padding needs no special case; lists[((blk*(LCAP/4) + t/4)*128 + thread)*4 + t%4]: one 8-byte
+//                     position (r^2 = 3e300 fails the cutoff test), so padding needs no special case; lists[((blk*(LCAP/4) + t/4)*128 + thread)*4 + t%4]: one 8-byte
 //                     load = 4 entries; lcount packs the three cumulative group ends (in units of 4 entries, 8 bits each)
 #pragma once
 
@@ -173,7 +173,11 @@ __global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
 // ---------------------------------------------------------------------------------------------------------------
 // force: exact FP64 test + _loopBodyLJ over the listed pairs
 // ---------------------------------------------------------------------------------------------------------------
-template <bool COUNT>
+// COUNT: count the pairs inside the cutoff (pair statistics; the shift6 term of a shifted potential needs the count).
+// VI:    accumulate and store the per-molecule virial Vi (FullMolecule::calcFM, FullMolecule.cpp:551-631).  Inside ls1g_run
+//        nothing can read Vi between two steps, so only the last step of a run produces it; the other steps accumulate the
+//        scalar virial sum(f . d) = sum(sc r^2) directly (the record of every step still gets upot and virial).
+template <bool COUNT, bool VI>
 __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 	extern __shared__ __align__(16) double nl_tile[];
 	double* tile = nl_tile;                         // [tcap][3]: x y z of candidate k at tile[3k..3k+2]
@@ -221,9 +225,14 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 				const double lj2 = a.sig2 * inv, lj4 = lj2 * lj2, lj6 = lj4 * lj2, lj12 = lj6 * lj6, lj12m6 = lj12 - lj6;
 				const double sc = inv * (lj12 + lj12m6);
 				s6 += lj12m6;
-				const double px = dx[u] * sc, py = dy[u] * sc, pz = dz[u] * sc;
-				Fx += px; Fy += py; Fz += pz;
-				Vx += dx[u] * px; Vy += dy[u] * py; Vz += dz[u] * pz;
+				if (VI) {
+					const double px = dx[u] * sc, py = dy[u] * sc, pz = dz[u] * sc;
+					Fx += px; Fy += py; Fz += pz;
+					Vx += dx[u] * px; Vy += dy[u] * py; Vz += dz[u] * pz;
+				} else {
+					Fx = fma(dx[u], sc, Fx); Fy = fma(dy[u], sc, Fy); Fz = fma(dz[u], sc, Fz);
+					Vx = fma(r2[u], sc, Vx);                  // Vx carries the whole trace
+				}
 				if (COUNT) np_i += ok[u] ? 1 : 0;
 			}
 		};
@@ -237,7 +246,8 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 		for (int gz = 0; gz < 3; ++gz) {
 			if (gz) __syncthreads();                     // everyone is done with the previous row group
 			const int gbase = s_off[NL_GRP[gz]];
-			if (tid < NL_DUMMY) { double* q = tile + 3 * tid; q[0] = 1e300; q[1] = 1e300; q[2] = 1e300; }
+			// dummy entries: far outside any cutoff, yet r^2 = 3e300 stays FINITE (the trace accumulation multiplies r^2 by an exact 0)
+			if (tid < NL_DUMMY) { double* q = tile + 3 * tid; q[0] = 1e150; q[1] = 1e150; q[2] = 1e150; }
 			for (int r = NL_GRP[gz]; r < NL_GRP[gz + 1]; ++r) {
 				const int off = s_off[r] - gbase + NL_DUMMY, len = s_len[r];
 				const uint32_t beg = s_beg[r];
@@ -257,7 +267,8 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 			u6 = a.eps24 * s6;       // + shift6 * pairs: added by the caller's finalize when the potential is shifted (COUNT)
 			if (COUNT) u6 += a.shift6 * (double)np_i;
 			double* Fp = a.F + 3 * (size_t)i; double* Vp = a.Vi + 3 * (size_t)i;
-			Fp[0] = Fx; Fp[1] = Fy; Fp[2] = Fz; Vp[0] = 0.5 * Vx; Vp[1] = 0.5 * Vy; Vp[2] = 0.5 * Vz;
+			Fp[0] = Fx; Fp[1] = Fy; Fp[2] = Fz;
+			if (VI) { Vp[0] = 0.5 * Vx; Vp[1] = 0.5 * Vy; Vp[2] = 0.5 * Vz; }
 			acc[0] = u6; acc[2] = Vx + Vy + Vz; acc[4] = (double)np_i;
 		}
 	}

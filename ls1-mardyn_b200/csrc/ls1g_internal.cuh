@@ -122,7 +122,7 @@ struct ls1g_ctx {
 	unsigned long long* d_flags;            // [4]: max displacement^2 bits | overflow bits | max slab tile | snapshot of [0] (kernel guard)
 	int      guard_on;                      // force / integrate kernels return at once when d_flags[3] > disp_thr2 (lists expired)
 	double   disp_thr2;                     // (0.4995 skin)^2: the lists are exact while max |r - r_build|^2 <= this
-	cudaEvent_t disp_ev[2];                 // completion of the per-step copy of d_flags[0] into h_flags[4 + (step & 1)]
+	cudaEvent_t disp_ev[4];                 // completion of the per-step copy of d_flags[0] into h_flags[4 + step % 4]
 	unsigned long long* h_flags;            // pinned mirror      // device staging area of the host<->device transfers (transfer.cu)
 
 	// cells / sort scratch

@@ -105,13 +105,15 @@ int k_halo_refresh(ls1g_ctx* c);
 // Neighbour-list steps of ls1g_run (lists.cuh).  On entry the pre-kick of step 0 is done.  Runs steps [0, n_steps) unless
 // a buffer limit is hit while building lists for step s: then the bin grid is restored and *done = s tells the caller to
 // continue with the rebuild-every-step loop (the state is exactly what that loop expects).
-// One step is enqueued ahead of the host's knowledge: the displacement that decides whether step s may still use the
+// Steps are enqueued ahead of the host's knowledge: the displacement that decides whether step s may still use the
 // lists is produced by the integrate kernel of step s-1, and waiting for it before every launch would leave the device
 // idle for a host round trip per step.  So step s is enqueued GUARDED: its force and integrate kernels first read a
 // snapshot of the displacement flag (d_flags[3]) and return at once when the lists have expired.  The host reads the
-// same value one step late (pinned copy + event), rebuilds, and enqueues step s again.  Device and host evaluate the
+// same value up to NL_AHEAD steps late (pinned copy + event), rebuilds, and enqueues the skipped steps again.  Device and host evaluate the
 // identical comparison d2 > disp_thr2 on the identical bits; the flag is monotone between builds (atomicMax), so an
 // expired step stays skipped however many kernels follow it.
+#define NL_AHEAD 3      // steps the host may enqueue beyond the last displacement flag it has read
+#define NL_RING 4       // pinned flag copies / events in flight (> NL_AHEAD)
 static int flag_snapshot(ls1g_ctx* c, int ring) {
 	if (c->n_ranks > 1 && comm_allreduce_max(c, (double*)c->d_flags, 1)) return 1;      // non-negative doubles: bit order == value order
 	CUDA_TRY(cudaMemcpyAsync(c->d_flags + 3, c->d_flags, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, c->stream));
@@ -136,63 +138,71 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 	int rebuilds = 0, repeats = 0;
 	double t_build = 0., t_wait = 0., t_enq = 0., t_max_wait = 0., t_max_enq = 0.;     // host wall clock, LS1G_DEBUG only
 	auto now = [&]() { if (!dbg) return 0.; struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6; };
-	while (s < n_steps && !rc) {
-		const bool built = need_build;
-		const double t0 = now();
-		if (need_build) {
-			c->sorted = 0; c->track_disp = 0; c->guard_on = 0;
-			c->forces_valid = 0;
-			rc = c->n_ranks > 1 ? comm_exchange_build(c) : k_sort(c, 1);
-			c->forces_valid = 1;
-			if (!rc) rc = k_halo_map(c);
-			if (!rc) rc = k_list_build(c);             // zeroes d_flags[0..2]
-			if (!rc && cudaMemsetAsync(c->d_flags + 3, 0, sizeof(unsigned long long), c->stream) != cudaSuccess) rc = 1;
-			if (!rc && sync_check(c, "ls1g_run (list build)")) rc = 1;
-			if (!rc && c->n_ranks > 1) {         // every rank must take the same decision
-				double ovf = c->h_flags[1] ? 1. : 0.;
-				if (cudaMemcpyAsync(c->d_scalars + 12, &ovf, sizeof(double), cudaMemcpyHostToDevice, c->stream) != cudaSuccess) rc = 1;
-				if (!rc) rc = comm_allreduce_max(c, c->d_scalars + 12, 1);
-				if (!rc && cudaMemcpyAsync(&ovf, c->d_scalars + 12, sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess) rc = 1;
+	// s   = next step to enqueue
+	// chk = next step whose displacement flag (written by its integrate kernel, deciding step chk + 1) the host has not read
+	int chk = 0;
+	while (!rc) {
+		if (s < n_steps && s - chk < NL_AHEAD) {
+			const bool built = need_build;
+			const double t0 = now();
+			if (need_build) {
+				c->sorted = 0; c->track_disp = 0; c->guard_on = 0;
+				c->forces_valid = 0;
+				rc = c->n_ranks > 1 ? comm_exchange_build(c) : k_sort(c, 1);
+				c->forces_valid = 1;
+				if (!rc) rc = k_halo_map(c);
+				if (!rc) rc = k_list_build(c);             // zeroes d_flags[0..2]
+				if (!rc && cudaMemsetAsync(c->d_flags + 3, 0, sizeof(unsigned long long), c->stream) != cudaSuccess) rc = 1;
 				if (!rc && sync_check(c, "ls1g_run (list build)")) rc = 1;
-				if (ovf != 0. && !c->h_flags[1]) c->h_flags[1] = 8;
+				if (!rc && c->n_ranks > 1) {         // every rank must take the same decision
+					double ovf = c->h_flags[1] ? 1. : 0.;
+					if (cudaMemcpyAsync(c->d_scalars + 12, &ovf, sizeof(double), cudaMemcpyHostToDevice, c->stream) != cudaSuccess) rc = 1;
+					if (!rc) rc = comm_allreduce_max(c, c->d_scalars + 12, 1);
+					if (!rc && cudaMemcpyAsync(&ovf, c->d_scalars + 12, sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess) rc = 1;
+					if (!rc && sync_check(c, "ls1g_run (list build)")) rc = 1;
+					if (ovf != 0. && !c->h_flags[1]) c->h_flags[1] = 8;
+				}
+				if (rc) break;
+				if (c->h_flags[1]) {                 // tile / list / row capacity exceeded: this system is too dense for the list buffers
+					c->list_disabled = 1; c->in_list_mode = 0; c->track_disp = 0;
+					if (dbg) fprintf(stderr, "ls1g: neighbour lists disabled, overflow bits %llu (1 tile, 2 list, 4 row), bpr %d\n", c->h_flags[1], c->list_bpr);
+					nl_set_bin_grid(c, 0);
+					*done = s;
+					return 0;
+				}
+				c->track_disp = 1;
+				c->list_tcap = (int)((c->h_flags[2] + 63) & ~63ull);
+				if (c->list_tcap < 64) c->list_tcap = 64;
+				if (dbg) fprintf(stderr, "ls1g: list build at step %d: max tile %llu, bpr %d, slots %zu, bin grid %d %d %d\n", s, c->h_flags[2], c->list_bpr, c->n_slots, c->bgrid.cpd[0], c->bgrid.cpd[1], c->bgrid.cpd[2]);
+				need_build = false; ++rebuilds;
+				t_build += now() - t0;
+			} else {
+				if (c->n_ranks > 1) rc = comm_refresh(c);
+				if (!rc) rc = k_halo_refresh(c);
 			}
-			if (rc) break;
-			if (c->h_flags[1]) {                 // tile / list / row capacity exceeded: this system is too dense for the list buffers
-				c->list_disabled = 1; c->in_list_mode = 0; c->track_disp = 0;
-				if (dbg) fprintf(stderr, "ls1g: neighbour lists disabled, overflow bits %llu (1 tile, 2 list, 4 row), bpr %d\n", c->h_flags[1], c->list_bpr);
-				nl_set_bin_grid(c, 0);
-				*done = s;
-				return 0;
-			}
-			c->track_disp = 1;
-			c->list_tcap = (int)((c->h_flags[2] + 63) & ~63ull);
-			if (c->list_tcap < 64) c->list_tcap = 64;
-			if (dbg) fprintf(stderr, "ls1g: list build at step %d: max tile %llu, bpr %d, slots %zu, bin grid %d %d %d\n", s, c->h_flags[2], c->list_bpr, c->n_slots, c->bgrid.cpd[0], c->bgrid.cpd[1], c->bgrid.cpd[2]);
-			need_build = false; ++rebuilds;
-			t_build += now() - t0;
-		} else {
-			if (c->n_ranks > 1) rc = comm_refresh(c);
-			if (!rc) rc = k_halo_refresh(c);
-		}
-		const double t1 = now();
-		c->guard_on = built ? 0 : 1;
-		if (!rc) rc = k_forces_list(c, s + 1 == n_steps);      // pair statistics only for the last step (ls1g_last_pair_count)
-		if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s, c->d_scalars, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
-		if (!rc) rc = k_post_pre(c, dt, 1, s + 1 < n_steps, thermo, target_T);
-		if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s + 4, c->d_scalars + 4, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
-		c->guard_on = 0;
-		if (!rc && s + 1 < n_steps) rc = flag_snapshot(c, s & 1);      // decides step s + 1
-		if (rc) break;
-		const double t2 = now();
-		t_enq += t2 - t1; if (t2 - t1 > t_max_enq) t_max_enq = t2 - t1;
-		if (!built && s > 0) {
-			// did step s really run?  its guard was the flag written by step s - 1
-			if (cudaEventSynchronize(c->disp_ev[(s - 1) & 1]) != cudaSuccess) { rc = 1; break; }
+			const double t1 = now();
+			c->guard_on = built ? 0 : 1;
+			if (!rc) rc = k_forces_list(c, s + 1 == n_steps);      // pair statistics + per-molecule virial only for the last step
+			if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s, c->d_scalars, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
+			if (!rc) rc = k_post_pre(c, dt, 1, s + 1 < n_steps, thermo, target_T);
+			if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s + 4, c->d_scalars + 4, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
+			c->guard_on = 0;
+			if (!rc && s + 1 < n_steps) rc = flag_snapshot(c, s % NL_RING);      // decides step s + 1
+			const double t2 = now();
+			t_enq += t2 - t1; if (t2 - t1 > t_max_enq) t_max_enq = t2 - t1;
+			++s;
+		} else if (chk < s && chk + 1 < n_steps) {
+			// did the steps after chk really run?  step chk + 1 was guarded by the flag step chk wrote
+			const double t2 = now();
+			if (cudaEventSynchronize(c->disp_ev[chk % NL_RING]) != cudaSuccess) { rc = 1; break; }
 			const double t3 = now();
 			t_wait += t3 - t2; if (t3 - t2 > t_max_wait) t_max_wait = t3 - t2;
-			if (expired((s - 1) & 1)) { need_build = true; ++repeats; continue; }        // skipped on the device: rebuild, repeat step s
-		}
-		++s;
+			if (expired(chk % NL_RING)) {      // steps chk + 1 .. s - 1 were skipped on the device: rebuild and enqueue them again
+				repeats += s - (chk + 1);
+				s = chk + 1; need_build = true;
+			}
+			++chk;
+		} else break;
 	}
 	c->guard_on = 0;
 	if (!rc && sync_check(c, "ls1g_run (list steps)")) rc = 1;
