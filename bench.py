@@ -89,10 +89,12 @@ def distance_checks(cell, cpd):
     return float(tot)
 
 
-def lj_flops(n_dist, n_pairs):
+def lj_flops(n_dist, n_pairs, per_molecule_virial=True):
     """FlopCounter model (adapter/FlopCounter.cpp:19-75, FlopCounter.h:243-269) for one LJ site per molecule:
-    8 per distance check + (8 + 15 + 12) per in-cutoff site pair + (4 + 2) macroscopic"""
-    return 8.0 * n_dist + (8.0 + 15.0 + 12.0 + 4.0 + 2.0) * n_pairs
+    8 per distance check + (8 + 15 + 12) per in-cutoff site pair + (4 + 2) macroscopic = 41 per pair.
+    Steps that do not accumulate the per-molecule virial Vi are counted with the reference's own figure for that case
+    (its reduced-memory mode, FlopCounter.cpp:33-39): (8 + 12 + 6) + (7 + 2) = 35 per pair."""
+    return 8.0 * n_dist + (41.0 if per_molecule_virial else 35.0) * n_pairs
 
 
 # ----------------------------------------------------------------------------------------------------------
@@ -429,7 +431,10 @@ def main_b200(args):
     c.traverse_cells()
     n_pairs = c.last_pair_count()
     del cells_all
-    flops = lj_flops(n_dist, n_pairs)
+    # ls1g_run produces Vi on the last step of a run only (nothing can read it in between): K-1 launches at 35, one at 41 flop/pair
+    vi_all = bool(int(os.environ.get("LS1G_VI_EVERY_STEP", "0") or 0))
+    k_t = max(args.steps, 1)
+    flops = lj_flops(n_dist, n_pairs, True) if vi_all else (lj_flops(n_dist, n_pairs, False) * (k_t - 1) + lj_flops(n_dist, n_pairs, True)) / k_t
     force_ms = tm["force"]["ms"] / max(tm["force"]["launches"], 1)
     traffic, traffic_src = None, None
     prof = os.path.join(ROOT, "profiles", "r01_ncu_nl_force_10M_summary.csv")
@@ -490,7 +495,7 @@ def main_b200(args):
                              "frac": round(achieved / peak, 4) if peak > 0 else None, "traffic": traffic, "traffic_source": traffic_src,
                              "peak_source": "measured here: dependent-free DFMA kernel (ls1g_measure_fp64_peak); MEASURED_PEAKS.json has no FP64 figure",
                              "flops_per_launch": flops, "n_dist": n_dist, "n_pairs": n_pairs, "kernel_ms": round(force_ms, 4),
-                             "model": "FlopCounter: 8*N_dist + 41*N_pairs (Newton-3 counts); the kernel is owner-computes and executes ~2x these",
+                             "model": "FlopCounter: 8*N_dist + 41*N_pairs with per-molecule virial (last step of the run), 8*N_dist + 35*N_pairs without (the other steps; the reference's own count for that case); Newton-3 counts, the owner-computes kernel executes ~2x these",
                              "note": "bound is the FP64 FMA pipe (SURVEY 8d), not HBM/tensor: ncu sm__pipe_fp64_cycles_active 64 % (profiles/)"},
                 "kernel_ms_per_step": {k: round(t["ms"] / args.steps, 4) for k, t in tm.items()},
                 "clocks": clk}

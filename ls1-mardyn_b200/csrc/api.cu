@@ -172,6 +172,7 @@ extern "C" int ls1g_create(const ls1g_config* cfg, ls1g_ctx** out) {
 	{ const char* fk = getenv("LS1G_FORCE_KERNEL"); c->force_variant = (fk && !strcmp(fk, "simple")) ? 1 : 0; }
 	if (grid_init(c->grid, c->cfg)) { delete c; return 1; }
 	c->bgrid = c->grid;
+	{ const char* e = getenv("LS1G_VI_EVERY_STEP"); c->vi_every_step = e && atoi(e) != 0; }
 	{ const char* sk = getenv("LS1G_SKIN"); c->skin = sk ? atof(sk) : 0.12 * c->cfg.cutoff; if (c->skin < 0.) c->skin = 0.; }
 	c->rc2 = c->cfg.cutoff * c->cfg.cutoff;
 	c->rclj2 = c->cfg.lj_cutoff * c->cfg.lj_cutoff;

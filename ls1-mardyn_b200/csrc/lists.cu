@@ -87,7 +87,7 @@ int k_forces_list(ls1g_ctx* c, int last_step) {
 	a.tcap = c->list_tcap;      // the largest tile of the last build: shared memory sized to what this system needs
 	timer_start(c, LS1G_T_FORCE);
 	// last step of a run: pair statistics + per-molecule virial; other steps: forces + the scalar sums of the step record
-	if (last_step) nl_force_kernel<true, true><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
+	if (last_step || c->vi_every_step) nl_force_kernel<true, true><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
 	else if (c->shift6_h[0] != 0.) nl_force_kernel<true, false><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
 	else nl_force_kernel<false, false><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
 	timer_stop(c, LS1G_T_FORCE, 1);

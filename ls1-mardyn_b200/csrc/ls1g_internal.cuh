@@ -120,6 +120,7 @@ struct ls1g_ctx {
 	int      list_tcap;                     // tile capacity used by the list force kernel (max tile of the last build, padded)
 	int      list_bpr;                      // blocks per cell row
 	unsigned long long* d_flags;            // [4]: max displacement^2 bits | overflow bits | max slab tile | snapshot of [0] (kernel guard)
+	int      vi_every_step;                 // LS1G_VI_EVERY_STEP=1: per-molecule virial on every list step, not only the last of a run
 	int      guard_on;                      // force / integrate kernels return at once when d_flags[3] > disp_thr2 (lists expired)
 	double   disp_thr2;                     // (0.4995 skin)^2: the lists are exact while max |r - r_build|^2 <= this
 	cudaEvent_t disp_ev[4];                 // completion of the per-step copy of d_flags[0] into h_flags[4 + step % 4]
