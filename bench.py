@@ -97,6 +97,21 @@ def lj_flops(n_dist, n_pairs, per_molecule_virial=True):
     return 8.0 * n_dist + (41.0 if per_molecule_virial else 35.0) * n_pairs
 
 
+def hbm_kernels(tm, steps, n_local):
+    """achieved HBM GB/s of the memory-bound kernels against the measured copy peak (MEASURED_PEAKS.json).
+    integrate (fused post+pre, 1CLJ): read pos 32 + vel 24 + F 24 + cell 4, write pos 32 + vel 24 = 140 B per
+    molecule-update; the list mode adds a 32-B read of the build position (not counted)."""
+    peak, src = 6548.5, "fallback (B200_PROFILING.md)"
+    try:
+        peak, src = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "MEASURED_PEAKS.json"
+    except (OSError, KeyError, ValueError):
+        pass
+    ms = tm["integrate"]["ms"] / max(steps, 1)
+    gbs = 140.0 * n_local / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
+    return {"integrate": {"bound": "hbm", "achieved": round(gbs, 1), "peak": peak, "unit": "GB/s", "frac": round(gbs / peak, 4),
+                          "bytes_per_molecule": 140, "ms_per_step": round(ms, 4), "peak_source": src}}
+
+
 # ----------------------------------------------------------------------------------------------------------
 # clocks
 # ----------------------------------------------------------------------------------------------------------
@@ -498,6 +513,7 @@ def main_b200(args):
                              "model": "FlopCounter: 8*N_dist + 41*N_pairs with per-molecule virial (last step of the run), 8*N_dist + 35*N_pairs without (the other steps; the reference's own count for that case); Newton-3 counts, the owner-computes kernel executes ~2x these",
                              "note": "bound is the FP64 FMA pipe (SURVEY 8d), not HBM/tensor: ncu sm__pipe_fp64_cycles_active 64 % (profiles/)"},
                 "kernel_ms_per_step": {k: round(t["ms"] / args.steps, 4) for k, t in tm.items()},
+                "hbm_kernels": hbm_kernels(tm, args.steps, n_local),
                 "clocks": clk}
         if cb is not None:
             line["cpu_baseline"] = cb

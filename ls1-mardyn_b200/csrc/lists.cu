@@ -65,7 +65,9 @@ int k_list_build(ls1g_ctx* c) {
 	CUDA_TRY(cudaMemsetAsync(c->d_flags, 0, 3 * sizeof(unsigned long long), c->stream));
 	CUDA_TRY(cudaMemcpyAsync(c->pos_build, c->cur.pos, c->n_slots * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));
 	NLArgs a = nl_args(c);
-	nl_build_kernel<<<(unsigned)nb, NL_BT, 0, c->stream>>>(a);
+	static bool battr = false;
+	if (!battr) { CUDA_TRY(cudaFuncSetAttribute(nl_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, NL_BUILD_SMEM)); battr = true; }
+	nl_build_kernel<<<(unsigned)nb, NL_BT, NL_BUILD_SMEM, c->stream>>>(a);
 	CUDA_TRY(cudaGetLastError());
 	CUDA_TRY(cudaMemcpyAsync(c->h_flags, c->d_flags, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
 	timer_stop(c, LS1G_T_SORT, 2);

@@ -99,8 +99,13 @@ __device__ __forceinline__ NLBlock nl_plan(const NLArgs& a, uint32_t* s_beg, int
 // ---------------------------------------------------------------------------------------------------------------
 // build: FP32 candidate filter with radius rc + skin -> per-molecule lists of tile indices
 // ---------------------------------------------------------------------------------------------------------------
+#define NL_QCAP 64         // per-lane queue entries of one row group (shared memory), multiple of 4
+#define NL_BUILD_SMEM (3 * NL_TCAP * 4 + NL_QCAP * NL_BT * 2)
+
 __global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
-	__shared__ __align__(16) float xs[NL_TCAP], ys[NL_TCAP], zs[NL_TCAP];
+	extern __shared__ __align__(16) unsigned char nl_bsm[];
+	float* xs = (float*)nl_bsm; float* ys = xs + NL_TCAP; float* zs = ys + NL_TCAP;
+	unsigned short* q = (unsigned short*)(zs + NL_TCAP);          // q[t][tid]: survivors of the current row group, one column per lane
 	__shared__ uint32_t s_beg[9]; __shared__ int s_off[10], s_len[9];
 	const Grid& g = a.g;
 	const int tid = threadIdx.x, lane = tid & 31;
@@ -136,8 +141,13 @@ __global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
 	const bool active = i < w1;
 	float fx = -1e30f, fy = -1e30f, fz = -1e30f;
 	if (active) { const double4 Pi = a.pos[i]; fx = (float)(Pi.x - ox); fy = (float)(Pi.y - oy); fz = (float)(Pi.z - oz); }
-	unsigned short* my = a.lists + ((size_t)blockIdx.x * (NL_LCAP / 4) * NL_BT + tid) * 4;     // entry t at my[(t/4)*NL_BT*4 + t%4]
-	int cnt = 0; bool ovf = false;
+	uint2* my = (uint2*)(a.lists + ((size_t)blockIdx.x * (NL_LCAP / 4) * NL_BT + tid) * 4);     // entries 4t..4t+3 at my[t * NL_BT]
+	unsigned short* const q0 = q + tid;
+	// the queue is addressed through one 32-bit shared-window register (append = st.shared.u16 + add, both predicated)
+	const uint32_t qa0 = (uint32_t)__cvta_generic_to_shared(q0);
+	const uint32_t qalim = qa0 + (NL_QCAP - 4) * NL_BT * 2;       // room for one more scan iteration
+	uint32_t qa = qa0;
+	int done4 = 0; bool ovf = false;       // groups of 4 entries already written to the list
 	uint32_t ends = 0;
 	const float rl2 = a.rl2f;
 	int grp = 0;
@@ -148,22 +158,36 @@ __global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
 		const uint32_t lo = a.cell_start[cr + xw_first - 1], hi = a.cell_start[cr + xw_last + 2];
 		const uint32_t beg = s_beg[p];
 		const int k0 = s_off[p] + (int)((lo - beg) & ~3u), k1 = s_off[p] + (int)((hi - beg + 3u) & ~3u);
-		for (int k = k0; k < k1; k += 4) {
+		int val = k0 - gbase + NL_DUMMY;               // list entry of candidate k0
+		for (int k = k0; k < k1; k += 4, val += 4) {
 			const float4 cx4 = *(const float4*)(xs + k), cy4 = *(const float4*)(ys + k), cz4 = *(const float4*)(zs + k);
 			const float cxa[4] = {cx4.x, cx4.y, cx4.z, cx4.w}, cya[4] = {cy4.x, cy4.y, cy4.z, cy4.w}, cza[4] = {cz4.x, cz4.y, cz4.z, cz4.w};
 #pragma unroll
 			for (int u = 0; u < 4; ++u) {
 				const float dx = fx - cxa[u], dy = fy - cya[u], dz = fz - cza[u];
 				const float r2 = dx * dx + dy * dy + dz * dz;
-				if (r2 < rl2) { my[(cnt >> 2) * (NL_BT * 4) + (cnt & 3)] = (unsigned short)(k + u - gbase + NL_DUMMY); ++cnt; }
+				if (r2 < rl2) { asm volatile("st.shared.u16 [%0], %1;" :: "r"(qa), "h"((unsigned short)(val + u)) : "memory"); qa += NL_BT * 2; }
 			}
-			if (cnt > NL_LCAP - 12) { ovf = true; cnt = 0; }
+			if (qa > qalim) { ovf = true; qa = qa0; }
 		}
-		if (p + 1 == NL_GRP[grp + 1]) {                 // end of a row group: pad it to a multiple of 4 with sentinels
-			while (cnt & 3) { my[(cnt >> 2) * (NL_BT * 4) + (cnt & 3)] = 0; ++cnt; }        // index 0 = dummy tile entry
-			ends |= (uint32_t)(cnt >> 2) << (8 * grp);
+		if (p + 1 == NL_GRP[grp + 1]) {                 // end of a row group: pad to a multiple of 4 with the dummy entry, flush
+			int cnt = (int)(qa - qa0) / (NL_BT * 2);
+			while (cnt & 3) { q0[cnt * NL_BT] = 0; ++cnt; }
+			const int n4 = cnt >> 2;
+			if (done4 + n4 > NL_LCAP / 4) { ovf = true; }
+			else {
+				for (int t = 0; t < n4; ++t) {
+					const unsigned short* e = q0 + 4 * t * NL_BT;
+					uint2 w;
+					w.x = (uint32_t)e[0] | ((uint32_t)e[NL_BT] << 16);
+					w.y = (uint32_t)e[2 * NL_BT] | ((uint32_t)e[3 * NL_BT] << 16);
+					my[(size_t)(done4 + t) * NL_BT] = w;
+				}
+				done4 += n4;
+			}
+			ends |= (uint32_t)done4 << (8 * grp);
 			++grp;
-			if (cnt > NL_LCAP - 12) { ovf = true; cnt = 0; }
+			qa = qa0;
 		}
 	}
 	if (active) a.lcount[(size_t)blockIdx.x * NL_BT + tid] = ends;
