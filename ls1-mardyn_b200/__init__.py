@@ -7,7 +7,8 @@ Host-side mirror of the reference's operator surface for this path, as a thin ct
 from .binding import (Container, Ls1gError, build, lib, lib_path, decomp_grid, decomp_box, fp64_peak_tflops,
                       exchange_group, comm_init_local, comm_unique_id, components_from_tables,
                       lj_component, FIELDS, EXPORTS)
+from . import phasespace
 
 __all__ = ["Container", "Ls1gError", "build", "lib", "lib_path", "decomp_grid", "decomp_box",
            "fp64_peak_tflops", "exchange_group", "comm_init_local", "comm_unique_id", "components_from_tables",
-           "lj_component", "FIELDS", "EXPORTS"]
+           "lj_component", "FIELDS", "EXPORTS", "phasespace"]

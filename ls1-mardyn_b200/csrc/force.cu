@@ -67,159 +67,348 @@ struct ForceArgs {
 	double rc2, rclj2, epsRFInvrc3;
 	double *F, *M, *Vi;
 	double* partials;               // [blocks][5]: upot6lj, upotXpoles, virial, myRF, pairs
+	double eps24_c[16], sig2_c[16], shift6_c[16];   // single-component kernels (S <= 4): the LJ tables travel in the kernel parameters (constant bank)
 };
 
 __device__ __forceinline__ V3 ld3(const double4& a) { return v3(a.x, a.y, a.z); }
 
+// Accumulators of one owned molecule (registers of its thread).
+struct MolAcc {
+	V3 F, M, V;
+	double u6, uX, rf;
+	unsigned long long np;
+};
+
+// All site-site interactions of the molecule pair (i, j): the ten ordered loops of _calculatePairs
+// (VectorizedCellProcessor.cpp:1031-2720) seen from molecule i; m = R_i - R_j (molecule centres), in_lj / in_rc the two
+// molecule-centre cutoff decisions (:1013-1024).
+__device__ __forceinline__ void pair_body(const ForceArgs& a, const V3& Ri, const CompDev& ci, const double4* __restrict__ si,
+                                          const int i_ch0, const int i_di0, const int i_qu0,
+                                          const uint32_t j, const double4& Pj, const V3& m, const bool in_lj, const bool in_rc, MolAcc& A_) {
+	V3& F = A_.F; V3& M = A_.M; V3& V = A_.V; double& u6 = A_.u6; double& uX = A_.uX; double& rf = A_.rf;
+	{
+		const CompDev cj = a.comps[pos_cid(Pj)];
+		const double4* sj = a.cache + (size_t)j * a.stride;
+		const int j_ch0 = cj.n_lj, j_di0 = cj.n_lj + cj.n_ch, j_qu0 = j_di0 + 2 * cj.n_di;
+		// ---- LJ - LJ (VectorizedCellProcessor.cpp:1031-1180)
+		if (in_lj)
+			for (int s1 = 0; s1 < ci.n_lj; ++s1) {
+				const double4 A = si[s1];
+				const int ida = (int)__double_as_longlong(A.w);
+				V3 fa = v3(0, 0, 0);
+				for (int s2 = 0; s2 < cj.n_lj; ++s2) {
+					const double4 B = sj[s2];
+					const int k = ida * a.S + (int)__double_as_longlong(B.w);
+					V3 f; double u;
+					pot_lj(v3(A.x - B.x, A.y - B.y, A.z - B.z), a.eps24[k], a.sig2[k], a.shift6[k], f, u);
+					fa.x += f.x; fa.y += f.y; fa.z += f.z; u6 += u;
+				}
+				F.x += fa.x; F.y += fa.y; F.z += fa.z;
+				V.x += m.x * fa.x; V.y += m.y * fa.y; V.z += m.z * fa.z;
+				V3 t = cross(v3(A.x - Ri.x, A.y - Ri.y, A.z - Ri.z), fa);
+				M.x += t.x; M.y += t.y; M.z += t.z;
+			}
+		if (!in_rc) return;
+		// ---- charges of i
+		for (int s1 = 0; s1 < ci.n_ch; ++s1) {
+			const double4 A = si[i_ch0 + s1];
+			V3 fa = v3(0, 0, 0);
+			for (int s2 = 0; s2 < cj.n_ch; ++s2) {                     // q - q (:1192-1319)
+				const double4 B = sj[j_ch0 + s2];
+				V3 f; double u;
+				pot_qq(v3(A.x - B.x, A.y - B.y, A.z - B.z), A.w * B.w, f, u);
+				fa.x += f.x; fa.y += f.y; fa.z += f.z; uX += u;
+			}
+			for (int s2 = 0; s2 < cj.n_di; ++s2) {                     // q_i - mu_j (:1847-2006)
+				const double4 B = sj[j_di0 + 2 * s2], E = sj[j_di0 + 2 * s2 + 1];
+				V3 f, M2; double u;
+				pot_q_mu(v3(A.x - B.x, A.y - B.y, A.z - B.z), A.w, ld3(E), B.w, f, M2, u);
+				fa.x += f.x; fa.y += f.y; fa.z += f.z; uX += u;
+			}
+			for (int s2 = 0; s2 < cj.n_qu; ++s2) {                     // q_i - Q_j (:2380-2538)
+				const double4 B = sj[j_qu0 + 2 * s2], E = sj[j_qu0 + 2 * s2 + 1];
+				V3 f, M2; double u;
+				pot_q_Q(v3(A.x - B.x, A.y - B.y, A.z - B.z), A.w, ld3(E), B.w, f, M2, u);
+				fa.x += f.x; fa.y += f.y; fa.z += f.z; uX += u;
+			}
+			F.x += fa.x; F.y += fa.y; F.z += fa.z;
+			V.x += m.x * fa.x; V.y += m.y * fa.y; V.z += m.z * fa.z;
+			V3 t = cross(v3(A.x - Ri.x, A.y - Ri.y, A.z - Ri.z), fa);
+			M.x += t.x; M.y += t.y; M.z += t.z;
+		}
+		// ---- dipoles of i
+		for (int s1 = 0; s1 < ci.n_di; ++s1) {
+			const double4 A = si[i_di0 + 2 * s1]; const V3 e1 = ld3(si[i_di0 + 2 * s1 + 1]);
+			V3 fa = v3(0, 0, 0), ta = v3(0, 0, 0);
+			for (int s2 = 0; s2 < cj.n_ch; ++s2) {                     // mu_i - q_j (:1323-1481): charge is site 1
+				const double4 B = sj[j_ch0 + s2];
+				V3 f, M2; double u;
+				pot_q_mu(v3(B.x - A.x, B.y - A.y, B.z - A.z), B.w, e1, A.w, f, M2, u);
+				fa.x -= f.x; fa.y -= f.y; fa.z -= f.z; uX += u;
+				ta.x += M2.x; ta.y += M2.y; ta.z += M2.z;
+			}
+			for (int s2 = 0; s2 < cj.n_di; ++s2) {                     // mu - mu (:1667-1845)
+				const double4 B = sj[j_di0 + 2 * s2]; const V3 e2 = ld3(sj[j_di0 + 2 * s2 + 1]);
+				V3 f, M1, M2; double u, r;
+				pot_mu_mu(v3(A.x - B.x, A.y - B.y, A.z - B.z), e1, A.w, e2, B.w, a.epsRFInvrc3, f, M1, M2, u, r);
+				fa.x += f.x; fa.y += f.y; fa.z += f.z; uX += u; rf -= r;
+				ta.x += M1.x; ta.y += M1.y; ta.z += M1.z;
+			}
+			for (int s2 = 0; s2 < cj.n_qu; ++s2) {                     // mu_i - Q_j (:2540-2720)
+				const double4 B = sj[j_qu0 + 2 * s2]; const V3 e2 = ld3(sj[j_qu0 + 2 * s2 + 1]);
+				V3 f, M1, M2; double u;
+				pot_mu_Q(v3(A.x - B.x, A.y - B.y, A.z - B.z), e1, A.w, e2, B.w, f, M1, M2, u);
+				fa.x += f.x; fa.y += f.y; fa.z += f.z; uX += u;
+				ta.x += M1.x; ta.y += M1.y; ta.z += M1.z;
+			}
+			F.x += fa.x; F.y += fa.y; F.z += fa.z;
+			V.x += m.x * fa.x; V.y += m.y * fa.y; V.z += m.z * fa.z;
+			V3 t = cross(v3(A.x - Ri.x, A.y - Ri.y, A.z - Ri.z), fa);
+			M.x += t.x + ta.x; M.y += t.y + ta.y; M.z += t.z + ta.z;
+		}
+		// ---- quadrupoles of i
+		for (int s1 = 0; s1 < ci.n_qu; ++s1) {
+			const double4 A = si[i_qu0 + 2 * s1]; const V3 e1 = ld3(si[i_qu0 + 2 * s1 + 1]);
+			V3 fa = v3(0, 0, 0), ta = v3(0, 0, 0);
+			for (int s2 = 0; s2 < cj.n_ch; ++s2) {                     // Q_i - q_j (:1485-1650): charge is site 1
+				const double4 B = sj[j_ch0 + s2];
+				V3 f, M2; double u;
+				pot_q_Q(v3(B.x - A.x, B.y - A.y, B.z - A.z), B.w, e1, A.w, f, M2, u);
+				fa.x -= f.x; fa.y -= f.y; fa.z -= f.z; uX += u;
+				ta.x += M2.x; ta.y += M2.y; ta.z += M2.z;
+			}
+			for (int s2 = 0; s2 < cj.n_di; ++s2) {                     // Q_i - mu_j (:2008-2192): dipole is site 1
+				const double4 B = sj[j_di0 + 2 * s2]; const V3 e2 = ld3(sj[j_di0 + 2 * s2 + 1]);
+				V3 f, M1, M2; double u;
+				pot_mu_Q(v3(B.x - A.x, B.y - A.y, B.z - A.z), e2, B.w, e1, A.w, f, M1, M2, u);
+				fa.x -= f.x; fa.y -= f.y; fa.z -= f.z; uX += u;
+				ta.x += M2.x; ta.y += M2.y; ta.z += M2.z;
+			}
+			for (int s2 = 0; s2 < cj.n_qu; ++s2) {                     // Q - Q (:2202-2378)
+				const double4 B = sj[j_qu0 + 2 * s2]; const V3 e2 = ld3(sj[j_qu0 + 2 * s2 + 1]);
+				V3 f, M1, M2; double u;
+				pot_Q_Q(v3(A.x - B.x, A.y - B.y, A.z - B.z), e1, A.w, e2, B.w, f, M1, M2, u);
+				fa.x += f.x; fa.y += f.y; fa.z += f.z; uX += u;
+				ta.x += M1.x; ta.y += M1.y; ta.z += M1.z;
+			}
+			F.x += fa.x; F.y += fa.y; F.z += fa.z;
+			V.x += m.x * fa.x; V.y += m.y * fa.y; V.z += m.z * fa.z;
+			V3 t = cross(v3(A.x - Ri.x, A.y - Ri.y, A.z - Ri.z), fa);
+			M.x += t.x + ta.x; M.y += t.y + ta.y; M.z += t.z + ta.z;
+		}
+	}
+}
+
+// The same ten loops for a SINGLE-COMPONENT system whose site counts are compile-time constants: every loop unrolls, the
+// site rows of both molecules live in registers, the LJ tables come from the constant bank.
+template <int NLJ, int NCH, int NDI, int NQU>
+__device__ __forceinline__ void pair_body_fixed(const ForceArgs& a, const V3& Ri, const double4* si, const double4* sj,
+                                                const V3& m, const bool in_lj, const bool in_rc, MolAcc& A_) {
+	constexpr int i_ch0 = NLJ, i_di0 = NLJ + NCH, i_qu0 = NLJ + NCH + 2 * NDI;
+	constexpr int j_ch0 = i_ch0, j_di0 = i_di0, j_qu0 = i_qu0;
+	V3& F = A_.F; V3& M = A_.M; V3& V = A_.V; double& u6 = A_.u6; double& uX = A_.uX; double& rf = A_.rf;
+	{
+		// ---- LJ - LJ (VectorizedCellProcessor.cpp:1031-1180)
+		if (in_lj)
+			_Pragma("unroll") for (int s1 = 0; s1 < NLJ; ++s1) {
+				const double4 A = si[s1];
+				V3 fa = v3(0, 0, 0);
+				_Pragma("unroll") for (int s2 = 0; s2 < NLJ; ++s2) {
+					const double4 B = sj[s2];
+					const int k = s1 * NLJ + s2;      // single component: global LJ id == site index
+					V3 f; double u;
+					pot_lj(v3(A.x - B.x, A.y - B.y, A.z - B.z), a.eps24_c[k], a.sig2_c[k], a.shift6_c[k], f, u);
+					fa.x += f.x; fa.y += f.y; fa.z += f.z; u6 += u;
+				}
+				F.x += fa.x; F.y += fa.y; F.z += fa.z;
+				V.x += m.x * fa.x; V.y += m.y * fa.y; V.z += m.z * fa.z;
+				V3 t = cross(v3(A.x - Ri.x, A.y - Ri.y, A.z - Ri.z), fa);
+				M.x += t.x; M.y += t.y; M.z += t.z;
+			}
+		if (!in_rc) return;
+		// ---- charges of i
+		_Pragma("unroll") for (int s1 = 0; s1 < NCH; ++s1) {
+			const double4 A = si[i_ch0 + s1];
+			V3 fa = v3(0, 0, 0);
+			_Pragma("unroll") for (int s2 = 0; s2 < NCH; ++s2) {                     // q - q (:1192-1319)
+				const double4 B = sj[j_ch0 + s2];
+				V3 f; double u;
+				pot_qq(v3(A.x - B.x, A.y - B.y, A.z - B.z), A.w * B.w, f, u);
+				fa.x += f.x; fa.y += f.y; fa.z += f.z; uX += u;
+			}
+			_Pragma("unroll") for (int s2 = 0; s2 < NDI; ++s2) {                     // q_i - mu_j (:1847-2006)
+				const double4 B = sj[j_di0 + 2 * s2], E = sj[j_di0 + 2 * s2 + 1];
+				V3 f, M2; double u;
+				pot_q_mu(v3(A.x - B.x, A.y - B.y, A.z - B.z), A.w, ld3(E), B.w, f, M2, u);
+				fa.x += f.x; fa.y += f.y; fa.z += f.z; uX += u;
+			}
+			_Pragma("unroll") for (int s2 = 0; s2 < NQU; ++s2) {                     // q_i - Q_j (:2380-2538)
+				const double4 B = sj[j_qu0 + 2 * s2], E = sj[j_qu0 + 2 * s2 + 1];
+				V3 f, M2; double u;
+				pot_q_Q(v3(A.x - B.x, A.y - B.y, A.z - B.z), A.w, ld3(E), B.w, f, M2, u);
+				fa.x += f.x; fa.y += f.y; fa.z += f.z; uX += u;
+			}
+			F.x += fa.x; F.y += fa.y; F.z += fa.z;
+			V.x += m.x * fa.x; V.y += m.y * fa.y; V.z += m.z * fa.z;
+			V3 t = cross(v3(A.x - Ri.x, A.y - Ri.y, A.z - Ri.z), fa);
+			M.x += t.x; M.y += t.y; M.z += t.z;
+		}
+		// ---- dipoles of i
+		_Pragma("unroll") for (int s1 = 0; s1 < NDI; ++s1) {
+			const double4 A = si[i_di0 + 2 * s1]; const V3 e1 = ld3(si[i_di0 + 2 * s1 + 1]);
+			V3 fa = v3(0, 0, 0), ta = v3(0, 0, 0);
+			_Pragma("unroll") for (int s2 = 0; s2 < NCH; ++s2) {                     // mu_i - q_j (:1323-1481): charge is site 1
+				const double4 B = sj[j_ch0 + s2];
+				V3 f, M2; double u;
+				pot_q_mu(v3(B.x - A.x, B.y - A.y, B.z - A.z), B.w, e1, A.w, f, M2, u);
+				fa.x -= f.x; fa.y -= f.y; fa.z -= f.z; uX += u;
+				ta.x += M2.x; ta.y += M2.y; ta.z += M2.z;
+			}
+			_Pragma("unroll") for (int s2 = 0; s2 < NDI; ++s2) {                     // mu - mu (:1667-1845)
+				const double4 B = sj[j_di0 + 2 * s2]; const V3 e2 = ld3(sj[j_di0 + 2 * s2 + 1]);
+				V3 f, M1, M2; double u, r;
+				pot_mu_mu(v3(A.x - B.x, A.y - B.y, A.z - B.z), e1, A.w, e2, B.w, a.epsRFInvrc3, f, M1, M2, u, r);
+				fa.x += f.x; fa.y += f.y; fa.z += f.z; uX += u; rf -= r;
+				ta.x += M1.x; ta.y += M1.y; ta.z += M1.z;
+			}
+			_Pragma("unroll") for (int s2 = 0; s2 < NQU; ++s2) {                     // mu_i - Q_j (:2540-2720)
+				const double4 B = sj[j_qu0 + 2 * s2]; const V3 e2 = ld3(sj[j_qu0 + 2 * s2 + 1]);
+				V3 f, M1, M2; double u;
+				pot_mu_Q(v3(A.x - B.x, A.y - B.y, A.z - B.z), e1, A.w, e2, B.w, f, M1, M2, u);
+				fa.x += f.x; fa.y += f.y; fa.z += f.z; uX += u;
+				ta.x += M1.x; ta.y += M1.y; ta.z += M1.z;
+			}
+			F.x += fa.x; F.y += fa.y; F.z += fa.z;
+			V.x += m.x * fa.x; V.y += m.y * fa.y; V.z += m.z * fa.z;
+			V3 t = cross(v3(A.x - Ri.x, A.y - Ri.y, A.z - Ri.z), fa);
+			M.x += t.x + ta.x; M.y += t.y + ta.y; M.z += t.z + ta.z;
+		}
+		// ---- quadrupoles of i
+		_Pragma("unroll") for (int s1 = 0; s1 < NQU; ++s1) {
+			const double4 A = si[i_qu0 + 2 * s1]; const V3 e1 = ld3(si[i_qu0 + 2 * s1 + 1]);
+			V3 fa = v3(0, 0, 0), ta = v3(0, 0, 0);
+			_Pragma("unroll") for (int s2 = 0; s2 < NCH; ++s2) {                     // Q_i - q_j (:1485-1650): charge is site 1
+				const double4 B = sj[j_ch0 + s2];
+				V3 f, M2; double u;
+				pot_q_Q(v3(B.x - A.x, B.y - A.y, B.z - A.z), B.w, e1, A.w, f, M2, u);
+				fa.x -= f.x; fa.y -= f.y; fa.z -= f.z; uX += u;
+				ta.x += M2.x; ta.y += M2.y; ta.z += M2.z;
+			}
+			_Pragma("unroll") for (int s2 = 0; s2 < NDI; ++s2) {                     // Q_i - mu_j (:2008-2192): dipole is site 1
+				const double4 B = sj[j_di0 + 2 * s2]; const V3 e2 = ld3(sj[j_di0 + 2 * s2 + 1]);
+				V3 f, M1, M2; double u;
+				pot_mu_Q(v3(B.x - A.x, B.y - A.y, B.z - A.z), e2, B.w, e1, A.w, f, M1, M2, u);
+				fa.x -= f.x; fa.y -= f.y; fa.z -= f.z; uX += u;
+				ta.x += M2.x; ta.y += M2.y; ta.z += M2.z;
+			}
+			_Pragma("unroll") for (int s2 = 0; s2 < NQU; ++s2) {                     // Q - Q (:2202-2378)
+				const double4 B = sj[j_qu0 + 2 * s2]; const V3 e2 = ld3(sj[j_qu0 + 2 * s2 + 1]);
+				V3 f, M1, M2; double u;
+				pot_Q_Q(v3(A.x - B.x, A.y - B.y, A.z - B.z), e1, A.w, e2, B.w, f, M1, M2, u);
+				fa.x += f.x; fa.y += f.y; fa.z += f.z; uX += u;
+				ta.x += M1.x; ta.y += M1.y; ta.z += M1.z;
+			}
+			F.x += fa.x; F.y += fa.y; F.z += fa.z;
+			V.x += m.x * fa.x; V.y += m.y * fa.y; V.z += m.z * fa.z;
+			V3 t = cross(v3(A.x - Ri.x, A.y - Ri.y, A.z - Ri.z), fa);
+			M.x += t.x + ta.x; M.y += t.y + ta.y; M.z += t.z + ta.z;
+		}
+	}
+}
+
+#define GQ_CAP 88        // queue entries per lane (molecule pairs inside the cutoff waiting for their site loops)
+#define GQ_CHUNK 16      // candidates scanned between two "queue nearly full?" votes
+
 // generic multi-site, multi-component kernel: one thread per owned molecule.
+// The molecule-centre cutoff accepts only ~10 % of the candidates of the 27 cells, and the site loops behind it are long:
+// evaluating them under that branch leaves ~3 of 32 lanes busy.  So every lane first SCANS candidates and queues the
+// survivors (shared memory, one column per lane); when some lane's queue is nearly full - or the candidates are
+// exhausted - all lanes DRAIN their queues through the site loops together.
+// NLJ >= 0: single-component system with compile-time site counts (pair_body_fixed); NLJ < 0: anything (pair_body).
+template <int NLJ, int NCH, int NDI, int NQU>
 __global__ void __launch_bounds__(FORCE_THREADS) force_generic_kernel(ForceArgs a) {
+	constexpr bool FIXED = NLJ >= 0;
+	constexpr int NS = FIXED ? NLJ + NCH + 2 * NDI + 2 * NQU : 1;      // site-cache rows per molecule
 	__shared__ double red[5 * 32];
+	__shared__ uint32_t queue[GQ_CAP * FORCE_THREADS];
 	size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
 	double acc[5] = {0., 0., 0., 0., 0.};
 	uint32_t cflag = i < a.n ? a.cell[i] : HALO_FLAG;
-	if (!(cflag & HALO_FLAG)) {
-		const Grid& g = a.g;
-		const double4 Pi = a.pos[i];
-		const V3 Ri = ld3(Pi);
-		const CompDev ci = a.comps[pos_cid(Pi)];
-		const double4* si = a.cache + i * (size_t)a.stride;
-		const int i_ch0 = ci.n_lj, i_di0 = ci.n_lj + ci.n_ch, i_qu0 = i_di0 + 2 * ci.n_di;
-		V3 F = v3(0, 0, 0), M = v3(0, 0, 0), V = v3(0, 0, 0);
-		double u6 = 0., uX = 0., rf = 0.; unsigned long long np = 0;
-		const int cx = cflag % g.cpd[0], cy = (cflag / g.cpd[0]) % g.cpd[1], cz = cflag / (g.cpd[0] * g.cpd[1]);
-		for (int dz = -1; dz <= 1; ++dz)
-		for (int dy = -1; dy <= 1; ++dy) {
-			// the three x-neighbours of a row are contiguous in the cell-sorted arrays
-			uint32_t crow = (uint32_t)(((cz + dz) * g.cpd[1] + (cy + dy)) * g.cpd[0] + cx);
-			uint32_t j0 = a.cell_start[crow - 1], j1 = a.cell_start[crow + 2];
-			uint32_t own0 = a.cell_start[cflag], own1 = a.cell_start[cflag + 1];
-			bool own_row = (dz == 0 && dy == 0);
-			for (uint32_t j = j0; j < j1; ++j) {
-				if (j == (uint32_t)i) continue;
-				const double4 Pj = a.pos[j];
-				const V3 m = v3(Ri.x - Pj.x, Ri.y - Pj.y, Ri.z - Pj.z);
-				const double m2 = dot(m, m);
-				// SingleCellPolicy_::GetForceMask: pairs at distance 0 inside one cell are skipped (Helpers.h:367-376)
-				if (own_row && j >= own0 && j < own1 && m2 == 0.0) continue;
-				const bool in_lj = m2 < a.rclj2, in_rc = m2 < a.rc2;
-				if (!(in_lj || in_rc)) continue;
-				++np;
-				const CompDev cj = a.comps[pos_cid(Pj)];
-				const double4* sj = a.cache + (size_t)j * a.stride;
-				const int j_ch0 = cj.n_lj, j_di0 = cj.n_lj + cj.n_ch, j_qu0 = j_di0 + 2 * cj.n_di;
-				// ---- LJ - LJ (VectorizedCellProcessor.cpp:1031-1180)
-				if (in_lj)
-					for (int s1 = 0; s1 < ci.n_lj; ++s1) {
-						const double4 A = si[s1];
-						const int ida = (int)__double_as_longlong(A.w);
-						V3 fa = v3(0, 0, 0);
-						for (int s2 = 0; s2 < cj.n_lj; ++s2) {
-							const double4 B = sj[s2];
-							const int k = ida * a.S + (int)__double_as_longlong(B.w);
-							V3 f; double u;
-							pot_lj(v3(A.x - B.x, A.y - B.y, A.z - B.z), a.eps24[k], a.sig2[k], a.shift6[k], f, u);
-							fa.x += f.x; fa.y += f.y; fa.z += f.z; u6 += u;
-						}
-						F.x += fa.x; F.y += fa.y; F.z += fa.z;
-						V.x += m.x * fa.x; V.y += m.y * fa.y; V.z += m.z * fa.z;
-						V3 t = cross(v3(A.x - Ri.x, A.y - Ri.y, A.z - Ri.z), fa);
-						M.x += t.x; M.y += t.y; M.z += t.z;
-					}
-				if (!in_rc) continue;
-				// ---- charges of i
-				for (int s1 = 0; s1 < ci.n_ch; ++s1) {
-					const double4 A = si[i_ch0 + s1];
-					V3 fa = v3(0, 0, 0);
-					for (int s2 = 0; s2 < cj.n_ch; ++s2) {                     // q - q (:1192-1319)
-						const double4 B = sj[j_ch0 + s2];
-						V3 f; double u;
-						pot_qq(v3(A.x - B.x, A.y - B.y, A.z - B.z), A.w * B.w, f, u);
-						fa.x += f.x; fa.y += f.y; fa.z += f.z; uX += u;
-					}
-					for (int s2 = 0; s2 < cj.n_di; ++s2) {                     // q_i - mu_j (:1847-2006)
-						const double4 B = sj[j_di0 + 2 * s2], E = sj[j_di0 + 2 * s2 + 1];
-						V3 f, M2; double u;
-						pot_q_mu(v3(A.x - B.x, A.y - B.y, A.z - B.z), A.w, ld3(E), B.w, f, M2, u);
-						fa.x += f.x; fa.y += f.y; fa.z += f.z; uX += u;
-					}
-					for (int s2 = 0; s2 < cj.n_qu; ++s2) {                     // q_i - Q_j (:2380-2538)
-						const double4 B = sj[j_qu0 + 2 * s2], E = sj[j_qu0 + 2 * s2 + 1];
-						V3 f, M2; double u;
-						pot_q_Q(v3(A.x - B.x, A.y - B.y, A.z - B.z), A.w, ld3(E), B.w, f, M2, u);
-						fa.x += f.x; fa.y += f.y; fa.z += f.z; uX += u;
-					}
-					F.x += fa.x; F.y += fa.y; F.z += fa.z;
-					V.x += m.x * fa.x; V.y += m.y * fa.y; V.z += m.z * fa.z;
-					V3 t = cross(v3(A.x - Ri.x, A.y - Ri.y, A.z - Ri.z), fa);
-					M.x += t.x; M.y += t.y; M.z += t.z;
+	const bool owned = !(cflag & HALO_FLAG);
+	const Grid& g = a.g;
+	double4 Pi = make_double4(0., 0., 0., 0.);
+	if (owned) Pi = a.pos[i];
+	const V3 Ri = ld3(Pi);
+	CompDev ci; ci.n_lj = ci.n_ch = ci.n_di = ci.n_qu = 0;
+	if (owned) ci = a.comps[pos_cid(Pi)];
+	const double4* si = a.cache + i * (size_t)a.stride;
+	const int i_ch0 = ci.n_lj, i_di0 = ci.n_lj + ci.n_ch, i_qu0 = i_di0 + 2 * ci.n_di;
+	double4 sir[NS];                       // FIXED: the molecule's own site rows in registers
+	if (FIXED && owned) {
+#pragma unroll
+		for (int k = 0; k < NS; ++k) sir[k] = si[k];
+	}
+	MolAcc A_; A_.F = v3(0, 0, 0); A_.M = v3(0, 0, 0); A_.V = v3(0, 0, 0); A_.u6 = 0.; A_.uX = 0.; A_.rf = 0.; A_.np = 0;
+	const int cx = cflag % g.cpd[0], cy = (cflag / g.cpd[0]) % g.cpd[1], cz = cflag / (g.cpd[0] * g.cpd[1]);
+	uint32_t own0 = 0, own1 = 0;
+	if (owned) { own0 = a.cell_start[cflag]; own1 = a.cell_start[cflag + 1]; }
+	uint32_t* q = queue + threadIdx.x;
+	int cnt = 0;
+	int row = owned ? 0 : 9;              // rows of the 27-cell neighbourhood: the three x-neighbours of a row are contiguous slots
+	uint32_t j = 0, jend = 0;
+	auto open_row = [&]() {
+		const int dz = row / 3 - 1, dy = row % 3 - 1;
+		const uint32_t crow = (uint32_t)(((cz + dz) * g.cpd[1] + (cy + dy)) * g.cpd[0] + cx);
+		j = a.cell_start[crow - 1]; jend = a.cell_start[crow + 2];
+	};
+	if (owned) open_row();
+	for (;;) {
+		// ---- scan: molecule-centre distances only ----------------------------------------------------------------
+		for (;;) {
+			if (row < 9) {
+				const uint32_t je = min(jend, j + GQ_CHUNK);
+				const bool own_row = row == 4;
+				for (; j < je; ++j) {
+					const double4 Pj = a.pos[j];
+					const double mx = Ri.x - Pj.x, my = Ri.y - Pj.y, mz = Ri.z - Pj.z;
+					const double m2 = mx * mx + my * my + mz * mz;
+					bool take = (m2 < a.rclj2 || m2 < a.rc2) && j != (uint32_t)i;
+					// SingleCellPolicy_::GetForceMask: pairs at distance 0 inside one cell are skipped (Helpers.h:367-376)
+					if (own_row && j >= own0 && j < own1 && m2 == 0.0) take = false;
+					if (take) { q[cnt * FORCE_THREADS] = j; ++cnt; }
 				}
-				// ---- dipoles of i
-				for (int s1 = 0; s1 < ci.n_di; ++s1) {
-					const double4 A = si[i_di0 + 2 * s1]; const V3 e1 = ld3(si[i_di0 + 2 * s1 + 1]);
-					V3 fa = v3(0, 0, 0), ta = v3(0, 0, 0);
-					for (int s2 = 0; s2 < cj.n_ch; ++s2) {                     // mu_i - q_j (:1323-1481): charge is site 1
-						const double4 B = sj[j_ch0 + s2];
-						V3 f, M2; double u;
-						pot_q_mu(v3(B.x - A.x, B.y - A.y, B.z - A.z), B.w, e1, A.w, f, M2, u);
-						fa.x -= f.x; fa.y -= f.y; fa.z -= f.z; uX += u;
-						ta.x += M2.x; ta.y += M2.y; ta.z += M2.z;
-					}
-					for (int s2 = 0; s2 < cj.n_di; ++s2) {                     // mu - mu (:1667-1845)
-						const double4 B = sj[j_di0 + 2 * s2]; const V3 e2 = ld3(sj[j_di0 + 2 * s2 + 1]);
-						V3 f, M1, M2; double u, r;
-						pot_mu_mu(v3(A.x - B.x, A.y - B.y, A.z - B.z), e1, A.w, e2, B.w, a.epsRFInvrc3, f, M1, M2, u, r);
-						fa.x += f.x; fa.y += f.y; fa.z += f.z; uX += u; rf -= r;
-						ta.x += M1.x; ta.y += M1.y; ta.z += M1.z;
-					}
-					for (int s2 = 0; s2 < cj.n_qu; ++s2) {                     // mu_i - Q_j (:2540-2720)
-						const double4 B = sj[j_qu0 + 2 * s2]; const V3 e2 = ld3(sj[j_qu0 + 2 * s2 + 1]);
-						V3 f, M1, M2; double u;
-						pot_mu_Q(v3(A.x - B.x, A.y - B.y, A.z - B.z), e1, A.w, e2, B.w, f, M1, M2, u);
-						fa.x += f.x; fa.y += f.y; fa.z += f.z; uX += u;
-						ta.x += M1.x; ta.y += M1.y; ta.z += M1.z;
-					}
-					F.x += fa.x; F.y += fa.y; F.z += fa.z;
-					V.x += m.x * fa.x; V.y += m.y * fa.y; V.z += m.z * fa.z;
-					V3 t = cross(v3(A.x - Ri.x, A.y - Ri.y, A.z - Ri.z), fa);
-					M.x += t.x + ta.x; M.y += t.y + ta.y; M.z += t.z + ta.z;
-				}
-				// ---- quadrupoles of i
-				for (int s1 = 0; s1 < ci.n_qu; ++s1) {
-					const double4 A = si[i_qu0 + 2 * s1]; const V3 e1 = ld3(si[i_qu0 + 2 * s1 + 1]);
-					V3 fa = v3(0, 0, 0), ta = v3(0, 0, 0);
-					for (int s2 = 0; s2 < cj.n_ch; ++s2) {                     // Q_i - q_j (:1485-1650): charge is site 1
-						const double4 B = sj[j_ch0 + s2];
-						V3 f, M2; double u;
-						pot_q_Q(v3(B.x - A.x, B.y - A.y, B.z - A.z), B.w, e1, A.w, f, M2, u);
-						fa.x -= f.x; fa.y -= f.y; fa.z -= f.z; uX += u;
-						ta.x += M2.x; ta.y += M2.y; ta.z += M2.z;
-					}
-					for (int s2 = 0; s2 < cj.n_di; ++s2) {                     // Q_i - mu_j (:2008-2192): dipole is site 1
-						const double4 B = sj[j_di0 + 2 * s2]; const V3 e2 = ld3(sj[j_di0 + 2 * s2 + 1]);
-						V3 f, M1, M2; double u;
-						pot_mu_Q(v3(B.x - A.x, B.y - A.y, B.z - A.z), e2, B.w, e1, A.w, f, M1, M2, u);
-						fa.x -= f.x; fa.y -= f.y; fa.z -= f.z; uX += u;
-						ta.x += M2.x; ta.y += M2.y; ta.z += M2.z;
-					}
-					for (int s2 = 0; s2 < cj.n_qu; ++s2) {                     // Q - Q (:2202-2378)
-						const double4 B = sj[j_qu0 + 2 * s2]; const V3 e2 = ld3(sj[j_qu0 + 2 * s2 + 1]);
-						V3 f, M1, M2; double u;
-						pot_Q_Q(v3(A.x - B.x, A.y - B.y, A.z - B.z), e1, A.w, e2, B.w, f, M1, M2, u);
-						fa.x += f.x; fa.y += f.y; fa.z += f.z; uX += u;
-						ta.x += M1.x; ta.y += M1.y; ta.z += M1.z;
-					}
-					F.x += fa.x; F.y += fa.y; F.z += fa.z;
-					V.x += m.x * fa.x; V.y += m.y * fa.y; V.z += m.z * fa.z;
-					V3 t = cross(v3(A.x - Ri.x, A.y - Ri.y, A.z - Ri.z), fa);
-					M.x += t.x + ta.x; M.y += t.y + ta.y; M.z += t.z + ta.z;
-				}
+				if (j == jend) { ++row; if (row < 9) open_row(); }
+			}
+			const bool any_full = __any_sync(0xffffffffu, cnt > GQ_CAP - GQ_CHUNK);
+			const bool any_more = __any_sync(0xffffffffu, row < 9);
+			if (any_full || !any_more) break;
+		}
+		// ---- drain: the site loops of the queued pairs -----------------------------------------------------------
+		for (int t = 0; t < cnt; ++t) {
+			const uint32_t jj = q[t * FORCE_THREADS];
+			const double4 Pj = a.pos[jj];
+			const V3 m = v3(Ri.x - Pj.x, Ri.y - Pj.y, Ri.z - Pj.z);
+			const double m2 = dot(m, m);
+			++A_.np;
+			if constexpr (FIXED) {
+				double4 sjr[NS];
+				const double4* sj = a.cache + (size_t)jj * a.stride;
+#pragma unroll
+				for (int k = 0; k < NS; ++k) sjr[k] = sj[k];
+				pair_body_fixed<NLJ, NCH, NDI, NQU>(a, Ri, sir, sjr, m, m2 < a.rclj2, m2 < a.rc2, A_);
+			} else {
+				pair_body(a, Ri, ci, si, i_ch0, i_di0, i_qu0, jj, Pj, m, m2 < a.rclj2, m2 < a.rc2, A_);
 			}
 		}
+		cnt = 0;
+		if (!__any_sync(0xffffffffu, row < 9)) break;
+	}
+	if (owned) {
 		// calcFM (FullMolecule.cpp:551-631): Vi = 1/2 sum V_site
-		a.F[3 * i] = F.x; a.F[3 * i + 1] = F.y; a.F[3 * i + 2] = F.z;
-		a.M[3 * i] = M.x; a.M[3 * i + 1] = M.y; a.M[3 * i + 2] = M.z;
-		a.Vi[3 * i] = 0.5 * V.x; a.Vi[3 * i + 1] = 0.5 * V.y; a.Vi[3 * i + 2] = 0.5 * V.z;
-		acc[0] = u6; acc[1] = uX; acc[2] = V.x + V.y + V.z; acc[3] = rf; acc[4] = (double)np;
+		a.F[3 * i] = A_.F.x; a.F[3 * i + 1] = A_.F.y; a.F[3 * i + 2] = A_.F.z;
+		a.M[3 * i] = A_.M.x; a.M[3 * i + 1] = A_.M.y; a.M[3 * i + 2] = A_.M.z;
+		a.Vi[3 * i] = 0.5 * A_.V.x; a.Vi[3 * i + 1] = 0.5 * A_.V.y; a.Vi[3 * i + 2] = 0.5 * A_.V.z;
+		acc[0] = A_.u6; acc[1] = A_.uX; acc[2] = A_.V.x + A_.V.y + A_.V.z; acc[3] = A_.rf; acc[4] = (double)A_.np;
 	}
 	block_sum<5>(acc, red);
 	if (threadIdx.x == 0) {
@@ -304,8 +493,25 @@ int k_forces(ls1g_ctx* c) {
 		a.eps24 = c->eps24; a.sig2 = c->sig2; a.shift6 = c->shift6; a.S = c->S_lj;
 		a.rc2 = c->rc2; a.rclj2 = c->rclj2; a.epsRFInvrc3 = c->epsRFInvrc3;
 		a.F = c->F; a.M = c->M; a.Vi = c->Vi; a.partials = c->partials;
+		// single-component systems of the common rigid models get a kernel with compile-time site counts
+		const CompDev& c0 = c->comps_h[0];
+		const int key = c->n_comp == 1 && c->S_lj <= 4 ? c0.n_lj * 1000 + c0.n_ch * 100 + c0.n_di * 10 + c0.n_qu : -1;
+		if (key >= 0)
+			for (int k = 0; k < c->S_lj * c->S_lj; ++k) { a.eps24_c[k] = c->eps24_h[k]; a.sig2_c[k] = c->sig2_h[k]; a.shift6_c[k] = c->shift6_h[k]; }
 		timer_start(c, LS1G_T_FORCE);
-		force_generic_kernel<<<nb, FORCE_THREADS, 0, c->stream>>>(a);
+		switch (key) {
+#define LS1G_FIXED_CASE(L, Q, D, U) case L * 1000 + Q * 100 + D * 10 + U: force_generic_kernel<L, Q, D, U><<<nb, FORCE_THREADS, 0, c->stream>>>(a); break;
+		LS1G_FIXED_CASE(3, 3, 0, 0)      // CO2 (3 LJ + 3 charges), examples/CO2
+		LS1G_FIXED_CASE(3, 0, 1, 0)      // ethylene oxide (3 LJ + dipole), examples/EOX
+		LS1G_FIXED_CASE(3, 0, 0, 1)      // CO2 Merker (3 LJ + quadrupole)
+		LS1G_FIXED_CASE(2, 0, 0, 1)      // 2CLJQ
+		LS1G_FIXED_CASE(2, 0, 1, 0)      // 2CLJD
+		LS1G_FIXED_CASE(1, 0, 1, 0)      // Stockmayer
+		LS1G_FIXED_CASE(2, 0, 0, 0)      // 2CLJ
+		LS1G_FIXED_CASE(4, 0, 0, 0)      // 4 LJ sites
+#undef LS1G_FIXED_CASE
+		default: force_generic_kernel<-1, 0, 0, 0><<<nb, FORCE_THREADS, 0, c->stream>>>(a);
+		}
 		timer_stop(c, LS1G_T_FORCE, 1);
 	}
 	if (k_force_finalize(c, nb)) return 1;
