@@ -67,6 +67,7 @@ struct ForceArgs {
 	double rc2, rclj2, epsRFInvrc3;
 	double *F, *M, *Vi;
 	double* partials;               // [blocks][5]: upot6lj, upotXpoles, virial, myRF, pairs
+	int bpr, nyi;                   // blocks per owned cell row, owned rows per z layer
 	double eps24_c[16], sig2_c[16], shift6_c[16];   // single-component kernels (S <= 4): the LJ tables travel in the kernel parameters (constant bank)
 };
 
@@ -331,11 +332,19 @@ __global__ void __launch_bounds__(FORCE_THREADS) force_generic_kernel(ForceArgs 
 	constexpr int NS = FIXED ? NLJ + NCH + 2 * NDI + 2 * NQU : 1;      // site-cache rows per molecule
 	__shared__ double red[5 * 32];
 	__shared__ uint32_t queue[GQ_CAP * FORCE_THREADS];
-	size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-	double acc[5] = {0., 0., 0., 0., 0.};
-	uint32_t cflag = i < a.n ? a.cell[i] : HALO_FLAG;
-	const bool owned = !(cflag & HALO_FLAG);
+	// block (row, b) = 128 consecutive OWNED slots of one cell row (y, z): the owned cells of a row are contiguous in the
+	// cell-sorted arrays, so no lane is spent on a halo slot
 	const Grid& g = a.g;
+	double acc[5] = {0., 0., 0., 0., 0.};
+	size_t i; bool owned;
+	{
+		const int row = blockIdx.x / a.bpr, bi = blockIdx.x % a.bpr;
+		const uint32_t crow0 = (uint32_t)(((row / a.nyi + 1) * g.cpd[1] + (row % a.nyi + 1)) * g.cpd[0]);
+		const uint32_t rs = a.cell_start[crow0 + 1], re = a.cell_start[crow0 + g.cpd[0] - 1];
+		i = (size_t)rs + (size_t)bi * FORCE_THREADS + threadIdx.x;
+		owned = i < re;
+	}
+	const uint32_t cflag = owned ? a.cell[i] : HALO_FLAG;
 	double4 Pi = make_double4(0., 0., 0., 0.);
 	if (owned) Pi = a.pos[i];
 	const V3 Ri = ld3(Pi);
@@ -384,8 +393,18 @@ __global__ void __launch_bounds__(FORCE_THREADS) force_generic_kernel(ForceArgs 
 			if (any_full || !any_more) break;
 		}
 		// ---- drain: the site loops of the queued pairs -----------------------------------------------------------
-		for (int t = 0; t < cnt; ++t) {
-			const uint32_t jj = q[t * FORCE_THREADS];
+		// Not everything: every lane takes the D newest entries of its queue, D = the smallest backlog in the warp (all
+		// lanes busy), but at least what the fullest lane must shed to scan on.  Only the last round empties the queues.
+		const bool last_round = !__any_sync(0xffffffffu, row < 9);
+		int D = GQ_CAP;
+		if (!last_round) {
+			const int mn = __reduce_min_sync(0xffffffffu, owned && (row < 9 || cnt > 0) ? cnt : GQ_CAP);
+			const int mx = __reduce_max_sync(0xffffffffu, cnt);
+			D = max(mn, mx - (GQ_CAP - GQ_CHUNK));
+		}
+		const int take = min(cnt, D);
+		for (int t = 0; t < take; ++t) {
+			const uint32_t jj = q[(cnt - 1 - t) * FORCE_THREADS];
 			const double4 Pj = a.pos[jj];
 			const V3 m = v3(Ri.x - Pj.x, Ri.y - Pj.y, Ri.z - Pj.z);
 			const double m2 = dot(m, m);
@@ -400,8 +419,8 @@ __global__ void __launch_bounds__(FORCE_THREADS) force_generic_kernel(ForceArgs 
 				pair_body(a, Ri, ci, si, i_ch0, i_di0, i_qu0, jj, Pj, m, m2 < a.rclj2, m2 < a.rc2, A_);
 			}
 		}
-		cnt = 0;
-		if (!__any_sync(0xffffffffu, row < 9)) break;
+		cnt -= take;
+		if (last_round) break;
 	}
 	if (owned) {
 		// calcFM (FullMolecule.cpp:551-631): Vi = 1/2 sum V_site
@@ -481,7 +500,9 @@ int k_forces(ls1g_ctx* c) {
 	if (!c->sorted) LS1G_FAIL("ls1g_traverse: container not sorted (call ls1g_update / ls1g_exchange first)");
 	if (c->simple_1clj) return k_forces_1clj(c);
 	size_t n = c->n_slots;
-	unsigned nb = nblk(n, FORCE_THREADS);
+	const int bpr = (int)((c->max_row + FORCE_THREADS - 1) / FORCE_THREADS);
+	const int nyi = c->bgrid.cpd[1] - 2, nzi = c->bgrid.cpd[2] - 2;
+	unsigned nb = n ? (unsigned)((size_t)nyi * nzi * (bpr > 0 ? bpr : 1)) : 0;
 	if (ls1g_ensure_partials(c, nb ? nb : 1, 5)) return 1;
 	if (n) {
 		timer_start(c, LS1G_T_AUX);
@@ -493,6 +514,7 @@ int k_forces(ls1g_ctx* c) {
 		a.eps24 = c->eps24; a.sig2 = c->sig2; a.shift6 = c->shift6; a.S = c->S_lj;
 		a.rc2 = c->rc2; a.rclj2 = c->rclj2; a.epsRFInvrc3 = c->epsRFInvrc3;
 		a.F = c->F; a.M = c->M; a.Vi = c->Vi; a.partials = c->partials;
+		a.bpr = bpr > 0 ? bpr : 1; a.nyi = nyi;
 		// single-component systems of the common rigid models get a kernel with compile-time site counts
 		const CompDev& c0 = c->comps_h[0];
 		const int key = c->n_comp == 1 && c->S_lj <= 4 ? c0.n_lj * 1000 + c0.n_ch * 100 + c0.n_di * 10 + c0.n_qu : -1;
