@@ -29,7 +29,7 @@ int nl_set_bin_grid(ls1g_ctx* c, int list_mode) {
 static NLArgs nl_args(ls1g_ctx* c) {
 	NLArgs a;
 	a.g = c->bgrid; a.pos = c->cur.pos; a.cell = c->cur.cell; a.cell_start = c->cell_start;
-	a.lists = c->lists; a.lcount = c->lcount; a.flags = c->d_flags; a.bpr = c->list_bpr; a.nyi = c->bgrid.cpd[1] - 2;
+	a.lists = c->lists; a.lcount = c->lcount; a.flags = c->d_flags; a.bpr = c->list_bpr; a.nyi = c->bgrid.cpd[1] - 2; a.lcap4 = c->list_lcap / 4; a.btcap = c->build_tcap;
 	a.tcap = NL_TCAP;
 	const double rl = c->cfg.lj_cutoff + c->skin;
 	// FP32 filter: coordinates relative to the block centre are < 8 cell lengths: relative error on r^2 near rl^2 < 2e-5;
@@ -49,7 +49,9 @@ int k_list_build(ls1g_ctx* c) {
 	c->list_bpr = (int)((c->max_row + NL_BT - 1) / NL_BT);
 	if (c->list_bpr < 1) c->list_bpr = 1;
 	const size_t nb = nl_blocks(c);
-	const size_t want_l = nb * NL_LCAP * NL_BT, want_c = nb * NL_BT;
+	if (c->list_lcap < NL_LCAP0) c->list_lcap = NL_LCAP0;
+	if (c->build_tcap < NL_TCAP0) c->build_tcap = NL_TCAP0;
+	const size_t want_l = nb * (size_t)c->list_lcap * NL_BT, want_c = nb * NL_BT;
 	if (want_l > c->lists_cap) {
 		cudaFree(c->lists); c->lists = nullptr; c->lists_cap = 0;
 		CUDA_TRY(cudaMalloc((void**)&c->lists, want_l * sizeof(unsigned short)));
@@ -66,8 +68,8 @@ int k_list_build(ls1g_ctx* c) {
 	CUDA_TRY(cudaMemcpyAsync(c->pos_build, c->cur.pos, c->n_slots * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));
 	NLArgs a = nl_args(c);
 	static bool battr = false;
-	if (!battr) { CUDA_TRY(cudaFuncSetAttribute(nl_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, NL_BUILD_SMEM)); battr = true; }
-	nl_build_kernel<<<(unsigned)nb, NL_BT, NL_BUILD_SMEM, c->stream>>>(a);
+	if (!battr) { CUDA_TRY(cudaFuncSetAttribute(nl_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, NL_BUILD_SMEM(NL_TCAP))); battr = true; }
+	nl_build_kernel<<<(unsigned)nb, NL_BT, NL_BUILD_SMEM(a.btcap), c->stream>>>(a);
 	CUDA_TRY(cudaGetLastError());
 	CUDA_TRY(cudaMemcpyAsync(c->h_flags, c->d_flags, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
 	timer_stop(c, LS1G_T_SORT, 2);

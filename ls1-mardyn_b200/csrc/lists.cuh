@@ -26,8 +26,10 @@
 #pragma once
 
 #define NL_BT 128          // threads per block = molecules per block
-#define NL_TCAP 3072       // capacity of the build kernel's 9-row FP32 tile (candidates), multiple of 4
-#define NL_LCAP 128        // list entries per molecule, multiple of 4
+#define NL_TCAP0 3072      // capacity of the build kernel's 9-row FP32 tile (candidates) to start with, multiple of 4
+#define NL_TCAP 5120       // ... after a tile overflow (denser systems; fewer resident blocks)
+#define NL_LCAP0 128       // list entries per molecule to start with (multiple of 4); doubled on overflow up to NL_LCAP_MAX
+#define NL_LCAP_MAX 1020   // lcount packs the group ends in units of 4 entries, 8 bits each
 #define NL_DUMMY 4         // dummy entries at the start of every group tile (keeps real entries 4-aligned)
 
 // staging / scan order of the 9 neighbour rows (r = 3*(dz+1) + (dy+1)): three point-symmetric groups
@@ -43,6 +45,8 @@ struct NLArgs {
 	unsigned short* lists; uint32_t* lcount;
 	unsigned long long* flags;  // [1] |= NL_OVF_*
 	int bpr;                    // blocks per row
+	int lcap4;                  // list capacity per molecule in units of 4 entries
+	int btcap;                  // capacity of the build kernel's 9-row tile (NL_TCAP0 or NL_TCAP)
 	int nyi;
 	int tcap;                   // slab tile capacity of the force launch (max slab tile of the last build), multiple of 4
 	float rl2f;                 // (rc + skin)^2 * (1 + margin), FP32 filter
@@ -89,7 +93,7 @@ __device__ __forceinline__ NLBlock nl_plan(const NLArgs& a, uint32_t* s_beg, int
 	}
 	__syncthreads();
 	b.total = s_off[9];
-	if (b.total > NL_TCAP) {
+	if (b.total > a.btcap) {
 		if (threadIdx.x == 0) atomicOr(a.flags + 1, (unsigned long long)NL_OVF_TILE);
 		b.live = false;
 	}
@@ -100,12 +104,12 @@ __device__ __forceinline__ NLBlock nl_plan(const NLArgs& a, uint32_t* s_beg, int
 // build: FP32 candidate filter with radius rc + skin -> per-molecule lists of tile indices
 // ---------------------------------------------------------------------------------------------------------------
 #define NL_QCAP 64         // per-lane queue entries of one row group (shared memory), multiple of 4
-#define NL_BUILD_SMEM (3 * NL_TCAP * 4 + NL_QCAP * NL_BT * 2)
+#define NL_BUILD_SMEM(tcap) (3 * (tcap) * 4 + NL_QCAP * NL_BT * 2)
 
 __global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
 	extern __shared__ __align__(16) unsigned char nl_bsm[];
-	float* xs = (float*)nl_bsm; float* ys = xs + NL_TCAP; float* zs = ys + NL_TCAP;
-	unsigned short* q = (unsigned short*)(zs + NL_TCAP);          // q[t][tid]: survivors of the current row group, one column per lane
+	float* xs = (float*)nl_bsm; float* ys = xs + a.btcap; float* zs = ys + a.btcap;
+	unsigned short* q = (unsigned short*)(zs + a.btcap);          // q[t][tid]: survivors of the current row group, one column per lane
 	__shared__ uint32_t s_beg[9]; __shared__ int s_off[10], s_len[9];
 	const Grid& g = a.g;
 	const int tid = threadIdx.x, lane = tid & 31;
@@ -141,7 +145,7 @@ __global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
 	const bool active = i < w1;
 	float fx = -1e30f, fy = -1e30f, fz = -1e30f;
 	if (active) { const double4 Pi = a.pos[i]; fx = (float)(Pi.x - ox); fy = (float)(Pi.y - oy); fz = (float)(Pi.z - oz); }
-	uint2* my = (uint2*)(a.lists + ((size_t)blockIdx.x * (NL_LCAP / 4) * NL_BT + tid) * 4);     // entries 4t..4t+3 at my[t * NL_BT]
+	uint2* my = (uint2*)(a.lists + ((size_t)blockIdx.x * a.lcap4 * NL_BT + tid) * 4);     // entries 4t..4t+3 at my[t * NL_BT]
 	unsigned short* const q0 = q + tid;
 	// the queue is addressed through one 32-bit shared-window register (append = st.shared.u16 + add, both predicated)
 	const uint32_t qa0 = (uint32_t)__cvta_generic_to_shared(q0);
@@ -151,6 +155,26 @@ __global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
 	uint32_t ends = 0;
 	const float rl2 = a.rl2f;
 	int grp = 0;
+	// queue -> list: complete quads go out as packed 8-byte stores; a mid-group flush (queue full) keeps the 0..3 left-over
+	// entries at the front of the queue, the flush at the end of a row group pads them with the dummy entry
+	auto flush = [&](bool final) {
+		int cnt = (int)(qa - qa0) / (NL_BT * 2);
+		if (final) while (cnt & 3) { q0[cnt * NL_BT] = 0; ++cnt; }
+		const int n4 = cnt >> 2, rem = cnt & 3;
+		if (done4 + n4 > a.lcap4) ovf = true;
+		else {
+			for (int t = 0; t < n4; ++t) {
+				const unsigned short* e = q0 + 4 * t * NL_BT;
+				uint2 w;
+				w.x = (uint32_t)e[0] | ((uint32_t)e[NL_BT] << 16);
+				w.y = (uint32_t)e[2 * NL_BT] | ((uint32_t)e[3 * NL_BT] << 16);
+				my[(size_t)(done4 + t) * NL_BT] = w;
+			}
+			done4 += n4;
+		}
+		for (int t = 0; t < rem; ++t) q0[t * NL_BT] = q0[(4 * n4 + t) * NL_BT];
+		qa = qa0 + rem * (NL_BT * 2);
+	};
 	for (int p = 0; p < 9; ++p) {
 		const int r = NL_ORD[p];
 		const int gbase = s_off[NL_GRP[grp]];          // indices are relative to the row group's tile
@@ -168,26 +192,12 @@ __global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
 				const float r2 = dx * dx + dy * dy + dz * dz;
 				if (r2 < rl2) { asm volatile("st.shared.u16 [%0], %1;" :: "r"(qa), "h"((unsigned short)(val + u)) : "memory"); qa += NL_BT * 2; }
 			}
-			if (qa > qalim) { ovf = true; qa = qa0; }
+			if (qa > qalim) flush(false);
 		}
 		if (p + 1 == NL_GRP[grp + 1]) {                 // end of a row group: pad to a multiple of 4 with the dummy entry, flush
-			int cnt = (int)(qa - qa0) / (NL_BT * 2);
-			while (cnt & 3) { q0[cnt * NL_BT] = 0; ++cnt; }
-			const int n4 = cnt >> 2;
-			if (done4 + n4 > NL_LCAP / 4) { ovf = true; }
-			else {
-				for (int t = 0; t < n4; ++t) {
-					const unsigned short* e = q0 + 4 * t * NL_BT;
-					uint2 w;
-					w.x = (uint32_t)e[0] | ((uint32_t)e[NL_BT] << 16);
-					w.y = (uint32_t)e[2 * NL_BT] | ((uint32_t)e[3 * NL_BT] << 16);
-					my[(size_t)(done4 + t) * NL_BT] = w;
-				}
-				done4 += n4;
-			}
+			flush(true);
 			ends |= (uint32_t)done4 << (8 * grp);
 			++grp;
-			qa = qa0;
 		}
 	}
 	if (active) a.lcount[(size_t)blockIdx.x * NL_BT + tid] = ends;
@@ -218,7 +228,7 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 		double4 Pi = make_double4(0., 0., 0., 0.);
 		uint32_t ends = 0;
 		if (active) { Pi = a.pos[i]; ends = a.lcount[(size_t)blockIdx.x * NL_BT + tid]; }
-		const uint2* my = (const uint2*)(a.lists + ((size_t)blockIdx.x * (NL_LCAP / 4) * NL_BT + tid) * 4);   // 4 entries per load
+		const uint2* my = (const uint2*)(a.lists + ((size_t)blockIdx.x * a.lcap4 * NL_BT + tid) * 4);   // 4 entries per load
 		double Fx = 0., Fy = 0., Fz = 0., Vx = 0., Vy = 0., Vz = 0., u6 = 0.;
 		int np_i = 0;
 		// 4 pairs at a time, branch-free (invalid pairs contribute exact zeros) so that the dependency chains overlap.

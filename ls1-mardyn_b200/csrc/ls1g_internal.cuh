@@ -119,6 +119,8 @@ struct ls1g_ctx {
 	int      track_disp;                    // integrate kernels track max |r - pos_build|^2 into d_flags[0]
 	int      list_tcap;                     // tile capacity used by the list force kernel (max tile of the last build, padded)
 	int      list_bpr;                      // blocks per cell row
+	int      build_tcap;                    // 9-row tile capacity of the build kernel, raised once on overflow
+	int      list_lcap;                     // list entries per molecule (multiple of 4), grown on overflow
 	unsigned long long* d_flags;            // [4]: max displacement^2 bits | overflow bits | max slab tile | snapshot of [0] (kernel guard)
 	int      vi_every_step;                 // LS1G_VI_EVERY_STEP=1: per-molecule virial on every list step, not only the last of a run
 	int      guard_on;                      // force / integrate kernels return at once when d_flags[3] > disp_thr2 (lists expired)

@@ -112,6 +112,10 @@ int k_halo_refresh(ls1g_ctx* c);
 // same value up to NL_AHEAD steps late (pinned copy + event), rebuilds, and enqueues the skipped steps again.  Device and host evaluate the
 // identical comparison d2 > disp_thr2 on the identical bits; the flag is monotone between builds (atomicMax), so an
 // expired step stays skipped however many kernels follow it.
+#define NL_OVF_LIST_BIT 2ull      // lists.cuh: NL_OVF_LIST
+#define NL_OVF_TILE_BIT 1ull      // lists.cuh: NL_OVF_TILE
+#define NL_TCAP_MAX_H 5120        // lists.cuh: NL_TCAP
+#define NL_LCAP_MAX_H 1020        // lists.cuh: NL_LCAP_MAX
 #define NL_AHEAD 3      // steps the host may enqueue beyond the last displacement flag it has read
 #define NL_RING 4       // pinned flag copies / events in flight (> NL_AHEAD)
 static int flag_snapshot(ls1g_ctx* c, int ring) {
@@ -135,7 +139,7 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 		need_build = expired(0);
 	} else if (nl_set_bin_grid(c, 1)) return 1;
 	c->in_list_mode = 1;
-	int rebuilds = 0, repeats = 0;
+	int rebuilds = 0, repeats = 0, regrow = 0;
 	double t_build = 0., t_wait = 0., t_enq = 0., t_max_wait = 0., t_max_enq = 0.;     // host wall clock, LS1G_DEBUG only
 	auto now = [&]() { if (!dbg) return 0.; struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6; };
 	// s   = next step to enqueue
@@ -154,15 +158,32 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 				if (!rc) rc = k_list_build(c);             // zeroes d_flags[0..2]
 				if (!rc && cudaMemsetAsync(c->d_flags + 3, 0, sizeof(unsigned long long), c->stream) != cudaSuccess) rc = 1;
 				if (!rc && sync_check(c, "ls1g_run (list build)")) rc = 1;
-				if (!rc && c->n_ranks > 1) {         // every rank must take the same decision
-					double ovf = c->h_flags[1] ? 1. : 0.;
-					if (cudaMemcpyAsync(c->d_scalars + 12, &ovf, sizeof(double), cudaMemcpyHostToDevice, c->stream) != cudaSuccess) rc = 1;
-					if (!rc) rc = comm_allreduce_max(c, c->d_scalars + 12, 1);
-					if (!rc && cudaMemcpyAsync(&ovf, c->d_scalars + 12, sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess) rc = 1;
+				if (!rc && c->n_ranks > 1) {         // every rank must take the same decision: [hard overflow, list overflow, tile overflow]
+					const unsigned long long hb = c->h_flags[1];
+					double ovf[3] = {(hb & ~(NL_OVF_LIST_BIT | NL_OVF_TILE_BIT)) ? 1. : 0., (hb & NL_OVF_LIST_BIT) ? 1. : 0., (hb & NL_OVF_TILE_BIT) ? 1. : 0.};
+					if (cudaMemcpyAsync(c->d_scalars + 12, ovf, 3 * sizeof(double), cudaMemcpyHostToDevice, c->stream) != cudaSuccess) rc = 1;
+					if (!rc) rc = comm_allreduce_max(c, c->d_scalars + 12, 3);
+					if (!rc && cudaMemcpyAsync(ovf, c->d_scalars + 12, 3 * sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess) rc = 1;
 					if (!rc && sync_check(c, "ls1g_run (list build)")) rc = 1;
-					if (ovf != 0. && !c->h_flags[1]) c->h_flags[1] = 8;
+					if (ovf[0] != 0.) c->h_flags[1] |= 8;
+					if (ovf[1] != 0.) c->h_flags[1] |= NL_OVF_LIST_BIT;
+					if (ovf[2] != 0.) c->h_flags[1] |= NL_OVF_TILE_BIT;
 				}
 				if (rc) break;
+				{
+					// more neighbours per molecule than the lists hold / a denser neighbourhood than the build tile holds: raise
+					// the capacity and build again (the sort is repeated too - it is idempotent on sorted data)
+					const unsigned long long hb = c->h_flags[1];
+					bool grown = false;
+					if ((hb & NL_OVF_LIST_BIT) && c->list_lcap < NL_LCAP_MAX_H) { c->list_lcap = c->list_lcap * 2 > NL_LCAP_MAX_H ? NL_LCAP_MAX_H : c->list_lcap * 2; grown = true; }
+					else if (hb & NL_OVF_LIST_BIT) grown = false;
+					if ((hb & NL_OVF_TILE_BIT) && c->build_tcap < NL_TCAP_MAX_H) { c->build_tcap = c->build_tcap + 1024 > NL_TCAP_MAX_H ? NL_TCAP_MAX_H : c->build_tcap + 1024; grown = true; }
+					const bool fixable = !(hb & ~(NL_OVF_LIST_BIT | NL_OVF_TILE_BIT)) && (!(hb & NL_OVF_LIST_BIT) || c->list_lcap <= NL_LCAP_MAX_H) && grown;
+					if (hb && fixable && ++regrow <= 6) {
+						if (dbg) fprintf(stderr, "ls1g: list buffers raised to %d entries per molecule, build tile %d (overflow bits %llu)\n", c->list_lcap, c->build_tcap, hb);
+						continue;
+					}
+				}
 				if (c->h_flags[1]) {                 // tile / list / row capacity exceeded: this system is too dense for the list buffers
 					c->list_disabled = 1; c->in_list_mode = 0; c->track_disp = 0;
 					if (dbg) fprintf(stderr, "ls1g: neighbour lists disabled, overflow bits %llu (1 tile, 2 list, 4 row), bpr %d\n", c->h_flags[1], c->list_bpr);
