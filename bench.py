@@ -106,6 +106,11 @@ def hbm_kernels(tm, steps, n_local):
         peak, src = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "MEASURED_PEAKS.json"
     except (OSError, KeyError, ValueError):
         pass
+    if tm["integrate"]["launches"] < 2 * steps:
+        # NVE steps of ls1g_run: the integrator runs in the epilogue of the force kernel, only the last step of a run
+        # launches integrate_kernel - nothing to rate separately
+        return {"integrate": {"bound": "hbm", "fused_into": "nl_force_kernel (lists.cuh, FUSE)", "separate_launches": int(tm["integrate"]["launches"]),
+                              "bytes_per_molecule": 140, "peak": peak, "unit": "GB/s", "peak_source": src}}
     ms = tm["integrate"]["ms"] / max(steps, 1)
     gbs = 140.0 * n_local / (ms * 1e-3) / 1e9 if ms > 0 else 0.0
     return {"integrate": {"bound": "hbm", "achieved": round(gbs, 1), "peak": peak, "unit": "GB/s", "frac": round(gbs / peak, 4),

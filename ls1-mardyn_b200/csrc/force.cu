@@ -474,12 +474,13 @@ __global__ void __launch_bounds__(256) reduce_partials_kernel(const double* __re
 		for (int k = 0; k < NV; ++k) out[(size_t)blockIdx.x * NV + k] = s[k];
 }
 
-// reduces partials[nb][nv] (nv = 4 or 5) to at most 256 rows when nb is large; returns the rows to finalize and their base
+// reduces partials[nb][nv] (nv = 4, 5 or 8) to at most 256 rows when nb is large; returns the rows to finalize and their base
 int ls1g_prereduce(ls1g_ctx* c, size_t& nb, int nv, const double*& base) {
 	base = c->partials;
 	if (nb <= 2048) return 0;
 	double* out = c->partials + nb * nv;          // ensure_partials reserves twice the requested size
 	if (nv == 5) reduce_partials_kernel<5><<<256, 256, 0, c->stream>>>(c->partials, nb, out);
+	else if (nv == 8) reduce_partials_kernel<8><<<256, 256, 0, c->stream>>>(c->partials, nb, out);
 	else reduce_partials_kernel<4><<<256, 256, 0, c->stream>>>(c->partials, nb, out);
 	CUDA_TRY(cudaGetLastError());
 	nb = 256; base = out;

@@ -8,6 +8,7 @@
 
 int ls1g_ensure_partials(ls1g_ctx* c, size_t blocks, int nv);
 int k_force_finalize(ls1g_ctx* c, size_t nb);
+int ls1g_prereduce(ls1g_ctx* c, size_t& nb, int nv, const double*& base);   // force.cu
 
 static inline unsigned nblk(size_t n, unsigned t) { return (unsigned)((n + t - 1) / t); }
 
@@ -66,6 +67,7 @@ int k_list_build(ls1g_ctx* c) {
 	timer_start(c, LS1G_T_SORT);
 	CUDA_TRY(cudaMemsetAsync(c->d_flags, 0, 3 * sizeof(unsigned long long), c->stream));
 	CUDA_TRY(cudaMemcpyAsync(c->pos_build, c->cur.pos, c->n_slots * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));
+	CUDA_TRY(cudaMemcpyAsync(c->alt.pos, c->cur.pos, c->n_slots * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));   // fused steps ping-pong cur.pos / alt.pos
 	NLArgs a = nl_args(c);
 	static bool battr = false;
 	if (!battr) { CUDA_TRY(cudaFuncSetAttribute(nl_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, NL_BUILD_SMEM(NL_TCAP))); battr = true; }
@@ -77,25 +79,74 @@ int k_list_build(ls1g_ctx* c) {
 }
 
 // count_pairs: also count the pairs inside the cutoff (ls1g_last_pair_count); always on when the potential is shifted
+static int nl_force_attrs() {
+	static bool attr_set = false;
+	if (!attr_set) {
+		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
+		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
+		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
+		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
+		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
+		attr_set = true;
+	}
+	return 0;
+}
+
 int k_forces_list(ls1g_ctx* c, int last_step) {
 	const size_t nb = nl_blocks(c);
 	if (ls1g_ensure_partials(c, nb ? nb : 1, 5)) return 1;
-	static bool attr_set = false;
-	if (!attr_set) {
-		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
-		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
-		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
-		attr_set = true;
-	}
+	if (nl_force_attrs()) return 1;
 	NLArgs a = nl_args(c);
 	a.tcap = c->list_tcap;      // the largest tile of the last build: shared memory sized to what this system needs
 	timer_start(c, LS1G_T_FORCE);
 	// last step of a run: pair statistics + per-molecule virial; other steps: forces + the scalar sums of the step record
-	if (last_step || c->vi_every_step) nl_force_kernel<true, true><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
-	else if (c->shift6_h[0] != 0.) nl_force_kernel<true, false><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
-	else nl_force_kernel<false, false><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
+	if (last_step || c->vi_every_step) nl_force_kernel<true, true, false><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
+	else if (c->shift6_h[0] != 0.) nl_force_kernel<true, false, false><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
+	else nl_force_kernel<false, false, false><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
 	timer_stop(c, LS1G_T_FORCE, 1);
 	if (k_force_finalize(c, nb)) return 1;
+	CUDA_TRY(cudaGetLastError());
+	return 0;
+}
+
+// endTraversal + the kinetic sums of the fused step: partials[nb][8] = u6, -, virial, -, pairs, sum m v^2, N, -
+// out[0..3] = upot, virial, pairs, 0 (as force_finalize_kernel);  out[4..7] = summv2, sumIw2 = 0, N, rotDOF = 0
+__global__ void __launch_bounds__(256) fused_finalize_kernel(const double* __restrict__ partials, size_t nb, double* __restrict__ out) {
+	__shared__ double red[8 * 32];
+	double s[8];
+#pragma unroll
+	for (int k = 0; k < 8; ++k) s[k] = 0.;
+	for (size_t b = threadIdx.x; b < nb; b += blockDim.x)
+#pragma unroll
+		for (int k = 0; k < 8; ++k) s[k] += partials[b * 8 + k];
+	block_sum<8>(s, red);
+	if (threadIdx.x == 0) {
+		out[0] = 0.5 * s[0] / 6.0; out[1] = 0.5 * s[2]; out[2] = 0.5 * s[4]; out[3] = 0.;
+		out[4] = s[5]; out[5] = 0.; out[6] = s[6]; out[7] = 0.;
+	}
+}
+
+// One NVE step of the list loop in ONE pass: forces, post(n), pre(n+1) (nl_force_kernel<.., FUSE>).  Reads c->cur.pos, writes
+// the new owned positions to c->alt.pos (free between sorts) and swaps the two pointers.
+int k_forces_list_fused(ls1g_ctx* c, double dt) {
+	const size_t nb = nl_blocks(c);
+	if (ls1g_ensure_partials(c, nb ? nb : 1, 8)) return 1;
+	if (nl_force_attrs()) return 1;
+	NLArgs a = nl_args(c);
+	a.tcap = c->list_tcap;
+	a.dt = dt; a.dt_half = 0.5 * dt; a.mass = c->comps_h[0].mass;
+	a.vel = c->cur.vel; a.pos_out = c->alt.pos; a.pos_build = c->pos_build;
+	timer_start(c, LS1G_T_FORCE);
+	if (c->shift6_h[0] != 0.) nl_force_kernel<true, false, true><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
+	else nl_force_kernel<false, false, true><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
+	timer_stop(c, LS1G_T_FORCE, 1);
+	std::swap(c->cur.pos, c->alt.pos);
+	timer_start(c, LS1G_T_AUX);
+	size_t nbr = nb; const double* base;
+	const int extra = nb > 2048;
+	if (ls1g_prereduce(c, nbr, 8, base)) return 1;
+	fused_finalize_kernel<<<1, 256, 0, c->stream>>>(base, nbr, c->d_scalars);
+	timer_stop(c, LS1G_T_AUX, 1 + extra);
 	CUDA_TRY(cudaGetLastError());
 	return 0;
 }

@@ -54,6 +54,11 @@ struct NLArgs {
 	double *F, *Vi;
 	double* partials;           // [blocks][5]
 	const unsigned long long* guard; unsigned long long guard_thr;   // skip the launch when *guard > guard_thr (lists expired)
+	// FUSE: leapfrog post(n) + pre(n+1) in the epilogue (NVE steps of ls1g_run)
+	double dt, dt_half, mass;
+	double* vel;                // [slots][3], updated in place
+	double4* pos_out;           // the OTHER position buffer: new positions of the owned molecules (tiles still read pos)
+	const double4* pos_build;   // positions at the last list build
 };
 
 struct NLBlock {
@@ -211,17 +216,32 @@ __global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
 // VI:    accumulate and store the per-molecule virial Vi (FullMolecule::calcFM, FullMolecule.cpp:551-631).  Inside ls1g_run
 //        nothing can read Vi between two steps, so only the last step of a run produces it; the other steps accumulate the
 //        scalar virial sum(f . d) = sum(sc r^2) directly (the record of every step still gets upot and virial).
-template <bool COUNT, bool VI>
+// FUSE:  the Leapfrog half-kick of this step and the half-kick + drift of the next one (integrate_kernel<POST, PRE>,
+//        Leapfrog.cpp:42-68, FullMolecule::upd_postF / upd_preF) run in the epilogue, on the force still in registers:
+//        v += dt/2m F; sum m v^2; v += dt/2m F; r += dt v.  F is not stored, the new position goes to the other position
+//        buffer (other blocks still stage the old one), the displacement since the list build is tracked as in
+//        integrate_kernel.  Saves one pass over r, v, F per step.  partials then hold 8 values per block.
+template <bool COUNT, bool VI, bool FUSE>
 __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 	extern __shared__ __align__(16) double nl_tile[];
 	double* tile = nl_tile;                         // [tcap][3]: x y z of candidate k at tile[3k..3k+2]
 	__shared__ uint32_t s_beg[9]; __shared__ int s_off[10], s_len[9];
-	__shared__ double red[5 * 32];
+	__shared__ double red[(FUSE ? 8 : 5) * 32];
 	const int tid = threadIdx.x;
-	if (a.guard && *a.guard > a.guard_thr) return;      // speculatively enqueued step whose lists turned out expired: the host rebuilds and repeats it
+	// speculatively enqueued step whose lists turned out expired: nothing is computed, the host rebuilds and repeats it
+	if (!FUSE && a.guard && *a.guard > a.guard_thr) return;
 	int x_first = 0, x_last = 0;
 	const NLBlock b = nl_plan(a, s_beg, s_off, s_len, x_first, x_last);
-	double acc[5] = {0., 0., 0., 0., 0.};
+	if (FUSE && a.guard && *a.guard > a.guard_thr) {      // the host swaps the two position buffers after every fused launch: carry the positions over
+		const uint32_t i = b.s0 + tid;
+		if (i < b.s1) a.pos_out[i] = a.pos[i];
+		return;
+	}
+	constexpr int NV = FUSE ? 8 : 5;
+	double acc[NV];
+#pragma unroll
+	for (int k = 0; k < NV; ++k) acc[k] = 0.;
+	double disp2 = 0.;
 	if (b.live) {
 		const uint32_t i = b.s0 + tid;
 		const bool active = i < b.s1;
@@ -300,16 +320,45 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 			Fx *= a.eps24; Fy *= a.eps24; Fz *= a.eps24; Vx *= a.eps24; Vy *= a.eps24; Vz *= a.eps24;
 			u6 = a.eps24 * s6;       // + shift6 * pairs: added by the caller's finalize when the potential is shifted (COUNT)
 			if (COUNT) u6 += a.shift6 * (double)np_i;
-			double* Fp = a.F + 3 * (size_t)i; double* Vp = a.Vi + 3 * (size_t)i;
-			Fp[0] = Fx; Fp[1] = Fy; Fp[2] = Fz;
-			if (VI) { Vp[0] = 0.5 * Vx; Vp[1] = 0.5 * Vy; Vp[2] = 0.5 * Vz; }
+			if (FUSE) {
+				const double m = a.mass;
+				double* vp = a.vel + 3 * (size_t)i;
+				double vx = vp[0], vy = vp[1], vz = vp[2];       // (requesting these before the pair loops costs 16 registers = 2 resident blocks: slower)
+				{	// upd_postF
+					const double dtInv2m = a.dt_half / m;
+					vx += dtInv2m * Fx; vy += dtInv2m * Fy; vz += dtInv2m * Fz;
+					double v2 = 0.;
+					v2 += vx * vx; v2 += vy * vy; v2 += vz * vz;
+					acc[5] = m * v2; acc[6] = 1.0;
+				}
+				{	// upd_preF
+					const double dt_halve = .5 * a.dt, dtInv2m = dt_halve / m;
+					vx += dtInv2m * Fx; vy += dtInv2m * Fy; vz += dtInv2m * Fz;
+					Pi.x += a.dt * vx; Pi.y += a.dt * vy; Pi.z += a.dt * vz;
+				}
+				vp[0] = vx; vp[1] = vy; vp[2] = vz;
+				a.pos_out[i] = Pi;
+				const double4 bp = a.pos_build[i];
+				const double ex = Pi.x - bp.x, ey = Pi.y - bp.y, ez = Pi.z - bp.z;
+				disp2 = ex * ex + ey * ey + ez * ez;
+			} else {
+				double* Fp = a.F + 3 * (size_t)i;
+				Fp[0] = Fx; Fp[1] = Fy; Fp[2] = Fz;
+				if (VI) { double* Vp = a.Vi + 3 * (size_t)i; Vp[0] = 0.5 * Vx; Vp[1] = 0.5 * Vy; Vp[2] = 0.5 * Vz; }
+			}
 			acc[0] = u6; acc[2] = Vx + Vy + Vz; acc[4] = (double)np_i;
 		}
 	}
-	block_sum<5>(acc, red);
+	if (FUSE) {          // displacement criterion of the neighbour lists, as in integrate_kernel
+#pragma unroll
+		for (int o = 16; o > 0; o >>= 1) disp2 = fmax(disp2, __shfl_xor_sync(0xffffffffu, disp2, o));
+		const unsigned long long bits = (unsigned long long)__double_as_longlong(disp2);
+		if ((tid & 31) == 0 && bits > *(volatile unsigned long long*)a.flags) atomicMax(a.flags, bits);
+	}
+	block_sum<NV>(acc, red);
 	if (tid == 0) {
 #pragma unroll
-		for (int k = 0; k < 5; ++k) a.partials[(size_t)blockIdx.x * 5 + k] = acc[k];
+		for (int k = 0; k < NV; ++k) a.partials[(size_t)blockIdx.x * NV + k] = acc[k];
 	}
 }
 

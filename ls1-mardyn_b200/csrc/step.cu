@@ -100,6 +100,7 @@ int nl_applicable(const ls1g_ctx* c);
 int nl_set_bin_grid(ls1g_ctx* c, int list_mode);
 int k_list_build(ls1g_ctx* c);
 int k_forces_list(ls1g_ctx* c, int count_pairs);
+int k_forces_list_fused(ls1g_ctx* c, double dt);
 int k_halo_refresh(ls1g_ctx* c);
 
 // Neighbour-list steps of ls1g_run (lists.cuh).  On entry the pre-kick of step 0 is done.  Runs steps [0, n_steps) unless
@@ -133,6 +134,9 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 	c->disp_thr2 = (0.4995 * c->skin) * (0.4995 * c->skin);    // lists stay exact while no molecule moved more than skin/2
 	c->guard_on = 0;
 	const bool dbg = getenv("LS1G_DEBUG") != nullptr;
+	// the integrator is fused into the force kernel on NVE steps (LS1G_FUSE=0 keeps the separate integrate kernel)
+	const char* fe = getenv("LS1G_FUSE");
+	const bool fuse_nve = !thermo && !c->vi_every_step && !(fe && atoi(fe) == 0);
 	auto expired = [&](int ring) { double d2; memcpy(&d2, c->h_flags + 4 + ring, sizeof(double)); return d2 > c->disp_thr2; };
 	if (c->in_list_mode) {       // continuing the previous ls1g_run: the pre-kick above was tracked; rebuild only if the lists expired
 		if (flag_snapshot(c, 0) || sync_check(c, "ls1g_run (displacement)")) return 1;
@@ -203,10 +207,16 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 			}
 			const double t1 = now();
 			c->guard_on = built ? 0 : 1;
-			if (!rc) rc = k_forces_list(c, s + 1 == n_steps);      // pair statistics + per-molecule virial only for the last step
-			if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s, c->d_scalars, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
-			if (!rc) rc = k_post_pre(c, dt, 1, s + 1 < n_steps, thermo, target_T);
-			if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s + 4, c->d_scalars + 4, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
+			if (fuse_nve && s + 1 < n_steps) {
+				// NVE step that is not the last of the run: forces + post(s) + pre(s + 1) in one kernel
+				rc = k_forces_list_fused(c, dt);
+				if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s, c->d_scalars, 8 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
+			} else {
+				if (!rc) rc = k_forces_list(c, s + 1 == n_steps);      // pair statistics + per-molecule virial only for the last step
+				if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s, c->d_scalars, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
+				if (!rc) rc = k_post_pre(c, dt, 1, s + 1 < n_steps, thermo, target_T);
+				if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s + 4, c->d_scalars + 4, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
+			}
 			c->guard_on = 0;
 			if (!rc && s + 1 < n_steps) rc = flag_snapshot(c, s % NL_RING);      // decides step s + 1
 			const double t2 = now();
