@@ -10,8 +10,12 @@ is DomainDecomposition's block grid, halo + leaving exchange over NCCL).  One st
 leapfrog pre -> wrap/halo/sort -> force pass (+calcFM, upot, virial) -> leapfrog post + kinetic sums.
 MUPS is the reference's own definition, N_global * steps / time of the loop (src/MarDyn.cpp:264-266).
 
-Prints ONE JSON line (rank 0).  `value`: device-resident loop, inputs in HBM.  `e2e`: the same step driven through the
-public API with HOST (pinned) buffers: every step uploads id,cid,r,v,F and downloads id,r,v,F."""
+Prints ONE JSON line (rank 0).  `value`: device-resident loop, inputs in HBM.  `e2e` (N=1): the reference-facing drop-in end
+to end - ls1-MarDyn's own executable and unmodified time loop with <datastructure type="GpuLinkedCells"> (MarDynGpu,
+ls1-mardyn_b200/host/) on the same XML the reference arm runs: host Molecule objects -> device, K steps with the step
+scalars read back every step, full state back into host Molecule objects; its `c_abi_full_state_roundtrip_every_step` entry
+(and `e2e` itself at N>1, where the MPI-less reference executable cannot run) is the C-ABI worst case: every step uploads
+id,cid,r,v,F from pinned host memory and downloads id,r,v,F."""
 import argparse
 import importlib
 import json
@@ -173,7 +177,7 @@ MARDYN_XML = """<?xml version='1.0' encoding='UTF-8'?>
 <mardyn version="20100525">
   <refunits type="SI"><length unit="nm">0.1</length><mass unit="u">1</mass><energy unit="K">1</energy></refunits>
   <simulation type="MD">
-    <integrator type="Leapfrog"><timestep unit="reduced">{dt}</timestep></integrator>
+    <integrator type="{integrator}"><timestep unit="reduced">{dt}</timestep></integrator>
     <run><currenttime>0</currenttime><production><steps>{steps}</steps></production></run>
     <ensemble type="NVT">
       <temperature unit="reduced">{temp}</temperature>
@@ -202,7 +206,7 @@ MARDYN_XML = """<?xml version='1.0' encoding='UTF-8'?>
     </ensemble>
     <algorithm>
       <parallelisation type="DomainDecomposition"></parallelisation>
-      <datastructure type="LinkedCells"><cellsInCutoffRadius>1</cellsInCutoffRadius></datastructure>
+      <datastructure type="{container}"><cellsInCutoffRadius>1</cellsInCutoffRadius></datastructure>
       <cutoffs type="CenterOfMass"><defaultCutoff unit="reduced">{rc}</defaultCutoff><radiusLJ unit="reduced">{rc}</radiusLJ></cutoffs>
       <electrostatic type="ReactionField"><epsilon>1.0e+10</epsilon></electrostatic>
     </algorithm>
@@ -269,7 +273,7 @@ def run_reference_sample(sample_cells, steps, threads, exe=None):
     with tempfile.TemporaryDirectory() as td:
         cfg = os.path.join(td, "cfg.xml")
         with open(cfg, "w") as f:
-            f.write(MARDYN_XML.format(dt=DT, steps=steps, temp=TEMP, L=repr(L), rho=RHO, rc=RC))
+            f.write(MARDYN_XML.format(dt=DT, steps=steps, temp=TEMP, L=repr(L), rho=RHO, rc=RC, integrator="Leapfrog", container="LinkedCells"))
         env = dict(os.environ, OMP_NUM_THREADS=str(threads), OMP_PROC_BIND="close", OMP_PLACES="cores")
         t0 = time.time()
         p = subprocess.run([exe, cfg, "--steps", str(steps)], cwd=td, env=env, capture_output=True, text=True, timeout=3000)
@@ -283,6 +287,41 @@ def run_reference_sample(sample_cells, steps, threads, exe=None):
     vec = re.search(r"VectorizedCellProcessor: using (\S+) intrinsics", out)
     return dict(mmups=n * steps / loop_s / 1e6, n=n, loop_s=loop_s, force_s=float(m.group(1)) if m else None,
                 binary=os.path.basename(exe), simd=vec.group(1) if vec else "?", wall_s=wall)
+
+
+MARDYN_GPU = os.path.join(ROOT, "ls1-mardyn_b200", "host", "_build", "MarDynGpu")
+
+
+def run_mardyn_gpu(cells, steps, threads, timeout=1500):
+    """The reference-facing drop-in, end to end: ls1-MarDyn's own executable and unmodified time loop with
+    <datastructure type="GpuLinkedCells"> + <integrator type="GpuLeapfrog"> (ls1-mardyn_b200/host/), on the same XML the
+    reference arm runs (its MultiObjectGenerator fcc lattice, NVT).  HOST buffers on both sides: the molecules start as the
+    reference's host Molecule objects (uploaded once, in prepare_start) and end as host Molecule objects again (full-state
+    mirror download at the last step, inside the loop timer).  Returns dict(mmups over upload + loop, ...) or None when the
+    binary was not built (needs the reference tree at build time)."""
+    if not (os.path.exists(MARDYN_GPU) and os.access(MARDYN_GPU, os.X_OK)):
+        return None
+    a = (4.0 / RHO) ** (1.0 / 3.0)
+    L = cells * a
+    with tempfile.TemporaryDirectory() as td:
+        cfg = os.path.join(td, "cfg.xml")
+        with open(cfg, "w") as f:
+            f.write(MARDYN_XML.format(dt=DT, steps=steps, temp=TEMP, L=repr(L), rho=RHO, rc=RC, integrator="GpuLeapfrog", container="GpuLinkedCells"))
+        env = dict(os.environ, OMP_NUM_THREADS=str(threads), OMP_PROC_BIND="close", OMP_PLACES="cores")
+        t0 = time.time()
+        p = subprocess.run([MARDYN_GPU, cfg, "--steps", str(steps), "--final-checkpoint=0"], cwd=td, env=env, capture_output=True, text=True, timeout=timeout)
+        wall = time.time() - t0
+    out = p.stdout + p.stderr
+    if p.returncode != 0 or "Exit code would have been" in out:
+        raise RuntimeError("MarDynGpu failed (%d): %s" % (p.returncode, out[-2000:]))
+    n = int(re.search(r"globally inserted molecules:\s*(\d+)", out).group(1))
+    loop_s = float(re.search(r"Computation in main loop took:\s*([0-9.eE+-]+)", out).group(1))
+    g = re.search(r"GpuLinkedCells: (\d+) device steps took ([0-9.eE+-]+) s; upload ([0-9.eE+-]+) s \((\d+) B\); (\d+) host mirror download\(s\) took ([0-9.eE+-]+) s \((\d+) B\); context creation ([0-9.eE+-]+) s", out)
+    dev_s, up_s, up_b, mirrors, mir_s, mir_b = float(g.group(2)), float(g.group(3)), int(g.group(4)), int(g.group(5)), float(g.group(6)), int(g.group(7))
+    ctx_s = float(g.group(8))
+    total = loop_s + up_s
+    return dict(mmups=n * steps / total / 1e6, n=n, steps=steps, loop_s=loop_s, upload_s=up_s, device_s=dev_s, mirror_s=mir_s, mirrors=mirrors,
+                h2d_bytes=up_b, d2h_bytes=mir_b + 48 * steps, wall_s=wall, context_s=ctx_s, loop_only_mmups=n * steps / loop_s / 1e6)
 
 
 def run_oracle_port_sample(sample_cells, steps):
@@ -470,12 +509,16 @@ def main_b200(args):
     achieved = flops / (force_ms * 1e-3) / 1e12 if force_ms > 0 else 0.0
     launches = sum(t["launches"] for t in tm.values())
 
-    # ---- e2e: the same step through the public API with host buffers ---------------------------------------------
-    def e2e_step(n):
-        c.add_particles(host["id"][:n], host["cid"][:n], host["r"][:n], host["v"][:n])
-        c.set_forces(host["F"][:n])
-        c.run(1, DT, records=True)
-        out = c.download(("id", "r", "v", "F"), out=host)
+    # ---- e2e, C ABI with host buffers: every step moves the FULL state host -> device -> host (worst case of the boundary) ----
+    tparts = np.zeros(4)
+    def e2e_step(n, acc=None):
+        t = [time.perf_counter()]
+        c.add_particles(host["id"][:n], host["cid"][:n], host["r"][:n], host["v"][:n]); t.append(time.perf_counter())
+        c.set_forces(host["F"][:n]); t.append(time.perf_counter())
+        c.run(1, DT, records=True); t.append(time.perf_counter())
+        out = c.download(("id", "r", "v", "F"), out=host); t.append(time.perf_counter())
+        if acc is not None:
+            acc += np.diff(t)
         return len(out["id"])
     c.delete_outer_particles()
     n_cur = len(c.download(("id", "r", "v", "F"), out=host)["id"])
@@ -488,7 +531,7 @@ def main_b200(args):
     e0.record(stream)
     for _ in range(k_e2e):
         h2d += n_cur * (8 + 4 + 24 + 24 + 24)
-        n_cur = e2e_step(n_cur)
+        n_cur = e2e_step(n_cur, tparts)
         d2h += n_cur * (8 + 24 + 24 + 24) + 48
     e1.record(stream)
     barrier()
@@ -497,6 +540,29 @@ def main_b200(args):
     if world > 1:
         dist.all_reduce(mt, op=dist.ReduceOp.MAX)
     e2e_val = n_global * k_e2e / (float(mt.item()) * 1e-3) / 1e6
+    roundtrip = {"value": round(e2e_val, 2), "unit": "MMUPS", "h2d_bytes_per_step": h2d // k_e2e, "d2h_bytes_per_step": d2h // k_e2e, "steps": k_e2e,
+                 "ms_per_step": {k: round(1e3 * v / k_e2e, 2) for k, v in zip(("upload", "upload_forces", "run_1_step", "download"), tparts)},
+                 "what": "C ABI, full state both ways EVERY step: add_particles(id,cid,r,v)+set_forces(F) from pinned host, ls1g_run(1), download(id,r,v,F) to pinned host"}
+    e2e = dict(roundtrip)
+    c.close()
+
+    # ---- e2e, the reference-facing drop-in: ls1-MarDyn's own executable + time loop with the GpuLinkedCells container ----------
+    md = None
+    if rank == 0 and world == 1 and not args.no_mardyn_gpu:
+        try:
+            md = run_mardyn_gpu(args.e2e_cells or args.cells, args.steps, host_cores())
+        except Exception as ex:                                  # reported, never silently replaced
+            e2e["mardyn_gpu_error"] = str(ex)[-400:]
+    if md is not None:
+        e2e = {"value": round(md["mmups"], 2), "unit": "MMUPS", "h2d_bytes_per_step": md["h2d_bytes"] // md["steps"],
+               "d2h_bytes_per_step": md["d2h_bytes"] // md["steps"], "steps": md["steps"], "n_molecules": md["n"],
+               "what": "MarDynGpu = the reference's executable and unmodified Simulation::simulate loop with <datastructure type=GpuLinkedCells> + "
+                       "<integrator type=GpuLeapfrog> (ls1-mardyn_b200/host/): host Molecule objects -> device (once) -> %d steps, scalars to Domain every step "
+                       "-> full state back into host Molecule objects at the last step; time = upload + the reference's own loop timer" % md["steps"],
+               "seconds": {"upload": round(md["upload_s"], 3), "loop": round(md["loop_s"], 3), "of_loop_device_calls": round(md["device_s"], 3),
+                           "of_loop_final_mirror": round(md["mirror_s"], 3), "process_wall": round(md["wall_s"], 1),
+                           "cuda_context_creation_not_counted": round(md["context_s"], 3)},
+               "loop_only_mmups": round(md["loop_only_mmups"], 2), "c_abi_full_state_roundtrip_every_step": roundtrip}
 
     if rank == 0:
         cb = cpu_baseline() if (world == 1 and not args.no_cpu_baseline) else None
@@ -508,8 +574,7 @@ def main_b200(args):
                            "n_molecules": n_global, "rank_grid": shard["grid"], "cells_per_dim": cpd,
                            "l2": "inputs larger than L2 (pos+vel+F = %.0f MB per GPU)" % (n_local * 80 / 1e6),
                            "nve_rel_energy_drift_over_timed_steps": drift, "upot_per_molecule_t0": u0 / max(n_local, 1)},
-                "e2e": {"value": round(e2e_val, 2), "unit": "MMUPS", "h2d_bytes_per_step": h2d // k_e2e, "d2h_bytes_per_step": d2h // k_e2e,
-                        "steps": k_e2e, "what": "per step: add_particles(id,cid,r,v)+set_forces(F) from pinned host, ls1g_run(1), download(id,r,v,F) to pinned host"},
+                "e2e": e2e,
                 "gpu_launches": int(launches),
                 "roofline": {"bound": "fp64", "kernel": "nl_force_kernel (lists.cuh)", "achieved": round(achieved, 3), "peak": round(peak, 3), "unit": "TFLOP/s",
                              "frac": round(achieved / peak, 4) if peak > 0 else None, "traffic": traffic, "traffic_source": traffic_src,
@@ -523,7 +588,6 @@ def main_b200(args):
         if cb is not None:
             line["cpu_baseline"] = cb
         print(json.dumps(line), flush=True)
-    c.close()
     if world > 1:
         dist.destroy_process_group()
     return 0
@@ -539,6 +603,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=5)
     ap.add_argument("--ref-cells", type=int, default=64, help="fcc unit cells per dimension of the reference arm's sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-mardyn-gpu", action="store_true", help="skip the MarDynGpu end-to-end arm (e2e then = the C-ABI round trip)")
+    ap.add_argument("--e2e-cells", type=int, default=0, help="fcc unit cells per dimension of the MarDynGpu end-to-end run (0 = --cells)")
     args = ap.parse_args()
     if args.impl == "reference":
         return main_reference(args)

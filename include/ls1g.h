@@ -153,6 +153,10 @@ int ls1g_integrate_post(ls1g_ctx* ctx, double dt_half, double* summv2, double* s
                         uint64_t* n, uint64_t* rot_dof);
 /* replaces: VelocityScalingThermostat::apply (VelocityScalingThermostat.cpp:45-80), global betas */
 int ls1g_scale(ls1g_ctx* ctx, double beta_trans, double beta_rot);
+/* replaces: the per-molecule "explosion heuristics" of Domain::calculateGlobalValues (Domain.cpp:254-295), which the reference
+ * runs when a global beta falls below MIN_BETA (Domain.h:20): molecules with U_trans > limit_trans_energy (= KINLIMIT_PER_T * T)
+ * get v and F scaled by sqrt(limit / U_trans), molecules with U_rot > 3 * rotDOF * temperature get D and M scaled likewise. */
+int ls1g_selective_thermostat(ls1g_ctx* ctx, double limit_trans_energy, double temperature);
 
 /* Device-resident time loop: n_steps x { integrate_pre, update+exchange, traverse, delete_outer,
  * integrate_post, [thermostat] } in the order of Simulation::simulate (Simulation.cpp:979-1177).

@@ -15,7 +15,7 @@ EXPORTS = [
     "ls1g_last_error", "ls1g_version", "ls1g_create", "ls1g_destroy", "ls1g_set_components", "ls1g_get_grid",
     "ls1g_cell_index_of_points_host", "ls1g_cell_index_of_points", "ls1g_debug_cell_pairs", "ls1g_upload",
     "ls1g_upload_forces", "ls1g_stream", "ls1g_count", "ls1g_download", "ls1g_update", "ls1g_exchange", "ls1g_traverse", "ls1g_delete_outer",
-    "ls1g_integrate_pre", "ls1g_integrate_post", "ls1g_scale", "ls1g_run", "ls1g_decomp_box", "ls1g_decomp_grid",
+    "ls1g_integrate_pre", "ls1g_integrate_post", "ls1g_scale", "ls1g_selective_thermostat", "ls1g_run", "ls1g_decomp_box", "ls1g_decomp_grid",
     "ls1g_comm_unique_id", "ls1g_comm_init", "ls1g_allreduce_sum", "ls1g_comm_init_local", "ls1g_exchange_group",
     "ls1g_timers", "ls1g_measure_fp64_peak", "ls1g_last_pair_count",
 ]
@@ -312,6 +312,10 @@ class Container:
 
     def scale(self, beta_trans, beta_rot=1.0):
         _chk(lib().ls1g_scale(self._ctx, C.c_double(beta_trans), C.c_double(beta_rot)))
+
+    def selective_thermostat(self, limit_trans_energy, temperature):
+        """Domain::calculateGlobalValues explosion heuristics (Domain.cpp:254-295): cap U_trans / U_rot per molecule"""
+        _chk(lib().ls1g_selective_thermostat(self._ctx, C.c_double(limit_trans_energy), C.c_double(temperature)))
 
     def run(self, n_steps, dt, target_temperature=0.0, records=True):
         """device-resident time loop; returns array [n_steps][6]: upot virial summv2 sumIw2 N rotDOF"""

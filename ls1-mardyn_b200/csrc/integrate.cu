@@ -158,6 +158,37 @@ __global__ void __launch_bounds__(INT_THREADS) scale_kernel(size_t n, const uint
 	for (int d = 0; d < 3; ++d) { vel[3 * i + d] *= bt; if (L) L[3 * i + d] *= br; }
 }
 
+// Selective thermostat of the reference's "explosion heuristics" (Domain::calculateGlobalValues, Domain.cpp:254-295): a molecule
+// whose translational energy exceeds limit_energy gets v and F scaled by sqrt(limit/U_trans); one whose rotational energy
+// (FullMolecule::U_rot, FullMolecule.cpp:392-400) exceeds 3 * rotDOF * Ti gets D and M scaled by sqrt(limit/U_rot).
+__global__ void __launch_bounds__(INT_THREADS) selective_kernel(size_t n, const uint32_t* __restrict__ cell, const double4* __restrict__ pos,
+                                                                 double* vel, double* F, const double4* __restrict__ q, double* L, double* M,
+                                                                 const CompDev* __restrict__ comps, double limit_energy, double Ti) {
+	size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (i >= n || (cell[i] & HALO_FLAG)) return;
+	const CompDev& cp = comps[pos_cid(pos[i])];
+	const double v0 = vel[3 * i], v1 = vel[3 * i + 1], v2 = vel[3 * i + 2];
+	const double Utrans = 0.5 * cp.mass * (v0 * v0 + v1 * v1 + v2 * v2);
+	if (Utrans > limit_energy) {
+		const double vcorr = sqrt(limit_energy / Utrans);
+#pragma unroll
+		for (int d = 0; d < 3; ++d) { vel[3 * i + d] *= vcorr; F[3 * i + d] *= vcorr; }
+	}
+	if (q && cp.rot_dof > 0) {
+		const double limit_rot = 3.0 * cp.rot_dof * Ti;
+		double Lm[3] = {L[3 * i], L[3 * i + 1], L[3 * i + 2]}, w[3], Iw2 = 0.;
+		quat_rotateinv(q[i], Lm, w);
+#pragma unroll
+		for (int d = 0; d < 3; ++d) { w[d] *= cp.invI[d]; Iw2 += cp.I[d] * w[d] * w[d]; }
+		const double Urot = 0.5 * Iw2;
+		if (Urot > limit_rot) {
+			const double Dcorr = sqrt(limit_rot / Urot);
+#pragma unroll
+			for (int d = 0; d < 3; ++d) { L[3 * i + d] *= Dcorr; M[3 * i + d] *= Dcorr; }
+		}
+	}
+}
+
 int ls1g_prereduce(ls1g_ctx* c, size_t& nb, int nv, const double*& base);   // force.cu
 
 // ------------------------------------------------------------------------------------------------
@@ -196,6 +227,16 @@ int k_scale(ls1g_ctx* c, double bt, double br) {
 	timer_start(c, LS1G_T_INTEGRATE);
 	scale_kernel<<<nblk(c->n_slots, INT_THREADS), INT_THREADS, 0, c->stream>>>(c->n_slots, c->cur.cell, c->cur.vel,
 	                                                                         c->has_rot ? c->cur.L : nullptr, bt, br);
+	CUDA_TRY(cudaGetLastError());
+	timer_stop(c, LS1G_T_INTEGRATE, 1);
+	return 0;
+}
+
+int k_selective(ls1g_ctx* c, double limit_energy, double Ti) {
+	if (c->n_slots == 0) return 0;
+	timer_start(c, LS1G_T_INTEGRATE);
+	selective_kernel<<<nblk(c->n_slots, INT_THREADS), INT_THREADS, 0, c->stream>>>(c->n_slots, c->cur.cell, c->cur.pos, c->cur.vel, c->F,
+	                                                                             c->has_rot ? c->cur.q : nullptr, c->cur.L, c->M, c->comps, limit_energy, Ti);
 	CUDA_TRY(cudaGetLastError());
 	timer_stop(c, LS1G_T_INTEGRATE, 1);
 	return 0;

@@ -91,9 +91,18 @@ extern "C" int ls1g_integrate_post(ls1g_ctx* c, double dt_half, double* summv2, 
 }
 
 extern "C" int ls1g_scale(ls1g_ctx* c, double bt, double br) {
-	NEED_REF(c);
+	NEED(c);      // velocities only: valid in the frozen neighbour-list layout too (no ls1g_nl_leave)
 	if (k_scale(c, bt, br)) return 1;
 	return sync_check(c, "ls1g_scale");
+}
+
+// Domain::calculateGlobalValues explosion heuristics (Domain.cpp:254-295)
+int k_selective(ls1g_ctx* c, double limit_energy, double Ti);
+extern "C" int ls1g_selective_thermostat(ls1g_ctx* c, double limit_trans_energy, double temperature) {
+	NEED(c);      // v, F, D, M only: valid in the frozen neighbour-list layout too
+	if (!c->forces_valid) LS1G_FAIL("ls1g_selective_thermostat: forces missing (F and M are scaled together with v and D)");
+	if (k_selective(c, limit_trans_energy, temperature)) return 1;
+	return sync_check(c, "ls1g_selective_thermostat");
 }
 
 int nl_applicable(const ls1g_ctx* c);

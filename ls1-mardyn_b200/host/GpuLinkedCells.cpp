@@ -1,0 +1,454 @@
+/*
+ * GpuLinkedCells.cpp — see GpuLinkedCells.h.  Every device operation is one call of the C ABI (include/ls1g.h); this file
+ * only converts between the reference's host objects (Molecule, Component, Domain) and plain arrays.
+ */
+#include "GpuLinkedCells.h"
+
+#include "Domain.h"
+#include "Simulation.h"
+#include "ensemble/EnsembleBase.h"
+#include "molecules/Component.h"
+#include "molecules/Molecule.h"
+#include "particleContainer/adapter/CellProcessor.h"
+#include "particleContainer/adapter/LegacyCellProcessor.h"
+#include "particleContainer/adapter/VectorizedCellProcessor.h"
+#include "utils/Logger.h"
+#include "utils/xmlfileUnits.h"
+
+extern "C" {
+#include "ls1g.h"
+}
+
+#include <chrono>
+#include <cmath>
+#include <string>
+
+#if defined(_OPENMP)
+#include <omp.h>
+#endif
+
+using Log::global_log;
+
+namespace {
+double wall() {
+	return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+}  // namespace
+
+GpuLinkedCells::GpuLinkedCells() : LinkedCells() {}
+
+GpuLinkedCells::~GpuLinkedCells() {
+	// no logging here: main deletes global_log before the Simulation object (and with it this container) is destroyed
+	if (_ctx != nullptr) ls1g_destroy(_ctx);
+}
+
+void GpuLinkedCells::printSummary() const {
+	global_log->info() << "GpuLinkedCells: " << _steps << " device steps took " << _tDevice << " s; upload "
+	                   << _tUpload << " s (" << _bytesUp << " B); " << _mirrors << " host mirror download(s) took "
+	                   << _tMirror << " s (" << _bytesDown << " B); context creation " << _tContext << " s; selective thermostat applied "
+	                   << _selective << " time(s)" << std::endl;
+}
+
+void GpuLinkedCells::fail(const char* what) const {
+	global_log->error_always_output() << "GpuLinkedCells: " << what << ": " << ls1g_last_error() << std::endl;
+	Simulation::exit(1);      // the reference's own fatal path (LinkedCells.cpp:101,162,239,549)
+	std::abort();
+}
+
+void GpuLinkedCells::chk(int rc, const char* what) const {
+	if (rc != 0) fail(what);
+}
+
+void GpuLinkedCells::readXML(XMLfileUnits& xmlconfig) {
+	LinkedCells::readXML(xmlconfig);
+	if (xmlconfig.getNodeValue_int("cellsInCutoffRadius", 1) != 1) {
+		global_log->error_always_output() << "GpuLinkedCells: cellsInCutoffRadius must be 1" << std::endl;
+		Simulation::exit(1);
+	}
+	std::string mode = "fused";
+	xmlconfig.getNodeValue("mode", mode);
+	if (mode == "fused") {
+		_mode = FUSED;
+	} else if (mode == "operators") {
+		_mode = OPERATORS;
+	} else {
+		global_log->error_always_output() << "GpuLinkedCells: unknown mode " << mode << " (fused | operators)" << std::endl;
+		Simulation::exit(1);
+	}
+	_mirrorFrequency = static_cast<unsigned long>(xmlconfig.getNodeValue_long("mirrorfrequency", 0));
+	_device = xmlconfig.getNodeValue_int("device", 0);
+	global_log->info() << "GpuLinkedCells: mode " << mode << ", mirror frequency " << _mirrorFrequency << ", device "
+	                   << _device << std::endl;
+}
+
+bool GpuLinkedCells::rebuild(double bBoxMin[3], double bBoxMax[3]) {
+	if (_ctx != nullptr) {      // new bounding box: the device context is rebuilt at its next use
+		if (_devicePhase && !_mirrorValid) downloadMirror();
+		ls1g_destroy(_ctx);
+		_ctx = nullptr;
+		_deviceLoaded = false;
+		_devicePhase = false;
+		_mirrorValid = false;
+	}
+	return LinkedCells::rebuild(bBoxMin, bBoxMax);
+}
+
+// The context is created at first use, not in rebuild(): components, mixing coefficients and the reaction-field epsilon
+// are only complete once Simulation::readXML has finished.
+void GpuLinkedCells::ensureContext() {
+	if (_ctx != nullptr) return;
+	const double t0 = wall();
+	Domain* domain = global_simulation->getDomain();
+	// component-wise and directed-velocity thermostats act per molecule on the host (VelocityScalingThermostat.cpp:45-80)
+	if (domain->severalThermostats() || domain->thermostatIsUndirected(0)) {
+		global_log->error_always_output() << "GpuLinkedCells: component-wise and undirected thermostats are not supported" << std::endl;
+		Simulation::exit(1);
+	}
+	ls1g_config cfg{};
+	cfg.device = _device;
+	for (int d = 0; d < 3; ++d) {
+		cfg.box_min[d] = getBoundingBoxMin(d);
+		cfg.box_max[d] = getBoundingBoxMax(d);
+		cfg.global_length[d] = domain->getGlobalLength(d);
+		cfg.rank_grid[d] = 1;
+		cfg.rank_coords[d] = 0;
+	}
+	cfg.cutoff = getCutoff();
+	cfg.lj_cutoff = global_simulation->getLJCutoff();
+	cfg.eps_rf = domain->getepsilonRF();
+	cfg.grid_mode = LS1G_GRID_REBUILD;
+	cfg.capacity = 0;
+	chk(ls1g_create(&cfg, &_ctx), "ls1g_create");
+	uploadComponents();
+	int cpd[3];
+	double len[3];
+	chk(ls1g_get_grid(_ctx, cpd, len), "ls1g_get_grid");
+	const double* mine = getCellLength();
+	for (int d = 0; d < 3; ++d) {
+		if (len[d] != mine[d]) {
+			global_log->error_always_output() << "GpuLinkedCells: device cell grid differs from LinkedCells::rebuild in dimension "
+			                                  << d << " (" << len[d] << " vs " << mine[d] << ")" << std::endl;
+			Simulation::exit(1);
+		}
+	}
+	global_log->info() << "GpuLinkedCells: device context created, " << cpd[0] << " x " << cpd[1] << " x " << cpd[2]
+	                   << " cells" << std::endl;
+	_tContext += wall() - t0;
+}
+
+// Component tables (src/molecules/Component.h, Site.h) and Domain::getmixcoeff -> ls1g_set_components
+void GpuLinkedCells::uploadComponents() {
+	std::vector<Component>& comps = *global_simulation->getEnsemble()->getComponents();
+	const size_t nc = comps.size();
+	std::vector<std::vector<double>> lj(nc), ch(nc), di(nc), qu(nc);
+	std::vector<ls1g_component> rows(nc);
+	for (size_t k = 0; k < nc; ++k) {
+		const Component& c = comps[k];
+		for (unsigned i = 0; i < c.numLJcenters(); ++i) {
+			const LJcenter& s = c.ljcenter(i);
+			lj[k].insert(lj[k].end(), {s.rx(), s.ry(), s.rz(), s.m(), s.eps(), s.sigma(), s.shift6()});
+		}
+		for (unsigned i = 0; i < c.numCharges(); ++i) {
+			const Charge& s = c.charge(i);
+			ch[k].insert(ch[k].end(), {s.rx(), s.ry(), s.rz(), s.m(), s.q()});
+		}
+		for (unsigned i = 0; i < c.numDipoles(); ++i) {
+			const Dipole& s = c.dipole(i);
+			di[k].insert(di[k].end(), {s.rx(), s.ry(), s.rz(), s.ex(), s.ey(), s.ez(), s.absMy()});
+		}
+		for (unsigned i = 0; i < c.numQuadrupoles(); ++i) {
+			const Quadrupole& s = c.quadrupole(i);
+			qu[k].insert(qu[k].end(), {s.rx(), s.ry(), s.rz(), s.ex(), s.ey(), s.ez(), s.absQ()});
+		}
+		ls1g_component& r = rows[k];
+		r.mass = c.m();
+		r.inertia[0] = c.I11();
+		r.inertia[1] = c.I22();
+		r.inertia[2] = c.I33();
+		r.rot_dof = static_cast<int>(c.getRotationalDegreesOfFreedom());
+		r.n_lj = static_cast<int>(c.numLJcenters());
+		r.n_charge = static_cast<int>(c.numCharges());
+		r.n_dipole = static_cast<int>(c.numDipoles());
+		r.n_quadrupole = static_cast<int>(c.numQuadrupoles());
+		r.lj = lj[k].empty() ? nullptr : lj[k].data();
+		r.charge = ch[k].empty() ? nullptr : ch[k].data();
+		r.dipole = di[k].empty() ? nullptr : di[k].data();
+		r.quadrupole = qu[k].empty() ? nullptr : qu[k].data();
+	}
+	std::vector<double>& mix = global_simulation->getDomain()->getmixcoeff();
+	chk(ls1g_set_components(_ctx, static_cast<int>(nc), rows.data(), mix.empty() ? nullptr : mix.data(),
+	                        static_cast<int>(mix.size())),
+	    "ls1g_set_components");
+}
+
+// host cells (owned molecules) -> ls1g_upload.  The device orders molecules by (cell, id), so the gather order is free.
+void GpuLinkedCells::uploadFromHost() {
+	ensureContext();
+	const double t0 = wall();
+	std::vector<uint64_t> id;
+	std::vector<uint32_t> cid;
+	std::vector<double> r, v, q, L;
+#if defined(_OPENMP)
+#pragma omp parallel
+#endif
+	{
+		std::vector<uint64_t> id_t;
+		std::vector<uint32_t> cid_t;
+		std::vector<double> r_t, v_t, q_t, L_t;
+		for (auto m = LinkedCells::iterator(ParticleIterator::ONLY_INNER_AND_BOUNDARY); m.isValid(); ++m) {
+			id_t.push_back(m->getID());
+			cid_t.push_back(m->componentid());
+			for (int d = 0; d < 3; ++d) {
+				r_t.push_back(m->r(d));
+				v_t.push_back(m->v(d));
+				L_t.push_back(m->D(d));
+			}
+			const Quaternion& qq = m->q();
+			q_t.insert(q_t.end(), {qq.qw(), qq.qx(), qq.qy(), qq.qz()});
+		}
+#if defined(_OPENMP)
+#pragma omp critical
+#endif
+		{
+			id.insert(id.end(), id_t.begin(), id_t.end());
+			cid.insert(cid.end(), cid_t.begin(), cid_t.end());
+			r.insert(r.end(), r_t.begin(), r_t.end());
+			v.insert(v.end(), v_t.begin(), v_t.end());
+			q.insert(q.end(), q_t.begin(), q_t.end());
+			L.insert(L.end(), L_t.begin(), L_t.end());
+		}
+	}
+	const size_t n = id.size();
+	chk(ls1g_upload(_ctx, n, id.data(), cid.data(), r.data(), v.data(), q.data(), L.data()), "ls1g_upload");
+	_bytesUp += n * (8 + 4 + 13 * 8);
+	_deviceLoaded = true;
+	_tUpload += wall() - t0;
+}
+
+void GpuLinkedCells::update() {
+	if (!_devicePhase) {
+		LinkedCells::update();
+		return;
+	}
+	if (_mode == OPERATORS) {
+		const double t0 = wall();
+		// wrap leaving molecules, create the periodic halo images, re-sort: LinkedCells::update +
+		// DomainDecompBase::exchangeMolecules in one call (the host-side exchange that follows finds empty cells)
+		chk(ls1g_exchange(_ctx), "ls1g_exchange");
+		_tDevice += wall() - t0;
+	}
+}
+
+void GpuLinkedCells::updateMoleculeCaches() {
+	// host phase: the reference's own SoA caches, so that host passes over the molecules (Simulation::updateForces ->
+	// calcFM, plugins) stay valid; device phase: site positions are computed inside the force kernels
+	if (!_devicePhase) LinkedCells::updateMoleculeCaches();
+}
+
+void GpuLinkedCells::traverseCells(CellProcessor& cellProcessor) {
+	const bool forceProcessor = dynamic_cast<VectorizedCellProcessor*>(&cellProcessor) != nullptr ||
+	                            dynamic_cast<LegacyCellProcessor*>(&cellProcessor) != nullptr;
+	if (!forceProcessor) {
+		// counting / sampling processors (FlopCounter, RDFCellProcessor, ...) run on the host cells
+		if (_devicePhase && !_mirrorValid) {
+			global_log->error_always_output() << "GpuLinkedCells: only the force cell processors run on the device; other cell "
+			                                     "processors need the host cells (host phase or a mirror step)" << std::endl;
+			Simulation::exit(1);
+		}
+		LinkedCells::traverseCells(cellProcessor);
+		return;
+	}
+	Domain* domain = global_simulation->getDomain();
+	double upot = 0., virial = 0.;
+	if (!_devicePhase) {
+		// prepare_start (Simulation.cpp:813-844): the host cells are authoritative; the device gets a copy and keeps F
+		uploadFromHost();
+		const double t0 = wall();
+		chk(ls1g_exchange(_ctx), "ls1g_exchange");
+		chk(ls1g_traverse(_ctx, &upot, &virial), "ls1g_traverse");
+		_tDevice += wall() - t0;
+	} else if (_mode == FUSED && _inStep && !_ranThisStep) {
+		const double t0 = wall();
+		ls1g_step_record rec{};
+		// pre -> exchange -> forces (+calcFM) -> deleteOuter -> post, as one device-resident step; NVE inside, the
+		// thermostat betas are the Domain's own (integratePre)
+		chk(ls1g_run(_ctx, 1, _dt, -1., &rec), "ls1g_run");
+		upot = rec.upot;
+		virial = rec.virial;
+		_summv2 = rec.summv2;
+		_sumIw2 = rec.sumIw2;
+		_n = rec.n;
+		_rotDOF = rec.rot_dof;
+		_ranThisStep = true;
+		_tDevice += wall() - t0;
+	} else {
+		const double t0 = wall();
+		chk(ls1g_traverse(_ctx, &upot, &virial), "ls1g_traverse");
+		_tDevice += wall() - t0;
+	}
+	domain->setLocalUpot(upot);          // VectorizedCellProcessor::endTraversal (VectorizedCellProcessor.cpp:155-156)
+	domain->setLocalVirial(virial);
+}
+
+void GpuLinkedCells::traverseNonInnermostCells(CellProcessor&) {
+	global_log->error_always_output() << "GpuLinkedCells: overlapping traversal is not supported (set overlappingP2P off)" << std::endl;
+	Simulation::exit(1);
+}
+
+void GpuLinkedCells::traversePartialInnermostCells(CellProcessor&, unsigned int, int) {
+	global_log->error_always_output() << "GpuLinkedCells: overlapping traversal is not supported (set overlappingP2P off)" << std::endl;
+	Simulation::exit(1);
+}
+
+void GpuLinkedCells::deleteOuterParticles() {
+	if (!_devicePhase) {
+		LinkedCells::deleteOuterParticles();
+		if (_deviceLoaded) chk(ls1g_delete_outer(_ctx), "ls1g_delete_outer");
+		return;
+	}
+	if (_mode == OPERATORS || !_ranThisStep) {
+		const double t0 = wall();
+		chk(ls1g_delete_outer(_ctx), "ls1g_delete_outer");
+		_tDevice += wall() - t0;
+	}
+}
+
+unsigned long GpuLinkedCells::getNumberOfParticles() {
+	if (!_devicePhase || _mirrorValid) return LinkedCells::getNumberOfParticles();
+	uint64_t owned = 0, halo = 0;
+	chk(ls1g_count(_ctx, &owned, &halo), "ls1g_count");
+	return owned + halo;
+}
+
+void GpuLinkedCells::clear() {
+	LinkedCells::clear();
+	if (_ctx != nullptr && _deviceLoaded) {
+		uint64_t id = 0;
+		uint32_t cid = 0;
+		double r[3] = {0., 0., 0.};
+		chk(ls1g_upload(_ctx, 0, &id, &cid, r, nullptr, nullptr, nullptr), "ls1g_upload");
+	}
+	_deviceLoaded = false;
+	_devicePhase = false;
+	_mirrorValid = false;
+}
+
+bool GpuLinkedCells::mirrorWanted() const {
+	const unsigned long step = global_simulation->getSimulationStep();
+	if (step >= global_simulation->getNumTimesteps()) return true;       // final checkpoint / plugin finish
+	return _mirrorFrequency > 0 && step % _mirrorFrequency == 0;
+}
+
+// Leapfrog::eventNewTimestep (Leapfrog.cpp:48-68)
+void GpuLinkedCells::integratePre(double dt, Domain* domain) {
+	_dt = dt;
+	if (!_deviceLoaded) {
+		global_log->error_always_output() << "GpuLinkedCells: time step without an initial force calculation" << std::endl;
+		Simulation::exit(1);
+	}
+	if (!_devicePhase || _mirrorValid) {
+		// from here on the device is authoritative: drop the host copies so that the host-side passes of the time loop
+		// (exchangeMolecules, updateForces, thermostat apply) have nothing to do
+		LinkedCells::clear();
+		_devicePhase = true;
+		_mirrorValid = false;
+	}
+	const double t0 = wall();
+	if (_steps > 0 && !domain->NVE()) {
+		// velocity scaling of the previous step (Simulation.cpp:1108-1136) with the betas Domain::calculateGlobalValues
+		// computed (Domain.cpp:226-247); nothing reads v in between
+		const double bt = domain->getGlobalBetaTrans();
+		const double br = domain->getGlobalBetaRot();
+		// "Explosion heuristics" (Domain.cpp:254-311): when a raw beta is below MIN_BETA, calculateGlobalValues caps the kinetic
+		// energy per molecule and replaces the betas by (1, beta_rot^0.0091).  Its molecule loop ran over the (empty) host
+		// cells; the same capping is done here on the device.  The raw betas are recomputed from the very sums handed to Domain.
+		const double Ti = _lastTfactor * domain->getTargetTemperature(0);
+		if (Ti > 0.0 && _n > 0) {
+			const double rawBt = std::pow(3.0 * _n * Ti / _summv2, 0.4);
+			const double rawBr = (_sumIw2 == 0.0 || _rotDOF == 0) ? 1.0 : std::pow(_rotDOF * Ti / _sumIw2, 0.4);
+			if ((rawBt < MIN_BETA || rawBr < MIN_BETA) && bt == 1.0 && std::fabs(br - std::pow(rawBr, 0.0091)) <= 1e-14) {
+				chk(ls1g_selective_thermostat(_ctx, KINLIMIT_PER_T * Ti, Ti), "ls1g_selective_thermostat");
+				++_selective;
+			}
+		}
+		if (bt != 1.0 || br != 1.0) chk(ls1g_scale(_ctx, bt, br), "ls1g_scale");
+	}
+	if (_mode == OPERATORS) chk(ls1g_integrate_pre(_ctx, dt), "ls1g_integrate_pre");
+	_tDevice += wall() - t0;
+	_inStep = true;
+	_ranThisStep = false;
+}
+
+// Leapfrog::eventForcesCalculated (Leapfrog.cpp:70-155)
+void GpuLinkedCells::integratePost(double dt, Domain* domain) {
+	if (!_devicePhase) {
+		global_log->error_always_output() << "GpuLinkedCells: eventForcesCalculated without eventNewTimestep" << std::endl;
+		Simulation::exit(1);
+	}
+	const double t0 = wall();
+	if (_mode == OPERATORS || !_ranThisStep) {
+		chk(ls1g_integrate_post(_ctx, 0.5 * dt, &_summv2, &_sumIw2, &_n, &_rotDOF), "ls1g_integrate_post");
+	}
+	_tDevice += wall() - t0;
+	domain->setLocalSummv2(_summv2, 0);                  // Leapfrog.cpp:146-150
+	domain->setLocalSumIw2(_sumIw2, 0);
+	domain->setLocalNrotDOF(0, _n, _rotDOF);
+	_inStep = false;
+	_ranThisStep = false;
+	_lastTfactor = global_simulation->Tfactor(global_simulation->getSimulationStep());   // the factor calculateGlobalValues gets next
+	++_steps;
+	if (mirrorWanted()) downloadMirror();
+	if (global_simulation->getSimulationStep() >= global_simulation->getNumTimesteps()) printSummary();
+}
+
+// device -> host cells.  The download is cell-sorted on the reference grid, so threads fill disjoint cells.
+void GpuLinkedCells::downloadMirror() {
+	if (_ctx == nullptr || !_deviceLoaded) return;
+	const double t0 = wall();
+	LinkedCells::clear();
+	uint64_t owned = 0, halo = 0;
+	chk(ls1g_count(_ctx, &owned, &halo), "ls1g_count");
+	const size_t cap = owned + halo;
+	std::vector<uint64_t> id(cap);
+	std::vector<uint32_t> cid(cap), cell(cap);
+	std::vector<double> r(3 * cap), v(3 * cap), q(4 * cap), L(3 * cap), F(3 * cap), M(3 * cap), Vi(3 * cap);
+	ls1g_fields f{};
+	f.id = id.data();
+	f.cid = cid.data();
+	f.cell = cell.data();
+	f.r = r.data();
+	f.v = v.data();
+	f.q = q.data();
+	f.L = L.data();
+	f.F = F.data();
+	f.M = M.data();
+	f.Vi = Vi.data();
+	size_t n = 0;
+	const int mask = LS1G_F_ID | LS1G_F_CID | LS1G_F_CELL | LS1G_F_R | LS1G_F_V | LS1G_F_Q | LS1G_F_L | LS1G_F_F | LS1G_F_M | LS1G_F_VI;
+	chk(ls1g_download(_ctx, mask, 0, cap, &f, &n), "ls1g_download");
+	std::vector<Component>& comps = *global_simulation->getEnsemble()->getComponents();
+	// first molecule of every run of equal cell index
+	std::vector<size_t> runs;
+	for (size_t i = 0; i < n; ++i)
+		if (i == 0 || cell[i] != cell[i - 1]) runs.push_back(i);
+	runs.push_back(n);
+	const long nruns = static_cast<long>(runs.size()) - 1;
+#if defined(_OPENMP)
+#pragma omp parallel for schedule(static)
+#endif
+	for (long k = 0; k < nruns; ++k) {
+		ParticleCell& pc = getCellReference(static_cast<int>(cell[runs[k]]));
+		for (size_t i = runs[k]; i < runs[k + 1]; ++i) {
+			Molecule m(id[i], &comps[cid[i]], r[3 * i], r[3 * i + 1], r[3 * i + 2], v[3 * i], v[3 * i + 1], v[3 * i + 2],
+			           q[4 * i], q[4 * i + 1], q[4 * i + 2], q[4 * i + 3], L[3 * i], L[3 * i + 1], L[3 * i + 2]);
+			m.setF(&F[3 * i]);
+			m.setM(&M[3 * i]);
+			m.setVi(&Vi[3 * i]);
+			pc.addParticle(m);
+		}
+	}
+	_bytesDown += n * (8 + 4 + 4 + 22 * 8);
+	_mirrorValid = true;
+	++_mirrors;
+	_tMirror += wall() - t0;
+}

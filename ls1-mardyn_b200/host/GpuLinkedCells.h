@@ -1,0 +1,95 @@
+/*
+ * GpuLinkedCells — ls1-MarDyn ParticleContainer whose short-range force pass, re-sort, halo images and integration run on
+ * one B200 through the C ABI in include/ls1g.h (libls1g.so).  Selected like every other container:
+ *
+ *   <datastructure type="GpuLinkedCells">
+ *     <cellsInCutoffRadius>1</cellsInCutoffRadius>
+ *     <mode>fused</mode>                    fused (default): one ls1g_run step per traverseCells; operators: one C-ABI call per reference operator
+ *     <mirrorfrequency>0</mirrorfrequency>  every k-th step the host cells are refilled from the device (writers, plugins); 0 = last step only
+ *     <device>0</device>
+ *   </datastructure>
+ *   <integrator type="GpuLeapfrog"> ... </integrator>
+ *
+ * This is host code of the reference's own kind: it is compiled against the reference headers (src/particleContainer/
+ * LinkedCells.h, src/integrators/Integrator.h) and linked with the reference objects, see ls1-mardyn_b200/host/Makefile.
+ * It derives from LinkedCells because ParticleIterator is a concrete class over std::vector<ParticleCell>
+ * (src/particleContainer/ParticleIterator.h:50-90): readers, generators, writers and plugins keep working on the host
+ * cells, which hold the molecules before the first time step ("host phase") and on mirror steps.  Precedent for a
+ * container that ignores the cell processor's kernels and publishes upot/virial itself: AutoPasContainer::traverseCells
+ * (src/particleContainer/AutoPasContainer.cpp:282-395).
+ *
+ * The unmodified time loop Simulation::simulate (src/Simulation.cpp:979-1177) drives it:
+ *   eventNewTimestep -> update -> balanceAndExchange -> updateMoleculeCaches -> traverseCells -> updateForces ->
+ *   deleteOuterParticles -> eventForcesCalculated -> calculateGlobalValues -> thermostat
+ * In the device phase the host cells are empty, so the host-side passes of the loop (DomainDecompBase::exchangeMolecules,
+ * Simulation::updateForces, VelocityScalingThermostat::apply) find nothing to do; their work happens in the calls above.
+ */
+#ifndef GPULINKEDCELLS_H_
+#define GPULINKEDCELLS_H_
+
+#include "particleContainer/LinkedCells.h"
+
+#include <cstdint>
+#include <vector>
+
+struct ls1g_ctx;
+class Domain;
+
+class GpuLinkedCells : public LinkedCells {
+public:
+	GpuLinkedCells();
+	~GpuLinkedCells() override;
+
+	void readXML(XMLfileUnits& xmlconfig) override;                         // LinkedCells.cpp:128-134
+	bool rebuild(double bBoxMin[3], double bBoxMax[3]) override;            // LinkedCells.cpp:136-204
+	void update() override;                                                 // LinkedCells.cpp:243-356
+	void updateMoleculeCaches() override;                                   // LinkedCells.cpp:1076-1086
+	void updateInnerMoleculeCaches() override { updateMoleculeCaches(); }
+	void updateBoundaryAndHaloMoleculeCaches() override {}
+	void traverseCells(CellProcessor& cellProcessor) override;              // LinkedCells.cpp:564-575
+	void traverseNonInnermostCells(CellProcessor& cellProcessor) override;
+	void traversePartialInnermostCells(CellProcessor& cellProcessor, unsigned int stage, int stageCount) override;
+	void deleteOuterParticles() override;                                   // LinkedCells.cpp:611-628
+	unsigned long getNumberOfParticles() override;                          // LinkedCells.cpp:577-588
+	void clear() override;                                                  // LinkedCells.cpp:590-595
+	bool requiresForceExchange() const override { return false; }           // full shell: halo forces are never sent back
+	std::string getName() override { return "GpuLinkedCells"; }
+
+	// called by GpuLeapfrog (Integrator::eventNewTimestep / eventForcesCalculated)
+	void integratePre(double dt, Domain* domain);                           // Leapfrog.cpp:48-68
+	void integratePost(double dt, Domain* domain);                          // Leapfrog.cpp:70-155
+
+	/** refill the host cells from the device (r, v, q, D, F, M, Vi); they are dropped again at the next time step */
+	void downloadMirror();
+	ls1g_ctx* ctx() { return _ctx; }
+
+private:
+	enum Mode { FUSED, OPERATORS };
+	void ensureContext();
+	void uploadComponents();
+	void uploadFromHost();
+	bool mirrorWanted() const;
+	void printSummary() const;
+	[[noreturn]] void fail(const char* what) const;
+	void chk(int rc, const char* what) const;
+
+	ls1g_ctx* _ctx = nullptr;
+	Mode _mode = FUSED;
+	int _device = 0;
+	unsigned long _mirrorFrequency = 0;
+	bool _devicePhase = false;     // false: the host cells hold the molecules (before the first time step)
+	bool _deviceLoaded = false;    // the device holds a copy with valid forces
+	bool _mirrorValid = false;     // host cells hold a snapshot of the device state
+	bool _inStep = false;          // between integratePre and integratePost
+	bool _ranThisStep = false;     // fused mode: the step already ran inside traverseCells
+	double _dt = 0.;
+	double _summv2 = 0., _sumIw2 = 0.;
+	uint64_t _n = 0, _rotDOF = 0;
+	// wall clock of the host<->device phases (logged after the last time step)
+	double _tUpload = 0., _tDevice = 0., _tMirror = 0., _tContext = 0.;
+	unsigned long _steps = 0, _mirrors = 0, _selective = 0;
+	double _lastTfactor = 1.0;
+	size_t _bytesUp = 0, _bytesDown = 0;
+};
+
+#endif /* GPULINKEDCELLS_H_ */

@@ -137,3 +137,35 @@ def run(sysm, g, global_len, cid, r, v, q, L, F, M, steps, dt, target_T=0.0):
                      int(steps), C.c_double(dt), C.c_double(target_T), _p(series))
     assert rc == 0
     return dict(r=st[0], v=st[1], q=st[2], L=st[3], F=st[4], M=st[5], series=series)
+
+
+def selective_thermostat(sysm, cid, v, F, q, L, M, limit_energy, Ti):
+    """numpy restatement of the reference's "explosion heuristics" molecule loop (Domain::calculateGlobalValues,
+    src/Domain.cpp:266-292): U_trans = 1/2 m v^2 > limit_energy  ->  v, F *= sqrt(limit/U_trans);
+    U_rot (FullMolecule::U_rot, src/molecules/FullMolecule.cpp:392-400; w = I^-1 rotateinv(q, D)) > 3 rotDOF Ti -> D, M *= sqrt(limit/U_rot).
+    rotDOF = number of non-zero principal moments (Component::updateMassInertia).  Returns (v, F, L, M) copies."""
+    v, F, L, M = (np.array(a, dtype=np.float64, copy=True) for a in (v, F, L, M))
+    m = sysm.scal[cid, 0]
+    I = sysm.scal[cid, 1:4]
+    ut = 0.5 * m * (v[:, 0] * v[:, 0] + v[:, 1] * v[:, 1] + v[:, 2] * v[:, 2])
+    hot = ut > limit_energy
+    c = np.sqrt(limit_energy / ut[hot])
+    v[hot] *= c[:, None]
+    F[hot] *= c[:, None]
+    w_, x, y, z = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+    ww, xx, yy, zz = w_ * w_, x * x, y * y, z * z
+    wx, wy, wz, xy, xz, yz = w_ * x, w_ * y, w_ * z, x * y, x * z, y * z
+    w = np.empty_like(L)                                            # Quaternion::rotateinv (Quaternion.cpp:64-83)
+    w[:, 0] = (ww + xx - yy - zz) * L[:, 0] + 2. * (xy + wz) * L[:, 1] + 2. * (xz - wy) * L[:, 2]
+    w[:, 1] = 2. * (xy - wz) * L[:, 0] + (ww - xx + yy - zz) * L[:, 1] + 2. * (yz + wx) * L[:, 2]
+    w[:, 2] = 2. * (xz + wy) * L[:, 0] + 2. * (yz - wx) * L[:, 1] + (ww - xx - yy + zz) * L[:, 2]
+    invI = np.where(I != 0., 1. / np.where(I != 0., I, 1.), 0.)
+    w *= invI
+    urot = 0.5 * (I * w * w).sum(axis=1)
+    rot_dof = (I != 0.).sum(axis=1)
+    lim = 3.0 * rot_dof * Ti
+    hot = (rot_dof > 0) & (urot > lim)
+    c = np.sqrt(lim[hot] / urot[hot])
+    L[hot] *= c[:, None]
+    M[hot] *= c[:, None]
+    return v, F, L, M

@@ -1,0 +1,62 @@
+"""The drop-in itself: ls1-MarDyn's own executable and UNMODIFIED time loop (Simulation::simulate, src/Simulation.cpp:920-1214)
+with <datastructure type="GpuLinkedCells"> + <integrator type="GpuLeapfrog"> (ls1-mardyn_b200/host/) against the same
+executable with LinkedCells + Leapfrog, on the reference's shipped examples (initial states from the golden fixtures).
+Compared per time step: U_pot, p, beta_trans, beta_rot as the reference's ResultWriter prints them (15 digits), and the
+final checkpoint (r, v, q, D per molecule)."""
+import os
+
+import numpy as np
+import pytest
+
+from tests import mardyn_cases as M
+
+STEPS = 20
+needs_binaries = pytest.mark.skipif(not (os.path.exists(M.REF_EXE) and os.path.exists(M.GPU_EXE)),
+                                    reason="oracle/_ref/MarDyn or host/_build/MarDynGpu not built (needs the reference tree at build time)")
+
+
+def rel(a, b):
+    return float(np.max(np.abs(a - b)) / max(np.max(np.abs(b)), 1e-300))
+
+
+@needs_binaries
+def test_patched_binary_keeps_the_reference_path_bit_identical(tmp_path):
+    """MarDynGpu = reference objects + two dispatch branches: with LinkedCells/Leapfrog it must reproduce MarDyn exactly"""
+    a = M.run(M.REF_EXE, M.write_case(str(tmp_path), "ex_EOX", 5, "cpu"), 5, threads=1)
+    os.rename(tmp_path / "ex_EOX_cpu.res", tmp_path / "first.res")
+    b = M.run(M.GPU_EXE, M.write_case(str(tmp_path), "ex_EOX", 5, "cpu"), 5, threads=1)
+    assert np.array_equal(a["res"], b["res"])
+    for k in ("id", "r", "v", "q", "D"):
+        assert np.array_equal(a["final"][k], b["final"][k]), k
+
+
+@needs_binaries
+def test_gpu_container_fails_loudly_without_a_device(tmp_path):
+    """no CPU fallback: without a CUDA device the GPU container ends the run through the reference's fatal path"""
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    with pytest.raises(RuntimeError, match="no CUDA device"):
+        M.run(M.GPU_EXE, M.write_case(str(tmp_path), "ex_Argon", 2, "fused"), 2, threads=2)
+
+
+@pytest.mark.gpu
+@needs_binaries
+@pytest.mark.parametrize("variant", ["fused", "operators"])
+@pytest.mark.parametrize("name", ["ex_Argon", "ex_CO2", "ex_EOX"])
+def test_reference_time_loop_on_the_gpu_container(name, variant, tmp_path):
+    cpu = M.run(M.REF_EXE, M.write_case(str(tmp_path), name, STEPS, "cpu"), STEPS)
+    gpu = M.run(M.GPU_EXE, M.write_case(str(tmp_path), name, STEPS, variant), STEPS)
+    assert "GpuLinkedCells: device context created" in gpu["log"]
+    assert gpu["gpu"]["steps"] == STEPS and gpu["gpu"]["mirrors"] == 1
+    assert cpu["res"].shape == gpu["res"].shape == (STEPS + 1, 10)
+    # ResultWriter columns: step time U_pot U_pot_avg p p_avg beta_trans beta_rot c_v N
+    for col, what, tol in ((2, "U_pot", 1e-8), (4, "p", 1e-8), (6, "beta_trans", 1e-9), (7, "beta_rot", 1e-9), (9, "N", 0.0)):
+        assert rel(gpu["res"][:, col], cpu["res"][:, col]) <= tol, (what, rel(gpu["res"][:, col], cpu["res"][:, col]))
+    assert np.array_equal(cpu["final"]["id"], gpu["final"]["id"]) and np.array_equal(cpu["final"]["cid"], gpu["final"]["cid"])
+    box = M.load(name)["box"]
+    dr = cpu["final"]["r"] - gpu["final"]["r"]
+    dr -= box * np.round(dr / box)                     # a molecule on the periodic boundary may be wrapped on one side only
+    assert np.max(np.abs(dr)) <= 1e-7 * box[0]
+    for k in ("v", "q", "D"):
+        assert rel(gpu["final"][k], cpu["final"][k]) <= 1e-6, (k, rel(gpu["final"][k], cpu["final"][k]))
