@@ -165,6 +165,19 @@ int ls1g_selective_thermostat(ls1g_ctx* ctx, double limit_trans_energy, double t
  * Requires forces from a previous ls1g_traverse (as prepare_start does, Simulation.cpp:813-844). */
 int ls1g_run(ls1g_ctx* ctx, int n_steps, double dt, double target_temperature, ls1g_step_record* records);
 
+/* One time step for a HOST-DRIVEN loop (the reference's Simulation::simulate calling the container once per step,
+ * Simulation.cpp:979-1177):  VelocityScalingThermostat::apply(beta_trans, beta_rot) of the previous step (Simulation.cpp:1108-1136,
+ * fused into this step's pre-kick) -> integrate_pre -> update+exchange -> traverse -> delete_outer -> integrate_post.
+ * Equals ls1g_scale + ls1g_run(1 step, NVE); the betas stay the caller's (Domain::calculateGlobalValues).
+ * flags: LS1G_STEP_VI = also produce the per-molecule virial Vi and the pair count (needed only when Vi is read back). */
+enum { LS1G_STEP_VI = 1 };
+int ls1g_step(ls1g_ctx* ctx, double dt, double beta_trans, double beta_rot, int flags, ls1g_step_record* record);
+
+/* Page-locked host staging memory: ls1g_upload / ls1g_download run at full PCIe rate from/to it (any other host pointer
+ * works too, at the pageable rate).  replaces: nothing in the reference - it is the device boundary's own buffer. */
+int ls1g_host_alloc(ls1g_ctx* ctx, size_t bytes, void** out);
+int ls1g_host_free(ls1g_ctx* ctx, void* p);
+
 /* --- multi-GPU (one context per rank/GPU) --------------------------------------------------
  * replaces: DomainDecomposition::getBoundingBoxMin/Max (DomainDecomposition.cpp:116-125); host only */
 int ls1g_decomp_box(const int rank_grid[3], const int rank_coords[3], const double global_length[3],

@@ -15,7 +15,7 @@ EXPORTS = [
     "ls1g_last_error", "ls1g_version", "ls1g_create", "ls1g_destroy", "ls1g_set_components", "ls1g_get_grid",
     "ls1g_cell_index_of_points_host", "ls1g_cell_index_of_points", "ls1g_debug_cell_pairs", "ls1g_upload",
     "ls1g_upload_forces", "ls1g_stream", "ls1g_count", "ls1g_download", "ls1g_update", "ls1g_exchange", "ls1g_traverse", "ls1g_delete_outer",
-    "ls1g_integrate_pre", "ls1g_integrate_post", "ls1g_scale", "ls1g_selective_thermostat", "ls1g_run", "ls1g_decomp_box", "ls1g_decomp_grid",
+    "ls1g_integrate_pre", "ls1g_integrate_post", "ls1g_scale", "ls1g_selective_thermostat", "ls1g_run", "ls1g_step", "ls1g_host_alloc", "ls1g_host_free", "ls1g_decomp_box", "ls1g_decomp_grid",
     "ls1g_comm_unique_id", "ls1g_comm_init", "ls1g_allreduce_sum", "ls1g_comm_init_local", "ls1g_exchange_group",
     "ls1g_timers", "ls1g_measure_fp64_peak", "ls1g_last_pair_count",
 ]
@@ -324,6 +324,12 @@ class Container:
         if not records:
             return None
         return np.array([[x.upot, x.virial, x.summv2, x.sumIw2, x.n, x.rot_dof] for x in rec[:n_steps]], dtype=np.float64).reshape(n_steps, 6)
+
+    def step(self, dt, beta_trans=1.0, beta_rot=1.0, vi=True):
+        """one host-driven time step (ls1g_step): previous step's thermostat betas fused into the pre-kick; returns the step record"""
+        rec = _StepRecord()
+        _chk(lib().ls1g_step(self._ctx, C.c_double(dt), C.c_double(beta_trans), C.c_double(beta_rot), int(bool(vi)), C.byref(rec)))
+        return np.array([rec.upot, rec.virial, rec.summv2, rec.sumIw2, rec.n, rec.rot_dof], dtype=np.float64)
 
     # -- multi-GPU ------------------------------------------------------------------------------------
     def comm_init(self, n_ranks, rank, unique_id):

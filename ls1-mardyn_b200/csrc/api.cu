@@ -403,6 +403,19 @@ extern "C" int ls1g_upload_forces(ls1g_ctx* c, size_t n, const double* F, const 
 	return 0;
 }
 
+int k_host_alloc(size_t bytes, void** out);
+int k_host_free(void* p);
+extern "C" int ls1g_host_alloc(ls1g_ctx* c, size_t bytes, void** out) {
+	if (!c || !out) LS1G_FAIL("null argument");
+	CUDA_TRY(cudaSetDevice(c->cfg.device));
+	return k_host_alloc(bytes, out);
+}
+extern "C" int ls1g_host_free(ls1g_ctx* c, void* p) {
+	if (!c) LS1G_FAIL("null context");
+	CUDA_TRY(cudaSetDevice(c->cfg.device));
+	return k_host_free(p);
+}
+
 // the CUDA stream all work of this context is issued on (cudaStream_t), for event timing by the caller
 extern "C" int ls1g_stream(ls1g_ctx* c, void** stream) {
 	if (!c || !stream) LS1G_FAIL("null argument");

@@ -242,6 +242,21 @@ int k_selective(ls1g_ctx* c, double limit_energy, double Ti) {
 	return 0;
 }
 
+// VelocityScalingThermostat::apply with host-given betas fused into the pre-kick (upd_preF) of the next step: one pass over v
+int k_scale_pre(ls1g_ctx* c, double dt, double bt, double br) {
+	unsigned nb = nblk(c->n_slots, INT_THREADS);
+	if (!nb) return 0;
+	timer_start(c, LS1G_T_INTEGRATE);
+	c->h_scalars[8] = bt; c->h_scalars[9] = br;       // pinned; consumed by the copy below before any later call can rewrite it (callers sync)
+	CUDA_TRY(cudaMemcpyAsync(c->d_scalars + 8, c->h_scalars + 8, 2 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+	IntArgs a = make_args(c); a.dt = dt; a.dt_half = 0.5 * dt; a.partials = c->partials;
+	a.betas = c->d_scalars + 8;
+	launch_int<false, true>(c, a, nb);
+	CUDA_TRY(cudaGetLastError());
+	timer_stop(c, LS1G_T_INTEGRATE, 1);
+	return 0;
+}
+
 // [post(step n)] [+ thermostat] [+ pre(step n+1)].
 //   no thermostat : ONE kernel (post+pre fused when both are requested) + the partial-sum finalize
 //   thermostat    : post, finalize (betas computed on the device, Domain.cpp:226-247), then scale(+pre) in one kernel

@@ -136,7 +136,7 @@ static int flag_snapshot(ls1g_ctx* c, int ring) {
 	return 0;
 }
 
-static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, double target_T, double* d_rec, int* done) {
+static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, double target_T, double* d_rec, int* done, int want_vi = 1) {
 	*done = 0;
 	bool need_build = true;
 	int rc = 0, s = 0;
@@ -221,7 +221,7 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 				rc = k_forces_list_fused(c, dt);
 				if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s, c->d_scalars, 8 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
 			} else {
-				if (!rc) rc = k_forces_list(c, s + 1 == n_steps);      // pair statistics + per-molecule virial only for the last step
+				if (!rc) rc = k_forces_list(c, s + 1 == n_steps && want_vi);      // pair statistics + per-molecule virial only for the last step
 				if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s, c->d_scalars, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
 				if (!rc) rc = k_post_pre(c, dt, 1, s + 1 < n_steps, thermo, target_T);
 				if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s + 4, c->d_scalars + 4, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
@@ -257,17 +257,17 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 
 // Device-resident loop.  Per step: pre -> exchange (wrap, images, sort) -> forces (+calcFM) -> post -> thermostat.
 // post(n), the thermostat and pre(n+1) run as one kernel between two force passes.
-extern "C" int ls1g_run(ls1g_ctx* c, int n_steps, double dt, double target_T, ls1g_step_record* records) {
-	NEED(c);
-	if (n_steps <= 0) return 0;
+// bt, br: betas applied to v, D before the first pre-kick (fused into it); want_vi: per-molecule virial + pair count on the last step.
+int k_scale_pre(ls1g_ctx* c, double dt, double bt, double br);
+static int run_impl(ls1g_ctx* c, int n_steps, double dt, double target_T, ls1g_step_record* records, double bt, double br, int want_vi) {
 	if (c->in_list_mode && !nl_applicable(c) && ls1g_nl_leave(c)) return 1;
 	if (!c->forces_valid) LS1G_FAIL("ls1g_run: forces missing - call ls1g_exchange + ls1g_traverse once (prepare_start, Simulation.cpp:813-844)");
 	const int thermo = target_T > 0.;
 	double* d_rec = nullptr;
 	if (records) CUDA_TRY(cudaMallocAsync((void**)&d_rec, (size_t)n_steps * 8 * sizeof(double), c->stream));
-	int rc = k_post_pre(c, dt, 0, 1, 0, 0.);
+	int rc = (bt != 1.0 || br != 1.0) ? k_scale_pre(c, dt, bt, br) : k_post_pre(c, dt, 0, 1, 0, 0.);
 	int s0 = 0;
-	if (!rc && nl_applicable(c)) rc = run_list_steps(c, n_steps, dt, thermo, target_T, d_rec, &s0);
+	if (!rc && nl_applicable(c)) rc = run_list_steps(c, n_steps, dt, thermo, target_T, d_rec, &s0, want_vi);
 	for (int s = s0; s < n_steps && !rc; ++s) {
 		c->sorted = 0;
 		c->forces_valid = 0;     // F is recomputed before its next use: do not carry it through the sort
@@ -295,6 +295,20 @@ extern "C" int ls1g_run(ls1g_ctx* c, int n_steps, double dt, double target_T, ls
 			c->last_pairs = (uint64_t)llround(r[2]);
 		}
 	return 0;
+}
+
+extern "C" int ls1g_run(ls1g_ctx* c, int n_steps, double dt, double target_T, ls1g_step_record* records) {
+	NEED(c);
+	if (n_steps <= 0) return 0;
+	return run_impl(c, n_steps, dt, target_T, records, 1.0, 1.0, 1);
+}
+
+// One time step for a host-driven loop: VelocityScalingThermostat::apply(beta_trans, beta_rot) of the PREVIOUS step fused into
+// this step's pre-kick, then exchange / forces / deleteOuter / post as ls1g_run(1).  NVE inside: the betas are the caller's
+// (Domain::calculateGlobalValues), so the reference's own thermostat logic stays in charge.
+extern "C" int ls1g_step(ls1g_ctx* c, double dt, double beta_trans, double beta_rot, int flags, ls1g_step_record* record) {
+	NEED(c);
+	return run_impl(c, 1, dt, -1., record, beta_trans, beta_rot, (flags & LS1G_STEP_VI) ? 1 : 0);
 }
 
 // ------------------------------------------------------------------------------------------------

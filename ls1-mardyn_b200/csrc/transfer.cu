@@ -192,3 +192,14 @@ int k_download(ls1g_ctx* c, int mask, int include_halo, size_t n_ret, ls1g_field
 	CUDA_TRY(cudaGetLastError());
 	return 0;
 }
+
+// pinned host staging memory for ls1g_upload / ls1g_download (full PCIe rate; pageable user memory is staged by the driver)
+int k_host_alloc(size_t bytes, void** out) {
+	*out = nullptr;
+	CUDA_TRY(cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocDefault));
+	return 0;
+}
+int k_host_free(void* p) {
+	if (p) CUDA_TRY(cudaFreeHost(p));
+	return 0;
+}

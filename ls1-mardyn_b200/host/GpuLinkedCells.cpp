@@ -21,6 +21,8 @@ extern "C" {
 
 #include <chrono>
 #include <cmath>
+#include <cstdlib>
+#include <memory>
 #include <string>
 
 #if defined(_OPENMP)
@@ -39,14 +41,29 @@ GpuLinkedCells::GpuLinkedCells() : LinkedCells() {}
 
 GpuLinkedCells::~GpuLinkedCells() {
 	// no logging here: main deletes global_log before the Simulation object (and with it this container) is destroyed
-	if (_ctx != nullptr) ls1g_destroy(_ctx);
+	if (_ctx != nullptr) {
+		if (_stage != nullptr) {
+			if (_stagePinned) ls1g_host_free(_ctx, _stage);
+			else std::free(_stage);
+		}
+		ls1g_destroy(_ctx);
+	}
 }
 
 void GpuLinkedCells::printSummary() const {
+	double ms[LS1G_T_COUNT];
+	uint64_t launches[LS1G_T_COUNT];
+	if (_ctx != nullptr && ls1g_timers(_ctx, ms, launches, 0) == 0) {
+		global_log->info() << "GpuLinkedCells: kernel time [ms] force " << ms[LS1G_T_FORCE] << " (" << launches[LS1G_T_FORCE] << " launches), sort "
+		                   << ms[LS1G_T_SORT] << " (" << launches[LS1G_T_SORT] << "), integrate " << ms[LS1G_T_INTEGRATE] << " ("
+		                   << launches[LS1G_T_INTEGRATE] << "), exchange " << ms[LS1G_T_EXCHANGE] << " (" << launches[LS1G_T_EXCHANGE]
+		                   << "), aux " << ms[LS1G_T_AUX] << " (" << launches[LS1G_T_AUX] << ")" << std::endl;
+	}
 	global_log->info() << "GpuLinkedCells: " << _steps << " device steps took " << _tDevice << " s; upload "
 	                   << _tUpload << " s (" << _bytesUp << " B); " << _mirrors << " host mirror download(s) took "
 	                   << _tMirror << " s (" << _bytesDown << " B); context creation " << _tContext << " s; selective thermostat applied "
-	                   << _selective << " time(s)" << std::endl;
+	                   << _selective << " time(s); first steps [s] " << _tFirstSteps[0] << " " << _tFirstSteps[1] << " "
+	                   << _tFirstSteps[2] << " " << _tFirstSteps[3] << ", slowest step " << _tMaxStep << std::endl;
 }
 
 void GpuLinkedCells::fail(const char* what) const {
@@ -84,6 +101,12 @@ void GpuLinkedCells::readXML(XMLfileUnits& xmlconfig) {
 bool GpuLinkedCells::rebuild(double bBoxMin[3], double bBoxMax[3]) {
 	if (_ctx != nullptr) {      // new bounding box: the device context is rebuilt at its next use
 		if (_devicePhase && !_mirrorValid) downloadMirror();
+		if (_stage != nullptr) {
+			if (_stagePinned) ls1g_host_free(_ctx, _stage);
+			else std::free(_stage);
+		}
+		_stage = nullptr;
+		_stageMolecules = 0;
 		ls1g_destroy(_ctx);
 		_ctx = nullptr;
 		_deviceLoaded = false;
@@ -131,6 +154,7 @@ void GpuLinkedCells::ensureContext() {
 			Simulation::exit(1);
 		}
 	}
+	_numCells = static_cast<size_t>(cpd[0]) * cpd[1] * cpd[2];
 	global_log->info() << "GpuLinkedCells: device context created, " << cpd[0] << " x " << cpd[1] << " x " << cpd[2]
 	                   << " cells" << std::endl;
 	_tContext += wall() - t0;
@@ -181,48 +205,113 @@ void GpuLinkedCells::uploadComponents() {
 	    "ls1g_set_components");
 }
 
-// host cells (owned molecules) -> ls1g_upload.  The device orders molecules by (cell, id), so the gather order is free.
+// One page-locked block (ls1g_host_alloc) carved into the arrays of ls1g_upload / ls1g_download; allocated once, grown on demand.
+double GpuLinkedCells::ensureStaging(size_t molecules) {
+	if (_stage != nullptr && _stageMolecules >= molecules) return 0.;
+	const double t0 = wall();
+	const char* pinnedEnv = std::getenv("LS1G_SHIM_PINNED");       // 0: plain (pageable) host memory for the staging block
+	const bool pinned = !(pinnedEnv != nullptr && std::atoi(pinnedEnv) == 0);
+	if (_stage != nullptr) {
+		if (_stagePinned) chk(ls1g_host_free(_ctx, _stage), "ls1g_host_free");
+		else std::free(_stage);
+	}
+	_stage = nullptr;
+	_stageMolecules = molecules + molecules / 16 + 1024;
+	_stagePinned = pinned;
+	if (pinned) {
+		chk(ls1g_host_alloc(_ctx, _stageMolecules * kStageBytesPerMolecule, &_stage), "ls1g_host_alloc");
+	} else {
+		_stage = std::malloc(_stageMolecules * kStageBytesPerMolecule);
+		if (_stage == nullptr) fail("staging allocation");
+	}
+	char* p = static_cast<char*>(_stage);
+	auto take = [&](size_t bytesPerMolecule) { void* q = p; p += _stageMolecules * bytesPerMolecule; return q; };
+	_sR = static_cast<double*>(take(24));      // 8-byte aligned arrays first
+	_sV = static_cast<double*>(take(24));
+	_sQ = static_cast<double*>(take(32));
+	_sL = static_cast<double*>(take(24));
+	_sF = static_cast<double*>(take(24));
+	_sM = static_cast<double*>(take(24));
+	_sVi = static_cast<double*>(take(24));
+	_sId = static_cast<uint64_t*>(take(8));
+	_sCid = static_cast<uint32_t*>(take(4));
+	_sCell = static_cast<uint32_t*>(take(4));
+	_tContext += wall() - t0;
+	return wall() - t0;
+}
+
+// host cells (owned molecules) -> ls1g_upload.  The device orders molecules by (cell, id), so the gather order is free;
+// here it is cell order: count per cell, prefix sum, then every thread fills the slices of its cells.
 void GpuLinkedCells::uploadFromHost() {
 	ensureContext();
 	const double t0 = wall();
-	std::vector<uint64_t> id;
-	std::vector<uint32_t> cid;
-	std::vector<double> r, v, q, L;
+	const long nc = static_cast<long>(_numCells);
+	std::vector<size_t> first(nc + 1, 0);
 #if defined(_OPENMP)
-#pragma omp parallel
+#pragma omp parallel for schedule(static)
 #endif
-	{
-		std::vector<uint64_t> id_t;
-		std::vector<uint32_t> cid_t;
-		std::vector<double> r_t, v_t, q_t, L_t;
-		for (auto m = LinkedCells::iterator(ParticleIterator::ONLY_INNER_AND_BOUNDARY); m.isValid(); ++m) {
-			id_t.push_back(m->getID());
-			cid_t.push_back(m->componentid());
+	for (long c = 0; c < nc; ++c) {
+		ParticleCell& pc = getCellReference(static_cast<int>(c));
+		first[c + 1] = pc.isHaloCell() ? 0 : static_cast<size_t>(pc.getMoleculeCount());
+	}
+	for (long c = 0; c < nc; ++c) first[c + 1] += first[c];
+	const size_t n = first[nc];
+	const double tStage = ensureStaging(n);       // set-up (page-locking), accounted with the context creation
+	uint64_t* id = _sId;
+	uint32_t* cid = _sCid;
+	double *r = _sR, *v = _sV, *q = _sQ, *L = _sL;
+#if defined(_OPENMP)
+#pragma omp parallel for schedule(static)
+#endif
+	for (long c = 0; c < nc; ++c) {
+		if (first[c + 1] == first[c]) continue;
+		size_t i = first[c];
+		ParticleCell& pc = getCellReference(static_cast<int>(c));
+		for (auto m = pc.iterator(); m.isValid(); ++m, ++i) {
+			id[i] = m->getID();
+			cid[i] = m->componentid();
 			for (int d = 0; d < 3; ++d) {
-				r_t.push_back(m->r(d));
-				v_t.push_back(m->v(d));
-				L_t.push_back(m->D(d));
+				r[3 * i + d] = m->r(d);
+				v[3 * i + d] = m->v(d);
+				L[3 * i + d] = m->D(d);
 			}
 			const Quaternion& qq = m->q();
-			q_t.insert(q_t.end(), {qq.qw(), qq.qx(), qq.qy(), qq.qz()});
-		}
-#if defined(_OPENMP)
-#pragma omp critical
-#endif
-		{
-			id.insert(id.end(), id_t.begin(), id_t.end());
-			cid.insert(cid.end(), cid_t.begin(), cid_t.end());
-			r.insert(r.end(), r_t.begin(), r_t.end());
-			v.insert(v.end(), v_t.begin(), v_t.end());
-			q.insert(q.end(), q_t.begin(), q_t.end());
-			L.insert(L.end(), L_t.begin(), L_t.end());
+			q[4 * i] = qq.qw();
+			q[4 * i + 1] = qq.qx();
+			q[4 * i + 2] = qq.qy();
+			q[4 * i + 3] = qq.qz();
 		}
 	}
-	const size_t n = id.size();
-	chk(ls1g_upload(_ctx, n, id.data(), cid.data(), r.data(), v.data(), q.data(), L.data()), "ls1g_upload");
+	chk(ls1g_upload(_ctx, n, id, cid, r, v, q, L), "ls1g_upload");
 	_bytesUp += n * (8 + 4 + 13 * 8);
 	_deviceLoaded = true;
-	_tUpload += wall() - t0;
+	_tUpload += wall() - t0 - tStage;
+}
+
+// LinkedCells::clear (LinkedCells.cpp:590-595) walks the cells serially; with 10^7 host molecules to free that is the slowest
+// host pass of the first time step, so the cells are emptied by all threads.
+void GpuLinkedCells::clearHostCells() {
+	const long nc = static_cast<long>(_numCells);
+	if (nc == 0) {
+		LinkedCells::clear();
+		return;
+	}
+#if defined(_OPENMP)
+#pragma omp parallel for schedule(static)
+#endif
+	for (long c = 0; c < nc; ++c) getCellReference(static_cast<int>(c)).deallocateAllParticles();
+}
+
+// In the device phase the host cells are empty: hand out iterators that are invalid from the start instead of ones that walk
+// every (empty) cell, so that the host-side passes of the time loop cost nothing.
+ParticleIterator GpuLinkedCells::iterator(ParticleIterator::Type t) {
+	if (_devicePhase && !_mirrorValid) return ParticleIterator();
+	return LinkedCells::iterator(t);
+}
+
+RegionParticleIterator GpuLinkedCells::regionIterator(const double startRegion[3], const double endRegion[3], ParticleIterator::Type type) {
+	if (_devicePhase && !_mirrorValid) return RegionParticleIterator();
+	return LinkedCells::regionIterator(startRegion, endRegion, type);
 }
 
 void GpuLinkedCells::update() {
@@ -270,9 +359,10 @@ void GpuLinkedCells::traverseCells(CellProcessor& cellProcessor) {
 	} else if (_mode == FUSED && _inStep && !_ranThisStep) {
 		const double t0 = wall();
 		ls1g_step_record rec{};
-		// pre -> exchange -> forces (+calcFM) -> deleteOuter -> post, as one device-resident step; NVE inside, the
-		// thermostat betas are the Domain's own (integratePre)
-		chk(ls1g_run(_ctx, 1, _dt, -1., &rec), "ls1g_run");
+		// [thermostat of the previous step] -> pre -> exchange -> forces (+calcFM) -> deleteOuter -> post, as one device-resident
+		// step; the betas are the Domain's own (integratePre).  Vi and the pair count only when the host will read them.
+		chk(ls1g_step(_ctx, _dt, _pendingBt, _pendingBr, mirrorWanted() ? LS1G_STEP_VI : 0, &rec), "ls1g_step");
+		_pendingBt = _pendingBr = 1.0;
 		upot = rec.upot;
 		virial = rec.virial;
 		_summv2 = rec.summv2;
@@ -280,7 +370,10 @@ void GpuLinkedCells::traverseCells(CellProcessor& cellProcessor) {
 		_n = rec.n;
 		_rotDOF = rec.rot_dof;
 		_ranThisStep = true;
-		_tDevice += wall() - t0;
+		const double dtStep = wall() - t0;
+		_tDevice += dtStep;
+		if (_steps < 4) _tFirstSteps[_steps] = dtStep;
+		if (dtStep > _tMaxStep) _tMaxStep = dtStep;
 	} else {
 		const double t0 = wall();
 		chk(ls1g_traverse(_ctx, &upot, &virial), "ls1g_traverse");
@@ -349,7 +442,7 @@ void GpuLinkedCells::integratePre(double dt, Domain* domain) {
 	if (!_devicePhase || _mirrorValid) {
 		// from here on the device is authoritative: drop the host copies so that the host-side passes of the time loop
 		// (exchangeMolecules, updateForces, thermostat apply) have nothing to do
-		LinkedCells::clear();
+		clearHostCells();
 		_devicePhase = true;
 		_mirrorValid = false;
 	}
@@ -371,7 +464,12 @@ void GpuLinkedCells::integratePre(double dt, Domain* domain) {
 				++_selective;
 			}
 		}
-		if (bt != 1.0 || br != 1.0) chk(ls1g_scale(_ctx, bt, br), "ls1g_scale");
+		if (_mode == FUSED) {          // applied inside ls1g_step, fused into the pre-kick
+			_pendingBt = bt;
+			_pendingBr = br;
+		} else if (bt != 1.0 || br != 1.0) {
+			chk(ls1g_scale(_ctx, bt, br), "ls1g_scale");
+		}
 	}
 	if (_mode == OPERATORS) chk(ls1g_integrate_pre(_ctx, dt), "ls1g_integrate_pre");
 	_tDevice += wall() - t0;
@@ -386,8 +484,11 @@ void GpuLinkedCells::integratePost(double dt, Domain* domain) {
 		Simulation::exit(1);
 	}
 	const double t0 = wall();
-	if (_mode == OPERATORS || !_ranThisStep) {
+	if (_mode == OPERATORS) {
 		chk(ls1g_integrate_post(_ctx, 0.5 * dt, &_summv2, &_sumIw2, &_n, &_rotDOF), "ls1g_integrate_post");
+	} else if (!_ranThisStep) {
+		global_log->error_always_output() << "GpuLinkedCells (fused mode): time step without traverseCells" << std::endl;
+		Simulation::exit(1);
 	}
 	_tDevice += wall() - t0;
 	domain->setLocalSummv2(_summv2, 0);                  // Leapfrog.cpp:146-150
@@ -405,24 +506,25 @@ void GpuLinkedCells::integratePost(double dt, Domain* domain) {
 void GpuLinkedCells::downloadMirror() {
 	if (_ctx == nullptr || !_deviceLoaded) return;
 	const double t0 = wall();
-	LinkedCells::clear();
+	clearHostCells();
 	uint64_t owned = 0, halo = 0;
 	chk(ls1g_count(_ctx, &owned, &halo), "ls1g_count");
-	const size_t cap = owned + halo;
-	std::vector<uint64_t> id(cap);
-	std::vector<uint32_t> cid(cap), cell(cap);
-	std::vector<double> r(3 * cap), v(3 * cap), q(4 * cap), L(3 * cap), F(3 * cap), M(3 * cap), Vi(3 * cap);
+	const size_t cap = owned + halo + 1;
+	const double tStage = ensureStaging(cap);
+	uint64_t* id = _sId;
+	uint32_t *cid = _sCid, *cell = _sCell;
+	double *r = _sR, *v = _sV, *q = _sQ, *L = _sL, *F = _sF, *M = _sM, *Vi = _sVi;
 	ls1g_fields f{};
-	f.id = id.data();
-	f.cid = cid.data();
-	f.cell = cell.data();
-	f.r = r.data();
-	f.v = v.data();
-	f.q = q.data();
-	f.L = L.data();
-	f.F = F.data();
-	f.M = M.data();
-	f.Vi = Vi.data();
+	f.id = id;
+	f.cid = cid;
+	f.cell = cell;
+	f.r = r;
+	f.v = v;
+	f.q = q;
+	f.L = L;
+	f.F = F;
+	f.M = M;
+	f.Vi = Vi;
 	size_t n = 0;
 	const int mask = LS1G_F_ID | LS1G_F_CID | LS1G_F_CELL | LS1G_F_R | LS1G_F_V | LS1G_F_Q | LS1G_F_L | LS1G_F_F | LS1G_F_M | LS1G_F_VI;
 	chk(ls1g_download(_ctx, mask, 0, cap, &f, &n), "ls1g_download");
@@ -438,6 +540,7 @@ void GpuLinkedCells::downloadMirror() {
 #endif
 	for (long k = 0; k < nruns; ++k) {
 		ParticleCell& pc = getCellReference(static_cast<int>(cell[runs[k]]));
+		pc.increaseMoleculeStorage(runs[k + 1] - runs[k]);
 		for (size_t i = runs[k]; i < runs[k + 1]; ++i) {
 			Molecule m(id[i], &comps[cid[i]], r[3 * i], r[3 * i + 1], r[3 * i + 2], v[3 * i], v[3 * i + 1], v[3 * i + 2],
 			           q[4 * i], q[4 * i + 1], q[4 * i + 2], q[4 * i + 3], L[3 * i], L[3 * i + 1], L[3 * i + 2]);
@@ -450,5 +553,5 @@ void GpuLinkedCells::downloadMirror() {
 	_bytesDown += n * (8 + 4 + 4 + 22 * 8);
 	_mirrorValid = true;
 	++_mirrors;
-	_tMirror += wall() - t0;
+	_tMirror += wall() - t0 - tStage;
 }

@@ -54,6 +54,9 @@ public:
 	void clear() override;                                                  // LinkedCells.cpp:590-595
 	bool requiresForceExchange() const override { return false; }           // full shell: halo forces are never sent back
 	std::string getName() override { return "GpuLinkedCells"; }
+	ParticleIterator iterator(ParticleIterator::Type t) override;          // LinkedCells.h:245-250
+	RegionParticleIterator regionIterator(const double startRegion[3], const double endRegion[3],
+	                                      ParticleIterator::Type type) override;
 
 	// called by GpuLeapfrog (Integrator::eventNewTimestep / eventForcesCalculated)
 	void integratePre(double dt, Domain* domain);                           // Leapfrog.cpp:48-68
@@ -68,6 +71,8 @@ private:
 	void ensureContext();
 	void uploadComponents();
 	void uploadFromHost();
+	double ensureStaging(size_t molecules);
+	void clearHostCells();
 	bool mirrorWanted() const;
 	void printSummary() const;
 	[[noreturn]] void fail(const char* what) const;
@@ -89,7 +94,17 @@ private:
 	double _tUpload = 0., _tDevice = 0., _tMirror = 0., _tContext = 0.;
 	unsigned long _steps = 0, _mirrors = 0, _selective = 0;
 	double _lastTfactor = 1.0;
-	size_t _bytesUp = 0, _bytesDown = 0;
+	size_t _bytesUp = 0, _bytesDown = 0, _numCells = 0;
+	double _pendingBt = 1.0, _pendingBr = 1.0;   // fused mode: betas of the previous step, applied inside the next ls1g_step
+	// page-locked staging block (ls1g_host_alloc): r v q L F M Vi id cid cell, 192 bytes per molecule
+	static constexpr size_t kStageBytesPerMolecule = 24 * 6 + 32 + 8 + 4 + 4;
+	void* _stage = nullptr;
+	bool _stagePinned = true;
+	double _tFirstSteps[4] = {0., 0., 0., 0.}, _tMaxStep = 0.;
+	size_t _stageMolecules = 0;
+	double *_sR = nullptr, *_sV = nullptr, *_sQ = nullptr, *_sL = nullptr, *_sF = nullptr, *_sM = nullptr, *_sVi = nullptr;
+	uint64_t* _sId = nullptr;
+	uint32_t *_sCid = nullptr, *_sCell = nullptr;
 };
 
 #endif /* GPULINKEDCELLS_H_ */

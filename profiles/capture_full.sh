@@ -7,7 +7,7 @@ tag=${1:-r01_nl_force_10M}
 kern=${2:-nl_force_kernel}
 skip=${3:-4}
 mkdir -p gpurun_out
-python bench.py --steps 10 --warmup 3 --no-cpu-baseline --e2e-steps 1 > gpurun_out/${tag}_plain.json 2> gpurun_out/${tag}_plain.err
+python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-mardyn-gpu --e2e-steps 1 > gpurun_out/${tag}_plain.json 2> gpurun_out/${tag}_plain.err
 # launch-skip 4: past the warm-up launches, a steady-state force pass in the frozen list layout
 ncu --set full --clock-control none --import-source on -k regex:$kern --launch-skip $skip --launch-count 1 \
-    -f -o gpurun_out/${tag} python bench.py --steps 10 --warmup 3 --no-cpu-baseline --e2e-steps 1 > gpurun_out/${tag}_ncu.log 2>&1
+    -f -o gpurun_out/${tag} python bench.py --steps 10 --warmup 3 --no-cpu-baseline --no-mardyn-gpu --e2e-steps 1 > gpurun_out/${tag}_ncu.log 2>&1

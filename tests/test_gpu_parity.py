@@ -398,6 +398,36 @@ def test_selective_thermostat_matches_oracle(name, list_mode):
         assert np.abs(after[k] - ref).max() <= tol * scale, (k, np.abs(after[k] - ref).max() / scale)
 
 
+@pytest.mark.parametrize("name", ["ex_Argon", "ex_EOX"])
+def test_host_driven_step_equals_scale_plus_run(name):
+    """ls1g_step(dt, betas) = ls1g_scale(betas) + ls1g_run(1): the entry point the reference's time loop drives through
+    GpuLinkedCells (thermostat of the previous step fused into the pre-kick); Argon takes the neighbour-list path, EOX the per-step one"""
+    d = load(name)
+    st = initial_state(d)
+    dt = float(d["dt"][0])
+    betas = [(1.0, 1.0), (0.97, 0.99), (1.02, 1.0), (0.995, 1.01), (1.0, 1.0), (0.9, 0.95)]
+    out = []
+    for fused in (False, True):
+        with container_of(d) as c:
+            c.add_particles(st["id"], st["cid"], st["r"], st["v"], st["q"], st["L"])
+            c.exchange()
+            c.traverse_cells()
+            c.delete_outer_particles()
+            recs = []
+            for k, (bt, br) in enumerate(betas):
+                if fused:
+                    recs.append(c.step(dt, bt, br, vi=(k == len(betas) - 1)))
+                else:
+                    c.scale(bt, br)
+                    recs.append(c.run(1, dt)[0])
+            out.append((np.array(recs), by_id(c.download(("id", "r", "v", "q", "L", "F", "M", "Vi")))))
+    (ra, sa), (rb, sb) = out
+    assert np.all(np.abs(ra - rb) <= 1e-11 * np.maximum(np.abs(ra), 1e-300)), np.abs(ra - rb).max()
+    for k in ("r", "v", "q", "L", "F", "M", "Vi"):
+        scale = max(np.abs(sa[k]).max(), 1e-300)
+        assert np.abs(sa[k] - sb[k]).max() <= 1e-10 * scale, (k, np.abs(sa[k] - sb[k]).max() / scale)
+
+
 def test_thermostat_run_holds_temperature():
     """NVT: Domain::calculateGlobalValues betas (Domain.cpp:226-247) drive T to the target"""
     r, v, box = fcc_lattice(10, seed=1, temperature=1.0)
