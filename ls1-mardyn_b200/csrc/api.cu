@@ -179,6 +179,13 @@ extern "C" int ls1g_create(const ls1g_config* cfg, ls1g_ctx** out) {
 	// VectorizedCellProcessor.cpp:24
 	c->epsRFInvrc3 = 2. * (c->cfg.eps_rf - 1.) / ((c->cfg.cutoff * c->cfg.cutoff * c->cfg.cutoff) * (2. * c->cfg.eps_rf + 1.));
 	CUDA_TRY(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+	{
+		int lo = 0, hi = 0;
+		CUDA_TRY(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+		CUDA_TRY(cudaStreamCreateWithPriority(&c->stream_comm, cudaStreamNonBlocking, hi));
+		CUDA_TRY(cudaEventCreateWithFlags(&c->ev_pos, cudaEventDisableTiming));
+		CUDA_TRY(cudaEventCreateWithFlags(&c->ev_halo, cudaEventDisableTiming));
+	}
 	size_t nc = (size_t)c->grid.n_cells + 1;
 	CUDA_TRY(cudaMalloc((void**)&c->cell_count, nc * sizeof(uint32_t)));
 	CUDA_TRY(cudaMalloc((void**)&c->cell_fill, nc * sizeof(uint32_t)));
@@ -190,8 +197,8 @@ extern "C" int ls1g_create(const ls1g_config* cfg, ls1g_ctx** out) {
 	CUDA_TRY(cudaMalloc((void**)&c->d_scalars, 16 * sizeof(double)));
 	CUDA_TRY(cudaMemset(c->d_scalars, 0, 16 * sizeof(double)));
 	CUDA_TRY(cudaMallocHost((void**)&c->h_scalars, 16 * sizeof(double)));
-	CUDA_TRY(cudaMalloc((void**)&c->d_flags, 4 * sizeof(unsigned long long)));
-	CUDA_TRY(cudaMemset(c->d_flags, 0, 4 * sizeof(unsigned long long)));
+	CUDA_TRY(cudaMalloc((void**)&c->d_flags, 8 * sizeof(unsigned long long)));
+	CUDA_TRY(cudaMemset(c->d_flags, 0, 8 * sizeof(unsigned long long)));
 	CUDA_TRY(cudaMallocHost((void**)&c->h_flags, 8 * sizeof(unsigned long long)));
 	for (int k = 0; k < 4; ++k) CUDA_TRY(cudaEventCreateWithFlags(&c->disp_ev[k], cudaEventDisableTiming));
 	*out = c;
@@ -212,6 +219,10 @@ extern "C" int ls1g_destroy(ls1g_ctx* c) {
 	for (int k = 0; k < 4; ++k) if (c->disp_ev[k]) cudaEventDestroy(c->disp_ev[k]);
 	cudaFree(c->d_counters); cudaFreeHost(c->h_counters); cudaFree(c->partials); cudaFree(c->d_scalars); cudaFreeHost(c->h_scalars);
 	for (int k = 0; k < 2; ++k) { cudaFree(c->send_buf[k]); cudaFree(c->recv_buf[k]); }
+	if (c->ev_pos) cudaEventDestroy(c->ev_pos);
+	if (c->ev_halo) cudaEventDestroy(c->ev_halo);
+	if (c->stream_comm) cudaStreamDestroy(c->stream_comm);
+	cudaFree(c->bmap); cudaFree(c->bflag);
 	if (c->stream) cudaStreamDestroy(c->stream);
 	delete c;
 	return 0;

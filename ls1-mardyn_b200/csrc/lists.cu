@@ -39,6 +39,7 @@ static NLArgs nl_args(ls1g_ctx* c) {
 	a.eps24 = c->eps24_h[0]; a.sig2 = c->sig2_h[0]; a.shift6 = c->shift6_h[0]; a.rclj2 = c->rclj2;
 	a.F = c->F; a.Vi = c->Vi; a.partials = c->partials;
 	a.guard = c->guard_on ? c->d_flags + 3 : nullptr; a.guard_thr = (unsigned long long)host_double_bits(c->disp_thr2);
+	a.bmap = c->bmap; a.bflag = c->bflag; a.phase = 0; a.nzi = c->bgrid.cpd[2] - 2;
 	return a;
 }
 
@@ -64,8 +65,15 @@ int k_list_build(ls1g_ctx* c) {
 		c->lcount_cap = want_c;
 	}
 	if (!c->pos_build) CUDA_TRY(cudaMalloc((void**)&c->pos_build, c->cap * sizeof(double4)));
+	if (nb > c->bmap_cap) {
+		cudaFree(c->bmap); cudaFree(c->bflag); c->bmap = nullptr; c->bflag = nullptr; c->bmap_cap = 0;
+		CUDA_TRY(cudaMalloc((void**)&c->bmap, nb * sizeof(uint32_t)));
+		CUDA_TRY(cudaMalloc((void**)&c->bflag, nb));
+		c->bmap_cap = nb;
+	}
 	timer_start(c, LS1G_T_SORT);
 	CUDA_TRY(cudaMemsetAsync(c->d_flags, 0, 3 * sizeof(unsigned long long), c->stream));
+	CUDA_TRY(cudaMemsetAsync(c->d_flags + 5, 0, sizeof(unsigned long long), c->stream));      // boundary-block count
 	CUDA_TRY(cudaMemcpyAsync(c->pos_build, c->cur.pos, c->n_slots * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));
 	CUDA_TRY(cudaMemcpyAsync(c->alt.pos, c->cur.pos, c->n_slots * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));   // fused steps ping-pong cur.pos / alt.pos
 	NLArgs a = nl_args(c);
@@ -74,6 +82,7 @@ int k_list_build(ls1g_ctx* c) {
 	nl_build_kernel<<<(unsigned)nb, NL_BT, NL_BUILD_SMEM(a.btcap), c->stream>>>(a);
 	CUDA_TRY(cudaGetLastError());
 	CUDA_TRY(cudaMemcpyAsync(c->h_flags, c->d_flags, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+	CUDA_TRY(cudaMemcpyAsync(c->h_flags + 3, c->d_flags + 5, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));   // read by the caller after its sync
 	timer_stop(c, LS1G_T_SORT, 2);
 	return 0;
 }
@@ -128,7 +137,8 @@ __global__ void __launch_bounds__(256) fused_finalize_kernel(const double* __res
 
 // One NVE step of the list loop in ONE pass: forces, post(n), pre(n+1) (nl_force_kernel<.., FUSE>).  Reads c->cur.pos, writes
 // the new owned positions to c->alt.pos (free between sorts) and swaps the two pointers.
-int k_forces_list_fused(ls1g_ctx* c, double dt) {
+// phase: 0 = one launch; 1 = inner blocks only (no finalize, no swap); 2 = boundary blocks, then finalize + swap (see NLArgs::phase)
+int k_forces_list_fused(ls1g_ctx* c, double dt, int phase) {
 	const size_t nb = nl_blocks(c);
 	if (ls1g_ensure_partials(c, nb ? nb : 1, 8)) return 1;
 	if (nl_force_attrs()) return 1;
@@ -136,10 +146,16 @@ int k_forces_list_fused(ls1g_ctx* c, double dt) {
 	a.tcap = c->list_tcap;
 	a.dt = dt; a.dt_half = 0.5 * dt; a.mass = c->comps_h[0].mass;
 	a.vel = c->cur.vel; a.pos_out = c->alt.pos; a.pos_build = c->pos_build;
+	a.phase = phase;
+	const size_t grid = phase == 2 ? (size_t)c->n_boundary_blocks : nb;
 	timer_start(c, LS1G_T_FORCE);
-	if (c->shift6_h[0] != 0.) nl_force_kernel<true, false, true><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
-	else nl_force_kernel<false, false, true><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
-	timer_stop(c, LS1G_T_FORCE, 1);
+	if (grid) {
+		if (c->shift6_h[0] != 0.) nl_force_kernel<true, false, true><<<(unsigned)grid, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
+		else nl_force_kernel<false, false, true><<<(unsigned)grid, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
+	}
+	timer_stop(c, LS1G_T_FORCE, grid ? 1 : 0);
+	CUDA_TRY(cudaGetLastError());
+	if (phase == 1) return 0;
 	std::swap(c->cur.pos, c->alt.pos);
 	timer_start(c, LS1G_T_AUX);
 	size_t nbr = nb; const double* base;

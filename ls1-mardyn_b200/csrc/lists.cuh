@@ -59,6 +59,12 @@ struct NLArgs {
 	double* vel;                // [slots][3], updated in place
 	double4* pos_out;           // the OTHER position buffer: new positions of the owned molecules (tiles still read pos)
 	const double4* pos_build;   // positions at the last list build
+	// multi-rank overlap of the halo exchange with the force pass: blocks whose tile touches no halo cell ("inner") need no
+	// received data.  The build kernel classifies every block once per build; the force kernel runs as two launches:
+	// phase 1 = all blocks, boundary blocks return at once; phase 2 = a compact grid over bmap (the boundary blocks).  phase 0 = one launch.
+	uint32_t* bmap;             // [n_boundary] block ids of the boundary blocks (order irrelevant: every block owns its outputs)
+	unsigned char* bflag;       // [blocks] 1 = boundary
+	int phase, nzi;
 };
 
 struct NLBlock {
@@ -68,10 +74,10 @@ struct NLBlock {
 };
 
 // Common prologue: slot range, tile plan (s_beg/s_off per row) - identical in build and force kernels.
-__device__ __forceinline__ NLBlock nl_plan(const NLArgs& a, uint32_t* s_beg, int* s_off, int* s_len, int& x_first, int& x_last) {
+__device__ __forceinline__ NLBlock nl_plan(const NLArgs& a, uint32_t* s_beg, int* s_off, int* s_len, int& x_first, int& x_last, const unsigned blk) {
 	const Grid& g = a.g;
 	const int nx = g.cpd[0], ny = g.cpd[1];
-	const int row = blockIdx.x / a.bpr, bi = blockIdx.x % a.bpr;
+	const int row = blk / a.bpr, bi = blk % a.bpr;
 	const int cy = row % a.nyi + 1, cz = row / a.nyi + 1;
 	const int crow = (cz * ny + cy) * nx;
 	const uint32_t rs = a.cell_start[crow + 1], re = a.cell_start[crow + nx - 1];
@@ -119,7 +125,13 @@ __global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
 	const Grid& g = a.g;
 	const int tid = threadIdx.x, lane = tid & 31;
 	int x_first = 0, x_last = 0;
-	const NLBlock b = nl_plan(a, s_beg, s_off, s_len, x_first, x_last);
+	const NLBlock b = nl_plan(a, s_beg, s_off, s_len, x_first, x_last, blockIdx.x);
+	if (tid == 0 && a.bflag) {      // inner / boundary classification for the overlapped multi-rank force pass (see NLArgs)
+		const int row_ = blockIdx.x / a.bpr, cy_ = row_ % a.nyi + 1, cz_ = row_ / a.nyi + 1;
+		const bool boundary = b.live && (cy_ == 1 || cy_ == a.nyi || cz_ == 1 || cz_ == a.nzi || x_first <= 1 || x_last >= a.g.cpd[0] - 2);
+		a.bflag[blockIdx.x] = boundary ? 1 : 0;
+		if (boundary) a.bmap[atomicAdd(a.flags + 5, 1ull)] = blockIdx.x;
+	}
 	if (!b.live) return;
 	if (tid == 0) {      // largest slab tile of this build: sizes the force kernel's shared memory
 		const int m = max(max(s_off[3], s_off[7] - s_off[3]), s_off[9] - s_off[7]) + NL_DUMMY;
@@ -228,10 +240,12 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 	__shared__ uint32_t s_beg[9]; __shared__ int s_off[10], s_len[9];
 	__shared__ double red[(FUSE ? 8 : 5) * 32];
 	const int tid = threadIdx.x;
+	const unsigned blk = a.phase == 2 ? a.bmap[blockIdx.x] : blockIdx.x;
+	if (a.phase == 1 && a.bflag[blk]) return;         // boundary block: runs in phase 2, after the halo positions arrived
 	// speculatively enqueued step whose lists turned out expired: nothing is computed, the host rebuilds and repeats it
 	if (!FUSE && a.guard && *a.guard > a.guard_thr) return;
 	int x_first = 0, x_last = 0;
-	const NLBlock b = nl_plan(a, s_beg, s_off, s_len, x_first, x_last);
+	const NLBlock b = nl_plan(a, s_beg, s_off, s_len, x_first, x_last, blk);
 	if (FUSE && a.guard && *a.guard > a.guard_thr) {      // the host swaps the two position buffers after every fused launch: carry the positions over
 		const uint32_t i = b.s0 + tid;
 		if (i < b.s1) a.pos_out[i] = a.pos[i];
@@ -247,8 +261,8 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 		const bool active = i < b.s1;
 		double4 Pi = make_double4(0., 0., 0., 0.);
 		uint32_t ends = 0;
-		if (active) { Pi = a.pos[i]; ends = a.lcount[(size_t)blockIdx.x * NL_BT + tid]; }
-		const uint2* my = (const uint2*)(a.lists + ((size_t)blockIdx.x * a.lcap4 * NL_BT + tid) * 4);   // 4 entries per load
+		if (active) { Pi = a.pos[i]; ends = a.lcount[(size_t)blk * NL_BT + tid]; }
+		const uint2* my = (const uint2*)(a.lists + ((size_t)blk * a.lcap4 * NL_BT + tid) * 4);   // 4 entries per load
 		double Fx = 0., Fy = 0., Fz = 0., Vx = 0., Vy = 0., Vz = 0., u6 = 0.;
 		int np_i = 0;
 		// 4 pairs at a time, branch-free (invalid pairs contribute exact zeros) so that the dependency chains overlap.
@@ -358,7 +372,7 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 	block_sum<NV>(acc, red);
 	if (tid == 0) {
 #pragma unroll
-		for (int k = 0; k < NV; ++k) a.partials[(size_t)blockIdx.x * NV + k] = acc[k];
+		for (int k = 0; k < NV; ++k) a.partials[(size_t)blk * NV + k] = acc[k];
 	}
 }
 

@@ -116,6 +116,10 @@ struct ls1g_ctx {
 	double4* pos_build;                     // [cap] positions when the lists were built (displacement criterion)
 	unsigned short* lists; size_t lists_cap;// [blocks][LCAP][128] tile indices
 	uint32_t* lcount; size_t lcount_cap;    // [blocks*128]
+	uint32_t* bmap; unsigned char* bflag; size_t bmap_cap;   // boundary blocks of the last build (lists.cuh: NLArgs::bmap)
+	uint32_t n_boundary_blocks;
+	cudaStream_t stream_comm;               // high-priority stream of the overlapped halo refresh (multi-rank list steps)
+	cudaEvent_t ev_pos, ev_halo;
 	int      track_disp;                    // integrate kernels track max |r - pos_build|^2 into d_flags[0]
 	int      list_tcap;                     // tile capacity used by the list force kernel (max tile of the last build, padded)
 	int      list_bpr;                      // blocks per cell row

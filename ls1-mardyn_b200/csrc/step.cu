@@ -109,7 +109,7 @@ int nl_applicable(const ls1g_ctx* c);
 int nl_set_bin_grid(ls1g_ctx* c, int list_mode);
 int k_list_build(ls1g_ctx* c);
 int k_forces_list(ls1g_ctx* c, int count_pairs);
-int k_forces_list_fused(ls1g_ctx* c, double dt);
+int k_forces_list_fused(ls1g_ctx* c, double dt, int phase);
 int k_halo_refresh(ls1g_ctx* c);
 
 // Neighbour-list steps of ls1g_run (lists.cuh).  On entry the pre-kick of step 0 is done.  Runs steps [0, n_steps) unless
@@ -146,6 +146,9 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 	// the integrator is fused into the force kernel on NVE steps (LS1G_FUSE=0 keeps the separate integrate kernel)
 	const char* fe = getenv("LS1G_FUSE");
 	const bool fuse_nve = !thermo && !c->vi_every_step && !(fe && atoi(fe) == 0);
+	// multi-rank: overlap the halo refresh with the inner blocks of the force pass (LS1G_OVERLAP=0: exchange first, then one launch)
+	const char* oe = getenv("LS1G_OVERLAP");
+	const bool overlap = c->n_ranks > 1 && !(oe && atoi(oe) == 0);
 	auto expired = [&](int ring) { double d2; memcpy(&d2, c->h_flags + 4 + ring, sizeof(double)); return d2 > c->disp_thr2; };
 	if (c->in_list_mode) {       // continuing the previous ls1g_run: the pre-kick above was tracked; rebuild only if the lists expired
 		if (flag_snapshot(c, 0) || sync_check(c, "ls1g_run (displacement)")) return 1;
@@ -161,6 +164,7 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 	while (!rc) {
 		if (s < n_steps && s - chk < NL_AHEAD) {
 			const bool built = need_build;
+			bool overlapped = false;
 			const double t0 = now();
 			if (need_build) {
 				c->sorted = 0; c->track_disp = 0; c->guard_on = 0;
@@ -205,20 +209,36 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 					return 0;
 				}
 				c->track_disp = 1;
+				c->n_boundary_blocks = (uint32_t)c->h_flags[3];
 				c->list_tcap = (int)((c->h_flags[2] + 63) & ~63ull);
 				if (c->list_tcap < 64) c->list_tcap = 64;
 				if (dbg) fprintf(stderr, "ls1g: list build at step %d: max tile %llu, bpr %d, slots %zu, bin grid %d %d %d\n", s, c->h_flags[2], c->list_bpr, c->n_slots, c->bgrid.cpd[0], c->bgrid.cpd[1], c->bgrid.cpd[2]);
 				need_build = false; ++rebuilds;
 				t_build += now() - t0;
+			} else if (overlap && fuse_nve && s + 1 < n_steps) {
+				// multi-rank NVE step: the halo positions travel on the communication stream while the inner blocks run
+				overlapped = true;
+				if (cudaEventRecord(c->ev_pos, c->stream) != cudaSuccess || cudaStreamWaitEvent(c->stream_comm, c->ev_pos, 0) != cudaSuccess) rc = 1;
+				cudaStream_t main_stream = c->stream;
+				c->stream = c->stream_comm;
+				if (!rc) rc = comm_refresh(c);
+				if (!rc) rc = k_halo_refresh(c);
+				c->stream = main_stream;
+				if (!rc && cudaEventRecord(c->ev_halo, c->stream_comm) != cudaSuccess) rc = 1;
 			} else {
 				if (c->n_ranks > 1) rc = comm_refresh(c);
 				if (!rc) rc = k_halo_refresh(c);
 			}
 			const double t1 = now();
 			c->guard_on = built ? 0 : 1;
-			if (fuse_nve && s + 1 < n_steps) {
+			if (overlapped) {
+				if (!rc) rc = k_forces_list_fused(c, dt, 1);
+				if (!rc && cudaStreamWaitEvent(c->stream, c->ev_halo, 0) != cudaSuccess) rc = 1;
+				if (!rc) rc = k_forces_list_fused(c, dt, 2);
+				if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s, c->d_scalars, 8 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
+			} else if (fuse_nve && s + 1 < n_steps) {
 				// NVE step that is not the last of the run: forces + post(s) + pre(s + 1) in one kernel
-				rc = k_forces_list_fused(c, dt);
+				if (!rc) rc = k_forces_list_fused(c, dt, 0);
 				if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s, c->d_scalars, 8 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
 			} else {
 				if (!rc) rc = k_forces_list(c, s + 1 == n_steps && want_vi);      // pair statistics + per-molecule virial only for the last step
