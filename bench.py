@@ -496,7 +496,7 @@ def main_b200(args):
     flops = lj_flops(n_dist, n_pairs, True) if vi_all else (lj_flops(n_dist, n_pairs, False) * (k_t - 1) + lj_flops(n_dist, n_pairs, True)) / k_t
     force_ms = tm["force"]["ms"] / max(tm["force"]["launches"], 1)
     traffic, traffic_src = None, None
-    prof = os.path.join(ROOT, "profiles", "r01_ncu_nl_force_10M_summary.csv")
+    prof = os.path.join(ROOT, "profiles", "r01c_ncu_nl_force_fused_10M_summary.csv")
     if os.path.exists(prof) and args.cells == CELLS_PER_GPU:      # dram bytes of ONE launch from the committed ncu --set full capture
         vals = {}
         for ln in open(prof):
@@ -504,7 +504,7 @@ def main_b200(args):
             if len(f) >= 3 and f[0].startswith("dram__bytes_"):
                 vals[f[0]] = float(f[1]) * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}.get(f[2], 1.0)
         if len(vals) == 2:
-            traffic, traffic_src = sum(vals.values()), "profiles/r01_ncu_nl_force_10M_summary.csv (ncu --set full, one launch, same workload)"
+            traffic, traffic_src = sum(vals.values()), "profiles/r01c_ncu_nl_force_fused_10M_summary.csv (ncu --set full, one launch, same workload)"
     peak = ls1g.fp64_peak_tflops(local) if rank == 0 else 0.0
     achieved = flops / (force_ms * 1e-3) / 1e12 if force_ms > 0 else 0.0
     launches = sum(t["launches"] for t in tm.values())
@@ -581,7 +581,7 @@ def main_b200(args):
                              "peak_source": "measured here: dependent-free DFMA kernel (ls1g_measure_fp64_peak); MEASURED_PEAKS.json has no FP64 figure",
                              "flops_per_launch": flops, "n_dist": n_dist, "n_pairs": n_pairs, "kernel_ms": round(force_ms, 4),
                              "model": "FlopCounter: 8*N_dist + 41*N_pairs with per-molecule virial (last step of the run), 8*N_dist + 35*N_pairs without (the other steps; the reference's own count for that case); Newton-3 counts, the owner-computes kernel executes ~2x these",
-                             "note": "bound is the FP64 FMA pipe (SURVEY 8d), not HBM/tensor: ncu sm__pipe_fp64_cycles_active 64 % (profiles/)"},
+                             "note": "bound is the FP64 FMA pipe (SURVEY 8d), not HBM/tensor: ncu sm__pipe_fp64_cycles_active 51 % of this owner-computes kernel, DRAM 1.5 TB/s = 23 % of the copy peak (profiles/r01c_ncu_nl_force_fused_10M_summary.csv)"},
                 "kernel_ms_per_step": {k: round(t["ms"] / args.steps, 4) for k, t in tm.items()},
                 "hbm_kernels": hbm_kernels(tm, args.steps, n_local),
                 "clocks": clk}

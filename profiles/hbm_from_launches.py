@@ -2,7 +2,7 @@
    python profiles/hbm_from_launches.py <launches.csv> <n_slots> <n_owned> [peak_GBs]
 ALGORITHMIC bytes per launch (slots = owned molecules + halo copies at that launch):
   bin_kernel        read pos 32 + write cell 4 + slot key 8/record                                    44 B x slots
-  scatter_kernel    read pos 32 + cell 4, write slot records 17                                       53 B x slots
+  scatter_kernel    read pos 32 + cell 4 + id 8, write slot records 17                                61 B x slots
   gather_kernel     read records 17 + payload (pos 32 + vel 24 + id 8), write payload + cell 4       149 B x slots
   integrate <0,1,0> (pre)   read pos 32 + vel 24 + F 24 + cell 4 (+ build pos 32 in list mode), write pos 32 + vel 24    140 B x owned
   integrate <1,0,0> (post)  read pos(cid) 32 + vel 24 + F 24 + cell 4, write vel 24                                      108 B x owned
@@ -15,7 +15,7 @@ path, slots, owned = sys.argv[1], float(sys.argv[2]), float(sys.argv[3])
 peak = float(sys.argv[4]) if len(sys.argv) > 4 else 6455.9
 halo = slots - owned
 BYTES = {
-    "bin_kernel": 44 * slots, "scatter_kernel": 53 * slots, "gather_kernel": 149 * slots,
+    "bin_kernel": 44 * slots, "scatter_kernel": 61 * slots, "gather_kernel": 149 * slots,
     "void integrate_kernel<0, 1, 0>": 140 * owned, "void integrate_kernel<1, 0, 0>": 108 * owned, "void integrate_kernel<1, 1, 0>": 140 * owned,
     "halo_refresh_kernel": 4 * slots + 69 * halo, "pack_kernel": 36 * slots, "pack_pos_kernel": (24 + 4 + 32) * owned,
     "void compact_f64_kernel<3>": (24 + 24 + 4) * owned, "compact_pos_kernel": (32 + 24 + 4) * owned,
