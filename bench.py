@@ -487,6 +487,7 @@ def main_b200(args):
     c.exchange()                                      # halo copies back for the cell census (not timed)
     cells_all = c.download(("cell",), include_halo=True)["cell"]
     n_dist = distance_checks(cells_all, cpd)
+    fc = c.flop_count()                               # the reference's FlopCounter on the same cells, counted on the device
     c.traverse_cells()
     n_pairs = c.last_pair_count()
     del cells_all
@@ -580,6 +581,11 @@ def main_b200(args):
                              "frac": round(achieved / peak, 4) if peak > 0 else None, "traffic": traffic, "traffic_source": traffic_src,
                              "peak_source": "measured here: dependent-free DFMA kernel (ls1g_measure_fp64_peak); MEASURED_PEAKS.json has no FP64 figure",
                              "flops_per_launch": flops, "n_dist": n_dist, "n_pairs": n_pairs, "kernel_ms": round(force_ms, 4),
+                             "flopcounter": {"flops": fc["flops"], "molecule_distances": fc["molecule_distances"], "lj_kernel_calls": float(fc["kernel"][0]),
+                                             "lj_macro_calls": float(fc["macro"][0]),
+                                             "note": "ls1g_flop_count = the reference's FlopCounter as a device cell processor (bit-equal to the reference on the golden fixtures); "
+                                                     "it visits a pair across the periodic boundary from both images, so its total lies a few % above the Newton-3 count "
+                                                     "(every pair once) that flops_per_launch and frac are quoted on"},
                              "model": "FlopCounter: 8*N_dist + 41*N_pairs with per-molecule virial (last step of the run), 8*N_dist + 35*N_pairs without (the other steps; the reference's own count for that case); Newton-3 counts, the owner-computes kernel executes ~2x these",
                              "note": "bound is the FP64 FMA pipe (SURVEY 8d), not HBM/tensor: ncu sm__pipe_fp64_cycles_active 51 % of this owner-computes kernel, DRAM 1.5 TB/s = 23 % of the copy peak (profiles/r01c_ncu_nl_force_fused_10M_summary.csv)"},
                 "kernel_ms_per_step": {k: round(t["ms"] / args.steps, 4) for k, t in tm.items()},

@@ -207,6 +207,17 @@ int ls1g_timers(ls1g_ctx* ctx, double ms[LS1G_T_COUNT], uint64_t launches[LS1G_T
 int ls1g_stream(ls1g_ctx* ctx, void** stream);
 /* dependent-free DFMA micro-kernel: measured FP64 FMA peak of this GPU in TFLOP/s (roofline denominator) */
 int ls1g_measure_fp64_peak(int device, double* tflops);
+/* replaces: FlopCounter as the cell processor of one traversal (adapter/FlopCounter.cpp:196-421; count -> FLOP model FlopCounter.h:150-283,
+ * multipliers FlopCounter.cpp:19-75), as io/FlopRateWriter.cpp runs it: the reference's own count of the ALGORITHMIC (Newton-3) floating
+ * point work of a force pass over the current cells.  Potentials in the order of FlopCounter.h:138-147: LJ, charge, charge-dipole,
+ * dipole, charge-quadrupole, dipole-quadrupole, quadrupole.  Needs halo copies in place (after ls1g_exchange, before ls1g_delete_outer). */
+typedef struct {
+	double molecule_distances;   /* _moleculeDistances */
+	double kernel_calls[7];      /* _numKernelCalls per potential */
+	double macro_calls[7];       /* _numMacroCalls per potential */
+	double flops;                /* _Counts::getTotalFlops() */
+} ls1g_flop_counts;
+int ls1g_flop_count(ls1g_ctx* ctx, ls1g_flop_counts* out);
 /* pair statistics of the last traverse: molecule pairs inside the cutoff (counted once) */
 int ls1g_last_pair_count(ls1g_ctx* ctx, uint64_t* pairs_in_cutoff);
 

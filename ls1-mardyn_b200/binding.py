@@ -17,7 +17,7 @@ EXPORTS = [
     "ls1g_upload_forces", "ls1g_stream", "ls1g_count", "ls1g_download", "ls1g_update", "ls1g_exchange", "ls1g_traverse", "ls1g_delete_outer",
     "ls1g_integrate_pre", "ls1g_integrate_post", "ls1g_scale", "ls1g_selective_thermostat", "ls1g_run", "ls1g_step", "ls1g_host_alloc", "ls1g_host_free", "ls1g_decomp_box", "ls1g_decomp_grid",
     "ls1g_comm_unique_id", "ls1g_comm_init", "ls1g_allreduce_sum", "ls1g_comm_init_local", "ls1g_exchange_group",
-    "ls1g_timers", "ls1g_measure_fp64_peak", "ls1g_last_pair_count",
+    "ls1g_timers", "ls1g_measure_fp64_peak", "ls1g_last_pair_count", "ls1g_flop_count",
 ]
 
 FIELDS = dict(id=1, cid=2, r=4, v=8, q=16, L=32, F=64, M=128, Vi=256, cell=512)
@@ -43,6 +43,10 @@ class _Component(C.Structure):
 
 class _Fields(C.Structure):
     _fields_ = [(k, C.c_void_p) for k in ("id", "cid", "r", "v", "q", "L", "F", "M", "Vi", "cell")]
+
+
+class _FlopCounts(C.Structure):
+    _fields_ = [("molecule_distances", C.c_double), ("kernel_calls", C.c_double * 7), ("macro_calls", C.c_double * 7), ("flops", C.c_double)]
 
 
 class _StepRecord(C.Structure):
@@ -312,6 +316,12 @@ class Container:
 
     def scale(self, beta_trans, beta_rot=1.0):
         _chk(lib().ls1g_scale(self._ctx, C.c_double(beta_trans), C.c_double(beta_rot)))
+
+    def flop_count(self):
+        """the reference's FlopCounter over the current cells (halo copies in place): dict(molecule_distances, kernel[7], macro[7], flops)"""
+        f = _FlopCounts()
+        _chk(lib().ls1g_flop_count(self._ctx, C.byref(f)))
+        return dict(molecule_distances=f.molecule_distances, kernel=np.array(list(f.kernel_calls)), macro=np.array(list(f.macro_calls)), flops=f.flops)
 
     def selective_thermostat(self, limit_trans_energy, temperature):
         """Domain::calculateGlobalValues explosion heuristics (Domain.cpp:254-295): cap U_trans / U_rot per molecule"""

@@ -91,11 +91,14 @@ int k_list_build(ls1g_ctx* c) {
 static int nl_force_attrs() {
 	static bool attr_set = false;
 	if (!attr_set) {
-		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<true, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
-		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
-		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
-		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<true, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
-		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
+		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<true, true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
+		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<true, false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
+		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<false, false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
+		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<true, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
+		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<false, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
+		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<true, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
+		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<true, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
+		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<false, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
 		attr_set = true;
 	}
 	return 0;
@@ -109,9 +112,9 @@ int k_forces_list(ls1g_ctx* c, int last_step) {
 	a.tcap = c->list_tcap;      // the largest tile of the last build: shared memory sized to what this system needs
 	timer_start(c, LS1G_T_FORCE);
 	// last step of a run: pair statistics + per-molecule virial; other steps: forces + the scalar sums of the step record
-	if (last_step || c->vi_every_step) nl_force_kernel<true, true, false><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
-	else if (c->shift6_h[0] != 0.) nl_force_kernel<true, false, false><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
-	else nl_force_kernel<false, false, false><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
+	if (last_step || c->vi_every_step) nl_force_kernel<true, true, 0><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
+	else if (c->shift6_h[0] != 0.) nl_force_kernel<true, false, 0><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
+	else nl_force_kernel<false, false, 0><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
 	timer_stop(c, LS1G_T_FORCE, 1);
 	if (k_force_finalize(c, nb)) return 1;
 	CUDA_TRY(cudaGetLastError());
@@ -150,13 +153,41 @@ int k_forces_list_fused(ls1g_ctx* c, double dt, int phase) {
 	const size_t grid = phase == 2 ? (size_t)c->n_boundary_blocks : nb;
 	timer_start(c, LS1G_T_FORCE);
 	if (grid) {
-		if (c->shift6_h[0] != 0.) nl_force_kernel<true, false, true><<<(unsigned)grid, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
-		else nl_force_kernel<false, false, true><<<(unsigned)grid, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
+		if (c->shift6_h[0] != 0.) nl_force_kernel<true, false, 1><<<(unsigned)grid, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
+		else nl_force_kernel<false, false, 1><<<(unsigned)grid, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
 	}
 	timer_stop(c, LS1G_T_FORCE, grid ? 1 : 0);
 	CUDA_TRY(cudaGetLastError());
 	if (phase == 1) return 0;
 	std::swap(c->cur.pos, c->alt.pos);
+	timer_start(c, LS1G_T_AUX);
+	size_t nbr = nb; const double* base;
+	const int extra = nb > 2048;
+	if (ls1g_prereduce(c, nbr, 8, base)) return 1;
+	fused_finalize_kernel<<<1, 256, 0, c->stream>>>(base, nbr, c->d_scalars);
+	timer_stop(c, LS1G_T_AUX, 1 + extra);
+	CUDA_TRY(cudaGetLastError());
+	return 0;
+}
+
+// forces + post(n) in one pass (nl_force_kernel<.., FUSE = 2>): the last step of a run / the single step of ls1g_step.
+// vi: per-molecule virial + pair statistics.  Leaves the step scalars in d_scalars[0..7] like the fused NVE step.
+int k_forces_list_post(ls1g_ctx* c, double dt, int vi) {
+	const size_t nb = nl_blocks(c);
+	if (ls1g_ensure_partials(c, nb ? nb : 1, 8)) return 1;
+	if (nl_force_attrs()) return 1;
+	NLArgs a = nl_args(c);
+	a.tcap = c->list_tcap;
+	a.dt = dt; a.dt_half = 0.5 * dt; a.mass = c->comps_h[0].mass;
+	a.vel = c->cur.vel; a.pos_out = nullptr; a.pos_build = c->pos_build;
+	timer_start(c, LS1G_T_FORCE);
+	if (nb) {
+		if (vi || c->vi_every_step) nl_force_kernel<true, true, 2><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
+		else if (c->shift6_h[0] != 0.) nl_force_kernel<true, false, 2><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
+		else nl_force_kernel<false, false, 2><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
+	}
+	timer_stop(c, LS1G_T_FORCE, nb ? 1 : 0);
+	CUDA_TRY(cudaGetLastError());
 	timer_start(c, LS1G_T_AUX);
 	size_t nbr = nb; const double* base;
 	const int extra = nb > 2048;

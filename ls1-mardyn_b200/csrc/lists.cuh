@@ -233,7 +233,9 @@ __global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
 //        v += dt/2m F; sum m v^2; v += dt/2m F; r += dt v.  F is not stored, the new position goes to the other position
 //        buffer (other blocks still stage the old one), the displacement since the list build is tracked as in
 //        integrate_kernel.  Saves one pass over r, v, F per step.  partials then hold 8 values per block.
-template <bool COUNT, bool VI, bool FUSE>
+//        FUSE == 2: only the half-kick of THIS step (upd_postF) - the last step of a run and the host-driven ls1g_step, where the
+//        next pre-kick is a separate call; F (and Vi) are stored as well, positions stay where they are.
+template <bool COUNT, bool VI, int FUSE>
 __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 	extern __shared__ __align__(16) double nl_tile[];
 	double* tile = nl_tile;                         // [tcap][3]: x y z of candidate k at tile[3k..3k+2]
@@ -243,10 +245,10 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 	const unsigned blk = a.phase == 2 ? a.bmap[blockIdx.x] : blockIdx.x;
 	if (a.phase == 1 && a.bflag[blk]) return;         // boundary block: runs in phase 2, after the halo positions arrived
 	// speculatively enqueued step whose lists turned out expired: nothing is computed, the host rebuilds and repeats it
-	if (!FUSE && a.guard && *a.guard > a.guard_thr) return;
+	if (FUSE != 1 && a.guard && *a.guard > a.guard_thr) return;
 	int x_first = 0, x_last = 0;
 	const NLBlock b = nl_plan(a, s_beg, s_off, s_len, x_first, x_last, blk);
-	if (FUSE && a.guard && *a.guard > a.guard_thr) {      // the host swaps the two position buffers after every fused launch: carry the positions over
+	if (FUSE == 1 && a.guard && *a.guard > a.guard_thr) {      // the host swaps the two position buffers after every fused launch: carry the positions over
 		const uint32_t i = b.s0 + tid;
 		if (i < b.s1) a.pos_out[i] = a.pos[i];
 		return;
@@ -334,7 +336,19 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 			Fx *= a.eps24; Fy *= a.eps24; Fz *= a.eps24; Vx *= a.eps24; Vy *= a.eps24; Vz *= a.eps24;
 			u6 = a.eps24 * s6;       // + shift6 * pairs: added by the caller's finalize when the potential is shifted (COUNT)
 			if (COUNT) u6 += a.shift6 * (double)np_i;
-			if (FUSE) {
+			if (FUSE == 2) {
+				const double m = a.mass, dtInv2m = a.dt_half / m;         // upd_postF
+				double* vp = a.vel + 3 * (size_t)i;
+				double vx = vp[0], vy = vp[1], vz = vp[2];
+				vx += dtInv2m * Fx; vy += dtInv2m * Fy; vz += dtInv2m * Fz;
+				double v2 = 0.;
+				v2 += vx * vx; v2 += vy * vy; v2 += vz * vz;
+				acc[5] = m * v2; acc[6] = 1.0;
+				vp[0] = vx; vp[1] = vy; vp[2] = vz;
+				double* Fp = a.F + 3 * (size_t)i;
+				Fp[0] = Fx; Fp[1] = Fy; Fp[2] = Fz;
+				if (VI) { double* Vp = a.Vi + 3 * (size_t)i; Vp[0] = 0.5 * Vx; Vp[1] = 0.5 * Vy; Vp[2] = 0.5 * Vz; }
+			} else if (FUSE == 1) {
 				const double m = a.mass;
 				double* vp = a.vel + 3 * (size_t)i;
 				double vx = vp[0], vy = vp[1], vz = vp[2];       // (requesting these before the pair loops costs 16 registers = 2 resident blocks: slower)
@@ -363,7 +377,7 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 			acc[0] = u6; acc[2] = Vx + Vy + Vz; acc[4] = (double)np_i;
 		}
 	}
-	if (FUSE) {          // displacement criterion of the neighbour lists, as in integrate_kernel
+	if (FUSE == 1) {          // displacement criterion of the neighbour lists, as in integrate_kernel
 #pragma unroll
 		for (int o = 16; o > 0; o >>= 1) disp2 = fmax(disp2, __shfl_xor_sync(0xffffffffu, disp2, o));
 		const unsigned long long bits = (unsigned long long)__double_as_longlong(disp2);

@@ -110,6 +110,7 @@ int nl_set_bin_grid(ls1g_ctx* c, int list_mode);
 int k_list_build(ls1g_ctx* c);
 int k_forces_list(ls1g_ctx* c, int count_pairs);
 int k_forces_list_fused(ls1g_ctx* c, double dt, int phase);
+int k_forces_list_post(ls1g_ctx* c, double dt, int vi);
 int k_halo_refresh(ls1g_ctx* c);
 
 // Neighbour-list steps of ls1g_run (lists.cuh).  On entry the pre-kick of step 0 is done.  Runs steps [0, n_steps) unless
@@ -146,6 +147,7 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 	// the integrator is fused into the force kernel on NVE steps (LS1G_FUSE=0 keeps the separate integrate kernel)
 	const char* fe = getenv("LS1G_FUSE");
 	const bool fuse_nve = !thermo && !c->vi_every_step && !(fe && atoi(fe) == 0);
+	const bool post_fuse = !thermo && c->n_ranks == 1 && !(fe && atoi(fe) == 0);      // single rank: the kinetic sums need no all-reduce
 	// multi-rank: overlap the halo refresh with the inner blocks of the force pass (LS1G_OVERLAP=0: exchange first, then one launch)
 	const char* oe = getenv("LS1G_OVERLAP");
 	const bool overlap = c->n_ranks > 1 && !(oe && atoi(oe) == 0);
@@ -239,6 +241,10 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 			} else if (fuse_nve && s + 1 < n_steps) {
 				// NVE step that is not the last of the run: forces + post(s) + pre(s + 1) in one kernel
 				if (!rc) rc = k_forces_list_fused(c, dt, 0);
+				if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s, c->d_scalars, 8 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
+			} else if (post_fuse && s + 1 == n_steps) {
+				// last step of the run (or the single step of ls1g_step): forces + post(s) in one kernel, no pre
+				if (!rc) rc = k_forces_list_post(c, dt, want_vi);
 				if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s, c->d_scalars, 8 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
 			} else {
 				if (!rc) rc = k_forces_list(c, s + 1 == n_steps && want_vi);      // pair statistics + per-molecule virial only for the last step
@@ -379,6 +385,14 @@ extern "C" int ls1g_timers(ls1g_ctx* c, double ms[LS1G_T_COUNT], uint64_t launch
 		if (reset) { c->timers[k].ms = 0.; c->timers[k].launches = 0; }
 	}
 	return 0;
+}
+
+int k_flop_count(ls1g_ctx* c, ls1g_flop_counts* out);
+extern "C" int ls1g_flop_count(ls1g_ctx* c, ls1g_flop_counts* out) {
+	if (!out) LS1G_FAIL("null argument");
+	NEED_REF(c);
+	if (!c->sorted) LS1G_FAIL("ls1g_flop_count: container not sorted (call ls1g_update / ls1g_exchange first)");
+	return k_flop_count(c, out);
 }
 
 extern "C" int ls1g_measure_fp64_peak(int device, double* tflops) {

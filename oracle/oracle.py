@@ -169,3 +169,68 @@ def selective_thermostat(sysm, cid, v, F, q, L, M, limit_energy, Ti):
     L[hot] *= c[:, None]
     M[hot] *= c[:, None]
     return v, F, L, M
+
+
+# FlopCounter multipliers (src/particleContainer/adapter/FlopCounter.cpp:19-75): kernel, macro, sum force/torque, sum macro;
+# order = FlopCounter.h:138-147 (LJ, charge, charge-dipole, dipole, charge-quadrupole, dipole-quadrupole, quadrupole)
+FLOP_MULT = np.array([[15, 4, 12, 2], [10, 2, 12, 2], [34, 3, 15, 2], [101, 5, 18, 3], [52, 2, 15, 2], [121, 2, 18, 2], [131, 2, 18, 2]], dtype=np.float64)
+
+
+def flop_count(sysm, g, cid, r):
+    """numpy restatement of the reference's FlopCounter used as the cell processor of one traversal
+    (FlopCounter.cpp:196-421, FlopCounter.h:150-283).  cid, r: all molecules incl. halo copies (as for forces()).
+    processCell: non-halo cells, pairs i < j; processCellPair over the C08 cell pairs (halo-halo skipped): all i x j pairs,
+    kernel calls always, macro calls unless exactly one cell is halo and index(non-halo) >= index(halo) (:275-311).
+    A molecule pair adds nLJ_i nLJ_j LJ calls when the CENTRE distance^2 < rcLJ^2 and the electrostatic products when < rc^2.
+    Returns dict(molecule_distances, kernel[7], macro[7], flops)."""
+    cid = np.asarray(cid, dtype=np.int64)
+    r = np.ascontiguousarray(r, dtype=np.float64).reshape(-1, 3)
+    cell = cell_indices(g, r).astype(np.int64)
+    cpd = np.array(list(g.cpd), dtype=np.int64)
+    order = np.argsort(cell, kind="stable")
+    start = np.searchsorted(cell[order], np.arange(int(cpd.prod()) + 1))
+    cnt = sysm.counts[cid, :4].astype(np.float64)                      # nLJ, nCharge, nDipole, nQuadrupole per molecule
+
+    def is_halo(c):
+        x, y, z = c % cpd[0], (c // cpd[0]) % cpd[1], c // (cpd[0] * cpd[1])
+        return x == 0 or y == 0 or z == 0 or x == cpd[0] - 1 or y == cpd[1] - 1 or z == cpd[2] - 1
+
+    rc2, rclj2 = sysm.rc * sysm.rc, sysm.rc_lj * sysm.rc_lj
+    mm, kernel, macro = 0.0, np.zeros(7), np.zeros(7)
+
+    def add(ia, ib, same, with_macro):
+        nonlocal mm
+        if len(ia) == 0 or len(ib) == 0:
+            return
+        d = r[ia][:, None, :] - r[ib][None, :, :]
+        d2 = d[..., 0] * d[..., 0] + d[..., 1] * d[..., 1] + d[..., 2] * d[..., 2]
+        use = np.triu(np.ones(d2.shape, dtype=bool), 1) if same else np.ones(d2.shape, dtype=bool)
+        mm += float(use.sum())
+        lj = use & (d2 < rclj2)
+        el = use & (d2 < rc2)
+        a, b = cnt[ia], cnt[ib]
+        k = np.zeros(7)
+        k[0] = (np.outer(a[:, 0], b[:, 0]) * lj).sum()
+        k[1] = (np.outer(a[:, 1], b[:, 1]) * el).sum()
+        k[2] = ((np.outer(a[:, 1], b[:, 2]) + np.outer(a[:, 2], b[:, 1])) * el).sum()
+        k[3] = (np.outer(a[:, 2], b[:, 2]) * el).sum()
+        k[4] = ((np.outer(a[:, 1], b[:, 3]) + np.outer(a[:, 3], b[:, 1])) * el).sum()
+        k[5] = ((np.outer(a[:, 2], b[:, 3]) + np.outer(a[:, 3], b[:, 2])) * el).sum()
+        k[6] = (np.outer(a[:, 3], b[:, 3]) * el).sum()
+        kernel[:] += k
+        if with_macro:
+            macro[:] += k
+
+    for c1, c2, kind in c08_pairs(g).astype(np.int64):
+        i1 = order[start[c1]:start[c1 + 1]]
+        if kind == 0:                                                   # processCell
+            if not is_halo(c1) and len(i1) >= 2:
+                add(i1, i1, True, True)
+            continue
+        i2 = order[start[c2]:start[c2 + 1]]
+        h1, h2 = is_halo(c1), is_halo(c2)
+        if h1 and h2:
+            continue
+        add(i1, i2, False, (not h1 and not h2) or c1 < c2)              # the traversal passes the non-halo cell first
+    flops = 8.0 * mm + 8.0 * kernel.sum() + (kernel * (FLOP_MULT[:, 0] + FLOP_MULT[:, 2])).sum() + (macro * (FLOP_MULT[:, 1] + FLOP_MULT[:, 3])).sum()
+    return dict(molecule_distances=mm, kernel=kernel, macro=macro, flops=float(flops))

@@ -87,6 +87,22 @@ def test_forces_match_reference(name):
     assert scalar_close(virial, w, tol, 1e-3 if name == "vcp_F0" else 1e-300)
 
 
+@pytest.mark.parametrize("name", FORCE_CASES)
+def test_flop_count_matches_reference(name):
+    """ls1g_flop_count (the reference's FlopCounter as a device cell processor, adapter/FlopCounter.cpp:196-421) against the
+    reference's own total for the same cells (fixture 'flops') and the per-potential counts of the oracle restatement: exact"""
+    d = load(name)
+    periodic = bool(d["meta"][0])
+    with container_of(d) as c:
+        _load_into(c, d, periodic)
+        fc = c.flop_count()
+    assert fc["flops"] == float(d["flops"][0])
+    s, g = system_and_grid(d)
+    ref = O.flop_count(s, g, d["f_cid"], d["f_r"])
+    assert fc["molecule_distances"] == ref["molecule_distances"]
+    assert np.array_equal(fc["kernel"], ref["kernel"]) and np.array_equal(fc["macro"], ref["macro"])
+
+
 def test_known_answers_u0_f0():
     """VectorizedCellProcessorTest.cpp:45-134"""
     d = load("vcp_U0")
