@@ -43,7 +43,7 @@ XML = """<?xml version='1.0' encoding='UTF-8'?>
 <mardyn version="20100525">
   <refunits type="SI"><length unit="nm">0.0529177</length><mass unit="u">1000</mass><energy unit="eV">27.2126</energy></refunits>
   <simulation type="MD">
-    <integrator type="Leapfrog"><timestep unit="reduced">{dt}</timestep></integrator>
+    <integrator type="{integrator}"><timestep unit="reduced">{dt}</timestep></integrator>
     <run><currenttime>0</currenttime><production><steps>{steps}</steps></production></run>
     <ensemble type="NVT">
       <temperature unit="reduced">{temp}</temperature>
@@ -55,7 +55,7 @@ XML = """<?xml version='1.0' encoding='UTF-8'?>
     </ensemble>
     <algorithm>
       <parallelisation type="DomainDecomposition"></parallelisation>
-      <datastructure type="LinkedCells"><cellsInCutoffRadius>1</cellsInCutoffRadius></datastructure>
+      <datastructure type="{container}"><cellsInCutoffRadius>1</cellsInCutoffRadius></datastructure>
       <cutoffs type="CenterOfMass"><defaultCutoff unit="reduced">{rc}</defaultCutoff><radiusLJ unit="reduced">{rclj}</radiusLJ></cutoffs>
       <electrostatic type="ReactionField"><epsilon>{epsrf}</epsilon></electrostatic>
     </algorithm>
@@ -89,9 +89,12 @@ def ascii_components(d, ls1g):
     return out
 
 
-def run_reference(d, temp, k, steps, threads, ls1g):
-    exe = B.reference_binary()
-    if exe is None:
+def run_reference(d, temp, k, steps, threads, ls1g, gpu=False):
+    """gpu=False: the reference executable (CPU arm).  gpu=True: the same executable with <datastructure type="GpuLinkedCells"> +
+    <integrator type="GpuLeapfrog"> (MarDynGpu, ls1-mardyn_b200/host/) - the end-to-end arm: ASCII phase space -> host Molecule
+    objects -> device -> steps driven by the reference's time loop -> host Molecule objects"""
+    exe = B.MARDYN_GPU if gpu else B.reference_binary()
+    if exe is None or not os.path.exists(exe):
         return None
     P = ls1g.phasespace
     m, box = replicate(d, k)
@@ -101,17 +104,24 @@ def run_reference(d, temp, k, steps, threads, ls1g):
     with tempfile.TemporaryDirectory() as td:
         P.write_ascii(os.path.join(td, "sample.inp"), ps)
         with open(os.path.join(td, "cfg.xml"), "w") as f:
-            f.write(XML.format(dt=repr(float(d["dt"][0])), steps=steps, temp=repr(temp), L=repr(float(box[0])), components=inner,
+            f.write(XML.format(integrator="GpuLeapfrog" if gpu else "Leapfrog", container="GpuLinkedCells" if gpu else "LinkedCells",
+                               dt=repr(float(d["dt"][0])), steps=steps, temp=repr(temp), L=repr(float(box[0])), components=inner,
                                rc=repr(float(d["rc"][0])), rclj=repr(float(d["rc"][1])), epsrf=repr(float(d["epsRF"][0]))))
         env = dict(os.environ, OMP_NUM_THREADS=str(threads), OMP_PROC_BIND="close", OMP_PLACES="cores")
-        p = subprocess.run([exe, "cfg.xml", "--steps", str(steps)], cwd=td, env=env, capture_output=True, text=True, timeout=3000)
+        p = subprocess.run([exe, "cfg.xml", "--steps", str(steps), "--final-checkpoint=0"], cwd=td, env=env, capture_output=True, text=True, timeout=3000)
     out = p.stdout + p.stderr
-    if p.returncode != 0:
+    if p.returncode != 0 or "Exit code would have been" in out:
         raise RuntimeError("reference MarDyn failed (%d): %s" % (p.returncode, out[-3000:]))
     loop_s = float(re.search(r"Computation in main loop took:\s*([0-9.eE+-]+)", out).group(1))
     fm = re.search(r"Force calculation took:\s*([0-9.eE+-]+)", out)
     n = len(m["id"])
-    return dict(mmups=n * steps / loop_s / 1e6, n=n, loop_s=loop_s, force_s=float(fm.group(1)) if fm else None, binary=os.path.basename(exe))
+    res = dict(mmups=n * steps / loop_s / 1e6, n=n, loop_s=loop_s, force_s=float(fm.group(1)) if fm else None, binary=os.path.basename(exe))
+    g = re.search(r"GpuLinkedCells: (\d+) device steps took ([0-9.eE+-]+) s; upload ([0-9.eE+-]+) s \((\d+) B\); (\d+) host mirror download\(s\) took ([0-9.eE+-]+) s \((\d+) B\)", out)
+    if g:
+        res.update(device_s=float(g.group(2)), upload_s=float(g.group(3)), h2d_bytes=int(g.group(4)), mirror_s=float(g.group(6)), d2h_bytes=int(g.group(7)) + 48 * steps,
+                   selective=int(re.search(r"selective thermostat applied (\d+)", out).group(1)))
+        res["mmups_e2e"] = n * steps / (loop_s + res["upload_s"]) / 1e6
+    return res
 
 
 def main():
@@ -123,6 +133,8 @@ def main():
     ap.add_argument("--ref-replicas", type=int, default=3)
     ap.add_argument("--ref-steps", type=int, default=5)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true", help="skip the MarDynGpu end-to-end arm")
+    ap.add_argument("--e2e-replicas", type=int, default=4, help="replicas per dimension of the MarDynGpu arm (ASCII input: 4 -> 131 072 molecules)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     args = ap.parse_args()
     ls1g = importlib.import_module("ls1-mardyn_b200")
@@ -198,6 +210,16 @@ def main():
                          "frac": round(achieved / peak, 4) if peak > 0 else None, "traffic": None, "flops_per_launch": flops, "kernel_ms": round(force_ms, 4),
                          "model": model},
             "kernel_ms_per_step": {k: round(t["ms"] / args.steps, 4) for k, t in tm.items()}, "clocks": clk}
+    if not args.no_e2e:
+        md = run_reference(d, temp, args.e2e_replicas, args.steps, threads, ls1g, gpu=True)
+        if md is not None:
+            line["e2e"] = {"value": round(md["mmups_e2e"], 2), "unit": "MMUPS", "h2d_bytes_per_step": md["h2d_bytes"] // args.steps,
+                           "d2h_bytes_per_step": md["d2h_bytes"] // args.steps, "steps": args.steps, "n_molecules": md["n"],
+                           "what": "MarDynGpu: the reference executable + unmodified time loop with GpuLinkedCells/GpuLeapfrog on the same example replicated %d^3 "
+                                   "(ASCII phase space read by the reference's own reader); time = upload + the reference's loop timer (last-step mirror inside)" % args.e2e_replicas,
+                           "seconds": {"upload": round(md["upload_s"], 4), "loop": round(md["loop_s"], 4), "of_loop_device_calls": round(md["device_s"], 4),
+                                       "of_loop_final_mirror": round(md["mirror_s"], 4)},
+                           "selective_thermostat_steps": md["selective"]}
     if not args.no_cpu_baseline:
         res = run_reference(d, temp, args.ref_replicas, args.ref_steps, threads, ls1g)
         if res is not None:

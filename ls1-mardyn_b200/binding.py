@@ -55,7 +55,8 @@ class _StepRecord(C.Structure):
 
 
 def lib_path():
-    return os.path.join(_HERE, "libls1g.so")
+    # LS1G_LIB: another build of the same library (A/B timing of two builds on one box); default = the in-tree build
+    return os.environ.get("LS1G_LIB") or os.path.join(_HERE, "libls1g.so")
 
 
 def build(force=False):

@@ -59,7 +59,7 @@ def phase_space_of(d):
                         id=d["in_id"].astype(np.uint64), cid=d["in_cid"].astype(np.uint32), r=d["in_r"], v=d["in_v"], q=d["in_q"], D=d["in_L"])
 
 
-def write_case(dirname, name, steps, variant, temperature=None, replicate=1):
+def write_case(dirname, name, steps, variant, temperature=None, replicate=1, container_options=""):
     """variant: 'cpu' (LinkedCells + Leapfrog), 'fused' / 'operators' (GpuLinkedCells + GpuLeapfrog).  Returns the config path."""
     P = importlib.import_module("ls1-mardyn_b200").phasespace
     d = load(name)
@@ -71,15 +71,29 @@ def write_case(dirname, name, steps, variant, temperature=None, replicate=1):
         P.write_ascii(inp, ps)
     xml = P.components_xml(ps["components"])
     moleculetypes = "\n".join(l for l in xml.splitlines() if not l.startswith("<?xml") and "components" not in l)
-    gpu = variant != "cpu"
+    gpu = variant != "cpu"                    # variant may carry a suffix after "-" to keep file names apart (e.g. "fused-mirror")
     cfg = os.path.join(dirname, "%s_%s.xml" % (name, variant))
     with open(cfg, "w") as f:
         f.write(CONFIG.format(integrator="GpuLeapfrog" if gpu else "Leapfrog", container="GpuLinkedCells" if gpu else "LinkedCells",
-                              container_options="<mode>%s</mode>" % variant if gpu else "", dt=float(d["dt"][0]), steps=steps,
+                              container_options=("<mode>%s</mode>" % variant.split("-")[0] + container_options) if gpu else "", dt=float(d["dt"][0]), steps=steps,
                               temperature=float(TEMPERATURE[name] if temperature is None else temperature),
                               lx=float(ps["box"][0]), ly=float(ps["box"][1]), lz=float(ps["box"][2]), moleculetypes=moleculetypes,
                               inp=os.path.basename(inp), rc=float(d["rc"][0]), rclj=float(d["rc"][1]), eps_rf=float(d["epsRF"][0]),
                               prefix="%s_%s" % (name, variant)))
+    return cfg
+
+
+def write_fcc_case(dirname, cells, steps, gpu, tag):
+    """bench.py's workload (1CLJ fcc from the reference's own MultiObjectGenerator) with a ResultWriter; returns the config path"""
+    import bench
+    L = cells * (4.0 / bench.RHO) ** (1.0 / 3.0)
+    xml = bench.MARDYN_XML.format(dt=bench.DT, steps=steps, temp=bench.TEMP, L=repr(L), rho=bench.RHO, rc=bench.RC,
+                                  integrator="GpuLeapfrog" if gpu else "Leapfrog", container="GpuLinkedCells" if gpu else "LinkedCells")
+    xml = xml.replace("<output></output>", "<output><outputplugin name=\"ResultWriter\"><writefrequency>1</writefrequency><writeprecision>15</writeprecision>"
+                                           "<outputprefix>%s</outputprefix></outputplugin></output>" % tag)
+    cfg = os.path.join(dirname, tag + ".xml")
+    with open(cfg, "w") as f:
+        f.write(xml)
     return cfg
 
 

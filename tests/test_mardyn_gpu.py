@@ -60,3 +60,31 @@ def test_reference_time_loop_on_the_gpu_container(name, variant, tmp_path):
     assert np.max(np.abs(dr)) <= 1e-7 * box[0]
     for k in ("v", "q", "D"):
         assert rel(gpu["final"][k], cpu["final"][k]) <= 1e-6, (k, rel(gpu["final"][k], cpu["final"][k]))
+
+
+@pytest.mark.gpu
+@needs_binaries
+def test_mirror_every_step_changes_nothing(tmp_path):
+    """<mirrorfrequency>1: the host cells are refilled from the device after every post-kick (the reference's thermostat then scales the
+    host copies, the device applies the same betas at the next pre-kick) - the trajectory must be that of the run without mirrors"""
+    a = M.run(M.GPU_EXE, M.write_case(str(tmp_path), "ex_EOX", STEPS, "fused"), STEPS)
+    b = M.run(M.GPU_EXE, M.write_case(str(tmp_path), "ex_EOX", STEPS, "fused-mirror", container_options="<mirrorfrequency>1</mirrorfrequency>"), STEPS)
+    assert a["gpu"]["mirrors"] == 1 and b["gpu"]["mirrors"] == STEPS
+    for col in (2, 4, 6, 7, 9):
+        assert rel(b["res"][:, col], a["res"][:, col]) <= 1e-12, col
+    for k in ("r", "v", "q", "D"):
+        assert rel(b["final"][k], a["final"][k]) <= 1e-10, k
+
+
+@pytest.mark.gpu
+@needs_binaries
+def test_reference_time_loop_fcc_one_million(tmp_path):
+    """bench.py's workload at 64^3 fcc cells (1 048 576 molecules, the reference's own generator, NVT): the neighbour-list path
+    inside the reference's time loop against the CPU reference, 8 steps"""
+    steps = 8
+    threads = min(os.cpu_count() or 1, 16)
+    cpu = M.run(M.REF_EXE, M.write_fcc_case(str(tmp_path), 64, steps, False, "fcc_cpu"), steps, threads=threads)
+    gpu = M.run(M.GPU_EXE, M.write_fcc_case(str(tmp_path), 64, steps, True, "fcc_gpu"), steps, threads=threads)
+    assert cpu["res"].shape == gpu["res"].shape == (steps + 1, 10) and gpu["res"][0, 9] == 1048576
+    for col, what, tol in ((2, "U_pot", 1e-9), (4, "p", 1e-8), (6, "beta_trans", 1e-10), (9, "N", 0.0)):
+        assert rel(gpu["res"][:, col], cpu["res"][:, col]) <= tol, (what, rel(gpu["res"][:, col], cpu["res"][:, col]))
