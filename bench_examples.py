@@ -37,6 +37,9 @@ WORKLOADS = {
     "argon": ("ex_Argon", 0.000633363365, "examples/Argon/200K_18mol_l (1 LJ site)"),
     "co2": ("ex_CO2", 0.00117172223, "examples/CO2/370K_15mol_l (3 LJ + 3 charges)"),
     "eox": ("ex_EOX", 0.0019000901, "examples/EOX/600K_15mol_l (3 LJ + 1 dipole)"),
+    # SURVEY.md cfg C variant (CO2-Merker type, 3 LJ + 1 point quadrupole): the CO2 example's molecules with the three charges
+    # replaced by the point quadrupole of the same charge distribution, Q = sum q_i z_i^2 (synthetic parameters, real geometry)
+    "co2q": ("ex_CO2", 0.00117172223, "examples/CO2/370K_15mol_l geometry as a 3 LJ + 1 quadrupole model (CO2-Merker type)"),
 }
 
 XML = """<?xml version='1.0' encoding='UTF-8'?>
@@ -65,8 +68,17 @@ XML = """<?xml version='1.0' encoding='UTF-8'?>
 """
 
 
-def fixture(name):
-    return np.load(os.path.join(ROOT, "tests", "golden", name + ".npz"))
+def fixture(name, workload=None):
+    d = dict(np.load(os.path.join(ROOT, "tests", "golden", name + ".npz")))
+    if workload == "co2q":
+        ch = d["charge_sites"]
+        Q = float((ch[:, 4] * ch[:, 2] ** 2).sum())
+        d["comp_counts"] = np.array([[3, 0, 0, 1, 2, 0]], dtype=d["comp_counts"].dtype)
+        d["charge_sites"] = np.zeros((0, 5))
+        d["quadrupole_sites"] = np.array([[0.0, 0.0, 0.0, 0.0, 0.0, 1.0, Q]])
+        d.pop("flops", None)                 # no reference count for this variant: ls1g_flop_count supplies it
+        d.pop("upot_virial", None)
+    return d
 
 
 def replicate(d, k):
@@ -139,7 +151,7 @@ def main():
     args = ap.parse_args()
     ls1g = importlib.import_module("ls1-mardyn_b200")
     fx, temp, label = WORKLOADS[args.workload]
-    d = fixture(fx)
+    d = fixture(fx, args.workload)
     dt = float(d["dt"][0])
     threads = B.host_cores()
     metric = "MMUPS (million molecule-updates/s), %s replicated k^3, force+integrate step, NVT" % label
@@ -166,6 +178,7 @@ def main():
         c.set_components(comps, d["mixcoeff"])
         c.add_particles(m["id"], m["cid"], m["r"], m["v"], q=m["q"], L=m["D"])
         c.exchange()
+        fc = c.flop_count()               # the reference's FlopCounter on THIS replicated system, counted on the device
         u0, w0 = c.traverse_cells()
         clocks.start()
         t_wait = time.time()
@@ -189,8 +202,10 @@ def main():
         tm = c.timers(reset=True)
         n_pairs = c.last_pair_count()
         peak = ls1g.fp64_peak_tflops(0)
-    flops = float(d["flops"][0]) * args.replicas ** 3
-    model = "the reference's FlopCounter total for this configuration (fixture 'flops', Newton-3 counts) x replicas^3"
+    flops = fc["flops"]
+    model = ("the reference's FlopCounter (Newton-3 counts) on the replicated system at t = 0, counted on the device by ls1g_flop_count "
+             "(bit-equal to the reference's own count on the golden fixtures)")
+    fixture_flops = float(d["flops"][0]) * args.replicas ** 3 if "flops" in d else None
     if args.workload == "argon" and args.steps > 1:
         # single LJ site: the neighbour-list loop accumulates the per-molecule virial on the last step of a run only; the other
         # launches are priced like the reference prices that case (FlopCounter.cpp:33-39: 35 instead of 41 flop per pair)
@@ -198,7 +213,7 @@ def main():
         model += "; minus 6 flop per pair on the %d of %d launches without per-molecule virial" % (args.steps - 1, args.steps)
     force_ms = tm["force"]["ms"] / max(tm["force"]["launches"], 1)
     achieved = flops / (force_ms * 1e-3) / 1e12 if force_ms > 0 else 0.0
-    ref_u = float(d["upot_virial"][0]) / len(d["in_id"])
+    ref_u = float(d["upot_virial"][0]) / len(d["in_id"]) if "upot_virial" in d else u0 / n
     line = {"metric": metric, "value": round(n * args.steps / (ms * 1e-3) / 1e6, 2), "unit": "MMUPS", "n_gpus": 1, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True, "dtype": "f64",
             "data": "reference example input (golden fixture), replicated",
@@ -208,7 +223,8 @@ def main():
             "gpu_launches": int(sum(t["launches"] for t in tm.values())),
             "roofline": {"bound": "fp64", "achieved": round(achieved, 3), "peak": round(peak, 3), "unit": "TFLOP/s",
                          "frac": round(achieved / peak, 4) if peak > 0 else None, "traffic": None, "flops_per_launch": flops, "kernel_ms": round(force_ms, 4),
-                         "model": model},
+                         "model": model, "reference_fixture_flops_x_replicas3": fixture_flops,
+                         "kernel_calls": {k: float(v) for k, v in zip(("lj", "charge", "charge_dipole", "dipole", "charge_quadrupole", "dipole_quadrupole", "quadrupole"), fc["kernel"]) if v}},
             "kernel_ms_per_step": {k: round(t["ms"] / args.steps, 4) for k, t in tm.items()}, "clocks": clk}
     if not args.no_e2e:
         md = run_reference(d, temp, args.e2e_replicas, args.steps, threads, ls1g, gpu=True)
