@@ -178,7 +178,10 @@ def main():
         c.set_components(comps, d["mixcoeff"])
         c.add_particles(m["id"], m["cid"], m["r"], m["v"], q=m["q"], L=m["D"])
         c.exchange()
-        fc = c.flop_count()               # the reference's FlopCounter on THIS replicated system, counted on the device
+        try:
+            fc = c.flop_count()           # the reference's FlopCounter on THIS replicated system, counted on the device
+        except AttributeError:            # LS1G_LIB pointing at an older build of the library (A/B timing only)
+            fc = dict(flops=float(d["flops"][0]) * args.replicas ** 3, kernel=np.zeros(7))
         u0, w0 = c.traverse_cells()
         clocks.start()
         t_wait = time.time()
