@@ -23,6 +23,8 @@ extern "C" {
 #include <cmath>
 #include <cstdlib>
 #include <memory>
+#include <numeric>
+#include <set>
 #include <string>
 
 #if defined(_OPENMP)
@@ -92,10 +94,55 @@ void GpuLinkedCells::readXML(XMLfileUnits& xmlconfig) {
 		global_log->error_always_output() << "GpuLinkedCells: unknown mode " << mode << " (fused | operators)" << std::endl;
 		Simulation::exit(1);
 	}
-	_mirrorFrequency = static_cast<unsigned long>(xmlconfig.getNodeValue_long("mirrorfrequency", 0));
+	std::string mirror = "auto";
+	xmlconfig.getNodeValue("mirrorfrequency", mirror);
+	if (mirror == "auto") {
+		_mirrorFrequency = mirrorFrequencyFromPlugins(xmlconfig);
+	} else {
+		_mirrorFrequency = static_cast<unsigned long>(xmlconfig.getNodeValue_long("mirrorfrequency", 0));
+	}
 	_device = xmlconfig.getNodeValue_int("device", 0);
-	global_log->info() << "GpuLinkedCells: mode " << mode << ", mirror frequency " << _mirrorFrequency << ", device "
-	                   << _device << std::endl;
+	global_log->info() << "GpuLinkedCells: mode " << mode << ", mirror frequency " << _mirrorFrequency
+	                   << (mirror == "auto" ? " (from the plugins' write frequencies)" : "") << ", device " << _device << std::endl;
+}
+
+// <mirrorfrequency>auto</mirrorfrequency> (the default): the end-of-step plugins that read molecules decide on which steps
+// the host cells must hold a snapshot (PluginBase::endStep, Simulation.cpp:1150-1158).  Plugins that only use Domain
+// values or timers are ignored; known molecule readers contribute their <writefrequency>; any other plugin is assumed to
+// read molecules on every step.  Mirrors are read-only snapshots: a plugin that CHANGES molecules is not supported, and
+// the ones that act before or after the force pass (PluginBase::beforeForces/afterForces) never see molecules.
+unsigned long GpuLinkedCells::mirrorFrequencyFromPlugins(XMLfileUnits& xmlconfig) const {
+	static const std::set<std::string> noMolecules = {"ResultWriter", "SysMonOutput", "TimerWriter", "LoadbalanceWriter",
+	                                                  "DecompWriter", "CommunicationPartnerWriter", "KDTreePrinter"};
+	static const std::set<std::string> readers = {"CheckpointWriter", "MPICheckpointWriter", "XyzWriter", "MmpldWriter",
+	                                              "MmspdWriter", "MmspdBinWriter", "PovWriter", "VISWriter", "MaxWriter",
+	                                              "EnergyLogWriter"};
+	const std::string oldpath = xmlconfig.getcurrentnodepath();
+	unsigned long freq = 0;
+	for (const char* category : {"/mardyn/simulation/output/outputplugin", "/mardyn/simulation/plugin"}) {
+		XMLfile::Query query = xmlconfig.query(category);
+		for (auto it = query.begin(); it; ++it) {
+			xmlconfig.changecurrentnode(it);
+			std::string name;
+			xmlconfig.getNodeValue("@name", name);
+			bool enabled = true;
+			xmlconfig.getNodeValue("@enabled", enabled);
+			if (!enabled || noMolecules.count(name) != 0) continue;
+			unsigned long f = 1;
+			if (readers.count(name) != 0) {
+				const long w = xmlconfig.getNodeValue_long(name == "MmpldWriter" ? "writecontrol/writefrequency" : "writefrequency", 1);
+				f = w > 0 ? static_cast<unsigned long>(w) : 1;
+			} else {
+				global_log->warning() << "GpuLinkedCells: plugin " << name << " is not known to be a read-only end-of-step writer: "
+				                      << "the host cells are refilled on every step for it, changes it makes to molecules are NOT "
+				                      << "carried to the device" << std::endl;
+			}
+			global_log->info() << "GpuLinkedCells: plugin " << name << " reads molecules every " << f << " step(s)" << std::endl;
+			freq = std::gcd(freq, f);
+		}
+	}
+	xmlconfig.changecurrentnode(oldpath);
+	return freq;
 }
 
 bool GpuLinkedCells::rebuild(double bBoxMin[3], double bBoxMax[3]) {

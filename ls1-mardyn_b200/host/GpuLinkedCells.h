@@ -5,7 +5,8 @@
  *   <datastructure type="GpuLinkedCells">
  *     <cellsInCutoffRadius>1</cellsInCutoffRadius>
  *     <mode>fused</mode>                    fused (default): one ls1g_run step per traverseCells; operators: one C-ABI call per reference operator
- *     <mirrorfrequency>0</mirrorfrequency>  every k-th step the host cells are refilled from the device (writers, plugins); 0 = last step only
+ *     <mirrorfrequency>auto</mirrorfrequency>  every k-th step the host cells are refilled from the device (writers, plugins); 0 = last step only;
+ *                                              auto (default) = gcd of the write frequencies of the plugins that read molecules
  *     <device>0</device>
  *   </datastructure>
  *   <integrator type="GpuLeapfrog"> ... </integrator>
@@ -74,6 +75,7 @@ private:
 	double ensureStaging(size_t molecules);
 	void clearHostCells();
 	bool mirrorWanted() const;
+	unsigned long mirrorFrequencyFromPlugins(XMLfileUnits& xmlconfig) const;
 	void printSummary() const;
 	[[noreturn]] void fail(const char* what) const;
 	void chk(int rc, const char* what) const;

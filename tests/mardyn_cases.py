@@ -37,7 +37,7 @@ CONFIG = """<?xml version='1.0' encoding='UTF-8'?>
       <electrostatic type="ReactionField"><epsilon>{eps_rf!r}</epsilon></electrostatic>
     </algorithm>
     <output>
-      <outputplugin name="ResultWriter"><writefrequency>1</writefrequency><writeprecision>15</writeprecision><outputprefix>{prefix}</outputprefix></outputplugin>
+      <outputplugin name="ResultWriter"><writefrequency>1</writefrequency><writeprecision>15</writeprecision><outputprefix>{prefix}</outputprefix></outputplugin>{output_plugins}
     </output>
   </simulation>
 </mardyn>
@@ -59,8 +59,9 @@ def phase_space_of(d):
                         id=d["in_id"].astype(np.uint64), cid=d["in_cid"].astype(np.uint32), r=d["in_r"], v=d["in_v"], q=d["in_q"], D=d["in_L"])
 
 
-def write_case(dirname, name, steps, variant, temperature=None, replicate=1, container_options=""):
-    """variant: 'cpu' (LinkedCells + Leapfrog), 'fused' / 'operators' (GpuLinkedCells + GpuLeapfrog).  Returns the config path."""
+def write_case(dirname, name, steps, variant, temperature=None, replicate=1, container_options="", output_plugins=""):
+    """variant: 'cpu' (LinkedCells + Leapfrog), 'fused' / 'operators' (GpuLinkedCells + GpuLeapfrog); output_plugins: extra
+    <outputplugin> elements.  Returns the config path."""
     P = importlib.import_module("ls1-mardyn_b200").phasespace
     d = load(name)
     ps = phase_space_of(d)
@@ -79,7 +80,7 @@ def write_case(dirname, name, steps, variant, temperature=None, replicate=1, con
                               temperature=float(TEMPERATURE[name] if temperature is None else temperature),
                               lx=float(ps["box"][0]), ly=float(ps["box"][1]), lz=float(ps["box"][2]), moleculetypes=moleculetypes,
                               inp=os.path.basename(inp), rc=float(d["rc"][0]), rclj=float(d["rc"][1]), eps_rf=float(d["epsRF"][0]),
-                              prefix="%s_%s" % (name, variant)))
+                              prefix="%s_%s" % (name, variant), output_plugins=output_plugins))
     return cfg
 
 
@@ -125,8 +126,9 @@ def read_checkpoint_molecules(path):
     return dict(id=a[:, 0].astype(np.uint64), cid=a[:, 1].astype(np.uint32) - 1, r=a[:, 2:5], v=a[:, 5:8], q=a[:, 8:12], D=a[:, 12:15])
 
 
-def run(exe, cfg, steps, threads=None, timeout=1800):
-    """runs MarDyn / MarDynGpu in the config's directory; returns dict(log, res[steps+1, 9], loop_s, final (PhaseSpace))"""
+def run(exe, cfg, steps, threads=None, timeout=1800, check=True):
+    """runs MarDyn / MarDynGpu in the config's directory; returns dict(log, res[steps+1, 9], loop_s, final (PhaseSpace));
+    check=False: a failed run returns dict(log, returncode) instead of raising"""
     P = importlib.import_module("ls1-mardyn_b200").phasespace
     cwd = os.path.dirname(cfg)
     env = dict(os.environ)
@@ -135,6 +137,8 @@ def run(exe, cfg, steps, threads=None, timeout=1800):
     p = subprocess.run([exe, os.path.basename(cfg), "--steps", str(steps), "--final-checkpoint=1"], cwd=cwd, env=env,
                        capture_output=True, text=True, timeout=timeout)
     log = p.stdout + p.stderr
+    if (p.returncode != 0 or "Exit code would have been" in log) and not check:
+        return dict(log=log, returncode=p.returncode)
     if p.returncode != 0 or "Exit code would have been" in log:
         raise RuntimeError("%s %s failed (%d):\n%s" % (os.path.basename(exe), cfg, p.returncode, log[-3000:]))
     prefix = os.path.splitext(os.path.basename(cfg))[0]

@@ -40,6 +40,52 @@ def test_gpu_container_fails_loudly_without_a_device(tmp_path):
         M.run(M.GPU_EXE, M.write_case(str(tmp_path), "ex_Argon", 2, "fused"), 2, threads=2)
 
 
+WRITERS = ('<outputplugin name="CheckpointWriter"><type>ASCII</type><writefrequency>%d</writefrequency><outputprefix>%s</outputprefix>'
+           '<incremental>1</incremental></outputplugin>'
+           '<outputplugin name="XyzWriter"><writefrequency>%d</writefrequency><outputprefix>%s</outputprefix></outputplugin>'
+           '<outputplugin name="SysMonOutput"><writefrequency>1</writefrequency><expression>procloadavg:loadavg1</expression></outputplugin>')
+
+
+@needs_binaries
+def test_mirror_frequency_follows_the_writers(tmp_path):
+    """<mirrorfrequency> defaults to auto: gcd of the write frequencies of the plugins that read molecules (CheckpointWriter 6,
+    XyzWriter 4 -> 2); ResultWriter and SysMonOutput only use Domain values and do not count.  Runs up to the first force pass on CPU."""
+    import torch
+    cfg = M.write_case(str(tmp_path), "ex_Argon", 2, "fused", output_plugins=WRITERS % (6, "cp", 4, "xyz"))
+    out = M.run(M.GPU_EXE, cfg, 2, threads=2, check=False)
+    assert "GpuLinkedCells: plugin CheckpointWriter reads molecules every 6 step(s)" in out["log"]
+    assert "GpuLinkedCells: plugin XyzWriter reads molecules every 4 step(s)" in out["log"]
+    assert "mirror frequency 2 (from the plugins' write frequencies)" in out["log"]
+    assert "plugin ResultWriter" not in out["log"] and "plugin SysMonOutput" not in out["log"]
+    if not torch.cuda.is_available():
+        assert "no CUDA device" in out["log"]
+    # an explicit number wins
+    cfg = M.write_case(str(tmp_path), "ex_Argon", 2, "fused-explicit", container_options="<mirrorfrequency>0</mirrorfrequency>",
+                       output_plugins=WRITERS % (6, "cp", 4, "xyz"))
+    out = M.run(M.GPU_EXE, cfg, 2, threads=2, check=False)
+    assert "mirror frequency 0, device" in out["log"]
+
+
+@pytest.mark.gpu
+@needs_binaries
+def test_checkpoints_written_during_the_run_match_the_reference(tmp_path):
+    """CheckpointWriter every 5 steps of a 10-step EOX run (NVT; the limiter of Domain.cpp:254-311 acts in the first steps): the
+    writer reads the host cells, which the container refills on exactly those steps - both checkpoints equal the CPU reference's"""
+    cpu_dir, gpu_dir = tmp_path / "cpu", tmp_path / "gpu"
+    cpu_dir.mkdir(), gpu_dir.mkdir()
+    M.run(M.REF_EXE, M.write_case(str(cpu_dir), "ex_EOX", 10, "cpu", output_plugins=WRITERS % (5, "cp", 5, "xyz")), 10)
+    gpu = M.run(M.GPU_EXE, M.write_case(str(gpu_dir), "ex_EOX", 10, "fused", output_plugins=WRITERS % (5, "cp", 5, "xyz")), 10)
+    assert "mirror frequency 5 (from the plugins' write frequencies)" in gpu["log"]
+    assert gpu["gpu"]["mirrors"] == 2
+    for k in (0, 1, 2):            # 0 = the start configuration (Simulation::prepare_start), written from the host phase
+        a = M.read_checkpoint_molecules(str(cpu_dir / ("cp-%d.restart.dat" % k)))
+        b = M.read_checkpoint_molecules(str(gpu_dir / ("cp-%d.restart.dat" % k)))
+        ia, ib = np.argsort(a["id"]), np.argsort(b["id"])
+        assert np.array_equal(a["id"][ia], b["id"][ib]) and len(ia) > 0
+        for key in ("r", "v", "q", "D"):
+            assert np.allclose(a[key][ia], b[key][ib], rtol=1e-7, atol=1e-9), (k, key)
+
+
 @pytest.mark.gpu
 @needs_binaries
 @pytest.mark.parametrize("variant", ["fused", "operators"])
