@@ -218,6 +218,23 @@ typedef struct {
 	double flops;                /* _Counts::getTotalFlops() */
 } ls1g_flop_counts;
 int ls1g_flop_count(ls1g_ctx* ctx, ls1g_flop_counts* out);
+/* replaces: RDFCellProcessor as the cell processor of one traversal (adapter/RDFCellProcessor.cpp:18-133) feeding the counters of the
+ * RDF plugin (io/RDF.h:95-160: observeRDFMolecule, observeRDFSite, observeARDFMolecule; MoleculeInterface.h:157-190), as
+ * RDF::afterForces runs it (io/RDF.cpp:573-581).  The counts of this traversal are ADDED to the caller's arrays (RDF::_distribution.local
+ * etc. accumulate over the sampling steps in the same way):
+ *   mol  [nc (nc + 1) / 2][bins]           component pairs (i, j >= i) in the order (0,0) (0,1) ... (1,1) ...   = _distribution.local[i][j-i]
+ *   site [S][S][bins]                       S = all sites of all components, rows in component order, inside a component LJ centres,
+ *                                           charges, dipoles, quadrupoles (Component::numSites order); entry (site0_i + m, site0_j + n) =
+ *                                           _siteDistribution.local[i][j-i][m][n]; may be NULL when no component pair has more than 2 sites
+ *   ardf [nc][nc][bins * angular_bins]      = _ARDFdistribution.local[i][j]; may be NULL when angular_bins <= 1
+ * Needs halo copies in place (after ls1g_exchange, before ls1g_delete_outer).  On a multi-rank context every rank counts the pairs
+ * the reference counts on that rank; the caller sums over ranks (RDF::collectRDF). */
+typedef struct {
+	uint32_t bins;               /* RDF::_bins */
+	uint32_t angular_bins;       /* RDF::_angularBins; <= 1: no angular RDF */
+	double   interval_length;    /* RDF::_intervalLength; pairs beyond interval_length * bins are not counted */
+} ls1g_rdf_params;
+int ls1g_rdf(ls1g_ctx* ctx, const ls1g_rdf_params* params, uint64_t* mol, uint64_t* site, uint64_t* ardf);
 /* pair statistics of the last traverse: molecule pairs inside the cutoff (counted once) */
 int ls1g_last_pair_count(ls1g_ctx* ctx, uint64_t* pairs_in_cutoff);
 

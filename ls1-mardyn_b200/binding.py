@@ -17,7 +17,7 @@ EXPORTS = [
     "ls1g_upload_forces", "ls1g_stream", "ls1g_count", "ls1g_download", "ls1g_update", "ls1g_exchange", "ls1g_traverse", "ls1g_delete_outer",
     "ls1g_integrate_pre", "ls1g_integrate_post", "ls1g_scale", "ls1g_selective_thermostat", "ls1g_run", "ls1g_step", "ls1g_host_alloc", "ls1g_host_free", "ls1g_decomp_box", "ls1g_decomp_grid",
     "ls1g_comm_unique_id", "ls1g_comm_init", "ls1g_allreduce_sum", "ls1g_comm_init_local", "ls1g_exchange_group",
-    "ls1g_timers", "ls1g_measure_fp64_peak", "ls1g_last_pair_count", "ls1g_flop_count",
+    "ls1g_timers", "ls1g_measure_fp64_peak", "ls1g_last_pair_count", "ls1g_flop_count", "ls1g_rdf",
 ]
 
 FIELDS = dict(id=1, cid=2, r=4, v=8, q=16, L=32, F=64, M=128, Vi=256, cell=512)
@@ -47,6 +47,10 @@ class _Fields(C.Structure):
 
 class _FlopCounts(C.Structure):
     _fields_ = [("molecule_distances", C.c_double), ("kernel_calls", C.c_double * 7), ("macro_calls", C.c_double * 7), ("flops", C.c_double)]
+
+
+class _RdfParams(C.Structure):
+    _fields_ = [("bins", C.c_uint32), ("angular_bins", C.c_uint32), ("interval_length", C.c_double)]
 
 
 class _StepRecord(C.Structure):
@@ -211,6 +215,8 @@ class Container:
         mix = np.ascontiguousarray(mixcoeff, dtype=np.float64).ravel()
         _chk(lib().ls1g_set_components(self._ctx, len(comps), arr, _p(mix) if len(mix) else None, int(len(mix))))
         self.n_components = len(comps)
+        self.n_sites = [sum(len(np.reshape(c.get(k, ()), (-1,))) // w for k, w in (("lj", 7), ("charge", 5), ("dipole", 7), ("quadrupole", 7)))
+                        for c in comps]
 
     # -- grid ---------------------------------------------------------------------------------------
     def get_grid(self):
@@ -323,6 +329,17 @@ class Container:
         f = _FlopCounts()
         _chk(lib().ls1g_flop_count(self._ctx, C.byref(f)))
         return dict(molecule_distances=f.molecule_distances, kernel=np.array(list(f.kernel_calls)), macro=np.array(list(f.macro_calls)), flops=f.flops)
+
+    def rdf(self, bins, interval_length, angular_bins=1):
+        """the reference's RDFCellProcessor + RDF counters over the current cells (halo copies in place): dict(mol[nc(nc+1)/2, bins],
+        site[S, S, bins] over the global site rows, ardf[nc, nc, bins*angular_bins]) of this one traversal"""
+        nc, S = self.n_components, int(sum(self.n_sites))
+        mol = np.zeros((nc * (nc + 1) // 2, bins), dtype=np.uint64)
+        site = np.zeros((S, S, bins), dtype=np.uint64)
+        ardf = np.zeros((nc, nc, bins * max(angular_bins, 1)), dtype=np.uint64)
+        p = _RdfParams(int(bins), int(angular_bins), float(interval_length))
+        _chk(lib().ls1g_rdf(self._ctx, C.byref(p), _p(mol), _p(site), _p(ardf) if angular_bins > 1 else None))
+        return dict(mol=mol, site=site, ardf=ardf if angular_bins > 1 else ardf[:, :, :0])
 
     def selective_thermostat(self, limit_trans_energy, temperature):
         """Domain::calculateGlobalValues explosion heuristics (Domain.cpp:254-295): cap U_trans / U_rot per molecule"""

@@ -395,6 +395,15 @@ extern "C" int ls1g_flop_count(ls1g_ctx* c, ls1g_flop_counts* out) {
 	return k_flop_count(c, out);
 }
 
+int k_rdf(ls1g_ctx* c, const ls1g_rdf_params* p, uint64_t* mol, uint64_t* site, uint64_t* ardf);
+extern "C" int ls1g_rdf(ls1g_ctx* c, const ls1g_rdf_params* p, uint64_t* mol, uint64_t* site, uint64_t* ardf) {
+	if (!p || !mol) LS1G_FAIL("null argument");
+	if (p->bins == 0 || !(p->interval_length > 0.)) LS1G_FAIL("ls1g_rdf: bins and interval_length must be positive");
+	NEED_REF(c);
+	if (!c->sorted) LS1G_FAIL("ls1g_rdf: container not sorted (call ls1g_update / ls1g_exchange first)");
+	return k_rdf(c, p, mol, site, ardf);
+}
+
 extern "C" int ls1g_measure_fp64_peak(int device, double* tflops) {
 	if (!tflops) LS1G_FAIL("null argument");
 	return k_fp64_peak(device, tflops);

@@ -7,10 +7,12 @@
 #include "Domain.h"
 #include "Simulation.h"
 #include "ensemble/EnsembleBase.h"
+#include "io/RDF.h"
 #include "molecules/Component.h"
 #include "molecules/Molecule.h"
 #include "particleContainer/adapter/CellProcessor.h"
 #include "particleContainer/adapter/LegacyCellProcessor.h"
+#include "particleContainer/adapter/RDFCellProcessor.h"
 #include "particleContainer/adapter/VectorizedCellProcessor.h"
 #include "utils/Logger.h"
 #include "utils/xmlfileUnits.h"
@@ -64,7 +66,7 @@ void GpuLinkedCells::printSummary() const {
 	global_log->info() << "GpuLinkedCells: " << _steps << " device steps took " << _tDevice << " s; upload "
 	                   << _tUpload << " s (" << _bytesUp << " B); " << _mirrors << " host mirror download(s) took "
 	                   << _tMirror << " s (" << _bytesDown << " B); context creation " << _tContext << " s; selective thermostat applied "
-	                   << _selective << " time(s); first steps [s] " << _tFirstSteps[0] << " " << _tFirstSteps[1] << " "
+	                   << _selective << " time(s); " << _rdfSamples << " RDF sample(s) on the device; first steps [s] " << _tFirstSteps[0] << " " << _tFirstSteps[1] << " "
 	                   << _tFirstSteps[2] << " " << _tFirstSteps[3] << ", slowest step " << _tMaxStep << std::endl;
 }
 
@@ -113,7 +115,8 @@ void GpuLinkedCells::readXML(XMLfileUnits& xmlconfig) {
 // the ones that act before or after the force pass (PluginBase::beforeForces/afterForces) never see molecules.
 unsigned long GpuLinkedCells::mirrorFrequencyFromPlugins(XMLfileUnits& xmlconfig) const {
 	static const std::set<std::string> noMolecules = {"ResultWriter", "SysMonOutput", "TimerWriter", "LoadbalanceWriter",
-	                                                  "DecompWriter", "CommunicationPartnerWriter", "KDTreePrinter"};
+	                                                  "DecompWriter", "CommunicationPartnerWriter", "KDTreePrinter",
+	                                                  "RDF"};      // RDF: its traversal is counted on the device (sampleRDF)
 	static const std::set<std::string> readers = {"CheckpointWriter", "MPICheckpointWriter", "XyzWriter", "MmpldWriter",
 	                                              "MmspdWriter", "MmspdBinWriter", "PovWriter", "VISWriter", "MaxWriter",
 	                                              "EnergyLogWriter"};
@@ -385,7 +388,11 @@ void GpuLinkedCells::traverseCells(CellProcessor& cellProcessor) {
 	const bool forceProcessor = dynamic_cast<VectorizedCellProcessor*>(&cellProcessor) != nullptr ||
 	                            dynamic_cast<LegacyCellProcessor*>(&cellProcessor) != nullptr;
 	if (!forceProcessor) {
-		// counting / sampling processors (FlopCounter, RDFCellProcessor, ...) run on the host cells
+		if (_devicePhase && !_mirrorValid && dynamic_cast<RDFCellProcessor*>(&cellProcessor) != nullptr) {
+			sampleRDF();      // RDF::afterForces (io/RDF.cpp:573-581): the pair histograms are counted on the device
+			return;
+		}
+		// other counting / sampling processors (FlopCounter, ...) run on the host cells
 		if (_devicePhase && !_mirrorValid) {
 			global_log->error_always_output() << "GpuLinkedCells: only the force cell processors run on the device; other cell "
 			                                     "processors need the host cells (host phase or a mirror step)" << std::endl;
@@ -428,6 +435,75 @@ void GpuLinkedCells::traverseCells(CellProcessor& cellProcessor) {
 	}
 	domain->setLocalUpot(upot);          // VectorizedCellProcessor::endTraversal (VectorizedCellProcessor.cpp:155-156)
 	domain->setLocalVirial(virial);
+}
+
+// io/RDF.h:39 declares `friend class RDFTest` for the reference's unit test (io/tests/RDFTest.cpp, which is not part of the
+// executable).  The same door lets the container read the plugin's binning and add the device-side counts of one traversal
+// to its counters; upstream, a public RDF::addLocalCounts(...) would take its place.
+class RDFTest {
+public:
+	struct Shape { unsigned long bins, angularBins; double interval; bool site, angular; };
+	static Shape shape(const RDF& rdf) {
+		return Shape{rdf._bins, rdf._angularBins, rdf._intervalLength, rdf._doCollectSiteRDF, rdf._doARDF};
+	}
+	static void add(RDF& rdf, const std::vector<Component>& comps, const std::vector<uint64_t>& mol,
+	                const std::vector<uint64_t>& site, const std::vector<uint64_t>& ardf) {
+		const size_t nC = comps.size(), bins = rdf._bins;
+		std::vector<size_t> site0(nC + 1, 0);
+		for (size_t i = 0; i < nC; ++i) site0[i + 1] = site0[i] + comps[i].numSites();
+		const size_t S = site0[nC];
+		size_t row = 0;
+		for (size_t i = 0; i < nC; ++i) {
+			for (size_t k = 0; i + k < nC; ++k, ++row) {
+				for (size_t l = 0; l < bins; ++l) rdf._distribution.local[i][k][l] += mol[row * bins + l];
+				const size_t ni = comps[i].numSites(), nj = comps[i + k].numSites();
+				if (ni + nj > 2) {
+					for (size_t m = 0; m < ni; ++m)
+						for (size_t n = 0; n < nj; ++n)
+							for (size_t l = 0; l < bins; ++l)
+								rdf._siteDistribution.local[i][k][m][n][l] += site[((site0[i] + m) * S + site0[i + k] + n) * bins + l];
+				}
+			}
+			if (rdf._doARDF) {
+				const size_t per = bins * rdf._angularBins;
+				for (size_t k = 0; k < nC; ++k)
+					for (size_t l = 0; l < per; ++l) rdf._ARDFdistribution.local[i][k][l] += ardf[(i * nC + k) * per + l];
+			}
+		}
+	}
+};
+
+void GpuLinkedCells::sampleRDF() {
+	RDF* rdf = nullptr;
+	for (PluginBase* p : *global_simulation->getPluginList()) {
+		rdf = dynamic_cast<RDF*>(p);
+		if (rdf != nullptr) break;
+	}
+	if (rdf == nullptr) {
+		global_log->error_always_output() << "GpuLinkedCells: RDFCellProcessor without an RDF plugin" << std::endl;
+		Simulation::exit(1);
+	}
+	const double t0 = wall();
+	const std::vector<Component>& comps = *global_simulation->getEnsemble()->getComponents();
+	const RDFTest::Shape sh = RDFTest::shape(*rdf);
+	size_t S = 0;
+	for (const Component& c : comps) S += c.numSites();
+	const size_t nC = comps.size();
+	std::vector<uint64_t> mol(nC * (nC + 1) / 2 * sh.bins, 0), site(sh.site ? S * S * sh.bins : 0, 0),
+	    ardf(sh.angular ? nC * nC * sh.bins * sh.angularBins : 0, 0);
+	ls1g_rdf_params prm{};
+	prm.bins = static_cast<uint32_t>(sh.bins);
+	prm.angular_bins = sh.angular ? static_cast<uint32_t>(sh.angularBins) : 1;
+	prm.interval_length = sh.interval;
+	// the fused step has already dropped the halo copies (and may sit in the neighbour-list layout): put them back for this
+	// traversal, as they are when the reference's plugin runs (Simulation.cpp:1037-1086)
+	const bool stepDone = _mode == FUSED && _ranThisStep;
+	if (stepDone) chk(ls1g_exchange(_ctx), "ls1g_exchange");
+	chk(ls1g_rdf(_ctx, &prm, mol.data(), site.empty() ? nullptr : site.data(), ardf.empty() ? nullptr : ardf.data()), "ls1g_rdf");
+	if (stepDone) chk(ls1g_delete_outer(_ctx), "ls1g_delete_outer");
+	RDFTest::add(*rdf, comps, mol, site, ardf);
+	++_rdfSamples;
+	_tDevice += wall() - t0;
 }
 
 void GpuLinkedCells::traverseNonInnermostCells(CellProcessor&) {

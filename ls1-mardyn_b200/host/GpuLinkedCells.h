@@ -77,6 +77,7 @@ private:
 	bool mirrorWanted() const;
 	unsigned long mirrorFrequencyFromPlugins(XMLfileUnits& xmlconfig) const;
 	void printSummary() const;
+	void sampleRDF();
 	[[noreturn]] void fail(const char* what) const;
 	void chk(int rc, const char* what) const;
 
@@ -94,7 +95,7 @@ private:
 	uint64_t _n = 0, _rotDOF = 0;
 	// wall clock of the host<->device phases (logged after the last time step)
 	double _tUpload = 0., _tDevice = 0., _tMirror = 0., _tContext = 0.;
-	unsigned long _steps = 0, _mirrors = 0, _selective = 0;
+	unsigned long _steps = 0, _mirrors = 0, _selective = 0, _rdfSamples = 0;
 	double _lastTfactor = 1.0;
 	size_t _bytesUp = 0, _bytesDown = 0, _numCells = 0;
 	double _pendingBt = 1.0, _pendingBr = 1.0;   // fused mode: betas of the previous step, applied inside the next ls1g_step

@@ -234,3 +234,132 @@ def flop_count(sysm, g, cid, r):
         add(i1, i2, False, (not h1 and not h2) or c1 < c2)              # the traversal passes the non-halo cell first
     flops = 8.0 * mm + 8.0 * kernel.sum() + (kernel * (FLOP_MULT[:, 0] + FLOP_MULT[:, 2])).sum() + (macro * (FLOP_MULT[:, 1] + FLOP_MULT[:, 3])).sum()
     return dict(molecule_distances=mm, kernel=kernel, macro=macro, flops=float(flops))
+
+
+def _rotate(q, d):
+    """Quaternion::rotate (Quaternion.cpp:43-62), q = (w, x, y, z) rows, d one body-frame vector"""
+    w, x, y, z = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+    ww, xx, yy, zz = w * w, x * x, y * y, z * z
+    wx, wy, wz, xy, xz, yz = w * x, w * y, w * z, x * y, x * z, y * z
+    return np.stack([(ww + xx - yy - zz) * d[0] + 2. * (xy - wz) * d[1] + 2. * (wy + xz) * d[2],
+                     2. * (wz + xy) * d[0] + (ww - xx + yy - zz) * d[1] + 2. * (yz - wx) * d[2],
+                     2. * (xz - wy) * d[0] + 2. * (wx + yz) * d[1] + (ww - xx - yy + zz) * d[2]], axis=1)
+
+
+def site_table(sysm):
+    """body-frame offsets of all sites in Component::numSites order (LJ, charges, dipoles, quadrupoles; FullMolecule.h:171-186):
+    returns (site0[nc + 1], d[S, 3])"""
+    rows, site0 = [], [0]
+    o = np.zeros(4, dtype=np.int64)
+    for c in sysm.counts:
+        for t, tab in enumerate((sysm.lj, sysm.ch, sysm.di, sysm.qu)):
+            rows.append(tab[o[t]:o[t] + c[t], :3])
+            o[t] += c[t]
+        site0.append(site0[-1] + int(c[:4].sum()))
+    return np.array(site0, dtype=np.int64), (np.concatenate(rows) if rows else np.zeros((0, 3)))
+
+
+def rdf(sysm, g, cid, r, q, bins, interval, angular_bins=1):
+    """numpy restatement of one traversal with the reference's RDFCellProcessor feeding the RDF plugin's counters
+    (adapter/RDFCellProcessor.cpp:18-133, io/RDF.h:95-160, MoleculeInterface.h:157-190).  cid, r, q: all molecules incl. halo copies.
+    processCell (non-halo cells): pairs i < j; processCellPair(c1, c2) with the non-halo cell first: all pairs, except that a
+    (boundary, halo) cell pair only counts when index(c1) < index(c2).  A pair with centre distance^2 dd < rc^2 is observed:
+      molecule RDF  bin floor(sqrt(dd)/interval) of component pair (min, max), skipped when dd > (interval*bins)^2;
+      site RDF      (when either molecule has more than one site) every site pair (m, n), absolute site positions, same binning,
+                    canonical component order; same component and m != n counts [m][n] and [n][m];
+      angular RDF   (angular_bins > 1) cos(phi) between each molecule's body z axis and the centre-centre vector.
+    Returns dict(mol[nc(nc+1)/2, bins] in (i, j-i) order, site[S, S, bins] dense over global site rows, ardf[nc, nc, bins*angular_bins])."""
+    cid = np.asarray(cid, dtype=np.int64)
+    r = np.ascontiguousarray(r, dtype=np.float64).reshape(-1, 3)
+    q = np.ascontiguousarray(q, dtype=np.float64).reshape(-1, 4)
+    nc = len(sysm.counts)
+    cell = cell_indices(g, r).astype(np.int64)
+    cpd = np.array(list(g.cpd), dtype=np.int64)
+    order = np.argsort(cell, kind="stable")
+    start = np.searchsorted(cell[order], np.arange(int(cpd.prod()) + 1))
+    site0, sd = site_table(sysm)
+    S = int(site0[-1])
+    nsites = np.diff(site0)
+    qn = q / np.sqrt((q * q).sum(axis=1))[:, None]                     # FullMolecule::normalizeQuaternion before the site positions
+    pair_row = {}
+    for i in range(nc):
+        for k in range(nc - i):
+            pair_row[(i, i + k)] = len(pair_row)
+    mol = np.zeros((len(pair_row), bins), dtype=np.int64)
+    site = np.zeros((S, S, bins), dtype=np.int64)
+    ardf = np.zeros((nc, nc, bins * angular_bins), dtype=np.int64)
+    rc2 = sysm.rc * sysm.rc
+    max2 = interval * interval * bins * bins
+    aw = 2.0 / angular_bins
+
+    def is_halo(c):
+        x, y, z = c % cpd[0], (c // cpd[0]) % cpd[1], c // (cpd[0] * cpd[1])
+        return x == 0 or y == 0 or z == 0 or x == cpd[0] - 1 or y == cpd[1] - 1 or z == cpd[2] - 1
+
+    def cos_phi(a, b, dd):                                              # a.orientationAngle(b): dr = r_b - r_a
+        qa = q[a]                                                       # (w, x, y, z), not re-normalised (MoleculeInterface.h:167-190)
+        ov = np.stack([2. * (qa[:, 1] * qa[:, 3] + qa[:, 0] * qa[:, 2]), 2. * (qa[:, 2] * qa[:, 3] - qa[:, 0] * qa[:, 1]),
+                       1. - 2. * (qa[:, 1] * qa[:, 1] + qa[:, 2] * qa[:, 2])], axis=1)
+        dr = r[b] - r[a]
+        ov2 = ov[:, 0] * ov[:, 0] + ov[:, 1] * ov[:, 1] + ov[:, 2] * ov[:, 2]
+        c = np.zeros(len(a))
+        for d in range(3):
+            c = c + ov[:, d] * dr[:, d] / np.sqrt(ov2) / np.sqrt(dd)
+        return c
+
+    def observe(a, b):                                                  # molecule1 = a, molecule2 = b (index arrays of equal length)
+        d = r[a] - r[b]                                                 # molecule2.dist2(molecule1): r1 - r2
+        dd = d[:, 0] * d[:, 0] + d[:, 1] * d[:, 1] + d[:, 2] * d[:, 2]
+        keep = dd < rc2
+        a, b, dd = a[keep], b[keep], dd[keep]
+        if len(a) == 0:
+            return
+        inr = ~(dd > max2)
+        lo, hi = np.minimum(cid[a], cid[b]), np.maximum(cid[a], cid[b])
+        rows = np.array([pair_row[(int(x), int(y))] for x, y in zip(lo[inr], hi[inr])], dtype=np.int64)
+        np.add.at(mol, (rows, np.floor(np.sqrt(dd[inr]) / interval).astype(np.int64)), 1)
+        if angular_bins > 1 and inr.any():
+            a2, b2, d2 = a[inr], b[inr], dd[inr]
+            c1, c2 = cos_phi(a2, b2, d2), cos_phi(b2, a2, d2)
+            rb = np.floor(np.sqrt(d2) / interval).astype(np.int64)
+            np.add.at(ardf, (cid[a2], cid[b2], rb * angular_bins + np.floor((-c1 + 1.) / aw).astype(np.int64)), 1)
+            np.add.at(ardf, (cid[b2], cid[a2], rb * angular_bins + np.floor((-c2 + 1.) / aw).astype(np.int64)), 1)
+        for ci in range(nc):
+            for cj in range(nc):
+                if nsites[ci] + nsites[cj] <= 2:
+                    continue
+                sel = (cid[a] == ci) & (cid[b] == cj)
+                if not sel.any():
+                    continue
+                aa, bb = a[sel], b[sel]
+                for m in range(nsites[ci]):
+                    pa = r[aa] + _rotate(qn[aa], sd[site0[ci] + m])
+                    for n in range(nsites[cj]):
+                        pb = r[bb] + _rotate(qn[bb], sd[site0[cj] + n])
+                        ds = pa - pb
+                        d2 = ds[:, 0] * ds[:, 0] + ds[:, 1] * ds[:, 1] + ds[:, 2] * ds[:, 2]
+                        ok = ~(d2 > max2)
+                        bn = np.floor(np.sqrt(d2[ok]) / interval).astype(np.int64)
+                        ga, gb = (site0[ci] + m, site0[cj] + n) if ci <= cj else (site0[cj] + n, site0[ci] + m)
+                        np.add.at(site, (np.full(len(bn), ga), np.full(len(bn), gb), bn), 1)
+                        if ci == cj and m != n:
+                            np.add.at(site, (np.full(len(bn), gb), np.full(len(bn), ga), bn), 1)
+
+    for c1, c2, kind in c08_pairs(g).astype(np.int64):
+        i1 = order[start[c1]:start[c1 + 1]]
+        if kind == 0:
+            if not is_halo(c1) and len(i1) >= 2:
+                ia, ib = np.triu_indices(len(i1), 1)
+                observe(i1[ia], i1[ib])
+            continue
+        i2 = order[start[c2]:start[c2 + 1]]
+        h1, h2 = is_halo(c1), is_halo(c2)
+        if (h1 and h2) or len(i1) == 0 or len(i2) == 0:
+            continue
+        if h1:                                                          # the traversal passes the non-halo cell first
+            c1, c2, i1, i2, h1, h2 = c2, c1, i2, i1, h2, h1
+        if h2 and not c1 < c2:
+            continue
+        ia, ib = np.meshgrid(np.arange(len(i1)), np.arange(len(i2)), indexing="ij")
+        observe(i1[ia.ravel()], i2[ib.ravel()])
+    return dict(mol=mol, site=site, ardf=ardf)

@@ -13,6 +13,7 @@
 //
 //   ref_driver run <file.inp> <rc> <rcLJ> <open|periodic> <ctor|rebuild> <steps> <dt> <out.bin> [epsRF]
 //   ref_driver cellindex <L0> <L1> <L2> <rc> <ctor|rebuild> <points.bin> <out.bin>
+//   ref_driver rdf <file.inp> <rc> <open|periodic> <ctor|rebuild> <bins> <intervallength> <angularbins> <out.bin>
 
 #include <cstdio>
 #include <cstdlib>
@@ -37,6 +38,8 @@
 #include "particleContainer/adapter/ParticlePairs2PotForceAdapter.h"
 #include "particleContainer/adapter/FlopCounter.h"
 #include "integrators/Leapfrog.h"
+#include "io/RDF.h"
+#include "particleContainer/adapter/RDFCellProcessor.h"
 #include "utils/Logger.h"
 
 using Log::global_log;
@@ -280,12 +283,96 @@ static int cmdCellIndex(int argc, char** argv) {
 	return 0;
 }
 
+// ------------------------------------------------------------------- rdf ----
+// RDF as the reference's own unit test drives it (src/io/tests/RDFTest.cpp:41-90): the plugin object is configured through
+// the friend declaration `friend class RDFTest` (src/io/RDF.h:39), one traversal with RDFCellProcessor, local counters dumped.
+class RDFTest {
+public:
+	static int run(int argc, char** argv) {
+		if (argc < 10) { fprintf(stderr, "usage: rdf inp rc open|periodic ctor|rebuild bins intervallength angularbins out\n"); return 2; }
+		std::string inp = argv[2];
+		double rc = atof(argv[3]);
+		bool periodic = std::string(argv[4]) == "periodic";
+		std::string how = argv[5];
+		unsigned long bins = strtoul(argv[6], nullptr, 10);
+		double interval = atof(argv[7]);
+		unsigned long abins = strtoul(argv[8], nullptr, 10);
+		g_out = fopen(argv[9], "wb");
+
+		Simulation* sim = new Simulation();
+		Domain* domain = sim->getDomain();
+		DomainDecompBase* decomp = &sim->domainDecomposition();
+		sim->setcutoffRadius(rc);
+		sim->setLJCutoff(rc);
+		ASCIIReader reader;
+		reader.setPhaseSpaceHeaderFile(inp);
+		reader.setPhaseSpaceFile(inp);
+		reader.readPhaseSpaceHeader(domain, 0.001);
+		double bmin[3], bmax[3];
+		for (int d = 0; d < 3; ++d) { bmin[d] = decomp->getBoundingBoxMin(d, domain); bmax[d] = decomp->getBoundingBoxMax(d, domain); }
+		LinkedCells* lc = makeContainer(bmin, bmax, rc, how);
+		reader.readPhaseSpace(lc, domain, decomp);
+		lc->deleteOuterParticles();
+		lc->update();
+		lc->updateMoleculeCaches();
+		dumpComponents(domain);
+		putd("rc", std::vector<double>{rc, rc});
+		if (periodic) { decomp->exchangeMolecules(lc, domain); lc->updateMoleculeCaches(); }
+		{
+			int* bw = lc->getBoxWidthInNumCells();
+			puti("cells_per_dim", std::vector<int64_t>{bw[0] + 2, bw[1] + 2, bw[2] + 2});
+		}
+		dumpRows("pre_", snapshot(lc), false);
+
+		std::vector<Component>* comps = global_simulation->getEnsemble()->getComponents();
+		RDF rdf;
+		rdf._intervalLength = interval;
+		rdf._bins = bins;
+		rdf._angularBins = abins;
+		rdf._components = comps;
+		rdf._writeFrequency = 25000;
+		rdf._outputPrefix = "out";
+		rdf._readConfig = true;
+		rdf.init();
+		rdf.tickRDF();
+		RDFCellProcessor cp(rc, &rdf);
+		lc->traverseCells(cp);
+
+		const size_t nC = comps->size();
+		std::vector<size_t> site0(nC + 1, 0);
+		for (size_t i = 0; i < nC; ++i) site0[i + 1] = site0[i] + (*comps)[i].numSites();
+		const size_t S = site0[nC];
+		std::vector<int64_t> mol, site(S * S * bins, 0), ardf;
+		for (size_t i = 0; i < nC; ++i)
+			for (size_t k = 0; i + k < nC; ++k) {
+				for (size_t l = 0; l < bins; ++l) mol.push_back((int64_t)rdf._distribution.local[i][k][l]);
+				const size_t ni = (*comps)[i].numSites(), nj = (*comps)[i + k].numSites();
+				if (ni + nj > 2)
+					for (size_t m = 0; m < ni; ++m)
+						for (size_t n = 0; n < nj; ++n)
+							for (size_t l = 0; l < bins; ++l)
+								site[((site0[i] + m) * S + site0[i + k] + n) * bins + l] = (int64_t)rdf._siteDistribution.local[i][k][m][n][l];
+			}
+		if (rdf._doARDF)
+			for (size_t i = 0; i < nC; ++i)
+				for (size_t k = 0; k < nC; ++k)
+					for (size_t l = 0; l < bins * abins; ++l) ardf.push_back((int64_t)rdf._ARDFdistribution.local[i][k][l]);
+		puti("rdf_mol", mol, {mol.size() / bins, bins});
+		puti("rdf_site", site, {S, S, bins});
+		puti("rdf_ardf", ardf, {ardf.size()});
+		putd("rdf_params", std::vector<double>{(double)bins, interval, (double)abins, rdf._doCollectSiteRDF ? 1.0 : 0.0});
+		fclose(g_out);
+		return 0;
+	}
+};
+
 int main(int argc, char** argv) {
 	global_log = new Log::Logger(Log::Error);
-	if (argc < 2) { fprintf(stderr, "usage: ref_driver run|cellindex ...\n"); return 2; }
+	if (argc < 2) { fprintf(stderr, "usage: ref_driver run|cellindex|rdf ...\n"); return 2; }
 	std::string cmd = argv[1];
 	if (cmd == "run") return cmdRun(argc, argv);
 	if (cmd == "cellindex") return cmdCellIndex(argc, argv);
+	if (cmd == "rdf") return RDFTest::run(argc, argv);
 	fprintf(stderr, "unknown command %s\n", cmd.c_str());
 	return 2;
 }

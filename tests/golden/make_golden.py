@@ -12,6 +12,9 @@ Cases
                  grid (LinkedCells::rebuild), plus N leapfrog steps NVE.
   ex_<name>      shipped examples (Argon 1CLJ, CO2 3LJ+3q, EOX 3LJ+dipole), periodic, rebuild grid, 5 steps.
   cellindex_*    adversarial points on/near cell borders -> LinkedCells::getCellIndexOfPoint.
+  rdf_<name>     RDFCellProcessor + RDF plugin counters of one traversal (molecule pairs per component pair, site-site, angular),
+                 driven like the reference's RDFTest (io/tests/RDFTest.cpp: 1clj-regular-2x2x3, 1clj-regular-12x12x12, 2clj-regular
+                 with its expected bin counts) and on the shipped examples / multi-component inputs.   --rdf-only writes just these.
 """
 import os
 import subprocess
@@ -125,7 +128,45 @@ def cellindex_case(name, L, rc, how, seed):
     print(name, os.path.getsize(path) // 1024, "KiB", "cpd", d["cells_per_dim"])
 
 
+RDF = [  # (name, file, rc, periodic, how, bins, intervallength, angular bins)
+    ("1clj_2x2x3_open", os.path.join(TI, "1clj-regular-2x2x3.inp"), 1.8, False, "ctor", 100, 0.018, 1),      # RDFTest.cpp:52-90
+    ("1clj_2x2x3", os.path.join(TI, "1clj-regular-2x2x3.inp"), 1.8, True, "ctor", 100, 0.018, 1),            # RDFTest.cpp:92-120
+    ("1clj_12x12x12", os.path.join(TI, "1clj-regular-12x12x12.inp"), 1.8, True, "ctor", 100, 0.018, 1),      # RDFTest.cpp:124-160
+    ("2clj", os.path.join(TI, "2clj-regular.inp"), 3.5, True, "ctor", 101, 0.05, 1),                         # RDFTest.cpp:205-260
+    ("ex_Argon", os.path.join(EX, "Argon/200K_18mol_l/Argon_200K_18mol_l.inp"), 33.0702, True, "rebuild", 64, 0.6, 1),
+    ("ex_CO2", os.path.join(EX, "CO2/370K_15mol_l/CO2_370K_15mol_l.inp"), 33.0702, True, "rebuild", 50, 0.5, 8),
+    ("ex_EOX", os.path.join(EX, "EOX/600K_15mol_l/EOX_600K_15mol_l.inp"), 33.0702, True, "rebuild", 40, 0.9, 5),
+    ("Multi", os.path.join(TI, "VectorizationMultiComponentMultiPotentials.inp"), 35.0, True, "rebuild", 30, 1.0, 4),
+    ("DipoleQuadrupole", os.path.join(TI, "VectorizationDipoleQuadrupole.inp"), 35.0, False, "ctor", 25, 1.5, 6),
+]
+
+
+def rdf_case(name, inp, rc, periodic, how, bins, interval, abins):
+    with tempfile.TemporaryDirectory() as td:
+        out = os.path.join(td, "o.bin")
+        run_driver(["rdf", inp, rc, "periodic" if periodic else "open", how, bins, interval, abins, out])
+        d = read_dump(out)
+    keep = {k: d[k] for k in ("comp_counts", "comp_scalars", "lj_sites", "charge_sites", "dipole_sites", "quadrupole_sites",
+                              "mixcoeff", "epsRF", "box", "rc", "cells_per_dim", "rdf_params")}
+    halo = is_halo(d["pre_cell"], d["cells_per_dim"])
+    keep["f_owned"] = (~halo).astype(np.uint8)
+    for k in ("id", "cid", "cell", "r", "q"):        # all molecules incl. halo copies, container order (as the f_ rows of the force cases)
+        keep["f_" + k] = d["pre_" + k]
+    keep["rdf_mol"] = d["rdf_mol"].astype(np.uint32)
+    keep["rdf_site"] = d["rdf_site"].astype(np.uint32)
+    keep["rdf_ardf"] = d["rdf_ardf"].astype(np.uint32)
+    keep["meta"] = np.array([int(periodic), 1 if how == "ctor" else 0, 0], dtype=np.int64)
+    path = os.path.join(HERE, "rdf_" + name + ".npz")
+    np.savez_compressed(path, **keep)
+    print("rdf_" + name, os.path.getsize(path) // 1024, "KiB", "pairs", int(keep["rdf_mol"].sum()), "site", int(keep["rdf_site"].sum()),
+          "ardf", int(keep["rdf_ardf"].sum()))
+
+
 def main():
+    if "--rdf-only" in sys.argv:
+        for c in RDF:
+            rdf_case(*c)
+        return
     for name, f, rc in VCP:
         case("vcp_" + name, os.path.join(TI, f), rc, False, "ctor", 0, 0.001)
     for name, f, rc, steps, dt in PER:
@@ -136,6 +177,8 @@ def main():
     cellindex_case("cellindex_rebuild_b", [22.8421, 17.3, 30.0], 2.5, "rebuild", 2)
     cellindex_case("cellindex_ctor_a", [10.0, 10.0, 10.0], 1.0, "ctor", 3)
     cellindex_case("cellindex_ctor_b", [7.7, 9.1, 13.3], 1.1, "ctor", 4)
+    for c in RDF:
+        rdf_case(*c)
 
 
 if __name__ == "__main__":

@@ -21,7 +21,7 @@ CONFIG = """<?xml version='1.0' encoding='UTF-8'?>
   <refunits type="SI"><length unit="nm">0.0529177</length><mass unit="u">1000</mass><energy unit="eV">27.2126</energy></refunits>
   <simulation type="MD">
     <integrator type="{integrator}"><timestep unit="reduced">{dt!r}</timestep></integrator>
-    <run><currenttime>0</currenttime><production><steps>{steps}</steps></production></run>
+    <run><currenttime>0</currenttime>{equilibration}<production><steps>{steps}</steps></production></run>
     <ensemble type="NVT">
       <temperature unit="reduced">{temperature!r}</temperature>
       <domain type="box"><lx>{lx!r}</lx><ly>{ly!r}</ly><lz>{lz!r}</lz></domain>
@@ -59,9 +59,9 @@ def phase_space_of(d):
                         id=d["in_id"].astype(np.uint64), cid=d["in_cid"].astype(np.uint32), r=d["in_r"], v=d["in_v"], q=d["in_q"], D=d["in_L"])
 
 
-def write_case(dirname, name, steps, variant, temperature=None, replicate=1, container_options="", output_plugins=""):
+def write_case(dirname, name, steps, variant, temperature=None, replicate=1, container_options="", output_plugins="", equilibration=None):
     """variant: 'cpu' (LinkedCells + Leapfrog), 'fused' / 'operators' (GpuLinkedCells + GpuLeapfrog); output_plugins: extra
-    <outputplugin> elements.  Returns the config path."""
+    <outputplugin> elements; equilibration: <run><equilibration><steps> (sampling plugins start after it, default 20000).  Returns the config path."""
     P = importlib.import_module("ls1-mardyn_b200").phasespace
     d = load(name)
     ps = phase_space_of(d)
@@ -80,7 +80,8 @@ def write_case(dirname, name, steps, variant, temperature=None, replicate=1, con
                               temperature=float(TEMPERATURE[name] if temperature is None else temperature),
                               lx=float(ps["box"][0]), ly=float(ps["box"][1]), lz=float(ps["box"][2]), moleculetypes=moleculetypes,
                               inp=os.path.basename(inp), rc=float(d["rc"][0]), rclj=float(d["rc"][1]), eps_rf=float(d["epsRF"][0]),
-                              prefix="%s_%s" % (name, variant), output_plugins=output_plugins))
+                              prefix="%s_%s" % (name, variant), output_plugins=output_plugins,
+                              equilibration="" if equilibration is None else "<equilibration><steps>%d</steps></equilibration>" % equilibration))
     return cfg
 
 

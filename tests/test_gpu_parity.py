@@ -532,3 +532,63 @@ def test_decomposed_matches_single_rank(n_ranks, case):
         assert np.abs(out[k] - ref[k]).max() <= tol * max(np.abs(ref[k]).max(), 1e-300), k
     assert vec_rel_err(out["F"], ref["F"]) < 100 * tol
     assert np.all(np.abs(rec[:, :4] - ref_rec[:, :4]) <= 100 * tol * np.maximum(np.abs(ref_rec[:, :4]).max(axis=0), 1e-300))
+
+
+@pytest.mark.parametrize("name", golden_cases("rdf_"))
+def test_rdf_matches_reference(name):
+    """ls1g_rdf (the reference's RDFCellProcessor + RDF counters as a device cell processor, adapter/RDFCellProcessor.cpp:18-133,
+    io/RDF.h:95-160) against the reference's own counters after one traversal of the same cells - among them the inputs and
+    expected counts of its RDFTest - and against the oracle restatement: molecule, site-site and angular histograms, every bin exact"""
+    d = load(name)
+    own = d["f_owned"].astype(bool)
+    order = np.argsort(d["f_id"][own])
+    n = int(own.sum())
+    bins, interval, abins, _ = d["rdf_params"]
+    with container_of(d) as c:
+        c.add_particles(d["f_id"][own][order].astype(np.uint64), d["f_cid"][own][order].astype(np.uint32), d["f_r"][own][order],
+                        np.zeros((n, 3)), d["f_q"][own][order], np.zeros((n, 3)))
+        if d["meta"][0]:
+            c.exchange()
+        else:
+            c.update()
+        res = c.rdf(int(bins), float(interval), int(abins))
+        again = c.rdf(int(bins), float(interval), int(abins))
+    assert np.array_equal(res["mol"], d["rdf_mol"])
+    assert np.array_equal(res["site"], d["rdf_site"])
+    if abins > 1:
+        assert np.array_equal(res["ardf"].ravel(), d["rdf_ardf"])
+    for k in res:
+        assert np.array_equal(res[k], again[k])
+    s, g = system_and_grid(d)
+    ref = O.rdf(s, g, d["f_cid"], d["f_r"], d["f_q"], int(bins), float(interval), int(abins))
+    assert np.array_equal(res["mol"], ref["mol"]) and np.array_equal(res["site"], ref["site"])
+
+
+def test_rdf_of_the_bench_lattice_after_steps():
+    """fcc 1CLJ (bench.py's workload, 16^3 cells): ls1g_rdf after 10 device-resident steps (leaves the neighbour-list layout, halo copies
+    rebuilt) equals the oracle on the downloaded state; the forces survive the re-sort (the next step continues the same trajectory)"""
+    r, v, box = fcc_lattice(16, seed=21)
+    ids = np.arange(len(r))
+
+    def fresh():
+        c = ls1g.Container(box, 2.5)
+        c.set_components([ls1g.lj_component()])
+        c.add_particles(ids, np.zeros(len(ids), dtype=np.uint32), r, v)
+        c.exchange()
+        c.traverse_cells()
+        return c
+
+    with fresh() as c, fresh() as plain:
+        c.run(10, 0.002)
+        plain.run(10, 0.002)
+        c.exchange()
+        res = c.rdf(100, 0.025)
+        allm = c.download(("id", "cid", "r"), include_halo=True)
+        c.delete_outer()
+        a, b = c.run(5, 0.002), plain.run(5, 0.002)
+    assert np.allclose(a, b, rtol=1e-12, atol=0)
+    s = O.System.single_lj(rc=2.5)
+    g = O.grid([0, 0, 0], box, 2.5, 0)
+    q = np.tile(np.array([1.0, 0, 0, 0]), (len(allm["id"]), 1))
+    ref = O.rdf(s, g, allm["cid"], allm["r"], q, 100, 0.025)
+    assert res["mol"].sum() > 20 * len(ids) and np.array_equal(res["mol"], ref["mol"])

@@ -86,6 +86,46 @@ def test_checkpoints_written_during_the_run_match_the_reference(tmp_path):
             assert np.allclose(a[key][ia], b[key][ib], rtol=1e-7, atol=1e-9), (k, key)
 
 
+RDF_PLUGIN = ('<outputplugin name="RDF"><writefrequency>3</writefrequency><samplingfrequency>1</samplingfrequency><outputprefix>rdf</outputprefix>'
+              '<bins>50</bins><intervallength>0.5</intervallength><angularbins>4</angularbins></outputplugin>')
+
+
+def _rdf_tables(dirname):
+    out = {}
+    for f in sorted(os.listdir(dirname)):
+        if f.endswith(".rdf") or f.endswith(".ardf"):
+            rows = [l.split() for l in open(os.path.join(dirname, f)) if l.strip() and not l.lstrip().startswith("#")]
+            out[f] = np.array([[float(x) for x in row] for row in rows])
+    return out
+
+
+@pytest.mark.gpu
+@needs_binaries
+@pytest.mark.parametrize("variant", ["fused", "operators"])
+def test_rdf_plugin_samples_on_the_device(variant, tmp_path):
+    """<outputplugin name="RDF"> (molecule, site-site and angular RDF of CO2, sampled every step, written every 3rd) in the reference's
+    unmodified loop: RDF::afterForces hands its RDFCellProcessor to traverseCells, the container counts the pairs on the device
+    (ls1g_rdf) and adds them to the plugin's counters; the files the plugin writes equal the CPU reference's"""
+    cpu_dir, gpu_dir = tmp_path / "cpu", tmp_path / "gpu"
+    cpu_dir.mkdir(), gpu_dir.mkdir()
+    M.run(M.REF_EXE, M.write_case(str(cpu_dir), "ex_CO2", 6, "cpu", output_plugins=RDF_PLUGIN, equilibration=0), 6)
+    gpu = M.run(M.GPU_EXE, M.write_case(str(gpu_dir), "ex_CO2", 6, variant, output_plugins=RDF_PLUGIN, equilibration=0), 6)
+    assert "6 RDF sample(s) on the device" in gpu["log"]
+    assert "mirror frequency 0 (from the plugins' write frequencies)" in gpu["log"]
+    a, b = _rdf_tables(str(cpu_dir)), _rdf_tables(str(gpu_dir))
+    assert len(a) == 4 and sorted(a) == sorted(b)          # rdf_0-0.{3,6}.rdf and .ardf
+    same = total = 0
+    for f in a:
+        assert a[f].shape == b[f].shape and a[f].shape[0] >= 50, f
+        assert np.abs(a[f]).sum() > 0
+        # a pair within 1e-8 of a bin border may land in the neighbouring bin on one side
+        scale = np.maximum(np.abs(a[f]).max(axis=0), 1e-300)
+        assert (np.abs(a[f] - b[f]) / scale).max() < 2e-3, f
+        same += int((a[f] == b[f]).sum())
+        total += a[f].size
+    assert same > 0.99 * total
+
+
 @pytest.mark.gpu
 @needs_binaries
 @pytest.mark.parametrize("variant", ["fused", "operators"])
