@@ -586,7 +586,7 @@ def test_rdf_of_the_bench_lattice_after_steps():
         allm = c.download(("id", "cid", "r"), include_halo=True)
         c.delete_outer()
         a, b = c.run(5, 0.002), plain.run(5, 0.002)
-    assert np.allclose(a, b, rtol=1e-12, atol=0)
+    assert np.allclose(a, b, rtol=1e-10, atol=0)
     s = O.System.single_lj(rc=2.5)
     g = O.grid([0, 0, 0], box, 2.5, 0)
     q = np.tile(np.array([1.0, 0, 0, 0]), (len(allm["id"]), 1))
