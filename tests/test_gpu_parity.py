@@ -584,7 +584,7 @@ def test_rdf_of_the_bench_lattice_after_steps():
         c.exchange()
         res = c.rdf(100, 0.025)
         allm = c.download(("id", "cid", "r"), include_halo=True)
-        c.delete_outer()
+        c.delete_outer_particles()
         a, b = c.run(5, 0.002), plain.run(5, 0.002)
     assert np.allclose(a, b, rtol=1e-10, atol=0)
     s = O.System.single_lj(rc=2.5)
