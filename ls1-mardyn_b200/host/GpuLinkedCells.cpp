@@ -96,6 +96,19 @@ void GpuLinkedCells::readXML(XMLfileUnits& xmlconfig) {
 		global_log->error_always_output() << "GpuLinkedCells: unknown mode " << mode << " (fused | operators)" << std::endl;
 		Simulation::exit(1);
 	}
+	// per-molecule host passes of the time loop that would silently find empty cells in the device phase
+	{
+		const std::string oldpath = xmlconfig.getcurrentnodepath();
+		std::string lrc;
+		if (xmlconfig.changecurrentnode("/mardyn/simulation/algorithm/longrange")) xmlconfig.getNodeValue("@type", lrc);
+		xmlconfig.changecurrentnode(oldpath);
+		const bool tempControl = xmlconfig.query("/mardyn/simulation/algorithm/thermostats/thermostat[@type='TemperatureControl']").card() > 0;
+		if (lrc == "planar" || tempControl) {
+			global_log->error_always_output() << "GpuLinkedCells: " << (tempControl ? "the TemperatureControl thermostat" : "the planar long-range correction")
+			                                  << " works on host molecules inside the time loop and is not supported" << std::endl;
+			Simulation::exit(1);
+		}
+	}
 	std::string mirror = "auto";
 	xmlconfig.getNodeValue("mirrorfrequency", mirror);
 	if (mirror == "auto") {

@@ -86,6 +86,21 @@ def test_checkpoints_written_during_the_run_match_the_reference(tmp_path):
             assert np.allclose(a[key][ia], b[key][ib], rtol=1e-7, atol=1e-9), (k, key)
 
 
+@needs_binaries
+@pytest.mark.parametrize("what,xml", [
+    ("planar long-range correction", '<longrange type="planar"><slabs>10</slabs></longrange></algorithm>'),
+    ("TemperatureControl thermostat", '<thermostats><thermostat type="TemperatureControl"></thermostat></thermostats></algorithm>')])
+def test_host_side_per_molecule_passes_are_rejected_at_start_up(what, xml, tmp_path):
+    """features of the reference that loop over host molecules inside the time loop would find empty cells in the device phase:
+    the container ends the run while reading the configuration instead of skipping them silently"""
+    cfg = M.write_case(str(tmp_path), "ex_Argon", 2, "fused")
+    text = open(cfg).read().replace("</algorithm>", xml)
+    open(cfg, "w").write(text)
+    out = M.run(M.GPU_EXE, cfg, 2, threads=2, check=False)
+    assert "GpuLinkedCells: the %s works on host molecules inside the time loop and is not supported" % what in out["log"]
+    assert "device context created" not in out["log"]
+
+
 RDF_PLUGIN = ('<outputplugin name="RDF"><writefrequency>3</writefrequency><samplingfrequency>1</samplingfrequency><outputprefix>rdf</outputprefix>'
               '<bins>50</bins><intervallength>0.5</intervallength><angularbins>4</angularbins></outputplugin>')
 
