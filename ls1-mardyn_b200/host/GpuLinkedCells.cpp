@@ -67,7 +67,8 @@ void GpuLinkedCells::printSummary() const {
 	                   << _tUpload << " s (" << _bytesUp << " B); " << _mirrors << " host mirror download(s) took "
 	                   << _tMirror << " s (" << _bytesDown << " B); context creation " << _tContext << " s; selective thermostat applied "
 	                   << _selective << " time(s); " << _rdfSamples << " RDF sample(s) on the device; first steps [s] " << _tFirstSteps[0] << " " << _tFirstSteps[1] << " "
-	                   << _tFirstSteps[2] << " " << _tFirstSteps[3] << ", slowest step " << _tMaxStep << std::endl;
+	                   << _tFirstSteps[2] << " " << _tFirstSteps[3] << ", slowest step " << _tMaxStep
+	                   << "; upload = gather " << _tGather << " + copy " << _tH2D << ", mirror = copy " << _tD2H << " + fill " << _tFill << std::endl;
 }
 
 void GpuLinkedCells::fail(const char* what) const {
@@ -262,6 +263,9 @@ void GpuLinkedCells::uploadComponents() {
 		r.dipole = di[k].empty() ? nullptr : di[k].data();
 		r.quadrupole = qu[k].empty() ? nullptr : qu[k].data();
 	}
+	// the library's own rule for "no orientation kept" (one component, one LJ centre at the origin, no rotational DOF)
+	_pointMolecules = nc == 1 && rows[0].n_lj == 1 && rows[0].n_charge == 0 && rows[0].n_dipole == 0 && rows[0].n_quadrupole == 0 &&
+	                  rows[0].rot_dof == 0 && lj[0][0] == 0. && lj[0][1] == 0. && lj[0][2] == 0.;
 	std::vector<double>& mix = global_simulation->getDomain()->getmixcoeff();
 	chk(ls1g_set_components(_ctx, static_cast<int>(nc), rows.data(), mix.empty() ? nullptr : mix.data(),
 	                        static_cast<int>(mix.size())),
@@ -336,8 +340,9 @@ void GpuLinkedCells::uploadFromHost() {
 			for (int d = 0; d < 3; ++d) {
 				r[3 * i + d] = m->r(d);
 				v[3 * i + d] = m->v(d);
-				L[3 * i + d] = m->D(d);
 			}
+			if (_pointMolecules) continue;      // the device keeps no orientation for a single LJ centre at the origin
+			for (int d = 0; d < 3; ++d) L[3 * i + d] = m->D(d);
 			const Quaternion& qq = m->q();
 			q[4 * i] = qq.qw();
 			q[4 * i + 1] = qq.qx();
@@ -345,8 +350,11 @@ void GpuLinkedCells::uploadFromHost() {
 			q[4 * i + 3] = qq.qz();
 		}
 	}
-	chk(ls1g_upload(_ctx, n, id, cid, r, v, q, L), "ls1g_upload");
-	_bytesUp += n * (8 + 4 + 13 * 8);
+	const double tCopy0 = wall();
+	_tGather += tCopy0 - t0 - tStage;
+	chk(ls1g_upload(_ctx, n, id, cid, r, v, _pointMolecules ? nullptr : q, _pointMolecules ? nullptr : L), "ls1g_upload");
+	_tH2D += wall() - tCopy0;
+	_bytesUp += n * (8 + 4 + (_pointMolecules ? 6 : 13) * 8);
 	_deviceLoaded = true;
 	_tUpload += wall() - t0 - tStage;
 }
@@ -662,8 +670,15 @@ void GpuLinkedCells::downloadMirror() {
 	f.M = M;
 	f.Vi = Vi;
 	size_t n = 0;
-	const int mask = LS1G_F_ID | LS1G_F_CID | LS1G_F_CELL | LS1G_F_R | LS1G_F_V | LS1G_F_Q | LS1G_F_L | LS1G_F_F | LS1G_F_M | LS1G_F_VI;
+	// a single LJ centre at the origin has no orientation on the device: q = (1, 0, 0, 0), D = M = 0 need not cross PCIe
+	const int mask = LS1G_F_ID | LS1G_F_CID | LS1G_F_CELL | LS1G_F_R | LS1G_F_V | LS1G_F_F | LS1G_F_VI |
+	                 (_pointMolecules ? 0 : (LS1G_F_Q | LS1G_F_L | LS1G_F_M));
+	const double tCopy0 = wall();
 	chk(ls1g_download(_ctx, mask, 0, cap, &f, &n), "ls1g_download");
+	const double tFill0 = wall();
+	_tD2H += tFill0 - tCopy0;
+	const bool point = _pointMolecules;
+	const double zero3[3] = {0., 0., 0.};
 	std::vector<Component>& comps = *global_simulation->getEnsemble()->getComponents();
 	// first molecule of every run of equal cell index
 	std::vector<size_t> runs;
@@ -678,15 +693,18 @@ void GpuLinkedCells::downloadMirror() {
 		ParticleCell& pc = getCellReference(static_cast<int>(cell[runs[k]]));
 		pc.increaseMoleculeStorage(runs[k + 1] - runs[k]);
 		for (size_t i = runs[k]; i < runs[k + 1]; ++i) {
-			Molecule m(id[i], &comps[cid[i]], r[3 * i], r[3 * i + 1], r[3 * i + 2], v[3 * i], v[3 * i + 1], v[3 * i + 2],
-			           q[4 * i], q[4 * i + 1], q[4 * i + 2], q[4 * i + 3], L[3 * i], L[3 * i + 1], L[3 * i + 2]);
+			Molecule m = point ? Molecule(id[i], &comps[cid[i]], r[3 * i], r[3 * i + 1], r[3 * i + 2], v[3 * i], v[3 * i + 1], v[3 * i + 2],
+			                              1., 0., 0., 0., 0., 0., 0.)
+			                   : Molecule(id[i], &comps[cid[i]], r[3 * i], r[3 * i + 1], r[3 * i + 2], v[3 * i], v[3 * i + 1], v[3 * i + 2],
+			                              q[4 * i], q[4 * i + 1], q[4 * i + 2], q[4 * i + 3], L[3 * i], L[3 * i + 1], L[3 * i + 2]);
 			m.setF(&F[3 * i]);
-			m.setM(&M[3 * i]);
+			m.setM(const_cast<double*>(point ? zero3 : &M[3 * i]));
 			m.setVi(&Vi[3 * i]);
 			pc.addParticle(m);
 		}
 	}
-	_bytesDown += n * (8 + 4 + 4 + 22 * 8);
+	_tFill += wall() - tFill0;
+	_bytesDown += n * (8 + 4 + 4 + (point ? 12 : 22) * 8);
 	_mirrorValid = true;
 	++_mirrors;
 	_tMirror += wall() - t0 - tStage;

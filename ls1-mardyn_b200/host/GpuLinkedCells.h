@@ -95,6 +95,8 @@ private:
 	uint64_t _n = 0, _rotDOF = 0;
 	// wall clock of the host<->device phases (logged after the last time step)
 	double _tUpload = 0., _tDevice = 0., _tMirror = 0., _tContext = 0.;
+	double _tGather = 0., _tH2D = 0., _tD2H = 0., _tFill = 0.;
+	bool _pointMolecules = false;  // one component, one LJ centre at the origin, no rotation: the device keeps no q / D / M
 	unsigned long _steps = 0, _mirrors = 0, _selective = 0, _rdfSamples = 0;
 	double _lastTfactor = 1.0;
 	size_t _bytesUp = 0, _bytesDown = 0, _numCells = 0;
