@@ -534,6 +534,56 @@ def test_decomposed_matches_single_rank(n_ranks, case):
     assert np.all(np.abs(rec[:, :4] - ref_rec[:, :4]) <= 100 * tol * np.maximum(np.abs(ref_rec[:, :4]).max(axis=0), 1e-300))
 
 
+@pytest.mark.parametrize("n_ranks", [2, 8])
+@pytest.mark.parametrize("case", ["1clj", "ex_CO2"])
+def test_rdf_decomposed_sums_to_single_rank(n_ranks, case):
+    """block decomposition: every rank counts the pairs the reference counts on that rank (a pair across a rank boundary is seen from
+    the side whose boundary cell index is below the halo cell index); summed over the ranks (RDF::collectRDF) the histograms are those
+    of the single-rank traversal"""
+    if case == "1clj":
+        r, v, box = fcc_lattice(12, seed=16)
+        rng = np.random.default_rng(18)
+        r = np.mod(r + rng.normal(scale=0.05, size=r.shape), box)
+        n = len(r)
+        ids, cid, q, L = np.arange(n), np.zeros(n, dtype=np.uint32), None, None
+        rc, rclj, comps, mix = 2.5, 2.5, [ls1g.lj_component()], ()
+        shape = dict(bins=80, interval_length=0.03)
+    else:
+        d = load(case)
+        st = initial_state(d)
+        ids, cid, r, v, q, L = st["id"], st["cid"], st["r"], st["v"], st["q"], st["L"]
+        box, rc, rclj = d["box"], float(d["rc"][0]), float(d["rc"][1])
+        from tests.gpu_helpers import components_of
+        comps, mix = components_of(d), d["mixcoeff"]
+        n = len(ids)
+        shape = dict(bins=40, interval_length=0.8, angular_bins=6)
+    with ls1g.Container(box, rc, lj_cutoff=rclj) as c:
+        c.set_components(comps, mix)
+        c.add_particles(ids, cid, r, v, q, L)
+        c.exchange()
+        ref = c.rdf(**shape)
+    ranks = []
+    try:
+        for rank in range(n_ranks):
+            grid, coords = ls1g.decomp_grid(n_ranks, rank)
+            bmin, bmax = ls1g.decomp_box(grid, coords, box)
+            c = ls1g.Container(bmax, rc, box_min=bmin, lj_cutoff=rclj, global_length=box, rank_grid=grid,
+                               rank_coords=coords, capacity=4 * n + 1024)
+            c.set_components(comps, mix)
+            mine = np.all((r >= np.array(bmin)) & (r < np.array(bmax)), axis=1)
+            c.add_particles(ids[mine], cid[mine], r[mine], v[mine], None if q is None else q[mine], None if L is None else L[mine])
+            ranks.append(c)
+        ls1g.comm_init_local(ranks)
+        ls1g.exchange_group(ranks)
+        parts = [c.rdf(**shape) for c in ranks]
+    finally:
+        for c in ranks:
+            c.close()
+    assert ref["mol"].sum() > 10 * n
+    for k in ref:
+        assert np.array_equal(sum(p[k] for p in parts), ref[k]), k
+
+
 @pytest.mark.parametrize("name", golden_cases("rdf_"))
 def test_rdf_matches_reference(name):
     """ls1g_rdf (the reference's RDFCellProcessor + RDF counters as a device cell processor, adapter/RDFCellProcessor.cpp:18-133,
