@@ -120,6 +120,9 @@ int ls1g_debug_cell_pairs(const ls1g_ctx* ctx, uint32_t* triplets, size_t capaci
 
 /* --- particle storage ---------------------------------------------------------------------
  * replaces: ParticleContainer::addParticles / clear (LinkedCells.cpp:445-520,596-601). Replaces the content. */
+/* std::vector::reserve for the device: allocates the molecule arrays and the transfer staging for n owned molecules (plus the
+ * halo copies the grid implies) ahead of ls1g_upload, which otherwise allocates on its first call.  Set-up cost, like ls1g_create. */
+int ls1g_reserve(ls1g_ctx* ctx, size_t n);
 int ls1g_upload(ls1g_ctx* ctx, size_t n, const uint64_t* id, const uint32_t* cid,
                 const double* r, const double* v, const double* q, const double* L);
 /* replaces: Molecule::setF / setM (molecules/FullMolecule.h) for a restart WITH forces: F (and M, may be NULL)

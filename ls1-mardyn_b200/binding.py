@@ -17,7 +17,7 @@ EXPORTS = [
     "ls1g_upload_forces", "ls1g_stream", "ls1g_count", "ls1g_download", "ls1g_update", "ls1g_exchange", "ls1g_traverse", "ls1g_delete_outer",
     "ls1g_integrate_pre", "ls1g_integrate_post", "ls1g_scale", "ls1g_selective_thermostat", "ls1g_run", "ls1g_step", "ls1g_host_alloc", "ls1g_host_free", "ls1g_decomp_box", "ls1g_decomp_grid",
     "ls1g_comm_unique_id", "ls1g_comm_init", "ls1g_allreduce_sum", "ls1g_comm_init_local", "ls1g_exchange_group",
-    "ls1g_timers", "ls1g_measure_fp64_peak", "ls1g_last_pair_count", "ls1g_flop_count", "ls1g_rdf",
+    "ls1g_timers", "ls1g_measure_fp64_peak", "ls1g_last_pair_count", "ls1g_flop_count", "ls1g_rdf", "ls1g_reserve",
 ]
 
 FIELDS = dict(id=1, cid=2, r=4, v=8, q=16, L=32, F=64, M=128, Vi=256, cell=512)
@@ -323,6 +323,10 @@ class Container:
 
     def scale(self, beta_trans, beta_rot=1.0):
         _chk(lib().ls1g_scale(self._ctx, C.c_double(beta_trans), C.c_double(beta_rot)))
+
+    def reserve(self, n):
+        """allocate the device arrays for n owned molecules ahead of add_particles (set-up, like the constructor)"""
+        _chk(lib().ls1g_reserve(self._ctx, C.c_size_t(int(n))))
 
     def flop_count(self):
         """the reference's FlopCounter over the current cells (halo copies in place): dict(molecule_distances, kernel[7], macro[7], flops)"""

@@ -365,6 +365,22 @@ static size_t default_capacity(const ls1g_ctx* c, size_t n) {
 	return n + (size_t)std::min(est, hard) + (size_t)(0.05 * n);
 }
 
+int k_reserve_stage(ls1g_ctx* c);
+extern "C" int ls1g_reserve(ls1g_ctx* c, size_t n) {
+	if (!c) LS1G_FAIL("null context");
+	if (c->n_comp == 0) LS1G_FAIL("ls1g_reserve: call ls1g_set_components first");
+	CUDA_TRY(cudaSetDevice(c->cfg.device));
+	const size_t want = c->cfg.capacity ? (size_t)c->cfg.capacity : default_capacity(c, n);
+	if (want < n) LS1G_FAIL("ls1g_reserve: more molecules than the configured capacity");
+	if (c->cap < want || c->cap == 0) {
+		if (c->n_slots) LS1G_FAIL("ls1g_reserve: the context already holds molecules");
+		if (alloc_molecules(c, std::max<size_t>(want, 1))) return 1;
+	}
+	if (k_reserve_stage(c)) return 1;
+	CUDA_TRY(cudaDeviceSynchronize());
+	return 0;
+}
+
 extern "C" int ls1g_upload(ls1g_ctx* c, size_t n, const uint64_t* id, const uint32_t* cid,
                            const double* r, const double* v, const double* q, const double* L) {
 	if (!c) LS1G_FAIL("null context");

@@ -100,6 +100,8 @@ static int ensure_stage(ls1g_ctx* c) {
 	return 0;
 }
 
+int k_reserve_stage(ls1g_ctx* c) { return ensure_stage(c); }
+
 // --------------------------------------------------------------------------------------------------
 int k_upload(ls1g_ctx* c, size_t n, const uint64_t* id, const uint32_t* cid, const double* r, const double* v, const double* q, const double* L) {
 	if (ensure_stage(c)) return 1;

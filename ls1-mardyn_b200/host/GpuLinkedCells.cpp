@@ -323,7 +323,13 @@ void GpuLinkedCells::uploadFromHost() {
 	}
 	for (long c = 0; c < nc; ++c) first[c + 1] += first[c];
 	const size_t n = first[nc];
-	const double tStage = ensureStaging(n);       // set-up (page-locking), accounted with the context creation
+	double tStage = ensureStaging(n);             // set-up (page-locking), accounted with the context creation
+	if (!_deviceLoaded) {                         // ... and so is the allocation of the device arrays
+		const double tr = wall();
+		chk(ls1g_reserve(_ctx, n), "ls1g_reserve");
+		_tContext += wall() - tr;
+		tStage += wall() - tr;
+	}
 	uint64_t* id = _sId;
 	uint32_t* cid = _sCid;
 	double *r = _sR, *v = _sV, *q = _sQ, *L = _sL;

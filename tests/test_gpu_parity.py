@@ -642,3 +642,25 @@ def test_rdf_of_the_bench_lattice_after_steps():
     q = np.tile(np.array([1.0, 0, 0, 0]), (len(allm["id"]), 1))
     ref = O.rdf(s, g, allm["cid"], allm["r"], q, 100, 0.025)
     assert res["mol"].sum() > 20 * len(ids) and np.array_equal(res["mol"], ref["mol"])
+
+
+def test_reserve_allocates_ahead_of_the_upload():
+    """ls1g_reserve: the device arrays exist before the first upload (set-up cost outside a timed upload); results are unchanged and a
+    loaded context refuses to be re-allocated"""
+    r, v, box = fcc_lattice(6, seed=2)
+    n = len(r)
+    out = []
+    for reserve in (False, True):
+        with ls1g.Container(box, 2.5) as c:
+            c.set_components([ls1g.lj_component()])
+            if reserve:
+                c.reserve(n)
+                c.reserve(n)
+            c.add_particles(np.arange(n), np.zeros(n, dtype=np.uint32), r, v)
+            c.exchange()
+            u, w = c.traverse_cells()
+            out.append((u, w, by_id(c.download(("id", "F")))["F"]))
+            if reserve:
+                with pytest.raises(ls1g.Ls1gError, match="already holds molecules"):
+                    c.reserve(100 * n)
+    assert out[0][0] == out[1][0] and out[0][1] == out[1][1] and np.array_equal(out[0][2], out[1][2])
