@@ -135,6 +135,14 @@ int ls1g_count(ls1g_ctx* ctx, uint64_t* n_owned, uint64_t* n_halo);
  * Molecules come in cell-sorted order; include_halo selects ALL_CELLS. Returns count in *n_out. */
 int ls1g_download(ls1g_ctx* ctx, int field_mask, int include_halo, size_t capacity,
                   ls1g_fields* out, size_t* n_out);
+/* Raw SLOTS [first, first + count) of the device's cell-sorted storage, 0 <= first + count <= ls1g_slot_count: owned molecules in
+ * the order ls1g_download returns them, interleaved with the slots of (possibly already dropped) halo copies, which carry
+ * LS1G_HALO_FLAG in `cell` and must be skipped by the caller.  The output pointers address element 0 of the RANGE.  No compaction
+ * pass, and a caller can overlap the copy of one chunk with its own work on the previous one (GpuLinkedCells::downloadMirror
+ * refills the host cells that way; ParticleIterator semantics stay with ls1g_download). */
+#define LS1G_HALO_FLAG 0x80000000u
+int ls1g_slot_count(ls1g_ctx* ctx, uint64_t* n_slots);
+int ls1g_download_range(ls1g_ctx* ctx, int field_mask, size_t first, size_t count, ls1g_fields* out);
 
 /* --- per-step operators ------------------------------------------------------------------- */
 /* replaces: LinkedCells::update (LinkedCells.cpp:243-356): re-bin into cells (device sort) */

@@ -11,13 +11,15 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 _LIB = None
 
+HALO_FLAG = 0x80000000
+
 EXPORTS = [
     "ls1g_last_error", "ls1g_version", "ls1g_create", "ls1g_destroy", "ls1g_set_components", "ls1g_get_grid",
     "ls1g_cell_index_of_points_host", "ls1g_cell_index_of_points", "ls1g_debug_cell_pairs", "ls1g_upload",
     "ls1g_upload_forces", "ls1g_stream", "ls1g_count", "ls1g_download", "ls1g_update", "ls1g_exchange", "ls1g_traverse", "ls1g_delete_outer",
     "ls1g_integrate_pre", "ls1g_integrate_post", "ls1g_scale", "ls1g_selective_thermostat", "ls1g_run", "ls1g_step", "ls1g_host_alloc", "ls1g_host_free", "ls1g_decomp_box", "ls1g_decomp_grid",
     "ls1g_comm_unique_id", "ls1g_comm_init", "ls1g_allreduce_sum", "ls1g_comm_init_local", "ls1g_exchange_group",
-    "ls1g_timers", "ls1g_measure_fp64_peak", "ls1g_last_pair_count", "ls1g_flop_count", "ls1g_rdf", "ls1g_reserve",
+    "ls1g_timers", "ls1g_measure_fp64_peak", "ls1g_last_pair_count", "ls1g_flop_count", "ls1g_rdf", "ls1g_reserve", "ls1g_download_range", "ls1g_slot_count",
 ]
 
 FIELDS = dict(id=1, cid=2, r=4, v=8, q=16, L=32, F=64, M=128, Vi=256, cell=512)
@@ -293,6 +295,23 @@ class Container:
         n = C.c_size_t()
         _chk(lib().ls1g_download(self._ctx, mask, int(bool(include_halo)), C.c_size_t(cap), C.byref(f), C.byref(n)))
         return {k: a[:n.value] for k, a in out.items()}
+
+    def download_slots(self, fields, first=0, count=None):
+        """raw slots [first, first + count) of the cell-sorted storage (ls1g_download_range): halo copies included, flagged with
+        HALO_FLAG in 'cell'"""
+        ns = C.c_uint64()
+        _chk(lib().ls1g_slot_count(self._ctx, C.byref(ns)))
+        count = ns.value - first if count is None else count
+        widths = dict(id=((count,), np.uint64), cid=((count,), np.uint32), r=((count, 3), np.float64), v=((count, 3), np.float64),
+                      q=((count, 4), np.float64), L=((count, 3), np.float64), F=((count, 3), np.float64), M=((count, 3), np.float64),
+                      Vi=((count, 3), np.float64), cell=((count,), np.uint32))
+        out, f, mask = {}, _Fields(), 0
+        for k in fields:
+            out[k] = np.zeros(*widths[k])
+            setattr(f, k, _p(out[k]))
+            mask |= FIELDS[k]
+        _chk(lib().ls1g_download_range(self._ctx, mask, C.c_size_t(first), C.c_size_t(count), C.byref(f)))
+        return out
 
     # -- per-step operators ---------------------------------------------------------------------------
     def update(self):

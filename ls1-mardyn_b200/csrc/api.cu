@@ -418,6 +418,24 @@ extern "C" int ls1g_download(ls1g_ctx* c, int mask, int include_halo, size_t cap
 	return k_download(c, mask, halo_ok ? 1 : 0, n_ret, out);
 }
 
+int k_download_range(ls1g_ctx* c, int mask, size_t first, size_t count, ls1g_fields* out);
+extern "C" int ls1g_download_range(ls1g_ctx* c, int mask, size_t first, size_t count, ls1g_fields* out) {
+	if (!c || !out) LS1G_FAIL("null argument");
+	CUDA_TRY(cudaSetDevice(c->cfg.device));
+	if (c->in_list_mode && ls1g_nl_leave(c)) return 1;
+	if (!c->sorted) LS1G_FAIL("ls1g_download_range: container not sorted (call ls1g_update / ls1g_exchange first)");
+	if (first > c->n_slots || count > c->n_slots - first) LS1G_FAIL("ls1g_download_range: range outside the slots");
+	return k_download_range(c, mask, first, count, out);
+}
+
+extern "C" int ls1g_slot_count(ls1g_ctx* c, uint64_t* n_slots) {
+	if (!c || !n_slots) LS1G_FAIL("null argument");
+	CUDA_TRY(cudaSetDevice(c->cfg.device));
+	if (c->in_list_mode && ls1g_nl_leave(c)) return 1;
+	*n_slots = c->n_slots;
+	return 0;
+}
+
 // Molecule::setF / setM for the molecules of the last ls1g_upload, same order (restart with forces:
 // the leapfrog half-kick of the next step needs F(t), Leapfrog.cpp:48-68)
 extern "C" int ls1g_upload_forces(ls1g_ctx* c, size_t n, const double* F, const double* M) {

@@ -195,6 +195,48 @@ int k_download(ls1g_ctx* c, int mask, int include_halo, size_t n_ret, ls1g_field
 	return 0;
 }
 
+// Range variant over raw SLOTS of the cell-sorted storage (owned molecules and halo copies, the latter flagged in cell[]): the
+// per-molecule arrays are contiguous in slot order, so every field but r / cid (packed in pos) goes straight from its device
+// array to the host.  Lets the caller pipeline the copy of chunk k+1 with its own work on chunk k.
+__global__ void __launch_bounds__(256) unpack_pos_kernel(size_t n, const double4* __restrict__ pos, double* __restrict__ r, uint32_t* __restrict__ cid) {
+	size_t s = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (s >= n) return;
+	const double4 p = pos[s];
+	if (r) { r[3 * s] = p.x; r[3 * s + 1] = p.y; r[3 * s + 2] = p.z; }
+	if (cid) cid[s] = pos_cid(p);
+}
+
+int k_download_range(ls1g_ctx* c, int mask, size_t first, size_t count, ls1g_fields* out) {
+	if (count == 0) return 0;
+	if (ensure_stage(c)) return 1;
+	cudaStream_t st = c->stream;
+	const bool want_r = (mask & LS1G_F_R) && out->r, want_cid = (mask & LS1G_F_CID) && out->cid;
+	double* sr = (double*)c->stage;                                        // stage holds cap * 32 bytes: r (24 B) + cid (4 B) per molecule fit
+	uint32_t* sc = (uint32_t*)((char*)c->stage + count * 3 * sizeof(double));
+	if (want_r || want_cid) {
+		unpack_pos_kernel<<<nblk(count, 256), 256, 0, st>>>(count, c->cur.pos + first, want_r ? sr : nullptr, want_cid ? sc : nullptr);
+		if (want_r) CUDA_TRY(cudaMemcpyAsync(out->r, sr, count * 3 * sizeof(double), cudaMemcpyDeviceToHost, st));
+		if (want_cid) CUDA_TRY(cudaMemcpyAsync(out->cid, sc, count * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+	}
+	if ((mask & LS1G_F_ID) && out->id) CUDA_TRY(cudaMemcpyAsync(out->id, c->cur.id + first, count * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+	if ((mask & LS1G_F_CELL) && out->cell) CUDA_TRY(cudaMemcpyAsync(out->cell, c->cur.cell + first, count * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+	auto f64 = [&](const double* dev, double* dst, int w) -> int {
+		if (!dst) return 0;
+		if (dev) CUDA_TRY(cudaMemcpyAsync(dst, dev + first * w, count * w * sizeof(double), cudaMemcpyDeviceToHost, st));
+		else for (size_t i = 0; i < count * w; ++i) dst[i] = (w == 4 && i % 4 == 0) ? 1. : 0.;      // no orientation kept: q = (1,0,0,0), L = M = 0
+		return 0;
+	};
+	if ((mask & LS1G_F_V) && f64(c->cur.vel, out->v, 3)) return 1;
+	if ((mask & LS1G_F_L) && f64(c->has_rot ? c->cur.L : nullptr, out->L, 3)) return 1;
+	if ((mask & LS1G_F_F) && f64(c->F, out->F, 3)) return 1;
+	if ((mask & LS1G_F_M) && f64(c->has_rot ? c->M : nullptr, out->M, 3)) return 1;
+	if ((mask & LS1G_F_VI) && f64(c->Vi, out->Vi, 3)) return 1;
+	if ((mask & LS1G_F_Q) && f64(c->has_rot ? (const double*)c->cur.q : nullptr, out->q, 4)) return 1;
+	CUDA_TRY(cudaStreamSynchronize(st));
+	CUDA_TRY(cudaGetLastError());
+	return 0;
+}
+
 // pinned host staging memory for ls1g_upload / ls1g_download (full PCIe rate; pageable user memory is staged by the driver)
 int k_host_alloc(size_t bytes, void** out) {
 	*out = nullptr;

@@ -21,6 +21,7 @@ extern "C" {
 #include "ls1g.h"
 }
 
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <cstdlib>
@@ -28,6 +29,7 @@ extern "C" {
 #include <numeric>
 #include <set>
 #include <string>
+#include <thread>
 
 #if defined(_OPENMP)
 #include <omp.h>
@@ -323,7 +325,16 @@ void GpuLinkedCells::uploadFromHost() {
 	}
 	for (long c = 0; c < nc; ++c) first[c + 1] += first[c];
 	const size_t n = first[nc];
-	double tStage = ensureStaging(n);             // set-up (page-locking), accounted with the context creation
+	// set-up (page-locking), accounted with the context creation.  Sized for the mirror, which brings the device's slots back:
+	// the owned molecules plus one slot per periodic image in the halo cells (on average owned * halo cells / real cells).
+	double tot = 1., real = 1.;
+	const int* realCells = getBoxWidthInNumCells();          // without the halo layer (one cell wide: cellsInCutoffRadius == 1)
+	for (int d = 0; d < 3; ++d) {
+		tot *= realCells[d] + 2;
+		real *= std::max(1, realCells[d]);
+	}
+	const size_t slots = static_cast<size_t>(std::min(28.0 * n + 64., n * (1. + (tot / real - 1.) * 1.3) + 4096.));
+	double tStage = ensureStaging(std::max(n, slots));
 	if (!_deviceLoaded) {                         // ... and so is the allocation of the device arrays
 		const double tr = wall();
 		chk(ls1g_reserve(_ctx, n), "ls1g_reserve");
@@ -657,60 +668,113 @@ void GpuLinkedCells::downloadMirror() {
 	if (_ctx == nullptr || !_deviceLoaded) return;
 	const double t0 = wall();
 	clearHostCells();
-	uint64_t owned = 0, halo = 0;
-	chk(ls1g_count(_ctx, &owned, &halo), "ls1g_count");
-	const size_t cap = owned + halo + 1;
-	const double tStage = ensureStaging(cap);
+	uint64_t slots = 0;
+	chk(ls1g_slot_count(_ctx, &slots), "ls1g_slot_count");     // owned molecules + the slots of the (dropped) halo copies
+	const size_t ns = static_cast<size_t>(slots);
+	const double tStage = ensureStaging(ns + 1);
 	uint64_t* id = _sId;
 	uint32_t *cid = _sCid, *cell = _sCell;
 	double *r = _sR, *v = _sV, *q = _sQ, *L = _sL, *F = _sF, *M = _sM, *Vi = _sVi;
-	ls1g_fields f{};
-	f.id = id;
-	f.cid = cid;
-	f.cell = cell;
-	f.r = r;
-	f.v = v;
-	f.q = q;
-	f.L = L;
-	f.F = F;
-	f.M = M;
-	f.Vi = Vi;
-	size_t n = 0;
 	// a single LJ centre at the origin has no orientation on the device: q = (1, 0, 0, 0), D = M = 0 need not cross PCIe
-	const int mask = LS1G_F_ID | LS1G_F_CID | LS1G_F_CELL | LS1G_F_R | LS1G_F_V | LS1G_F_F | LS1G_F_VI |
-	                 (_pointMolecules ? 0 : (LS1G_F_Q | LS1G_F_L | LS1G_F_M));
-	const double tCopy0 = wall();
-	chk(ls1g_download(_ctx, mask, 0, cap, &f, &n), "ls1g_download");
-	const double tFill0 = wall();
-	_tD2H += tFill0 - tCopy0;
 	const bool point = _pointMolecules;
-	const double zero3[3] = {0., 0., 0.};
-	std::vector<Component>& comps = *global_simulation->getEnsemble()->getComponents();
-	// first molecule of every run of equal cell index
+	const int mask = LS1G_F_ID | LS1G_F_CID | LS1G_F_R | LS1G_F_V | LS1G_F_F | LS1G_F_VI | (point ? 0 : (LS1G_F_Q | LS1G_F_L | LS1G_F_M));
+	const double tCopy0 = wall();
+	{	// the cell index of every slot first (4 bytes each): the chunks of the pipeline below are cut at cell borders
+		ls1g_fields fc{};
+		fc.cell = cell;
+		chk(ls1g_download_range(_ctx, LS1G_F_CELL, 0, ns, &fc), "ls1g_download_range");
+	}
+	double tCopy = wall() - tCopy0;
+	const double tFill0 = wall();
+	// first slot of every run of equal cell index (halo runs are skipped when filling)
 	std::vector<size_t> runs;
-	for (size_t i = 0; i < n; ++i)
-		if (i == 0 || cell[i] != cell[i - 1]) runs.push_back(i);
-	runs.push_back(n);
-	const long nruns = static_cast<long>(runs.size()) - 1;
+	{
+		int nt = 1;
 #if defined(_OPENMP)
-#pragma omp parallel for schedule(static)
+		nt = omp_get_max_threads();
 #endif
-	for (long k = 0; k < nruns; ++k) {
-		ParticleCell& pc = getCellReference(static_cast<int>(cell[runs[k]]));
-		pc.increaseMoleculeStorage(runs[k + 1] - runs[k]);
-		for (size_t i = runs[k]; i < runs[k + 1]; ++i) {
-			Molecule m = point ? Molecule(id[i], &comps[cid[i]], r[3 * i], r[3 * i + 1], r[3 * i + 2], v[3 * i], v[3 * i + 1], v[3 * i + 2],
-			                              1., 0., 0., 0., 0., 0., 0.)
-			                   : Molecule(id[i], &comps[cid[i]], r[3 * i], r[3 * i + 1], r[3 * i + 2], v[3 * i], v[3 * i + 1], v[3 * i + 2],
-			                              q[4 * i], q[4 * i + 1], q[4 * i + 2], q[4 * i + 3], L[3 * i], L[3 * i + 1], L[3 * i + 2]);
-			m.setF(&F[3 * i]);
-			m.setM(const_cast<double*>(point ? zero3 : &M[3 * i]));
-			m.setVi(&Vi[3 * i]);
-			pc.addParticle(m);
+		std::vector<std::vector<size_t>> part(nt);
+#if defined(_OPENMP)
+#pragma omp parallel num_threads(nt)
+#endif
+		{
+			int t = 0;
+#if defined(_OPENMP)
+			t = omp_get_thread_num();
+#endif
+			const size_t a = ns * t / nt, b = ns * (t + 1) / nt;
+			for (size_t i = a; i < b; ++i)
+				if (i == 0 || cell[i] != cell[i - 1]) part[t].push_back(i);
+		}
+		for (int t = 0; t < nt; ++t) runs.insert(runs.end(), part[t].begin(), part[t].end());
+	}
+	runs.push_back(ns);
+	const long nruns = static_cast<long>(runs.size()) - 1;
+	const long nchunks = std::max<long>(1, std::min<long>(16, static_cast<long>(ns / 262144)));
+	const long rpc = std::max<long>(1, (nruns + nchunks - 1) / nchunks);      // runs per chunk
+	const long block = 64;
+	std::atomic<long> ready(0), cursor(0);
+	std::vector<Component>& comps = *global_simulation->getEnsemble()->getComponents();
+	const double zero3[3] = {0., 0., 0.};
+	size_t n = 0;
+	// thread 0 brings chunk after chunk over PCIe (ls1g_download_range blocks until the chunk is in host memory) while the other
+	// threads refill the host cells of the chunks that have arrived; then it joins them
+#if defined(_OPENMP)
+#pragma omp parallel reduction(+ : n)
+#endif
+	{
+		bool copier = true;
+#if defined(_OPENMP)
+		copier = omp_get_thread_num() == 0;
+#endif
+		if (copier) {
+			const double tc = wall();
+			for (long k = 0; k * rpc < nruns; ++k) {
+				const long ra = k * rpc, rb = std::min((k + 1) * rpc, nruns);
+				const size_t s0 = runs[ra], cnt = runs[rb] - s0;
+				ls1g_fields f{};
+				f.id = id + s0;
+				f.cid = cid + s0;
+				f.r = r + 3 * s0;
+				f.v = v + 3 * s0;
+				f.q = q + 4 * s0;
+				f.L = L + 3 * s0;
+				f.F = F + 3 * s0;
+				f.M = M + 3 * s0;
+				f.Vi = Vi + 3 * s0;
+				chk(ls1g_download_range(_ctx, mask, s0, cnt, &f), "ls1g_download_range");
+				ready.store(k + 1, std::memory_order_release);
+			}
+			tCopy += wall() - tc;
+		}
+		for (;;) {
+			const long a = cursor.fetch_add(block);
+			if (a >= nruns) break;
+			const long b = std::min(a + block, nruns);
+			const long need = (b - 1) / rpc + 1;
+			while (ready.load(std::memory_order_acquire) < need) std::this_thread::yield();
+			for (long k = a; k < b; ++k) {
+				if ((cell[runs[k]] & LS1G_HALO_FLAG) != 0u) continue;
+				ParticleCell& pc = getCellReference(static_cast<int>(cell[runs[k]]));
+				pc.increaseMoleculeStorage(runs[k + 1] - runs[k]);
+				for (size_t i = runs[k]; i < runs[k + 1]; ++i) {
+					Molecule m = point ? Molecule(id[i], &comps[cid[i]], r[3 * i], r[3 * i + 1], r[3 * i + 2], v[3 * i], v[3 * i + 1], v[3 * i + 2],
+					                              1., 0., 0., 0., 0., 0., 0.)
+					                   : Molecule(id[i], &comps[cid[i]], r[3 * i], r[3 * i + 1], r[3 * i + 2], v[3 * i], v[3 * i + 1], v[3 * i + 2],
+					                              q[4 * i], q[4 * i + 1], q[4 * i + 2], q[4 * i + 3], L[3 * i], L[3 * i + 1], L[3 * i + 2]);
+					m.setF(&F[3 * i]);
+					m.setM(const_cast<double*>(point ? zero3 : &M[3 * i]));
+					m.setVi(&Vi[3 * i]);
+					pc.addParticle(m);
+				}
+				n += runs[k + 1] - runs[k];
+			}
 		}
 	}
+	_tD2H += tCopy;                  // overlapped with the refill
 	_tFill += wall() - tFill0;
-	_bytesDown += n * (8 + 4 + 4 + (point ? 12 : 22) * 8);
+	_bytesDown += ns * (8 + 4 + 4 + (point ? 12 : 22) * 8);
+	(void)n;
 	_mirrorValid = true;
 	++_mirrors;
 	_tMirror += wall() - t0 - tStage;

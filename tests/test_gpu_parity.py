@@ -664,3 +664,29 @@ def test_reserve_allocates_ahead_of_the_upload():
                 with pytest.raises(ls1g.Ls1gError, match="already holds molecules"):
                     c.reserve(100 * n)
     assert out[0][0] == out[1][0] and out[0][1] == out[1][1] and np.array_equal(out[0][2], out[1][2])
+
+
+@pytest.mark.parametrize("name", ["ex_CO2", "per_LennardJones"])
+def test_slot_ranges_hold_the_owned_molecules_in_download_order(name):
+    """ls1g_download_range: raw slots of the cell-sorted storage, chunk by chunk; the slots without HALO_FLAG are exactly what
+    ls1g_download returns, in the same order - before and after the halo copies are dropped"""
+    d = load(name)
+    with container_of(d) as c:
+        _load_into(c, d, True)
+        c.traverse_cells()
+        for dropped in (False, True):
+            if dropped:
+                c.delete_outer_particles()
+            ref = c.download(("id", "cid", "r", "v", "q", "L", "F", "M", "Vi", "cell"))
+            full = c.download_slots(("cell",))
+            ns = len(full["cell"])
+            assert ns > len(ref["id"])
+            parts = [c.download_slots(("id", "cid", "r", "v", "q", "L", "F", "M", "Vi", "cell"), a, min(ns, a + 700) - a) for a in range(0, ns, 700)]
+            got = {k: np.concatenate([p[k] for p in parts]) for k in parts[0]}
+            assert np.array_equal(got["cell"], full["cell"])
+            own = (got["cell"] & ls1g.binding.HALO_FLAG) == 0
+            assert own.sum() == len(ref["id"])
+            for k in ref:
+                assert np.array_equal(got[k][own], ref[k]), k
+        with pytest.raises(ls1g.Ls1gError, match="range outside"):
+            c.download_slots(("id",), ns - 1, 2)
