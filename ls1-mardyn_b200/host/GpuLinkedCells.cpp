@@ -679,7 +679,7 @@ void GpuLinkedCells::downloadMirror() {
 	const bool point = _pointMolecules;
 	const int mask = LS1G_F_ID | LS1G_F_CID | LS1G_F_R | LS1G_F_V | LS1G_F_F | LS1G_F_VI | (point ? 0 : (LS1G_F_Q | LS1G_F_L | LS1G_F_M));
 	const double tCopy0 = wall();
-	{	// the cell index of every slot first (4 bytes each): the chunks of the pipeline below are cut at cell borders
+	if (ns > 0) {	// the cell index of every slot first (4 bytes each): the chunks of the pipeline below are cut at cell borders
 		ls1g_fields fc{};
 		fc.cell = cell;
 		chk(ls1g_download_range(_ctx, LS1G_F_CELL, 0, ns, &fc), "ls1g_download_range");
