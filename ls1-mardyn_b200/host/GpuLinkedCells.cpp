@@ -287,20 +287,22 @@ double GpuLinkedCells::ensureStaging(size_t molecules) {
 	_stage = nullptr;
 	_stageMolecules = molecules + molecules / 16 + 1024;
 	_stagePinned = pinned;
+	// single-centre molecules keep no q / D / M on the device: their 80 bytes per molecule are not staged (nor page-locked)
+	const size_t perMolecule = kStageBytesPerMolecule - (_pointMolecules ? 32 + 24 + 24 : 0);
 	if (pinned) {
-		chk(ls1g_host_alloc(_ctx, _stageMolecules * kStageBytesPerMolecule, &_stage), "ls1g_host_alloc");
+		chk(ls1g_host_alloc(_ctx, _stageMolecules * perMolecule, &_stage), "ls1g_host_alloc");
 	} else {
-		_stage = std::malloc(_stageMolecules * kStageBytesPerMolecule);
+		_stage = std::malloc(_stageMolecules * perMolecule);
 		if (_stage == nullptr) fail("staging allocation");
 	}
 	char* p = static_cast<char*>(_stage);
 	auto take = [&](size_t bytesPerMolecule) { void* q = p; p += _stageMolecules * bytesPerMolecule; return q; };
 	_sR = static_cast<double*>(take(24));      // 8-byte aligned arrays first
 	_sV = static_cast<double*>(take(24));
-	_sQ = static_cast<double*>(take(32));
-	_sL = static_cast<double*>(take(24));
+	_sQ = _pointMolecules ? nullptr : static_cast<double*>(take(32));
+	_sL = _pointMolecules ? nullptr : static_cast<double*>(take(24));
 	_sF = static_cast<double*>(take(24));
-	_sM = static_cast<double*>(take(24));
+	_sM = _pointMolecules ? nullptr : static_cast<double*>(take(24));
 	_sVi = static_cast<double*>(take(24));
 	_sId = static_cast<uint64_t*>(take(8));
 	_sCid = static_cast<uint32_t*>(take(4));
@@ -737,10 +739,10 @@ void GpuLinkedCells::downloadMirror() {
 				f.cid = cid + s0;
 				f.r = r + 3 * s0;
 				f.v = v + 3 * s0;
-				f.q = q + 4 * s0;
-				f.L = L + 3 * s0;
+				f.q = point ? nullptr : q + 4 * s0;
+				f.L = point ? nullptr : L + 3 * s0;
 				f.F = F + 3 * s0;
-				f.M = M + 3 * s0;
+				f.M = point ? nullptr : M + 3 * s0;
 				f.Vi = Vi + 3 * s0;
 				chk(ls1g_download_range(_ctx, mask, s0, cnt, &f), "ls1g_download_range");
 				ready.store(k + 1, std::memory_order_release);
