@@ -130,3 +130,20 @@ def test_bench_sharding_two_ranks_gloo():
     assert res[0][1] == res[1][1]
     assert res[0][2] == [2, 1, 1] and res[0][3] == [0, 0, 0] and res[1][3] == [1, 0, 0]
     assert np.allclose(res[0][4], v.mean(axis=0)) and res[0][4] == res[1][4]
+
+
+def test_library_holds_sm100a_code_for_the_hot_kernels():
+    """the product is native sm_100a code: every embedded cubin is built for sm_100a and the kernels of the hot path are in it"""
+    import shutil
+    import subprocess
+    if shutil.which("cuobjdump") is None:
+        pytest.skip("cuobjdump not on PATH")
+    so = ls1g.lib_path()
+    elfs = subprocess.run(["cuobjdump", "-lelf", so], capture_output=True, text=True).stdout.split("\n")
+    elfs = [l for l in elfs if "ELF file" in l]
+    assert len(elfs) >= 10 and all("sm_100a" in l for l in elfs)
+    sass = subprocess.run(["cuobjdump", "-sass", so], capture_output=True, text=True).stdout
+    for k in ("nl_force_kernel", "nl_build_kernel", "force_generic_kernel", "force_1clj_tile_kernel", "integrate_kernel", "bin_kernel",
+              "scatter_kernel", "pack_kernel", "unpack_kernel", "halo_refresh_kernel", "selective_kernel", "flop_count_kernel", "rdf_kernel"):
+        assert re.search(r"Function : \S*%s" % k, sass), k
+    assert "DFMA" in sass and "MUFU.RCP64H" in sass
