@@ -173,6 +173,7 @@ extern "C" int ls1g_create(const ls1g_config* cfg, ls1g_ctx** out) {
 	if (grid_init(c->grid, c->cfg)) { delete c; return 1; }
 	c->bgrid = c->grid;
 	{ const char* e = getenv("LS1G_VI_EVERY_STEP"); c->vi_every_step = e && atoi(e) != 0; }
+	{ const char* lr = getenv("LS1G_LIST_ROWS"); c->list_R = lr && atoi(lr) == 1 ? 1 : 4; }
 	{ const char* sk = getenv("LS1G_SKIN"); c->skin = sk ? atof(sk) : 0.12 * c->cfg.cutoff; if (c->skin < 0.) c->skin = 0.; }
 	c->rc2 = c->cfg.cutoff * c->cfg.cutoff;
 	c->rclj2 = c->cfg.lj_cutoff * c->cfg.lj_cutoff;
@@ -192,14 +193,16 @@ extern "C" int ls1g_create(const ls1g_config* cfg, ls1g_ctx** out) {
 	CUDA_TRY(cudaMalloc((void**)&c->cell_start, (nc + 8) * sizeof(uint32_t)));
 	CUDA_TRY(cudaMemset(c->cell_start, 0, (nc + 8) * sizeof(uint32_t)));
 	CUDA_TRY(cudaMalloc((void**)&c->scan_block, (nc / 2048 + 8) * sizeof(uint32_t)));
-	CUDA_TRY(cudaMalloc((void**)&c->d_counters, 8 * sizeof(uint32_t)));
-	CUDA_TRY(cudaMallocHost((void**)&c->h_counters, 8 * sizeof(uint32_t)));
+	CUDA_TRY(cudaMalloc((void**)&c->d_counters, 16 * sizeof(uint32_t)));
+	CUDA_TRY(cudaMemset(c->d_counters, 0, 16 * sizeof(uint32_t)));
+	CUDA_TRY(cudaMallocHost((void**)&c->h_counters, 16 * sizeof(uint32_t)));
 	CUDA_TRY(cudaMalloc((void**)&c->d_scalars, 16 * sizeof(double)));
 	CUDA_TRY(cudaMemset(c->d_scalars, 0, 16 * sizeof(double)));
 	CUDA_TRY(cudaMallocHost((void**)&c->h_scalars, 16 * sizeof(double)));
-	CUDA_TRY(cudaMalloc((void**)&c->d_flags, 8 * sizeof(unsigned long long)));
-	CUDA_TRY(cudaMemset(c->d_flags, 0, 8 * sizeof(unsigned long long)));
-	CUDA_TRY(cudaMallocHost((void**)&c->h_flags, 8 * sizeof(unsigned long long)));
+	CUDA_TRY(cudaMalloc((void**)&c->d_flags, 16 * sizeof(unsigned long long)));
+	CUDA_TRY(cudaMemset(c->d_flags, 0, 16 * sizeof(unsigned long long)));
+	CUDA_TRY(cudaMallocHost((void**)&c->h_flags, 16 * sizeof(unsigned long long)));
+	memset(c->h_flags, 0, 16 * sizeof(unsigned long long));
 	for (int k = 0; k < 4; ++k) CUDA_TRY(cudaEventCreateWithFlags(&c->disp_ev[k], cudaEventDisableTiming));
 	*out = c;
 	return 0;

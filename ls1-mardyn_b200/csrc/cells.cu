@@ -211,6 +211,9 @@ struct GatherArgs {
 	int has_rot;
 	uint32_t* slot_dst;      // [n_new] final slot of scatter entry s
 	uint32_t* new_of_old;    // [n_old] new slot of every surviving (non-image) molecule; aliases src.cell
+	int geometric;           // 1: a molecule in a halo cell is a halo copy (after an exchange: images, received copies, leavers kept by the
+	                         // sender); 0: LinkedCells::update - an owned molecule that left the box sits in a halo cell and STAYS owned
+	                         // until the next exchange wraps or sends it (LinkedCells.cpp:243-356 moves molecules, it never deletes them)
 };
 
 __global__ void __launch_bounds__(256) gather_kernel(Grid g, size_t n_new, GatherArgs a, const uint32_t* __restrict__ cell_start,
@@ -235,7 +238,7 @@ __global__ void __launch_bounds__(256) gather_kernel(Grid g, size_t n_new, Gathe
 	if (code) image_pos(g, code, p.x, p.y, p.z);
 	a.dst.pos[dst] = p;
 	a.dst.id[dst] = key;
-	bool halo = grid_is_halo(g, c);
+	bool halo = (a.geometric || code) && grid_is_halo(g, c);
 	a.dst.cell[dst] = c | (halo ? HALO_FLAG : 0u);
 #pragma unroll
 	for (int d = 0; d < 3; ++d) a.dst.vel[3 * dst + d] = a.src.vel[3 * (size_t)src + d];
@@ -318,6 +321,24 @@ __global__ void __launch_bounds__(256) row_max_kernel(Grid g, const uint32_t* __
 	if ((threadIdx.x & 31) == 0 && n) atomicMax(out, n);
 }
 
+// owned molecules of the fullest 2 x 2 bundle of cell rows (2gy+1.., 2gz+1..): sizes the block grid of the bundled list kernels
+__global__ void __launch_bounds__(256) bundle_max_kernel(Grid g, const uint32_t* __restrict__ cell_start, uint32_t* __restrict__ out) {
+	const int nyi = g.cpd[1] - 2, nzi = g.cpd[2] - 2, nyg = (nyi + 1) / 2, nzg = (nzi + 1) / 2;
+	int b = blockIdx.x * blockDim.x + threadIdx.x;
+	uint32_t n = 0;
+	if (b < nyg * nzg) {
+		const int gy = b % nyg, gz = b / nyg;
+		for (int q = 0; q < 4; ++q) {
+			const int cy = 2 * gy + 1 + (q & 1), cz = 2 * gz + 1 + (q >> 1);
+			if (cy > nyi || cz > nzi) continue;
+			const int crow = (cz * g.cpd[1] + cy) * g.cpd[0];
+			n += cell_start[crow + g.cpd[0] - 1] - cell_start[crow + 1];
+		}
+	}
+	n = __reduce_max_sync(0xffffffffu, n);
+	if ((threadIdx.x & 31) == 0 && n) atomicMax(out, n);
+}
+
 int k_sort(ls1g_ctx* c, int make_images) {
 	const Grid& g = c->bgrid;
 	const int nc = g.n_cells;
@@ -328,13 +349,15 @@ int k_sort(ls1g_ctx* c, int make_images) {
 	int launches = 0;
 	if (n) { bin_kernel<<<nblk(n, 256), 256, 0, c->stream>>>(g, n, c->cur.pos, c->cur.cell, c->cell_count, make_images); ++launches; }
 	if (ls1g_scan_cells(c, c->cell_count, c->cell_start)) return 1;
-	CUDA_TRY(cudaMemsetAsync(c->d_counters + 7, 0, sizeof(uint32_t), c->stream));
+	CUDA_TRY(cudaMemsetAsync(c->d_counters + 7, 0, 2 * sizeof(uint32_t), c->stream));
 	row_max_kernel<<<nblk((size_t)(g.cpd[1] - 2) * (g.cpd[2] - 2), 256), 256, 0, c->stream>>>(g, c->cell_start, c->d_counters + 7);
-	launches += 4;
-	CUDA_TRY(cudaMemcpyAsync(c->h_counters, c->d_counters, 8 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+	bundle_max_kernel<<<nblk((size_t)((g.cpd[1] - 1) / 2) * ((g.cpd[2] - 1) / 2), 256), 256, 0, c->stream>>>(g, c->cell_start, c->d_counters + 8);
+	launches += 5;
+	CUDA_TRY(cudaMemcpyAsync(c->h_counters, c->d_counters, 9 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
 	CUDA_TRY(cudaStreamSynchronize(c->stream));
 	size_t n_new = c->h_counters[0];
 	c->max_row = c->h_counters[7];
+	c->max_bundle = c->h_counters[8];
 	if (n_new > c->cap) {
 		timer_stop(c, LS1G_T_SORT, launches);
 		LS1G_FAIL("ls1g: capacity exceeded by halo copies (" + std::to_string(n_new) + " > " + std::to_string(c->cap) + ")");
@@ -347,7 +370,7 @@ int k_sort(ls1g_ctx* c, int make_images) {
 	if (n_new) {
 		GatherArgs a;
 		a.src = c->cur; a.dst = c->alt; a.has_rot = c->has_rot;
-		a.slot_dst = c->slot_dst; a.new_of_old = c->cur.cell;
+		a.slot_dst = c->slot_dst; a.new_of_old = c->cur.cell; a.geometric = make_images ? 1 : 0;
 		// forces are carried through a re-sort only when they exist (API use outside ls1g_run); Vi is not carried
 		bool carry = c->forces_valid;
 		a.F_src = carry ? c->F : nullptr; a.F_dst = c->F_alt;

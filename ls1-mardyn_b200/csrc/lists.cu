@@ -4,6 +4,7 @@
 #include "lists.cuh"
 
 #include <math.h>
+#include <algorithm>
 #include <string.h>
 
 int ls1g_ensure_partials(ls1g_ctx* c, size_t blocks, int nv);
@@ -31,6 +32,7 @@ static NLArgs nl_args(ls1g_ctx* c) {
 	NLArgs a;
 	a.g = c->bgrid; a.pos = c->cur.pos; a.cell = c->cur.cell; a.cell_start = c->cell_start;
 	a.lists = c->lists; a.lcount = c->lcount; a.flags = c->d_flags; a.bpr = c->list_bpr; a.nyi = c->bgrid.cpd[1] - 2; a.lcap4 = c->list_lcap / 4; a.btcap = c->build_tcap;
+	a.nzi = c->bgrid.cpd[2] - 2; a.nyg = (a.nyi + 1) / 2;
 	a.tcap = NL_TCAP;
 	const double rl = c->cfg.lj_cutoff + c->skin;
 	// FP32 filter: coordinates relative to the block centre are < 8 cell lengths: relative error on r^2 near rl^2 < 2e-5;
@@ -39,21 +41,72 @@ static NLArgs nl_args(ls1g_ctx* c) {
 	a.eps24 = c->eps24_h[0]; a.sig2 = c->sig2_h[0]; a.shift6 = c->shift6_h[0]; a.rclj2 = c->rclj2;
 	a.F = c->F; a.Vi = c->Vi; a.partials = c->partials;
 	a.guard = c->guard_on ? c->d_flags + 3 : nullptr; a.guard_thr = (unsigned long long)host_double_bits(c->disp_thr2);
-	a.bmap = c->bmap; a.bflag = c->bflag; a.phase = 0; a.nzi = c->bgrid.cpd[2] - 2;
+	a.bmap = c->bmap; a.bflag = c->bflag; a.phase = 0;
 	return a;
 }
 
-static size_t nl_blocks(const ls1g_ctx* c) { return (size_t)(c->bgrid.cpd[1] - 2) * (c->bgrid.cpd[2] - 2) * (size_t)c->list_bpr; }
+// blocks = cell rows (R = 1) or 2 x 2 row bundles (R = 4) times the blocks per row
+static size_t nl_blocks(const ls1g_ctx* c) {
+	const size_t nyi = c->bgrid.cpd[1] - 2, nzi = c->bgrid.cpd[2] - 2;
+	const size_t groups = c->list_R == 4 ? ((nyi + 1) / 2) * ((nzi + 1) / 2) : nyi * nzi;
+	return groups * (size_t)c->list_bpr;
+}
+static size_t nl_bt(const ls1g_ctx* c) { return c->list_R == 4 ? NLGeom<4>::BT : NLGeom<1>::BT; }
+
+// dynamic shared memory limits are per function AND per device: set once for every device a context lives on
+#define NL_FORCE_SMEM_MAX (3 * (NL_TCAP + 64) * 8)
+template <bool COUNT, bool VI, int FUSE>
+static cudaError_t nl_attr() {
+	cudaError_t e = cudaFuncSetAttribute(nl_force_kernel<COUNT, VI, FUSE, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, NL_FORCE_SMEM_MAX);
+	if (e == cudaSuccess) e = cudaFuncSetAttribute(nl_force_kernel<COUNT, VI, FUSE, true, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, NL_FORCE_SMEM_MAX);
+	if (e == cudaSuccess) e = cudaFuncSetAttribute(nl_force_kernel<COUNT, VI, FUSE, false, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, NL_FORCE_SMEM_MAX);
+	if (e == cudaSuccess) e = cudaFuncSetAttribute(nl_force_kernel<COUNT, VI, FUSE, true, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, NL_FORCE_SMEM_MAX);
+	return e;
+}
+static int nl_force_attrs(const ls1g_ctx* c) {
+	static unsigned long long done_mask = 0;       // bit d: attributes set on device d (ordinals < 64)
+	const int d = c->cfg.device;
+	if (d < 64 && (done_mask >> d & 1ull)) return 0;
+	CUDA_TRY(cudaFuncSetAttribute(nl_build_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, NL_BUILD_SMEM(1, NL_TCAP)));
+	CUDA_TRY(cudaFuncSetAttribute(nl_build_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, NL_BUILD_SMEM(4, NL_TCAP)));
+	CUDA_TRY((nl_attr<true, true, 0>()));
+	CUDA_TRY((nl_attr<true, false, 0>()));
+	CUDA_TRY((nl_attr<false, false, 0>()));
+	CUDA_TRY((nl_attr<true, false, 1>()));
+	CUDA_TRY((nl_attr<false, false, 1>()));
+	CUDA_TRY((nl_attr<true, true, 2>()));
+	CUDA_TRY((nl_attr<true, false, 2>()));
+	CUDA_TRY((nl_attr<false, false, 2>()));
+	if (d < 64) done_mask |= 1ull << d;
+	return 0;
+}
+// ZCHK variant only while the last build saw a (nearly) coincident pair; R as the lists were built (lists.cuh)
+template <bool COUNT, bool VI, int FUSE>
+static void nl_launch(const ls1g_ctx* c, const NLArgs& a, size_t grid) {
+	const size_t sm = (size_t)3 * a.tcap * 8;
+	if (c->list_R == 4) {
+		if (c->list_zchk) nl_force_kernel<COUNT, VI, FUSE, true, 4><<<(unsigned)grid, NLGeom<4>::BT, sm, c->stream>>>(a);
+		else nl_force_kernel<COUNT, VI, FUSE, false, 4><<<(unsigned)grid, NLGeom<4>::BT, sm, c->stream>>>(a);
+	} else {
+		if (c->list_zchk) nl_force_kernel<COUNT, VI, FUSE, true, 1><<<(unsigned)grid, NLGeom<1>::BT, sm, c->stream>>>(a);
+		else nl_force_kernel<COUNT, VI, FUSE, false, 1><<<(unsigned)grid, NLGeom<1>::BT, sm, c->stream>>>(a);
+	}
+}
 
 // after k_sort on the bin grid: size the block grid, build the lists, remember the build positions.
 // The caller synchronises and reads h_flags[1] (overflow bits).
 int k_list_build(ls1g_ctx* c) {
-	c->list_bpr = (int)((c->max_row + NL_BT - 1) / NL_BT);
-	if (c->list_bpr < 1) c->list_bpr = 1;
-	const size_t nb = nl_blocks(c);
 	if (c->list_lcap < NL_LCAP0) c->list_lcap = NL_LCAP0;
-	if (c->build_tcap < NL_TCAP0) c->build_tcap = NL_TCAP0;
-	const size_t want_l = nb * (size_t)c->list_lcap * NL_BT, want_c = nb * NL_BT;
+	if (c->list_R != 1 && c->list_R != 4) c->list_R = 4;
+	if (c->bgrid.cpd[1] - 2 < 2 || c->bgrid.cpd[2] - 2 < 2) c->list_R = 1;      // nothing to bundle
+	// R = 1: 128 slots of a row per block; R = 4: every bundle is cut into ceil(molecules / NL_BUNDLE_FILL) blocks (lists.cuh: nl_plan)
+	c->list_bpr = c->list_R == 4 ? std::max((int)((c->max_bundle + NL_BUNDLE_FILL - 1) / NL_BUNDLE_FILL), (c->bgrid.cpd[0] - 2 + NL_XSPAN - 1) / NL_XSPAN)
+	                             : (int)((c->max_row + NL_BT - 1) / NL_BT);
+	if (c->list_bpr < 1) c->list_bpr = 1;
+	if (c->list_R == 4) c->build_tcap = NL_TCAP;         // 16-row tiles: the large build tile from the start
+	else if (c->build_tcap < NL_TCAP0) c->build_tcap = NL_TCAP0;
+	const size_t nb = nl_blocks(c);
+	const size_t want_l = nb * (size_t)c->list_lcap * nl_bt(c), want_c = nb * nl_bt(c);
 	if (want_l > c->lists_cap) {
 		cudaFree(c->lists); c->lists = nullptr; c->lists_cap = 0;
 		CUDA_TRY(cudaMalloc((void**)&c->lists, want_l * sizeof(unsigned short)));
@@ -73,48 +126,32 @@ int k_list_build(ls1g_ctx* c) {
 	}
 	timer_start(c, LS1G_T_SORT);
 	CUDA_TRY(cudaMemsetAsync(c->d_flags, 0, 3 * sizeof(unsigned long long), c->stream));
-	CUDA_TRY(cudaMemsetAsync(c->d_flags + 5, 0, sizeof(unsigned long long), c->stream));      // boundary-block count
+	CUDA_TRY(cudaMemsetAsync(c->d_flags + 5, 0, 2 * sizeof(unsigned long long), c->stream));      // boundary-block count, near-pair flag
 	CUDA_TRY(cudaMemcpyAsync(c->pos_build, c->cur.pos, c->n_slots * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));
 	CUDA_TRY(cudaMemcpyAsync(c->alt.pos, c->cur.pos, c->n_slots * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));   // fused steps ping-pong cur.pos / alt.pos
 	NLArgs a = nl_args(c);
-	static bool battr = false;
-	if (!battr) { CUDA_TRY(cudaFuncSetAttribute(nl_build_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, NL_BUILD_SMEM(NL_TCAP))); battr = true; }
-	nl_build_kernel<<<(unsigned)nb, NL_BT, NL_BUILD_SMEM(a.btcap), c->stream>>>(a);
+	if (nl_force_attrs(c)) return 1;
+	if (c->list_R == 4) nl_build_kernel<4><<<(unsigned)nb, NLGeom<4>::BT, NL_BUILD_SMEM(4, a.btcap), c->stream>>>(a);
+	else nl_build_kernel<1><<<(unsigned)nb, NLGeom<1>::BT, NL_BUILD_SMEM(1, a.btcap), c->stream>>>(a);
 	CUDA_TRY(cudaGetLastError());
 	CUDA_TRY(cudaMemcpyAsync(c->h_flags, c->d_flags, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
 	CUDA_TRY(cudaMemcpyAsync(c->h_flags + 3, c->d_flags + 5, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));   // read by the caller after its sync
+	CUDA_TRY(cudaMemcpyAsync(c->h_flags + 8, c->d_flags + 6, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));   // near-pair flag
 	timer_stop(c, LS1G_T_SORT, 2);
-	return 0;
-}
-
-// count_pairs: also count the pairs inside the cutoff (ls1g_last_pair_count); always on when the potential is shifted
-static int nl_force_attrs() {
-	static bool attr_set = false;
-	if (!attr_set) {
-		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<true, true, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
-		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<true, false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
-		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<false, false, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
-		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<true, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
-		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<false, false, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
-		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<true, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
-		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<true, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
-		CUDA_TRY(cudaFuncSetAttribute(nl_force_kernel<false, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * NL_TCAP * 8));
-		attr_set = true;
-	}
 	return 0;
 }
 
 int k_forces_list(ls1g_ctx* c, int last_step) {
 	const size_t nb = nl_blocks(c);
 	if (ls1g_ensure_partials(c, nb ? nb : 1, 5)) return 1;
-	if (nl_force_attrs()) return 1;
+	if (nl_force_attrs(c)) return 1;
 	NLArgs a = nl_args(c);
 	a.tcap = c->list_tcap;      // the largest tile of the last build: shared memory sized to what this system needs
 	timer_start(c, LS1G_T_FORCE);
 	// last step of a run: pair statistics + per-molecule virial; other steps: forces + the scalar sums of the step record
-	if (last_step || c->vi_every_step) nl_force_kernel<true, true, 0><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
-	else if (c->shift6_h[0] != 0.) nl_force_kernel<true, false, 0><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
-	else nl_force_kernel<false, false, 0><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
+	if (last_step || c->vi_every_step) nl_launch<true, true, 0>(c, a, nb);
+	else if (c->shift6_h[0] != 0.) nl_launch<true, false, 0>(c, a, nb);
+	else nl_launch<false, false, 0>(c, a, nb);
 	timer_stop(c, LS1G_T_FORCE, 1);
 	if (k_force_finalize(c, nb)) return 1;
 	CUDA_TRY(cudaGetLastError());
@@ -144,7 +181,7 @@ __global__ void __launch_bounds__(256) fused_finalize_kernel(const double* __res
 int k_forces_list_fused(ls1g_ctx* c, double dt, int phase) {
 	const size_t nb = nl_blocks(c);
 	if (ls1g_ensure_partials(c, nb ? nb : 1, 8)) return 1;
-	if (nl_force_attrs()) return 1;
+	if (nl_force_attrs(c)) return 1;
 	NLArgs a = nl_args(c);
 	a.tcap = c->list_tcap;
 	a.dt = dt; a.dt_half = 0.5 * dt; a.mass = c->comps_h[0].mass;
@@ -153,8 +190,8 @@ int k_forces_list_fused(ls1g_ctx* c, double dt, int phase) {
 	const size_t grid = phase == 2 ? (size_t)c->n_boundary_blocks : nb;
 	timer_start(c, LS1G_T_FORCE);
 	if (grid) {
-		if (c->shift6_h[0] != 0.) nl_force_kernel<true, false, 1><<<(unsigned)grid, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
-		else nl_force_kernel<false, false, 1><<<(unsigned)grid, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
+		if (c->shift6_h[0] != 0.) nl_launch<true, false, 1>(c, a, grid);
+		else nl_launch<false, false, 1>(c, a, grid);
 	}
 	timer_stop(c, LS1G_T_FORCE, grid ? 1 : 0);
 	CUDA_TRY(cudaGetLastError());
@@ -175,16 +212,16 @@ int k_forces_list_fused(ls1g_ctx* c, double dt, int phase) {
 int k_forces_list_post(ls1g_ctx* c, double dt, int vi) {
 	const size_t nb = nl_blocks(c);
 	if (ls1g_ensure_partials(c, nb ? nb : 1, 8)) return 1;
-	if (nl_force_attrs()) return 1;
+	if (nl_force_attrs(c)) return 1;
 	NLArgs a = nl_args(c);
 	a.tcap = c->list_tcap;
 	a.dt = dt; a.dt_half = 0.5 * dt; a.mass = c->comps_h[0].mass;
 	a.vel = c->cur.vel; a.pos_out = nullptr; a.pos_build = c->pos_build;
 	timer_start(c, LS1G_T_FORCE);
 	if (nb) {
-		if (vi || c->vi_every_step) nl_force_kernel<true, true, 2><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
-		else if (c->shift6_h[0] != 0.) nl_force_kernel<true, false, 2><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
-		else nl_force_kernel<false, false, 2><<<(unsigned)nb, NL_BT, (size_t)3 * a.tcap * 8, c->stream>>>(a);
+		if (vi || c->vi_every_step) nl_launch<true, true, 2>(c, a, nb);
+		else if (c->shift6_h[0] != 0.) nl_launch<true, false, 2>(c, a, nb);
+		else nl_launch<false, false, 2>(c, a, nb);
 	}
 	timer_stop(c, LS1G_T_FORCE, nb ? 1 : 0);
 	CUDA_TRY(cudaGetLastError());

@@ -11,31 +11,45 @@
 // Frozen layout: between rebuilds molecules keep their slot (no re-sort, no wrap); periodic images are refreshed from
 // their source slot (halo_refresh_kernel).  The sort bins on c->bgrid whose cells are >= rc + skin.
 //
-// Work decomposition (both kernels, identical so that tile indices stay valid):
-//   block (row, b)  = 128 consecutive owned slots [s0, s1) of one cell row (y, z); lane = one molecule
-//   tile            = the 9 neighbouring rows cut to cells [x_first-1, x_last+1] of the block's molecules: 9 contiguous
-//                     slot ranges, staged in shared memory (FP64 originals; the build adds FP32 copies for the filter)
-//   row groups      = the force kernel stages the tile in three phases (less than half the shared memory, twice the
-//                     resident warps).  Every group is point-symmetric about the own row: {own row + 2 opposite corner
-//                     rows}, {the 4 edge rows}, {the other 2 corner rows}; wherever a molecule sits in its cell, what it
-//                     loses in one row of a group it gains in the opposite one, so the lanes of a warp stay in step.  A
-//                     molecule's list is grouped accordingly, each group padded to a multiple of 4 entries with index 0
-//   list entry      = 16-bit index into the group's tile + NL_DUMMY; tile entries 0..NL_DUMMY-1 hold a far-away dummy
-//                     position (r^2 = 3e300 fails the cutoff test), so padding needs no special case; lists[((blk*(LCAP/4) + t/4)*128 + thread)*4 + t%4]: one 8-byte
-//                     load = 4 entries; lcount packs the three cumulative group ends (in units of 4 entries, 8 bits each)
+// Work decomposition (both kernels, identical so that tile indices stay valid), template parameter R:
+//   block           = R = 1: 128 consecutive owned slots of one cell row (y, z), 128 threads.
+//                     R = 4 (default): a 2 x 2 bundle of cell rows (2gy+1.., 2gz+1..) holding M molecules is cut into
+//                     nbk = max(ceil(M / 508), ceil(cells in x / 8)) blocks of 512 threads; block j owns the j-th nbk-th OF EVERY ROW (slots
+//                     [j n_r / nbk, (j+1) n_r / nbk) of row r): rows of different density - the lanes of an fcc lattice - still
+//                     line up in x as long as each row is about homogeneous along x.  lane = one molecule, rows back to back.
+//                     The 4 x 4 rows around a bundle are 16 tile rows for ~500 molecules where four single-row blocks stage 36:
+//                     less than half the shared memory and staging traffic per molecule, which is what lets 32 warps stay
+//                     resident with the WHOLE tile on chip.  Where the rows do not line up the tile outgrows its capacity, the
+//                     build reports it and the host falls back to R = 1
+//   tile            = the 9 (16) neighbouring rows cut to cells [x_first-1, x_last+1] of the block's molecules: contiguous slot
+//                     ranges.  The force kernel keeps the whole tile in shared memory as two arrays, Z[k] (8 B) and XY[k] (16 B):
+//                     one LDS.64 + one LDS.128 per listed partner, entry k of both addressed from one 16-bit list entry.  The tile
+//                     is staged with cp.async (LDGSTS: global -> shared without registers) in two batches, each signalling an
+//                     mbarrier; a warp waits for the data it is about to read, never for other warps: no __syncthreads between
+//                     the prologue and the final block sum, and the second batch lands while the first is being evaluated
+//   list entry      = 16 bits, 8 * (tile index + NL_DUMMY) = byte offset of the partner in Z (twice that in XY); tile entries
+//                     0..NL_DUMMY-1 hold a far-away dummy position (r^2 = 3e300 fails the cutoff test), so padding needs no
+//                     special case.  lists[((blk*(LCAP/4) + t/4)*BT + thread)*4 + t%4]: one 8-byte load = 4 entries, padded
+//                     to a multiple of 4 with entry 0.  The molecule itself is not in its list.  Order: tile rows in staging
+//                     order, x ascending.  lcount = quads of the molecule | quads that lie entirely in batch A << 16
 #pragma once
 
-#define NL_BT 128          // threads per block = molecules per block
-#define NL_TCAP0 3072      // capacity of the build kernel's 9-row FP32 tile (candidates) to start with, multiple of 4
+#define NL_BT 128          // owned slots per cell row and block
+#define NL_TCAP0 3072      // capacity of the build kernel's FP32 tile (candidates) to start with, multiple of 4
 #define NL_TCAP 5120       // ... after a tile overflow (denser systems; fewer resident blocks)
 #define NL_LCAP0 128       // list entries per molecule to start with (multiple of 4); doubled on overflow up to NL_LCAP_MAX
-#define NL_LCAP_MAX 1020   // lcount packs the group ends in units of 4 entries, 8 bits each
-#define NL_DUMMY 4         // dummy entries at the start of every group tile (keeps real entries 4-aligned)
+#define NL_LCAP_MAX 1020   // lcount packs quad counts in 16 bits
+#define NL_DUMMY 4         // dummy entries at the start of the tile (keeps real entries 4-aligned)
+#define NL_MAXROWS 16
+#define NL_BUNDLE_FILL 508 // R = 4: molecules per block a bundle is cut for (4 rows x integer rounding stay within 512 threads)
+#define NL_XSPAN 8         // R = 4: a block spans at most about this many cells in x (bundles at the upper faces hold fewer than 4 rows)
 
-// staging / scan order of the 9 neighbour rows (r = 3*(dz+1) + (dy+1)): three point-symmetric groups
+template <int R> struct NLGeom;
+template <> struct NLGeom<1> { static constexpr int BT = NL_BT, NR = 9, ROWS_A = 3, QCAP = 64; };
+template <> struct NLGeom<4> { static constexpr int BT = 4 * NL_BT, NR = 16, ROWS_A = 8, QCAP = 32; };
+
+// R = 1: staging / scan order of the 9 neighbour rows (r = 3*(dz+1) + (dy+1)): own row first, then point-symmetric pairs
 __device__ __constant__ int NL_ORD[9] = {4, 0, 8, 1, 7, 3, 5, 2, 6};
-__device__ __constant__ int NL_GRP[4] = {0, 3, 7, 9};      // group g = positions [NL_GRP[g], NL_GRP[g+1]) of NL_ORD
-
 
 enum { NL_OVF_TILE = 1, NL_OVF_LIST = 2, NL_OVF_ROW = 4 };
 
@@ -44,15 +58,16 @@ struct NLArgs {
 	const double4* pos; const uint32_t* cell; const uint32_t* cell_start;
 	unsigned short* lists; uint32_t* lcount;
 	unsigned long long* flags;  // [1] |= NL_OVF_*
-	int bpr;                    // blocks per row
+	int bpr;                    // blocks per row (R = 4: per row bundle)
 	int lcap4;                  // list capacity per molecule in units of 4 entries
-	int btcap;                  // capacity of the build kernel's 9-row tile (NL_TCAP0 or NL_TCAP)
-	int nyi;
-	int tcap;                   // slab tile capacity of the force launch (max slab tile of the last build), multiple of 4
+	int btcap;                  // capacity of the build kernel's tile (NL_TCAP0 or NL_TCAP)
+	int nyi, nzi;               // owned rows per dimension
+	int nyg;                    // R = 4: row bundles in y = ceil(nyi / 2)
+	int tcap;                   // tile capacity of the force launch (largest tile of the last build), multiple of 4
 	float rl2f;                 // (rc + skin)^2 * (1 + margin), FP32 filter
 	double eps24, sig2, shift6, rclj2;
 	double *F, *Vi;
-	double* partials;           // [blocks][5]
+	double* partials;           // [blocks][5 or 8]
 	const unsigned long long* guard; unsigned long long guard_thr;   // skip the launch when *guard > guard_thr (lists expired)
 	// FUSE: leapfrog post(n) + pre(n+1) in the epilogue (NVE steps of ls1g_run)
 	double dt, dt_half, mass;
@@ -64,161 +79,242 @@ struct NLArgs {
 	// phase 1 = all blocks, boundary blocks return at once; phase 2 = a compact grid over bmap (the boundary blocks).  phase 0 = one launch.
 	uint32_t* bmap;             // [n_boundary] block ids of the boundary blocks (order irrelevant: every block owns its outputs)
 	unsigned char* bflag;       // [blocks] 1 = boundary
-	int phase, nzi;
+	int phase;
 };
 
-struct NLBlock {
-	uint32_t s0, s1;            // owned slots of this block
-	int total;                  // tile entries (padded)
-	bool live;
+// Shared-memory plan of one block, identical in build and force kernels
+struct NLPlan {
+	uint32_t beg[NL_MAXROWS];   // first slot of tile row p
+	int len[NL_MAXROWS];        // slots of tile row p (0: row outside the grid or next to no live owned row)
+	int off[NL_MAXROWS + 1];    // tile index of its first entry (rows padded to multiples of 4)
+	uint32_t s0[4], s1[4];      // owned slots of owned row q (s0 == s1: none)
+	int o[5];                   // first thread of owned row q (rows back to back); o[R] = molecules of the block
+	int xf[4], xl[4];           // first / last cell (x) of those slots
+	int ty[4], tz[4];           // cell row (y, z) of owned row q
+	int x_first, x_last, live, boundary;
 };
 
-// Common prologue: slot range, tile plan (s_beg/s_off per row) - identical in build and force kernels.
-__device__ __forceinline__ NLBlock nl_plan(const NLArgs& a, uint32_t* s_beg, int* s_off, int* s_len, int& x_first, int& x_last, const unsigned blk) {
+// tile row p of block (gy, gz) -> cell row (y, z), or y < 0 when outside the grid
+template <int R>
+__device__ __forceinline__ void nl_tile_row(const NLArgs& a, int gy, int gz, int p, int& y, int& z) {
+	if (R == 1) { const int r = NL_ORD[p]; y = gy + r % 3 - 1; z = gz + r / 3 - 1; }
+	else { y = 2 * gy + (p & 3); z = 2 * gz + (p >> 2); if (y > a.g.cpd[1] - 1 || z > a.g.cpd[2] - 1) y = -1; }
+}
+
+// Common prologue: owned slot ranges, tile plan.  All threads call it; three __syncthreads.
+template <int R>
+__device__ __forceinline__ void nl_plan(const NLArgs& a, NLPlan& P, const unsigned blk) {
 	const Grid& g = a.g;
 	const int nx = g.cpd[0], ny = g.cpd[1];
-	const int row = blk / a.bpr, bi = blk % a.bpr;
-	const int cy = row % a.nyi + 1, cz = row / a.nyi + 1;
-	const int crow = (cz * ny + cy) * nx;
-	const uint32_t rs = a.cell_start[crow + 1], re = a.cell_start[crow + nx - 1];
-	NLBlock b;
-	b.s0 = rs + (uint32_t)bi * NL_BT;
-	b.live = b.s0 < re;
-	b.s1 = min(b.s0 + NL_BT, re);
-	b.total = 0;
-	if (bi == a.bpr - 1 && b.s0 + NL_BT < re && threadIdx.x == 0) atomicOr(a.flags + 1, (unsigned long long)NL_OVF_ROW);
-	if (!b.live) return b;
-	x_first = (int)((a.cell[b.s0] & ~HALO_FLAG) % (uint32_t)nx);
-	x_last = (int)((a.cell[b.s1 - 1] & ~HALO_FLAG) % (uint32_t)nx);
-	if (threadIdx.x < 9) {
-		const int r = NL_ORD[threadIdx.x];               // s_beg / s_len / s_off are indexed by POSITION in NL_ORD
-		const int cr = ((cz + r / 3 - 1) * ny + (cy + r % 3 - 1)) * nx;
-		const uint32_t beg = a.cell_start[cr + x_first - 1], end = a.cell_start[cr + x_last + 2];
-		s_beg[threadIdx.x] = beg; s_len[threadIdx.x] = (int)(end - beg);
+	const int grp = blk / a.bpr, bi = blk % a.bpr;
+	// R = 1: gy, gz = the cell row itself; R = 4: bundle coordinates, owned rows (2gy+1+(q&1), 2gz+1+(q>>1))
+	const int gy = R == 1 ? grp % a.nyi + 1 : grp % a.nyg, gz = R == 1 ? grp / a.nyi + 1 : grp / a.nyg;
+	const int tid = threadIdx.x;
+	if (tid < R) {
+		const int q = tid;
+		const int cy = R == 1 ? gy : 2 * gy + 1 + (q & 1), cz = R == 1 ? gz : 2 * gz + 1 + (q >> 1);
+		uint32_t s0 = 0, s1 = 0; int xf = 0x7fffffff, xl = -1;
+		if (R == 1) {
+			const int crow = (cz * ny + cy) * nx;
+			const uint32_t rs = a.cell_start[crow + 1], re = a.cell_start[crow + nx - 1];
+			s0 = rs + (uint32_t)bi * NL_BT; s1 = min(s0 + NL_BT, re);
+			if (bi == a.bpr - 1 && s0 + NL_BT < re) atomicOr(a.flags + 1, (unsigned long long)NL_OVF_ROW);
+			if (s0 >= re) s1 = s0;
+		} else {
+			// every thread q sums the whole bundle (4 x 2 loads) so that no barrier separates M from the cut
+			uint32_t M = 0, rs = 0, n = 0;
+#pragma unroll
+			for (int r = 0; r < 4; ++r) {
+				const int ry = 2 * gy + 1 + (r & 1), rz = 2 * gz + 1 + (r >> 1);
+				if (ry > a.nyi || rz > a.nzi) continue;
+				const int crow = (rz * ny + ry) * nx;
+				const uint32_t b0 = a.cell_start[crow + 1], b1 = a.cell_start[crow + nx - 1];
+				M += b1 - b0;
+				if (r == q) { rs = b0; n = b1 - b0; }
+			}
+			const uint32_t nbk = max(max(1u, (M + NL_BUNDLE_FILL - 1) / NL_BUNDLE_FILL), (uint32_t)(nx - 2 + NL_XSPAN - 1) / NL_XSPAN);
+			if ((uint32_t)bi < nbk) {
+				s0 = rs + (uint32_t)((unsigned long long)bi * n / nbk);
+				s1 = rs + (uint32_t)((unsigned long long)(bi + 1) * n / nbk);
+			}
+			if (q == 0 && nbk > (uint32_t)a.bpr) atomicOr(a.flags + 1, (unsigned long long)NL_OVF_ROW);
+		}
+		if (s0 < s1) {
+			xf = (int)((a.cell[s0] & ~HALO_FLAG) % (uint32_t)nx);
+			xl = (int)((a.cell[s1 - 1] & ~HALO_FLAG) % (uint32_t)nx);
+		}
+		P.s0[q] = s0; P.s1[q] = s1; P.xf[q] = xf; P.xl[q] = xl; P.ty[q] = cy; P.tz[q] = cz;
 	}
 	__syncthreads();
-	if (threadIdx.x == 0) {
+	int x_first = 0x7fffffff, x_last = -1;
+#pragma unroll
+	for (int q = 0; q < R; ++q) { x_first = min(x_first, P.xf[q]); x_last = max(x_last, P.xl[q]); }
+	const bool live = x_last >= 0;
+	if (tid < NLGeom<R>::NR) {
+		int y, z;
+		nl_tile_row<R>(a, gy, gz, tid, y, z);
+		uint32_t beg = 0; int len = 0;
+		bool need = live && y >= 0;
+		if (need && R > 1) {          // only rows next to an owned row that has molecules in this block
+			need = false;
+#pragma unroll
+			for (int q = 0; q < R; ++q) if (P.xl[q] >= 0 && abs(P.ty[q] - y) <= 1 && abs(P.tz[q] - z) <= 1) need = true;
+		}
+		if (need) {
+			const int cr = (z * ny + y) * nx;
+			beg = a.cell_start[cr + x_first - 1];
+			len = (int)(a.cell_start[cr + x_last + 2] - beg);
+		}
+		P.beg[tid] = beg; P.len[tid] = len;
+	}
+	__syncthreads();
+	if (tid == 0) {
 		int off = 0;
-		for (int r = 0; r < 9; ++r) { s_off[r] = off; off += (s_len[r] + 3) & ~3; }
-		s_off[9] = off;
+		for (int r = 0; r < NLGeom<R>::NR; ++r) { P.off[r] = off; off += (P.len[r] + 3) & ~3; }
+		P.off[NLGeom<R>::NR] = off;
+		P.x_first = x_first; P.x_last = x_last;
+		P.o[0] = 0;
+		for (int q = 0; q < R; ++q) P.o[q + 1] = P.o[q] + (int)(P.s1[q] - P.s0[q]);
+		bool lv = live;
+		if (lv && off > a.btcap) { atomicOr(a.flags + 1, (unsigned long long)NL_OVF_TILE); lv = false; }
+		P.live = lv ? 1 : 0;
+		// a block is "boundary" when its tile reaches into a halo cell (the positions there arrive with the halo refresh)
+		const int ylo = R == 1 ? gy - 1 : 2 * gy, yhi = R == 1 ? gy + 1 : min(2 * gy + 3, ny - 1);
+		const int zlo = R == 1 ? gz - 1 : 2 * gz, zhi = R == 1 ? gz + 1 : min(2 * gz + 3, g.cpd[2] - 1);
+		P.boundary = lv && (ylo == 0 || zlo == 0 || yhi == ny - 1 || zhi == g.cpd[2] - 1 || x_first <= 1 || x_last >= nx - 2);
 	}
 	__syncthreads();
-	b.total = s_off[9];
-	if (b.total > a.btcap) {
-		if (threadIdx.x == 0) atomicOr(a.flags + 1, (unsigned long long)NL_OVF_TILE);
-		b.live = false;
+}
+
+// thread -> (owned row q, slot i); has = the thread has a molecule
+template <int R>
+__device__ __forceinline__ void nl_my_slot(const NLPlan& P, int tid, int& q, uint32_t& i, bool& has) {
+	if (R == 1) { q = 0; i = P.s0[0] + (uint32_t)tid; has = i < P.s1[0]; }
+	else {
+		q = (tid >= P.o[1]) + (tid >= P.o[2]) + (tid >= P.o[3]);
+		i = P.s0[q] + (uint32_t)(tid - P.o[q]);
+		has = tid < P.o[4];
 	}
-	return b;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
 // build: FP32 candidate filter with radius rc + skin -> per-molecule lists of tile indices
 // ---------------------------------------------------------------------------------------------------------------
-#define NL_QCAP 64         // per-lane queue entries of one row group (shared memory), multiple of 4
-#define NL_BUILD_SMEM(tcap) (3 * (tcap) * 4 + NL_QCAP * NL_BT * 2)
+#define NL_BUILD_SMEM(R, tcap) (3 * (tcap) * 4 + NLGeom<R>::QCAP * NLGeom<R>::BT * 2)
 
-__global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
+template <int R>
+__global__ void __launch_bounds__(NLGeom<R>::BT) nl_build_kernel(NLArgs a) {
+	constexpr int BT = NLGeom<R>::BT, NR = NLGeom<R>::NR, QCAP = NLGeom<R>::QCAP;
 	extern __shared__ __align__(16) unsigned char nl_bsm[];
 	float* xs = (float*)nl_bsm; float* ys = xs + a.btcap; float* zs = ys + a.btcap;
-	unsigned short* q = (unsigned short*)(zs + a.btcap);          // q[t][tid]: survivors of the current row group, one column per lane
-	__shared__ uint32_t s_beg[9]; __shared__ int s_off[10], s_len[9];
+	unsigned short* q = (unsigned short*)(zs + a.btcap);          // q[t][tid]: queued survivors, one column per lane
+	__shared__ NLPlan P;
 	const Grid& g = a.g;
-	const int tid = threadIdx.x, lane = tid & 31;
-	int x_first = 0, x_last = 0;
-	const NLBlock b = nl_plan(a, s_beg, s_off, s_len, x_first, x_last, blockIdx.x);
+	const int tid = threadIdx.x;
+	nl_plan<R>(a, P, blockIdx.x);
 	if (tid == 0 && a.bflag) {      // inner / boundary classification for the overlapped multi-rank force pass (see NLArgs)
-		const int row_ = blockIdx.x / a.bpr, cy_ = row_ % a.nyi + 1, cz_ = row_ / a.nyi + 1;
-		const bool boundary = b.live && (cy_ == 1 || cy_ == a.nyi || cz_ == 1 || cz_ == a.nzi || x_first <= 1 || x_last >= a.g.cpd[0] - 2);
-		a.bflag[blockIdx.x] = boundary ? 1 : 0;
-		if (boundary) a.bmap[atomicAdd(a.flags + 5, 1ull)] = blockIdx.x;
+		a.bflag[blockIdx.x] = P.boundary ? 1 : 0;
+		if (P.boundary) a.bmap[atomicAdd(a.flags + 5, 1ull)] = blockIdx.x;
 	}
-	if (!b.live) return;
-	if (tid == 0) {      // largest slab tile of this build: sizes the force kernel's shared memory
-		const int m = max(max(s_off[3], s_off[7] - s_off[3]), s_off[9] - s_off[7]) + NL_DUMMY;
+	if (!P.live) return;
+	if (tid == 0) {      // largest tile of this build: sizes the force kernel's shared memory
+		const int m = P.off[NR] + NL_DUMMY;
 		if ((unsigned long long)m > *(volatile unsigned long long*)(a.flags + 2)) atomicMax(a.flags + 2, (unsigned long long)m);
 	}
 	const int nx = g.cpd[0], ny = g.cpd[1];
-	const int row = blockIdx.x / a.bpr;
-	const int cy = row % a.nyi + 1, cz = row / a.nyi + 1;
+	const int x_first = P.x_first, x_last = P.x_last;
+	// origin of the FP32 coordinates: the block centre
 	const double ox = g.halo_min[0] + 0.5 * (x_first + x_last + 1) * g.cell_len[0];
-	const double oy = g.halo_min[1] + (cy + 0.5) * g.cell_len[1];
-	const double oz = g.halo_min[2] + (cz + 0.5) * g.cell_len[2];
-	for (int r = 0; r < 9; ++r) {
-		const int off = s_off[r], len = s_len[r], padded = (len + 3) & ~3;
-		const uint32_t beg = s_beg[r];
-		for (int t = tid; t < padded; t += NL_BT) {
+	const double oy = g.halo_min[1] + (R == 1 ? P.ty[0] + 0.5 : P.ty[0] + 1.0) * g.cell_len[1];
+	const double oz = g.halo_min[2] + (R == 1 ? P.tz[0] + 0.5 : P.tz[0] + 1.0) * g.cell_len[2];
+	for (int r = 0; r < NR; ++r) {
+		const int off = P.off[r], len = P.len[r], padded = (len + 3) & ~3;
+		const uint32_t beg = P.beg[r];
+		for (int t = tid; t < padded; t += BT) {
 			float x = 1e30f, y = 1e30f, z = 1e30f;
-			if (t < len) { const double4 P = a.pos[beg + t]; x = (float)(P.x - ox); y = (float)(P.y - oy); z = (float)(P.z - oz); }
+			if (t < len) { const double4 Q = a.pos[beg + t]; x = (float)(Q.x - ox); y = (float)(Q.y - oy); z = (float)(Q.z - oz); }
 			xs[off + t] = x; ys[off + t] = y; zs[off + t] = z;
 		}
 	}
 	__syncthreads();
-	// this warp's molecules and the cells they span
-	const uint32_t w0 = b.s0 + (uint32_t)(tid & ~31);
-	if (w0 >= b.s1) return;
-	const uint32_t w1 = min(w0 + 32u, b.s1);
-	const int xw_first = (int)((a.cell[w0] & ~HALO_FLAG) % (uint32_t)nx), xw_last = (int)((a.cell[w1 - 1] & ~HALO_FLAG) % (uint32_t)nx);
-	const uint32_t i = w0 + lane;
-	const bool active = i < w1;
+	// this thread's molecule; a warp may hold molecules of more than one owned row (R = 4: rows back to back)
+	int qr; uint32_t i; bool active;
+	nl_my_slot<R>(P, tid, qr, i, active);
+	unsigned todo = __ballot_sync(0xffffffffu, active);
+	if (!todo) return;
 	float fx = -1e30f, fy = -1e30f, fz = -1e30f;
 	if (active) { const double4 Pi = a.pos[i]; fx = (float)(Pi.x - ox); fy = (float)(Pi.y - oy); fz = (float)(Pi.z - oz); }
-	uint2* my = (uint2*)(a.lists + ((size_t)blockIdx.x * a.lcap4 * NL_BT + tid) * 4);     // entries 4t..4t+3 at my[t * NL_BT]
+	uint2* my = (uint2*)(a.lists + ((size_t)blockIdx.x * a.lcap4 * BT + tid) * 4);     // entries 4t..4t+3 at my[t * BT]
 	unsigned short* const q0 = q + tid;
 	// the queue is addressed through one 32-bit shared-window register (append = st.shared.u16 + add, both predicated)
 	const uint32_t qa0 = (uint32_t)__cvta_generic_to_shared(q0);
-	const uint32_t qalim = qa0 + (NL_QCAP - 4) * NL_BT * 2;       // room for one more scan iteration
+	const uint32_t qalim = qa0 + (QCAP - 4) * BT * 2;       // room for one more scan iteration
 	uint32_t qa = qa0;
 	int done4 = 0; bool ovf = false;       // groups of 4 entries already written to the list
-	uint32_t ends = 0;
+	int nA4 = 0;                           // quads that only hold entries of staging batch A
+	bool near = false;                     // a partner closer than 1e-4 (possibly coincident): the force kernel keeps its r2 == 0 test
 	const float rl2 = a.rl2f;
-	int grp = 0;
-	// queue -> list: complete quads go out as packed 8-byte stores; a mid-group flush (queue full) keeps the 0..3 left-over
-	// entries at the front of the queue, the flush at the end of a row group pads them with the dummy entry
+	// queue -> list: complete quads go out as packed 8-byte stores; a flush in between (queue full) keeps the 0..3 left-over
+	// entries at the front of the queue, the final flush pads them with the dummy entry
 	auto flush = [&](bool final) {
-		int cnt = (int)(qa - qa0) / (NL_BT * 2);
-		if (final) while (cnt & 3) { q0[cnt * NL_BT] = 0; ++cnt; }
+		int cnt = (int)(qa - qa0) / (BT * 2);
+		if (final) while (cnt & 3) { q0[cnt * BT] = 0; ++cnt; }
 		const int n4 = cnt >> 2, rem = cnt & 3;
 		if (done4 + n4 > a.lcap4) ovf = true;
 		else {
 			for (int t = 0; t < n4; ++t) {
-				const unsigned short* e = q0 + 4 * t * NL_BT;
+				const unsigned short* e = q0 + 4 * t * BT;
 				uint2 w;
-				w.x = (uint32_t)e[0] | ((uint32_t)e[NL_BT] << 16);
-				w.y = (uint32_t)e[2 * NL_BT] | ((uint32_t)e[3 * NL_BT] << 16);
-				my[(size_t)(done4 + t) * NL_BT] = w;
+				w.x = (uint32_t)e[0] | ((uint32_t)e[BT] << 16);
+				w.y = (uint32_t)e[2 * BT] | ((uint32_t)e[3 * BT] << 16);
+				my[(size_t)(done4 + t) * BT] = w;
 			}
 			done4 += n4;
 		}
-		for (int t = 0; t < rem; ++t) q0[t * NL_BT] = q0[(4 * n4 + t) * NL_BT];
-		qa = qa0 + rem * (NL_BT * 2);
+		for (int t = 0; t < rem; ++t) q0[t * BT] = q0[(4 * n4 + t) * BT];
+		qa = qa0 + rem * (BT * 2);
 	};
-	for (int p = 0; p < 9; ++p) {
-		const int r = NL_ORD[p];
-		const int gbase = s_off[NL_GRP[grp]];          // indices are relative to the row group's tile
-		const int cr = ((cz + r / 3 - 1) * ny + (cy + r % 3 - 1)) * nx;
-		const uint32_t lo = a.cell_start[cr + xw_first - 1], hi = a.cell_start[cr + xw_last + 2];
-		const uint32_t beg = s_beg[p];
-		const int k0 = s_off[p] + (int)((lo - beg) & ~3u), k1 = s_off[p] + (int)((hi - beg + 3u) & ~3u);
-		int val = k0 - gbase + NL_DUMMY;               // list entry of candidate k0
-		for (int k = k0; k < k1; k += 4, val += 4) {
-			const float4 cx4 = *(const float4*)(xs + k), cy4 = *(const float4*)(ys + k), cz4 = *(const float4*)(zs + k);
-			const float cxa[4] = {cx4.x, cx4.y, cx4.z, cx4.w}, cya[4] = {cy4.x, cy4.y, cy4.z, cy4.w}, cza[4] = {cz4.x, cz4.y, cz4.z, cz4.w};
+	const int gy = R == 1 ? P.ty[0] : (P.ty[0] - 1) / 2, gz = R == 1 ? P.tz[0] : (P.tz[0] - 1) / 2;
+	while (todo) {      // one pass per owned row present in this warp (warp-uniform control flow)
+		const int qq = __shfl_sync(0xffffffffu, qr, __ffs(todo) - 1);
+		const unsigned grp = __ballot_sync(0xffffffffu, active && qr == qq);
+		todo &= ~grp;
+		const bool mine = active && qr == qq;
+		// the cells the lanes of this row span (slots ascend with the lane)
+		const uint32_t iw0 = __shfl_sync(0xffffffffu, i, __ffs(grp) - 1), iw1 = __shfl_sync(0xffffffffu, i, 31 - __clz(grp));
+		const int xw_first = (int)((a.cell[iw0] & ~HALO_FLAG) % (uint32_t)nx), xw_last = (int)((a.cell[iw1] & ~HALO_FLAG) % (uint32_t)nx);
+		const int cy = P.ty[qq], cz = P.tz[qq];
+		const float gx = mine ? fx : -1e30f, gyf = mine ? fy : -1e30f, gzf = mine ? fz : -1e30f;
+		for (int p = 0; p < NR; ++p) {
+			int y, z;
+			nl_tile_row<R>(a, gy, gz, p, y, z);
+			if (y >= 0 && abs(y - cy) <= 1 && abs(z - cz) <= 1 && P.len[p] > 0) {
+				const int cr = (z * ny + y) * nx;
+				const uint32_t lo = a.cell_start[cr + xw_first - 1], hi = a.cell_start[cr + xw_last + 2];
+				const uint32_t beg = P.beg[p];
+				const int k0 = P.off[p] + (int)((lo - beg) & ~3u), k1 = P.off[p] + (int)((hi - beg + 3u) & ~3u);
+				int val = (k0 + NL_DUMMY) * 8;                 // list entry of candidate k0
+				const int selfv = (y == cy && z == cz && mine) ? (P.off[p] + (int)(i - beg) + NL_DUMMY) * 8 : -1;      // the molecule itself
+				for (int k = k0; k < k1; k += 4, val += 32) {
+					const float4 cx4 = *(const float4*)(xs + k), cy4 = *(const float4*)(ys + k), cz4 = *(const float4*)(zs + k);
+					const float cxa[4] = {cx4.x, cx4.y, cx4.z, cx4.w}, cya[4] = {cy4.x, cy4.y, cy4.z, cy4.w}, cza[4] = {cz4.x, cz4.y, cz4.z, cz4.w};
 #pragma unroll
-			for (int u = 0; u < 4; ++u) {
-				const float dx = fx - cxa[u], dy = fy - cya[u], dz = fz - cza[u];
-				const float r2 = dx * dx + dy * dy + dz * dz;
-				if (r2 < rl2) { asm volatile("st.shared.u16 [%0], %1;" :: "r"(qa), "h"((unsigned short)(val + u)) : "memory"); qa += NL_BT * 2; }
+					for (int u = 0; u < 4; ++u) {
+						const float dx = gx - cxa[u], dy = gyf - cya[u], dz = gzf - cza[u];
+						const float r2 = dx * dx + dy * dy + dz * dz;
+						if (r2 < 1e-8f && val + 8 * u != selfv) near = true;
+						if (r2 < rl2 && val + 8 * u != selfv) { asm volatile("st.shared.u16 [%0], %1;" :: "r"(qa), "h"((unsigned short)(val + 8 * u)) : "memory"); qa += BT * 2; }
+					}
+					if (qa > qalim) flush(false);
+				}
 			}
-			if (qa > qalim) flush(false);
-		}
-		if (p + 1 == NL_GRP[grp + 1]) {                 // end of a row group: pad to a multiple of 4 with the dummy entry, flush
-			flush(true);
-			ends |= (uint32_t)done4 << (8 * grp);
-			++grp;
+			if (p + 1 == NLGeom<R>::ROWS_A && mine) nA4 = done4 + (int)(qa - qa0) / (BT * 2 * 4);      // everything listed so far lies in batch A
 		}
 	}
-	if (active) a.lcount[(size_t)blockIdx.x * NL_BT + tid] = ends;
+	flush(true);
+	if (active) a.lcount[(size_t)blockIdx.x * BT + tid] = (uint32_t)done4 | ((uint32_t)nA4 << 16);
 	if (ovf && active) atomicOr(a.flags + 1, (unsigned long long)NL_OVF_LIST);
+	if (near && active) a.flags[6] = 1ull;
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -235,22 +331,86 @@ __global__ void __launch_bounds__(NL_BT) nl_build_kernel(NLArgs a) {
 //        integrate_kernel.  Saves one pass over r, v, F per step.  partials then hold 8 values per block.
 //        FUSE == 2: only the half-kick of THIS step (upd_postF) - the last step of a run and the host-driven ls1g_step, where the
 //        next pre-kick is a separate call; F (and Vi) are stored as well, positions stay where they are.
-template <bool COUNT, bool VI, int FUSE>
-__global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
-	extern __shared__ __align__(16) double nl_tile[];
-	double* tile = nl_tile;                         // [tcap][3]: x y z of candidate k at tile[3k..3k+2]
-	__shared__ uint32_t s_beg[9]; __shared__ int s_off[10], s_len[9];
+// ZCHK:  keep the reference's "skip a coincident molecule of the same cell" test (see the comment at the cutoff predicate).
+
+// ---- asynchronous staging primitives (sm_80+: cp.async = LDGSTS; mbarrier completion instead of wait_group + __syncthreads) ----
+__device__ __forceinline__ uint32_t nl_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void nl_mbar_init(uint64_t* bar, unsigned count) {
+	asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" :: "r"(nl_smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void nl_cp_async_16(uint32_t dst, const void* src) {
+	asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void nl_cp_async_8(uint32_t dst, const void* src) {
+	asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" :: "r"(dst), "l"(src) : "memory");
+}
+// one arrival on `bar` once all cp.async operations this thread has issued so far have landed in shared memory
+__device__ __forceinline__ void nl_cp_async_arrive(uint64_t* bar) {
+	asm volatile("cp.async.mbarrier.arrive.noinc.shared::cta.b64 [%0];" :: "r"(nl_smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void nl_mbar_wait(uint64_t* bar, unsigned parity) {
+	uint32_t done;
+	do {
+		asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+		             : "=r"(done) : "r"(nl_smem_u32(bar)), "r"(parity) : "memory");
+	} while (!done);
+}
+
+// Stages the tile rows of a block: Z[k] (8 B) and XY[k] (16 B) per entry, straight from the double4 positions (x y | z w).
+// Batch A = rows [0, ROWS_A) -> mbar[0], batch B = the rest -> mbar[1].  Every thread arrives on both barriers.
+template <int R>
+__device__ __forceinline__ void nl_stage_tile(const NLArgs& a, const NLPlan& P, double* Z, double2* XY, uint64_t* mbar) {
+	const uint32_t z0 = nl_smem_u32(Z), xy0 = nl_smem_u32(XY);
+	const int tid = threadIdx.x;
+#pragma unroll 1
+	for (int r = 0; r < NLGeom<R>::NR; ++r) {
+		const int off = P.off[r] + NL_DUMMY, len = P.len[r];
+		const double4* src = a.pos + P.beg[r];
+		for (int t = tid; t < len; t += NLGeom<R>::BT) {
+			nl_cp_async_16(xy0 + 16u * (uint32_t)(off + t), src + t);
+			nl_cp_async_8(z0 + 8u * (uint32_t)(off + t), (const char*)(src + t) + 16);
+		}
+		if (r + 1 == NLGeom<R>::ROWS_A) nl_cp_async_arrive(mbar);
+	}
+	nl_cp_async_arrive(mbar + 1);
+}
+
+// 1/a for a positive, normal double: hardware seed (MUFU.RCP64H writes the HIGH word of the estimate, relative error <= 2^-20) + ONE
+// third-order step x1 = x0 (1 + e + e^2), e = 1 - a x0.  The low word of the seed is taken from a itself instead of being
+// zeroed (one instruction less per pair): that moves the seed by < 2^-20 relative, so |e| < 2^-19 and the result is good to
+// e^3 < 2^-57 - below the rounding of the three FMAs that follow.
+__device__ __forceinline__ double nl_rcp3(double a) {
+	double x;
+	asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(x) : "d"(a));
+	x = __hiloint2double(__double2hiint(x), __double2loint(a));
+	const double e = fma(-a, x, 1.0);
+	const double t = fma(e, e, e);
+	return fma(x, t, x);
+}
+
+template <bool COUNT, bool VI, int FUSE, bool ZCHK, int R>
+__global__ void __launch_bounds__(NLGeom<R>::BT, R == 1 ? 6 : 2) nl_force_kernel(NLArgs a) {
+	constexpr int BT = NLGeom<R>::BT;
+	extern __shared__ __align__(16) unsigned char nl_tile[];
+	double* Z = (double*)nl_tile;                               // [tcap]   z of tile entry k
+	double2* XY = (double2*)(nl_tile + (size_t)a.tcap * 8);     // [tcap]   (x, y) of tile entry k; tcap is even
+	__shared__ NLPlan P;
 	__shared__ double red[(FUSE ? 8 : 5) * 32];
+	__shared__ __align__(8) uint64_t mbar[2];
 	const int tid = threadIdx.x;
 	const unsigned blk = a.phase == 2 ? a.bmap[blockIdx.x] : blockIdx.x;
 	if (a.phase == 1 && a.bflag[blk]) return;         // boundary block: runs in phase 2, after the halo positions arrived
 	// speculatively enqueued step whose lists turned out expired: nothing is computed, the host rebuilds and repeats it
 	if (FUSE != 1 && a.guard && *a.guard > a.guard_thr) return;
-	int x_first = 0, x_last = 0;
-	const NLBlock b = nl_plan(a, s_beg, s_off, s_len, x_first, x_last, blk);
+	if (tid == 0) { nl_mbar_init(mbar, BT); nl_mbar_init(mbar + 1, BT); }
+	// dummy entries: far outside any cutoff, yet r^2 = 3e300 stays FINITE (the trace accumulation multiplies r^2 by an exact 0)
+	if (tid < NL_DUMMY) { Z[tid] = 1e150; XY[tid] = make_double2(1e150, 1e150); }
+	nl_plan<R>(a, P, blk);                             // __syncthreads inside: barriers and dummies are visible afterwards
+	int qr; uint32_t i; bool has;
+	nl_my_slot<R>(P, tid, qr, i, has);
+	const bool active = P.live && has;
 	if (FUSE == 1 && a.guard && *a.guard > a.guard_thr) {      // the host swaps the two position buffers after every fused launch: carry the positions over
-		const uint32_t i = b.s0 + tid;
-		if (i < b.s1) a.pos_out[i] = a.pos[i];
+		if (has) a.pos_out[i] = a.pos[i];
 		return;
 	}
 	constexpr int NV = FUSE ? 8 : 5;
@@ -258,80 +418,81 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 #pragma unroll
 	for (int k = 0; k < NV; ++k) acc[k] = 0.;
 	double disp2 = 0.;
-	if (b.live) {
-		const uint32_t i = b.s0 + tid;
-		const bool active = i < b.s1;
+	if (P.live) {
+		nl_stage_tile<R>(a, P, Z, XY, mbar);
 		double4 Pi = make_double4(0., 0., 0., 0.);
-		uint32_t ends = 0;
-		if (active) { Pi = a.pos[i]; ends = a.lcount[(size_t)blk * NL_BT + tid]; }
-		const uint2* my = (const uint2*)(a.lists + ((size_t)blk * a.lcap4 * NL_BT + tid) * 4);   // 4 entries per load
+		uint32_t cnt = 0;
+		if (active) { Pi = a.pos[i]; cnt = a.lcount[(size_t)blk * BT + tid]; }
+		const uint2* my = (const uint2*)(a.lists + ((size_t)blk * a.lcap4 * BT + tid) * 4);   // 4 entries per load
 		double Fx = 0., Fy = 0., Fz = 0., Vx = 0., Vy = 0., Vz = 0., u6 = 0.;
 		int np_i = 0;
-		// 4 pairs at a time, branch-free (invalid pairs contribute exact zeros) so that the dependency chains overlap.
+		// 4 pairs at a time so that the dependency chains overlap.
 		// eps24 and shift6 are constants of the single component: F, V accumulate d * inv*(2 lj12 - lj6) and are scaled by
 		// eps24 once; upot6 = eps24 * sum(lj12 - lj6) + shift6 * pairs.
 		double s6 = 0.;
-		// 0 < r2 < rc^2  <=>  (r2b - 1) <u (rc2b - 1) on the bit patterns (r2b == 0 wraps to the largest unsigned): one predicate
-		const unsigned long long rc2m1 = (unsigned long long)__double_as_longlong(a.rclj2) - 1ull;
+		const unsigned long long rc2b = (unsigned long long)__double_as_longlong(a.rclj2), rc2m1 = rc2b - 1ull;
+		const char* const Zb = (const char*)Z; const char* const XYb = (const char*)XY;
 		auto quad = [&](const uint2& w) {
 			const uint32_t ww[2] = {w.x, w.y};
 			double dx[4], dy[4], dz[4], r2[4];
 			bool ok[4];
 #pragma unroll
 			for (int u = 0; u < 4; ++u) {
-				const int k = (int)((u & 1) ? (ww[u >> 1] >> 16) : (ww[u >> 1] & 0xffffu));
-				const double* pk = tile + 3 * k;
-				dx[u] = Pi.x - pk[0]; dy[u] = Pi.y - pk[1]; dz[u] = Pi.z - pk[2];
+				// 8 * tile entry; PRMT for the low half keeps the mask ahead of the doubling (one instruction each)
+				const uint32_t e = (u & 1) ? (ww[u >> 1] >> 16) : __byte_perm(ww[u >> 1], 0u, 0x4410u);
+				const double zk = *(const double*)(Zb + e);
+				const double2 xyk = *(const double2*)(XYb + (e + e));
+				dx[u] = Pi.x - xyk.x; dy[u] = Pi.y - xyk.y; dz[u] = Pi.z - zk;
 				r2[u] = dx[u] * dx[u] + dy[u] * dy[u] + dz[u] * dz[u];
-				// r2 == 0: the molecule itself, or a coincident molecule of the same cell (SingleCellPolicy_ mask, Helpers.h:367-376).
-				// r2 and rc^2 are non-negative doubles: their order is the order of their bit patterns, so both tests run on
-				// the integer pipe and leave the FP64 pipe to the force arithmetic
-				ok[u] = (unsigned long long)__double_as_longlong(r2[u]) - 1ull < rc2m1;
+				// r2 and rc^2 are non-negative doubles: their order is the order of their bit patterns, so the test runs on
+				// the integer pipe and leaves the FP64 pipe to the force arithmetic.
+				// ZCHK: r2 == 0 is a coincident molecule of the same cell, which the reference skips (SingleCellPolicy_ mask,
+				// Helpers.h:367-376): (r2b - 1) <u (rc2b - 1) folds that into the same predicate (r2b == 0 wraps to the largest
+				// unsigned).  The build kernel reports whether any listed pair is that close; without one the plain compare is exact.
+				const unsigned long long r2b = (unsigned long long)__double_as_longlong(r2[u]);
+				ok[u] = ZCHK ? (r2b - 1ull < rc2m1) : (r2b < rc2b);
 			}
 #pragma unroll
 			for (int u = 0; u < 4; ++u) {
-				double inv = fast_rcp3(r2[u]);
-				inv = ok[u] ? inv : 0.0;                  // rejected pair (possibly inf/nan): selected away, everything below is an exact 0
+				const double inv = nl_rcp3(r2[u]);
 				const double lj2 = a.sig2 * inv, lj4 = lj2 * lj2, lj6 = lj4 * lj2, lj12 = lj6 * lj6, lj12m6 = lj12 - lj6;
 				const double sc = inv * (lj12 + lj12m6);
-				s6 += lj12m6;
-				if (VI) {
-					const double px = dx[u] * sc, py = dy[u] * sc, pz = dz[u] * sc;
-					Fx += px; Fy += py; Fz += pz;
-					Vx += dx[u] * px; Vy += dy[u] * py; Vz += dz[u] * pz;
-				} else {
-					Fx = fma(dx[u], sc, Fx); Fy = fma(dy[u], sc, Fy); Fz = fma(dz[u], sc, Fz);
-					Vx = fma(r2[u], sc, Vx);                  // Vx carries the whole trace
+				// a rejected pair (its values may be inf/nan) is not accumulated: predicated FMAs, no selects
+				if (ok[u]) {
+					s6 += lj12m6;
+					if (VI) {
+						const double px = dx[u] * sc, py = dy[u] * sc, pz = dz[u] * sc;
+						Fx += px; Fy += py; Fz += pz;
+						Vx += dx[u] * px; Vy += dy[u] * py; Vz += dz[u] * pz;
+					} else {
+						Fx = fma(dx[u], sc, Fx); Fy = fma(dy[u], sc, Fy); Fz = fma(dz[u], sc, Fz);
+						Vx = fma(r2[u], sc, Vx);                  // Vx carries the whole trace
+					}
+					if (COUNT) ++np_i;
 				}
-				if (COUNT) np_i += ok[u] ? 1 : 0;
 			}
 		};
-		int o = 0;                                       // next group of 4 entries of this molecule
-		// list entries stream from HBM: keep three loads in flight per lane, across the row-group boundaries
-		const int oall = (int)((ends >> 16) & 0xffu);
+		// list entries stream from HBM: three loads in flight per lane, rotated by name (loop unrolled by 3, no register moves)
+		const int n4 = (int)(cnt & 0xffffu);
 		uint2 p0 = make_uint2(0, 0), p1 = p0, p2 = p0;
-		if (0 < oall) p0 = my[0];
-		if (1 < oall) p1 = my[NL_BT];
-		if (2 < oall) p2 = my[2 * NL_BT];
-		for (int gz = 0; gz < 3; ++gz) {
-			if (gz) __syncthreads();                     // everyone is done with the previous row group
-			const int gbase = s_off[NL_GRP[gz]];
-			// dummy entries: far outside any cutoff, yet r^2 = 3e300 stays FINITE (the trace accumulation multiplies r^2 by an exact 0)
-			if (tid < NL_DUMMY) { double* q = tile + 3 * tid; q[0] = 1e150; q[1] = 1e150; q[2] = 1e150; }
-			for (int r = NL_GRP[gz]; r < NL_GRP[gz + 1]; ++r) {
-				const int off = s_off[r] - gbase + NL_DUMMY, len = s_len[r];
-				const uint32_t beg = s_beg[r];
-				for (int t = tid; t < len; t += NL_BT) { const double4 P = a.pos[beg + t]; double* q = tile + 3 * (off + t); q[0] = P.x; q[1] = P.y; q[2] = P.z; }
-			}
-			__syncthreads();
-			const int oend = (int)((ends >> (8 * gz)) & 0xffu);
-			for (; o < oend; ++o) {
-				const uint2 cur = p0;
-				p0 = p1; p1 = p2;
-				if (o + 3 < oall) p2 = my[(o + 3) * NL_BT];
-				quad(cur);
-			}
-		}
+		if (0 < n4) p0 = my[0];
+		if (1 < n4) p1 = my[BT];
+		if (2 < n4) p2 = my[2 * BT];
+		auto step = [&](uint2& slot, int o) {
+			const uint2 cur = slot;
+			if (o + 3 < n4) slot = my[(size_t)(o + 3) * BT];
+			quad(cur);
+		};
+		// quads every lane of the warp has entirely inside batch A (a multiple of 3 keeps the rotation aligned): these run
+		// while batch B is still in flight
+		const int nA = (int)__reduce_min_sync(0xffffffffu, active ? (cnt >> 16) : 0xffffu);
+		const int oA = nA == 0xffff ? 0 : (nA / 3) * 3;
+		nl_mbar_wait(mbar, 0);
+		int o = 0;
+		for (; o < oA; o += 3) { step(p0, o); step(p1, o + 1); step(p2, o + 2); }
+		nl_mbar_wait(mbar + 1, 0);
+		for (; o + 3 <= n4; o += 3) { step(p0, o); step(p1, o + 1); step(p2, o + 2); }
+		if (o < n4) { step(p0, o); if (o + 1 < n4) step(p1, o + 1); }
 		if (active) {
 			Fx *= a.eps24; Fy *= a.eps24; Fz *= a.eps24; Vx *= a.eps24; Vy *= a.eps24; Vz *= a.eps24;
 			u6 = a.eps24 * s6;       // + shift6 * pairs: added by the caller's finalize when the potential is shifted (COUNT)
@@ -351,7 +512,7 @@ __global__ void __launch_bounds__(NL_BT) nl_force_kernel(NLArgs a) {
 			} else if (FUSE == 1) {
 				const double m = a.mass;
 				double* vp = a.vel + 3 * (size_t)i;
-				double vx = vp[0], vy = vp[1], vz = vp[2];       // (requesting these before the pair loops costs 16 registers = 2 resident blocks: slower)
+				double vx = vp[0], vy = vp[1], vz = vp[2];
 				{	// upd_postF
 					const double dtInv2m = a.dt_half / m;
 					vx += dtInv2m * Fx; vy += dtInv2m * Fy; vz += dtInv2m * Fz;

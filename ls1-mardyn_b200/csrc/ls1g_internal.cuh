@@ -99,6 +99,7 @@ struct ls1g_ctx {
 	size_t n_owned, n_halo;
 	size_t n_uploaded;                      // n of the last ls1g_upload (ls1g_upload_forces refers to it)
 	uint32_t max_row;                       // owned molecules of the fullest cell row after the last sort
+	uint32_t max_bundle;                    // ... of the fullest 2 x 2 bundle of cell rows
 	int    sorted;                          // cell[] / cell_start valid
 	int    forces_valid;
 	MolBuf cur, alt;                        // double buffer for the sort
@@ -121,11 +122,14 @@ struct ls1g_ctx {
 	cudaStream_t stream_comm;               // high-priority stream of the overlapped halo refresh (multi-rank list steps)
 	cudaEvent_t ev_pos, ev_halo;
 	int      track_disp;                    // integrate kernels track max |r - pos_build|^2 into d_flags[0]
+	int      list_R;                        // cell rows per block of the list kernels: 4 (2 x 2 bundle) or 1 (lists.cuh)
+	int      list_zchk;                     // the last build saw a (nearly) coincident pair: force kernels keep the r2 == 0 test
 	int      list_tcap;                     // tile capacity used by the list force kernel (max tile of the last build, padded)
 	int      list_bpr;                      // blocks per cell row
 	int      build_tcap;                    // 9-row tile capacity of the build kernel, raised once on overflow
 	int      list_lcap;                     // list entries per molecule (multiple of 4), grown on overflow
-	unsigned long long* d_flags;            // [4]: max displacement^2 bits | overflow bits | max slab tile | snapshot of [0] (kernel guard)
+	unsigned long long* d_flags;            // [16]: 0 max displacement^2 bits | 1 overflow bits | 2 max tile | 3 snapshot of [0] (kernel guard) |
+	                                        //       5 boundary blocks | 6 near-pair flag of the last build
 	int      vi_every_step;                 // LS1G_VI_EVERY_STEP=1: per-molecule virial on every list step, not only the last of a run
 	int      guard_on;                      // force / integrate kernels return at once when d_flags[3] > disp_thr2 (lists expired)
 	double   disp_thr2;                     // (0.4995 skin)^2: the lists are exact while max |r - r_build|^2 <= this

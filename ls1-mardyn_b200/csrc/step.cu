@@ -196,7 +196,8 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 					bool grown = false;
 					if ((hb & NL_OVF_LIST_BIT) && c->list_lcap < NL_LCAP_MAX_H) { c->list_lcap = c->list_lcap * 2 > NL_LCAP_MAX_H ? NL_LCAP_MAX_H : c->list_lcap * 2; grown = true; }
 					else if (hb & NL_OVF_LIST_BIT) grown = false;
-					if ((hb & NL_OVF_TILE_BIT) && c->build_tcap < NL_TCAP_MAX_H) { c->build_tcap = c->build_tcap + 1024 > NL_TCAP_MAX_H ? NL_TCAP_MAX_H : c->build_tcap + 1024; grown = true; }
+					if ((hb & NL_OVF_TILE_BIT) && c->list_R == 4) { c->list_R = 1; c->build_tcap = 0; grown = true; }      // inhomogeneous rows: single-row blocks
+					else if ((hb & NL_OVF_TILE_BIT) && c->build_tcap < NL_TCAP_MAX_H) { c->build_tcap = c->build_tcap + 1024 > NL_TCAP_MAX_H ? NL_TCAP_MAX_H : c->build_tcap + 1024; grown = true; }
 					const bool fixable = !(hb & ~(NL_OVF_LIST_BIT | NL_OVF_TILE_BIT)) && (!(hb & NL_OVF_LIST_BIT) || c->list_lcap <= NL_LCAP_MAX_H) && grown;
 					if (hb && fixable && ++regrow <= 6) {
 						if (dbg) fprintf(stderr, "ls1g: list buffers raised to %d entries per molecule, build tile %d (overflow bits %llu)\n", c->list_lcap, c->build_tcap, hb);
@@ -212,6 +213,7 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 				}
 				c->track_disp = 1;
 				c->n_boundary_blocks = (uint32_t)c->h_flags[3];
+				c->list_zchk = c->h_flags[8] != 0;
 				c->list_tcap = (int)((c->h_flags[2] + 63) & ~63ull);
 				if (c->list_tcap < 64) c->list_tcap = 64;
 				if (dbg) fprintf(stderr, "ls1g: list build at step %d: max tile %llu, bpr %d, slots %zu, bin grid %d %d %d\n", s, c->h_flags[2], c->list_bpr, c->n_slots, c->bgrid.cpd[0], c->bgrid.cpd[1], c->bgrid.cpd[2]);

@@ -272,6 +272,37 @@ def test_leaving_molecules_wrap():
     assert np.array_equal(mine[np.lexsort(mine.T[::-1])], ref[np.lexsort(ref.T[::-1])])
 
 
+def test_update_then_exchange_keeps_the_leavers():
+    """The reference's order in Simulation::updateParticleContainerAndDecomposition (Simulation.cpp:1193-1215): LinkedCells::update
+    first (leavers move into halo cells and stay molecules), then balanceAndExchange wraps them.  ls1g_update must not turn an
+    owned leaver into a halo copy that the next exchange drops."""
+    r, v, box = fcc_lattice(6, seed=5)
+    n = len(r)
+    g = O.grid([0, 0, 0], box, 2.5, 0)
+    v = v * 40.0                                           # one pre-kick/drift carries molecules near the faces out of the box
+    with ls1g.Container(box, 2.5) as c:
+        c.set_components([ls1g.lj_component()])
+        c.add_particles(np.arange(n), np.zeros(n, dtype=np.uint32), r, v)
+        c.exchange()
+        c.traverse_cells()
+        c.delete_outer_particles()
+        c.event_new_timestep(0.02)
+        moved = by_id(c.download(("id", "r")))
+        assert np.any(moved["r"] < 0) or np.any(moved["r"] >= box)
+        c.update()
+        assert c.count()[0] == n
+        after_update = by_id(c.download(("id", "r", "cell")))
+        assert np.array_equal(after_update["id"], np.arange(n)) and np.array_equal(after_update["r"], moved["r"])
+        assert np.array_equal(after_update["cell"], O.cell_indices(g, moved["r"]))
+        c.exchange()
+        assert c.count()[0] == n
+        out = by_id(c.download(("id", "r", "cell")))
+    r_wrapped, _, _ = O.exchange(g, box, moved["r"])
+    assert np.array_equal(out["id"], np.arange(n))
+    assert np.array_equal(out["r"], r_wrapped)
+    assert np.array_equal(out["cell"], O.cell_indices(g, r_wrapped))
+
+
 # ------------------------------------------------------------------------------------------------------
 # size-independent properties at a larger size
 # ------------------------------------------------------------------------------------------------------
