@@ -208,6 +208,14 @@ int ls1g_allreduce_sum(ls1g_ctx* ctx, double* values, int n);
 int ls1g_comm_init_local(ls1g_ctx** ctxs, int n);
 /* one leaving+halo exchange of all local ranks in lockstep (= ls1g_exchange on every rank) */
 int ls1g_exchange_group(ls1g_ctx** ctxs, int n);
+/* ls1g_run / ls1g_step for all ranks of a local group in lockstep (one host thread enqueues for every context; the contexts may live
+ * on different GPUs of the box).  The same loop as a NCCL rank runs - neighbour lists with persistent halo lists, halo refresh
+ * overlapped with the inner blocks of the force pass, guarded speculative steps - with device-to-device copies ordered by events in
+ * place of ncclSend/ncclRecv.  records / record hold the SUMS over the ranks, i.e. what one MPI rank owning the whole box would hand
+ * to Domain::setLocalUpot etc.
+ * replaces: Simulation::simulate on every rank of DomainDecomposition (Simulation.cpp:979-1177, DomainDecomposition.cpp:87-125) */
+int ls1g_run_group(ls1g_ctx** ctxs, int n, int n_steps, double dt, double target_temperature, ls1g_step_record* records);
+int ls1g_step_group(ls1g_ctx** ctxs, int n, double dt, double beta_trans, double beta_rot, int flags, ls1g_step_record* record);
 
 /* --- measurement -------------------------------------------------------------------------- */
 /* LS1G_T_FORCE brackets ONLY the pair kernel (the roofline kernel); its reductions and the site cache are LS1G_T_AUX */
@@ -246,6 +254,9 @@ typedef struct {
 	double   interval_length;    /* RDF::_intervalLength; pairs beyond interval_length * bins are not counted */
 } ls1g_rdf_params;
 int ls1g_rdf(ls1g_ctx* ctx, const ls1g_rdf_params* params, uint64_t* mol, uint64_t* site, uint64_t* ardf);
+/* neighbour-list bookkeeping of the device-resident loop (measurement): list builds so far, cell rows per block of the list kernels
+ * (4 = 2 x 2 bundles, 1 = single rows), list capacity per molecule, skin.  Any pointer may be NULL. */
+int ls1g_list_stats(ls1g_ctx* ctx, uint64_t* rebuilds, int* rows_per_block, int* entries_per_molecule, double* skin);
 /* pair statistics of the last traverse: molecule pairs inside the cutoff (counted once) */
 int ls1g_last_pair_count(ls1g_ctx* ctx, uint64_t* pairs_in_cutoff);
 

@@ -5,10 +5,10 @@ Host-side mirror of the reference's operator surface for this path, as a thin ct
 (symbol checks, host-side geometry), every compute call fails loudly without one.  There is no CPU fallback.
 """
 from .binding import (Container, Ls1gError, build, lib, lib_path, decomp_grid, decomp_box, fp64_peak_tflops,
-                      exchange_group, comm_init_local, comm_unique_id, components_from_tables,
+                      exchange_group, run_group, step_group, comm_init_local, comm_unique_id, components_from_tables,
                       lj_component, FIELDS, EXPORTS)
 from . import phasespace
 
 __all__ = ["Container", "Ls1gError", "build", "lib", "lib_path", "decomp_grid", "decomp_box",
-           "fp64_peak_tflops", "exchange_group", "comm_init_local", "comm_unique_id", "components_from_tables",
+           "fp64_peak_tflops", "exchange_group", "run_group", "step_group", "comm_init_local", "comm_unique_id", "components_from_tables",
            "lj_component", "FIELDS", "EXPORTS", "phasespace"]

@@ -20,6 +20,7 @@ EXPORTS = [
     "ls1g_integrate_pre", "ls1g_integrate_post", "ls1g_scale", "ls1g_selective_thermostat", "ls1g_run", "ls1g_step", "ls1g_host_alloc", "ls1g_host_free", "ls1g_decomp_box", "ls1g_decomp_grid",
     "ls1g_comm_unique_id", "ls1g_comm_init", "ls1g_allreduce_sum", "ls1g_comm_init_local", "ls1g_exchange_group",
     "ls1g_timers", "ls1g_measure_fp64_peak", "ls1g_last_pair_count", "ls1g_flop_count", "ls1g_rdf", "ls1g_reserve", "ls1g_download_range", "ls1g_slot_count",
+    "ls1g_run_group", "ls1g_step_group", "ls1g_list_stats",
 ]
 
 FIELDS = dict(id=1, cid=2, r=4, v=8, q=16, L=32, F=64, M=128, Vi=256, cell=512)
@@ -120,6 +121,22 @@ def comm_init_local(containers):
 def exchange_group(containers):
     arr = (C.c_void_p * len(containers))(*[c._ctx for c in containers])
     _chk(lib().ls1g_exchange_group(arr, len(containers)))
+
+
+def run_group(containers, n_steps, dt, target_temperature=0.0):
+    """ls1g_run for all ranks of a local group in lockstep; returns [n_steps][6] (upot virial summv2 sumIw2 N rotDOF), summed over the ranks"""
+    arr = (C.c_void_p * len(containers))(*[c._ctx for c in containers])
+    rec = (_StepRecord * max(n_steps, 1))()
+    _chk(lib().ls1g_run_group(arr, len(containers), int(n_steps), C.c_double(dt), C.c_double(target_temperature), rec))
+    return np.array([[x.upot, x.virial, x.summv2, x.sumIw2, x.n, x.rot_dof] for x in rec[:n_steps]], dtype=np.float64).reshape(n_steps, 6)
+
+
+def step_group(containers, dt, beta_trans=1.0, beta_rot=1.0, vi=True):
+    """ls1g_step for all ranks of a local group; returns the step record summed over the ranks"""
+    arr = (C.c_void_p * len(containers))(*[c._ctx for c in containers])
+    rec = _StepRecord()
+    _chk(lib().ls1g_step_group(arr, len(containers), C.c_double(dt), C.c_double(beta_trans), C.c_double(beta_rot), int(bool(vi)), C.byref(rec)))
+    return np.array([rec.upot, rec.virial, rec.summv2, rec.sumIw2, rec.n, rec.rot_dof], dtype=np.float64)
 
 
 def comm_unique_id():
@@ -399,6 +416,12 @@ class Container:
         _chk(lib().ls1g_timers(self._ctx, ms, ln, int(reset)))
         names = ("force", "sort", "integrate", "exchange", "aux")
         return {k: dict(ms=ms[i], launches=int(ln[i])) for i, k in enumerate(names)}
+
+    def list_stats(self):
+        """neighbour-list bookkeeping: dict(rebuilds, rows_per_block, entries_per_molecule, skin)"""
+        a, b, c, d = C.c_uint64(), C.c_int(), C.c_int(), C.c_double()
+        _chk(lib().ls1g_list_stats(self._ctx, C.byref(a), C.byref(b), C.byref(c), C.byref(d)))
+        return dict(rebuilds=a.value, rows_per_block=b.value, entries_per_molecule=c.value, skin=d.value)
 
     def last_pair_count(self):
         n = C.c_uint64()

@@ -168,6 +168,8 @@ extern "C" int ls1g_create(const ls1g_config* cfg, ls1g_ctx** out) {
 	c->partials = nullptr; c->partials_cap = 0; c->d_scalars = c->h_scalars = nullptr; c->d_pairs = nullptr; c->last_pairs = 0;
 	c->nccl_comm = nullptr; c->n_ranks = 1; c->rank = 0; c->comm_mode = 0;
 	c->send_buf[0] = c->send_buf[1] = c->recv_buf[0] = c->recv_buf[1] = nullptr; c->xbuf_cap = 0;
+	c->gbuf = nullptr; c->gbuf_owner = 0; c->gseq = 0; c->d_rec = nullptr; c->d_rec_cap = 0;
+	c->ev_pack = c->ev_read = c->ev_ar = nullptr;
 	memset(c->timers, 0, sizeof(c->timers));
 	{ const char* fk = getenv("LS1G_FORCE_KERNEL"); c->force_variant = (fk && !strcmp(fk, "simple")) ? 1 : 0; }
 	if (grid_init(c->grid, c->cfg)) { delete c; return 1; }
@@ -186,6 +188,9 @@ extern "C" int ls1g_create(const ls1g_config* cfg, ls1g_ctx** out) {
 		CUDA_TRY(cudaStreamCreateWithPriority(&c->stream_comm, cudaStreamNonBlocking, hi));
 		CUDA_TRY(cudaEventCreateWithFlags(&c->ev_pos, cudaEventDisableTiming));
 		CUDA_TRY(cudaEventCreateWithFlags(&c->ev_halo, cudaEventDisableTiming));
+		CUDA_TRY(cudaEventCreateWithFlags(&c->ev_pack, cudaEventDisableTiming));
+		CUDA_TRY(cudaEventCreateWithFlags(&c->ev_read, cudaEventDisableTiming));
+		CUDA_TRY(cudaEventCreateWithFlags(&c->ev_ar, cudaEventDisableTiming));
 	}
 	size_t nc = (size_t)c->grid.n_cells + 1;
 	CUDA_TRY(cudaMalloc((void**)&c->cell_count, nc * sizeof(uint32_t)));
@@ -224,6 +229,10 @@ extern "C" int ls1g_destroy(ls1g_ctx* c) {
 	for (int k = 0; k < 2; ++k) { cudaFree(c->send_buf[k]); cudaFree(c->recv_buf[k]); }
 	if (c->ev_pos) cudaEventDestroy(c->ev_pos);
 	if (c->ev_halo) cudaEventDestroy(c->ev_halo);
+	if (c->ev_pack) cudaEventDestroy(c->ev_pack);
+	if (c->ev_read) cudaEventDestroy(c->ev_read);
+	if (c->ev_ar) cudaEventDestroy(c->ev_ar);
+	cudaFree(c->d_rec);
 	if (c->stream_comm) cudaStreamDestroy(c->stream_comm);
 	cudaFree(c->bmap); cudaFree(c->bflag);
 	if (c->stream) cudaStreamDestroy(c->stream);

@@ -26,6 +26,7 @@
 #include <string.h>
 #include <stdlib.h>
 #include <vector>
+#include <algorithm>
 
 // ---- minimal NCCL surface (signatures from nccl.h 2.2x; loaded with dlsym) ------------------------
 typedef struct ncclComm* ncclComm_t;
@@ -64,13 +65,16 @@ static int nccl_load() {
 #define NCCL_TRY(expr) do { ncclResult_t _r = (expr); if (_r != 0) LS1G_FAIL(std::string(#expr) + ": " + g_nccl.GetErrorString(_r)); } while (0)
 
 // ------------------------------------------------------------------------------------------------
-// record = 8 doubles (x y z cid | vx vy vz id), +8 with rotation (qw qx qy qz | Lx Ly Lz 0)
+// record = 8 doubles (x y z cid | vx vy vz id), +8 with rotation (qw qx qy qz | Lx Ly Lz 0); when the forces of the sender are
+// valid (an exchange outside the time loop, e.g. on leaving the neighbour-list layout: the next half-kick needs F(t) of a molecule
+// that changes its rank) +4 (Fx Fy Fz 0) and, with rotation, +4 (Mx My Mz 0)
 // ------------------------------------------------------------------------------------------------
 struct PackArgs {
 	Grid g;
 	size_t n;
 	MolBuf m;
-	int has_rot, dim;
+	int has_rot, dim, rec;    // rec = doubles per record
+	const double *F, *M;      // carried when non-null
 	double shift[2];          // periodic shift applied for direction 0 (lower) / 1 (upper); 0 = none
 	double global_len;
 	double* out[2]; uint32_t* counters; uint32_t cap;
@@ -83,8 +87,7 @@ __device__ __forceinline__ void write_record(const PackArgs& a, int dir, size_t 
 	uint32_t k = atomicAdd(&a.counters[dir], 1u);
 	if (k >= a.cap) return;                     // overflow: detected on the host from the counter
 	if (a.mode == 2) a.rec_slot[dir][k] = (uint32_t)i;
-	const int rec = a.has_rot ? 16 : 8;
-	double* o = a.out[dir] + (size_t)k * rec;
+	double* o = a.out[dir] + (size_t)k * a.rec;
 	o[0] = p.x; o[1] = p.y; o[2] = p.z; o[3] = p.w;
 	o[4] = a.m.vel[3 * i]; o[5] = a.m.vel[3 * i + 1]; o[6] = a.m.vel[3 * i + 2];
 	o[7] = __longlong_as_double((long long)a.m.id[i]);
@@ -92,6 +95,11 @@ __device__ __forceinline__ void write_record(const PackArgs& a, int dir, size_t 
 		double4 q = a.m.q[i];
 		o[8] = q.x; o[9] = q.y; o[10] = q.z; o[11] = q.w;
 		o[12] = a.m.L[3 * i]; o[13] = a.m.L[3 * i + 1]; o[14] = a.m.L[3 * i + 2]; o[15] = 0.;
+	}
+	if (a.F) {
+		double* f = o + (a.has_rot ? 16 : 8);
+		f[0] = a.F[3 * i]; f[1] = a.F[3 * i + 1]; f[2] = a.F[3 * i + 2]; f[3] = 0.;
+		if (a.M) { f[4] = a.M[3 * i]; f[5] = a.M[3 * i + 1]; f[6] = a.M[3 * i + 2]; f[7] = 0.; }
 	}
 }
 
@@ -154,10 +162,10 @@ __global__ void __launch_bounds__(256) unpack_pos_list_kernel(size_t n, const ui
 	pos[s] = p;
 }
 
-__global__ void __launch_bounds__(256) unpack_kernel(const double* __restrict__ in, size_t n, size_t base, MolBuf m, int has_rot) {
+__global__ void __launch_bounds__(256) unpack_kernel(const double* __restrict__ in, size_t n, size_t base, MolBuf m, int has_rot, int rec,
+                                                      double* __restrict__ F, double* __restrict__ M) {
 	size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (k >= n) return;
-	const int rec = has_rot ? 16 : 8;
 	const double* r = in + k * rec;
 	size_t i = base + k;
 	m.pos[i] = make_double4(r[0], r[1], r[2], r[3]);
@@ -167,6 +175,11 @@ __global__ void __launch_bounds__(256) unpack_kernel(const double* __restrict__ 
 	if (has_rot) {
 		m.q[i] = make_double4(r[8], r[9], r[10], r[11]);
 		m.L[3 * i] = r[12]; m.L[3 * i + 1] = r[13]; m.L[3 * i + 2] = r[14];
+	}
+	if (F) {
+		const double* f = r + (has_rot ? 16 : 8);
+		F[3 * i] = f[0]; F[3 * i + 1] = f[1]; F[3 * i + 2] = f[2];
+		if (M) { M[3 * i] = f[4]; M[3 * i + 1] = f[5]; M[3 * i + 2] = f[6]; }
 	}
 }
 
@@ -179,7 +192,8 @@ __global__ void __launch_bounds__(256) count_owned_kernel(size_t n, const uint32
 
 // ------------------------------------------------------------------------------------------------
 static inline unsigned nblk(size_t n, unsigned t) { return (unsigned)((n + t - 1) / t); }
-static inline int rec_doubles(const ls1g_ctx* c) { return c->has_rot ? 16 : 8; }
+// forces travel with the molecules whenever they are valid (k_sort carries them through the re-sort under the same condition)
+static inline int rec_doubles(const ls1g_ctx* c) { return (c->has_rot ? 16 : 8) + (c->forces_valid ? (c->has_rot ? 8 : 4) : 0); }
 
 static int rank_of(const int grid[3], int cx, int cy, int cz) { return (cx * grid[1] + cy) * grid[2] + cz; }   // MPI_Cart_rank, row-major
 
@@ -191,10 +205,12 @@ static int neighbour_rank(const ls1g_ctx* c, int d, int dir) {
 }
 
 static int ensure_xbuf(ls1g_ctx* c) {
-	size_t want = c->cap;
+	// records per direction and stage: everything a small system holds may have to travel; of a large one only the boundary slab
+	// does (a stage that needs more fails with "send buffer overflow")
+	size_t want = c->cap < (1u << 20) ? c->cap : std::max<size_t>(c->cap / 4, 1u << 20);
 	if (c->xbuf_cap >= want && c->send_buf[0]) return 0;
 	for (int k = 0; k < 2; ++k) { cudaFree(c->send_buf[k]); cudaFree(c->recv_buf[k]); c->send_buf[k] = c->recv_buf[k] = nullptr; }
-	size_t bytes = want * rec_doubles(c) * sizeof(double);
+	size_t bytes = want * (c->has_rot ? 24 : 12) * sizeof(double);
 	for (int k = 0; k < 2; ++k) {
 		CUDA_TRY(cudaMalloc((void**)&c->send_buf[k], bytes));
 		CUDA_TRY(cudaMalloc((void**)&c->recv_buf[k], bytes));
@@ -210,7 +226,8 @@ static int stage_pack(ls1g_ctx* c, int d, int mode = 0) {
 	if (ensure_xbuf(c)) return 1;
 	CUDA_TRY(cudaMemsetAsync(c->d_counters + 2, 0, 2 * sizeof(uint32_t), c->stream));
 	PackArgs a;
-	a.g = c->bgrid; a.n = c->n_slots; a.m = c->cur; a.has_rot = c->has_rot; a.dim = d;
+	a.g = c->bgrid; a.n = c->n_slots; a.m = c->cur; a.has_rot = c->has_rot; a.dim = d; a.rec = rec_doubles(c);
+	a.F = c->forces_valid ? c->F : nullptr; a.M = c->forces_valid && c->has_rot ? c->M : nullptr;
 	a.global_len = c->cfg.global_length[d];
 	a.shift[0] = c->cfg.rank_coords[d] == 0 ? c->cfg.global_length[d] : 0.;
 	a.shift[1] = c->cfg.rank_coords[d] == c->cfg.rank_grid[d] - 1 ? -c->cfg.global_length[d] : 0.;
@@ -228,7 +245,8 @@ static int stage_unpack(ls1g_ctx* c, const uint32_t n_recv[2]) {
 	for (int k = 0; k < 2; ++k) {
 		if (!n_recv[k]) continue;
 		if (c->n_slots + n_recv[k] > c->cap) LS1G_FAIL("ls1g exchange: capacity exceeded by received particles (raise ls1g_config.capacity)");
-		unpack_kernel<<<nblk(n_recv[k], 256), 256, 0, c->stream>>>(c->recv_buf[k], n_recv[k], c->n_slots, c->cur, c->has_rot);
+		unpack_kernel<<<nblk(n_recv[k], 256), 256, 0, c->stream>>>(c->recv_buf[k], n_recv[k], c->n_slots, c->cur, c->has_rot, rec_doubles(c),
+		                                                         c->forces_valid ? c->F : nullptr, c->forces_valid && c->has_rot ? c->M : nullptr);
 		c->n_slots += n_recv[k];
 	}
 	CUDA_TRY(cudaGetLastError());
@@ -256,52 +274,95 @@ static int check_grid_order(const ls1g_ctx* c) {
 	return 0;
 }
 
-// ---- NCCL transport --------------------------------------------------------------------------------
-// one stage (dimension d): pack, exchange counts and records with both neighbours, append the received records.
+// ---- transports ------------------------------------------------------------------------------------
+// NCCL: one process per GPU, the group is this rank alone and the neighbours are reached by ncclSend/ncclRecv.
+// local: all ranks are contexts of this process (any number of GPUs >= 1); records move by device-to-device copies, ordered by
+//        events.  Everything around the transfer itself - pack / unpack kernels, persistent lists, slot translation, the
+//        overlapped two-phase force launch, the guarded steps - is the same code for both.
+static inline void set_dev(const ls1g_ctx* c) { cudaSetDevice(c->cfg.device); }
+
+// one stage (dimension d) of a NCCL rank: pack, exchange counts and records with both neighbours, append the received records.
 // n_recv_out[2]: records received from the upper / lower neighbour; *base_out: slot of the first appended record.
 static int nccl_stage(ls1g_ctx* c, int d, int mode, uint32_t n_recv_out[2], uint32_t* base_out) {
 	ncclComm_t comm = (ncclComm_t)c->nccl_comm;
 	const int rec = rec_doubles(c);
-	{
-		if (stage_pack(c, d, mode)) return 1;
-		const int lower = neighbour_rank(c, d, 0), upper = neighbour_rank(c, d, 1);
-		// counts: d_counters[2],[3] = my sends (lower, upper); [4] = from upper, [5] = from lower
-		NCCL_TRY(g_nccl.GroupStart());
-		NCCL_TRY(g_nccl.Send(c->d_counters + 2, 1, 3 /*ncclUint32*/, lower, comm, c->stream));
-		NCCL_TRY(g_nccl.Send(c->d_counters + 3, 1, 3, upper, comm, c->stream));
-		NCCL_TRY(g_nccl.Recv(c->d_counters + 4, 1, 3, upper, comm, c->stream));
-		NCCL_TRY(g_nccl.Recv(c->d_counters + 5, 1, 3, lower, comm, c->stream));
-		NCCL_TRY(g_nccl.GroupEnd());
-		CUDA_TRY(cudaMemcpyAsync(c->h_counters + 4, c->d_counters + 4, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
-		CUDA_TRY(cudaStreamSynchronize(c->stream));
-		uint32_t n_recv[2] = {c->h_counters[4], c->h_counters[5]};
-		if (n_recv[0] > c->xbuf_cap || n_recv[1] > c->xbuf_cap) LS1G_FAIL("ls1g exchange: receive buffer overflow (raise ls1g_config.capacity)");
-		NCCL_TRY(g_nccl.GroupStart());
-		if (c->h_counters[2]) NCCL_TRY(g_nccl.Send(c->send_buf[0], (size_t)c->h_counters[2] * rec, NCCL_DOUBLE, lower, comm, c->stream));
-		if (c->h_counters[3]) NCCL_TRY(g_nccl.Send(c->send_buf[1], (size_t)c->h_counters[3] * rec, NCCL_DOUBLE, upper, comm, c->stream));
-		if (n_recv[0]) NCCL_TRY(g_nccl.Recv(c->recv_buf[0], (size_t)n_recv[0] * rec, NCCL_DOUBLE, upper, comm, c->stream));
-		if (n_recv[1]) NCCL_TRY(g_nccl.Recv(c->recv_buf[1], (size_t)n_recv[1] * rec, NCCL_DOUBLE, lower, comm, c->stream));
-		NCCL_TRY(g_nccl.GroupEnd());
-		*base_out = (uint32_t)c->n_slots;
-		if (stage_unpack(c, n_recv)) return 1;
-		n_recv_out[0] = n_recv[0]; n_recv_out[1] = n_recv[1];
+	if (stage_pack(c, d, mode)) return 1;
+	const int lower = neighbour_rank(c, d, 0), upper = neighbour_rank(c, d, 1);
+	// counts: d_counters[2],[3] = my sends (lower, upper); [4] = from upper, [5] = from lower
+	NCCL_TRY(g_nccl.GroupStart());
+	NCCL_TRY(g_nccl.Send(c->d_counters + 2, 1, 3 /*ncclUint32*/, lower, comm, c->stream));
+	NCCL_TRY(g_nccl.Send(c->d_counters + 3, 1, 3, upper, comm, c->stream));
+	NCCL_TRY(g_nccl.Recv(c->d_counters + 4, 1, 3, upper, comm, c->stream));
+	NCCL_TRY(g_nccl.Recv(c->d_counters + 5, 1, 3, lower, comm, c->stream));
+	NCCL_TRY(g_nccl.GroupEnd());
+	CUDA_TRY(cudaMemcpyAsync(c->h_counters + 4, c->d_counters + 4, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+	CUDA_TRY(cudaStreamSynchronize(c->stream));
+	uint32_t n_recv[2] = {c->h_counters[4], c->h_counters[5]};
+	if (n_recv[0] > c->xbuf_cap || n_recv[1] > c->xbuf_cap) LS1G_FAIL("ls1g exchange: receive buffer overflow (raise ls1g_config.capacity)");
+	NCCL_TRY(g_nccl.GroupStart());
+	if (c->h_counters[2]) NCCL_TRY(g_nccl.Send(c->send_buf[0], (size_t)c->h_counters[2] * rec, NCCL_DOUBLE, lower, comm, c->stream));
+	if (c->h_counters[3]) NCCL_TRY(g_nccl.Send(c->send_buf[1], (size_t)c->h_counters[3] * rec, NCCL_DOUBLE, upper, comm, c->stream));
+	if (n_recv[0]) NCCL_TRY(g_nccl.Recv(c->recv_buf[0], (size_t)n_recv[0] * rec, NCCL_DOUBLE, upper, comm, c->stream));
+	if (n_recv[1]) NCCL_TRY(g_nccl.Recv(c->recv_buf[1], (size_t)n_recv[1] * rec, NCCL_DOUBLE, lower, comm, c->stream));
+	NCCL_TRY(g_nccl.GroupEnd());
+	*base_out = (uint32_t)c->n_slots;
+	if (stage_unpack(c, n_recv)) return 1;
+	n_recv_out[0] = n_recv[0]; n_recv_out[1] = n_recv[1];
+	return 0;
+}
+
+static int check_group(const Group& G) {
+	ls1g_ctx* c0 = G.c[0];
+	if (c0->n_ranks <= 1) return 0;
+	if (c0->comm_mode == 1) { if (G.n != 1) LS1G_FAIL("ls1g: a NCCL rank is driven alone (one process per GPU)"); return 0; }
+	if (c0->comm_mode != 2) LS1G_FAIL("ls1g: multi-rank context without a transport (ls1g_comm_init / ls1g_comm_init_local)");
+	if (G.n != c0->n_ranks || (int)c0->peers.size() != G.n) LS1G_FAIL("ls1g: a local group is driven as a whole (all ranks, in rank order)");
+	for (int r = 0; r < G.n; ++r) if (G.c[r] != c0->peers[r]) LS1G_FAIL("ls1g: contexts do not match the group of ls1g_comm_init_local");
+	return 0;
+}
+
+// one stage of every rank of the group (blocking).  nr[r][2], base[r] as nccl_stage.
+struct NR2 { uint32_t v[2]; uint32_t& operator[](int k) { return v[k]; } };
+static int group_stage(const Group& G, int d, int mode, NR2* nr, uint32_t* base) {
+	if (G.c[0]->comm_mode == 1) return nccl_stage(G.c[0], d, mode, nr[0].v, &base[0]);
+	for (int r = 0; r < G.n; ++r) { set_dev(G.c[r]); if (stage_pack(G.c[r], d, mode)) return 1; }      // synchronises: counts in h_counters[2], [3]
+	for (int r = 0; r < G.n; ++r) {
+		ls1g_ctx* c = G.c[r];
+		set_dev(c);
+		const int rec = rec_doubles(c);
+		ls1g_ctx* up = G.c[neighbour_rank(c, d, 1)];
+		ls1g_ctx* lo = G.c[neighbour_rank(c, d, 0)];
+		// from my upper neighbour I get what it sent downwards (its buffer 0); from my lower neighbour its buffer 1
+		nr[r][0] = up->h_counters[2]; nr[r][1] = lo->h_counters[3];
+		if (nr[r][0] > c->xbuf_cap || nr[r][1] > c->xbuf_cap) LS1G_FAIL("ls1g exchange: receive buffer overflow (raise ls1g_config.capacity)");
+		if (nr[r][0]) CUDA_TRY(cudaMemcpyAsync(c->recv_buf[0], up->send_buf[0], (size_t)nr[r][0] * rec * sizeof(double), cudaMemcpyDefault, c->stream));
+		if (nr[r][1]) CUDA_TRY(cudaMemcpyAsync(c->recv_buf[1], lo->send_buf[1], (size_t)nr[r][1] * rec * sizeof(double), cudaMemcpyDefault, c->stream));
+	}
+	for (int r = 0; r < G.n; ++r) {
+		ls1g_ctx* c = G.c[r];
+		set_dev(c);
+		base[r] = (uint32_t)c->n_slots;
+		if (stage_unpack(c, nr[r].v)) return 1;
+		CUDA_TRY(cudaStreamSynchronize(c->stream));   // send buffers are reused by the next stage
 	}
 	return 0;
 }
 
-int comm_exchange(ls1g_ctx* c) {
-	if (c->comm_mode != 1) LS1G_FAIL("ls1g_exchange: multi-rank context without NCCL communicator (local groups use ls1g_exchange_group)");
-	if (check_grid_order(c)) return 1;
-	timer_start(c, LS1G_T_EXCHANGE);
+int comm_exchange(const Group& G) {
+	if (check_group(G)) return 1;
+	if (check_grid_order(G.c[0])) return 1;
+	std::vector<uint32_t> base(G.n);
+	std::vector<NR2> nr(G.n);
+	for (int r = 0; r < G.n; ++r) { set_dev(G.c[r]); timer_start(G.c[r], LS1G_T_EXCHANGE); }
 	int launches = 0;
 	for (int d = 0; d < 3; ++d) {
-		if (c->cfg.rank_grid[d] <= 1) continue;
-		uint32_t nr[2], base;
-		if (nccl_stage(c, d, 0, nr, &base)) return 1;
+		if (G.c[0]->cfg.rank_grid[d] <= 1) continue;
+		if (group_stage(G, d, 0, nr.data(), base.data())) return 1;
 		launches += 4;
 	}
-	timer_stop(c, LS1G_T_EXCHANGE, launches);
-	return finish_exchange(c);
+	for (int r = 0; r < G.n; ++r) { set_dev(G.c[r]); timer_stop(G.c[r], LS1G_T_EXCHANGE, launches); }
+	for (int r = 0; r < G.n; ++r) { set_dev(G.c[r]); if (finish_exchange(G.c[r])) return 1; }
+	return 0;
 }
 
 static int ensure_u32(uint32_t** p, size_t* cap, size_t want) {
@@ -316,92 +377,150 @@ static int ensure_u32(uint32_t** p, size_t* cap, size_t want) {
 // leaver's old copy as the sender's halo particle (CommunicationPartner.h:55); with a frozen layout that copy would never be
 // refreshed, so here ownership moves first (pass 1), then the halo copies are created (pass 2) and every stage remembers
 // which slots it sent and where the received copies live: comm_refresh re-sends just their positions on later steps.
-int comm_exchange_build(ls1g_ctx* c) {
-	if (c->comm_mode != 1) LS1G_FAIL("ls1g_run: multi-rank neighbour lists need the NCCL transport");
-	if (check_grid_order(c)) return 1;
-	timer_start(c, LS1G_T_EXCHANGE);
+int comm_exchange_build(const Group& G) {
+	if (check_group(G)) return 1;
+	if (check_grid_order(G.c[0])) return 1;
+	std::vector<uint32_t> base(G.n);
+	std::vector<NR2> nr(G.n);
+	for (int r = 0; r < G.n; ++r) { set_dev(G.c[r]); timer_start(G.c[r], LS1G_T_EXCHANGE); }
 	int launches = 0;
-	uint32_t nr[2], base;
 	for (int d = 0; d < 3; ++d) {
-		if (c->cfg.rank_grid[d] <= 1) continue;
-		if (nccl_stage(c, d, 1, nr, &base)) return 1;
+		if (G.c[0]->cfg.rank_grid[d] <= 1) continue;
+		if (group_stage(G, d, 1, nr.data(), base.data())) return 1;
 		launches += 4;
 	}
 	// pre-sort bookkeeping of pass 2, translated after the sort
-	std::vector<uint32_t*> pre_copy;
 	for (int d = 0; d < 3; ++d) {
-		for (int k = 0; k < 2; ++k) { c->xl_n_send[d][k] = c->xl_n_recv[d][k] = 0; c->xl_recv_base[d][k] = 0; }
-		if (c->cfg.rank_grid[d] <= 1) continue;
-		if (nccl_stage(c, d, 2, nr, &base)) return 1;
+		for (int r = 0; r < G.n; ++r)
+			for (int k = 0; k < 2; ++k) { G.c[r]->xl_n_send[d][k] = G.c[r]->xl_n_recv[d][k] = 0; G.c[r]->xl_recv_base[d][k] = 0; }
+		if (G.c[0]->cfg.rank_grid[d] <= 1) continue;
+		if (group_stage(G, d, 2, nr.data(), base.data())) return 1;
 		launches += 4;
-		for (int k = 0; k < 2; ++k) {
-			c->xl_n_send[d][k] = c->h_counters[2 + k];
-			if (ensure_u32(&c->xl_send[d][k], &c->xl_send_cap[d][k], c->xl_n_send[d][k])) return 1;
-			// keep the pre-sort slots in xl_send until they are translated
-			if (c->xl_n_send[d][k]) CUDA_TRY(cudaMemcpyAsync(c->xl_send[d][k], c->xl_pre[k], c->xl_n_send[d][k] * sizeof(uint32_t), cudaMemcpyDeviceToDevice, c->stream));
+		for (int r = 0; r < G.n; ++r) {
+			ls1g_ctx* c = G.c[r];
+			set_dev(c);
+			for (int k = 0; k < 2; ++k) {
+				c->xl_n_send[d][k] = c->h_counters[2 + k];
+				if (ensure_u32(&c->xl_send[d][k], &c->xl_send_cap[d][k], c->xl_n_send[d][k])) return 1;
+				// keep the pre-sort slots in xl_send until they are translated
+				if (c->xl_n_send[d][k]) CUDA_TRY(cudaMemcpyAsync(c->xl_send[d][k], c->xl_pre[k], c->xl_n_send[d][k] * sizeof(uint32_t), cudaMemcpyDeviceToDevice, c->stream));
+			}
+			c->xl_n_recv[d][0] = nr[r][0]; c->xl_n_recv[d][1] = nr[r][1];
+			c->xl_recv_base[d][0] = base[r]; c->xl_recv_base[d][1] = base[r] + nr[r][0];
+			for (int k = 0; k < 2; ++k) if (ensure_u32(&c->xl_recv[d][k], &c->xl_recv_cap[d][k], c->xl_n_recv[d][k])) return 1;
+			CUDA_TRY(cudaStreamSynchronize(c->stream));      // xl_pre is rewritten by the next stage's pack
 		}
-		c->xl_n_recv[d][0] = nr[0]; c->xl_n_recv[d][1] = nr[1];
-		c->xl_recv_base[d][0] = base; c->xl_recv_base[d][1] = base + nr[0];
-		for (int k = 0; k < 2; ++k) if (ensure_u32(&c->xl_recv[d][k], &c->xl_recv_cap[d][k], c->xl_n_recv[d][k])) return 1;
 	}
-	timer_stop(c, LS1G_T_EXCHANGE, launches);
-	if (finish_exchange(c)) return 1;
-	const uint32_t* new_of_old = c->alt.cell;     // valid directly after k_sort (cells.cu: gather_kernel)
-	for (int d = 0; d < 3; ++d)
-		for (int k = 0; k < 2; ++k) {
-			if (c->xl_n_send[d][k])
-				translate_slots_kernel<<<nblk(c->xl_n_send[d][k], 256), 256, 0, c->stream>>>(c->xl_n_send[d][k], c->xl_send[d][k], 0, new_of_old, c->xl_send[d][k]);
-			if (c->xl_n_recv[d][k])
-				translate_slots_kernel<<<nblk(c->xl_n_recv[d][k], 256), 256, 0, c->stream>>>(c->xl_n_recv[d][k], nullptr, c->xl_recv_base[d][k], new_of_old, c->xl_recv[d][k]);
-		}
-	CUDA_TRY(cudaGetLastError());
+	for (int r = 0; r < G.n; ++r) {
+		ls1g_ctx* c = G.c[r];
+		set_dev(c);
+		timer_stop(c, LS1G_T_EXCHANGE, launches);
+		if (finish_exchange(c)) return 1;
+		const uint32_t* new_of_old = c->alt.cell;     // valid directly after k_sort (cells.cu: gather_kernel)
+		for (int d = 0; d < 3; ++d)
+			for (int k = 0; k < 2; ++k) {
+				if (c->xl_n_send[d][k])
+					translate_slots_kernel<<<nblk(c->xl_n_send[d][k], 256), 256, 0, c->stream>>>(c->xl_n_send[d][k], c->xl_send[d][k], 0, new_of_old, c->xl_send[d][k]);
+				if (c->xl_n_recv[d][k])
+					translate_slots_kernel<<<nblk(c->xl_n_recv[d][k], 256), 256, 0, c->stream>>>(c->xl_n_recv[d][k], nullptr, c->xl_recv_base[d][k], new_of_old, c->xl_recv[d][k]);
+			}
+		CUDA_TRY(cudaGetLastError());
+	}
 	return 0;
 }
 
 // frozen-layout step: positions of the halo copies follow their owners, stage by stage (x, y, z: forwarded copies are
-// refreshed before they are forwarded again)
-int comm_refresh(ls1g_ctx* c) {
-	ncclComm_t comm = (ncclComm_t)c->nccl_comm;
-	timer_start(c, LS1G_T_EXCHANGE);
-	int launches = 0;
+// refreshed before they are forwarded again).  Asynchronous on every rank's current stream (no host synchronisation).
+int comm_refresh(const Group& G) {
+	const bool local = G.c[0]->comm_mode == 2;
+	for (int r = 0; r < G.n; ++r) { set_dev(G.c[r]); timer_start(G.c[r], LS1G_T_EXCHANGE); }
+	std::vector<int> launches(G.n, 0);
 	for (int d = 0; d < 3; ++d) {
-		if (c->cfg.rank_grid[d] <= 1) continue;
-		const int lower = neighbour_rank(c, d, 0), upper = neighbour_rank(c, d, 1);
-		const double shift[2] = {c->cfg.rank_coords[d] == 0 ? c->cfg.global_length[d] : 0.,
-		                         c->cfg.rank_coords[d] == c->cfg.rank_grid[d] - 1 ? -c->cfg.global_length[d] : 0.};
-		for (int k = 0; k < 2; ++k)
-			if (c->xl_n_send[d][k]) {
-				pack_pos_list_kernel<<<nblk(c->xl_n_send[d][k], 256), 256, 0, c->stream>>>(c->xl_n_send[d][k], c->xl_send[d][k], c->cur.pos, d, shift[k], c->send_buf[k]);
-				++launches;
+		if (G.c[0]->cfg.rank_grid[d] <= 1) continue;
+		for (int r = 0; r < G.n; ++r) {
+			ls1g_ctx* c = G.c[r];
+			set_dev(c);
+			const double shift[2] = {c->cfg.rank_coords[d] == 0 ? c->cfg.global_length[d] : 0.,
+			                         c->cfg.rank_coords[d] == c->cfg.rank_grid[d] - 1 ? -c->cfg.global_length[d] : 0.};
+			if (local) {      // my send buffers are free once both neighbours have copied the previous stage out of them
+				CUDA_TRY(cudaStreamWaitEvent(c->stream, G.c[neighbour_rank(c, d, 1)]->ev_read, 0));
+				CUDA_TRY(cudaStreamWaitEvent(c->stream, G.c[neighbour_rank(c, d, 0)]->ev_read, 0));
 			}
-		NCCL_TRY(g_nccl.GroupStart());
-		if (c->xl_n_send[d][0]) NCCL_TRY(g_nccl.Send(c->send_buf[0], (size_t)c->xl_n_send[d][0] * 3, NCCL_DOUBLE, lower, comm, c->stream));
-		if (c->xl_n_send[d][1]) NCCL_TRY(g_nccl.Send(c->send_buf[1], (size_t)c->xl_n_send[d][1] * 3, NCCL_DOUBLE, upper, comm, c->stream));
-		if (c->xl_n_recv[d][0]) NCCL_TRY(g_nccl.Recv(c->recv_buf[0], (size_t)c->xl_n_recv[d][0] * 3, NCCL_DOUBLE, upper, comm, c->stream));
-		if (c->xl_n_recv[d][1]) NCCL_TRY(g_nccl.Recv(c->recv_buf[1], (size_t)c->xl_n_recv[d][1] * 3, NCCL_DOUBLE, lower, comm, c->stream));
-		NCCL_TRY(g_nccl.GroupEnd());
-		for (int k = 0; k < 2; ++k)
-			if (c->xl_n_recv[d][k]) {
-				unpack_pos_list_kernel<<<nblk(c->xl_n_recv[d][k], 256), 256, 0, c->stream>>>(c->xl_n_recv[d][k], c->xl_recv[d][k], c->recv_buf[k], c->cur.pos);
-				++launches;
+			for (int k = 0; k < 2; ++k)
+				if (c->xl_n_send[d][k]) {
+					pack_pos_list_kernel<<<nblk(c->xl_n_send[d][k], 256), 256, 0, c->stream>>>(c->xl_n_send[d][k], c->xl_send[d][k], c->cur.pos, d, shift[k], c->send_buf[k]);
+					++launches[r];
+				}
+			if (local) CUDA_TRY(cudaEventRecord(c->ev_pack, c->stream));
+		}
+		for (int r = 0; r < G.n; ++r) {
+			ls1g_ctx* c = G.c[r];
+			set_dev(c);
+			const int lower = neighbour_rank(c, d, 0), upper = neighbour_rank(c, d, 1);
+			if (local) {
+				ls1g_ctx *up = G.c[upper], *lo = G.c[lower];
+				CUDA_TRY(cudaStreamWaitEvent(c->stream, up->ev_pack, 0));
+				CUDA_TRY(cudaStreamWaitEvent(c->stream, lo->ev_pack, 0));
+				if (c->xl_n_recv[d][0]) CUDA_TRY(cudaMemcpyAsync(c->recv_buf[0], up->send_buf[0], (size_t)c->xl_n_recv[d][0] * 3 * sizeof(double), cudaMemcpyDefault, c->stream));
+				if (c->xl_n_recv[d][1]) CUDA_TRY(cudaMemcpyAsync(c->recv_buf[1], lo->send_buf[1], (size_t)c->xl_n_recv[d][1] * 3 * sizeof(double), cudaMemcpyDefault, c->stream));
+				CUDA_TRY(cudaEventRecord(c->ev_read, c->stream));
+			} else {
+				ncclComm_t comm = (ncclComm_t)c->nccl_comm;
+				NCCL_TRY(g_nccl.GroupStart());
+				if (c->xl_n_send[d][0]) NCCL_TRY(g_nccl.Send(c->send_buf[0], (size_t)c->xl_n_send[d][0] * 3, NCCL_DOUBLE, lower, comm, c->stream));
+				if (c->xl_n_send[d][1]) NCCL_TRY(g_nccl.Send(c->send_buf[1], (size_t)c->xl_n_send[d][1] * 3, NCCL_DOUBLE, upper, comm, c->stream));
+				if (c->xl_n_recv[d][0]) NCCL_TRY(g_nccl.Recv(c->recv_buf[0], (size_t)c->xl_n_recv[d][0] * 3, NCCL_DOUBLE, upper, comm, c->stream));
+				if (c->xl_n_recv[d][1]) NCCL_TRY(g_nccl.Recv(c->recv_buf[1], (size_t)c->xl_n_recv[d][1] * 3, NCCL_DOUBLE, lower, comm, c->stream));
+				NCCL_TRY(g_nccl.GroupEnd());
 			}
+			for (int k = 0; k < 2; ++k)
+				if (c->xl_n_recv[d][k]) {
+					unpack_pos_list_kernel<<<nblk(c->xl_n_recv[d][k], 256), 256, 0, c->stream>>>(c->xl_n_recv[d][k], c->xl_recv[d][k], c->recv_buf[k], c->cur.pos);
+					++launches[r];
+				}
+		}
 	}
-	CUDA_TRY(cudaGetLastError());
-	timer_stop(c, LS1G_T_EXCHANGE, launches);
+	for (int r = 0; r < G.n; ++r) { set_dev(G.c[r]); CUDA_TRY(cudaGetLastError()); timer_stop(G.c[r], LS1G_T_EXCHANGE, launches[r]); }
 	return 0;
 }
 
-int comm_allreduce_max(ls1g_ctx* c, double* d_vals, int n) {
-	if (c->n_ranks <= 1) return 0;
-	if (c->comm_mode != 1) LS1G_FAIL("ls1g: device all-reduce needs the NCCL transport");
-	NCCL_TRY(g_nccl.AllReduce(d_vals, d_vals, (size_t)n, NCCL_DOUBLE, 2 /* ncclMax */, (ncclComm_t)c->nccl_comm, c->stream));
-	return 0;
+// out[k] = op over ranks of g[r][k]; g is the pinned host ring slot every rank copied its values into (zero-copy reads)
+__global__ void group_reduce_kernel(const double* g, int n_ranks, int n, int op, double* __restrict__ out) {
+	const int k = threadIdx.x;
+	if (k >= n) return;
+	double v = __ldcv(g + k);
+	for (int r = 1; r < n_ranks; ++r) { const double x = __ldcv(g + 8 * r + k); v = op == COMM_MAX ? fmax(v, x) : v + x; }
+	out[k] = v;
 }
 
-int comm_allreduce(ls1g_ctx* c, double* d_vals, int n) {
-	if (c->n_ranks <= 1) return 0;
-	if (c->comm_mode != 1) LS1G_FAIL("ls1g: device all-reduce needs the NCCL transport (local groups reduce on the host)");
-	NCCL_TRY(g_nccl.AllReduce(d_vals, d_vals, (size_t)n, NCCL_DOUBLE, NCCL_SUM, (ncclComm_t)c->nccl_comm, c->stream));
+int comm_allreduce(const Group& G, int which, int off, int n, int op) {
+	ls1g_ctx* c0 = G.c[0];
+	if (c0->n_ranks <= 1) return 0;
+	if (n < 1 || n > 8) LS1G_FAIL("ls1g: group reduction of more than 8 values");
+	auto ptr = [&](ls1g_ctx* c) { return which == COMM_FLAGS ? (double*)c->d_flags + off : c->d_scalars + off; };
+	if (c0->comm_mode == 1) {
+		set_dev(c0);
+		NCCL_TRY(g_nccl.AllReduce(ptr(c0), ptr(c0), (size_t)n, NCCL_DOUBLE, op == COMM_MAX ? 2 /* ncclMax */ : NCCL_SUM, (ncclComm_t)c0->nccl_comm, c0->stream));
+		return 0;
+	}
+	if (c0->comm_mode != 2 || !c0->gbuf) LS1G_FAIL("ls1g: group reduction without a transport");
+	// ring of 4 slots: a rank can only be a full reduction ahead of the slowest one (every reduction waits for everybody's
+	// contribution), so slot s is not rewritten while somebody still reads it
+	double* slot = c0->gbuf + (size_t)(c0->gseq % 4) * G.n * 8;
+	for (int r = 0; r < G.n; ++r) {
+		ls1g_ctx* c = G.c[r];
+		set_dev(c);
+		CUDA_TRY(cudaMemcpyAsync(slot + 8 * r, ptr(c), n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
+		CUDA_TRY(cudaEventRecord(c->ev_ar, c->stream));
+	}
+	for (int r = 0; r < G.n; ++r) {
+		ls1g_ctx* c = G.c[r];
+		set_dev(c);
+		for (int q = 0; q < G.n; ++q) if (q != r) CUDA_TRY(cudaStreamWaitEvent(c->stream, G.c[q]->ev_ar, 0));
+		group_reduce_kernel<<<1, 32, 0, c->stream>>>(slot, G.n, n, op, ptr(c));
+		CUDA_TRY(cudaGetLastError());
+	}
+	for (int r = 0; r < G.n; ++r) G.c[r]->gseq = c0->gseq + 1;
 	return 0;
 }
 
@@ -432,22 +551,31 @@ extern "C" int ls1g_comm_init(ls1g_ctx* c, int n_ranks, int rank, const unsigned
 
 void comm_destroy(ls1g_ctx* c) {
 	if (c->comm_mode == 1 && c->nccl_comm && g_nccl.lib) g_nccl.CommDestroy((ncclComm_t)c->nccl_comm);
+	if (c->comm_mode == 2) {
+		// the group dissolves: the surviving members fall back to "no transport" (their next collective call fails loudly)
+		for (ls1g_ctx* p : c->peers) if (p != c) { p->peers.clear(); if (p->gbuf && !p->gbuf_owner) p->gbuf = nullptr; p->comm_mode = 0; }
+		if (c->gbuf && c->gbuf_owner) cudaFreeHost(c->gbuf);
+		else for (ls1g_ctx* p : c->peers) if (p != c && p->gbuf_owner && p->gbuf) { cudaFreeHost(p->gbuf); p->gbuf = nullptr; p->gbuf_owner = 0; }
+		c->gbuf = nullptr; c->gbuf_owner = 0; c->peers.clear();
+	}
 	c->nccl_comm = nullptr; c->comm_mode = 0;
 }
 
 extern "C" int ls1g_allreduce_sum(ls1g_ctx* c, double* values, int n) {
 	if (!c || !values || n < 0 || n > 8) LS1G_FAIL("ls1g_allreduce_sum: bad arguments (n <= 8)");
 	if (c->n_ranks <= 1) return 0;
+	if (c->comm_mode != 1) LS1G_FAIL("ls1g_allreduce_sum: NCCL ranks only (a local group lives in one process: sum on the host)");
 	CUDA_TRY(cudaSetDevice(c->cfg.device));
 	double* d = c->d_scalars + 8;
 	CUDA_TRY(cudaMemcpyAsync(d, values, n * sizeof(double), cudaMemcpyHostToDevice, c->stream));
-	if (comm_allreduce(c, d, n)) return 1;
+	Group G{&c, 1};
+	if (comm_allreduce(G, COMM_SCALARS, 8, n, COMM_SUM)) return 1;
 	CUDA_TRY(cudaMemcpyAsync(values, d, n * sizeof(double), cudaMemcpyDeviceToHost, c->stream));
 	CUDA_TRY(cudaStreamSynchronize(c->stream));
 	return 0;
 }
 
-// ---- local transport: all ranks are contexts of this process (test path, any number of GPUs >= 1) -----------
+// ---- local transport: all ranks are contexts of this process (any number of GPUs >= 1) ----------------------
 extern "C" int ls1g_comm_init_local(ls1g_ctx** ctxs, int n) {
 	if (!ctxs || n < 1) LS1G_FAIL("ls1g_comm_init_local: bad arguments");
 	for (int r = 0; r < n; ++r) {
@@ -457,39 +585,45 @@ extern "C" int ls1g_comm_init_local(ls1g_ctx** ctxs, int n) {
 		if (r != rank_of(c->cfg.rank_grid, c->cfg.rank_coords[0], c->cfg.rank_coords[1], c->cfg.rank_coords[2]))
 			LS1G_FAIL("ls1g_comm_init_local: contexts must be ordered by rank (row-major coords)");
 		if (check_grid_order(c)) return 1;
+		if (c->comm_mode != 0) LS1G_FAIL("ls1g_comm_init_local: context already has a transport");
+	}
+	double* gbuf = nullptr;
+	if (n > 1) {
+		CUDA_TRY(cudaSetDevice(ctxs[0]->cfg.device));
+		CUDA_TRY(cudaHostAlloc((void**)&gbuf, (size_t)4 * n * 8 * sizeof(double), cudaHostAllocPortable | cudaHostAllocMapped));
+		memset(gbuf, 0, (size_t)4 * n * 8 * sizeof(double));
+		// contexts on different GPUs: direct copies between them (falls back to staged copies where peer access is unavailable)
+		for (int r = 0; r < n; ++r)
+			for (int q = 0; q < n; ++q) {
+				const int a = ctxs[r]->cfg.device, b = ctxs[q]->cfg.device;
+				if (a == b) continue;
+				int can = 0;
+				if (cudaDeviceCanAccessPeer(&can, a, b) == cudaSuccess && can) {
+					cudaSetDevice(a);
+					cudaError_t e = cudaDeviceEnablePeerAccess(b, 0);
+					if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) LS1G_FAIL(std::string("cudaDeviceEnablePeerAccess: ") + cudaGetErrorString(e));
+					cudaGetLastError();
+				}
+			}
+	}
+	for (int r = 0; r < n; ++r) {
+		ls1g_ctx* c = ctxs[r];
 		c->n_ranks = n; c->rank = r; c->comm_mode = n > 1 ? 2 : 0;
+		c->peers.assign(ctxs, ctxs + n);
+		c->gbuf = gbuf; c->gbuf_owner = r == 0 && gbuf; c->gseq = 0;
 	}
 	return 0;
 }
 
-// one exchange of all ranks in lockstep
+// one leaving + halo exchange of all local ranks in lockstep (= ls1g_exchange on every rank)
+int ls1g_nl_leave_group(const Group& G);
 extern "C" int ls1g_exchange_group(ls1g_ctx** ctxs, int n) {
 	if (!ctxs || n < 1) LS1G_FAIL("ls1g_exchange_group: bad arguments");
 	if (n == 1) return ls1g_exchange(ctxs[0]);
-	for (int r = 0; r < n; ++r) if (ctxs[r]->in_list_mode && ls1g_nl_leave(ctxs[r])) return 1;
-	for (int r = 0; r < n; ++r) if (ctxs[r]->comm_mode != 2) LS1G_FAIL("ls1g_exchange_group: call ls1g_comm_init_local first");
-	for (int d = 0; d < 3; ++d) {
-		if (ctxs[0]->cfg.rank_grid[d] <= 1) continue;
-		for (int r = 0; r < n; ++r) { CUDA_TRY(cudaSetDevice(ctxs[r]->cfg.device)); if (stage_pack(ctxs[r], d)) return 1; }
-		std::vector<uint32_t> nrecv(2 * n);
-		for (int r = 0; r < n; ++r) {
-			ls1g_ctx* c = ctxs[r];
-			CUDA_TRY(cudaSetDevice(c->cfg.device));
-			const int rec = rec_doubles(c);
-			ls1g_ctx* up = ctxs[neighbour_rank(c, d, 1)];
-			ls1g_ctx* lo = ctxs[neighbour_rank(c, d, 0)];
-			// from my upper neighbour I get what it sent downwards (its buffer 0); from my lower neighbour its buffer 1
-			nrecv[2 * r] = up->h_counters[2]; nrecv[2 * r + 1] = lo->h_counters[3];
-			if (nrecv[2 * r] > c->xbuf_cap || nrecv[2 * r + 1] > c->xbuf_cap) LS1G_FAIL("ls1g exchange: receive buffer overflow");
-			if (nrecv[2 * r]) CUDA_TRY(cudaMemcpyAsync(c->recv_buf[0], up->send_buf[0], (size_t)nrecv[2 * r] * rec * sizeof(double), cudaMemcpyDefault, c->stream));
-			if (nrecv[2 * r + 1]) CUDA_TRY(cudaMemcpyAsync(c->recv_buf[1], lo->send_buf[1], (size_t)nrecv[2 * r + 1] * rec * sizeof(double), cudaMemcpyDefault, c->stream));
-		}
-		for (int r = 0; r < n; ++r) {
-			CUDA_TRY(cudaSetDevice(ctxs[r]->cfg.device));
-			if (stage_unpack(ctxs[r], &nrecv[2 * r])) return 1;
-			CUDA_TRY(cudaStreamSynchronize(ctxs[r]->stream));   // send buffers are reused by the next stage
-		}
-	}
-	for (int r = 0; r < n; ++r) { CUDA_TRY(cudaSetDevice(ctxs[r]->cfg.device)); if (finish_exchange(ctxs[r])) return 1; }
+	Group G{ctxs, n};
+	if (check_group(G)) return 1;
+	if (ls1g_nl_leave_group(G)) return 1;
+	if (comm_exchange(G)) return 1;
+	for (int r = 0; r < n; ++r) { set_dev(ctxs[r]); CUDA_TRY(cudaStreamSynchronize(ctxs[r]->stream)); }
 	return 0;
 }

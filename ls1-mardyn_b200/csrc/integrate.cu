@@ -273,19 +273,46 @@ int k_post_pre(ls1g_ctx* c, double dt, int do_post, int do_pre, int thermostat, 
 		if (ls1g_prereduce(c, nbr, 4, pbase)) return 1;
 		finalize_kernel<<<1, 256, 0, c->stream>>>(pbase, nbr, 4, c->d_scalars + 4, 0., nullptr); launches += 1 + (nbr != nb);
 	} else if (do_post) {
+		// one rank (several ranks: k_post_sums + group all-reduce + k_betas_scale_pre, see g_post_pre in step.cu)
 		if (nb) { launch_int<true, false>(c, a, nb); ++launches; }
 		if (ls1g_prereduce(c, nbr, 4, pbase)) return 1;
 		finalize_kernel<<<1, 256, 0, c->stream>>>(pbase, nbr, 4, c->d_scalars + 4, target_T, c->d_scalars + 8); launches += 1 + (nbr != nb);
-		if (c->n_ranks > 1) {
-			// global sums first, then the betas from the reduced values
-			if (comm_allreduce(c, c->d_scalars + 4, 4)) return 1;
-			finalize_kernel<<<1, 256, 0, c->stream>>>(c->d_scalars + 4, 1, 4, c->d_scalars + 4, target_T, c->d_scalars + 8); ++launches;
-		}
 		a.betas = c->d_scalars + 8;
 		if (nb) { if (do_pre) launch_int<false, true>(c, a, nb); else launch_int<false, false>(c, a, nb); ++launches; }
 	} else if (do_pre) {
 		if (nb) { launch_int<false, true>(c, a, nb); ++launches; }
 	}
+	CUDA_TRY(cudaGetLastError());
+	timer_stop(c, LS1G_T_INTEGRATE, launches);
+	return 0;
+}
+
+// Thermostat step on several ranks, first half: post kick + this rank's kinetic sums in d_scalars[4..7]
+int k_post_sums(ls1g_ctx* c, double dt) {
+	unsigned nb = nblk(c->n_slots, INT_THREADS);
+	if (ensure_partials(c, nb ? nb : 1, 4)) return 1;
+	timer_start(c, LS1G_T_INTEGRATE);
+	IntArgs a = make_args(c); a.dt = dt; a.dt_half = 0.5 * dt; a.partials = c->partials;
+	int launches = 0;
+	size_t nbr = nb; const double* pbase = c->partials;
+	if (nb) { launch_int<true, false>(c, a, nb); ++launches; }
+	if (ls1g_prereduce(c, nbr, 4, pbase)) return 1;
+	finalize_kernel<<<1, 256, 0, c->stream>>>(pbase, nbr, 4, c->d_scalars + 4, 0., nullptr); launches += 1 + (nbr != nb);
+	CUDA_TRY(cudaGetLastError());
+	timer_stop(c, LS1G_T_INTEGRATE, launches);
+	return 0;
+}
+
+// ... second half, after the all-reduce of the sums into d_scalars[12..15]: betas of Domain::calculateGlobalValues from the global sums, then
+// VelocityScalingThermostat::apply (+ the pre kick of the next step) in one kernel
+int k_betas_scale_pre(ls1g_ctx* c, double dt, int do_pre, double target_T) {
+	unsigned nb = nblk(c->n_slots, INT_THREADS);
+	timer_start(c, LS1G_T_INTEGRATE);
+	IntArgs a = make_args(c); a.dt = dt; a.dt_half = 0.5 * dt; a.partials = c->partials;
+	int launches = 1;
+	finalize_kernel<<<1, 256, 0, c->stream>>>(c->d_scalars + 12, 1, 4, c->d_scalars + 12, target_T, c->d_scalars + 8);
+	a.betas = c->d_scalars + 8;
+	if (nb) { if (do_pre) launch_int<false, true>(c, a, nb); else launch_int<false, false>(c, a, nb); ++launches; }
 	CUDA_TRY(cudaGetLastError());
 	timer_stop(c, LS1G_T_INTEGRATE, launches);
 	return 0;

@@ -13,9 +13,10 @@ int ls1g_prereduce(ls1g_ctx* c, size_t& nb, int nv, const double*& base);   // f
 
 static inline unsigned nblk(size_t n, unsigned t) { return (unsigned)((n + t - 1) / t); }
 
-// list mode applies to: one rank, single-centre LJ, default kernels, skin > 0, not disabled by an earlier overflow
+// list mode applies to: single-centre LJ, default kernels, skin > 0, not disabled by an earlier overflow; one rank or several with
+// either transport (NCCL, in-process group)
 int nl_applicable(const ls1g_ctx* c) {
-	return c->simple_1clj && (c->n_ranks == 1 || c->comm_mode == 1) && c->force_variant == 0 && c->skin > 0. && !c->list_disabled;
+	return c->simple_1clj && (c->n_ranks == 1 || c->comm_mode == 1 || c->comm_mode == 2) && c->force_variant == 0 && c->skin > 0. && !c->list_disabled;
 }
 
 // switch the bin grid: cells >= cutoff + skin (list mode) or the reference grid

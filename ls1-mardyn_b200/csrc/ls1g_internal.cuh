@@ -122,6 +122,7 @@ struct ls1g_ctx {
 	cudaStream_t stream_comm;               // high-priority stream of the overlapped halo refresh (multi-rank list steps)
 	cudaEvent_t ev_pos, ev_halo;
 	int      track_disp;                    // integrate kernels track max |r - pos_build|^2 into d_flags[0]
+	uint64_t list_rebuilds;                 // list builds since the context was created (ls1g_list_stats)
 	int      list_R;                        // cell rows per block of the list kernels: 4 (2 x 2 bundle) or 1 (lists.cuh)
 	int      list_zchk;                     // the last build saw a (nearly) coincident pair: force kernels keep the r2 == 0 test
 	int      list_tcap;                     // tile capacity used by the list force kernel (max tile of the last build, padded)
@@ -159,10 +160,24 @@ struct ls1g_ctx {
 	size_t   xl_send_cap[3][2], xl_recv_cap[3][2];
 	uint32_t xl_n_send[3][2], xl_n_recv[3][2], xl_recv_base[3][2];
 	uint32_t *xl_pre[2];                       // device scratch: pre-sort slot of every packed record (current stage)
+	// in-process transport (comm_mode 2): the ranks are contexts of one process, driven in lockstep by one host thread
+	std::vector<ls1g_ctx*> peers;              // all ranks of the local group in rank order (this context included)
+	cudaEvent_t ev_pack, ev_read;              // send buffers of the current stage packed / neighbours' buffers copied into my receive buffers
+	cudaEvent_t ev_ar;                         // my contribution to the current group reduction has reached gbuf
+	double* gbuf; int gbuf_owner;              // pinned host ring [4][n_ranks][8] of the group reductions (allocated by rank 0)
+	unsigned gseq;                             // group reductions issued so far (ring slot = gseq % 4)
+	// per-step records of ls1g_run / ls1g_step on the device (copied out once per call)
+	double* d_rec; size_t d_rec_cap;
 
 	Timer timers[LS1G_T_COUNT];
 	std::vector<PendingEvt> pending;        // event pairs not yet resolved into timers[]
 	std::vector<cudaEvent_t> evpool;
+};
+
+// One rank (single context, with or without NCCL) or all ranks of an in-process group, driven in lockstep
+struct Group {
+	ls1g_ctx* const* c; int n;
+	bool multi() const { return c[0]->n_ranks > 1; }
 };
 
 // error handling --------------------------------------------------------------------------------
@@ -193,11 +208,13 @@ int  k_forces(ls1g_ctx* c);                           // results in d_scalars[0.
 // peak.cu
 int  k_fp64_peak(int device, double* tflops);
 // comm.cu
-int  comm_exchange(ls1g_ctx* c);
-int  comm_exchange_build(ls1g_ctx* c);         // list mode: migrate leavers, then halo pass with persistent lists, sort
-int  comm_refresh(ls1g_ctx* c);                // list mode: refresh halo positions along the persistent lists
-int  comm_allreduce_max(ls1g_ctx* c, double* d_vals, int n);
-int  comm_allreduce(ls1g_ctx* c, double* d_vals, int n);
+int  comm_exchange(const Group& G);            // leaving + halo exchange of every rank of the group, then the local sort
+int  comm_exchange_build(const Group& G);      // list mode: migrate leavers, then halo pass with persistent lists, sort
+int  comm_refresh(const Group& G);             // list mode: refresh halo positions along the persistent lists (asynchronous)
+enum { COMM_SUM = 0, COMM_MAX = 2 };
+enum { COMM_SCALARS = 0, COMM_FLAGS = 1 };
+// all-reduce of n <= 8 doubles at d_scalars + off (COMM_SCALARS) or d_flags + off (COMM_FLAGS) of every rank, in place, asynchronous
+int  comm_allreduce(const Group& G, int which, int off, int n, int op);
 void comm_destroy(ls1g_ctx* c);
 
 void timer_start(ls1g_ctx* c, int which);

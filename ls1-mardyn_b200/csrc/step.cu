@@ -9,28 +9,45 @@
 #include <stdlib.h>
 
 int k_post_pre(ls1g_ctx* c, double dt, int do_post, int do_pre, int thermostat, double target_T);
+int k_post_sums(ls1g_ctx* c, double dt);                                       // integrate.cu: post kick + local kinetic sums
+int k_betas_scale_pre(ls1g_ctx* c, double dt, int do_pre, double target_T);   // integrate.cu: betas from the (global) sums, scale (+ pre)
 void ls1g_resolve_timers(ls1g_ctx* c);
 
 #define NEED(c) do { if (!(c)) LS1G_FAIL("null context"); CUDA_TRY(cudaSetDevice((c)->cfg.device)); } while (0)
 // per-step operators and transfers work on the reference-grid state: leave the neighbour-list layout first
-#define NEED_REF(c) do { NEED(c); if ((c)->in_list_mode && ls1g_nl_leave(c)) return 1; } while (0)
+#define NEED_REF(c) do { NEED(c); if ((c)->in_list_mode && ls1g_nl_leave(c)) return 1; CUDA_TRY(cudaSetDevice((c)->cfg.device)); } while (0)
 
 int nl_set_bin_grid(ls1g_ctx* c, int list_mode);
 static int sync_check(ls1g_ctx* c, const char* what);
+static inline void set_dev(const ls1g_ctx* c) { cudaSetDevice(c->cfg.device); }
+#define FOR_G(G, c) for (int _r = 0; _r < (G).n; ++_r) if (ls1g_ctx* c = (set_dev((G).c[_r]), (G).c[_r]))
+
+// the group a context is driven with: itself, or - for a member of an in-process group - all ranks of that group
+static Group group_of(ls1g_ctx*& self) {
+	if (self->comm_mode == 2 && !self->peers.empty()) return Group{self->peers.data(), (int)self->peers.size()};
+	return Group{&self, 1};
+}
 
 // ls1g_run leaves the container in the frozen neighbour-list layout so that the next ls1g_run continues without a
 // rebuild.  Everything else first restores what the per-step loop leaves behind: wrapped positions, molecules sorted on
 // the reference grid, halo copies dropped (one exchange; collective on multi-rank contexts, like the operators themselves).
+int ls1g_nl_leave_group(const Group& G) {
+	bool any = false;
+	for (int r = 0; r < G.n; ++r) any = any || G.c[r]->in_list_mode;
+	if (!any) return 0;
+	FOR_G(G, c) {
+		c->in_list_mode = 0; c->track_disp = 0;
+		if (nl_set_bin_grid(c, 0)) return 1;
+		c->sorted = 0;
+	}
+	if (G.multi() ? comm_exchange(G) : k_sort(G.c[0], 1)) return 1;
+	FOR_G(G, c) { if (k_drop_halo(c)) return 1; if (sync_check(c, "leaving the neighbour-list layout")) return 1; }
+	return 0;
+}
 int ls1g_nl_leave(ls1g_ctx* c) {
 	if (!c->in_list_mode) return 0;
-	c->in_list_mode = 0; c->track_disp = 0;
-	if (nl_set_bin_grid(c, 0)) return 1;
-	c->sorted = 0;
-	if (c->n_ranks > 1 ? comm_exchange(c) : k_sort(c, 1)) return 1;
-	if (k_drop_halo(c)) return 1;
-	return sync_check(c, "leaving the neighbour-list layout");
+	return ls1g_nl_leave_group(group_of(c));
 }
-
 
 static int sync_check(ls1g_ctx* c, const char* what) {
 	cudaError_t e = cudaStreamSynchronize(c->stream);
@@ -49,8 +66,11 @@ extern "C" int ls1g_update(ls1g_ctx* c) {
 // DomainDecompBase::exchangeMolecules (DomainDecompBase.cpp:51-86) / DomainDecomposition::balanceAndExchange
 extern "C" int ls1g_exchange(ls1g_ctx* c) {
 	NEED_REF(c);
-	if (c->n_ranks > 1) { if (comm_exchange(c)) return 1; }
-	else if (k_sort(c, 1)) return 1;
+	if (c->n_ranks > 1) {
+		if (c->comm_mode == 2) LS1G_FAIL("ls1g_exchange: the ranks of a local group exchange together (ls1g_exchange_group)");
+		Group G{&c, 1};
+		if (comm_exchange(G)) return 1;
+	} else if (k_sort(c, 1)) return 1;
 	return sync_check(c, "ls1g_exchange");
 }
 
@@ -106,12 +126,28 @@ extern "C" int ls1g_selective_thermostat(ls1g_ctx* c, double limit_trans_energy,
 }
 
 int nl_applicable(const ls1g_ctx* c);
-int nl_set_bin_grid(ls1g_ctx* c, int list_mode);
 int k_list_build(ls1g_ctx* c);
 int k_forces_list(ls1g_ctx* c, int count_pairs);
 int k_forces_list_fused(ls1g_ctx* c, double dt, int phase);
 int k_forces_list_post(ls1g_ctx* c, double dt, int vi);
 int k_halo_refresh(ls1g_ctx* c);
+
+// [post(step n)] [+ thermostat] [+ pre(step n+1)] on every rank.  With a thermostat on several ranks the betas come from the GLOBAL
+// kinetic sums (Domain::calculateGlobalValues, Domain.cpp:170-176,226-247): local sums, group all-reduce, then scale (+ pre).
+static int g_post_pre(const Group& G, double dt, int do_post, int do_pre, int thermo, double target_T) {
+	if (!(thermo && do_post && G.multi())) {
+		FOR_G(G, c) if (k_post_pre(c, dt, do_post, do_pre, thermo, target_T)) return 1;
+		return 0;
+	}
+	// d_scalars[4..7] keep this rank's sums (the step record); the global ones are formed in d_scalars[12..15]
+	FOR_G(G, c) {
+		if (k_post_sums(c, dt)) return 1;
+		CUDA_TRY(cudaMemcpyAsync(c->d_scalars + 12, c->d_scalars + 4, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream));
+	}
+	if (comm_allreduce(G, COMM_SCALARS, 12, 4, COMM_SUM)) return 1;
+	FOR_G(G, c) if (k_betas_scale_pre(c, dt, do_pre, target_T)) return 1;
+	return 0;
+}
 
 // Neighbour-list steps of ls1g_run (lists.cuh).  On entry the pre-kick of step 0 is done.  Runs steps [0, n_steps) unless
 // a buffer limit is hit while building lists for step s: then the bin grid is restored and *done = s tells the caller to
@@ -122,44 +158,60 @@ int k_halo_refresh(ls1g_ctx* c);
 // snapshot of the displacement flag (d_flags[3]) and return at once when the lists have expired.  The host reads the
 // same value up to NL_AHEAD steps late (pinned copy + event), rebuilds, and enqueues the skipped steps again.  Device and host evaluate the
 // identical comparison d2 > disp_thr2 on the identical bits; the flag is monotone between builds (atomicMax), so an
-// expired step stays skipped however many kernels follow it.
+// expired step stays skipped however many kernels follow it.  Several ranks (NCCL: this rank and its peers in other processes;
+// local group: all contexts of G) take every decision on the all-reduced maximum, so they rebuild at the same step.
 #define NL_OVF_LIST_BIT 2ull      // lists.cuh: NL_OVF_LIST
 #define NL_OVF_TILE_BIT 1ull      // lists.cuh: NL_OVF_TILE
 #define NL_TCAP_MAX_H 5120        // lists.cuh: NL_TCAP
 #define NL_LCAP_MAX_H 1020        // lists.cuh: NL_LCAP_MAX
 #define NL_AHEAD 3      // steps the host may enqueue beyond the last displacement flag it has read
 #define NL_RING 4       // pinned flag copies / events in flight (> NL_AHEAD)
-static int flag_snapshot(ls1g_ctx* c, int ring) {
-	if (c->n_ranks > 1 && comm_allreduce_max(c, (double*)c->d_flags, 1)) return 1;      // non-negative doubles: bit order == value order
-	CUDA_TRY(cudaMemcpyAsync(c->d_flags + 3, c->d_flags, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, c->stream));
-	CUDA_TRY(cudaMemcpyAsync(c->h_flags + 4 + ring, c->d_flags, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
-	CUDA_TRY(cudaEventRecord(c->disp_ev[ring], c->stream));
+static int flag_snapshot(const Group& G, int ring) {
+	if (G.multi() && comm_allreduce(G, COMM_FLAGS, 0, 1, COMM_MAX)) return 1;      // non-negative doubles: bit order == value order
+	FOR_G(G, c) {
+		CUDA_TRY(cudaMemcpyAsync(c->d_flags + 3, c->d_flags, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, c->stream));
+		CUDA_TRY(cudaMemcpyAsync(c->h_flags + 4 + ring, c->d_flags, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+		CUDA_TRY(cudaEventRecord(c->disp_ev[ring], c->stream));
+	}
 	return 0;
 }
 
-static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, double target_T, double* d_rec, int* done, int want_vi = 1) {
+static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, double target_T, int* done, int want_vi = 1) {
 	*done = 0;
 	bool need_build = true;
 	int rc = 0, s = 0;
-	c->disp_thr2 = (0.4995 * c->skin) * (0.4995 * c->skin);    // lists stay exact while no molecule moved more than skin/2
-	c->guard_on = 0;
+	ls1g_ctx* c0 = G.c[0];
+	for (int r = 0; r < G.n; ++r) {
+		G.c[r]->disp_thr2 = (0.4995 * c0->skin) * (0.4995 * c0->skin);    // lists stay exact while no molecule moved more than skin/2
+		G.c[r]->guard_on = 0;
+	}
 	const bool dbg = getenv("LS1G_DEBUG") != nullptr;
 	// the integrator is fused into the force kernel on NVE steps (LS1G_FUSE=0 keeps the separate integrate kernel)
 	const char* fe = getenv("LS1G_FUSE");
-	const bool fuse_nve = !thermo && !c->vi_every_step && !(fe && atoi(fe) == 0);
-	const bool post_fuse = !thermo && c->n_ranks == 1 && !(fe && atoi(fe) == 0);      // single rank: the kinetic sums need no all-reduce
-	// multi-rank: overlap the halo refresh with the inner blocks of the force pass (LS1G_OVERLAP=0: exchange first, then one launch)
+	const bool fuse_nve = !thermo && !c0->vi_every_step && !(fe && atoi(fe) == 0);
+	const bool post_fuse = !thermo && c0->n_ranks == 1 && !(fe && atoi(fe) == 0);      // single rank: the kinetic sums need no all-reduce
+	// several ranks: overlap the halo refresh with the inner blocks of the force pass (LS1G_OVERLAP=0: exchange first, then one launch)
 	const char* oe = getenv("LS1G_OVERLAP");
-	const bool overlap = c->n_ranks > 1 && !(oe && atoi(oe) == 0);
-	auto expired = [&](int ring) { double d2; memcpy(&d2, c->h_flags + 4 + ring, sizeof(double)); return d2 > c->disp_thr2; };
-	if (c->in_list_mode) {       // continuing the previous ls1g_run: the pre-kick above was tracked; rebuild only if the lists expired
-		if (flag_snapshot(c, 0) || sync_check(c, "ls1g_run (displacement)")) return 1;
+	const bool overlap = G.multi() && !(oe && atoi(oe) == 0);
+	auto expired = [&](int ring) { double d2; memcpy(&d2, c0->h_flags + 4 + ring, sizeof(double)); return d2 > c0->disp_thr2; };      // all ranks hold the same value
+	auto fail = [&]() { FOR_G(G, c) { c->track_disp = 0; c->in_list_mode = 0; c->guard_on = 0; nl_set_bin_grid(c, 0); cudaStreamSynchronize(c->stream); cudaStreamSynchronize(c->stream_comm); } return 1; };
+	bool cont = true;
+	for (int r = 0; r < G.n; ++r) cont = cont && G.c[r]->in_list_mode;
+	if (cont) {       // continuing the previous ls1g_run: the pre-kick above was tracked; rebuild only if the lists expired
+		if (flag_snapshot(G, 0)) return fail();
+		FOR_G(G, c) if (sync_check(c, "ls1g_run (displacement)")) return fail();
 		need_build = expired(0);
-	} else if (nl_set_bin_grid(c, 1)) return 1;
-	c->in_list_mode = 1;
+	} else {
+		FOR_G(G, c) if (nl_set_bin_grid(c, 1)) return fail();
+	}
+	for (int r = 0; r < G.n; ++r) G.c[r]->in_list_mode = 1;
 	int rebuilds = 0, repeats = 0, regrow = 0;
 	double t_build = 0., t_wait = 0., t_enq = 0., t_max_wait = 0., t_max_enq = 0.;     // host wall clock, LS1G_DEBUG only
 	auto now = [&]() { if (!dbg) return 0.; struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6; };
+	auto rec_copy = [&](ls1g_ctx* c, int step, int off, int n) {
+		if (c->d_rec && cudaMemcpyAsync(c->d_rec + 8 * (size_t)step + off, c->d_scalars + off, n * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) return 1;
+		return 0;
+	};
 	// s   = next step to enqueue
 	// chk = next step whose displacement flag (written by its integrate kernel, deciding step chk + 1) the host has not read
 	int chk = 0;
@@ -169,100 +221,113 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 			bool overlapped = false;
 			const double t0 = now();
 			if (need_build) {
-				c->sorted = 0; c->track_disp = 0; c->guard_on = 0;
-				c->forces_valid = 0;
-				rc = c->n_ranks > 1 ? comm_exchange_build(c) : k_sort(c, 1);
-				c->forces_valid = 1;
-				if (!rc) rc = k_halo_map(c);
-				if (!rc) rc = k_list_build(c);             // zeroes d_flags[0..2]
-				if (!rc && cudaMemsetAsync(c->d_flags + 3, 0, sizeof(unsigned long long), c->stream) != cudaSuccess) rc = 1;
-				if (!rc && sync_check(c, "ls1g_run (list build)")) rc = 1;
-				if (!rc && c->n_ranks > 1) {         // every rank must take the same decision: [hard overflow, list overflow, tile overflow]
-					const unsigned long long hb = c->h_flags[1];
-					double ovf[3] = {(hb & ~(NL_OVF_LIST_BIT | NL_OVF_TILE_BIT)) ? 1. : 0., (hb & NL_OVF_LIST_BIT) ? 1. : 0., (hb & NL_OVF_TILE_BIT) ? 1. : 0.};
-					if (cudaMemcpyAsync(c->d_scalars + 12, ovf, 3 * sizeof(double), cudaMemcpyHostToDevice, c->stream) != cudaSuccess) rc = 1;
-					if (!rc) rc = comm_allreduce_max(c, c->d_scalars + 12, 3);
-					if (!rc && cudaMemcpyAsync(ovf, c->d_scalars + 12, 3 * sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess) rc = 1;
-					if (!rc && sync_check(c, "ls1g_run (list build)")) rc = 1;
-					if (ovf[0] != 0.) c->h_flags[1] |= 8;
-					if (ovf[1] != 0.) c->h_flags[1] |= NL_OVF_LIST_BIT;
-					if (ovf[2] != 0.) c->h_flags[1] |= NL_OVF_TILE_BIT;
+				FOR_G(G, c) { c->sorted = 0; c->track_disp = 0; c->guard_on = 0; c->forces_valid = 0; }
+				rc = G.multi() ? comm_exchange_build(G) : k_sort(c0, 1);
+				FOR_G(G, c) {
+					c->forces_valid = 1;
+					if (!rc) rc = k_halo_map(c);
+					if (!rc) rc = k_list_build(c);             // zeroes d_flags[0..2]
+					if (!rc && cudaMemsetAsync(c->d_flags + 3, 0, sizeof(unsigned long long), c->stream) != cudaSuccess) rc = 1;
 				}
+				FOR_G(G, c) if (!rc && sync_check(c, "ls1g_run (list build)")) rc = 1;
 				if (rc) break;
+				// every rank must take the same decision: [hard overflow, list overflow, tile overflow] over all ranks
+				unsigned long long hb = 0;
+				for (int r = 0; r < G.n; ++r) hb |= G.c[r]->h_flags[1];
+				if (c0->comm_mode == 1) {
+					double ovf[3] = {(hb & ~(NL_OVF_LIST_BIT | NL_OVF_TILE_BIT)) ? 1. : 0., (hb & NL_OVF_LIST_BIT) ? 1. : 0., (hb & NL_OVF_TILE_BIT) ? 1. : 0.};
+					if (cudaMemcpyAsync(c0->d_scalars + 12, ovf, 3 * sizeof(double), cudaMemcpyHostToDevice, c0->stream) != cudaSuccess) rc = 1;
+					if (!rc) rc = comm_allreduce(G, COMM_SCALARS, 12, 3, COMM_MAX);
+					if (!rc && cudaMemcpyAsync(ovf, c0->d_scalars + 12, 3 * sizeof(double), cudaMemcpyDeviceToHost, c0->stream) != cudaSuccess) rc = 1;
+					if (!rc && sync_check(c0, "ls1g_run (list build)")) rc = 1;
+					if (rc) break;
+					if (ovf[0] != 0.) hb |= 8;
+					if (ovf[1] != 0.) hb |= NL_OVF_LIST_BIT;
+					if (ovf[2] != 0.) hb |= NL_OVF_TILE_BIT;
+				}
 				{
 					// more neighbours per molecule than the lists hold / a denser neighbourhood than the build tile holds: raise
 					// the capacity and build again (the sort is repeated too - it is idempotent on sorted data)
-					const unsigned long long hb = c->h_flags[1];
 					bool grown = false;
-					if ((hb & NL_OVF_LIST_BIT) && c->list_lcap < NL_LCAP_MAX_H) { c->list_lcap = c->list_lcap * 2 > NL_LCAP_MAX_H ? NL_LCAP_MAX_H : c->list_lcap * 2; grown = true; }
-					else if (hb & NL_OVF_LIST_BIT) grown = false;
-					if ((hb & NL_OVF_TILE_BIT) && c->list_R == 4) { c->list_R = 1; c->build_tcap = 0; grown = true; }      // inhomogeneous rows: single-row blocks
-					else if ((hb & NL_OVF_TILE_BIT) && c->build_tcap < NL_TCAP_MAX_H) { c->build_tcap = c->build_tcap + 1024 > NL_TCAP_MAX_H ? NL_TCAP_MAX_H : c->build_tcap + 1024; grown = true; }
-					const bool fixable = !(hb & ~(NL_OVF_LIST_BIT | NL_OVF_TILE_BIT)) && (!(hb & NL_OVF_LIST_BIT) || c->list_lcap <= NL_LCAP_MAX_H) && grown;
+					int lcap = c0->list_lcap, tcap = c0->build_tcap, R = c0->list_R;
+					if ((hb & NL_OVF_LIST_BIT) && lcap < NL_LCAP_MAX_H) { lcap = lcap * 2 > NL_LCAP_MAX_H ? NL_LCAP_MAX_H : lcap * 2; grown = true; }
+					if ((hb & NL_OVF_TILE_BIT) && R == 4) { R = 1; tcap = 0; grown = true; }      // rows that do not line up in x: single-row blocks
+					else if ((hb & NL_OVF_TILE_BIT) && tcap < NL_TCAP_MAX_H) { tcap = tcap + 1024 > NL_TCAP_MAX_H ? NL_TCAP_MAX_H : tcap + 1024; grown = true; }
+					for (int r = 0; r < G.n; ++r) { G.c[r]->list_lcap = lcap; G.c[r]->build_tcap = tcap; G.c[r]->list_R = R; }
+					const bool fixable = !(hb & ~(NL_OVF_LIST_BIT | NL_OVF_TILE_BIT)) && grown;
 					if (hb && fixable && ++regrow <= 6) {
-						if (dbg) fprintf(stderr, "ls1g: list buffers raised to %d entries per molecule, build tile %d (overflow bits %llu)\n", c->list_lcap, c->build_tcap, hb);
+						if (dbg) fprintf(stderr, "ls1g: list buffers raised to %d entries per molecule, build tile %d, rows per block %d (overflow bits %llu)\n", lcap, tcap, R, hb);
 						continue;
 					}
 				}
-				if (c->h_flags[1]) {                 // tile / list / row capacity exceeded: this system is too dense for the list buffers
-					c->list_disabled = 1; c->in_list_mode = 0; c->track_disp = 0;
-					if (dbg) fprintf(stderr, "ls1g: neighbour lists disabled, overflow bits %llu (1 tile, 2 list, 4 row), bpr %d\n", c->h_flags[1], c->list_bpr);
-					nl_set_bin_grid(c, 0);
+				if (hb) {                 // tile / list / row capacity exceeded: this system is too dense for the list buffers
+					FOR_G(G, c) { c->list_disabled = 1; c->in_list_mode = 0; c->track_disp = 0; nl_set_bin_grid(c, 0); }
+					if (dbg) fprintf(stderr, "ls1g: neighbour lists disabled, overflow bits %llu (1 tile, 2 list, 4 row), bpr %d\n", hb, c0->list_bpr);
 					*done = s;
 					return 0;
 				}
-				c->track_disp = 1;
-				c->n_boundary_blocks = (uint32_t)c->h_flags[3];
-				c->list_zchk = c->h_flags[8] != 0;
-				c->list_tcap = (int)((c->h_flags[2] + 63) & ~63ull);
-				if (c->list_tcap < 64) c->list_tcap = 64;
-				if (dbg) fprintf(stderr, "ls1g: list build at step %d: max tile %llu, bpr %d, slots %zu, bin grid %d %d %d\n", s, c->h_flags[2], c->list_bpr, c->n_slots, c->bgrid.cpd[0], c->bgrid.cpd[1], c->bgrid.cpd[2]);
+				FOR_G(G, c) {
+					c->track_disp = 1;
+					c->n_boundary_blocks = (uint32_t)c->h_flags[3];
+					c->list_zchk = c->h_flags[8] != 0;
+					c->list_tcap = (int)((c->h_flags[2] + 63) & ~63ull);
+					if (c->list_tcap < 64) c->list_tcap = 64;
+				}
+				if (dbg) fprintf(stderr, "ls1g: list build at step %d: max tile %llu, rows per block %d, bpr %d, slots %zu, bin grid %d %d %d\n", s, c0->h_flags[2], c0->list_R, c0->list_bpr, c0->n_slots, c0->bgrid.cpd[0], c0->bgrid.cpd[1], c0->bgrid.cpd[2]);
 				need_build = false; ++rebuilds;
 				t_build += now() - t0;
 			} else if (overlap && fuse_nve && s + 1 < n_steps) {
-				// multi-rank NVE step: the halo positions travel on the communication stream while the inner blocks run
+				// several ranks, NVE step: the halo positions travel on the communication stream while the inner blocks run
 				overlapped = true;
-				if (cudaEventRecord(c->ev_pos, c->stream) != cudaSuccess || cudaStreamWaitEvent(c->stream_comm, c->ev_pos, 0) != cudaSuccess) rc = 1;
-				cudaStream_t main_stream = c->stream;
-				c->stream = c->stream_comm;
-				if (!rc) rc = comm_refresh(c);
-				if (!rc) rc = k_halo_refresh(c);
-				c->stream = main_stream;
-				if (!rc && cudaEventRecord(c->ev_halo, c->stream_comm) != cudaSuccess) rc = 1;
+				FOR_G(G, c) {
+					if (cudaEventRecord(c->ev_pos, c->stream) != cudaSuccess || cudaStreamWaitEvent(c->stream_comm, c->ev_pos, 0) != cudaSuccess) rc = 1;
+					std::swap(c->stream, c->stream_comm);
+				}
+				if (!rc) rc = comm_refresh(G);
+				FOR_G(G, c) {
+					if (!rc) rc = k_halo_refresh(c);
+					std::swap(c->stream, c->stream_comm);
+					if (!rc && cudaEventRecord(c->ev_halo, c->stream_comm) != cudaSuccess) rc = 1;
+				}
 			} else {
-				if (c->n_ranks > 1) rc = comm_refresh(c);
-				if (!rc) rc = k_halo_refresh(c);
+				if (G.multi()) rc = comm_refresh(G);
+				FOR_G(G, c) if (!rc) rc = k_halo_refresh(c);
 			}
 			const double t1 = now();
-			c->guard_on = built ? 0 : 1;
-			if (overlapped) {
-				if (!rc) rc = k_forces_list_fused(c, dt, 1);
-				if (!rc && cudaStreamWaitEvent(c->stream, c->ev_halo, 0) != cudaSuccess) rc = 1;
-				if (!rc) rc = k_forces_list_fused(c, dt, 2);
-				if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s, c->d_scalars, 8 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
-			} else if (fuse_nve && s + 1 < n_steps) {
-				// NVE step that is not the last of the run: forces + post(s) + pre(s + 1) in one kernel
-				if (!rc) rc = k_forces_list_fused(c, dt, 0);
-				if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s, c->d_scalars, 8 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
-			} else if (post_fuse && s + 1 == n_steps) {
-				// last step of the run (or the single step of ls1g_step): forces + post(s) in one kernel, no pre
-				if (!rc) rc = k_forces_list_post(c, dt, want_vi);
-				if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s, c->d_scalars, 8 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
-			} else {
-				if (!rc) rc = k_forces_list(c, s + 1 == n_steps && want_vi);      // pair statistics + per-molecule virial only for the last step
-				if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s, c->d_scalars, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
-				if (!rc) rc = k_post_pre(c, dt, 1, s + 1 < n_steps, thermo, target_T);
-				if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s + 4, c->d_scalars + 4, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
+			FOR_G(G, c) {
+				c->guard_on = built ? 0 : 1;
+				if (overlapped) {
+					if (!rc) rc = k_forces_list_fused(c, dt, 1);
+					if (!rc && cudaStreamWaitEvent(c->stream, c->ev_halo, 0) != cudaSuccess) rc = 1;
+					if (!rc) rc = k_forces_list_fused(c, dt, 2);
+					if (!rc) rc = rec_copy(c, s, 0, 8);
+				} else if (fuse_nve && s + 1 < n_steps) {
+					// NVE step that is not the last of the run: forces + post(s) + pre(s + 1) in one kernel
+					if (!rc) rc = k_forces_list_fused(c, dt, 0);
+					if (!rc) rc = rec_copy(c, s, 0, 8);
+				} else if (post_fuse && s + 1 == n_steps) {
+					// last step of the run (or the single step of ls1g_step): forces + post(s) in one kernel, no pre
+					if (!rc) rc = k_forces_list_post(c, dt, want_vi);
+					if (!rc) rc = rec_copy(c, s, 0, 8);
+				} else {
+					if (!rc) rc = k_forces_list(c, s + 1 == n_steps && want_vi);      // pair statistics + per-molecule virial only for the last step
+					if (!rc) rc = rec_copy(c, s, 0, 4);
+				}
 			}
-			c->guard_on = 0;
-			if (!rc && s + 1 < n_steps) rc = flag_snapshot(c, s % NL_RING);      // decides step s + 1
+			if (!rc && !(overlapped || (fuse_nve && s + 1 < n_steps) || (post_fuse && s + 1 == n_steps))) {
+				rc = g_post_pre(G, dt, 1, s + 1 < n_steps, thermo, target_T);
+				FOR_G(G, c) if (!rc) rc = rec_copy(c, s, 4, 4);
+			}
+			FOR_G(G, c) c->guard_on = 0;
+			if (!rc && s + 1 < n_steps) rc = flag_snapshot(G, s % NL_RING);      // decides step s + 1
 			const double t2 = now();
 			t_enq += t2 - t1; if (t2 - t1 > t_max_enq) t_max_enq = t2 - t1;
 			++s;
 		} else if (chk < s && chk + 1 < n_steps) {
 			// did the steps after chk really run?  step chk + 1 was guarded by the flag step chk wrote
 			const double t2 = now();
-			if (cudaEventSynchronize(c->disp_ev[chk % NL_RING]) != cudaSuccess) { rc = 1; break; }
+			FOR_G(G, c) if (cudaEventSynchronize(c->disp_ev[chk % NL_RING]) != cudaSuccess) rc = 1;
+			if (rc) break;
 			const double t3 = now();
 			t_wait += t3 - t2; if (t3 - t2 > t_max_wait) t_max_wait = t3 - t2;
 			if (expired(chk % NL_RING)) {      // steps chk + 1 .. s - 1 were skipped on the device: rebuild and enqueue them again
@@ -272,13 +337,14 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 			++chk;
 		} else break;
 	}
-	c->guard_on = 0;
-	if (!rc && sync_check(c, "ls1g_run (list steps)")) rc = 1;
-	if (rc) { c->track_disp = 0; c->in_list_mode = 0; nl_set_bin_grid(c, 0); return 1; }
+	FOR_G(G, c) c->guard_on = 0;
+	FOR_G(G, c) if (!rc && sync_check(c, "ls1g_run (list steps)")) rc = 1;
+	if (rc) return fail();
 	if (dbg) fprintf(stderr, "ls1g: %d list steps, %d rebuilds, %d repeated steps; host ms: build %.2f, enqueue %.2f (max %.2f), wait %.2f (max %.2f)\n",
 	                 n_steps, rebuilds, repeats, t_build, t_enq, t_max_enq, t_wait, t_max_wait);
+	FOR_G(G, c) c->list_rebuilds += (uint64_t)rebuilds;
 	// stay in the frozen layout (in_list_mode): the next ls1g_run continues, any other entry point calls ls1g_nl_leave first
-	if (k_drop_halo(c)) return 1;
+	FOR_G(G, c) if (k_drop_halo(c)) return 1;
 	*done = n_steps;
 	return 0;
 }
@@ -286,49 +352,77 @@ static int run_list_steps(ls1g_ctx* c, int n_steps, double dt, int thermo, doubl
 // Device-resident loop.  Per step: pre -> exchange (wrap, images, sort) -> forces (+calcFM) -> post -> thermostat.
 // post(n), the thermostat and pre(n+1) run as one kernel between two force passes.
 // bt, br: betas applied to v, D before the first pre-kick (fused into it); want_vi: per-molecule virial + pair count on the last step.
+// records: [n_steps], sums over the ranks of G (a NCCL rank reports its own part, as the reference's Domain::setLocal* values).
 int k_scale_pre(ls1g_ctx* c, double dt, double bt, double br);
-static int run_impl(ls1g_ctx* c, int n_steps, double dt, double target_T, ls1g_step_record* records, double bt, double br, int want_vi) {
-	if (c->in_list_mode && !nl_applicable(c) && ls1g_nl_leave(c)) return 1;
-	if (!c->forces_valid) LS1G_FAIL("ls1g_run: forces missing - call ls1g_exchange + ls1g_traverse once (prepare_start, Simulation.cpp:813-844)");
+int ls1g_ensure_rec(ls1g_ctx* c, size_t n_steps);
+static int run_impl(const Group& G, int n_steps, double dt, double target_T, ls1g_step_record* records, double bt, double br, int want_vi) {
+	bool lists_ok = true;
+	for (int r = 0; r < G.n; ++r) lists_ok = lists_ok && nl_applicable(G.c[r]);
+	bool in_list = false;
+	for (int r = 0; r < G.n; ++r) in_list = in_list || G.c[r]->in_list_mode;
+	if (in_list && !lists_ok && ls1g_nl_leave_group(G)) return 1;
+	for (int r = 0; r < G.n; ++r)
+		if (!G.c[r]->forces_valid) LS1G_FAIL("ls1g_run: forces missing - call ls1g_exchange + ls1g_traverse once (prepare_start, Simulation.cpp:813-844)");
 	const int thermo = target_T > 0.;
-	double* d_rec = nullptr;
-	if (records) CUDA_TRY(cudaMallocAsync((void**)&d_rec, (size_t)n_steps * 8 * sizeof(double), c->stream));
-	int rc = (bt != 1.0 || br != 1.0) ? k_scale_pre(c, dt, bt, br) : k_post_pre(c, dt, 0, 1, 0, 0.);
+	int rc = 0;
+	FOR_G(G, c) {
+		if (!rc && records) rc = ls1g_ensure_rec(c, (size_t)n_steps);
+		if (!records) { /* no records wanted: the kernels still reduce the step scalars, nothing is kept */ }
+		if (!rc) rc = (bt != 1.0 || br != 1.0) ? k_scale_pre(c, dt, bt, br) : k_post_pre(c, dt, 0, 1, 0, 0.);
+	}
+	std::vector<double*> keep(G.n);
+	for (int r = 0; r < G.n; ++r) { keep[r] = G.c[r]->d_rec; if (!records) G.c[r]->d_rec = nullptr; }      // rec_copy tests d_rec
 	int s0 = 0;
-	if (!rc && nl_applicable(c)) rc = run_list_steps(c, n_steps, dt, thermo, target_T, d_rec, &s0, want_vi);
+	if (!rc && lists_ok) rc = run_list_steps(G, n_steps, dt, thermo, target_T, &s0, want_vi);
 	for (int s = s0; s < n_steps && !rc; ++s) {
-		c->sorted = 0;
-		c->forces_valid = 0;     // F is recomputed before its next use: do not carry it through the sort
-		rc = c->n_ranks > 1 ? comm_exchange(c) : k_sort(c, 1);
-		c->forces_valid = 1;
-		if (!rc) rc = k_forces(c);
-		if (!rc) rc = k_drop_halo(c);
-		if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s, c->d_scalars, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
-		if (!rc) rc = k_post_pre(c, dt, 1, s + 1 < n_steps, thermo, target_T);
-		if (!rc && d_rec && cudaMemcpyAsync(d_rec + 8 * (size_t)s + 4, c->d_scalars + 4, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
+		FOR_G(G, c) { c->sorted = 0; c->forces_valid = 0; }     // F is recomputed before its next use: do not carry it through the sort
+		rc = G.multi() ? comm_exchange(G) : k_sort(G.c[0], 1);
+		FOR_G(G, c) {
+			c->forces_valid = 1;
+			if (!rc) rc = k_forces(c);
+			if (!rc) rc = k_drop_halo(c);
+			if (!rc && c->d_rec && cudaMemcpyAsync(c->d_rec + 8 * (size_t)s, c->d_scalars, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
+		}
+		if (!rc) rc = g_post_pre(G, dt, 1, s + 1 < n_steps, thermo, target_T);
+		FOR_G(G, c)
+			if (!rc && c->d_rec && cudaMemcpyAsync(c->d_rec + 8 * (size_t)s + 4, c->d_scalars + 4, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
 	}
-	std::vector<double> h;
-	if (!rc && d_rec) {
-		h.resize((size_t)n_steps * 8);
-		if (cudaMemcpyAsync(h.data(), d_rec, h.size() * sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess) rc = 1;
+	std::vector<std::vector<double>> h(G.n);
+	FOR_G(G, c) {
+		if (!rc && c->d_rec) {
+			h[_r].resize((size_t)n_steps * 8);
+			if (cudaMemcpyAsync(h[_r].data(), c->d_rec, h[_r].size() * sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess) rc = 1;
+		}
 	}
-	if (d_rec) cudaFreeAsync(d_rec, c->stream);
-	if (rc) { cudaStreamSynchronize(c->stream); return 1; }
-	if (sync_check(c, "ls1g_run")) return 1;
+	for (int r = 0; r < G.n; ++r) G.c[r]->d_rec = keep[r];
+	if (rc) { FOR_G(G, c) cudaStreamSynchronize(c->stream); return 1; }
+	FOR_G(G, c) if (sync_check(c, "ls1g_run")) return 1;
 	if (records)
 		for (int s = 0; s < n_steps; ++s) {
-			const double* r = &h[(size_t)s * 8];
-			records[s].upot = r[0]; records[s].virial = r[1]; records[s].summv2 = r[4]; records[s].sumIw2 = r[5];
-			records[s].n = (uint64_t)llround(r[6]); records[s].rot_dof = (uint64_t)llround(r[7]);
-			c->last_pairs = (uint64_t)llround(r[2]);
+			double t[8] = {0., 0., 0., 0., 0., 0., 0., 0.};
+			for (int r = 0; r < G.n; ++r) for (int k = 0; k < 8; ++k) t[k] += h[r][(size_t)s * 8 + k];
+			records[s].upot = t[0]; records[s].virial = t[1]; records[s].summv2 = t[4]; records[s].sumIw2 = t[5];
+			records[s].n = (uint64_t)llround(t[6]); records[s].rot_dof = (uint64_t)llround(t[7]);
+			for (int r = 0; r < G.n; ++r) G.c[r]->last_pairs = (uint64_t)llround(h[r][(size_t)s * 8 + 2]);
 		}
+	return 0;
+}
+
+static int check_run_group(ls1g_ctx** ctxs, int n, const char* who) {
+	if (!ctxs || n < 1) LS1G_FAIL(std::string(who) + ": bad arguments");
+	for (int r = 0; r < n; ++r) if (!ctxs[r]) LS1G_FAIL(std::string(who) + ": null context");
+	if (n == 1) return 0;
+	for (int r = 0; r < n; ++r)
+		if (ctxs[r]->comm_mode != 2 || (int)ctxs[r]->peers.size() != n || ctxs[r]->peers[r] != ctxs[r]) LS1G_FAIL(std::string(who) + ": call ls1g_comm_init_local with exactly these contexts first");
 	return 0;
 }
 
 extern "C" int ls1g_run(ls1g_ctx* c, int n_steps, double dt, double target_T, ls1g_step_record* records) {
 	NEED(c);
 	if (n_steps <= 0) return 0;
-	return run_impl(c, n_steps, dt, target_T, records, 1.0, 1.0, 1);
+	if (c->comm_mode == 2) LS1G_FAIL("ls1g_run: the ranks of a local group step together (ls1g_run_group)");
+	Group G{&c, 1};
+	return run_impl(G, n_steps, dt, target_T, records, 1.0, 1.0, 1);
 }
 
 // One time step for a host-driven loop: VelocityScalingThermostat::apply(beta_trans, beta_rot) of the PREVIOUS step fused into
@@ -336,7 +430,33 @@ extern "C" int ls1g_run(ls1g_ctx* c, int n_steps, double dt, double target_T, ls
 // (Domain::calculateGlobalValues), so the reference's own thermostat logic stays in charge.
 extern "C" int ls1g_step(ls1g_ctx* c, double dt, double beta_trans, double beta_rot, int flags, ls1g_step_record* record) {
 	NEED(c);
-	return run_impl(c, 1, dt, -1., record, beta_trans, beta_rot, (flags & LS1G_STEP_VI) ? 1 : 0);
+	if (c->comm_mode == 2) LS1G_FAIL("ls1g_step: the ranks of a local group step together (ls1g_step_group)");
+	Group G{&c, 1};
+	return run_impl(G, 1, dt, -1., record, beta_trans, beta_rot, (flags & LS1G_STEP_VI) ? 1 : 0);
+}
+
+extern "C" int ls1g_run_group(ls1g_ctx** ctxs, int n, int n_steps, double dt, double target_T, ls1g_step_record* records) {
+	if (check_run_group(ctxs, n, "ls1g_run_group")) return 1;
+	if (n_steps <= 0) return 0;
+	if (n == 1) return ls1g_run(ctxs[0], n_steps, dt, target_T, records);
+	Group G{ctxs, n};
+	return run_impl(G, n_steps, dt, target_T, records, 1.0, 1.0, 1);
+}
+
+extern "C" int ls1g_step_group(ls1g_ctx** ctxs, int n, double dt, double beta_trans, double beta_rot, int flags, ls1g_step_record* record) {
+	if (check_run_group(ctxs, n, "ls1g_step_group")) return 1;
+	if (n == 1) return ls1g_step(ctxs[0], dt, beta_trans, beta_rot, flags, record);
+	Group G{ctxs, n};
+	return run_impl(G, 1, dt, -1., record, beta_trans, beta_rot, (flags & LS1G_STEP_VI) ? 1 : 0);
+}
+
+int ls1g_ensure_rec(ls1g_ctx* c, size_t n_steps) {
+	if (c->d_rec && c->d_rec_cap >= n_steps) return 0;
+	cudaFree(c->d_rec); c->d_rec = nullptr; c->d_rec_cap = 0;
+	const size_t cap = n_steps < 1024 ? 1024 : n_steps;
+	CUDA_TRY(cudaMalloc((void**)&c->d_rec, cap * 8 * sizeof(double)));
+	c->d_rec_cap = cap;
+	return 0;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -409,6 +529,15 @@ extern "C" int ls1g_rdf(ls1g_ctx* c, const ls1g_rdf_params* p, uint64_t* mol, ui
 extern "C" int ls1g_measure_fp64_peak(int device, double* tflops) {
 	if (!tflops) LS1G_FAIL("null argument");
 	return k_fp64_peak(device, tflops);
+}
+
+extern "C" int ls1g_list_stats(ls1g_ctx* c, uint64_t* rebuilds, int* rows_per_block, int* entries_per_molecule, double* skin) {
+	if (!c) LS1G_FAIL("null context");
+	if (rebuilds) *rebuilds = c->list_rebuilds;
+	if (rows_per_block) *rows_per_block = c->list_R;
+	if (entries_per_molecule) *entries_per_molecule = c->list_lcap;
+	if (skin) *skin = c->skin;
+	return 0;
 }
 
 extern "C" int ls1g_last_pair_count(ls1g_ctx* c, uint64_t* pairs) {

@@ -565,6 +565,126 @@ def test_decomposed_matches_single_rank(n_ranks, case):
     assert np.all(np.abs(rec[:, :4] - ref_rec[:, :4]) <= 100 * tol * np.maximum(np.abs(ref_rec[:, :4]).max(axis=0), 1e-300))
 
 
+def _group_of_ranks(n_ranks, box, rc, ids, r, v, capacity):
+    ranks = []
+    for rank in range(n_ranks):
+        grid, coords = ls1g.decomp_grid(n_ranks, rank)
+        bmin, bmax = ls1g.decomp_box(grid, coords, box)
+        c = ls1g.Container(bmax, rc, box_min=bmin, global_length=box, rank_grid=grid, rank_coords=coords, capacity=capacity)
+        c.set_components([ls1g.lj_component()])
+        mine = np.all((r >= np.array(bmin)) & (r < np.array(bmax)), axis=1)
+        c.add_particles(ids[mine], np.zeros(int(mine.sum()), dtype=np.uint32), r[mine], v[mine])
+        ranks.append(c)
+    ls1g.comm_init_local(ranks)
+    ls1g.exchange_group(ranks)
+    for c in ranks:
+        c.traverse_cells()
+    return ranks
+
+
+def _run_group_case(n_ranks, box, rc, ids, r, v, steps, dt):
+    ranks = _group_of_ranks(n_ranks, box, rc, ids, r, v, capacity=4 * len(ids) + 4096)
+    try:
+        rec = ls1g.run_group(ranks, steps, dt)
+        stats = ranks[0].list_stats()
+        parts = [c.download(("id", "r", "v", "F")) for c in ranks]      # leaves the list layout: one exchange of the whole group
+    finally:
+        for c in ranks:
+            c.close()
+    return rec, by_id({k: np.concatenate([p[k] for p in parts]) for k in parts[0]}), stats
+
+
+@pytest.mark.parametrize("n_ranks", [2, 4, 8])
+def test_group_list_loop_matches_oracle(n_ranks, monkeypatch):
+    """The code path the multi-GPU bench times - neighbour lists over a block decomposition: two-pass build exchange, persistent
+    halo lists refreshed every step, two-phase force launch overlapped with the refresh, guarded speculative steps, rebuilds agreed on
+    the all-reduced displacement - driven here through the in-process transport (all ranks are contexts on this GPU; only the
+    ncclSend/ncclRecv calls are replaced by event-ordered copies).  Held to the CPU oracle's trajectory of the same global system
+    (per-step upot, virial, kinetic sums; final r, v, F), 72 steps with several rebuilds; overlap on and off are bitwise equal."""
+    r, v, box = fcc_lattice(12, seed=6, temperature=2.0)
+    rng = np.random.default_rng(8)
+    r = np.mod(r + rng.normal(scale=0.05, size=r.shape), box)
+    n = len(r)
+    ids, cid = np.arange(n), np.zeros(n, dtype=np.uint32)
+    steps, dt, rc = 72, 0.004, 2.5
+    sysm = O.System.single_lj(rc=rc)
+    g = O.grid([0, 0, 0], box, rc, 0)
+    q = np.tile([1.0, 0, 0, 0], (n, 1))
+    f0 = _oracle_forces(sysm, g, box, cid, r, q)
+    ref = O.run(sysm, g, box, cid, r, v, q, np.zeros((n, 3)), f0["F"], np.zeros((n, 3)), steps, dt)
+    out = {}
+    for overlap in ("1", "0"):
+        monkeypatch.setenv("LS1G_OVERLAP", overlap)
+        out[overlap] = _run_group_case(n_ranks, box, rc, ids, r, v, steps, dt)
+    rec, st, stats = out["1"]
+    assert stats["rebuilds"] >= 3, stats                              # the first build and at least two displacement-triggered ones
+    assert np.all(rec[:, 4] == n)
+    ser = ref["series"]
+    assert np.all(np.abs(rec[:, :3] - ser[:, :3]) <= 1e-9 * np.abs(ser[:, :3]).max(axis=0)), np.abs(rec[:, :3] - ser[:, :3]).max(axis=0)
+    order = np.argsort(ids)
+    dr = np.abs(st["r"] - ref["r"][order])
+    dr = np.minimum(dr, np.abs(dr - np.asarray(box)))                 # a molecule exactly on the periodic boundary may sit on either side
+    assert dr.max() < 1e-9 and np.abs(st["v"] - ref["v"][order]).max() < 1e-8
+    assert vec_rel_err(st["F"], ref["F"][order]) < 1e-6                # trajectory divergence over 72 steps, not arithmetic
+    rec0, st0, _ = out["0"]
+    assert np.array_equal(rec, rec0)
+    for k in ("id", "r", "v", "F"):
+        assert np.array_equal(st[k], st0[k]), k
+
+
+@pytest.mark.parametrize("skin", ["0.04", "0.11"])
+def test_group_list_loop_with_lists_expiring_in_flight(skin, monkeypatch):
+    """Lists that expire every two to four steps while up to three guarded steps are already enqueued: the skipped steps (odd and even
+    counts; the fused kernel swaps the position buffers on every launch, skipped or not) are repeated after the rebuild.  Same pairs
+    and the same trajectory as the rebuild-every-step loop of the same group (LS1G_SKIN=0), and as a single rank."""
+    r, v, box = fcc_lattice(12, seed=16, temperature=3.0)
+    n = len(r)
+    ids = np.arange(n)
+    steps, dt, rc = 40, 0.004, 2.5
+    res = {}
+    for sk in ("0", skin):
+        monkeypatch.setenv("LS1G_SKIN", sk)
+        res[sk] = _run_group_case(4, box, rc, ids, r, v, steps, dt)
+    with ls1g.Container(box, rc) as c:                                  # single rank, lists with the same small skin
+        c.set_components([ls1g.lj_component()])
+        c.add_particles(ids, np.zeros(n, dtype=np.uint32), r, v)
+        c.exchange()
+        c.traverse_cells()
+        rec1 = c.run(steps, dt)
+        st1 = by_id(c.download(("id", "r", "v", "F")))
+        single_stats = c.list_stats()
+    rec, st, stats = res[skin]
+    rec0, st0, stats0 = res["0"]
+    assert stats0["rebuilds"] == 0 and stats["rebuilds"] >= steps // 5 and single_stats["rebuilds"] >= steps // 5, (stats0, stats, single_stats)
+    for other_rec, other_st in ((rec0, st0), (rec1, st1)):
+        assert np.all(np.abs(rec - other_rec) <= 1e-9 * np.maximum(np.abs(other_rec).max(axis=0), 1e-300))
+        for k in ("r", "v"):
+            assert np.abs(st[k] - other_st[k]).max() <= 1e-9 * np.abs(other_st[k]).max(), k
+        assert np.array_equal(st["id"], other_st["id"])
+
+
+def test_group_thermostat_uses_the_global_kinetic_sums():
+    """NVT on a local group: the betas come from the all-reduced sums (Domain::calculateGlobalValues collComm, Domain.cpp:170-176),
+    so the decomposed run follows the single-rank one"""
+    r, v, box = fcc_lattice(12, seed=3, temperature=1.0)
+    n = len(r)
+    ids = np.arange(n)
+    with ls1g.Container(box, 2.5) as c:
+        c.set_components([ls1g.lj_component()])
+        c.add_particles(ids, np.zeros(n, dtype=np.uint32), r, v)
+        c.exchange()
+        c.traverse_cells()
+        ref = c.run(30, 0.002, target_temperature=1.3)
+    ranks = _group_of_ranks(4, box, 2.5, ids, r, v, capacity=4 * n + 4096)
+    try:
+        rec = ls1g.run_group(ranks, 30, 0.002, target_temperature=1.3)
+    finally:
+        for c in ranks:
+            c.close()
+    assert np.all(rec[:, 4] == n)
+    assert np.all(np.abs(rec[:, :3] - ref[:, :3]) <= 1e-9 * np.abs(ref[:, :3]).max(axis=0))
+
+
 @pytest.mark.parametrize("n_ranks", [2, 8])
 @pytest.mark.parametrize("case", ["1clj", "ex_CO2"])
 def test_rdf_decomposed_sums_to_single_rank(n_ranks, case):
