@@ -113,6 +113,15 @@ int ls1g_get_grid(const ls1g_ctx* ctx, int cells_per_dim[3], double cell_length[
 int ls1g_cell_index_of_points_host(const ls1g_ctx* ctx, size_t n, const double* points, uint32_t* out);
 /* same on the device (the kernel the sort uses) */
 int ls1g_cell_index_of_points(ls1g_ctx* ctx, size_t n, const double* points, uint32_t* out);
+/* NO counterpart in the reference: added for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same kernel and same result as
+ * ls1g_cell_index_of_points, but the call allocates and frees NOTHING: the device staging of `points` and of the result is a fixed
+ * file-scope __device__ array (1.75 MiB, held by every GPU that loads the library until the process exits).
+ * n > LS1G_NOALLOC_MAX_POINTS is rejected with an error.  The array is shared by every call and every context of a device and keeps
+ * the last call's contents (nothing in it needs clearing: each call overwrites and reads back exactly [0, n)); calls that overlap on
+ * the GPU race on it, so callers serialise. */
+#define LS1G_NOALLOC_MAX_POINTS 65536
+int ls1g_cell_index_of_points_noalloc(ls1g_ctx* ctx, size_t n, const double* points, uint32_t* out);
 /* replaces: C08CellPairTraversal::traverseCellPairs + C08BasedTraversals::processBaseCell
  * (C08CellPairTraversal.h:50-80, C08BasedTraversals.h:48-102): emits (cell1, cell2, kind) triplets,
  * kind 0 = processCell, 1 = processCellPair, in colour/base-cell order.  pairs may be NULL to count. */

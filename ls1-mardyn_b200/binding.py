@@ -20,7 +20,7 @@ EXPORTS = [
     "ls1g_integrate_pre", "ls1g_integrate_post", "ls1g_scale", "ls1g_selective_thermostat", "ls1g_run", "ls1g_step", "ls1g_host_alloc", "ls1g_host_free", "ls1g_decomp_box", "ls1g_decomp_grid",
     "ls1g_comm_unique_id", "ls1g_comm_init", "ls1g_allreduce_sum", "ls1g_comm_init_local", "ls1g_exchange_group",
     "ls1g_timers", "ls1g_measure_fp64_peak", "ls1g_last_pair_count", "ls1g_flop_count", "ls1g_rdf", "ls1g_reserve", "ls1g_download_range", "ls1g_slot_count",
-    "ls1g_run_group", "ls1g_step_group", "ls1g_list_stats",
+    "ls1g_run_group", "ls1g_step_group", "ls1g_list_stats", "ls1g_cell_index_of_points_noalloc",
 ]
 
 FIELDS = dict(id=1, cid=2, r=4, v=8, q=16, L=32, F=64, M=128, Vi=256, cell=512)
@@ -249,6 +249,15 @@ class Container:
         out = np.empty(len(pts), dtype=np.uint32)
         f = lib().ls1g_cell_index_of_points_host if host else lib().ls1g_cell_index_of_points
         _chk(f(self._ctx, C.c_size_t(len(pts)), _p(pts), _p(out)))
+        return out
+
+    NOALLOC_MAX_POINTS = 65536      # LS1G_NOALLOC_MAX_POINTS
+
+    def cell_index_of_points_noalloc(self, pts):
+        """ls1g_cell_index_of_points_noalloc: same kernel, device staging in a fixed __device__ array (no cudaMalloc in the call)"""
+        pts = np.ascontiguousarray(pts, dtype=np.float64).reshape(-1, 3)
+        out = np.empty(len(pts), dtype=np.uint32)
+        _chk(lib().ls1g_cell_index_of_points_noalloc(self._ctx, C.c_size_t(len(pts)), _p(pts), _p(out)))
         return out
 
     def cell_pairs(self):

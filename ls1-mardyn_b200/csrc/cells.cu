@@ -297,6 +297,50 @@ int k_cell_index(ls1g_ctx* c, size_t n, const double* d_pts, uint32_t* d_out) {
 	return 0;
 }
 
+// ------------------------------------------------------------------------------------------------
+// ls1g_cell_index_of_points_noalloc: the same cell_index_kernel as ls1g_cell_index_of_points, for callers that cannot call
+// cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  No counterpart in the reference.
+// The device staging of the points and of the result - which the ordinary entry point
+// cudaMallocs and frees on every call - lives in a file-scope __device__ array of fixed size: every GPU that loads the library
+// holds these 1.75 MiB until the process exits.  The array is SHARED by all calls and all contexts of a device and keeps the
+// contents of the last call: nothing in it has to start at zero (the copy overwrites points [0, n), the kernel writes every
+// result [0, n), only those are read back), but two calls that overlap on the GPU (different contexts/streams, different
+// threads) race on it - callers serialise.
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol, never a device address: its address comes from
+// cudaGetSymbolAddress, asked once per device with that device current.
+// ------------------------------------------------------------------------------------------------
+#define NOALLOC_PTS_BYTES ((size_t)LS1G_NOALLOC_MAX_POINTS * 3 * sizeof(double))       // 1 572 864: a multiple of 256
+#define NOALLOC_BYTES (NOALLOC_PTS_BYTES + (size_t)LS1G_NOALLOC_MAX_POINTS * sizeof(uint32_t))
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_BYTES];
+#define NOALLOC_MAX_DEVICES 64
+static unsigned char* g_noalloc_addr[NOALLOC_MAX_DEVICES];      // device address of the array on device d (0 = not asked yet)
+
+extern "C" int ls1g_cell_index_of_points_noalloc(ls1g_ctx* c, size_t n, const double* pts, uint32_t* out) {
+	if (!c) LS1G_FAIL("null context");
+	if (n > (size_t)LS1G_NOALLOC_MAX_POINTS)
+		LS1G_FAIL("ls1g_cell_index_of_points_noalloc: " + std::to_string(n) + " points exceed the fixed scratch of LS1G_NOALLOC_MAX_POINTS = " +
+		          std::to_string(LS1G_NOALLOC_MAX_POINTS) + " (split the call, or use ls1g_cell_index_of_points)");
+	if (n == 0) return 0;
+	if (!pts || !out) LS1G_FAIL("ls1g_cell_index_of_points_noalloc: null argument");
+	const int dev = c->cfg.device;
+	if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) LS1G_FAIL("ls1g_cell_index_of_points_noalloc: device ordinal out of range");
+	CUDA_TRY(cudaSetDevice(dev));
+	if (!g_noalloc_addr[dev]) {          // set-up, once per device, with that device current
+		unsigned char* p = nullptr;
+		CUDA_TRY(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+		if (!p) LS1G_FAIL("ls1g_cell_index_of_points_noalloc: cudaGetSymbolAddress returned a null address");
+		g_noalloc_addr[dev] = p;
+	}
+	double* d_p = (double*)g_noalloc_addr[dev];
+	uint32_t* d_o = (uint32_t*)(g_noalloc_addr[dev] + NOALLOC_PTS_BYTES);
+	CUDA_TRY(cudaMemcpyAsync(d_p, pts, n * 3 * sizeof(double), cudaMemcpyHostToDevice, c->stream));
+	if (k_cell_index(c, n, d_p, d_o)) return 1;
+	CUDA_TRY(cudaMemcpyAsync(out, d_o, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+	cudaError_t e = cudaStreamSynchronize(c->stream);
+	if (e != cudaSuccess) { ls1g_set_error(std::string("cell index kernel (noalloc): ") + cudaGetErrorString(e)); return 1; }
+	return 0;
+}
+
 // exclusive scan over the n_cells entries of `in` -> out[0..n_cells]; the total also lands in d_counters[0]
 int ls1g_scan_cells(ls1g_ctx* c, const uint32_t* in, uint32_t* out) {
 	const int nc = c->bgrid.n_cells;
