@@ -176,6 +176,7 @@ extern "C" int ls1g_create(const ls1g_config* cfg, ls1g_ctx** out) {
 	c->bgrid = c->grid;
 	{ const char* e = getenv("LS1G_VI_EVERY_STEP"); c->vi_every_step = e && atoi(e) != 0; }
 	{ const char* lr = getenv("LS1G_LIST_ROWS"); c->list_R = lr && atoi(lr) == 1 ? 1 : 4; }
+	{ const char* lp = getenv("LS1G_LIST_PERMUTE"); c->list_permute = lp && atoi(lp) == 0 ? 0 : 1; }
 	{ const char* sk = getenv("LS1G_SKIN"); c->skin = sk ? atof(sk) : 0.12 * c->cfg.cutoff; if (c->skin < 0.) c->skin = 0.; }
 	c->rc2 = c->cfg.cutoff * c->cfg.cutoff;
 	c->rclj2 = c->cfg.lj_cutoff * c->cfg.lj_cutoff;
@@ -234,7 +235,7 @@ extern "C" int ls1g_destroy(ls1g_ctx* c) {
 	if (c->ev_ar) cudaEventDestroy(c->ev_ar);
 	cudaFree(c->d_rec);
 	if (c->stream_comm) cudaStreamDestroy(c->stream_comm);
-	cudaFree(c->bmap); cudaFree(c->bflag);
+	cudaFree(c->bmap); cudaFree(c->bflag); cudaFree(c->plans);
 	if (c->stream) cudaStreamDestroy(c->stream);
 	delete c;
 	return 0;

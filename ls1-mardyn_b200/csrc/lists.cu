@@ -4,6 +4,7 @@
 #include "lists.cuh"
 
 #include <math.h>
+#include <stdlib.h>
 #include <algorithm>
 #include <string.h>
 
@@ -32,7 +33,7 @@ int nl_set_bin_grid(ls1g_ctx* c, int list_mode) {
 static NLArgs nl_args(ls1g_ctx* c) {
 	NLArgs a;
 	a.g = c->bgrid; a.pos = c->cur.pos; a.cell = c->cur.cell; a.cell_start = c->cell_start;
-	a.lists = c->lists; a.lcount = c->lcount; a.flags = c->d_flags; a.bpr = c->list_bpr; a.nyi = c->bgrid.cpd[1] - 2; a.lcap4 = c->list_lcap / 4; a.btcap = c->build_tcap;
+	a.lists = c->lists; a.lcount = c->lcount; a.plans = (NLPlan*)c->plans; a.flags = c->d_flags; a.bpr = c->list_bpr; a.nyi = c->bgrid.cpd[1] - 2; a.lcap4 = c->list_lcap / 4; a.btcap = c->build_tcap;
 	a.nzi = c->bgrid.cpd[2] - 2; a.nyg = (a.nyi + 1) / 2;
 	a.tcap = NL_TCAP;
 	const double rl = c->cfg.lj_cutoff + c->skin;
@@ -70,6 +71,10 @@ static int nl_force_attrs(const ls1g_ctx* c) {
 	if (d < 64 && (done_mask >> d & 1ull)) return 0;
 	CUDA_TRY(cudaFuncSetAttribute(nl_build_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, NL_BUILD_SMEM(1, NL_TCAP)));
 	CUDA_TRY(cudaFuncSetAttribute(nl_build_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, NL_BUILD_SMEM(4, NL_TCAP)));
+	CUDA_TRY((cudaFuncSetAttribute(nl_permute_kernel<128, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NL_PERM_SMEM(128, 128))));
+	CUDA_TRY((cudaFuncSetAttribute(nl_permute_kernel<256, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NL_PERM_SMEM(256, 128))));
+	CUDA_TRY((cudaFuncSetAttribute(nl_permute_kernel<512, 64>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NL_PERM_SMEM(512, 64))));
+	CUDA_TRY((cudaFuncSetAttribute(nl_permute_kernel<1024, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NL_PERM_SMEM(1024, 32))));
 	CUDA_TRY((nl_attr<true, true, 0>()));
 	CUDA_TRY((nl_attr<true, false, 0>()));
 	CUDA_TRY((nl_attr<false, false, 0>()));
@@ -120,6 +125,8 @@ int k_list_build(ls1g_ctx* c) {
 	}
 	if (!c->pos_build) CUDA_TRY(cudaMalloc((void**)&c->pos_build, c->cap * sizeof(double4)));
 	if (nb > c->bmap_cap) {
+		cudaFree(c->plans); c->plans = nullptr;
+		CUDA_TRY(cudaMalloc((void**)&c->plans, nb * sizeof(NLPlan)));
 		cudaFree(c->bmap); cudaFree(c->bflag); c->bmap = nullptr; c->bflag = nullptr; c->bmap_cap = 0;
 		CUDA_TRY(cudaMalloc((void**)&c->bmap, nb * sizeof(uint32_t)));
 		CUDA_TRY(cudaMalloc((void**)&c->bflag, nb));
@@ -132,13 +139,23 @@ int k_list_build(ls1g_ctx* c) {
 	CUDA_TRY(cudaMemcpyAsync(c->alt.pos, c->cur.pos, c->n_slots * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));   // fused steps ping-pong cur.pos / alt.pos
 	NLArgs a = nl_args(c);
 	if (nl_force_attrs(c)) return 1;
+	CUDA_TRY(cudaMemsetAsync(c->lcount, 0, nb * nl_bt(c) * sizeof(uint32_t), c->stream));      // lanes without a molecule: empty lists
 	if (c->list_R == 4) nl_build_kernel<4><<<(unsigned)nb, NLGeom<4>::BT, NL_BUILD_SMEM(4, a.btcap), c->stream>>>(a);
 	else nl_build_kernel<1><<<(unsigned)nb, NLGeom<1>::BT, NL_BUILD_SMEM(1, a.btcap), c->stream>>>(a);
 	CUDA_TRY(cudaGetLastError());
+	if (c->list_permute) {      // bank-aware order of every list (lists.cuh: nl_permute_kernel)
+		const size_t lanes = nb * nl_bt(c);
+		const int bt = (int)nl_bt(c);
+		if (c->list_lcap <= 128) nl_permute_kernel<128, 128><<<nblk(lanes, 128), 128, NL_PERM_SMEM(128, 128), c->stream>>>(c->lists, c->lcount, a.lcap4, bt, lanes);
+		else if (c->list_lcap <= 256) nl_permute_kernel<256, 128><<<nblk(lanes, 128), 128, NL_PERM_SMEM(256, 128), c->stream>>>(c->lists, c->lcount, a.lcap4, bt, lanes);
+		else if (c->list_lcap <= 512) nl_permute_kernel<512, 64><<<nblk(lanes, 64), 64, NL_PERM_SMEM(512, 64), c->stream>>>(c->lists, c->lcount, a.lcap4, bt, lanes);
+		else nl_permute_kernel<1024, 32><<<nblk(lanes, 32), 32, NL_PERM_SMEM(1024, 32), c->stream>>>(c->lists, c->lcount, a.lcap4, bt, lanes);
+		CUDA_TRY(cudaGetLastError());
+	}
 	CUDA_TRY(cudaMemcpyAsync(c->h_flags, c->d_flags, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
 	CUDA_TRY(cudaMemcpyAsync(c->h_flags + 3, c->d_flags + 5, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));   // read by the caller after its sync
 	CUDA_TRY(cudaMemcpyAsync(c->h_flags + 8, c->d_flags + 6, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));   // near-pair flag
-	timer_stop(c, LS1G_T_SORT, 2);
+	timer_stop(c, LS1G_T_SORT, 2 + (c->list_permute ? 1 : 0));
 	return 0;
 }
 

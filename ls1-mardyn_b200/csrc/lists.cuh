@@ -41,12 +41,15 @@
 #define NL_LCAP_MAX 1020   // lcount packs quad counts in 16 bits
 #define NL_DUMMY 4         // dummy entries at the start of the tile (keeps real entries 4-aligned)
 #define NL_MAXROWS 16
-#define NL_BUNDLE_FILL 508 // R = 4: molecules per block a bundle is cut for (4 rows x integer rounding stay within 512 threads)
-#define NL_XSPAN 8         // R = 4: a block spans at most about this many cells in x (bundles at the upper faces hold fewer than 4 rows)
+#ifndef NL_R4_BT
+#define NL_R4_BT 512       // R = 4: threads per block
+#endif
+#define NL_BUNDLE_FILL (NL_R4_BT - 4) // R = 4: molecules per block a bundle is cut for (4 rows x integer rounding stay within the block)
+#define NL_XSPAN (NL_R4_BT / 64)      // R = 4: a block spans at most about this many cells in x (bundles at the upper faces hold fewer than 4 rows)
 
 template <int R> struct NLGeom;
 template <> struct NLGeom<1> { static constexpr int BT = NL_BT, NR = 9, ROWS_A = 3, QCAP = 64; };
-template <> struct NLGeom<4> { static constexpr int BT = 4 * NL_BT, NR = 16, ROWS_A = 8, QCAP = 32; };
+template <> struct NLGeom<4> { static constexpr int BT = NL_R4_BT, NR = 16, ROWS_A = 8, QCAP = NL_R4_BT >= 512 ? 32 : 64; };
 
 // R = 1: staging / scan order of the 9 neighbour rows (r = 3*(dz+1) + (dy+1)): own row first, then point-symmetric pairs
 __device__ __constant__ int NL_ORD[9] = {4, 0, 8, 1, 7, 3, 5, 2, 6};
@@ -57,6 +60,7 @@ struct NLArgs {
 	Grid g;                     // bin grid
 	const double4* pos; const uint32_t* cell; const uint32_t* cell_start;
 	unsigned short* lists; uint32_t* lcount;
+	struct NLPlan* plans;       // [blocks] the plan of every block as the build kernel computed it (the layout is frozen until the next build)
 	unsigned long long* flags;  // [1] |= NL_OVF_*
 	int bpr;                    // blocks per row (R = 4: per row bundle)
 	int lcap4;                  // list capacity per molecule in units of 4 entries
@@ -216,6 +220,8 @@ __global__ void __launch_bounds__(NLGeom<R>::BT) nl_build_kernel(NLArgs a) {
 		a.bflag[blockIdx.x] = P.boundary ? 1 : 0;
 		if (P.boundary) a.bmap[atomicAdd(a.flags + 5, 1ull)] = blockIdx.x;
 	}
+	// the force kernel loads the plan instead of re-deriving it (three dependent global loads behind three barriers)
+	if (tid < (int)(sizeof(NLPlan) / 4)) ((uint32_t*)(a.plans + blockIdx.x))[tid] = ((const uint32_t*)&P)[tid];
 	if (!P.live) return;
 	if (tid == 0) {      // largest tile of this build: sizes the force kernel's shared memory
 		const int m = P.off[NR] + NL_DUMMY;
@@ -318,6 +324,96 @@ __global__ void __launch_bounds__(NLGeom<R>::BT) nl_build_kernel(NLArgs a) {
 }
 
 // ---------------------------------------------------------------------------------------------------------------
+// permute: bank-aware order of every molecule's list
+// ---------------------------------------------------------------------------------------------------------------
+// The force kernel reads one tile entry per lane and list position: a random 8-byte (Z) and 16-byte (XY) shared-memory read per
+// lane.  In tile order these cost ~13 wavefronts per warp and position (conflict-free: 6), and the shared-memory pipe, not the FP64
+// pipe, bounds the kernel (ncu: 80 % busy, profiles/r02a_ncu_nl_force_bundled_10M_summary.csv).  The ORDER of a molecule's list is
+// free, so after the build every lane re-orders its entries: at list position t lane l wants an entry whose tile index is
+// = (l + t) mod 16 - then the 16 lanes of a half-warp hit 16 different 8-byte banks of Z and the 8 lanes of a quarter-warp 8
+// different 16-byte banks of XY.  Greedy per lane: the wanted residue if the lane still has such an entry, else the residue 8
+// further (keeps XY conflict-free), else from its fullest bucket.  ~7.9 wavefronts per position on a liquid (simulation), i.e. below
+// the 10 SM-cycles the FP64 pipe needs.  Entries of staging batch A stay in front of the others (lcount's second field), the pad
+// entries at the end.  The result is a fixed function of the build, so runs stay bitwise reproducible.
+// Working arrays in shared memory, one column per thread ([index][thread]: a dynamically indexed access of a warp is at most a
+// 2-way bank conflict; the same arrays in local memory cost 32 wavefronts per access): the bucket-sorted entries and, per segment
+// (0 = batch A, 1 = the rest) and residue, the read position and the end of the bucket.  The list is read from global memory twice
+// (count, scatter) and written once.
+#define NL_PERM_SMEM(CAP, TPB) ((size_t)(CAP) * (TPB) * 2 + 2 * 32 * (TPB) * 2)
+template <int CAP, int TPB>
+__global__ void __launch_bounds__(TPB) nl_permute_kernel(unsigned short* __restrict__ lists, const uint32_t* __restrict__ lcount, int lcap4, int BT, size_t n_lanes) {
+	extern __shared__ __align__(16) unsigned short nl_psm[];
+	unsigned short* srt = nl_psm + threadIdx.x;                       // srt[t * TPB]
+	unsigned short* pos = nl_psm + (size_t)CAP * TPB + threadIdx.x;   // pos[(16 seg + b) * TPB]
+	unsigned short* end = pos + 32 * TPB;
+	const size_t gl = (size_t)blockIdx.x * TPB + threadIdx.x;         // lane = blk * BT + tid
+	if (gl >= n_lanes) return;
+	const uint32_t cnt = lcount[gl];
+	const int n4 = (int)(cnt & 0xffffu), nA4 = min((int)(cnt >> 16), n4);
+	if (n4 == 0 || 4 * n4 > CAP) return;
+	const size_t blk = gl / (size_t)BT; const int tid = (int)(gl % (size_t)BT);
+	uint2* my = (uint2*)(lists + ((size_t)blk * lcap4 * BT + tid) * 4);
+	// pass 1: bucket sizes per segment (pad entries are 0 and are not counted)
+#pragma unroll
+	for (int k = 0; k < 32; ++k) pos[k * TPB] = 0;
+	for (int o = 0; o < n4; ++o) {
+		const uint2 w = my[(size_t)o * BT];
+		const int sb = o < nA4 ? 0 : 16;
+		const uint32_t ee[4] = {w.x & 0xffffu, w.x >> 16, w.y & 0xffffu, w.y >> 16};
+#pragma unroll
+		for (int u = 0; u < 4; ++u) if (ee[u]) ++pos[(sb + ((ee[u] >> 3) & 15)) * TPB];
+	}
+	int nrealA = 0, nrealB = 0;
+	{
+		int run = 0;
+#pragma unroll
+		for (int k = 0; k < 32; ++k) {
+			if (k == 16) { nrealA = run; run = 4 * nA4; }
+			const int c = pos[k * TPB];
+			pos[k * TPB] = (unsigned short)run; run += c; end[k * TPB] = (unsigned short)run;
+		}
+		nrealB = run - 4 * nA4;
+	}
+	// pass 2: scatter into the buckets (end[] serves as the fill pointer and is restored afterwards)
+#pragma unroll
+	for (int k = 0; k < 32; ++k) end[k * TPB] = pos[k * TPB];
+	for (int o = 0; o < n4; ++o) {
+		const uint2 w = my[(size_t)o * BT];
+		const int sb = o < nA4 ? 0 : 16;
+		const uint32_t ee[4] = {w.x & 0xffffu, w.x >> 16, w.y & 0xffffu, w.y >> 16};
+#pragma unroll
+		for (int u = 0; u < 4; ++u)
+			if (ee[u]) { unsigned short* f = end + (sb + ((ee[u] >> 3) & 15)) * TPB; srt[(size_t)(*f) * TPB] = (unsigned short)ee[u]; ++*f; }
+	}
+	// pass 3: emit in the wanted order, four entries per store
+	const int l16 = tid & 15;
+	for (int o = 0; o < n4; ++o) {
+		uint32_t q4[4];
+#pragma unroll
+		for (int u = 0; u < 4; ++u) {
+			const int t = 4 * o + u;
+			const int seg = o < nA4 ? 0 : 1, sb = 16 * seg;
+			const int rel = t - (seg ? 4 * nA4 : 0);
+			uint32_t ev = 0;
+			if (rel < (seg ? nrealB : nrealA)) {
+				int b = (l16 + t) & 15;
+				if (pos[(sb + b) * TPB] == end[(sb + b) * TPB]) {
+					b = (b + 8) & 15;
+					if (pos[(sb + b) * TPB] == end[(sb + b) * TPB]) {
+						int best = -1;
+						for (int k = 0; k < 16; ++k) { const int left = (int)end[(sb + k) * TPB] - (int)pos[(sb + k) * TPB]; if (left > best) { best = left; b = k; } }
+					}
+				}
+				unsigned short* pp = pos + (sb + b) * TPB;
+				ev = srt[(size_t)(*pp) * TPB]; ++*pp;
+			}
+			q4[u] = ev;
+		}
+		my[(size_t)o * BT] = make_uint2(q4[0] | (q4[1] << 16), q4[2] | (q4[3] << 16));
+	}
+}
+
+// ---------------------------------------------------------------------------------------------------------------
 // force: exact FP64 test + _loopBodyLJ over the listed pairs
 // ---------------------------------------------------------------------------------------------------------------
 // COUNT: count the pairs inside the cutoff (pair statistics; the shift6 term of a shifted potential needs the count).
@@ -389,7 +485,7 @@ __device__ __forceinline__ double nl_rcp3(double a) {
 }
 
 template <bool COUNT, bool VI, int FUSE, bool ZCHK, int R>
-__global__ void __launch_bounds__(NLGeom<R>::BT, R == 1 ? 6 : 2) nl_force_kernel(NLArgs a) {
+__global__ void __launch_bounds__(NLGeom<R>::BT, R == 1 ? 6 : 1024 / NLGeom<R>::BT) nl_force_kernel(NLArgs a) {
 	constexpr int BT = NLGeom<R>::BT;
 	extern __shared__ __align__(16) unsigned char nl_tile[];
 	double* Z = (double*)nl_tile;                               // [tcap]   z of tile entry k
@@ -405,9 +501,14 @@ __global__ void __launch_bounds__(NLGeom<R>::BT, R == 1 ? 6 : 2) nl_force_kernel
 	if (tid == 0) { nl_mbar_init(mbar, BT); nl_mbar_init(mbar + 1, BT); }
 	// dummy entries: far outside any cutoff, yet r^2 = 3e300 stays FINITE (the trace accumulation multiplies r^2 by an exact 0)
 	if (tid < NL_DUMMY) { Z[tid] = 1e150; XY[tid] = make_double2(1e150, 1e150); }
-	nl_plan<R>(a, P, blk);                             // __syncthreads inside: barriers and dummies are visible afterwards
+	if (tid < (int)(sizeof(NLPlan) / 4)) ((uint32_t*)&P)[tid] = ((const uint32_t*)(a.plans + blk))[tid];
+	__syncthreads();                                   // plan, barriers and dummies are visible afterwards
 	int qr; uint32_t i; bool has;
 	nl_my_slot<R>(P, tid, qr, i, has);
+	if (FUSE && has) {      // the epilogue's inputs: bring their lines into L2 now (no registers held)
+		asm volatile("prefetch.global.L2 [%0];" :: "l"(a.vel + 3 * (size_t)i));
+		if (FUSE == 1) asm volatile("prefetch.global.L2 [%0];" :: "l"(a.pos_build + i));
+	}
 	const bool active = P.live && has;
 	if (FUSE == 1 && a.guard && *a.guard > a.guard_thr) {      // the host swaps the two position buffers after every fused launch: carry the positions over
 		if (has) a.pos_out[i] = a.pos[i];
@@ -422,8 +523,18 @@ __global__ void __launch_bounds__(NLGeom<R>::BT, R == 1 ? 6 : 2) nl_force_kernel
 		nl_stage_tile<R>(a, P, Z, XY, mbar);
 		double4 Pi = make_double4(0., 0., 0., 0.);
 		uint32_t cnt = 0;
-		if (active) { Pi = a.pos[i]; cnt = a.lcount[(size_t)blk * BT + tid]; }
 		const uint2* my = (const uint2*)(a.lists + ((size_t)blk * a.lcap4 * BT + tid) * 4);   // 4 entries per load
+		// the first three quads are requested together with the count (the buffer holds >= 32 quads per lane).  What lies beyond a
+		// lane's count is uninitialised memory: cleared below, because a lane WITHOUT a molecule still walks the warp-uniform
+		// batch-A loop, where entry 0 (the dummy) is harmless and anything else would index beyond the tile
+		uint2 p0 = my[0], p1 = my[BT], p2 = my[2 * BT];
+		if (active) { Pi = a.pos[i]; cnt = a.lcount[(size_t)blk * BT + tid]; }
+		{
+			const int nq = (int)(cnt & 0xffffu);
+			if (nq < 1) p0 = make_uint2(0, 0);
+			if (nq < 2) p1 = make_uint2(0, 0);
+			if (nq < 3) p2 = make_uint2(0, 0);
+		}
 		double Fx = 0., Fy = 0., Fz = 0., Vx = 0., Vy = 0., Vz = 0., u6 = 0.;
 		int np_i = 0;
 		// 4 pairs at a time so that the dependency chains overlap.
@@ -474,10 +585,6 @@ __global__ void __launch_bounds__(NLGeom<R>::BT, R == 1 ? 6 : 2) nl_force_kernel
 		};
 		// list entries stream from HBM: three loads in flight per lane, rotated by name (loop unrolled by 3, no register moves)
 		const int n4 = (int)(cnt & 0xffffu);
-		uint2 p0 = make_uint2(0, 0), p1 = p0, p2 = p0;
-		if (0 < n4) p0 = my[0];
-		if (1 < n4) p1 = my[BT];
-		if (2 < n4) p2 = my[2 * BT];
 		auto step = [&](uint2& slot, int o) {
 			const uint2 cur = slot;
 			if (o + 3 < n4) slot = my[(size_t)(o + 3) * BT];

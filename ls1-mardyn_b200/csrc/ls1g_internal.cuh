@@ -117,6 +117,7 @@ struct ls1g_ctx {
 	double4* pos_build;                     // [cap] positions when the lists were built (displacement criterion)
 	unsigned short* lists; size_t lists_cap;// [blocks][LCAP][128] tile indices
 	uint32_t* lcount; size_t lcount_cap;    // [blocks*128]
+	void* plans;                            // [blocks] NLPlan of every block of the last build (lists.cuh), sized with bmap
 	uint32_t* bmap; unsigned char* bflag; size_t bmap_cap;   // boundary blocks of the last build (lists.cuh: NLArgs::bmap)
 	uint32_t n_boundary_blocks;
 	cudaStream_t stream_comm;               // high-priority stream of the overlapped halo refresh (multi-rank list steps)
@@ -124,6 +125,7 @@ struct ls1g_ctx {
 	int      track_disp;                    // integrate kernels track max |r - pos_build|^2 into d_flags[0]
 	uint64_t list_rebuilds;                 // list builds since the context was created (ls1g_list_stats)
 	int      list_R;                        // cell rows per block of the list kernels: 4 (2 x 2 bundle) or 1 (lists.cuh)
+	int      list_permute;                  // bank-aware list order after every build (LS1G_LIST_PERMUTE=0 keeps the tile order)
 	int      list_zchk;                     // the last build saw a (nearly) coincident pair: force kernels keep the r2 == 0 test
 	int      list_tcap;                     // tile capacity used by the list force kernel (max tile of the last build, padded)
 	int      list_bpr;                      // blocks per cell row

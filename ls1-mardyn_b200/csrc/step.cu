@@ -20,6 +20,13 @@ void ls1g_resolve_timers(ls1g_ctx* c);
 int nl_set_bin_grid(ls1g_ctx* c, int list_mode);
 static int sync_check(ls1g_ctx* c, const char* what);
 static inline void set_dev(const ls1g_ctx* c) { cudaSetDevice(c->cfg.device); }
+// CUDA call inside the step loops: 0 on success, else 1 with the error recorded (ls1g_last_error)
+static int cu_fail(cudaError_t e, const char* what, int line) {
+	if (e == cudaSuccess) return 0;
+	ls1g_set_error(std::string("ls1g step loop: ") + what + " (step.cu:" + std::to_string(line) + "): " + cudaGetErrorString(e));
+	return 1;
+}
+#define CU(expr) cu_fail((expr), #expr, __LINE__)
 #define FOR_G(G, c) for (int _r = 0; _r < (G).n; ++_r) if (ls1g_ctx* c = (set_dev((G).c[_r]), (G).c[_r]))
 
 // the group a context is driven with: itself, or - for a member of an in-process group - all ranks of that group
@@ -209,7 +216,7 @@ static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, do
 	double t_build = 0., t_wait = 0., t_enq = 0., t_max_wait = 0., t_max_enq = 0.;     // host wall clock, LS1G_DEBUG only
 	auto now = [&]() { if (!dbg) return 0.; struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6; };
 	auto rec_copy = [&](ls1g_ctx* c, int step, int off, int n) {
-		if (c->d_rec && cudaMemcpyAsync(c->d_rec + 8 * (size_t)step + off, c->d_scalars + off, n * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) return 1;
+		if (c->d_rec && CU(cudaMemcpyAsync(c->d_rec + 8 * (size_t)step + off, c->d_scalars + off, n * sizeof(double), cudaMemcpyDeviceToDevice, c->stream))) return 1;
 		return 0;
 	};
 	// s   = next step to enqueue
@@ -227,7 +234,7 @@ static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, do
 					c->forces_valid = 1;
 					if (!rc) rc = k_halo_map(c);
 					if (!rc) rc = k_list_build(c);             // zeroes d_flags[0..2]
-					if (!rc && cudaMemsetAsync(c->d_flags + 3, 0, sizeof(unsigned long long), c->stream) != cudaSuccess) rc = 1;
+					if (!rc && CU(cudaMemsetAsync(c->d_flags + 3, 0, sizeof(unsigned long long), c->stream))) rc = 1;
 				}
 				FOR_G(G, c) if (!rc && sync_check(c, "ls1g_run (list build)")) rc = 1;
 				if (rc) break;
@@ -236,9 +243,9 @@ static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, do
 				for (int r = 0; r < G.n; ++r) hb |= G.c[r]->h_flags[1];
 				if (c0->comm_mode == 1) {
 					double ovf[3] = {(hb & ~(NL_OVF_LIST_BIT | NL_OVF_TILE_BIT)) ? 1. : 0., (hb & NL_OVF_LIST_BIT) ? 1. : 0., (hb & NL_OVF_TILE_BIT) ? 1. : 0.};
-					if (cudaMemcpyAsync(c0->d_scalars + 12, ovf, 3 * sizeof(double), cudaMemcpyHostToDevice, c0->stream) != cudaSuccess) rc = 1;
+					if (CU(cudaMemcpyAsync(c0->d_scalars + 12, ovf, 3 * sizeof(double), cudaMemcpyHostToDevice, c0->stream))) rc = 1;
 					if (!rc) rc = comm_allreduce(G, COMM_SCALARS, 12, 3, COMM_MAX);
-					if (!rc && cudaMemcpyAsync(ovf, c0->d_scalars + 12, 3 * sizeof(double), cudaMemcpyDeviceToHost, c0->stream) != cudaSuccess) rc = 1;
+					if (!rc && CU(cudaMemcpyAsync(ovf, c0->d_scalars + 12, 3 * sizeof(double), cudaMemcpyDeviceToHost, c0->stream))) rc = 1;
 					if (!rc && sync_check(c0, "ls1g_run (list build)")) rc = 1;
 					if (rc) break;
 					if (ovf[0] != 0.) hb |= 8;
@@ -280,14 +287,14 @@ static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, do
 				// several ranks, NVE step: the halo positions travel on the communication stream while the inner blocks run
 				overlapped = true;
 				FOR_G(G, c) {
-					if (cudaEventRecord(c->ev_pos, c->stream) != cudaSuccess || cudaStreamWaitEvent(c->stream_comm, c->ev_pos, 0) != cudaSuccess) rc = 1;
+					if (CU(cudaEventRecord(c->ev_pos, c->stream)) || CU(cudaStreamWaitEvent(c->stream_comm, c->ev_pos, 0))) rc = 1;
 					std::swap(c->stream, c->stream_comm);
 				}
 				if (!rc) rc = comm_refresh(G);
 				FOR_G(G, c) {
 					if (!rc) rc = k_halo_refresh(c);
 					std::swap(c->stream, c->stream_comm);
-					if (!rc && cudaEventRecord(c->ev_halo, c->stream_comm) != cudaSuccess) rc = 1;
+					if (!rc && CU(cudaEventRecord(c->ev_halo, c->stream_comm))) rc = 1;
 				}
 			} else {
 				if (G.multi()) rc = comm_refresh(G);
@@ -298,7 +305,7 @@ static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, do
 				c->guard_on = built ? 0 : 1;
 				if (overlapped) {
 					if (!rc) rc = k_forces_list_fused(c, dt, 1);
-					if (!rc && cudaStreamWaitEvent(c->stream, c->ev_halo, 0) != cudaSuccess) rc = 1;
+					if (!rc && CU(cudaStreamWaitEvent(c->stream, c->ev_halo, 0))) rc = 1;
 					if (!rc) rc = k_forces_list_fused(c, dt, 2);
 					if (!rc) rc = rec_copy(c, s, 0, 8);
 				} else if (fuse_nve && s + 1 < n_steps) {
@@ -326,7 +333,7 @@ static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, do
 		} else if (chk < s && chk + 1 < n_steps) {
 			// did the steps after chk really run?  step chk + 1 was guarded by the flag step chk wrote
 			const double t2 = now();
-			FOR_G(G, c) if (cudaEventSynchronize(c->disp_ev[chk % NL_RING]) != cudaSuccess) rc = 1;
+			FOR_G(G, c) if (CU(cudaEventSynchronize(c->disp_ev[chk % NL_RING]))) rc = 1;
 			if (rc) break;
 			const double t3 = now();
 			t_wait += t3 - t2; if (t3 - t2 > t_max_wait) t_max_wait = t3 - t2;
@@ -381,17 +388,17 @@ static int run_impl(const Group& G, int n_steps, double dt, double target_T, ls1
 			c->forces_valid = 1;
 			if (!rc) rc = k_forces(c);
 			if (!rc) rc = k_drop_halo(c);
-			if (!rc && c->d_rec && cudaMemcpyAsync(c->d_rec + 8 * (size_t)s, c->d_scalars, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
+			if (!rc && c->d_rec && CU(cudaMemcpyAsync(c->d_rec + 8 * (size_t)s, c->d_scalars, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream))) rc = 1;
 		}
 		if (!rc) rc = g_post_pre(G, dt, 1, s + 1 < n_steps, thermo, target_T);
 		FOR_G(G, c)
-			if (!rc && c->d_rec && cudaMemcpyAsync(c->d_rec + 8 * (size_t)s + 4, c->d_scalars + 4, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream) != cudaSuccess) rc = 1;
+			if (!rc && c->d_rec && CU(cudaMemcpyAsync(c->d_rec + 8 * (size_t)s + 4, c->d_scalars + 4, 4 * sizeof(double), cudaMemcpyDeviceToDevice, c->stream))) rc = 1;
 	}
 	std::vector<std::vector<double>> h(G.n);
 	FOR_G(G, c) {
 		if (!rc && c->d_rec) {
 			h[_r].resize((size_t)n_steps * 8);
-			if (cudaMemcpyAsync(h[_r].data(), c->d_rec, h[_r].size() * sizeof(double), cudaMemcpyDeviceToHost, c->stream) != cudaSuccess) rc = 1;
+			if (CU(cudaMemcpyAsync(h[_r].data(), c->d_rec, h[_r].size() * sizeof(double), cudaMemcpyDeviceToHost, c->stream))) rc = 1;
 		}
 	}
 	for (int r = 0; r < G.n; ++r) G.c[r]->d_rec = keep[r];
