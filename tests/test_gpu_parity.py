@@ -13,7 +13,14 @@ from tests.gpu_helpers import ls1g, container_of, by_id, fcc_lattice, random_qua
 pytestmark = pytest.mark.gpu
 
 FORCE_CASES = golden_cases("vcp_") + golden_cases("per_") + golden_cases("ex_")
-# see tests/test_oracle_golden.py: the CO2 charge sites cancel to 1e-4 of their magnitude
+# examples/CO2 (charges +21.2 / -10.6 only 0.38 apart: the site forces cancel to 1e-4 of their magnitude) exists as two dumps of the
+# unmodified reference (tests/golden/make_golden_r2.py):
+#   ex_CO2        AVX2 build: 1/r^2 and 1/sqrt(r^2) are Newton-Raphson refined estimates (RealVecDouble.h:411-541)
+#   ex_CO2_novec  -DVECTOR_INSTRUCTIONS=NONE build: IEEE division and sqrt (SIMD_TYPES.h:79-95)
+# The reference's own two builds differ by 3.7e-10 in F on this input.  The CUDA path is held to the NOVEC dump at the stated bar of
+# 1e-10 (measured: F 7.9e-11, M 1.2e-11, Vi 8.4e-11, U 1.8e-13; profiles/probe_co2_parity.py) and to the AVX2 dump at 2e-9, which
+# only allows for the reference's own NR rounding.  ex_CO2Merker(_novec) - the 3 LJ + quadrupole model of
+# examples/surface-tension_LRC/CO2_Merker - has no such cancellation and agrees to 1e-13 with both builds.
 FORCE_TOL = {"ex_CO2": 2e-9}
 
 
