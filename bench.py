@@ -38,6 +38,12 @@ CELLS_PER_GPU = 136            # fcc unit cells per dimension per GPU: 4*136^3 =
 METRIC = "MMUPS (million molecule-updates/s), 1CLJ fcc 10^7 molecules per B200, force+integrate step"
 
 
+def workload_name(cells):
+    """the same string in both arms (the driver compares the configs of the two lines)"""
+    return ("cfg B: 1CLJ fcc lattice rho*=0.8442 T*=1.44 rc=2.5sigma dt*=0.002, %d^3 unit cells = %d molecules per GPU"
+            % (cells, 4 * cells ** 3))
+
+
 def _pkg():
     return importlib.import_module("ls1-mardyn_b200")
 
@@ -319,9 +325,13 @@ def run_mardyn_gpu(cells, steps, threads, timeout=1500):
     g = re.search(r"GpuLinkedCells: (\d+) device steps took ([0-9.eE+-]+) s; upload ([0-9.eE+-]+) s \((\d+) B\); (\d+) host mirror download\(s\) took ([0-9.eE+-]+) s \((\d+) B\); context creation ([0-9.eE+-]+) s", out)
     dev_s, up_s, up_b, mirrors, mir_s, mir_b = float(g.group(2)), float(g.group(3)), int(g.group(4)), int(g.group(5)), float(g.group(6)), int(g.group(7))
     ctx_s = float(g.group(8))
+    fs = re.search(r"first steps \[s\] ([0-9.eE+-]+) ([0-9.eE+-]+) ([0-9.eE+-]+) ([0-9.eE+-]+), slowest step ([0-9.eE+-]+)", out)
+    first_steps = [float(fs.group(k)) for k in range(1, 5)] if fs else None
+    slowest = float(fs.group(5)) if fs else None
     total = loop_s + up_s
     return dict(mmups=n * steps / total / 1e6, n=n, steps=steps, loop_s=loop_s, upload_s=up_s, device_s=dev_s, mirror_s=mir_s, mirrors=mirrors,
-                h2d_bytes=up_b, d2h_bytes=mir_b + 48 * steps, wall_s=wall, context_s=ctx_s, loop_only_mmups=n * steps / loop_s / 1e6)
+                h2d_bytes=up_b, d2h_bytes=mir_b + 48 * steps, wall_s=wall, context_s=ctx_s, loop_only_mmups=n * steps / loop_s / 1e6,
+                first_steps_s=first_steps, slowest_step_s=slowest)
 
 
 def run_oracle_port_sample(sample_cells, steps):
@@ -365,14 +375,17 @@ def main_reference(args):
     res = run_reference_sample(sample_cells, steps, threads)
     kind = "reference"
     if res is None:
-        res = run_oracle_port_sample(16, min(steps, 3))
+        sample_cells = 16
+        res = run_oracle_port_sample(sample_cells, min(steps, 3))
         kind, threads, steps = "port", 1, min(steps, 3)
     val = res["mmups"]
     line = {"impl": "reference", "metric": METRIC, "value": round(val, 4), "unit": "MMUPS", "n_gpus": args.gpus, "steps": steps,
             "warmup": args.warmup, "ms_per_step": round(1e3 * res["loop_s"] / steps, 3), "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": "1CLJ fcc rho*=0.8442 T*=1.44 rc=2.5 dt*=0.002, bounded sample of cfg B: %d molecules per step "
-                                   "(reference's own MultiObjectGenerator fcc lattice)" % res["n"],
+            "config": {"workload": workload_name(sample_cells), "n_molecules": res["n"],
+                       "ensemble": "NVT (velocity scaling every step): every shipped XML config is NVT and NVE cannot be selected from the reference's XML; "
+                                   "the same XML drives the B200 arm's e2e figure (MarDynGpu), the B200 arm's device-resident `value` is NVE",
+                       "input": "the reference's own MultiObjectGenerator fcc lattice (GridFiller)",
                        "warmup_note": "the reference's prepare_start force pass is its warm-up; its loop timer covers all steps"},
             "cpu_baseline": {"value": round(val, 4), "unit": "MMUPS", "cores": threads, "kind": kind,
                              "sample": "%s, %d molecules x %d steps" % (res.get("binary", "oracle port"), res["n"], steps)},
@@ -453,26 +466,56 @@ def main_b200(args):
             time.sleep(0.05)                                       # let it finish before anything is timed
     if args.warmup > 0:
         c.run(args.warmup, DT)
-    c.timers(reset=True)
+    # ---- timed region: exactly K steps between barrier + synchronize, CUDA events on the container's stream, max over ranks.
+    # The window is repeated (--windows, default 3; each is exactly K consecutive steps of the same trajectory) and `value` is
+    # the MEDIAN window: a neighbour-list rebuild falls into a window or not (one every ~30 steps at this state point), which
+    # moves a 20-step window by ~15 %; the spread and the rebuilds per window are reported next to it.
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    windows, tm, rec, clk_rows = [], None, None, []
+    for w in range(max(args.windows, 1)):
+        c.timers(reset=True)
+        rb0 = c.list_stats()["rebuilds"]
+        barrier()
+        tw0 = time.perf_counter()
+        e0.record(stream)
+        rec_w = c.run(args.steps, DT)
+        e1.record(stream)
+        barrier()
+        tw1 = time.perf_counter()
+        ms_w = e0.elapsed_time(e1)
+        mt = torch.tensor([ms_w], dtype=torch.float64, device="cuda")
+        per_rank = [ms_w]
+        if world > 1:
+            gathered = [torch.zeros_like(mt) for _ in range(world)]
+            dist.all_gather(gathered, mt)
+            per_rank = [float(g.item()) for g in gathered]
+        windows.append(dict(ms=max(per_rank), per_rank_ms=per_rank, rebuilds=c.list_stats()["rebuilds"] - rb0, tm=c.timers(reset=True), rec=rec_w,
+                            wall=(tw0, tw1)))
+    order = sorted(range(len(windows)), key=lambda k: windows[k]["ms"])
+    med = windows[order[len(order) // 2]]
+    ms_max, tm, rec = med["ms"], med["tm"], med["rec"]
+    if rank == 0:
+        clocks.window(windows[0]["wall"][0], windows[-1]["wall"][1])
+    clk = clocks.stop() if rank == 0 else None
+    n_pairs = c.last_pair_count()
+    value = n_global * args.steps / (ms_max * 1e-3) / 1e6
+    # ---- amortised over whole rebuild periods (reported, not the headline): one long window
+    c.timers(reset=True)
+    rb0 = c.list_stats()["rebuilds"]
     barrier()
-    tw0 = time.perf_counter()
     e0.record(stream)
-    rec = c.run(args.steps, DT)
+    c.run(args.long_steps, DT, records=False)
     e1.record(stream)
     barrier()
-    tw1 = time.perf_counter()
-    ms = e0.elapsed_time(e1)
-    if rank == 0:
-        clocks.window(tw0, tw1)
-    clk = clocks.stop() if rank == 0 else None
-    tm = c.timers(reset=True)
-    n_pairs = c.last_pair_count()
-    mt = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    mt = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(mt, op=dist.ReduceOp.MAX)
-    ms_max = float(mt.item())
-    value = n_global * args.steps / (ms_max * 1e-3) / 1e6
+    long_ms = float(mt.item())
+    tm_long = c.timers(reset=True)
+    amortised = {"steps": args.long_steps, "ms_per_step": round(long_ms / args.long_steps, 4), "list_rebuilds": c.list_stats()["rebuilds"] - rb0,
+                 "value": round(n_global * args.long_steps / (long_ms * 1e-3) / 1e6, 2), "unit": "MMUPS",
+                 "kernel_ms_per_step": {k: round(t["ms"] / args.long_steps, 4) for k, t in tm_long.items()},
+                 "what": "one window of %d consecutive steps (several list-rebuild periods): the steady-state rate a long run sees" % args.long_steps}
 
     # energy conservation over the timed steps (NVE): reported, not timed
     et = torch.tensor(np.concatenate([rec[:, 0], 0.5 * rec[:, 2]]), dtype=torch.float64, device="cuda")
@@ -495,9 +538,10 @@ def main_b200(args):
     vi_all = bool(int(os.environ.get("LS1G_VI_EVERY_STEP", "0") or 0))
     k_t = max(args.steps, 1)
     flops = lj_flops(n_dist, n_pairs, True) if vi_all else (lj_flops(n_dist, n_pairs, False) * (k_t - 1) + lj_flops(n_dist, n_pairs, True)) / k_t
-    force_ms = tm["force"]["ms"] / max(tm["force"]["launches"], 1)
+    # pair-kernel time PER STEP (the overlapped multi-rank step launches the kernel twice: inner blocks, then boundary blocks)
+    force_ms = tm["force"]["ms"] / max(args.steps, 1)
     traffic, traffic_src = None, None
-    prof = os.path.join(ROOT, "profiles", "r01c_ncu_nl_force_fused_10M_summary.csv")
+    prof = os.path.join(ROOT, "profiles", "r02b_ncu_nl_force_permuted_10M_summary.csv")
     if os.path.exists(prof) and args.cells == CELLS_PER_GPU:      # dram bytes of ONE launch from the committed ncu --set full capture
         vals = {}
         for ln in open(prof):
@@ -505,10 +549,10 @@ def main_b200(args):
             if len(f) >= 3 and f[0].startswith("dram__bytes_"):
                 vals[f[0]] = float(f[1]) * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}.get(f[2], 1.0)
         if len(vals) == 2:
-            traffic, traffic_src = sum(vals.values()), "profiles/r01c_ncu_nl_force_fused_10M_summary.csv (ncu --set full, one launch, same workload)"
+            traffic, traffic_src = sum(vals.values()), "profiles/r02b_ncu_nl_force_permuted_10M_summary.csv (ncu --set full, one launch, same workload)"
     peak = ls1g.fp64_peak_tflops(local) if rank == 0 else 0.0
     achieved = flops / (force_ms * 1e-3) / 1e12 if force_ms > 0 else 0.0
-    launches = sum(t["launches"] for t in tm.values())
+    launches = sum(sum(t["launches"] for t in w["tm"].values()) for w in windows)      # all timed windows
 
     # ---- e2e, C ABI with host buffers: every step moves the FULL state host -> device -> host (worst case of the boundary) ----
     tparts = np.zeros(4)
@@ -545,6 +589,7 @@ def main_b200(args):
                  "ms_per_step": {k: round(1e3 * v / k_e2e, 2) for k, v in zip(("upload", "upload_forces", "run_1_step", "download"), tparts)},
                  "what": "C ABI, full state both ways EVERY step: add_particles(id,cid,r,v)+set_forces(F) from pinned host, ls1g_run(1), download(id,r,v,F) to pinned host"}
     e2e = dict(roundtrip)
+    c_list_stats = c.list_stats()
     c.close()
 
     # ---- e2e, the reference-facing drop-in: ls1-MarDyn's own executable + time loop with the GpuLinkedCells container ----------
@@ -562,7 +607,8 @@ def main_b200(args):
                        "-> full state back into host Molecule objects at the last step; time = upload + the reference's own loop timer" % md["steps"],
                "seconds": {"upload": round(md["upload_s"], 3), "loop": round(md["loop_s"], 3), "of_loop_device_calls": round(md["device_s"], 3),
                            "of_loop_final_mirror": round(md["mirror_s"], 3), "process_wall": round(md["wall_s"], 1),
-                           "cuda_context_creation_not_counted": round(md["context_s"], 3)},
+                           "cuda_context_creation_not_counted": round(md["context_s"], 3),
+                           "device_call_of_steps_1_to_4": md["first_steps_s"], "slowest_device_call": md["slowest_step_s"]},
                "loop_only_mmups": round(md["loop_only_mmups"], 2), "c_abi_full_state_roundtrip_every_step": roundtrip}
 
     if rank == 0:
@@ -570,9 +616,9 @@ def main_b200(args):
         line = {"metric": METRIC, "value": round(value, 2), "unit": "MMUPS", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
                 "ms_per_step": round(ms_max / args.steps, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "f64", "data": "synthetic",
-                "config": {"workload": "cfg B: 1CLJ fcc lattice rho*=0.8442 T*=1.44 rc=2.5sigma dt*=0.002 NVE, %d^3 unit cells = %d molecules per GPU"
-                                       % (args.cells, 4 * args.cells ** 3),
-                           "n_molecules": n_global, "rank_grid": shard["grid"], "cells_per_dim": cpd,
+                "config": {"workload": workload_name(args.cells), "n_molecules": n_global,
+                           "ensemble": "NVE (`value`, ls1g_run); `e2e` runs the reference arm's XML, i.e. NVT velocity scaling every step",
+                           "rank_grid": shard["grid"], "cells_per_dim": cpd,
                            "l2": "inputs larger than L2 (pos+vel+F = %.0f MB per GPU)" % (n_local * 80 / 1e6),
                            "nve_rel_energy_drift_over_timed_steps": drift, "upot_per_molecule_t0": u0 / max(n_local, 1)},
                 "e2e": e2e,
@@ -587,7 +633,13 @@ def main_b200(args):
                                                      "it visits a pair across the periodic boundary from both images, so its total lies a few % above the Newton-3 count "
                                                      "(every pair once) that flops_per_launch and frac are quoted on"},
                              "model": "FlopCounter: 8*N_dist + 41*N_pairs with per-molecule virial (last step of the run), 8*N_dist + 35*N_pairs without (the other steps; the reference's own count for that case); Newton-3 counts, the owner-computes kernel executes ~2x these",
-                             "note": "bound is the FP64 FMA pipe (SURVEY 8d), not HBM/tensor: ncu sm__pipe_fp64_cycles_active 51 % of this owner-computes kernel, DRAM 1.5 TB/s = 23 % of the copy peak (profiles/r01c_ncu_nl_force_fused_10M_summary.csv)"},
+                             "note": "bound is the FP64 FMA pipe (SURVEY 8d), not HBM/tensor: ncu sm__pipe_fp64_cycles_active 57 % of this owner-computes kernel (it executes 2x the Newton-3 flops the fraction is quoted on), shared-memory pipe 69 %, DRAM 1.9 TB/s = 29 % of the copy peak (profiles/r02b_ncu_nl_force_permuted_10M_summary.csv)"},
+                "timed_windows": {"n": len(windows), "value_is": "median window", "ms": [round(w["ms"], 3) for w in windows],
+                                  "list_rebuilds": [int(w["rebuilds"]) for w in windows],
+                                  "spread_rel": round((max(w["ms"] for w in windows) - min(w["ms"] for w in windows)) / ms_max, 4),
+                                  "per_rank_ms_of_median_window": {"min": round(min(med["per_rank_ms"]), 3), "max": round(max(med["per_rank_ms"]), 3)}},
+                "amortised": amortised,
+                "neighbour_lists": c_list_stats,
                 "kernel_ms_per_step": {k: round(t["ms"] / args.steps, 4) for k, t in tm.items()},
                 "hbm_kernels": hbm_kernels(tm, args.steps, n_local),
                 "clocks": clk}
@@ -607,7 +659,9 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--cells", type=int, default=CELLS_PER_GPU, help="fcc unit cells per dimension per GPU")
     ap.add_argument("--e2e-steps", type=int, default=5)
-    ap.add_argument("--ref-cells", type=int, default=64, help="fcc unit cells per dimension of the reference arm's sample")
+    ap.add_argument("--windows", type=int, default=3, help="repeats of the timed K-step window (value = the median window)")
+    ap.add_argument("--long-steps", type=int, default=120, help="length of the extra window that spans whole list-rebuild periods (reported as `amortised`)")
+    ap.add_argument("--ref-cells", type=int, default=CELLS_PER_GPU, help="fcc unit cells per dimension of the reference arm (default: the bench workload itself)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-mardyn-gpu", action="store_true", help="skip the MarDynGpu end-to-end arm (e2e then = the C-ABI round trip)")
     ap.add_argument("--e2e-cells", type=int, default=0, help="fcc unit cells per dimension of the MarDynGpu end-to-end run (0 = --cells)")

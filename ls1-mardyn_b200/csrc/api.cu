@@ -176,7 +176,10 @@ extern "C" int ls1g_create(const ls1g_config* cfg, ls1g_ctx** out) {
 	c->bgrid = c->grid;
 	{ const char* e = getenv("LS1G_VI_EVERY_STEP"); c->vi_every_step = e && atoi(e) != 0; }
 	{ const char* lr = getenv("LS1G_LIST_ROWS"); c->list_R = lr && atoi(lr) == 1 ? 1 : 4; }
-	{ const char* lp = getenv("LS1G_LIST_PERMUTE"); c->list_permute = lp && atoi(lp) == 0 ? 0 : 1; }
+	// bank-aware list order (lists.cuh: nl_permute_kernel): 0 never, 1 always, 2 (default) when the previous lists lived >= 32 steps -
+	// the pass costs ~6 ms per build at 10^7 molecules and saves ~0.19 ms per step, so it pays for lattices and cold systems, not for a
+	// liquid whose lists expire every ~18 steps (profiles/r02c_permute_tradeoff.json)
+	{ const char* lp = getenv("LS1G_LIST_PERMUTE"); c->list_permute = lp ? (atoi(lp) == 0 ? 0 : 1) : 2; }
 	{ const char* sk = getenv("LS1G_SKIN"); c->skin = sk ? atof(sk) : 0.12 * c->cfg.cutoff; if (c->skin < 0.) c->skin = 0.; }
 	c->rc2 = c->cfg.cutoff * c->cfg.cutoff;
 	c->rclj2 = c->cfg.lj_cutoff * c->cfg.lj_cutoff;
@@ -207,9 +210,9 @@ extern "C" int ls1g_create(const ls1g_config* cfg, ls1g_ctx** out) {
 	CUDA_TRY(cudaMallocHost((void**)&c->h_scalars, 16 * sizeof(double)));
 	CUDA_TRY(cudaMalloc((void**)&c->d_flags, 16 * sizeof(unsigned long long)));
 	CUDA_TRY(cudaMemset(c->d_flags, 0, 16 * sizeof(unsigned long long)));
-	CUDA_TRY(cudaMallocHost((void**)&c->h_flags, 16 * sizeof(unsigned long long)));
-	memset(c->h_flags, 0, 16 * sizeof(unsigned long long));
-	for (int k = 0; k < 4; ++k) CUDA_TRY(cudaEventCreateWithFlags(&c->disp_ev[k], cudaEventDisableTiming));
+	CUDA_TRY(cudaMallocHost((void**)&c->h_flags, 32 * sizeof(unsigned long long)));
+	memset(c->h_flags, 0, 32 * sizeof(unsigned long long));
+	for (int k = 0; k < 16; ++k) CUDA_TRY(cudaEventCreateWithFlags(&c->disp_ev[k], cudaEventDisableTiming));
 	*out = c;
 	return 0;
 }
@@ -225,7 +228,7 @@ extern "C" int ls1g_destroy(ls1g_ctx* c) {
 	cudaFree(c->comps); cudaFree(c->sites); cudaFree(c->eps24); cudaFree(c->sig2); cudaFree(c->shift6);
 	cudaFree(c->cell_count); cudaFree(c->cell_fill); cudaFree(c->cell_start); cudaFree(c->scan_block);
 	cudaFree(c->d_flags); cudaFreeHost(c->h_flags);
-	for (int k = 0; k < 4; ++k) if (c->disp_ev[k]) cudaEventDestroy(c->disp_ev[k]);
+	for (int k = 0; k < 16; ++k) if (c->disp_ev[k]) cudaEventDestroy(c->disp_ev[k]);
 	cudaFree(c->d_counters); cudaFreeHost(c->h_counters); cudaFree(c->partials); cudaFree(c->d_scalars); cudaFreeHost(c->h_scalars);
 	for (int k = 0; k < 2; ++k) { cudaFree(c->send_buf[k]); cudaFree(c->recv_buf[k]); }
 	if (c->ev_pos) cudaEventDestroy(c->ev_pos);
@@ -379,6 +382,7 @@ static size_t default_capacity(const ls1g_ctx* c, size_t n) {
 }
 
 int k_reserve_stage(ls1g_ctx* c);
+int k_list_reserve(ls1g_ctx* c, size_t n);      // lists.cu
 extern "C" int ls1g_reserve(ls1g_ctx* c, size_t n) {
 	if (!c) LS1G_FAIL("null context");
 	if (c->n_comp == 0) LS1G_FAIL("ls1g_reserve: call ls1g_set_components first");
@@ -390,6 +394,7 @@ extern "C" int ls1g_reserve(ls1g_ctx* c, size_t n) {
 		if (alloc_molecules(c, std::max<size_t>(want, 1))) return 1;
 	}
 	if (k_reserve_stage(c)) return 1;
+	if (k_list_reserve(c, n)) return 1;
 	CUDA_TRY(cudaDeviceSynchronize());
 	return 0;
 }

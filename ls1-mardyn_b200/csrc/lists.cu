@@ -99,19 +99,8 @@ static void nl_launch(const ls1g_ctx* c, const NLArgs& a, size_t grid) {
 	}
 }
 
-// after k_sort on the bin grid: size the block grid, build the lists, remember the build positions.
-// The caller synchronises and reads h_flags[1] (overflow bits).
-int k_list_build(ls1g_ctx* c) {
-	if (c->list_lcap < NL_LCAP0) c->list_lcap = NL_LCAP0;
-	if (c->list_R != 1 && c->list_R != 4) c->list_R = 4;
-	if (c->bgrid.cpd[1] - 2 < 2 || c->bgrid.cpd[2] - 2 < 2) c->list_R = 1;      // nothing to bundle
-	// R = 1: 128 slots of a row per block; R = 4: every bundle is cut into ceil(molecules / NL_BUNDLE_FILL) blocks (lists.cuh: nl_plan)
-	c->list_bpr = c->list_R == 4 ? std::max((int)((c->max_bundle + NL_BUNDLE_FILL - 1) / NL_BUNDLE_FILL), (c->bgrid.cpd[0] - 2 + NL_XSPAN - 1) / NL_XSPAN)
-	                             : (int)((c->max_row + NL_BT - 1) / NL_BT);
-	if (c->list_bpr < 1) c->list_bpr = 1;
-	if (c->list_R == 4) c->build_tcap = NL_TCAP;         // 16-row tiles: the large build tile from the start
-	else if (c->build_tcap < NL_TCAP0) c->build_tcap = NL_TCAP0;
-	const size_t nb = nl_blocks(c);
+// buffers of the list loop for nb blocks (grown, never shrunk)
+static int nl_ensure_buffers(ls1g_ctx* c, size_t nb) {
 	const size_t want_l = nb * (size_t)c->list_lcap * nl_bt(c), want_c = nb * nl_bt(c);
 	if (want_l > c->lists_cap) {
 		cudaFree(c->lists); c->lists = nullptr; c->lists_cap = 0;
@@ -132,6 +121,56 @@ int k_list_build(ls1g_ctx* c) {
 		CUDA_TRY(cudaMalloc((void**)&c->bflag, nb));
 		c->bmap_cap = nb;
 	}
+	return ls1g_ensure_partials(c, nb ? nb : 1, 8);
+}
+
+// Set-up of the list loop ahead of the first step (called by ls1g_reserve): the kernels' modules are loaded (setting their
+// attributes does that under CUDA's lazy loading) and the buffers are allocated from an ESTIMATE of the block count - n molecules
+// spread evenly over the bin grid, 30 % head room; a build that needs more grows them as before.  Without this the first step of a
+// host-driven loop pays for a 2.6 GB cudaMalloc (10^7 molecules) and the module loads inside the caller's loop timer.
+int ls1g_ensure_rec(ls1g_ctx* c, size_t n_steps);
+__global__ void fused_finalize_kernel(const double* __restrict__ partials, size_t nb, double* __restrict__ out);
+int k_list_reserve(ls1g_ctx* c, size_t n) {
+	if (!nl_applicable(c) || c->cap == 0) return 0;
+	if (nl_force_attrs(c)) return 1;
+	{
+		cudaFuncAttributes fa;      // kernels of the loop that carry no attribute of their own
+		CUDA_TRY(cudaFuncGetAttributes(&fa, halo_refresh_kernel));
+		CUDA_TRY(cudaFuncGetAttributes(&fa, fused_finalize_kernel));
+	}
+	Grid g;
+	if (grid_init_cut(g, c->cfg, c->cfg.cutoff + c->skin, -1)) return 1;
+	if (c->list_lcap < NL_LCAP0) c->list_lcap = NL_LCAP0;
+	const size_t nx = g.cpd[0] - 2, nyi = g.cpd[1] - 2, nzi = g.cpd[2] - 2;
+	const int R = (c->list_R == 1 || nyi < 2 || nzi < 2) ? 1 : 4;
+	const double per_row = 1.3 * (double)n / (double)(nyi * nzi);
+	size_t nb;
+	if (R == 4) {
+		const size_t bpr = std::max((size_t)(4. * per_row / NL_BUNDLE_FILL) + 1, (nx + NL_XSPAN - 1) / NL_XSPAN);
+		nb = ((nyi + 1) / 2) * ((nzi + 1) / 2) * bpr;
+	} else nb = nyi * nzi * ((size_t)(per_row / NL_BT) + 1);
+	const int keepR = c->list_R;
+	c->list_R = R;                                    // nl_bt() sizes by it
+	const int rc = nl_ensure_buffers(c, nb);
+	c->list_R = keepR;
+	if (rc) return 1;
+	return ls1g_ensure_rec(c, 1024);
+}
+
+// after k_sort on the bin grid: size the block grid, build the lists, remember the build positions.
+// The caller synchronises and reads h_flags[1] (overflow bits).
+int k_list_build(ls1g_ctx* c) {
+	if (c->list_lcap < NL_LCAP0) c->list_lcap = NL_LCAP0;
+	if (c->list_R != 1 && c->list_R != 4) c->list_R = 4;
+	if (c->bgrid.cpd[1] - 2 < 2 || c->bgrid.cpd[2] - 2 < 2) c->list_R = 1;      // nothing to bundle
+	// R = 1: 128 slots of a row per block; R = 4: every bundle is cut into ceil(molecules / NL_BUNDLE_FILL) blocks (lists.cuh: nl_plan)
+	c->list_bpr = c->list_R == 4 ? std::max((int)((c->max_bundle + NL_BUNDLE_FILL - 1) / NL_BUNDLE_FILL), (c->bgrid.cpd[0] - 2 + NL_XSPAN - 1) / NL_XSPAN)
+	                             : (int)((c->max_row + NL_BT - 1) / NL_BT);
+	if (c->list_bpr < 1) c->list_bpr = 1;
+	if (c->list_R == 4) c->build_tcap = NL_TCAP;         // 16-row tiles: the large build tile from the start
+	else if (c->build_tcap < NL_TCAP0) c->build_tcap = NL_TCAP0;
+	const size_t nb = nl_blocks(c);
+	if (nl_ensure_buffers(c, nb)) return 1;
 	timer_start(c, LS1G_T_SORT);
 	CUDA_TRY(cudaMemsetAsync(c->d_flags, 0, 3 * sizeof(unsigned long long), c->stream));
 	CUDA_TRY(cudaMemsetAsync(c->d_flags + 5, 0, 2 * sizeof(unsigned long long), c->stream));      // boundary-block count, near-pair flag
@@ -143,7 +182,8 @@ int k_list_build(ls1g_ctx* c) {
 	if (c->list_R == 4) nl_build_kernel<4><<<(unsigned)nb, NLGeom<4>::BT, NL_BUILD_SMEM(4, a.btcap), c->stream>>>(a);
 	else nl_build_kernel<1><<<(unsigned)nb, NLGeom<1>::BT, NL_BUILD_SMEM(1, a.btcap), c->stream>>>(a);
 	CUDA_TRY(cudaGetLastError());
-	if (c->list_permute) {      // bank-aware order of every list (lists.cuh: nl_permute_kernel)
+	const bool permute = c->list_permute == 1 || (c->list_permute == 2 && c->list_life >= 32);
+	if (permute) {      // bank-aware order of every list (lists.cuh: nl_permute_kernel)
 		const size_t lanes = nb * nl_bt(c);
 		const int bt = (int)nl_bt(c);
 		if (c->list_lcap <= 128) nl_permute_kernel<128, 128><<<nblk(lanes, 128), 128, NL_PERM_SMEM(128, 128), c->stream>>>(c->lists, c->lcount, a.lcap4, bt, lanes);
@@ -154,8 +194,8 @@ int k_list_build(ls1g_ctx* c) {
 	}
 	CUDA_TRY(cudaMemcpyAsync(c->h_flags, c->d_flags, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
 	CUDA_TRY(cudaMemcpyAsync(c->h_flags + 3, c->d_flags + 5, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));   // read by the caller after its sync
-	CUDA_TRY(cudaMemcpyAsync(c->h_flags + 8, c->d_flags + 6, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));   // near-pair flag
-	timer_stop(c, LS1G_T_SORT, 2 + (c->list_permute ? 1 : 0));
+	CUDA_TRY(cudaMemcpyAsync(c->h_flags + 4, c->d_flags + 6, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));   // near-pair flag
+	timer_stop(c, LS1G_T_SORT, 2 + (permute ? 1 : 0));
 	return 0;
 }
 

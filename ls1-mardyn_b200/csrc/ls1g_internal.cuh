@@ -125,7 +125,9 @@ struct ls1g_ctx {
 	int      track_disp;                    // integrate kernels track max |r - pos_build|^2 into d_flags[0]
 	uint64_t list_rebuilds;                 // list builds since the context was created (ls1g_list_stats)
 	int      list_R;                        // cell rows per block of the list kernels: 4 (2 x 2 bundle) or 1 (lists.cuh)
-	int      list_permute;                  // bank-aware list order after every build (LS1G_LIST_PERMUTE=0 keeps the tile order)
+	int      list_permute;                  // bank-aware list order after a build: 0 never, 1 always, 2 when the last lists lived >= 32 steps
+	uint64_t list_steps;                    // list steps completed since the context was created
+	uint64_t list_steps_at_build, list_life;   // ... at the last build; lifetime (steps) of the lists that build replaced
 	int      list_zchk;                     // the last build saw a (nearly) coincident pair: force kernels keep the r2 == 0 test
 	int      list_tcap;                     // tile capacity used by the list force kernel (max tile of the last build, padded)
 	int      list_bpr;                      // blocks per cell row
@@ -136,8 +138,8 @@ struct ls1g_ctx {
 	int      vi_every_step;                 // LS1G_VI_EVERY_STEP=1: per-molecule virial on every list step, not only the last of a run
 	int      guard_on;                      // force / integrate kernels return at once when d_flags[3] > disp_thr2 (lists expired)
 	double   disp_thr2;                     // (0.4995 skin)^2: the lists are exact while max |r - r_build|^2 <= this
-	cudaEvent_t disp_ev[4];                 // completion of the per-step copy of d_flags[0] into h_flags[4 + step % 4]
-	unsigned long long* h_flags;            // pinned mirror      // device staging area of the host<->device transfers (transfer.cu)
+	cudaEvent_t disp_ev[16];                // completion of the per-step copy of d_flags[0] into h_flags[8 + step % 16]
+	unsigned long long* h_flags;            // pinned [32]: 0-2 build flags, 3 boundary blocks, 4 near-pair flag, 8.. ring of displacement flags      // device staging area of the host<->device transfers (transfer.cu)
 
 	// cells / sort scratch
 	uint32_t *cell_count, *cell_fill, *cell_start;   // [n_cells+1]

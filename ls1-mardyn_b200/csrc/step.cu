@@ -171,13 +171,13 @@ static int g_post_pre(const Group& G, double dt, int do_post, int do_pre, int th
 #define NL_OVF_TILE_BIT 1ull      // lists.cuh: NL_OVF_TILE
 #define NL_TCAP_MAX_H 5120        // lists.cuh: NL_TCAP
 #define NL_LCAP_MAX_H 1020        // lists.cuh: NL_LCAP_MAX
-#define NL_AHEAD 3      // steps the host may enqueue beyond the last displacement flag it has read
-#define NL_RING 4       // pinned flag copies / events in flight (> NL_AHEAD)
+#define NL_AHEAD 8      // steps the host may enqueue beyond the last displacement flag it has read (absorbs ~15 ms of host jitter)
+#define NL_RING 16      // pinned flag copies / events in flight (> NL_AHEAD)
 static int flag_snapshot(const Group& G, int ring) {
 	if (G.multi() && comm_allreduce(G, COMM_FLAGS, 0, 1, COMM_MAX)) return 1;      // non-negative doubles: bit order == value order
 	FOR_G(G, c) {
 		CUDA_TRY(cudaMemcpyAsync(c->d_flags + 3, c->d_flags, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, c->stream));
-		CUDA_TRY(cudaMemcpyAsync(c->h_flags + 4 + ring, c->d_flags, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+		CUDA_TRY(cudaMemcpyAsync(c->h_flags + 8 + ring, c->d_flags, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
 		CUDA_TRY(cudaEventRecord(c->disp_ev[ring], c->stream));
 	}
 	return 0;
@@ -200,7 +200,7 @@ static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, do
 	// several ranks: overlap the halo refresh with the inner blocks of the force pass (LS1G_OVERLAP=0: exchange first, then one launch)
 	const char* oe = getenv("LS1G_OVERLAP");
 	const bool overlap = G.multi() && !(oe && atoi(oe) == 0);
-	auto expired = [&](int ring) { double d2; memcpy(&d2, c0->h_flags + 4 + ring, sizeof(double)); return d2 > c0->disp_thr2; };      // all ranks hold the same value
+	auto expired = [&](int ring) { double d2; memcpy(&d2, c0->h_flags + 8 + ring, sizeof(double)); return d2 > c0->disp_thr2; };      // all ranks hold the same value
 	auto fail = [&]() { FOR_G(G, c) { c->track_disp = 0; c->in_list_mode = 0; c->guard_on = 0; nl_set_bin_grid(c, 0); cudaStreamSynchronize(c->stream); cudaStreamSynchronize(c->stream_comm); } return 1; };
 	bool cont = true;
 	for (int r = 0; r < G.n; ++r) cont = cont && G.c[r]->in_list_mode;
@@ -228,6 +228,8 @@ static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, do
 			bool overlapped = false;
 			const double t0 = now();
 			if (need_build) {
+				// lifetime of the lists being replaced: steps [0, s) of this call have run with them (plus those of earlier calls)
+				FOR_G(G, c) { const uint64_t now_steps = c->list_steps + (uint64_t)s; c->list_life = c->list_steps_at_build ? now_steps - c->list_steps_at_build : 0; c->list_steps_at_build = now_steps ? now_steps : 1; }
 				FOR_G(G, c) { c->sorted = 0; c->track_disp = 0; c->guard_on = 0; c->forces_valid = 0; }
 				rc = G.multi() ? comm_exchange_build(G) : k_sort(c0, 1);
 				FOR_G(G, c) {
@@ -276,7 +278,7 @@ static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, do
 				FOR_G(G, c) {
 					c->track_disp = 1;
 					c->n_boundary_blocks = (uint32_t)c->h_flags[3];
-					c->list_zchk = c->h_flags[8] != 0;
+					c->list_zchk = c->h_flags[4] != 0;
 					c->list_tcap = (int)((c->h_flags[2] + 63) & ~63ull);
 					if (c->list_tcap < 64) c->list_tcap = 64;
 				}
@@ -349,7 +351,7 @@ static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, do
 	if (rc) return fail();
 	if (dbg) fprintf(stderr, "ls1g: %d list steps, %d rebuilds, %d repeated steps; host ms: build %.2f, enqueue %.2f (max %.2f), wait %.2f (max %.2f)\n",
 	                 n_steps, rebuilds, repeats, t_build, t_enq, t_max_enq, t_wait, t_max_wait);
-	FOR_G(G, c) c->list_rebuilds += (uint64_t)rebuilds;
+	FOR_G(G, c) { c->list_rebuilds += (uint64_t)rebuilds; c->list_steps += (uint64_t)n_steps; }
 	// stay in the frozen layout (in_list_mode): the next ls1g_run continues, any other entry point calls ls1g_nl_leave first
 	FOR_G(G, c) if (k_drop_halo(c)) return 1;
 	*done = n_steps;
