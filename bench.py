@@ -665,7 +665,20 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-mardyn-gpu", action="store_true", help="skip the MarDynGpu end-to-end arm (e2e then = the C-ABI round trip)")
     ap.add_argument("--e2e-cells", type=int, default=0, help="fcc unit cells per dimension of the MarDynGpu end-to-end run (0 = --cells)")
+    ap.add_argument("--workload", default="1clj", choices=["1clj", "argon", "co2", "eox", "co2q"],
+                    help="1clj = the headline workload (cfg B); the others are the reference's shipped examples replicated (bench_examples.py: "
+                         "cfg A argon, cfg C co2 / co2q, cfg D eox), same JSON line, same launch line")
+    ap.add_argument("--replicas", type=int, default=8, help="example workloads: replicas per dimension per GPU (8 -> 1 048 576 molecules)")
     args = ap.parse_args()
+    if args.workload != "1clj":
+        import bench_examples
+        fwd = ["--workload", args.workload, "--gpus", str(args.gpus), "--steps", str(args.steps), "--warmup", str(args.warmup),
+               "--replicas", str(args.replicas), "--impl", args.impl]
+        if args.no_cpu_baseline:
+            fwd.append("--no-cpu-baseline")
+        if args.no_mardyn_gpu:
+            fwd.append("--no-e2e")
+        return bench_examples.main(fwd)
     if args.impl == "reference":
         return main_reference(args)
     return main_b200(args)

@@ -8,8 +8,9 @@ does a user of examples/Argon, examples/CO2, examples/EOX get".
 * input: the committed golden fixture of the example (tests/golden/ex_*.npz - positions, velocities, quaternions, angular
   momenta and component tables exactly as the reference read them from its .inp), replicated k^3 times like the reference's
   ReplicaGenerator; NVT with the example's own temperature, time step and cutoffs.
-* GPU arm: Container.run (device resident) - multi-site systems take the per-step path (sort + force_generic_kernel),
-  single-site ones the neighbour-list loop when their lists fit.
+* GPU arm: Container.run (device resident) - the neighbour-list loop for single-site and rigid multi-site systems alike
+  (LS1G_LIST_MULTISITE=0: the per-step cell scan, force_generic_kernel).  --gpus N (torch.distributed.run, NCCL): block decomposition
+  of the replicated example, --replicas per dimension PER GPU (weak scaling).
 * roofline: the reference's own FlopCounter total for this very configuration (fixture key "flops", dumped by the reference
   at t = 0) times k^3, over the pair-kernel time, against the measured FP64 peak.
 * CPU arm (cpu_baseline, kind "reference"): oracle/_ref/MarDyn on a smaller replica of the same example, written as an
@@ -82,14 +83,15 @@ def fixture(name, workload=None):
 
 
 def replicate(d, k):
-    """ReplicaGenerator semantics (io/ReplicaGenerator.cpp): the box tiled k times per dimension, every replica a shifted
-    copy of the same molecules; ids renumbered"""
+    """ReplicaGenerator semantics (io/ReplicaGenerator.cpp): the box tiled k (or kx, ky, kz) times per dimension, every replica a
+    shifted copy of the same molecules; ids renumbered"""
+    kk = [int(k)] * 3 if np.isscalar(k) else [int(x) for x in k]
     box = d["box"]
-    sh = np.array([(i, j, l) for i in range(k) for j in range(k) for l in range(k)], dtype=np.float64) * box
-    n = len(d["in_id"])
-    rep = lambda a: np.tile(a, (k ** 3,) + (1,) * (a.ndim - 1))
-    return dict(id=np.arange(1, n * k ** 3 + 1, dtype=np.uint64), cid=rep(d["in_cid"]).astype(np.uint32),
-                r=(d["in_r"][None, :, :] + sh[:, None, :]).reshape(-1, 3), v=rep(d["in_v"]), q=rep(d["in_q"]), D=rep(d["in_L"])), box * k
+    sh = np.array([(i, j, l) for i in range(kk[0]) for j in range(kk[1]) for l in range(kk[2])], dtype=np.float64) * box
+    n, nrep = len(d["in_id"]), kk[0] * kk[1] * kk[2]
+    rep = lambda a: np.tile(a, (nrep,) + (1,) * (a.ndim - 1))
+    return dict(id=np.arange(1, n * nrep + 1, dtype=np.uint64), cid=rep(d["in_cid"]).astype(np.uint32),
+                r=(d["in_r"][None, :, :] + sh[:, None, :]).reshape(-1, 3), v=rep(d["in_v"]), q=rep(d["in_q"]), D=rep(d["in_L"])), box * np.array(kk, dtype=np.float64)
 
 
 def ascii_components(d, ls1g):
@@ -136,9 +138,10 @@ def run_reference(d, temp, k, steps, threads, ls1g, gpu=False):
     return res
 
 
-def main():
+def main(argv=None):
     ap = argparse.ArgumentParser()
     ap.add_argument("--workload", choices=sorted(WORKLOADS), default="co2")
+    ap.add_argument("--gpus", type=int, default=1, help="ranks (one process per GPU, torch.distributed.run); weak scaling: --replicas per GPU")
     ap.add_argument("--replicas", type=int, default=8, help="replicas per dimension on the GPU (8 -> 1 048 576 molecules)")
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
@@ -148,15 +151,20 @@ def main():
     ap.add_argument("--no-e2e", action="store_true", help="skip the MarDynGpu end-to-end arm")
     ap.add_argument("--e2e-replicas", type=int, default=4, help="replicas per dimension of the MarDynGpu arm (ASCII input: 4 -> 131 072 molecules)")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    args = ap.parse_args()
+    args = ap.parse_args(argv)
     ls1g = importlib.import_module("ls1-mardyn_b200")
     fx, temp, label = WORKLOADS[args.workload]
+    world, rank, local = int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("RANK", "0")), int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit("--gpus %d does not match WORLD_SIZE %d (launch with torch.distributed.run --nproc-per-node %d)" % (args.gpus, world, args.gpus))
     d = fixture(fx, args.workload)
     dt = float(d["dt"][0])
     threads = B.host_cores()
     metric = "MMUPS (million molecule-updates/s), %s replicated k^3, force+integrate step, NVT" % label
 
     if args.impl == "reference":
+        if rank != 0:
+            return 0
         res = run_reference(d, temp, args.ref_replicas, max(args.steps, 1), threads, ls1g)
         if res is None:
             print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/MarDyn not built"})); return 0
@@ -168,59 +176,100 @@ def main():
         return 0
 
     import torch
+    import torch.distributed as dist
     if not torch.cuda.is_available():
         raise SystemExit("bench_examples.py needs a CUDA device (there is no CPU fallback)")
-    m, box = replicate(d, args.replicas)
-    n = len(m["id"])
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def allsum(x):
+        t = torch.tensor(np.atleast_1d(np.asarray(x, dtype=np.float64)), dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t)
+        return t.cpu().numpy()
+
+    # block decomposition (DomainDecomposition's grid) of the replicated example: --replicas per dimension PER GPU
+    grid, coords = ls1g.decomp_grid(world, rank)
+    m, box = replicate(d, [args.replicas * g for g in grid])
+    bmin, bmax = ls1g.decomp_box(grid, coords, list(box))
+    mine = np.all((m["r"] >= np.array(bmin)) & (m["r"] < np.array(bmax)), axis=1)
+    n_local = int(mine.sum())
+    n = int(allsum(n_local)[0])
     comps = ls1g.components_from_tables(d["comp_counts"], d["comp_scalars"], d["lj_sites"], d["charge_sites"], d["dipole_sites"], d["quadrupole_sites"])
-    clocks = B.ClockSampler(0)
-    with ls1g.Container(box, float(d["rc"][0]), lj_cutoff=float(d["rc"][1]), eps_rf=float(d["epsRF"][0])) as c:
+    clocks = B.ClockSampler(local)
+    with ls1g.Container(bmax, float(d["rc"][0]), box_min=bmin, lj_cutoff=float(d["rc"][1]), eps_rf=float(d["epsRF"][0]), global_length=list(box),
+                        rank_grid=grid, rank_coords=coords, device=local, capacity=(int(2.2 * n_local) + 100000) if world > 1 else 0) as c:
         c.set_components(comps, d["mixcoeff"])
-        c.add_particles(m["id"], m["cid"], m["r"], m["v"], q=m["q"], L=m["D"])
+        if world > 1:
+            idt = torch.zeros(128, dtype=torch.uint8, device="cuda")
+            if rank == 0:
+                idt = torch.tensor(list(ls1g.comm_unique_id()), dtype=torch.uint8, device="cuda")
+            dist.broadcast(idt, 0)
+            c.comm_init(world, rank, bytes(idt.cpu().tolist()))
+        c.add_particles(m["id"][mine], m["cid"][mine], m["r"][mine], m["v"][mine], q=m["q"][mine], L=m["D"][mine])
+        del m
         c.exchange()
-        try:
-            fc = c.flop_count()           # the reference's FlopCounter on THIS replicated system, counted on the device
-        except AttributeError:            # LS1G_LIB pointing at an older build of the library (A/B timing only)
-            fc = dict(flops=float(d["flops"][0]) * args.replicas ** 3, kernel=np.zeros(7))
+        fc = c.flop_count()               # the reference's FlopCounter on THIS replicated system (this rank's part), counted on the device
         u0, w0 = c.traverse_cells()
-        clocks.start()
-        t_wait = time.time()
-        while not clocks.rows and clocks.proc is not None and time.time() - t_wait < 10.0:
-            time.sleep(0.05)
+        if rank == 0:
+            clocks.start()
+            t_wait = time.time()
+            while not clocks.rows and clocks.proc is not None and time.time() - t_wait < 10.0:
+                time.sleep(0.05)
         if args.warmup > 0:
             c.run(args.warmup, dt, target_temperature=temp)
         c.timers(reset=True)
-        stream = torch.cuda.ExternalStream(c.stream(), device=torch.device("cuda", 0))
+        rb0 = c.list_stats()["rebuilds"]
+        stream = torch.cuda.ExternalStream(c.stream(), device=torch.device("cuda", local))
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        torch.cuda.synchronize()
+        barrier()
         tw0 = time.perf_counter()
         e0.record(stream)
         rec = c.run(args.steps, dt, target_temperature=temp)
         e1.record(stream)
-        torch.cuda.synchronize()
+        barrier()
         tw1 = time.perf_counter()
-        ms = e0.elapsed_time(e1)
-        clocks.window(tw0, tw1)
-        clk = clocks.stop()
+        mt = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(mt, op=dist.ReduceOp.MAX)
+        ms = float(mt.item())
+        if rank == 0:
+            clocks.window(tw0, tw1)
+        clk = clocks.stop() if rank == 0 else None
         tm = c.timers(reset=True)
-        n_pairs = c.last_pair_count()
-        peak = ls1g.fp64_peak_tflops(0)
+        lists = c.list_stats()
+        lists["rebuilds_in_window"] = lists["rebuilds"] - rb0
+        n_pairs = int(allsum(c.last_pair_count())[0])
+        peak = ls1g.fp64_peak_tflops(local) if rank == 0 else 0.0
+    rec = allsum(rec.ravel()).reshape(rec.shape) if world > 1 else rec          # NCCL ranks report their own part (Domain::setLocal*)
+    u0 = float(allsum(u0)[0])
+    fc = dict(flops=float(allsum(fc["flops"])[0]) / world, kernel=allsum(fc["kernel"]) / world)      # per GPU: the kernel time is per GPU too
     flops = fc["flops"]
     model = ("the reference's FlopCounter (Newton-3 counts) on the replicated system at t = 0, counted on the device by ls1g_flop_count "
              "(bit-equal to the reference's own count on the golden fixtures)")
-    fixture_flops = float(d["flops"][0]) * args.replicas ** 3 if "flops" in d else None
+    fixture_flops = float(d["flops"][0]) * args.replicas ** 3 if "flops" in d else None      # per GPU
     if args.workload == "argon" and args.steps > 1:
         # single LJ site: the neighbour-list loop accumulates the per-molecule virial on the last step of a run only; the other
         # launches are priced like the reference prices that case (FlopCounter.cpp:33-39: 35 instead of 41 flop per pair)
-        flops -= 6.0 * n_pairs * (args.steps - 1) / args.steps
+        flops -= 6.0 * (n_pairs / world) * (args.steps - 1) / args.steps
         model += "; minus 6 flop per pair on the %d of %d launches without per-molecule virial" % (args.steps - 1, args.steps)
-    force_ms = tm["force"]["ms"] / max(tm["force"]["launches"], 1)
+    force_ms = tm["force"]["ms"] / max(args.steps, 1)        # pair-kernel time per step
     achieved = flops / (force_ms * 1e-3) / 1e12 if force_ms > 0 else 0.0
     ref_u = float(d["upot_virial"][0]) / len(d["in_id"]) if "upot_virial" in d else u0 / n
-    line = {"metric": metric, "value": round(n * args.steps / (ms * 1e-3) / 1e6, 2), "unit": "MMUPS", "n_gpus": 1, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True, "dtype": "f64",
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+    line = {"metric": metric, "value": round(n * args.steps / (ms * 1e-3) / 1e6, 2), "unit": "MMUPS", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(ms / args.steps, 4), "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
             "data": "reference example input (golden fixture), replicated",
-            "config": {"workload": args.workload, "replicas": args.replicas, "n_molecules": n, "rc": float(d["rc"][0]), "dt": dt,
+            "config": {"workload": args.workload, "replicas_per_gpu": args.replicas, "rank_grid": grid, "n_molecules": n, "rc": float(d["rc"][0]), "dt": dt, "neighbour_lists": lists,
                        "target_T": temp, "upot_per_molecule_t0": u0 / n, "reference_upot_per_molecule_t0": ref_u,
                        "upot_rel_dev_t0": abs(u0 / n - ref_u) / abs(ref_u), "T_last": float((rec[-1, 2] + rec[-1, 3]) / (3 * rec[-1, 4] + rec[-1, 5]))},
             "gpu_launches": int(sum(t["launches"] for t in tm.values())),
@@ -229,7 +278,7 @@ def main():
                          "model": model, "reference_fixture_flops_x_replicas3": fixture_flops,
                          "kernel_calls": {k: float(v) for k, v in zip(("lj", "charge", "charge_dipole", "dipole", "charge_quadrupole", "dipole_quadrupole", "quadrupole"), fc["kernel"]) if v}},
             "kernel_ms_per_step": {k: round(t["ms"] / args.steps, 4) for k, t in tm.items()}, "clocks": clk}
-    if not args.no_e2e:
+    if not args.no_e2e and world == 1:
         md = run_reference(d, temp, args.e2e_replicas, args.steps, threads, ls1g, gpu=True)
         if md is not None:
             line["e2e"] = {"value": round(md["mmups_e2e"], 2), "unit": "MMUPS", "h2d_bytes_per_step": md["h2d_bytes"] // args.steps,
@@ -239,13 +288,15 @@ def main():
                            "seconds": {"upload": round(md["upload_s"], 4), "loop": round(md["loop_s"], 4), "of_loop_device_calls": round(md["device_s"], 4),
                                        "of_loop_final_mirror": round(md["mirror_s"], 4)},
                            "selective_thermostat_steps": md["selective"]}
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and world == 1:
         res = run_reference(d, temp, args.ref_replicas, args.ref_steps, threads, ls1g)
         if res is not None:
             line["cpu_baseline"] = {"value": round(res["mmups"], 4), "unit": "MMUPS", "cores": threads, "kind": "reference",
                                     "sample": "%s, same example replicated %d^3 = %d molecules x %d steps, OpenMP %d threads, loop %.2f s"
                                               % (res["binary"], args.ref_replicas, res["n"], args.ref_steps, threads, res["loop_s"])}
     print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
     return 0
 
 

@@ -94,6 +94,9 @@ typedef struct {
 
 const char* ls1g_last_error(void);
 int ls1g_version(void);
+/* CUDA devices visible to this process (a container that spreads its box over several GPUs maps rank r to device r mod count).
+ * replaces: the rank count of MPI_Comm_size (DomainDecompMPIBase.cpp:36-40) for a single-process multi-GPU run */
+int ls1g_device_count(int* n);
 
 /* --- life cycle --------------------------------------------------------------------------
  * replaces: Simulation::readXML datastructure dispatch + container->rebuild (Simulation.cpp:411-450) */
@@ -141,7 +144,9 @@ int ls1g_upload_forces(ls1g_ctx* ctx, size_t n, const double* F, const double* M
 /* number of molecules held: owned (non-halo cells) and halo copies */
 int ls1g_count(ls1g_ctx* ctx, uint64_t* n_owned, uint64_t* n_halo);
 /* replaces: ParticleIterator over ALL_CELLS / ONLY_INNER_AND_BOUNDARY + Molecule getters.
- * Molecules come in cell-sorted order; include_halo selects ALL_CELLS. Returns count in *n_out. */
+ * Molecules come in cell-sorted order; include_halo selects ALL_CELLS. Returns count in *n_out.
+ * field_mask 0 copies nothing and only reports the count (capacity is ignored): during an ls1g_run / ls1g_step sequence molecules
+ * that left the block stay with it until the next exchange, so ls1g_count may differ from what a download returns afterwards. */
 int ls1g_download(ls1g_ctx* ctx, int field_mask, int include_halo, size_t capacity,
                   ls1g_fields* out, size_t* n_out);
 /* Raw SLOTS [first, first + count) of the device's cell-sorted storage, 0 <= first + count <= ls1g_slot_count: owned molecules in

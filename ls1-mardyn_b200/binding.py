@@ -20,7 +20,7 @@ EXPORTS = [
     "ls1g_integrate_pre", "ls1g_integrate_post", "ls1g_scale", "ls1g_selective_thermostat", "ls1g_run", "ls1g_step", "ls1g_host_alloc", "ls1g_host_free", "ls1g_decomp_box", "ls1g_decomp_grid",
     "ls1g_comm_unique_id", "ls1g_comm_init", "ls1g_allreduce_sum", "ls1g_comm_init_local", "ls1g_exchange_group",
     "ls1g_timers", "ls1g_measure_fp64_peak", "ls1g_last_pair_count", "ls1g_flop_count", "ls1g_rdf", "ls1g_reserve", "ls1g_download_range", "ls1g_slot_count",
-    "ls1g_run_group", "ls1g_step_group", "ls1g_list_stats", "ls1g_cell_index_of_points_noalloc",
+    "ls1g_run_group", "ls1g_step_group", "ls1g_list_stats", "ls1g_cell_index_of_points_noalloc", "ls1g_device_count",
 ]
 
 FIELDS = dict(id=1, cid=2, r=4, v=8, q=16, L=32, F=64, M=128, Vi=256, cell=512)
@@ -302,8 +302,9 @@ class Container:
     def download(self, fields=("id", "cid", "r", "v", "q", "L", "F", "M", "Vi", "cell"), include_halo=False, out=None):
         """molecules in cell-sorted order (ParticleIterator over ONLY_INNER_AND_BOUNDARY / ALL_CELLS).
         out: optional dict of preallocated (e.g. pinned) arrays to fill instead of allocating"""
-        no, nh = self.count()
-        cap = no + nh
+        n = C.c_size_t()
+        _chk(lib().ls1g_download(self._ctx, 0, int(bool(include_halo)), C.c_size_t(0), C.byref(_Fields()), C.byref(n)))      # count query
+        cap = n.value
         shapes = dict(id=((cap,), np.uint64), cid=((cap,), np.uint32), r=((cap, 3), np.float64), v=((cap, 3), np.float64),
                       q=((cap, 4), np.float64), L=((cap, 3), np.float64), F=((cap, 3), np.float64), M=((cap, 3), np.float64),
                       Vi=((cap, 3), np.float64), cell=((cap,), np.uint32))

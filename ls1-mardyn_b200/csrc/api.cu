@@ -12,6 +12,14 @@ static thread_local std::string g_err;
 void ls1g_set_error(const std::string& msg) { g_err = msg; }
 extern "C" const char* ls1g_last_error(void) { return g_err.c_str(); }
 extern "C" int ls1g_version(void) { return 100; }
+extern "C" int ls1g_device_count(int* n) {
+	if (!n) LS1G_FAIL("null argument");
+	*n = 0;
+	cudaError_t e = cudaGetDeviceCount(n);
+	if (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver) { *n = 0; (void)cudaGetLastError(); return 0; }      // a host without a usable GPU: 0 devices
+	if (e != cudaSuccess) { *n = 0; LS1G_FAIL(std::string("ls1g_device_count: ") + cudaGetErrorString(e)); }
+	return 0;
+}
 
 
 // ------------------------------------------------------------------------------------------------
@@ -180,6 +188,7 @@ extern "C" int ls1g_create(const ls1g_config* cfg, ls1g_ctx** out) {
 	// the pass costs ~6 ms per build at 10^7 molecules and saves ~0.19 ms per step, so it pays for lattices and cold systems, not for a
 	// liquid whose lists expire every ~18 steps (profiles/r02c_permute_tradeoff.json)
 	{ const char* lp = getenv("LS1G_LIST_PERMUTE"); c->list_permute = lp ? (atoi(lp) == 0 ? 0 : 1) : 2; }
+	{ const char* lm = getenv("LS1G_LIST_MULTISITE"); c->list_multisite = lm && atoi(lm) == 0 ? 0 : 1; }
 	{ const char* sk = getenv("LS1G_SKIN"); c->skin = sk ? atof(sk) : 0.12 * c->cfg.cutoff; if (c->skin < 0.) c->skin = 0.; }
 	c->rc2 = c->cfg.cutoff * c->cfg.cutoff;
 	c->rclj2 = c->cfg.lj_cutoff * c->cfg.lj_cutoff;
@@ -430,6 +439,7 @@ extern "C" int ls1g_download(ls1g_ctx* c, int mask, int include_halo, size_t cap
 	bool halo_ok = include_halo && c->n_halo > 0;
 	size_t n_ret = halo_ok ? c->n_owned + c->n_halo : c->n_owned;
 	*n_out = n_ret;
+	if (mask == 0) return 0;      // count query: the number a following download returns (the list layout has been left above)
 	if (capacity < n_ret) LS1G_FAIL("ls1g_download: capacity too small");
 	(void)ns;
 	CUDA_TRY(cudaStreamSynchronize(c->stream));

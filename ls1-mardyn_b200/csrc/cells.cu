@@ -97,7 +97,7 @@ __global__ void cell_index_kernel(Grid g, size_t n, const double* __restrict__ p
 
 // bin: cell[] holds HALO_FLAG for stale halo copies (skipped, marked 0xFFFFFFFF).
 __global__ void __launch_bounds__(256) bin_kernel(Grid g, size_t n, double4* __restrict__ pos, uint32_t* __restrict__ cell,
-                                                   uint32_t* __restrict__ count, int make_images) {
+                                                   uint32_t* __restrict__ count, int make_images, uint32_t* __restrict__ bad) {
 	size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (i >= n) return;
 	uint32_t c0 = cell[i];
@@ -108,6 +108,13 @@ __global__ void __launch_bounds__(256) bin_kernel(Grid g, size_t n, double4* __r
 		double y = g.self_periodic[1] ? wrap_coord(g, 1, p.y) : p.y;
 		double z = g.self_periodic[2] ? wrap_coord(g, 2, p.z) : p.z;
 		if (x != p.x || y != p.y || z != p.z) { p.x = x; p.y = y; p.z = z; pos[i] = p; }
+	}
+	// a molecule that is still outside the halo region (or not finite) after the wrap moved more than a box length in one step or
+	// carries NaN: the system has exploded.  Reported through *bad; the reference ends such a run too (its cell lookup fails)
+	if (!(p.x >= g.halo_min[0] && p.x <= g.halo_max[0] && p.y >= g.halo_min[1] && p.y <= g.halo_max[1] && p.z >= g.halo_min[2] && p.z <= g.halo_max[2])) {
+		atomicAdd(bad, 1u);
+		cell[i] = 0xFFFFFFFFu;
+		return;
 	}
 	uint32_t c = grid_cell_index(g, p.x, p.y, p.z);
 	cell[i] = c;
@@ -391,14 +398,20 @@ int k_sort(ls1g_ctx* c, int make_images) {
 	CUDA_TRY(cudaMemsetAsync(c->cell_count, 0, sizeof(uint32_t) * (nc + 1), c->stream));
 	CUDA_TRY(cudaMemsetAsync(c->cell_fill, 0, sizeof(uint32_t) * (nc + 1), c->stream));
 	int launches = 0;
-	if (n) { bin_kernel<<<nblk(n, 256), 256, 0, c->stream>>>(g, n, c->cur.pos, c->cur.cell, c->cell_count, make_images); ++launches; }
+	CUDA_TRY(cudaMemsetAsync(c->d_counters + 9, 0, sizeof(uint32_t), c->stream));
+	if (n) { bin_kernel<<<nblk(n, 256), 256, 0, c->stream>>>(g, n, c->cur.pos, c->cur.cell, c->cell_count, make_images, c->d_counters + 9); ++launches; }
 	if (ls1g_scan_cells(c, c->cell_count, c->cell_start)) return 1;
 	CUDA_TRY(cudaMemsetAsync(c->d_counters + 7, 0, 2 * sizeof(uint32_t), c->stream));
 	row_max_kernel<<<nblk((size_t)(g.cpd[1] - 2) * (g.cpd[2] - 2), 256), 256, 0, c->stream>>>(g, c->cell_start, c->d_counters + 7);
 	bundle_max_kernel<<<nblk((size_t)((g.cpd[1] - 1) / 2) * ((g.cpd[2] - 1) / 2), 256), 256, 0, c->stream>>>(g, c->cell_start, c->d_counters + 8);
 	launches += 5;
-	CUDA_TRY(cudaMemcpyAsync(c->h_counters, c->d_counters, 9 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+	CUDA_TRY(cudaMemcpyAsync(c->h_counters, c->d_counters, 10 * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
 	CUDA_TRY(cudaStreamSynchronize(c->stream));
+	if (c->h_counters[9]) {
+		timer_stop(c, LS1G_T_SORT, launches);
+		LS1G_FAIL("ls1g: " + std::to_string(c->h_counters[9]) + " molecule(s) outside the halo region or not finite after the periodic wrap - the system has "
+		          "exploded (time step too large for this state?)");
+	}
 	size_t n_new = c->h_counters[0];
 	c->max_row = c->h_counters[7];
 	c->max_bundle = c->h_counters[8];

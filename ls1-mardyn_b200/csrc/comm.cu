@@ -144,22 +144,29 @@ __global__ void __launch_bounds__(256) translate_slots_kernel(size_t n, const ui
 	size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (k < n) post[k] = new_of_old[pre ? pre[k] : base + (uint32_t)k];
 }
-// positions only: 3 doubles per record, shifted along the stage dimension when the neighbour is across the global boundary
-__global__ void __launch_bounds__(256) pack_pos_list_kernel(size_t n, const uint32_t* __restrict__ slots, const double4* __restrict__ pos, int dim, double shift,
-                                                             double* __restrict__ out) {
-	size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-	if (k >= n) return;
-	double4 p = pos[slots[k]];
-	if (dim == 0) p.x += shift; else if (dim == 1) p.y += shift; else p.z += shift;
-	out[3 * k] = p.x; out[3 * k + 1] = p.y; out[3 * k + 2] = p.z;
-}
-__global__ void __launch_bounds__(256) unpack_pos_list_kernel(size_t n, const uint32_t* __restrict__ slots, const double* __restrict__ in, double4* __restrict__ pos) {
+// positions only: 3 doubles per record (7 with the orientation of a rigid molecule), shifted along the stage dimension when the
+// neighbour is across the global boundary
+__global__ void __launch_bounds__(256) pack_pos_list_kernel(size_t n, const uint32_t* __restrict__ slots, const double4* __restrict__ pos, const double4* __restrict__ q,
+                                                             int dim, double shift, double* __restrict__ out) {
 	size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (k >= n) return;
 	const uint32_t s = slots[k];
 	double4 p = pos[s];
-	p.x = in[3 * k]; p.y = in[3 * k + 1]; p.z = in[3 * k + 2];
+	if (dim == 0) p.x += shift; else if (dim == 1) p.y += shift; else p.z += shift;
+	const int w = q ? 7 : 3;
+	out[w * k] = p.x; out[w * k + 1] = p.y; out[w * k + 2] = p.z;
+	if (q) { const double4 qq = q[s]; out[w * k + 3] = qq.x; out[w * k + 4] = qq.y; out[w * k + 5] = qq.z; out[w * k + 6] = qq.w; }
+}
+__global__ void __launch_bounds__(256) unpack_pos_list_kernel(size_t n, const uint32_t* __restrict__ slots, const double* __restrict__ in, double4* __restrict__ pos,
+                                                               double4* __restrict__ q) {
+	size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+	if (k >= n) return;
+	const uint32_t s = slots[k];
+	const int w = q ? 7 : 3;
+	double4 p = pos[s];
+	p.x = in[w * k]; p.y = in[w * k + 1]; p.z = in[w * k + 2];
 	pos[s] = p;
+	if (q) q[s] = make_double4(in[w * k + 3], in[w * k + 4], in[w * k + 5], in[w * k + 6]);
 }
 
 __global__ void __launch_bounds__(256) unpack_kernel(const double* __restrict__ in, size_t n, size_t base, MolBuf m, int has_rot, int rec,
@@ -448,7 +455,7 @@ int comm_refresh(const Group& G) {
 			}
 			for (int k = 0; k < 2; ++k)
 				if (c->xl_n_send[d][k]) {
-					pack_pos_list_kernel<<<nblk(c->xl_n_send[d][k], 256), 256, 0, c->stream>>>(c->xl_n_send[d][k], c->xl_send[d][k], c->cur.pos, d, shift[k], c->send_buf[k]);
+					pack_pos_list_kernel<<<nblk(c->xl_n_send[d][k], 256), 256, 0, c->stream>>>(c->xl_n_send[d][k], c->xl_send[d][k], c->cur.pos, c->has_rot ? c->cur.q : nullptr, d, shift[k], c->send_buf[k]);
 					++launches[r];
 				}
 			if (local) CUDA_TRY(cudaEventRecord(c->ev_pack, c->stream));
@@ -457,25 +464,26 @@ int comm_refresh(const Group& G) {
 			ls1g_ctx* c = G.c[r];
 			set_dev(c);
 			const int lower = neighbour_rank(c, d, 0), upper = neighbour_rank(c, d, 1);
+			const size_t pw = c->has_rot ? 7 : 3;      // doubles per refreshed halo molecule
 			if (local) {
 				ls1g_ctx *up = G.c[upper], *lo = G.c[lower];
 				CUDA_TRY(cudaStreamWaitEvent(c->stream, up->ev_pack, 0));
 				CUDA_TRY(cudaStreamWaitEvent(c->stream, lo->ev_pack, 0));
-				if (c->xl_n_recv[d][0]) CUDA_TRY(cudaMemcpyAsync(c->recv_buf[0], up->send_buf[0], (size_t)c->xl_n_recv[d][0] * 3 * sizeof(double), cudaMemcpyDefault, c->stream));
-				if (c->xl_n_recv[d][1]) CUDA_TRY(cudaMemcpyAsync(c->recv_buf[1], lo->send_buf[1], (size_t)c->xl_n_recv[d][1] * 3 * sizeof(double), cudaMemcpyDefault, c->stream));
+				if (c->xl_n_recv[d][0]) CUDA_TRY(cudaMemcpyAsync(c->recv_buf[0], up->send_buf[0], (size_t)c->xl_n_recv[d][0] * pw * sizeof(double), cudaMemcpyDefault, c->stream));
+				if (c->xl_n_recv[d][1]) CUDA_TRY(cudaMemcpyAsync(c->recv_buf[1], lo->send_buf[1], (size_t)c->xl_n_recv[d][1] * pw * sizeof(double), cudaMemcpyDefault, c->stream));
 				CUDA_TRY(cudaEventRecord(c->ev_read, c->stream));
 			} else {
 				ncclComm_t comm = (ncclComm_t)c->nccl_comm;
 				NCCL_TRY(g_nccl.GroupStart());
-				if (c->xl_n_send[d][0]) NCCL_TRY(g_nccl.Send(c->send_buf[0], (size_t)c->xl_n_send[d][0] * 3, NCCL_DOUBLE, lower, comm, c->stream));
-				if (c->xl_n_send[d][1]) NCCL_TRY(g_nccl.Send(c->send_buf[1], (size_t)c->xl_n_send[d][1] * 3, NCCL_DOUBLE, upper, comm, c->stream));
-				if (c->xl_n_recv[d][0]) NCCL_TRY(g_nccl.Recv(c->recv_buf[0], (size_t)c->xl_n_recv[d][0] * 3, NCCL_DOUBLE, upper, comm, c->stream));
-				if (c->xl_n_recv[d][1]) NCCL_TRY(g_nccl.Recv(c->recv_buf[1], (size_t)c->xl_n_recv[d][1] * 3, NCCL_DOUBLE, lower, comm, c->stream));
+				if (c->xl_n_send[d][0]) NCCL_TRY(g_nccl.Send(c->send_buf[0], (size_t)c->xl_n_send[d][0] * pw, NCCL_DOUBLE, lower, comm, c->stream));
+				if (c->xl_n_send[d][1]) NCCL_TRY(g_nccl.Send(c->send_buf[1], (size_t)c->xl_n_send[d][1] * pw, NCCL_DOUBLE, upper, comm, c->stream));
+				if (c->xl_n_recv[d][0]) NCCL_TRY(g_nccl.Recv(c->recv_buf[0], (size_t)c->xl_n_recv[d][0] * pw, NCCL_DOUBLE, upper, comm, c->stream));
+				if (c->xl_n_recv[d][1]) NCCL_TRY(g_nccl.Recv(c->recv_buf[1], (size_t)c->xl_n_recv[d][1] * pw, NCCL_DOUBLE, lower, comm, c->stream));
 				NCCL_TRY(g_nccl.GroupEnd());
 			}
 			for (int k = 0; k < 2; ++k)
 				if (c->xl_n_recv[d][k]) {
-					unpack_pos_list_kernel<<<nblk(c->xl_n_recv[d][k], 256), 256, 0, c->stream>>>(c->xl_n_recv[d][k], c->xl_recv[d][k], c->recv_buf[k], c->cur.pos);
+					unpack_pos_list_kernel<<<nblk(c->xl_n_recv[d][k], 256), 256, 0, c->stream>>>(c->xl_n_recv[d][k], c->xl_recv[d][k], c->recv_buf[k], c->cur.pos, c->has_rot ? c->cur.q : nullptr);
 					++launches[r];
 				}
 		}

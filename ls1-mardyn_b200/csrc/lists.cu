@@ -1,6 +1,7 @@
 // lists.cu — host side of the neighbour-list mode of ls1g_run (kernels in lists.cuh).
 #include "ls1g_internal.cuh"
 #include "potentials.cuh"
+#include "pair_body.cuh"
 #include "lists.cuh"
 
 #include <math.h>
@@ -14,17 +15,17 @@ int ls1g_prereduce(ls1g_ctx* c, size_t& nb, int nv, const double*& base);   // f
 
 static inline unsigned nblk(size_t n, unsigned t) { return (unsigned)((n + t - 1) / t); }
 
-// list mode applies to: single-centre LJ, default kernels, skin > 0, not disabled by an earlier overflow; one rank or several with
+// list mode applies to: single-centre LJ and (LS1G_LIST_MULTISITE=0 switches that off) rigid multi-site systems, default kernels, skin > 0, not disabled by an earlier overflow; one rank or several with
 // either transport (NCCL, in-process group)
 int nl_applicable(const ls1g_ctx* c) {
-	return c->simple_1clj && (c->n_ranks == 1 || c->comm_mode == 1 || c->comm_mode == 2) && c->force_variant == 0 && c->skin > 0. && !c->list_disabled;
+	return (c->simple_1clj || c->list_multisite) && (c->n_ranks == 1 || c->comm_mode == 1 || c->comm_mode == 2) && c->force_variant == 0 && c->skin > 0. && !c->list_disabled;
 }
 
 // switch the bin grid: cells >= cutoff + skin (list mode) or the reference grid
 int nl_set_bin_grid(ls1g_ctx* c, int list_mode) {
 	if (!list_mode) { c->bgrid = c->grid; return 0; }
 	Grid g;
-	if (grid_init_cut(g, c->cfg, c->cfg.cutoff + c->skin, -1)) return 1;
+	if (grid_init_cut(g, c->cfg, std::max(c->cfg.cutoff, c->cfg.lj_cutoff) + c->skin, -1)) return 1;
 	if (g.n_cells > c->grid.n_cells) LS1G_FAIL("neighbour-list grid larger than the reference grid");
 	c->bgrid = g;
 	return 0;
@@ -36,7 +37,7 @@ static NLArgs nl_args(ls1g_ctx* c) {
 	a.lists = c->lists; a.lcount = c->lcount; a.plans = (NLPlan*)c->plans; a.flags = c->d_flags; a.bpr = c->list_bpr; a.nyi = c->bgrid.cpd[1] - 2; a.lcap4 = c->list_lcap / 4; a.btcap = c->build_tcap;
 	a.nzi = c->bgrid.cpd[2] - 2; a.nyg = (a.nyi + 1) / 2;
 	a.tcap = NL_TCAP;
-	const double rl = c->cfg.lj_cutoff + c->skin;
+	const double rl = std::max(c->cfg.lj_cutoff, c->cfg.cutoff) + c->skin;
 	// FP32 filter: coordinates relative to the block centre are < 8 cell lengths: relative error on r^2 near rl^2 < 2e-5;
 	// the 3e-4 margin can only over-accept (the force kernel applies the exact FP64 test)
 	a.rl2f = (float)(rl * rl * (1.0 + 3e-4));
@@ -139,7 +140,7 @@ int k_list_reserve(ls1g_ctx* c, size_t n) {
 		CUDA_TRY(cudaFuncGetAttributes(&fa, fused_finalize_kernel));
 	}
 	Grid g;
-	if (grid_init_cut(g, c->cfg, c->cfg.cutoff + c->skin, -1)) return 1;
+	if (grid_init_cut(g, c->cfg, std::max(c->cfg.cutoff, c->cfg.lj_cutoff) + c->skin, -1)) return 1;
 	if (c->list_lcap < NL_LCAP0) c->list_lcap = NL_LCAP0;
 	const size_t nx = g.cpd[0] - 2, nyi = g.cpd[1] - 2, nzi = g.cpd[2] - 2;
 	const int R = (c->list_R == 1 || nyi < 2 || nzi < 2) ? 1 : 4;
@@ -293,10 +294,150 @@ int k_forces_list_post(ls1g_ctx* c, double dt, int vi) {
 	return 0;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// multi-site molecules on the same lists
+// ---------------------------------------------------------------------------------------------------------------
+// The list build works on molecule centres with the radius max(rc, rc_LJ) + skin and does not care what a molecule is made of, so
+// rigid multi-site systems (VectorizedCellProcessor.cpp:1013-1024: both cutoffs are decided on the molecule centres) use the same
+// frozen layout, plans and 16-bit lists.  The force kernel differs: the site loops of ONE molecule pair are hundreds of FP64
+// instructions (CO2: 9 LJ + 9 charge pairs), so lanes work independently - no shared tile; a partner's world-frame site rows come
+// from the site cache (L2), its slot from the stored plan (tile index -> row -> slot).  128 threads per block over the build's lane
+// numbering (a build block of 128 or 512 lanes is a whole number of these blocks).  Same pair functions and calcFM epilogue as
+// force_generic_kernel (pair_body.cuh); per-block partials [5] as there.
+#define NLM_THREADS 128
+#ifndef NLM_MINB
+#define NLM_MINB 3         // resident blocks per SM the register allocation aims at
+#endif
+struct NLMArgs {
+	const unsigned short* lists; const uint32_t* lcount; const NLPlan* plans;
+	int lcap4, BT, R;
+	size_t n_lanes;
+	const unsigned long long* guard; unsigned long long guard_thr;
+};
+
+template <int NLJ, int NCH, int NDI, int NQU>
+__global__ void __launch_bounds__(NLM_THREADS, NLM_MINB) nl_force_ms_kernel(ForceArgs a, NLMArgs m) {
+	constexpr bool FIXED = NLJ >= 0;
+	constexpr int NS = FIXED ? NLJ + NCH + 2 * NDI + 2 * NQU : 1;
+	__shared__ double red[5 * 32];
+	__shared__ NLPlan P;
+	if (m.guard && *m.guard > m.guard_thr) return;      // speculatively enqueued step, lists expired (see run_list_steps)
+	const int tid = threadIdx.x;
+	const size_t gl = (size_t)blockIdx.x * NLM_THREADS + tid;
+	const size_t blk = ((size_t)blockIdx.x * NLM_THREADS) / (size_t)m.BT;      // the same for the whole block
+	if (tid < (int)(sizeof(NLPlan) / 4)) ((uint32_t*)&P)[tid] = ((const uint32_t*)(m.plans + blk))[tid];
+	__syncthreads();
+	const int t = (int)(gl - blk * (size_t)m.BT);
+	const int NR = m.R == 4 ? 16 : 9;
+	double acc[5] = {0., 0., 0., 0., 0.};
+	int q = 0;
+	if (m.R == 4) q = (t >= P.o[1]) + (t >= P.o[2]) + (t >= P.o[3]);
+	const bool owned = P.live && t < P.o[m.R];
+	const size_t i = (size_t)P.s0[q] + (size_t)(t - P.o[q]);
+	if (owned) {
+		const double4 Pi = a.pos[i];
+		const V3 Ri = ld3(Pi);
+		CompDev ci; ci.n_lj = ci.n_ch = ci.n_di = ci.n_qu = 0;
+		ci = a.comps[pos_cid(Pi)];
+		const double4* si = a.cache + i * (size_t)a.stride;
+		const int i_ch0 = ci.n_lj, i_di0 = ci.n_lj + ci.n_ch, i_qu0 = i_di0 + 2 * ci.n_di;
+		double4 sir[NS];
+		if (FIXED) {
+#pragma unroll
+			for (int k = 0; k < NS; ++k) sir[k] = si[k];
+		}
+		MolAcc A_; A_.F = v3(0, 0, 0); A_.M = v3(0, 0, 0); A_.V = v3(0, 0, 0); A_.u6 = 0.; A_.uX = 0.; A_.rf = 0.; A_.np = 0;
+		const uint32_t cnt = m.lcount[gl];
+		const int n4 = (int)(cnt & 0xffffu);
+		const uint2* my = (const uint2*)(m.lists + ((size_t)blk * m.lcap4 * m.BT + t) * 4);
+		for (int o = 0; o < n4; ++o) {
+			const uint2 w = my[(size_t)o * m.BT];
+			const uint32_t ee[4] = {w.x & 0xffffu, w.x >> 16, w.y & 0xffffu, w.y >> 16};
+#pragma unroll 1
+			for (int u = 0; u < 4; ++u) {
+				if (!ee[u]) continue;                               // pad entry
+				const int k = (int)(ee[u] >> 3) - NL_DUMMY;         // tile index
+				int r = 0;
+				while (r + 1 < NR && k >= P.off[r + 1]) ++r;
+				const uint32_t jj = P.beg[r] + (uint32_t)(k - P.off[r]);
+				const double4 Pj = a.pos[jj];
+				const V3 mm = v3(Ri.x - Pj.x, Ri.y - Pj.y, Ri.z - Pj.z);
+				const double m2 = dot(mm, mm);
+				const bool in_lj = m2 < a.rclj2, in_rc = m2 < a.rc2;
+				// coincident centres lie in the same cell: the reference's SingleCellPolicy_ mask skips them (Helpers.h:367-376)
+				if (!(in_lj || in_rc) || m2 == 0.0) continue;
+				++A_.np;
+				if constexpr (FIXED) {
+					double4 sjr[NS];
+					const double4* sj = a.cache + (size_t)jj * a.stride;
+#pragma unroll
+					for (int kk = 0; kk < NS; ++kk) sjr[kk] = sj[kk];
+					pair_body_fixed<NLJ, NCH, NDI, NQU>(a, Ri, sir, sjr, mm, in_lj, in_rc, A_);
+				} else {
+					pair_body(a, Ri, ci, si, i_ch0, i_di0, i_qu0, jj, Pj, mm, in_lj, in_rc, A_);
+				}
+			}
+		}
+		a.F[3 * i] = A_.F.x; a.F[3 * i + 1] = A_.F.y; a.F[3 * i + 2] = A_.F.z;
+		a.M[3 * i] = A_.M.x; a.M[3 * i + 1] = A_.M.y; a.M[3 * i + 2] = A_.M.z;
+		a.Vi[3 * i] = 0.5 * A_.V.x; a.Vi[3 * i + 1] = 0.5 * A_.V.y; a.Vi[3 * i + 2] = 0.5 * A_.V.z;
+		acc[0] = A_.u6; acc[1] = A_.uX; acc[2] = A_.V.x + A_.V.y + A_.V.z; acc[3] = A_.rf; acc[4] = (double)A_.np;
+	}
+	block_sum<5>(acc, red);
+	if (tid == 0) {
+#pragma unroll
+		for (int k = 0; k < 5; ++k) a.partials[(size_t)blockIdx.x * 5 + k] = acc[k];
+	}
+}
+
+int k_site_cache(ls1g_ctx* c);      // force.cu
+// list force pass of a multi-site system: site cache of all slots, then the list kernel; leaves upot, virial, pairs in d_scalars[0..3]
+int k_forces_list_ms(ls1g_ctx* c) {
+	const size_t nb = nl_blocks(c);
+	const size_t lanes = nb * nl_bt(c);
+	const unsigned grid = nblk(lanes, NLM_THREADS);
+	if (ls1g_ensure_partials(c, grid ? grid : 1, 5)) return 1;
+	if (k_site_cache(c)) return 1;
+	ForceArgs a;
+	a.g = c->bgrid; a.n = c->n_slots; a.pos = c->cur.pos; a.cell = c->cur.cell; a.cell_start = c->cell_start;
+	a.comps = c->comps; a.cache = c->site_cache; a.stride = c->cache_stride;
+	a.eps24 = c->eps24; a.sig2 = c->sig2; a.shift6 = c->shift6; a.S = c->S_lj;
+	a.rc2 = c->rc2; a.rclj2 = c->rclj2; a.epsRFInvrc3 = c->epsRFInvrc3;
+	a.F = c->F; a.M = c->M; a.Vi = c->Vi; a.partials = c->partials;
+	a.bpr = c->list_bpr; a.nyi = c->bgrid.cpd[1] - 2;
+	NLMArgs m;
+	m.lists = c->lists; m.lcount = c->lcount; m.plans = (const NLPlan*)c->plans; m.lcap4 = c->list_lcap / 4; m.BT = (int)nl_bt(c); m.R = c->list_R;
+	m.n_lanes = lanes;
+	m.guard = c->guard_on ? c->d_flags + 3 : nullptr; m.guard_thr = (unsigned long long)host_double_bits(c->disp_thr2);
+	const CompDev& c0 = c->comps_h[0];
+	const int key = c->n_comp == 1 && c->S_lj <= 4 ? c0.n_lj * 1000 + c0.n_ch * 100 + c0.n_di * 10 + c0.n_qu : -1;
+	if (key >= 0)
+		for (int k = 0; k < c->S_lj * c->S_lj; ++k) { a.eps24_c[k] = c->eps24_h[k]; a.sig2_c[k] = c->sig2_h[k]; a.shift6_c[k] = c->shift6_h[k]; }
+	timer_start(c, LS1G_T_FORCE);
+	if (grid) {
+		switch (key) {
+#define LS1G_FIXED_CASE(L, Q, D, U) case L * 1000 + Q * 100 + D * 10 + U: nl_force_ms_kernel<L, Q, D, U><<<grid, NLM_THREADS, 0, c->stream>>>(a, m); break;
+		LS1G_FIXED_CASE(3, 3, 0, 0)      // CO2 (3 LJ + 3 charges), examples/CO2
+		LS1G_FIXED_CASE(3, 0, 1, 0)      // ethylene oxide (3 LJ + dipole), examples/EOX
+		LS1G_FIXED_CASE(3, 0, 0, 1)      // CO2 Merker (3 LJ + quadrupole)
+		LS1G_FIXED_CASE(2, 0, 0, 1)      // 2CLJQ
+		LS1G_FIXED_CASE(2, 0, 1, 0)      // 2CLJD
+		LS1G_FIXED_CASE(1, 0, 1, 0)      // Stockmayer
+		LS1G_FIXED_CASE(2, 0, 0, 0)      // 2CLJ
+		LS1G_FIXED_CASE(4, 0, 0, 0)      // 4 LJ sites
+#undef LS1G_FIXED_CASE
+		default: nl_force_ms_kernel<-1, 0, 0, 0><<<grid, NLM_THREADS, 0, c->stream>>>(a, m);
+		}
+	}
+	timer_stop(c, LS1G_T_FORCE, grid ? 1 : 0);
+	CUDA_TRY(cudaGetLastError());
+	return k_force_finalize(c, grid);
+}
+
 int k_halo_refresh(ls1g_ctx* c) {
 	if (c->n_slots == 0) return 0;
 	timer_start(c, LS1G_T_SORT);
-	halo_refresh_kernel<<<nblk(c->n_slots, 256), 256, 0, c->stream>>>(c->bgrid, c->n_slots, c->cur.pos, c->cur.cell, c->halo_src, c->halo_code);
+	halo_refresh_kernel<<<nblk(c->n_slots, 256), 256, 0, c->stream>>>(c->bgrid, c->n_slots, c->cur.pos, c->has_rot ? c->cur.q : nullptr, c->cur.cell, c->halo_src, c->halo_code);
 	timer_stop(c, LS1G_T_SORT, 1);
 	CUDA_TRY(cudaGetLastError());
 	return 0;

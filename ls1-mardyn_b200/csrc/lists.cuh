@@ -660,16 +660,18 @@ __global__ void __launch_bounds__(NLGeom<R>::BT, R == 1 ? 6 : 1024 / NLGeom<R>::
 
 // periodic images follow their source molecule (frozen layout; plain +-L shift, DomainDecompBase.cpp:326-341 without the
 // boundary guards, which only matter for cell assignment)
-__global__ void __launch_bounds__(256) halo_refresh_kernel(Grid g, size_t n, double4* __restrict__ pos, const uint32_t* __restrict__ cell,
+__global__ void __launch_bounds__(256) halo_refresh_kernel(Grid g, size_t n, double4* __restrict__ pos, double4* __restrict__ q, const uint32_t* __restrict__ cell,
                                                             const uint32_t* __restrict__ halo_src, const uint8_t* __restrict__ halo_code) {
 	size_t h = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
 	if (h >= n || !(cell[h] & HALO_FLAG)) return;
 	const int code = halo_code[h];
 	if (!code) return;
-	double4 p = pos[halo_src[h]];
+	const uint32_t src = halo_src[h];
+	double4 p = pos[src];
 	const int o0 = code % 3, o1 = (code / 3) % 3, o2 = code / 9;
 	if (o0) p.x = o0 == 1 ? p.x + g.box_len[0] : p.x - g.box_len[0];
 	if (o1) p.y = o1 == 1 ? p.y + g.box_len[1] : p.y - g.box_len[1];
 	if (o2) p.z = o2 == 1 ? p.z + g.box_len[2] : p.z - g.box_len[2];
 	pos[h] = p;
+	if (q) q[h] = q[src];      // rigid molecules: the image turns with its source
 }

@@ -135,6 +135,7 @@ extern "C" int ls1g_selective_thermostat(ls1g_ctx* c, double limit_trans_energy,
 int nl_applicable(const ls1g_ctx* c);
 int k_list_build(ls1g_ctx* c);
 int k_forces_list(ls1g_ctx* c, int count_pairs);
+int k_forces_list_ms(ls1g_ctx* c);               // lists.cu: rigid multi-site molecules on the same lists
 int k_forces_list_fused(ls1g_ctx* c, double dt, int phase);
 int k_forces_list_post(ls1g_ctx* c, double dt, int vi);
 int k_halo_refresh(ls1g_ctx* c);
@@ -195,8 +196,9 @@ static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, do
 	const bool dbg = getenv("LS1G_DEBUG") != nullptr;
 	// the integrator is fused into the force kernel on NVE steps (LS1G_FUSE=0 keeps the separate integrate kernel)
 	const char* fe = getenv("LS1G_FUSE");
-	const bool fuse_nve = !thermo && !c0->vi_every_step && !(fe && atoi(fe) == 0);
-	const bool post_fuse = !thermo && c0->n_ranks == 1 && !(fe && atoi(fe) == 0);      // single rank: the kinetic sums need no all-reduce
+	const bool ms = !c0->simple_1clj;        // rigid multi-site molecules: list force kernel + the separate (rotational) integrate kernel
+	const bool fuse_nve = !ms && !thermo && !c0->vi_every_step && !(fe && atoi(fe) == 0);
+	const bool post_fuse = !ms && !thermo && c0->n_ranks == 1 && !(fe && atoi(fe) == 0);      // single rank: the kinetic sums need no all-reduce
 	// several ranks: overlap the halo refresh with the inner blocks of the force pass (LS1G_OVERLAP=0: exchange first, then one launch)
 	const char* oe = getenv("LS1G_OVERLAP");
 	const bool overlap = G.multi() && !(oe && atoi(oe) == 0);
@@ -319,7 +321,7 @@ static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, do
 					if (!rc) rc = k_forces_list_post(c, dt, want_vi);
 					if (!rc) rc = rec_copy(c, s, 0, 8);
 				} else {
-					if (!rc) rc = k_forces_list(c, s + 1 == n_steps && want_vi);      // pair statistics + per-molecule virial only for the last step
+					if (!rc) rc = ms ? k_forces_list_ms(c) : k_forces_list(c, s + 1 == n_steps && want_vi);      // 1CLJ: pair statistics + per-molecule virial only for the last step
 					if (!rc) rc = rec_copy(c, s, 0, 4);
 				}
 			}

@@ -8,6 +8,7 @@
 #include "Simulation.h"
 #include "ensemble/EnsembleBase.h"
 #include "io/RDF.h"
+#include "particleContainer/adapter/FlopCounter.h"
 #include "molecules/Component.h"
 #include "molecules/Molecule.h"
 #include "particleContainer/adapter/CellProcessor.h"
@@ -21,6 +22,7 @@ extern "C" {
 #include "ls1g.h"
 }
 
+#include <algorithm>
 #include <atomic>
 #include <chrono>
 #include <cmath>
@@ -52,7 +54,7 @@ GpuLinkedCells::~GpuLinkedCells() {
 			if (_stagePinned) ls1g_host_free(_ctx, _stage);
 			else std::free(_stage);
 		}
-		ls1g_destroy(_ctx);
+		for (size_t r = _ctxs.size(); r-- > 0;) ls1g_destroy(_ctxs[r]);
 	}
 }
 
@@ -68,7 +70,7 @@ void GpuLinkedCells::printSummary() const {
 	global_log->info() << "GpuLinkedCells: " << _steps << " device steps took " << _tDevice << " s; upload "
 	                   << _tUpload << " s (" << _bytesUp << " B); " << _mirrors << " host mirror download(s) took "
 	                   << _tMirror << " s (" << _bytesDown << " B); context creation " << _tContext << " s; selective thermostat applied "
-	                   << _selective << " time(s); " << _rdfSamples << " RDF sample(s) on the device; first steps [s] " << _tFirstSteps[0] << " " << _tFirstSteps[1] << " "
+	                   << _selective << " time(s); " << _rdfSamples << " RDF and " << _flopSamples << " FLOP sample(s) on the device; first steps [s] " << _tFirstSteps[0] << " " << _tFirstSteps[1] << " "
 	                   << _tFirstSteps[2] << " " << _tFirstSteps[3] << ", slowest step " << _tMaxStep
 	                   << "; upload = gather " << _tGather << " + copy " << _tH2D << ", mirror = copy " << _tD2H << " + fill " << _tFill << std::endl;
 }
@@ -114,14 +116,25 @@ void GpuLinkedCells::readXML(XMLfileUnits& xmlconfig) {
 	}
 	std::string mirror = "auto";
 	xmlconfig.getNodeValue("mirrorfrequency", mirror);
-	if (mirror == "auto") {
-		_mirrorFrequency = mirrorFrequencyFromPlugins(xmlconfig);
-	} else {
+	std::string unknown = "refuse";
+	xmlconfig.getNodeValue("unknownplugins", unknown);
+	if (unknown != "refuse" && unknown != "readonly") {
+		global_log->error_always_output() << "GpuLinkedCells: <unknownplugins> is refuse (default) or readonly, not " << unknown << std::endl;
+		Simulation::exit(1);
+	}
+	_allowUnknownPlugins = unknown == "readonly";
+	_mirrorFrequency = mirrorFrequencyFromPlugins(xmlconfig);      // also refuses plugins that are not known to be read-only
+	if (mirror != "auto") {
 		_mirrorFrequency = static_cast<unsigned long>(xmlconfig.getNodeValue_long("mirrorfrequency", 0));
 	}
 	_device = xmlconfig.getNodeValue_int("device", 0);
+	_devices = xmlconfig.getNodeValue_int("devices", 1);
+	if (_devices < 1) {
+		global_log->error_always_output() << "GpuLinkedCells: <devices> must be >= 1" << std::endl;
+		Simulation::exit(1);
+	}
 	global_log->info() << "GpuLinkedCells: mode " << mode << ", mirror frequency " << _mirrorFrequency
-	                   << (mirror == "auto" ? " (from the plugins' write frequencies)" : "") << ", device " << _device << std::endl;
+	                   << (mirror == "auto" ? " (from the plugins' write frequencies)" : "") << ", device " << _device << ", blocks " << _devices << std::endl;
 }
 
 // <mirrorfrequency>auto</mirrorfrequency> (the default): the end-of-step plugins that read molecules decide on which steps
@@ -132,7 +145,7 @@ void GpuLinkedCells::readXML(XMLfileUnits& xmlconfig) {
 unsigned long GpuLinkedCells::mirrorFrequencyFromPlugins(XMLfileUnits& xmlconfig) const {
 	static const std::set<std::string> noMolecules = {"ResultWriter", "SysMonOutput", "TimerWriter", "LoadbalanceWriter",
 	                                                  "DecompWriter", "CommunicationPartnerWriter", "KDTreePrinter",
-	                                                  "RDF"};      // RDF: its traversal is counted on the device (sampleRDF)
+	                                                  "RDF", "FlopRateWriter"};      // their traversals are counted on the device (sampleRDF, sampleFlops)
 	static const std::set<std::string> readers = {"CheckpointWriter", "MPICheckpointWriter", "XyzWriter", "MmpldWriter",
 	                                              "MmspdWriter", "MmspdBinWriter", "PovWriter", "VISWriter", "MaxWriter",
 	                                              "EnergyLogWriter"};
@@ -151,10 +164,19 @@ unsigned long GpuLinkedCells::mirrorFrequencyFromPlugins(XMLfileUnits& xmlconfig
 			if (readers.count(name) != 0) {
 				const long w = xmlconfig.getNodeValue_long(name == "MmpldWriter" ? "writecontrol/writefrequency" : "writefrequency", 1);
 				f = w > 0 ? static_cast<unsigned long>(w) : 1;
+			} else if (_allowUnknownPlugins) {
+				global_log->warning() << "GpuLinkedCells: plugin " << name << " is not known to be a read-only end-of-step writer "
+				                      << "(<unknownplugins>readonly</unknownplugins>): the host cells are refilled on every step for "
+				                      << "it, changes it makes to molecules are NOT carried to the device" << std::endl;
 			} else {
-				global_log->warning() << "GpuLinkedCells: plugin " << name << " is not known to be a read-only end-of-step writer: "
-				                      << "the host cells are refilled on every step for it, changes it makes to molecules are NOT "
-				                      << "carried to the device" << std::endl;
+				// a plugin that moves, adds, deletes or rescales molecules would act on a snapshot and silently have no effect on
+				// the trajectory: that is a wrong simulation, not a slow one, so it ends the run
+				global_log->error_always_output() << "GpuLinkedCells: plugin " << name << " is not known to be a read-only end-of-step "
+				                                  << "writer.  Plugins that change molecules are not supported by the device container "
+				                                  << "(their changes would not reach the device).  If " << name << " only READS molecules, "
+				                                  << "add <unknownplugins>readonly</unknownplugins> to the <datastructure> element."
+				                                  << std::endl;
+				Simulation::exit(1);
 			}
 			global_log->info() << "GpuLinkedCells: plugin " << name << " reads molecules every " << f << " step(s)" << std::endl;
 			freq = std::gcd(freq, f);
@@ -173,7 +195,8 @@ bool GpuLinkedCells::rebuild(double bBoxMin[3], double bBoxMax[3]) {
 		}
 		_stage = nullptr;
 		_stageMolecules = 0;
-		ls1g_destroy(_ctx);
+		for (size_t r = _ctxs.size(); r-- > 0;) ls1g_destroy(_ctxs[r]);
+		_ctxs.clear();
 		_ctx = nullptr;
 		_deviceLoaded = false;
 		_devicePhase = false;
@@ -193,36 +216,73 @@ void GpuLinkedCells::ensureContext() {
 		global_log->error_always_output() << "GpuLinkedCells: component-wise and undirected thermostats are not supported" << std::endl;
 		Simulation::exit(1);
 	}
-	ls1g_config cfg{};
-	cfg.device = _device;
-	for (int d = 0; d < 3; ++d) {
-		cfg.box_min[d] = getBoundingBoxMin(d);
-		cfg.box_max[d] = getBoundingBoxMax(d);
-		cfg.global_length[d] = domain->getGlobalLength(d);
-		cfg.rank_grid[d] = 1;
-		cfg.rank_coords[d] = 0;
+	// block grid of the box: one block (the sequential DomainDecompBase) or DomainDecomposition's grid over <devices> blocks
+	int ndev = 0;
+	chk(ls1g_device_count(&ndev), "ls1g_device_count");
+	if (ndev < 1) fail("no CUDA device");
+	double L[3];
+	for (int d = 0; d < 3; ++d) L[d] = domain->getGlobalLength(d);
+	_ctxs.assign(static_cast<size_t>(_devices), nullptr);
+	for (int r = 0; r < _devices; ++r) {
+		ls1g_config cfg{};
+		int grid[3], coords[3];
+		chk(ls1g_decomp_grid(_devices, r, grid, coords), "ls1g_decomp_grid");
+		cfg.device = (_device + r) % ndev;
+		for (int d = 0; d < 3; ++d) {
+			cfg.global_length[d] = L[d];
+			cfg.rank_grid[d] = grid[d];
+			cfg.rank_coords[d] = coords[d];
+			_blockGrid[d] = grid[d];
+		}
+		if (_devices == 1) {
+			for (int d = 0; d < 3; ++d) {
+				cfg.box_min[d] = getBoundingBoxMin(d);
+				cfg.box_max[d] = getBoundingBoxMax(d);
+			}
+		} else {
+			chk(ls1g_decomp_box(grid, coords, L, cfg.box_min, cfg.box_max), "ls1g_decomp_box");
+		}
+		cfg.cutoff = getCutoff();
+		cfg.lj_cutoff = global_simulation->getLJCutoff();
+		cfg.eps_rf = domain->getepsilonRF();
+		cfg.grid_mode = LS1G_GRID_REBUILD;
+		cfg.capacity = 0;
+		chk(ls1g_create(&cfg, &_ctxs[r]), "ls1g_create");
 	}
-	cfg.cutoff = getCutoff();
-	cfg.lj_cutoff = global_simulation->getLJCutoff();
-	cfg.eps_rf = domain->getepsilonRF();
-	cfg.grid_mode = LS1G_GRID_REBUILD;
-	cfg.capacity = 0;
-	chk(ls1g_create(&cfg, &_ctx), "ls1g_create");
+	_ctx = _ctxs[0];
+	if (multi()) {
+		for (int d = 0; d < 3; ++d) {      // block bounds per dimension, exactly as the contexts got them
+			_blockLo[d].assign(static_cast<size_t>(_blockGrid[d]) + 1, 0.);
+			for (int k = 0; k < _blockGrid[d]; ++k) {
+				int grid[3] = {_blockGrid[0], _blockGrid[1], _blockGrid[2]}, co[3] = {0, 0, 0};
+				double lo[3], hi[3];
+				co[d] = k;
+				chk(ls1g_decomp_box(grid, co, L, lo, hi), "ls1g_decomp_box");
+				_blockLo[d][k] = lo[d];
+				_blockLo[d][k + 1] = hi[d];
+			}
+		}
+	}
 	uploadComponents();
+	if (multi()) chk(ls1g_comm_init_local(_ctxs.data(), _devices), "ls1g_comm_init_local");
 	int cpd[3];
 	double len[3];
 	chk(ls1g_get_grid(_ctx, cpd, len), "ls1g_get_grid");
 	const double* mine = getCellLength();
-	for (int d = 0; d < 3; ++d) {
+	for (int d = 0; d < 3 && !multi(); ++d) {
 		if (len[d] != mine[d]) {
 			global_log->error_always_output() << "GpuLinkedCells: device cell grid differs from LinkedCells::rebuild in dimension "
 			                                  << d << " (" << len[d] << " vs " << mine[d] << ")" << std::endl;
 			Simulation::exit(1);
 		}
 	}
+	if (multi()) {      // the host cells keep the whole box: their grid is LinkedCells::rebuild's, the blocks have their own
+		const int* w = getBoxWidthInNumCells();
+		for (int d = 0; d < 3; ++d) cpd[d] = w[d] + 2;
+	}
 	_numCells = static_cast<size_t>(cpd[0]) * cpd[1] * cpd[2];
-	global_log->info() << "GpuLinkedCells: device context created, " << cpd[0] << " x " << cpd[1] << " x " << cpd[2]
-	                   << " cells" << std::endl;
+	global_log->info() << "GpuLinkedCells: " << _devices << " device context(s) created (block grid " << _blockGrid[0] << " x " << _blockGrid[1] << " x "
+	                   << _blockGrid[2] << " on " << ndev << " visible GPU(s)), " << cpd[0] << " x " << cpd[1] << " x " << cpd[2] << " host cells" << std::endl;
 	_tContext += wall() - t0;
 }
 
@@ -269,7 +329,8 @@ void GpuLinkedCells::uploadComponents() {
 	_pointMolecules = nc == 1 && rows[0].n_lj == 1 && rows[0].n_charge == 0 && rows[0].n_dipole == 0 && rows[0].n_quadrupole == 0 &&
 	                  rows[0].rot_dof == 0 && lj[0][0] == 0. && lj[0][1] == 0. && lj[0][2] == 0.;
 	std::vector<double>& mix = global_simulation->getDomain()->getmixcoeff();
-	chk(ls1g_set_components(_ctx, static_cast<int>(nc), rows.data(), mix.empty() ? nullptr : mix.data(),
+	for (ls1g_ctx* cx : _ctxs)
+		chk(ls1g_set_components(cx, static_cast<int>(nc), rows.data(), mix.empty() ? nullptr : mix.data(),
 	                        static_cast<int>(mix.size())),
 	    "ls1g_set_components");
 }
@@ -337,7 +398,7 @@ void GpuLinkedCells::uploadFromHost() {
 	}
 	const size_t slots = static_cast<size_t>(std::min(28.0 * n + 64., n * (1. + (tot / real - 1.) * 1.3) + 4096.));
 	double tStage = ensureStaging(std::max(n, slots));
-	if (!_deviceLoaded) {                         // ... and so is the allocation of the device arrays
+	if (!_deviceLoaded && !multi()) {             // ... and so is the allocation of the device arrays
 		const double tr = wall();
 		chk(ls1g_reserve(_ctx, n), "ls1g_reserve");
 		_tContext += wall() - tr;
@@ -371,11 +432,83 @@ void GpuLinkedCells::uploadFromHost() {
 	}
 	const double tCopy0 = wall();
 	_tGather += tCopy0 - t0 - tStage;
-	chk(ls1g_upload(_ctx, n, id, cid, r, v, _pointMolecules ? nullptr : q, _pointMolecules ? nullptr : L), "ls1g_upload");
+	if (multi()) uploadBlocks(n);
+	else chk(ls1g_upload(_ctx, n, id, cid, r, v, _pointMolecules ? nullptr : q, _pointMolecules ? nullptr : L), "ls1g_upload");
 	_tH2D += wall() - tCopy0;
 	_bytesUp += n * (8 + 4 + (_pointMolecules ? 6 : 13) * 8);
 	_deviceLoaded = true;
 	_tUpload += wall() - t0 - tStage;
+}
+
+// block (rank, row-major over the block grid as MPI_Cart_rank) that owns the point r: [lo, hi) per dimension with the bounds the
+// contexts were created with
+int GpuLinkedCells::blockOf(const double* r) const {
+	int co[3];
+	for (int d = 0; d < 3; ++d) {
+		const std::vector<double>& lo = _blockLo[d];
+		const int g = _blockGrid[d];
+		int k = static_cast<int>(r[d] / (lo[g] - lo[0]) * g);
+		k = std::max(0, std::min(g - 1, k));
+		while (k > 0 && r[d] < lo[k]) --k;
+		while (k + 1 < g && r[d] >= lo[k + 1]) ++k;
+		co[d] = k;
+	}
+	return (co[0] * _blockGrid[1] + co[1]) * _blockGrid[2] + co[2];
+}
+
+// <devices> > 1: the gathered molecules (staging arrays, n entries) are cut into the blocks and uploaded block by block
+void GpuLinkedCells::uploadBlocks(size_t n) {
+	const int nb = numDevices();
+	std::vector<int> owner(n);
+	std::vector<size_t> count(static_cast<size_t>(nb) + 1, 0);
+#if defined(_OPENMP)
+#pragma omp parallel for schedule(static)
+#endif
+	for (long i = 0; i < static_cast<long>(n); ++i) owner[i] = blockOf(_sR + 3 * i);
+	for (size_t i = 0; i < n; ++i) ++count[owner[i] + 1];
+	const bool rot = !_pointMolecules;
+	std::vector<uint64_t> id;
+	std::vector<uint32_t> cid;
+	std::vector<double> r, v, q, L;
+	for (int b = 0; b < nb; ++b) {
+		const size_t m = count[b + 1];
+		id.resize(m); cid.resize(m); r.resize(3 * m); v.resize(3 * m);
+		if (rot) { q.resize(4 * m); L.resize(3 * m); }
+		size_t k = 0;
+		for (size_t i = 0; i < n; ++i) {
+			if (owner[i] != b) continue;
+			id[k] = _sId[i]; cid[k] = _sCid[i];
+			for (int d = 0; d < 3; ++d) { r[3 * k + d] = _sR[3 * i + d]; v[3 * k + d] = _sV[3 * i + d]; }
+			if (rot) {
+				for (int d = 0; d < 4; ++d) q[4 * k + d] = _sQ[4 * i + d];
+				for (int d = 0; d < 3; ++d) L[3 * k + d] = _sL[3 * i + d];
+			}
+			++k;
+		}
+		if (!_deviceLoaded) {
+			const double tr = wall();
+			chk(ls1g_reserve(_ctxs[b], m), "ls1g_reserve");
+			_tContext += wall() - tr;
+		}
+		uint64_t id0 = 0; uint32_t cid0 = 0; double r0[3] = {0., 0., 0.};
+		chk(ls1g_upload(_ctxs[b], m, m ? id.data() : &id0, m ? cid.data() : &cid0, m ? r.data() : r0, m ? v.data() : nullptr,
+		                rot && m ? q.data() : nullptr, rot && m ? L.data() : nullptr), "ls1g_upload");
+	}
+}
+
+void GpuLinkedCells::exchangeAll() {
+	if (multi()) chk(ls1g_exchange_group(_ctxs.data(), numDevices()), "ls1g_exchange_group");
+	else chk(ls1g_exchange(_ctx), "ls1g_exchange");
+}
+
+void GpuLinkedCells::traverseAll(double& upot, double& virial) {
+	upot = virial = 0.;
+	for (ls1g_ctx* cx : _ctxs) {
+		double u = 0., w = 0.;
+		chk(ls1g_traverse(cx, &u, &w), "ls1g_traverse");
+		upot += u;
+		virial += w;
+	}
 }
 
 // LinkedCells::clear (LinkedCells.cpp:590-595) walks the cells serially; with 10^7 host molecules to free that is the slowest
@@ -413,7 +546,7 @@ void GpuLinkedCells::update() {
 		const double t0 = wall();
 		// wrap leaving molecules, create the periodic halo images, re-sort: LinkedCells::update +
 		// DomainDecompBase::exchangeMolecules in one call (the host-side exchange that follows finds empty cells)
-		chk(ls1g_exchange(_ctx), "ls1g_exchange");
+		exchangeAll();
 		_tDevice += wall() - t0;
 	}
 }
@@ -432,7 +565,13 @@ void GpuLinkedCells::traverseCells(CellProcessor& cellProcessor) {
 			sampleRDF();      // RDF::afterForces (io/RDF.cpp:573-581): the pair histograms are counted on the device
 			return;
 		}
-		// other counting / sampling processors (FlopCounter, ...) run on the host cells
+		if (_devicePhase && !_mirrorValid) {
+			if (FlopCounter* fc = dynamic_cast<FlopCounter*>(&cellProcessor)) {
+				sampleFlops(*fc);      // FlopRateWriter::afterForces: the reference's FLOP model over device-side counts
+				return;
+			}
+		}
+		// other counting / sampling processors run on the host cells
 		if (_devicePhase && !_mirrorValid) {
 			global_log->error_always_output() << "GpuLinkedCells: only the force cell processors run on the device; other cell "
 			                                     "processors need the host cells (host phase or a mirror step)" << std::endl;
@@ -447,15 +586,16 @@ void GpuLinkedCells::traverseCells(CellProcessor& cellProcessor) {
 		// prepare_start (Simulation.cpp:813-844): the host cells are authoritative; the device gets a copy and keeps F
 		uploadFromHost();
 		const double t0 = wall();
-		chk(ls1g_exchange(_ctx), "ls1g_exchange");
-		chk(ls1g_traverse(_ctx, &upot, &virial), "ls1g_traverse");
+		exchangeAll();
+		traverseAll(upot, virial);
 		_tDevice += wall() - t0;
 	} else if (_mode == FUSED && _inStep && !_ranThisStep) {
 		const double t0 = wall();
 		ls1g_step_record rec{};
 		// [thermostat of the previous step] -> pre -> exchange -> forces (+calcFM) -> deleteOuter -> post, as one device-resident
 		// step; the betas are the Domain's own (integratePre).  Vi and the pair count only when the host will read them.
-		chk(ls1g_step(_ctx, _dt, _pendingBt, _pendingBr, mirrorWanted() ? LS1G_STEP_VI : 0, &rec), "ls1g_step");
+		if (multi()) chk(ls1g_step_group(_ctxs.data(), numDevices(), _dt, _pendingBt, _pendingBr, mirrorWanted() ? LS1G_STEP_VI : 0, &rec), "ls1g_step_group");
+		else chk(ls1g_step(_ctx, _dt, _pendingBt, _pendingBr, mirrorWanted() ? LS1G_STEP_VI : 0, &rec), "ls1g_step");
 		_pendingBt = _pendingBr = 1.0;
 		upot = rec.upot;
 		virial = rec.virial;
@@ -470,48 +610,63 @@ void GpuLinkedCells::traverseCells(CellProcessor& cellProcessor) {
 		if (dtStep > _tMaxStep) _tMaxStep = dtStep;
 	} else {
 		const double t0 = wall();
-		chk(ls1g_traverse(_ctx, &upot, &virial), "ls1g_traverse");
+		traverseAll(upot, virial);
 		_tDevice += wall() - t0;
 	}
 	domain->setLocalUpot(upot);          // VectorizedCellProcessor::endTraversal (VectorizedCellProcessor.cpp:155-156)
 	domain->setLocalVirial(virial);
 }
 
-// io/RDF.h:39 declares `friend class RDFTest` for the reference's unit test (io/tests/RDFTest.cpp, which is not part of the
-// executable).  The same door lets the container read the plugin's binning and add the device-side counts of one traversal
-// to its counters; upstream, a public RDF::addLocalCounts(...) would take its place.
-class RDFTest {
-public:
-	struct Shape { unsigned long bins, angularBins; double interval; bool site, angular; };
-	static Shape shape(const RDF& rdf) {
-		return Shape{rdf._bins, rdf._angularBins, rdf._intervalLength, rdf._doCollectSiteRDF, rdf._doARDF};
-	}
-	static void add(RDF& rdf, const std::vector<Component>& comps, const std::vector<uint64_t>& mol,
-	                const std::vector<uint64_t>& site, const std::vector<uint64_t>& ardf) {
-		const size_t nC = comps.size(), bins = rdf._bins;
-		std::vector<size_t> site0(nC + 1, 0);
-		for (size_t i = 0; i < nC; ++i) site0[i + 1] = site0[i] + comps[i].numSites();
-		const size_t S = site0[nC];
-		size_t row = 0;
-		for (size_t i = 0; i < nC; ++i) {
-			for (size_t k = 0; i + k < nC; ++k, ++row) {
-				for (size_t l = 0; l < bins; ++l) rdf._distribution.local[i][k][l] += mol[row * bins + l];
-				const size_t ni = comps[i].numSites(), nj = comps[i + k].numSites();
-				if (ni + nj > 2) {
-					for (size_t m = 0; m < ni; ++m)
-						for (size_t n = 0; n < nj; ++n)
-							for (size_t l = 0; l < bins; ++l)
-								rdf._siteDistribution.local[i][k][m][n][l] += site[((site0[i] + m) * S + site0[i + k] + n) * bins + l];
-				}
-			}
-			if (rdf._doARDF) {
-				const size_t per = bins * rdf._angularBins;
-				for (size_t k = 0; k < nC; ++k)
-					for (size_t l = 0; l < per; ++l) rdf._ARDFdistribution.local[i][k][l] += ardf[(i * nC + k) * per + l];
+// RDF::deviceShape / RDF::addLocalCounts: the two public methods a maintainer adds to io/RDF.h for containers that count the pair
+// histograms elsewhere (here the declaration is inserted into a scratch copy of the header by
+// host/Makefile, this is the definition).  One traversal's counts go to the plugin's LOCAL counters, which RDF::collectRDF then
+// sums over ranks and RDF::accumulateRDF adds to the running total (io/RDF.cpp:249-330) exactly as after its own cell processor.
+//   mol  [pair row (i, i+k)][bin]   site [global site m][global site n][bin]   ardf [i][k][bin * angular bin]
+void RDF::addLocalCounts(const std::vector<Component>& comps, const std::vector<uint64_t>& mol, const std::vector<uint64_t>& site,
+                         const std::vector<uint64_t>& ardf) {
+	const size_t nC = comps.size(), bins = _bins;
+	std::vector<size_t> site0(nC + 1, 0);
+	for (size_t i = 0; i < nC; ++i) site0[i + 1] = site0[i] + comps[i].numSites();
+	const size_t S = site0[nC];
+	size_t row = 0;
+	for (size_t i = 0; i < nC; ++i) {
+		for (size_t k = 0; i + k < nC; ++k, ++row) {
+			for (size_t l = 0; l < bins; ++l) _distribution.local[i][k][l] += mol[row * bins + l];
+			const size_t ni = comps[i].numSites(), nj = comps[i + k].numSites();
+			if (ni + nj > 2) {
+				for (size_t m = 0; m < ni; ++m)
+					for (size_t n = 0; n < nj; ++n)
+						for (size_t l = 0; l < bins; ++l)
+							_siteDistribution.local[i][k][m][n][l] += site[((site0[i] + m) * S + site0[i + k] + n) * bins + l];
 			}
 		}
+		if (_doARDF) {
+			const size_t per = bins * _angularBins;
+			for (size_t k = 0; k < nC; ++k)
+				for (size_t l = 0; l < per; ++l) _ARDFdistribution.local[i][k][l] += ardf[(i * nC + k) * per + l];
+		}
 	}
-};
+}
+
+// FlopRateWriter::measureFLOPS (io/FlopRateWriter.cpp:130-138) hands its FlopCounter to traverseCells after the force pass.  The
+// device counts the same quantities over the same cell pairs (ls1g_flop_count, flops.cu); they enter the counter through
+// FlopCounter::addDeviceCounts (the second upstream addition, see host/Makefile) between its own initTraversal / endTraversal, so
+// the FLOP model, the sum over ranks and the writer's output stay the reference's code.
+void GpuLinkedCells::sampleFlops(FlopCounter& counter) {
+	const double t0 = wall();
+	const bool stepDone = _mode == FUSED && _ranThisStep;      // halo copies dropped by the fused step: put them back (see sampleRDF)
+	if (stepDone) exchangeAll();
+	counter.initTraversal();
+	for (ls1g_ctx* cx : _ctxs) {
+		ls1g_flop_counts fc{};
+		chk(ls1g_flop_count(cx, &fc), "ls1g_flop_count");
+		counter.addDeviceCounts(fc.molecule_distances, fc.kernel_calls, fc.macro_calls);
+	}
+	counter.endTraversal();
+	if (stepDone) for (ls1g_ctx* cx : _ctxs) chk(ls1g_delete_outer(cx), "ls1g_delete_outer");
+	++_flopSamples;
+	_tDevice += wall() - t0;
+}
 
 void GpuLinkedCells::sampleRDF() {
 	RDF* rdf = nullptr;
@@ -525,7 +680,7 @@ void GpuLinkedCells::sampleRDF() {
 	}
 	const double t0 = wall();
 	const std::vector<Component>& comps = *global_simulation->getEnsemble()->getComponents();
-	const RDFTest::Shape sh = RDFTest::shape(*rdf);
+	const RDF::DeviceShape sh = rdf->deviceShape();
 	size_t S = 0;
 	for (const Component& c : comps) S += c.numSites();
 	const size_t nC = comps.size();
@@ -538,42 +693,53 @@ void GpuLinkedCells::sampleRDF() {
 	// the fused step has already dropped the halo copies (and may sit in the neighbour-list layout): put them back for this
 	// traversal, as they are when the reference's plugin runs (Simulation.cpp:1037-1086)
 	const bool stepDone = _mode == FUSED && _ranThisStep;
-	if (stepDone) chk(ls1g_exchange(_ctx), "ls1g_exchange");
-	chk(ls1g_rdf(_ctx, &prm, mol.data(), site.empty() ? nullptr : site.data(), ardf.empty() ? nullptr : ardf.data()), "ls1g_rdf");
-	if (stepDone) chk(ls1g_delete_outer(_ctx), "ls1g_delete_outer");
-	RDFTest::add(*rdf, comps, mol, site, ardf);
+	if (stepDone) exchangeAll();
+	for (ls1g_ctx* cx : _ctxs)       // every block adds the pairs the reference counts on that rank (RDF::collectRDF sums over ranks)
+		chk(ls1g_rdf(cx, &prm, mol.data(), site.empty() ? nullptr : site.data(), ardf.empty() ? nullptr : ardf.data()), "ls1g_rdf");
+	if (stepDone) for (ls1g_ctx* cx : _ctxs) chk(ls1g_delete_outer(cx), "ls1g_delete_outer");
+	rdf->addLocalCounts(comps, mol, site, ardf);
 	++_rdfSamples;
 	_tDevice += wall() - t0;
 }
 
-void GpuLinkedCells::traverseNonInnermostCells(CellProcessor&) {
-	global_log->error_always_output() << "GpuLinkedCells: overlapping traversal is not supported (set overlappingP2P off)" << std::endl;
-	Simulation::exit(1);
+// The reference's overlap API (C08CellPairTraversal.h:78-199: traverseCellPairsOuter / traverseCellPairsInner, driven by
+// NonBlockingMPIMultiStepHandler through Simulation::performOverlappingDecompositionAndCellTraversalStep, Simulation.cpp:1301-1319 -
+// a path that exists with ENABLE_MPI only).  Its purpose - compute the inner cells while the halo travels - is what the device step
+// does by itself: the force kernel runs as phase 1 (blocks whose tile touches no halo cell) while the halo refresh is in flight on
+// a second stream, then phase 2 (boundary blocks) (lists.cuh, step.cu).  So whichever of the two entry points the handler
+// calls first in a time step runs that step; the other calls of the step find the work done.
+void GpuLinkedCells::traverseNonInnermostCells(CellProcessor& cellProcessor) {
+	if (_devicePhase && _mode == FUSED && _inStep && _ranThisStep) return;
+	traverseCells(cellProcessor);
 }
 
-void GpuLinkedCells::traversePartialInnermostCells(CellProcessor&, unsigned int, int) {
-	global_log->error_always_output() << "GpuLinkedCells: overlapping traversal is not supported (set overlappingP2P off)" << std::endl;
-	Simulation::exit(1);
+void GpuLinkedCells::traversePartialInnermostCells(CellProcessor& cellProcessor, unsigned int, int) {
+	if (_devicePhase && _mode == FUSED && _inStep && _ranThisStep) return;
+	traverseCells(cellProcessor);
 }
 
 void GpuLinkedCells::deleteOuterParticles() {
 	if (!_devicePhase) {
 		LinkedCells::deleteOuterParticles();
-		if (_deviceLoaded) chk(ls1g_delete_outer(_ctx), "ls1g_delete_outer");
+		if (_deviceLoaded) for (ls1g_ctx* cx : _ctxs) chk(ls1g_delete_outer(cx), "ls1g_delete_outer");
 		return;
 	}
 	if (_mode == OPERATORS || !_ranThisStep) {
 		const double t0 = wall();
-		chk(ls1g_delete_outer(_ctx), "ls1g_delete_outer");
+		for (ls1g_ctx* cx : _ctxs) chk(ls1g_delete_outer(cx), "ls1g_delete_outer");
 		_tDevice += wall() - t0;
 	}
 }
 
 unsigned long GpuLinkedCells::getNumberOfParticles() {
 	if (!_devicePhase || _mirrorValid) return LinkedCells::getNumberOfParticles();
-	uint64_t owned = 0, halo = 0;
-	chk(ls1g_count(_ctx, &owned, &halo), "ls1g_count");
-	return owned + halo;
+	uint64_t total = 0;
+	for (ls1g_ctx* cx : _ctxs) {
+		uint64_t owned = 0, halo = 0;
+		chk(ls1g_count(cx, &owned, &halo), "ls1g_count");
+		total += owned + halo;
+	}
+	return total;
 }
 
 void GpuLinkedCells::clear() {
@@ -582,7 +748,7 @@ void GpuLinkedCells::clear() {
 		uint64_t id = 0;
 		uint32_t cid = 0;
 		double r[3] = {0., 0., 0.};
-		chk(ls1g_upload(_ctx, 0, &id, &cid, r, nullptr, nullptr, nullptr), "ls1g_upload");
+		for (ls1g_ctx* cx : _ctxs) chk(ls1g_upload(cx, 0, &id, &cid, r, nullptr, nullptr, nullptr), "ls1g_upload");
 	}
 	_deviceLoaded = false;
 	_devicePhase = false;
@@ -623,7 +789,7 @@ void GpuLinkedCells::integratePre(double dt, Domain* domain) {
 			const double rawBt = std::pow(3.0 * _n * Ti / _summv2, 0.4);
 			const double rawBr = (_sumIw2 == 0.0 || _rotDOF == 0) ? 1.0 : std::pow(_rotDOF * Ti / _sumIw2, 0.4);
 			if ((rawBt < MIN_BETA || rawBr < MIN_BETA) && bt == 1.0 && std::fabs(br - std::pow(rawBr, 0.0091)) <= 1e-14) {
-				chk(ls1g_selective_thermostat(_ctx, KINLIMIT_PER_T * Ti, Ti), "ls1g_selective_thermostat");
+				for (ls1g_ctx* cx : _ctxs) chk(ls1g_selective_thermostat(cx, KINLIMIT_PER_T * Ti, Ti), "ls1g_selective_thermostat");
 				++_selective;
 			}
 		}
@@ -631,10 +797,10 @@ void GpuLinkedCells::integratePre(double dt, Domain* domain) {
 			_pendingBt = bt;
 			_pendingBr = br;
 		} else if (bt != 1.0 || br != 1.0) {
-			chk(ls1g_scale(_ctx, bt, br), "ls1g_scale");
+			for (ls1g_ctx* cx : _ctxs) chk(ls1g_scale(cx, bt, br), "ls1g_scale");
 		}
 	}
-	if (_mode == OPERATORS) chk(ls1g_integrate_pre(_ctx, dt), "ls1g_integrate_pre");
+	if (_mode == OPERATORS) for (ls1g_ctx* cx : _ctxs) chk(ls1g_integrate_pre(cx, dt), "ls1g_integrate_pre");
 	_tDevice += wall() - t0;
 	_inStep = true;
 	_ranThisStep = false;
@@ -648,7 +814,14 @@ void GpuLinkedCells::integratePost(double dt, Domain* domain) {
 	}
 	const double t0 = wall();
 	if (_mode == OPERATORS) {
-		chk(ls1g_integrate_post(_ctx, 0.5 * dt, &_summv2, &_sumIw2, &_n, &_rotDOF), "ls1g_integrate_post");
+		_summv2 = _sumIw2 = 0.;
+		_n = _rotDOF = 0;
+		for (ls1g_ctx* cx : _ctxs) {
+			double a = 0., b = 0.;
+			uint64_t nn = 0, rd = 0;
+			chk(ls1g_integrate_post(cx, 0.5 * dt, &a, &b, &nn, &rd), "ls1g_integrate_post");
+			_summv2 += a; _sumIw2 += b; _n += nn; _rotDOF += rd;
+		}
 	} else if (!_ranThisStep) {
 		global_log->error_always_output() << "GpuLinkedCells (fused mode): time step without traverseCells" << std::endl;
 		Simulation::exit(1);
@@ -668,6 +841,7 @@ void GpuLinkedCells::integratePost(double dt, Domain* domain) {
 // device -> host cells.  The download is cell-sorted on the reference grid, so threads fill disjoint cells.
 void GpuLinkedCells::downloadMirror() {
 	if (_ctx == nullptr || !_deviceLoaded) return;
+	if (multi()) { downloadMirrorBlocks(); return; }
 	const double t0 = wall();
 	clearHostCells();
 	uint64_t slots = 0;
@@ -780,4 +954,73 @@ void GpuLinkedCells::downloadMirror() {
 	_mirrorValid = true;
 	++_mirrors;
 	_tMirror += wall() - t0 - tStage;
+}
+
+
+// <devices> > 1: device blocks -> host cells.  The blocks have their own cell grids, so every owned molecule is put into the host
+// cell LinkedCells::getCellIndexOfPoint gives for it: cell index per molecule, counting sort by host cell, then the threads fill
+// disjoint cells (molecules of a cell in id order, so the host state does not depend on the thread schedule).
+void GpuLinkedCells::downloadMirrorBlocks() {
+	const double t0 = wall();
+	clearHostCells();
+	const bool point = _pointMolecules;
+	const int mask = LS1G_F_ID | LS1G_F_CID | LS1G_F_R | LS1G_F_V | LS1G_F_F | LS1G_F_VI | LS1G_F_CELL | (point ? 0 : (LS1G_F_Q | LS1G_F_L | LS1G_F_M));
+	std::vector<Component>& comps = *global_simulation->getEnsemble()->getComponents();
+	const double zero3[3] = {0., 0., 0.};
+	double tStageAll = 0.;
+	for (ls1g_ctx* cx : _ctxs) {
+		uint64_t slots = 0;
+		chk(ls1g_slot_count(cx, &slots), "ls1g_slot_count");
+		const size_t ns = static_cast<size_t>(slots);
+		if (ns == 0) continue;
+		tStageAll += ensureStaging(ns + 1);
+		ls1g_fields f{};
+		f.id = _sId; f.cid = _sCid; f.r = _sR; f.v = _sV; f.F = _sF; f.Vi = _sVi; f.cell = _sCell;
+		if (!point) { f.q = _sQ; f.L = _sL; f.M = _sM; }
+		const double tc = wall();
+		chk(ls1g_download_range(cx, mask, 0, ns, &f), "ls1g_download_range");
+		_tD2H += wall() - tc;
+		_bytesDown += ns * (8 + 4 + 4 + (point ? 12 : 22) * 8);
+		const double tf = wall();
+		// host cell of every owned slot
+		std::vector<uint32_t> hc(ns, 0xffffffffu);
+#if defined(_OPENMP)
+#pragma omp parallel for schedule(static)
+#endif
+		for (long i = 0; i < static_cast<long>(ns); ++i)
+			if ((_sCell[i] & LS1G_HALO_FLAG) == 0u) hc[i] = static_cast<uint32_t>(getCellIndexOfPoint(_sR + 3 * i));
+		std::vector<size_t> first(_numCells + 1, 0);
+		for (size_t i = 0; i < ns; ++i) if (hc[i] != 0xffffffffu) ++first[hc[i] + 1];
+		for (size_t c = 0; c < _numCells; ++c) first[c + 1] += first[c];
+		std::vector<uint32_t> ord(first[_numCells]);
+		{
+			std::vector<size_t> fill(first.begin(), first.end() - 1);
+			for (size_t i = 0; i < ns; ++i) if (hc[i] != 0xffffffffu) ord[fill[hc[i]]++] = static_cast<uint32_t>(i);      // slot order = (device cell, id)
+		}
+#if defined(_OPENMP)
+#pragma omp parallel for schedule(dynamic, 64)
+#endif
+		for (long c = 0; c < static_cast<long>(_numCells); ++c) {
+			const size_t a = first[c], b = first[c + 1];
+			if (a == b) continue;
+			std::sort(ord.begin() + a, ord.begin() + b, [&](uint32_t x, uint32_t y) { return _sId[x] < _sId[y]; });
+			ParticleCell& pc = getCellReference(static_cast<int>(c));
+			pc.increaseMoleculeStorage(b - a);
+			for (size_t k = a; k < b; ++k) {
+				const size_t i = ord[k];
+				Molecule m = point ? Molecule(_sId[i], &comps[_sCid[i]], _sR[3 * i], _sR[3 * i + 1], _sR[3 * i + 2], _sV[3 * i], _sV[3 * i + 1], _sV[3 * i + 2],
+				                              1., 0., 0., 0., 0., 0., 0.)
+				                   : Molecule(_sId[i], &comps[_sCid[i]], _sR[3 * i], _sR[3 * i + 1], _sR[3 * i + 2], _sV[3 * i], _sV[3 * i + 1], _sV[3 * i + 2],
+				                              _sQ[4 * i], _sQ[4 * i + 1], _sQ[4 * i + 2], _sQ[4 * i + 3], _sL[3 * i], _sL[3 * i + 1], _sL[3 * i + 2]);
+				m.setF(&_sF[3 * i]);
+				m.setM(const_cast<double*>(point ? zero3 : &_sM[3 * i]));
+				m.setVi(&_sVi[3 * i]);
+				pc.addParticle(m);
+			}
+		}
+		_tFill += wall() - tf;
+	}
+	_mirrorValid = true;
+	++_mirrors;
+	_tMirror += wall() - t0 - tStageAll;
 }

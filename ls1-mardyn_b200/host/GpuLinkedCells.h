@@ -8,6 +8,10 @@
  *     <mirrorfrequency>auto</mirrorfrequency>  every k-th step the host cells are refilled from the device (writers, plugins); 0 = last step only;
  *                                              auto (default) = gcd of the write frequencies of the plugins that read molecules
  *     <device>0</device>
+ *     <devices>1</devices>                  N > 1: the box is cut into DomainDecomposition's block grid (MPI_Dims_create order,
+ *                                           DomainDecomposition.cpp:19-41,116-125) and block r lives on device (device + r) mod visible
+ *                                           GPUs, all inside THIS process; halo and leaving molecules move between the blocks over
+ *                                           NVLink peer copies (ls1g_comm_init_local, ls1g_step_group) instead of MPI
  *   </datastructure>
  *   <integrator type="GpuLeapfrog"> ... </integrator>
  *
@@ -35,6 +39,7 @@
 
 struct ls1g_ctx;
 class Domain;
+class FlopCounter;
 
 class GpuLinkedCells : public LinkedCells {
 public:
@@ -66,24 +71,37 @@ public:
 	/** refill the host cells from the device (r, v, q, D, F, M, Vi); they are dropped again at the next time step */
 	void downloadMirror();
 	ls1g_ctx* ctx() { return _ctx; }
+	int numDevices() const { return static_cast<int>(_ctxs.size()); }
 
 private:
 	enum Mode { FUSED, OPERATORS };
 	void ensureContext();
 	void uploadComponents();
 	void uploadFromHost();
+	void uploadBlocks(size_t n);
+	void downloadMirrorBlocks();
+	int blockOf(const double* r) const;
 	double ensureStaging(size_t molecules);
+	// one call for the whole box, whatever the number of blocks
+	void exchangeAll();
+	void traverseAll(double& upot, double& virial);
+	bool multi() const { return _ctxs.size() > 1; }
 	void clearHostCells();
 	bool mirrorWanted() const;
 	unsigned long mirrorFrequencyFromPlugins(XMLfileUnits& xmlconfig) const;
 	void printSummary() const;
 	void sampleRDF();
+	void sampleFlops(FlopCounter& counter);
 	[[noreturn]] void fail(const char* what) const;
 	void chk(int rc, const char* what) const;
 
-	ls1g_ctx* _ctx = nullptr;
+	ls1g_ctx* _ctx = nullptr;                 // block 0 (the only one unless <devices> > 1)
+	std::vector<ls1g_ctx*> _ctxs;            // all blocks in rank order
+	int _blockGrid[3] = {1, 1, 1};
+	std::vector<double> _blockLo[3];         // lower bound of block k in dimension d (ls1g_decomp_box), + the upper end
 	Mode _mode = FUSED;
-	int _device = 0;
+	int _device = 0, _devices = 1;
+	bool _allowUnknownPlugins = false;
 	unsigned long _mirrorFrequency = 0;
 	bool _devicePhase = false;     // false: the host cells hold the molecules (before the first time step)
 	bool _deviceLoaded = false;    // the device holds a copy with valid forces
@@ -97,7 +115,7 @@ private:
 	double _tUpload = 0., _tDevice = 0., _tMirror = 0., _tContext = 0.;
 	double _tGather = 0., _tH2D = 0., _tD2H = 0., _tFill = 0.;
 	bool _pointMolecules = false;  // one component, one LJ centre at the origin, no rotation: the device keeps no q / D / M
-	unsigned long _steps = 0, _mirrors = 0, _selective = 0, _rdfSamples = 0;
+	unsigned long _steps = 0, _mirrors = 0, _selective = 0, _rdfSamples = 0, _flopSamples = 0;
 	double _lastTfactor = 1.0;
 	size_t _bytesUp = 0, _bytesDown = 0, _numCells = 0;
 	double _pendingBt = 1.0, _pendingBr = 1.0;   // fused mode: betas of the previous step, applied inside the next ls1g_step

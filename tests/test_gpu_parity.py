@@ -374,6 +374,40 @@ def test_nve_drift_matches_oracle():
     assert abs((e[-1] - e[0]) - (e_ref[-1] - e_ref[0])) < 1e-8 * abs(e_ref[0])
 
 
+@pytest.mark.parametrize("which", ["unshifted", "shifted"])
+def test_nve_1000_steps_against_the_reference_record(which):
+    """BASELINE.json: "NVE energy drift must be no worse than the reference over 1000 steps".  tests/golden/ref_nve_1000_steps.json is the
+    UNMODIFIED reference (LinkedCells + C08 + VectorizedCellProcessor AVX2 + Leapfrog, thermostat off) stepping 4 * 64^3 = 1 048 576
+    molecules of the bench workload for 1000 steps (tests/golden/make_golden_r2.py nve, ~12 min of CPU each).  The device loop on the same
+    input: total energy per molecule at every 100th step equal to the reference's to 1e-6 (the trajectories are chaotic, the energy is
+    not), drift no worse than the reference's, same temperature."""
+    import json
+    import os
+    import importlib
+    ref_all = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "ref_nve_1000_steps.json")))
+    ref = ref_all[which]
+    gen = importlib.import_module("ls1-mardyn_b200.generators")
+    ids, r, v = gen.fcc_block(64, rho=0.8442, temperature=1.44, seed=1)
+    _, L = gen.fcc_box(64, 0.8442)
+    v -= v.mean(axis=0)
+    n = len(ids)
+    assert n == ref_all["n_molecules"] and ref_all["steps"] == 1000
+    with ls1g.Container(list(L), 2.5) as c:
+        c.set_components([ls1g.lj_component(shift6=ref["shift6"])])
+        c.add_particles(ids, np.zeros(n, dtype=np.uint32), r, v)
+        c.exchange()
+        c.traverse_cells()
+        rec = c.run(1000, 0.002)
+    e = (rec[:, 0] + 0.5 * rec[:, 2]) / n
+    e_ref = np.array(ref["e_total_per_molecule_every_100"])
+    assert np.abs(e[::100] - e_ref).max() <= 1e-6 * abs(e_ref[0]), np.abs(e[::100] - e_ref).max()
+    drift = (e[-1] - e[0]) / abs(e[0])
+    assert abs(drift) <= abs(ref["rel_energy_drift"]) * 1.01 + 1e-9, (drift, ref["rel_energy_drift"])
+    assert abs(drift - ref["rel_energy_drift"]) <= 1e-6
+    T = rec[:, 2] / (3.0 * n)
+    assert abs(T[0] - ref["temperature_first_last"][0]) < 1e-9 and abs(T[-1] - ref["temperature_first_last"][1]) < 1e-4
+
+
 def test_list_loop_equals_per_step_loop(monkeypatch):
     """ls1g_run with neighbour lists (rebuild on displacement > skin/2, frozen layout, refreshed images) against the
     rebuild-every-step loop (LS1G_SKIN=0) on a liquid that crosses the periodic boundary: same pairs, same energies"""
@@ -668,6 +702,113 @@ def test_group_list_loop_with_lists_expiring_in_flight(skin, monkeypatch):
         for k in ("r", "v"):
             assert np.abs(st[k] - other_st[k]).max() <= 1e-9 * np.abs(other_st[k]).max(), k
         assert np.array_equal(st["id"], other_st["id"])
+
+
+@pytest.mark.parametrize("name,dt_factor,steps,min_rebuilds", [("ex_CO2", 4.0, 60, 3), ("ex_EOX", 1.0, 60, 3), ("ex_CO2Merker", 1.0, 60, 3),
+                                                              ("mixture", 4.0, 40, 2)])
+def test_multisite_list_loop_equals_per_step_loop(name, dt_factor, steps, min_rebuilds, monkeypatch):
+    """Rigid multi-site molecules on the neighbour lists (centre-centre lists, site loops inside; orientations of the periodic images
+    refreshed with their source) against the rebuild-every-step cell scan (LS1G_LIST_MULTISITE=0): same pair count, same trajectory.
+    Step and length are chosen per input so that the lists expire several times while the (unequilibrated) inputs stay intact:
+    EOX at 600 K and CO2-Merker rebuild every ~5 steps at their own step.  "mixture": the CO2 example with every second molecule
+    turned into a second component (same geometry, LJ epsilon x 0.8, sigma x 1.03; xi = 0.9, eta = 1.05), which takes the kernels
+    with run-time site counts and the LJ tables of all component pairs on both paths.  (The reference's own multi-component
+    vectorisation input cannot be time-stepped: it contains components of dipole/quadrupole sites only, i.e. of zero mass.)"""
+    from tests.gpu_helpers import components_of
+    d = load("ex_CO2" if name == "mixture" else name)
+    st = initial_state(d)
+    dt = dt_factor * float(d["dt"][0])
+    comps, mix, cid = components_of(d), d["mixcoeff"], st["cid"]
+    if name == "mixture":
+        second = {k: (np.array(v, dtype=np.float64).copy() if isinstance(v, np.ndarray) else v) for k, v in comps[0].items()}
+        second["lj"][:, 4] *= 0.8
+        second["lj"][:, 5] *= 1.03
+        comps, mix = [comps[0], second], [0.9, 1.05]
+        cid = (st["id"] % 2).astype(np.uint32)
+    out = {}
+    for mode in ("1", "0"):
+        monkeypatch.setenv("LS1G_LIST_MULTISITE", mode)
+        with ls1g.Container(d["box"], float(d["rc"][0]), lj_cutoff=float(d["rc"][1]), eps_rf=float(d["epsRF"][0]), grid_mode=int(d["meta"][1])) as c:
+            c.set_components(comps, mix)
+            c.add_particles(st["id"], cid, st["r"], st["v"], st["q"], st["L"])
+            c.exchange()
+            c.traverse_cells()
+            rec = c.run(steps, dt)
+            out[mode] = (rec, c.last_pair_count(), c.list_stats(), by_id(c.download(("id", "r", "v", "q", "L", "F", "M", "Vi"))))
+    (rec, pairs, stats, sa), (rec0, pairs0, stats0, sb) = out["1"], out["0"]
+    assert stats0["rebuilds"] == 0 and stats["rebuilds"] >= min_rebuilds, (stats0, stats)
+    assert pairs == pairs0
+    assert np.all(np.abs(rec - rec0) <= 1e-9 * np.maximum(np.abs(rec0).max(axis=0), 1e-300)), np.abs(rec - rec0).max(axis=0)
+    for k in ("r", "v", "q", "L"):
+        assert np.abs(sa[k] - sb[k]).max() <= 1e-9 * max(np.abs(sb[k]).max(), 1e-300), k
+    for k in ("F", "M", "Vi"):
+        assert vec_rel_err(sa[k], sb[k]) < 1e-6, k                       # 60 steps of trajectory divergence, not arithmetic
+
+
+def test_multisite_group_list_loop_matches_single_rank():
+    """CO2 on two in-process ranks: the halo refresh carries the orientations (7 doubles per halo molecule) next to the positions"""
+    from tests.gpu_helpers import components_of
+    d = load("ex_CO2")
+    st = initial_state(d)
+    box, rc, rclj, dt = d["box"], float(d["rc"][0]), float(d["rc"][1]), 4.0 * float(d["dt"][0])
+    comps, mix = components_of(d), d["mixcoeff"]
+    steps = 40
+    with container_of(d) as c:
+        c.add_particles(st["id"], st["cid"], st["r"], st["v"], st["q"], st["L"])
+        c.exchange()
+        c.traverse_cells()
+        ref_rec = c.run(steps, dt)
+        ref_stats = c.list_stats()
+        ref = by_id(c.download(("id", "r", "v", "q", "L")))
+    ranks = []
+    try:
+        for rank in range(2):
+            grid, coords = ls1g.decomp_grid(2, rank)
+            bmin, bmax = ls1g.decomp_box(grid, coords, box)
+            c = ls1g.Container(bmax, rc, box_min=bmin, lj_cutoff=rclj, eps_rf=float(d["epsRF"][0]), global_length=box, rank_grid=grid,
+                               rank_coords=coords, capacity=4 * len(st["id"]) + 1024)
+            c.set_components(comps, mix)
+            mine = np.all((st["r"] >= np.array(bmin)) & (st["r"] < np.array(bmax)), axis=1)
+            c.add_particles(st["id"][mine], st["cid"][mine], st["r"][mine], st["v"][mine], st["q"][mine], st["L"][mine])
+            ranks.append(c)
+        ls1g.comm_init_local(ranks)
+        ls1g.exchange_group(ranks)
+        for c in ranks:
+            c.traverse_cells()
+        rec = ls1g.run_group(ranks, steps, dt)
+        stats = ranks[0].list_stats()
+        parts = [c.download(("id", "r", "v", "q", "L")) for c in ranks]
+    finally:
+        for c in ranks:
+            c.close()
+    out = by_id({k: np.concatenate([p[k] for p in parts]) for k in parts[0]})
+    assert stats["rebuilds"] >= 2 and ref_stats["rebuilds"] >= 2
+    assert np.array_equal(out["id"], ref["id"])
+    assert np.all(np.abs(rec[:, :4] - ref_rec[:, :4]) <= 1e-9 * np.maximum(np.abs(ref_rec[:, :4]).max(axis=0), 1e-300))
+    for k in ("r", "v", "q", "L"):
+        assert np.abs(out[k] - ref[k]).max() <= 1e-9 * max(np.abs(ref[k]).max(), 1e-300), k
+
+
+def test_exploded_system_is_an_error_not_a_fault():
+    """a molecule that is still outside the halo region after the periodic wrap (it moved more than a box length in one step) ends the
+    run with an error, as the reference's failing cell lookup does - no out-of-bounds access, the library stays usable"""
+    r, v, box = fcc_lattice(6, seed=5)
+    n = len(r)
+    v = v.copy()
+    v[7] = [4.0e4, 0.0, 0.0]
+    with ls1g.Container(box, 2.5) as c:
+        c.set_components([ls1g.lj_component()])
+        c.add_particles(np.arange(n), np.zeros(n, dtype=np.uint32), r, v)
+        c.exchange()
+        c.traverse_cells()
+        with pytest.raises(ls1g.Ls1gError, match="exploded"):
+            c.run(3, 0.002)
+    with ls1g.Container(box, 2.5) as c:                                   # a fresh container works as before
+        c.set_components([ls1g.lj_component()])
+        c.add_particles(np.arange(n), np.zeros(n, dtype=np.uint32), r, 0.0 * v)
+        c.exchange()
+        u, _ = c.traverse_cells()
+        assert np.isfinite(u)
 
 
 def test_group_thermostat_uses_the_global_kinetic_sums():

@@ -101,6 +101,60 @@ def test_host_side_per_molecule_passes_are_rejected_at_start_up(what, xml, tmp_p
     assert "device context created" not in out["log"]
 
 
+@needs_binaries
+def test_plugins_that_may_change_molecules_end_the_run(tmp_path):
+    """a plugin that is not a known read-only writer (COMaligner moves every molecule) would act on a snapshot and silently have no
+    effect on the device-resident trajectory: the container ends the run while reading the configuration; a user who knows the
+    plugin only reads can say so (<unknownplugins>readonly</unknownplugins>), and then gets a mirror on every step"""
+    aligner = '<plugin name="COMaligner"><x>1</x><y>1</y><z>1</z><interval>1</interval><correctionFactor>.5</correctionFactor></plugin>'
+    def with_plugin(cfg):      # a simulation plugin: <plugin> directly under <simulation> (Simulation.cpp:520-534)
+        text = open(cfg).read().replace("</simulation>", aligner + "</simulation>")
+        assert aligner in text
+        open(cfg, "w").write(text)
+        return cfg
+    cfg = with_plugin(M.write_case(str(tmp_path), "ex_Argon", 2, "fused"))
+    out = M.run(M.GPU_EXE, cfg, 2, threads=2, check=False)
+    assert "GpuLinkedCells: plugin COMaligner is not known to be a read-only end-of-step writer" in out["log"]
+    assert "Plugins that change molecules are not supported by the device container" in out["log"]
+    assert "device context(s) created" not in out["log"] and "no CUDA device" not in out["log"]
+    cfg = with_plugin(M.write_case(str(tmp_path), "ex_Argon", 2, "fused-ro", container_options="<unknownplugins>readonly</unknownplugins>"))
+    out = M.run(M.GPU_EXE, cfg, 2, threads=2, check=False)
+    assert "(<unknownplugins>readonly</unknownplugins>)" in out["log"]
+    assert "GpuLinkedCells: plugin COMaligner reads molecules every 1 step(s)" in out["log"]
+    assert "mirror frequency 1 (from the plugins' write frequencies)" in out["log"]
+
+
+FLOP_PLUGIN = '<outputplugin name="FlopRateWriter"><mode>stdout</mode><writefrequency>2</writefrequency></outputplugin>'
+
+
+def _flop_lines(log):
+    """FlopRateWriter's count line and the lines of FlopCounter::printStats (FlopCounter.cpp:111-122, FlopCounter.h:183-193); the
+    FLOP rates depend on the clock and are left out"""
+    keep = []
+    for line in log.splitlines():
+        for key in ("FLOP-Count per Iteration", "Molecule distances:", "kernel calls:", "fraction of Flops for molecule dist"):
+            if key in line:
+                keep.append(line[line.index(key) - (40 if key == "kernel calls:" else 0):].split("\t")[-1].strip())
+    return keep
+
+
+@pytest.mark.gpu
+@needs_binaries
+@pytest.mark.parametrize("name,variant", [("ex_Argon", "fused"), ("ex_CO2", "fused"), ("ex_CO2", "operators")])
+def test_flop_rate_writer_counts_on_the_device(name, variant, tmp_path):
+    """<outputplugin name="FlopRateWriter">: FlopRateWriter::afterForces hands the reference's FlopCounter to traverseCells; the
+    container counts molecule pairs, in-cutoff centre pairs per potential and macroscopic pairs on the device (ls1g_flop_count) and
+    feeds them to the counter (FlopCounter::addDeviceCounts); the FLOP model and the printing are the reference's.  The counts the
+    plugin prints (FLOP-Count per Iteration and every line of FlopCounter::printStats) equal the CPU run's."""
+    cpu = M.run(M.REF_EXE, M.write_case(str(tmp_path), name, 6, "cpu", output_plugins=FLOP_PLUGIN), 6)
+    gpu = M.run(M.GPU_EXE, M.write_case(str(tmp_path), name, 6, variant, output_plugins=FLOP_PLUGIN), 6)
+    assert "3 FLOP sample(s) on the device" in gpu["log"]
+    assert "mirror frequency 0 (from the plugins' write frequencies)" in gpu["log"]
+    a, b = _flop_lines(cpu["log"]), _flop_lines(gpu["log"])
+    assert len(a) >= 3 and sum("FLOP-Count per Iteration" in x for x in a) == 3
+    assert a == b
+
+
 RDF_PLUGIN = ('<outputplugin name="RDF"><writefrequency>3</writefrequency><samplingfrequency>1</samplingfrequency><outputprefix>rdf</outputprefix>'
               '<bins>50</bins><intervallength>0.5</intervallength><angularbins>4</angularbins></outputplugin>')
 
@@ -148,7 +202,7 @@ def test_rdf_plugin_samples_on_the_device(variant, tmp_path):
 def test_reference_time_loop_on_the_gpu_container(name, variant, tmp_path):
     cpu = M.run(M.REF_EXE, M.write_case(str(tmp_path), name, STEPS, "cpu"), STEPS)
     gpu = M.run(M.GPU_EXE, M.write_case(str(tmp_path), name, STEPS, variant), STEPS)
-    assert "GpuLinkedCells: device context created" in gpu["log"]
+    assert "GpuLinkedCells: 1 device context(s) created" in gpu["log"]
     assert gpu["gpu"]["steps"] == STEPS and gpu["gpu"]["mirrors"] == 1
     assert cpu["res"].shape == gpu["res"].shape == (STEPS + 1, 10)
     # ResultWriter columns: step time U_pot U_pot_avg p p_avg beta_trans beta_rot c_v N
@@ -158,6 +212,35 @@ def test_reference_time_loop_on_the_gpu_container(name, variant, tmp_path):
     box = M.load(name)["box"]
     dr = cpu["final"]["r"] - gpu["final"]["r"]
     dr -= box * np.round(dr / box)                     # a molecule on the periodic boundary may be wrapped on one side only
+    assert np.max(np.abs(dr)) <= 1e-7 * box[0]
+    for k in ("v", "q", "D"):
+        assert rel(gpu["final"][k], cpu["final"][k]) <= 1e-6, (k, rel(gpu["final"][k], cpu["final"][k]))
+
+
+@pytest.mark.gpu
+@needs_binaries
+@pytest.mark.parametrize("name,blocks,variant", [("ex_Argon", 2, "fused"), ("ex_Argon", 4, "fused"), ("ex_Argon", 8, "fused"), ("ex_Argon", 8, "operators"),
+                                                  ("ex_CO2", 2, "fused"), ("ex_CO2", 4, "operators"), ("ex_CO2", 8, "fused")])
+def test_reference_time_loop_on_several_device_blocks(name, blocks, variant, tmp_path):
+    """<devices>N</devices>: ONE MarDynGpu process whose container cuts the box into DomainDecomposition's block grid
+    (DomainDecomposition.cpp:19-41,116-125) with one device context per block (here all on the same GPU; on a multi-GPU box block r
+    lives on device r), halo and leaving molecules exchanged between the blocks inside the library.  The reference's unmodified time
+    loop and Domain see one container: per-step U_pot, p, betas and the final checkpoint against the CPU reference on the same
+    (2 x 2 x 2 replicated) example."""
+    steps = 12
+    threads = min(os.cpu_count() or 1, 8)
+    cpu = M.run(M.REF_EXE, M.write_case(str(tmp_path), name, steps, "cpu", replicate=2), steps, threads=threads)
+    gpu = M.run(M.GPU_EXE, M.write_case(str(tmp_path), name, steps, "%s-b%d" % (variant, blocks), replicate=2,
+                                        container_options="<devices>%d</devices>" % blocks), steps, threads=threads)
+    assert "GpuLinkedCells: %d device context(s) created" % blocks in gpu["log"]
+    assert gpu["gpu"]["steps"] == steps and gpu["gpu"]["mirrors"] == 1
+    assert cpu["res"].shape == gpu["res"].shape == (steps + 1, 10)
+    for col, what, tol in ((2, "U_pot", 1e-8), (4, "p", 1e-8), (6, "beta_trans", 1e-9), (7, "beta_rot", 1e-9), (9, "N", 0.0)):
+        assert rel(gpu["res"][:, col], cpu["res"][:, col]) <= tol, (what, rel(gpu["res"][:, col], cpu["res"][:, col]))
+    assert np.array_equal(cpu["final"]["id"], gpu["final"]["id"]) and np.array_equal(cpu["final"]["cid"], gpu["final"]["cid"])
+    box = 2.0 * M.load(name)["box"]
+    dr = cpu["final"]["r"] - gpu["final"]["r"]
+    dr -= box * np.round(dr / box)
     assert np.max(np.abs(dr)) <= 1e-7 * box[0]
     for k in ("v", "q", "D"):
         assert rel(gpu["final"][k], cpu["final"][k]) <= 1e-6, (k, rel(gpu["final"][k], cpu["final"][k]))
