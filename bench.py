@@ -179,6 +179,16 @@ class ClockSampler:
 # ----------------------------------------------------------------------------------------------------------
 # the reference's own CPU implementation (oracle/_ref/MarDyn, built from the unmodified sources by oracle/ref/Makefile)
 # ----------------------------------------------------------------------------------------------------------
+def mardyn_xml(steps, cells, gpu, devices=1):
+    """the one configuration both arms run: `cells` = fcc unit cells per dimension (an int, or [nx, ny, nz] for the block grid of a
+    multi-GPU run); gpu selects <datastructure type="GpuLinkedCells"> + <integrator type="GpuLeapfrog">, everything else is equal"""
+    a = (4.0 / RHO) ** (1.0 / 3.0)
+    cx, cy, cz = (cells, cells, cells) if isinstance(cells, int) else cells
+    return MARDYN_XML.format(dt=DT, steps=steps, temp=TEMP, Lx=repr(cx * a), Ly=repr(cy * a), Lz=repr(cz * a), rho=RHO, rc=RC,
+                             integrator="GpuLeapfrog" if gpu else "Leapfrog", container="GpuLinkedCells" if gpu else "LinkedCells",
+                             container_options="<devices>%d</devices>" % devices if gpu and devices > 1 else "")
+
+
 MARDYN_XML = """<?xml version='1.0' encoding='UTF-8'?>
 <mardyn version="20100525">
   <refunits type="SI"><length unit="nm">0.1</length><mass unit="u">1</mass><energy unit="K">1</energy></refunits>
@@ -187,7 +197,7 @@ MARDYN_XML = """<?xml version='1.0' encoding='UTF-8'?>
     <run><currenttime>0</currenttime><production><steps>{steps}</steps></production></run>
     <ensemble type="NVT">
       <temperature unit="reduced">{temp}</temperature>
-      <domain type="box"><lx>{L}</lx><ly>{L}</ly><lz>{L}</lz></domain>
+      <domain type="box"><lx>{Lx}</lx><ly>{Ly}</ly><lz>{Lz}</lz></domain>
       <components>
         <moleculetype id="1" name="1CLJ">
           <site type="LJ126" id="1" name="LJ"><coords><x>0.0</x><y>0.0</y><z>0.0</z></coords><mass>1.0</mass><sigma>1.0</sigma><epsilon>1.0</epsilon><shifted>false</shifted></site>
@@ -204,7 +214,7 @@ MARDYN_XML = """<?xml version='1.0' encoding='UTF-8'?>
               <latticeOccupancy>1</latticeOccupancy>
               <density>{rho}</density>
             </filler>
-            <object type="Cuboid"><lower><x>0</x><y>0</y><z>0</z></lower><upper><x>{L}</x><y>{L}</y><z>{L}</z></upper></object>
+            <object type="Cuboid"><lower><x>0</x><y>0</y><z>0</z></lower><upper><x>{Lx}</x><y>{Ly}</y><z>{Lz}</z></upper></object>
             <velocityAssigner type="EqualVelocityDistribution"></velocityAssigner>
           </objectgenerator>
         </generator>
@@ -212,7 +222,7 @@ MARDYN_XML = """<?xml version='1.0' encoding='UTF-8'?>
     </ensemble>
     <algorithm>
       <parallelisation type="DomainDecomposition"></parallelisation>
-      <datastructure type="{container}"><cellsInCutoffRadius>1</cellsInCutoffRadius></datastructure>
+      <datastructure type="{container}"><cellsInCutoffRadius>1</cellsInCutoffRadius>{container_options}</datastructure>
       <cutoffs type="CenterOfMass"><defaultCutoff unit="reduced">{rc}</defaultCutoff><radiusLJ unit="reduced">{rc}</radiusLJ></cutoffs>
       <electrostatic type="ReactionField"><epsilon>1.0e+10</epsilon></electrostatic>
     </algorithm>
@@ -274,12 +284,10 @@ def run_reference_sample(sample_cells, steps, threads, exe=None):
                         trial[cand] = 0.0
                 _PICKED["exe"] = max(trial, key=trial.get)
             exe = _PICKED["exe"]
-    a = (4.0 / RHO) ** (1.0 / 3.0)
-    L = sample_cells * a
     with tempfile.TemporaryDirectory() as td:
         cfg = os.path.join(td, "cfg.xml")
         with open(cfg, "w") as f:
-            f.write(MARDYN_XML.format(dt=DT, steps=steps, temp=TEMP, L=repr(L), rho=RHO, rc=RC, integrator="Leapfrog", container="LinkedCells"))
+            f.write(mardyn_xml(steps, sample_cells, gpu=False))
         env = dict(os.environ, OMP_NUM_THREADS=str(threads), OMP_PROC_BIND="close", OMP_PLACES="cores")
         t0 = time.time()
         p = subprocess.run([exe, cfg, "--steps", str(steps)], cwd=td, env=env, capture_output=True, text=True, timeout=3000)
@@ -298,21 +306,21 @@ def run_reference_sample(sample_cells, steps, threads, exe=None):
 MARDYN_GPU = os.path.join(ROOT, "ls1-mardyn_b200", "host", "_build", "MarDynGpu")
 
 
-def run_mardyn_gpu(cells, steps, threads, timeout=1500):
+def run_mardyn_gpu(cells, steps, threads, timeout=1500, devices=1):
     """The reference-facing drop-in, end to end: ls1-MarDyn's own executable and unmodified time loop with
     <datastructure type="GpuLinkedCells"> + <integrator type="GpuLeapfrog"> (ls1-mardyn_b200/host/), on the same XML the
     reference arm runs (its MultiObjectGenerator fcc lattice, NVT).  HOST buffers on both sides: the molecules start as the
     reference's host Molecule objects (uploaded once, in prepare_start) and end as host Molecule objects again (full-state
     mirror download at the last step, inside the loop timer).  Returns dict(mmups over upload + loop, ...) or None when the
-    binary was not built (needs the reference tree at build time)."""
+    binary was not built (needs the reference tree at build time).
+    devices > 1: <devices>N</devices> - the one process owns N device blocks (DomainDecomposition's grid), one per GPU, and steps them
+    as a group (ls1g_step_group); cells is then [nx, ny, nz] of the whole box."""
     if not (os.path.exists(MARDYN_GPU) and os.access(MARDYN_GPU, os.X_OK)):
         return None
-    a = (4.0 / RHO) ** (1.0 / 3.0)
-    L = cells * a
     with tempfile.TemporaryDirectory() as td:
         cfg = os.path.join(td, "cfg.xml")
         with open(cfg, "w") as f:
-            f.write(MARDYN_XML.format(dt=DT, steps=steps, temp=TEMP, L=repr(L), rho=RHO, rc=RC, integrator="GpuLeapfrog", container="GpuLinkedCells"))
+            f.write(mardyn_xml(steps, cells, gpu=True, devices=devices))
         env = dict(os.environ, OMP_NUM_THREADS=str(threads), OMP_PROC_BIND="close", OMP_PLACES="cores")
         t0 = time.time()
         p = subprocess.run([MARDYN_GPU, cfg, "--steps", str(steps), "--final-checkpoint=0"], cwd=td, env=env, capture_output=True, text=True, timeout=timeout)
@@ -593,10 +601,18 @@ def main_b200(args):
     c.close()
 
     # ---- e2e, the reference-facing drop-in: ls1-MarDyn's own executable + time loop with the GpuLinkedCells container ----------
+    # N > 1: one MarDynGpu process owns all N GPUs (<devices>N</devices>, the blocks of DomainDecomposition's grid stepped as a group,
+    # ls1g_step_group).  The other ranks have released their devices by then: the process group is left first, rank 0 runs it alone.
     md = None
-    if rank == 0 and world == 1 and not args.no_mardyn_gpu:
+    if world > 1:
+        del host
+        torch.cuda.empty_cache()
+        barrier()
+        dist.destroy_process_group()
+    if rank == 0 and not args.no_mardyn_gpu:
         try:
-            md = run_mardyn_gpu(args.e2e_cells or args.cells, args.steps, host_cores())
+            cells_e2e = args.e2e_cells or args.cells
+            md = run_mardyn_gpu(cells_e2e if world == 1 else global_cells(world, cells_e2e), args.steps, host_cores(), devices=world)
         except Exception as ex:                                  # reported, never silently replaced
             e2e["mardyn_gpu_error"] = str(ex)[-400:]
     if md is not None:
@@ -604,7 +620,7 @@ def main_b200(args):
                "d2h_bytes_per_step": md["d2h_bytes"] // md["steps"], "steps": md["steps"], "n_molecules": md["n"],
                "what": "MarDynGpu = the reference's executable and unmodified Simulation::simulate loop with <datastructure type=GpuLinkedCells> + "
                        "<integrator type=GpuLeapfrog> (ls1-mardyn_b200/host/): host Molecule objects -> device (once) -> %d steps, scalars to Domain every step "
-                       "-> full state back into host Molecule objects at the last step; time = upload + the reference's own loop timer" % md["steps"],
+                       "-> full state back into host Molecule objects at the last step; time = upload + the reference's own loop timer%s" % (md["steps"], "" if world == 1 else "; ONE process drives all %d GPUs (<devices>%d</devices>)" % (world, world)),
                "seconds": {"upload": round(md["upload_s"], 3), "loop": round(md["loop_s"], 3), "of_loop_device_calls": round(md["device_s"], 3),
                            "of_loop_final_mirror": round(md["mirror_s"], 3), "process_wall": round(md["wall_s"], 1),
                            "cuda_context_creation_not_counted": round(md["context_s"], 3),
@@ -646,8 +662,6 @@ def main_b200(args):
         if cb is not None:
             line["cpu_baseline"] = cb
         print(json.dumps(line), flush=True)
-    if world > 1:
-        dist.destroy_process_group()
     return 0
 
 

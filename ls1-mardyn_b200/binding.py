@@ -107,6 +107,13 @@ def decomp_box(grid, coords, global_length):
     return list(bmin), list(bmax)
 
 
+def device_count():
+    """ls1g_device_count: CUDA devices this process can use (0 on a host without a usable GPU)"""
+    n = C.c_int(0)
+    _chk(lib().ls1g_device_count(C.byref(n)))
+    return n.value
+
+
 def fp64_peak_tflops(device=0):
     t = C.c_double()
     _chk(lib().ls1g_measure_fp64_peak(int(device), C.byref(t)))

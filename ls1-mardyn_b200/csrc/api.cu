@@ -382,11 +382,20 @@ extern "C" int ls1g_debug_cell_pairs(const ls1g_ctx* c, uint32_t* triplets, size
 // storage
 // ------------------------------------------------------------------------------------------------
 static size_t default_capacity(const ls1g_ctx* c, size_t n) {
-	// halo copies live in the shell of halo cells: N * (cells incl. halo / real cells - 1), with head room
-	double tot = 1., real = 1.;
-	for (int d = 0; d < 3; ++d) { tot *= c->grid.cpd[d]; real *= (c->grid.cpd[d] - 2); }
-	double est = (double)n * (tot / real - 1.) * 1.3 + 4096;
-	double hard = 27.0 * (double)n + 64;
+	// halo copies live in the shell of halo cells: N * (cells incl. halo / real cells - 1), with head room.  The neighbour-list loop
+	// bins into cells of cutoff + skin, whose shell is thicker: the larger of the two ratios counts.
+	auto shell = [](const Grid& g) {
+		double tot = 1., real = 1.;
+		for (int d = 0; d < 3; ++d) { tot *= g.cpd[d]; real *= (g.cpd[d] - 2); }
+		return tot / real - 1.;
+	};
+	double ratio = shell(c->grid);
+	if (c->skin > 0.) {
+		Grid g;
+		if (grid_init_cut(g, c->cfg, std::max(c->cfg.cutoff, c->cfg.lj_cutoff) + c->skin, -1) == 0) ratio = std::max(ratio, shell(g));
+	}
+	double est = (double)n * ratio * 1.3 + 4096;
+	double hard = 27.0 * (double)n + 4096;
 	return n + (size_t)std::min(est, hard) + (size_t)(0.05 * n);
 }
 

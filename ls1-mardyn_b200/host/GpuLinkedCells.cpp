@@ -459,40 +459,62 @@ int GpuLinkedCells::blockOf(const double* r) const {
 // <devices> > 1: the gathered molecules (staging arrays, n entries) are cut into the blocks and uploaded block by block
 void GpuLinkedCells::uploadBlocks(size_t n) {
 	const int nb = numDevices();
+	// counting sort of the staging arrays by owning block, all threads: per-thread histograms -> offsets -> scatter
 	std::vector<int> owner(n);
-	std::vector<size_t> count(static_cast<size_t>(nb) + 1, 0);
+	int nt = 1;
 #if defined(_OPENMP)
-#pragma omp parallel for schedule(static)
+	nt = omp_get_max_threads();
 #endif
-	for (long i = 0; i < static_cast<long>(n); ++i) owner[i] = blockOf(_sR + 3 * i);
-	for (size_t i = 0; i < n; ++i) ++count[owner[i] + 1];
+	std::vector<size_t> cursor(static_cast<size_t>(nt) * nb, 0), start(static_cast<size_t>(nb) + 1, 0);
 	const bool rot = !_pointMolecules;
-	std::vector<uint64_t> id;
-	std::vector<uint32_t> cid;
-	std::vector<double> r, v, q, L;
-	for (int b = 0; b < nb; ++b) {
-		const size_t m = count[b + 1];
-		id.resize(m); cid.resize(m); r.resize(3 * m); v.resize(3 * m);
-		if (rot) { q.resize(4 * m); L.resize(3 * m); }
-		size_t k = 0;
-		for (size_t i = 0; i < n; ++i) {
-			if (owner[i] != b) continue;
+	std::vector<uint64_t> id(n);
+	std::vector<uint32_t> cid(n);
+	std::vector<double> r(3 * n), v(3 * n), q(rot ? 4 * n : 0), L(rot ? 3 * n : 0);
+#if defined(_OPENMP)
+#pragma omp parallel num_threads(nt)
+#endif
+	{
+		int t = 0;
+#if defined(_OPENMP)
+		t = omp_get_thread_num();
+#endif
+		const size_t lo = n * static_cast<size_t>(t) / nt, hi = n * static_cast<size_t>(t + 1) / nt;
+		size_t* mine = cursor.data() + static_cast<size_t>(t) * nb;
+		for (size_t i = lo; i < hi; ++i) { owner[i] = blockOf(_sR + 3 * i); ++mine[owner[i]]; }
+#if defined(_OPENMP)
+#pragma omp barrier
+#pragma omp single
+#endif
+		{
+			for (int b = 0; b < nb; ++b) {
+				size_t run = start[b];
+				for (int u = 0; u < nt; ++u) { const size_t c = cursor[static_cast<size_t>(u) * nb + b]; cursor[static_cast<size_t>(u) * nb + b] = run; run += c; }
+				start[b + 1] = run;
+			}
+		}
+		for (size_t i = lo; i < hi; ++i) {
+			const size_t k = mine[owner[i]]++;
 			id[k] = _sId[i]; cid[k] = _sCid[i];
 			for (int d = 0; d < 3; ++d) { r[3 * k + d] = _sR[3 * i + d]; v[3 * k + d] = _sV[3 * i + d]; }
 			if (rot) {
 				for (int d = 0; d < 4; ++d) q[4 * k + d] = _sQ[4 * i + d];
 				for (int d = 0; d < 3; ++d) L[3 * k + d] = _sL[3 * i + d];
 			}
-			++k;
 		}
+	}
+	// every block is given room for the fullest one: its halo copies come from neighbours that may hold more molecules than itself
+	size_t fullest = 0;
+	for (int b = 0; b < nb; ++b) fullest = std::max(fullest, start[b + 1] - start[b]);
+	for (int b = 0; b < nb; ++b) {
+		const size_t m = start[b + 1] - start[b], o = start[b];
 		if (!_deviceLoaded) {
 			const double tr = wall();
-			chk(ls1g_reserve(_ctxs[b], m), "ls1g_reserve");
+			chk(ls1g_reserve(_ctxs[b], fullest + fullest / 8), "ls1g_reserve");
 			_tContext += wall() - tr;
 		}
 		uint64_t id0 = 0; uint32_t cid0 = 0; double r0[3] = {0., 0., 0.};
-		chk(ls1g_upload(_ctxs[b], m, m ? id.data() : &id0, m ? cid.data() : &cid0, m ? r.data() : r0, m ? v.data() : nullptr,
-		                rot && m ? q.data() : nullptr, rot && m ? L.data() : nullptr), "ls1g_upload");
+		chk(ls1g_upload(_ctxs[b], m, m ? id.data() + o : &id0, m ? cid.data() + o : &cid0, m ? r.data() + 3 * o : r0, m ? v.data() + 3 * o : nullptr,
+		                rot && m ? q.data() + 4 * o : nullptr, rot && m ? L.data() + 3 * o : nullptr), "ls1g_upload");
 	}
 }
 

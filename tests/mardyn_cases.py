@@ -88,9 +88,7 @@ def write_case(dirname, name, steps, variant, temperature=None, replicate=1, con
 def write_fcc_case(dirname, cells, steps, gpu, tag):
     """bench.py's workload (1CLJ fcc from the reference's own MultiObjectGenerator) with a ResultWriter; returns the config path"""
     import bench
-    L = cells * (4.0 / bench.RHO) ** (1.0 / 3.0)
-    xml = bench.MARDYN_XML.format(dt=bench.DT, steps=steps, temp=bench.TEMP, L=repr(L), rho=bench.RHO, rc=bench.RC,
-                                  integrator="GpuLeapfrog" if gpu else "Leapfrog", container="GpuLinkedCells" if gpu else "LinkedCells")
+    xml = bench.mardyn_xml(steps, cells, gpu)
     xml = xml.replace("<output></output>", "<output><outputplugin name=\"ResultWriter\"><writefrequency>1</writefrequency><writeprecision>15</writeprecision>"
                                            "<outputprefix>%s</outputprefix></outputplugin></output>" % tag)
     cfg = os.path.join(dirname, tag + ".xml")

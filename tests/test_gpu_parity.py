@@ -611,7 +611,9 @@ def _group_of_ranks(n_ranks, box, rc, ids, r, v, capacity):
     for rank in range(n_ranks):
         grid, coords = ls1g.decomp_grid(n_ranks, rank)
         bmin, bmax = ls1g.decomp_box(grid, coords, box)
-        c = ls1g.Container(bmax, rc, box_min=bmin, global_length=box, rank_grid=grid, rank_coords=coords, capacity=capacity)
+        # all ranks on this GPU on a one-GPU box; spread over the GPUs (peer copies over NVLink) where there are several
+        c = ls1g.Container(bmax, rc, box_min=bmin, global_length=box, rank_grid=grid, rank_coords=coords, capacity=capacity,
+                           device=rank % ls1g.device_count())
         c.set_components([ls1g.lj_component()])
         mine = np.all((r >= np.array(bmin)) & (r < np.array(bmax)), axis=1)
         c.add_particles(ids[mine], np.zeros(int(mine.sum()), dtype=np.uint32), r[mine], v[mine])
@@ -766,7 +768,7 @@ def test_multisite_group_list_loop_matches_single_rank():
             grid, coords = ls1g.decomp_grid(2, rank)
             bmin, bmax = ls1g.decomp_box(grid, coords, box)
             c = ls1g.Container(bmax, rc, box_min=bmin, lj_cutoff=rclj, eps_rf=float(d["epsRF"][0]), global_length=box, rank_grid=grid,
-                               rank_coords=coords, capacity=4 * len(st["id"]) + 1024)
+                               rank_coords=coords, capacity=4 * len(st["id"]) + 1024, device=rank % ls1g.device_count())
             c.set_components(comps, mix)
             mine = np.all((st["r"] >= np.array(bmin)) & (st["r"] < np.array(bmax)), axis=1)
             c.add_particles(st["id"][mine], st["cid"][mine], st["r"][mine], st["v"][mine], st["q"][mine], st["L"][mine])

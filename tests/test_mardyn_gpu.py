@@ -179,7 +179,7 @@ def test_rdf_plugin_samples_on_the_device(variant, tmp_path):
     cpu_dir.mkdir(), gpu_dir.mkdir()
     M.run(M.REF_EXE, M.write_case(str(cpu_dir), "ex_CO2", 6, "cpu", output_plugins=RDF_PLUGIN, equilibration=0), 6)
     gpu = M.run(M.GPU_EXE, M.write_case(str(gpu_dir), "ex_CO2", 6, variant, output_plugins=RDF_PLUGIN, equilibration=0), 6)
-    assert "6 RDF sample(s) on the device" in gpu["log"]
+    assert "6 RDF and 0 FLOP sample(s) on the device" in gpu["log"]
     assert "mirror frequency 0 (from the plugins' write frequencies)" in gpu["log"]
     a, b = _rdf_tables(str(cpu_dir)), _rdf_tables(str(gpu_dir))
     assert len(a) == 4 and sorted(a) == sorted(b)          # rdf_0-0.{3,6}.rdf and .ardf
