@@ -104,10 +104,11 @@ int k_forces_1clj(ls1g_ctx* c) {
 	if (ls1g_ensure_partials(c, nb ? nb : 1, 5)) return 1;
 	a.partials = c->partials;
 	if (n && nb) {
-		static bool attr_set = false;
-		if (!attr_set) {
+		static unsigned long long attr_set = 0;      // bit d: done on device d (function attributes are per device)
+		const int d = c->cfg.device;
+		if (d >= 64 || !(attr_set >> d & 1ull)) {
 			CUDA_TRY(cudaFuncSetAttribute(force_1clj_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, LJ3_SMEM_BYTES));
-			attr_set = true;
+			if (d < 64) attr_set |= 1ull << d;
 		}
 		timer_start(c, LS1G_T_FORCE);
 		force_1clj_tile_kernel<<<nb, LJ3_W * 32, LJ3_SMEM_BYTES, c->stream>>>(a);

@@ -210,8 +210,9 @@ template <int R>
 __global__ void __launch_bounds__(NLGeom<R>::BT) nl_build_kernel(NLArgs a) {
 	constexpr int BT = NLGeom<R>::BT, NR = NLGeom<R>::NR, QCAP = NLGeom<R>::QCAP;
 	extern __shared__ __align__(16) unsigned char nl_bsm[];
-	float* xs = (float*)nl_bsm; float* ys = xs + a.btcap; float* zs = ys + a.btcap;
-	unsigned short* q = (unsigned short*)(zs + a.btcap);          // q[t][tid]: queued survivors, one column per lane
+	// candidates in groups of four: [x0..x3 | y0..y3 | z0..z3], 48 bytes per group (three 16-byte loads off one address register)
+	float* cs = (float*)nl_bsm;
+	unsigned short* q = (unsigned short*)(cs + 3 * a.btcap);      // q[t][tid]: queued survivors, one column per lane
 	__shared__ NLPlan P;
 	const Grid& g = a.g;
 	const int tid = threadIdx.x;
@@ -239,7 +240,8 @@ __global__ void __launch_bounds__(NLGeom<R>::BT) nl_build_kernel(NLArgs a) {
 		for (int t = tid; t < padded; t += BT) {
 			float x = 1e30f, y = 1e30f, z = 1e30f;
 			if (t < len) { const double4 Q = a.pos[beg + t]; x = (float)(Q.x - ox); y = (float)(Q.y - oy); z = (float)(Q.z - oz); }
-			xs[off + t] = x; ys[off + t] = y; zs[off + t] = z;
+			float* c4 = cs + ((off + t) >> 2) * 12 + ((off + t) & 3);
+			c4[0] = x; c4[4] = y; c4[8] = z;
 		}
 	}
 	__syncthreads();
@@ -253,16 +255,19 @@ __global__ void __launch_bounds__(NLGeom<R>::BT) nl_build_kernel(NLArgs a) {
 	uint2* my = (uint2*)(a.lists + ((size_t)blockIdx.x * a.lcap4 * BT + tid) * 4);     // entries 4t..4t+3 at my[t * BT]
 	unsigned short* const q0 = q + tid;
 	// the queue is addressed through one 32-bit shared-window register (append = st.shared.u16 + add, both predicated)
-	const uint32_t qa0 = (uint32_t)__cvta_generic_to_shared(q0);
+	const uint32_t qa0 = (uint32_t)__cvta_generic_to_shared(q0), cs_a = (uint32_t)__cvta_generic_to_shared(cs);
 	const uint32_t qalim = qa0 + (QCAP - 4) * BT * 2;       // room for one more scan iteration
 	uint32_t qa = qa0;
 	int done4 = 0; bool ovf = false;       // groups of 4 entries already written to the list
 	int nA4 = 0;                           // quads that only hold entries of staging batch A
-	bool near = false;                     // a partner closer than 1e-4 (possibly coincident): the force kernel keeps its r2 == 0 test
+	float rmin = 1e30f;                    // a partner closer than 1e-4 (possibly coincident): the force kernel keeps its r2 == 0 test
 	const float rl2 = a.rl2f;
 	// queue -> list: complete quads go out as packed 8-byte stores; a flush in between (queue full) keeps the 0..3 left-over
 	// entries at the front of the queue, the final flush pads them with the dummy entry
+	// (the appends are asm statements without a memory clobber, so that the scan loop keeps its addresses in registers; the clobbers
+	// here order them against the queue reads and writes of the flush)
 	auto flush = [&](bool final) {
+		asm volatile("" ::: "memory");
 		int cnt = (int)(qa - qa0) / (BT * 2);
 		if (final) while (cnt & 3) { q0[cnt * BT] = 0; ++cnt; }
 		const int n4 = cnt >> 2, rem = cnt & 3;
@@ -279,6 +284,7 @@ __global__ void __launch_bounds__(NLGeom<R>::BT) nl_build_kernel(NLArgs a) {
 		}
 		for (int t = 0; t < rem; ++t) q0[t * BT] = q0[(4 * n4 + t) * BT];
 		qa = qa0 + rem * (BT * 2);
+		asm volatile("" ::: "memory");
 	};
 	const int gy = R == 1 ? P.ty[0] : (P.ty[0] - 1) / 2, gz = R == 1 ? P.tz[0] : (P.tz[0] - 1) / 2;
 	while (todo) {      // one pass per owned row present in this warp (warp-uniform control flow)
@@ -291,6 +297,9 @@ __global__ void __launch_bounds__(NLGeom<R>::BT) nl_build_kernel(NLArgs a) {
 		const int xw_first = (int)((a.cell[iw0] & ~HALO_FLAG) % (uint32_t)nx), xw_last = (int)((a.cell[iw1] & ~HALO_FLAG) % (uint32_t)nx);
 		const int cy = P.ty[qq], cz = P.tz[qq];
 		const float gx = mine ? fx : -1e30f, gyf = mine ? fy : -1e30f, gzf = mine ? fz : -1e30f;
+		float nx1 = -gx, ny1 = -gyf, nz1 = -gzf;
+		asm volatile("" : "+f"(nx1), "+f"(ny1), "+f"(nz1));      // opaque: kept in registers instead of being re-derived in every scan iteration
+		const float2 ngx = make_float2(nx1, nx1), ngy = make_float2(ny1, ny1), ngz = make_float2(nz1, nz1);
 		for (int p = 0; p < NR; ++p) {
 			int y, z;
 			nl_tile_row<R>(a, gy, gz, p, y, z);
@@ -300,19 +309,34 @@ __global__ void __launch_bounds__(NLGeom<R>::BT) nl_build_kernel(NLArgs a) {
 				const uint32_t beg = P.beg[p];
 				const int k0 = P.off[p] + (int)((lo - beg) & ~3u), k1 = P.off[p] + (int)((hi - beg + 3u) & ~3u);
 				int val = (k0 + NL_DUMMY) * 8;                 // list entry of candidate k0
-				const int selfv = (y == cy && z == cz && mine) ? (P.off[p] + (int)(i - beg) + NL_DUMMY) * 8 : -1;      // the molecule itself
-				for (int k = k0; k < k1; k += 4, val += 32) {
-					const float4 cx4 = *(const float4*)(xs + k), cy4 = *(const float4*)(ys + k), cz4 = *(const float4*)(zs + k);
-					const float cxa[4] = {cx4.x, cx4.y, cx4.z, cx4.w}, cya[4] = {cy4.x, cy4.y, cy4.z, cy4.w}, cza[4] = {cz4.x, cz4.y, cz4.z, cz4.w};
+				const bool own = y == cy && z == cz;         // the row that holds the lanes' own molecules (warp-uniform)
+				const int selfv = (own && mine) ? (P.off[p] + (int)(i - beg) + NL_DUMMY) * 8 : -1;      // the molecule itself
+				// OWN = false (8 of 9 rows): no candidate is the molecule itself, the index compare drops out of the loop
+				auto scan = [&](auto own_row) {
+					constexpr bool OWN = decltype(own_row)::value;
+					// candidate groups through one 32-bit shared-window address register (3 loads off it, one add per iteration)
+					for (uint32_t ca = cs_a + 12u * (uint32_t)k0, ce = cs_a + 12u * (uint32_t)k1; ca < ce; ca += 48u, val += 32) {
+						float4 cx4, cy4, cz4;
+						asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(cx4.x), "=f"(cx4.y), "=f"(cx4.z), "=f"(cx4.w) : "r"(ca));
+						asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+16];" : "=f"(cy4.x), "=f"(cy4.y), "=f"(cy4.z), "=f"(cy4.w) : "r"(ca));
+						asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4+32];" : "=f"(cz4.x), "=f"(cz4.y), "=f"(cz4.z), "=f"(cz4.w) : "r"(ca));
+						// two candidates per instruction: the packed FP32 pipe of sm_100 (FADD2 / FMUL2 / FFMA2); the filter is issue-bound
+						const float2 dxa = __fadd2_rn(make_float2(cx4.x, cx4.y), ngx), dxb = __fadd2_rn(make_float2(cx4.z, cx4.w), ngx);
+						const float2 dya = __fadd2_rn(make_float2(cy4.x, cy4.y), ngy), dyb = __fadd2_rn(make_float2(cy4.z, cy4.w), ngy);
+						const float2 dza = __fadd2_rn(make_float2(cz4.x, cz4.y), ngz), dzb = __fadd2_rn(make_float2(cz4.z, cz4.w), ngz);
+						const float2 ra = __ffma2_rn(dza, dza, __ffma2_rn(dya, dya, __fmul2_rn(dxa, dxa)));
+						const float2 rb = __ffma2_rn(dzb, dzb, __ffma2_rn(dyb, dyb, __fmul2_rn(dxb, dxb)));
+						float r2a[4] = {ra.x, ra.y, rb.x, rb.y};
 #pragma unroll
-					for (int u = 0; u < 4; ++u) {
-						const float dx = gx - cxa[u], dy = gyf - cya[u], dz = gzf - cza[u];
-						const float r2 = dx * dx + dy * dy + dz * dz;
-						if (r2 < 1e-8f && val + 8 * u != selfv) near = true;
-						if (r2 < rl2 && val + 8 * u != selfv) { asm volatile("st.shared.u16 [%0], %1;" :: "r"(qa), "h"((unsigned short)(val + 8 * u)) : "memory"); qa += BT * 2; }
+						for (int u = 0; u < 4; ++u) {
+							if (OWN && val + 8 * u == selfv) r2a[u] = 1e30f;
+							if (r2a[u] < rl2) { asm volatile("st.shared.u16 [%0], %1;" :: "r"(qa), "h"((unsigned short)(val + 8 * u))); qa += BT * 2; }
+						}
+						rmin = fminf(fminf(rmin, r2a[0]), fminf(fminf(r2a[1], r2a[2]), r2a[3]));
+						if (qa > qalim) flush(false);
 					}
-					if (qa > qalim) flush(false);
-				}
+				};
+				if (own) scan(std::true_type{}); else scan(std::false_type{});
 			}
 			if (p + 1 == NLGeom<R>::ROWS_A && mine) nA4 = done4 + (int)(qa - qa0) / (BT * 2 * 4);      // everything listed so far lies in batch A
 		}
@@ -320,7 +344,7 @@ __global__ void __launch_bounds__(NLGeom<R>::BT) nl_build_kernel(NLArgs a) {
 	flush(true);
 	if (active) a.lcount[(size_t)blockIdx.x * BT + tid] = (uint32_t)done4 | ((uint32_t)nA4 << 16);
 	if (ovf && active) atomicOr(a.flags + 1, (unsigned long long)NL_OVF_LIST);
-	if (near && active) a.flags[6] = 1ull;
+	if (rmin < 1e-8f && active) a.flags[6] = 1ull;
 }
 
 // ---------------------------------------------------------------------------------------------------------------

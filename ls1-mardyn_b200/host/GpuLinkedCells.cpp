@@ -407,32 +407,84 @@ void GpuLinkedCells::uploadFromHost() {
 	uint64_t* id = _sId;
 	uint32_t* cid = _sCid;
 	double *r = _sR, *v = _sV, *q = _sQ, *L = _sL;
+	const bool point = _pointMolecules;      // the device keeps no orientation for a single LJ centre at the origin
+	auto put = [=](const Molecule& m, size_t i) {
+		id[i] = m.getID();
+		cid[i] = m.componentid();
+		for (int d = 0; d < 3; ++d) {
+			r[3 * i + d] = m.r(d);
+			v[3 * i + d] = m.v(d);
+		}
+		if (point) return;
+		for (int d = 0; d < 3; ++d) L[3 * i + d] = m.D(d);
+		const Quaternion& qq = m.q();
+		q[4 * i] = qq.qw();
+		q[4 * i + 1] = qq.qx();
+		q[4 * i + 2] = qq.qy();
+		q[4 * i + 3] = qq.qz();
+	};
+	std::vector<size_t> blockStart;
+	if (!multi()) {
 #if defined(_OPENMP)
 #pragma omp parallel for schedule(static)
 #endif
-	for (long c = 0; c < nc; ++c) {
-		if (first[c + 1] == first[c]) continue;
-		size_t i = first[c];
-		ParticleCell& pc = getCellReference(static_cast<int>(c));
-		for (auto m = pc.iterator(); m.isValid(); ++m, ++i) {
-			id[i] = m->getID();
-			cid[i] = m->componentid();
-			for (int d = 0; d < 3; ++d) {
-				r[3 * i + d] = m->r(d);
-				v[3 * i + d] = m->v(d);
+		for (long c = 0; c < nc; ++c) {
+			if (first[c + 1] == first[c]) continue;
+			size_t i = first[c];
+			ParticleCell& pc = getCellReference(static_cast<int>(c));
+			for (auto m = pc.iterator(); m.isValid(); ++m, ++i) put(*m, i);
+		}
+	} else {
+		// <devices> > 1: the staging arrays are filled block by block (a counting sort by owning block, all threads: every thread
+		// counts the molecules of its cells per block, the prefix sums give it a private range in every block, then it writes)
+		const int nb = numDevices();
+		int nt = 1;
+#if defined(_OPENMP)
+		nt = omp_get_max_threads();
+#endif
+		std::vector<size_t> cursor(static_cast<size_t>(nt) * nb, 0);
+		blockStart.assign(static_cast<size_t>(nb) + 1, 0);
+#if defined(_OPENMP)
+#pragma omp parallel num_threads(nt)
+#endif
+		{
+			int t = 0;
+#if defined(_OPENMP)
+			t = omp_get_thread_num();
+#endif
+			const long c0 = nc * t / nt, c1 = nc * (t + 1) / nt;
+			size_t* mine = cursor.data() + static_cast<size_t>(t) * nb;
+			for (long c = c0; c < c1; ++c) {
+				if (first[c + 1] == first[c]) continue;
+				ParticleCell& pc = getCellReference(static_cast<int>(c));
+				for (auto m = pc.iterator(); m.isValid(); ++m) ++mine[blockOf(m->r_arr().data())];
 			}
-			if (_pointMolecules) continue;      // the device keeps no orientation for a single LJ centre at the origin
-			for (int d = 0; d < 3; ++d) L[3 * i + d] = m->D(d);
-			const Quaternion& qq = m->q();
-			q[4 * i] = qq.qw();
-			q[4 * i + 1] = qq.qx();
-			q[4 * i + 2] = qq.qy();
-			q[4 * i + 3] = qq.qz();
+#if defined(_OPENMP)
+#pragma omp barrier
+#pragma omp single
+#endif
+			{
+				for (int b = 0; b < nb; ++b) {
+					size_t run = blockStart[b];
+					for (int u = 0; u < nt; ++u) {
+						size_t& cu = cursor[static_cast<size_t>(u) * nb + b];
+						const size_t cnt = cu;
+						cu = run;
+						run += cnt;
+					}
+					blockStart[b + 1] = run;
+				}
+			}
+			for (long c = c0; c < c1; ++c) {
+				if (first[c + 1] == first[c]) continue;
+				ParticleCell& pc = getCellReference(static_cast<int>(c));
+				for (auto m = pc.iterator(); m.isValid(); ++m) put(*m, mine[blockOf(m->r_arr().data())]++);
+			}
 		}
 	}
 	const double tCopy0 = wall();
 	_tGather += tCopy0 - t0 - tStage;
-	if (multi()) uploadBlocks(n);
+	if (multi()) uploadBlocks(blockStart);
 	else chk(ls1g_upload(_ctx, n, id, cid, r, v, _pointMolecules ? nullptr : q, _pointMolecules ? nullptr : L), "ls1g_upload");
 	_tH2D += wall() - tCopy0;
 	_bytesUp += n * (8 + 4 + (_pointMolecules ? 6 : 13) * 8);
@@ -456,66 +508,31 @@ int GpuLinkedCells::blockOf(const double* r) const {
 	return (co[0] * _blockGrid[1] + co[1]) * _blockGrid[2] + co[2];
 }
 
-// <devices> > 1: the gathered molecules (staging arrays, n entries) are cut into the blocks and uploaded block by block
-void GpuLinkedCells::uploadBlocks(size_t n) {
+// <devices> > 1: the staging arrays hold the molecules block by block (start[b] .. start[b + 1]); one upload per block, straight from
+// the page-locked staging
+void GpuLinkedCells::uploadBlocks(const std::vector<size_t>& start) {
 	const int nb = numDevices();
-	// counting sort of the staging arrays by owning block, all threads: per-thread histograms -> offsets -> scatter
-	std::vector<int> owner(n);
-	int nt = 1;
-#if defined(_OPENMP)
-	nt = omp_get_max_threads();
-#endif
-	std::vector<size_t> cursor(static_cast<size_t>(nt) * nb, 0), start(static_cast<size_t>(nb) + 1, 0);
 	const bool rot = !_pointMolecules;
-	std::vector<uint64_t> id(n);
-	std::vector<uint32_t> cid(n);
-	std::vector<double> r(3 * n), v(3 * n), q(rot ? 4 * n : 0), L(rot ? 3 * n : 0);
-#if defined(_OPENMP)
-#pragma omp parallel num_threads(nt)
-#endif
-	{
-		int t = 0;
-#if defined(_OPENMP)
-		t = omp_get_thread_num();
-#endif
-		const size_t lo = n * static_cast<size_t>(t) / nt, hi = n * static_cast<size_t>(t + 1) / nt;
-		size_t* mine = cursor.data() + static_cast<size_t>(t) * nb;
-		for (size_t i = lo; i < hi; ++i) { owner[i] = blockOf(_sR + 3 * i); ++mine[owner[i]]; }
-#if defined(_OPENMP)
-#pragma omp barrier
-#pragma omp single
-#endif
-		{
-			for (int b = 0; b < nb; ++b) {
-				size_t run = start[b];
-				for (int u = 0; u < nt; ++u) { const size_t c = cursor[static_cast<size_t>(u) * nb + b]; cursor[static_cast<size_t>(u) * nb + b] = run; run += c; }
-				start[b + 1] = run;
-			}
-		}
-		for (size_t i = lo; i < hi; ++i) {
-			const size_t k = mine[owner[i]]++;
-			id[k] = _sId[i]; cid[k] = _sCid[i];
-			for (int d = 0; d < 3; ++d) { r[3 * k + d] = _sR[3 * i + d]; v[3 * k + d] = _sV[3 * i + d]; }
-			if (rot) {
-				for (int d = 0; d < 4; ++d) q[4 * k + d] = _sQ[4 * i + d];
-				for (int d = 0; d < 3; ++d) L[3 * k + d] = _sL[3 * i + d];
-			}
-		}
-	}
 	// every block is given room for the fullest one: its halo copies come from neighbours that may hold more molecules than itself
 	size_t fullest = 0;
 	for (int b = 0; b < nb; ++b) fullest = std::max(fullest, start[b + 1] - start[b]);
+	if (!_deviceLoaded) {
+		const double tr = wall();
+		for (int b = 0; b < nb; ++b) chk(ls1g_reserve(_ctxs[b], fullest + fullest / 8), "ls1g_reserve");
+		_tContext += wall() - tr;
+	}
+	// one host thread per block: the copies to the GPUs run side by side (each GPU has its own PCIe link)
+	std::vector<int> failed(static_cast<size_t>(nb), 0);
+#if defined(_OPENMP)
+#pragma omp parallel for schedule(static, 1) num_threads(nb)
+#endif
 	for (int b = 0; b < nb; ++b) {
 		const size_t m = start[b + 1] - start[b], o = start[b];
-		if (!_deviceLoaded) {
-			const double tr = wall();
-			chk(ls1g_reserve(_ctxs[b], fullest + fullest / 8), "ls1g_reserve");
-			_tContext += wall() - tr;
-		}
 		uint64_t id0 = 0; uint32_t cid0 = 0; double r0[3] = {0., 0., 0.};
-		chk(ls1g_upload(_ctxs[b], m, m ? id.data() + o : &id0, m ? cid.data() + o : &cid0, m ? r.data() + 3 * o : r0, m ? v.data() + 3 * o : nullptr,
-		                rot && m ? q.data() + 4 * o : nullptr, rot && m ? L.data() + 3 * o : nullptr), "ls1g_upload");
+		if (ls1g_upload(_ctxs[b], m, m ? _sId + o : &id0, m ? _sCid + o : &cid0, m ? _sR + 3 * o : r0, m ? _sV + 3 * o : nullptr,
+		                rot && m ? _sQ + 4 * o : nullptr, rot && m ? _sL + 3 * o : nullptr) != 0) failed[b] = 1;
 	}
+	for (int b = 0; b < nb; ++b) if (failed[b]) fail("ls1g_upload");
 }
 
 void GpuLinkedCells::exchangeAll() {
@@ -986,62 +1003,86 @@ void GpuLinkedCells::downloadMirrorBlocks() {
 	const double t0 = wall();
 	clearHostCells();
 	const bool point = _pointMolecules;
-	const int mask = LS1G_F_ID | LS1G_F_CID | LS1G_F_R | LS1G_F_V | LS1G_F_F | LS1G_F_VI | LS1G_F_CELL | (point ? 0 : (LS1G_F_Q | LS1G_F_L | LS1G_F_M));
+	const int mask = LS1G_F_ID | LS1G_F_CID | LS1G_F_R | LS1G_F_V | LS1G_F_F | LS1G_F_VI | (point ? 0 : (LS1G_F_Q | LS1G_F_L | LS1G_F_M));
 	std::vector<Component>& comps = *global_simulation->getEnsemble()->getComponents();
 	const double zero3[3] = {0., 0., 0.};
-	double tStageAll = 0.;
-	for (ls1g_ctx* cx : _ctxs) {
-		uint64_t slots = 0;
-		chk(ls1g_slot_count(cx, &slots), "ls1g_slot_count");
-		const size_t ns = static_cast<size_t>(slots);
-		if (ns == 0) continue;
-		tStageAll += ensureStaging(ns + 1);
+	const int nb = numDevices();
+	// owned molecules per block (the count query also takes the group out of the list layout: one exchange for all blocks)
+	std::vector<size_t> start(static_cast<size_t>(nb) + 1, 0);
+	for (int b = 0; b < nb; ++b) {
+		ls1g_fields none{};
+		size_t m = 0;
+		chk(ls1g_download(_ctxs[b], 0, 0, 0, &none, &m), "ls1g_download (count)");
+		start[b + 1] = start[b] + m;
+	}
+	const size_t n = start[nb];
+	const double tStageAll = ensureStaging(n + 1);
+	// every block copies its molecules into its own range of the page-locked staging; one host thread per block, so the copies of
+	// the GPUs run side by side (each GPU has its own PCIe link)
+	const double tc = wall();
+	std::vector<int> failed(static_cast<size_t>(nb), 0);
+#if defined(_OPENMP)
+#pragma omp parallel for schedule(static, 1) num_threads(nb)
+#endif
+	for (int b = 0; b < nb; ++b) {
+		const size_t o = start[b], m = start[b + 1] - start[b];
+		if (m == 0) continue;
 		ls1g_fields f{};
-		f.id = _sId; f.cid = _sCid; f.r = _sR; f.v = _sV; f.F = _sF; f.Vi = _sVi; f.cell = _sCell;
-		if (!point) { f.q = _sQ; f.L = _sL; f.M = _sM; }
-		const double tc = wall();
-		chk(ls1g_download_range(cx, mask, 0, ns, &f), "ls1g_download_range");
-		_tD2H += wall() - tc;
-		_bytesDown += ns * (8 + 4 + 4 + (point ? 12 : 22) * 8);
-		const double tf = wall();
-		// host cell of every owned slot
-		std::vector<uint32_t> hc(ns, 0xffffffffu);
+		f.id = _sId + o; f.cid = _sCid + o; f.r = _sR + 3 * o; f.v = _sV + 3 * o; f.F = _sF + 3 * o; f.Vi = _sVi + 3 * o;
+		if (!point) { f.q = _sQ + 4 * o; f.L = _sL + 3 * o; f.M = _sM + 3 * o; }
+		size_t got = 0;
+		if (ls1g_download(_ctxs[b], mask, 0, m, &f, &got) != 0 || got != m) failed[b] = 1;
+	}
+	for (int b = 0; b < nb; ++b) if (failed[b]) fail("ls1g_download");
+	_tD2H += wall() - tc;
+	_bytesDown += n * (8 + 4 + (point ? 12 : 22) * 8);
+	const double tf = wall();
+	// counting sort of all molecules by host cell, all threads (the order inside a cell is fixed by the id sort below)
+	std::vector<uint32_t> hc(n), first(_numCells + 1, 0), fill(_numCells, 0), ord(n);
 #if defined(_OPENMP)
 #pragma omp parallel for schedule(static)
 #endif
-		for (long i = 0; i < static_cast<long>(ns); ++i)
-			if ((_sCell[i] & LS1G_HALO_FLAG) == 0u) hc[i] = static_cast<uint32_t>(getCellIndexOfPoint(_sR + 3 * i));
-		std::vector<size_t> first(_numCells + 1, 0);
-		for (size_t i = 0; i < ns; ++i) if (hc[i] != 0xffffffffu) ++first[hc[i] + 1];
-		for (size_t c = 0; c < _numCells; ++c) first[c + 1] += first[c];
-		std::vector<uint32_t> ord(first[_numCells]);
-		{
-			std::vector<size_t> fill(first.begin(), first.end() - 1);
-			for (size_t i = 0; i < ns; ++i) if (hc[i] != 0xffffffffu) ord[fill[hc[i]]++] = static_cast<uint32_t>(i);      // slot order = (device cell, id)
-		}
+	for (long i = 0; i < static_cast<long>(n); ++i) {
+		hc[i] = static_cast<uint32_t>(getCellIndexOfPoint(_sR + 3 * i));
 #if defined(_OPENMP)
-#pragma omp parallel for schedule(dynamic, 64)
+#pragma omp atomic
 #endif
-		for (long c = 0; c < static_cast<long>(_numCells); ++c) {
-			const size_t a = first[c], b = first[c + 1];
-			if (a == b) continue;
-			std::sort(ord.begin() + a, ord.begin() + b, [&](uint32_t x, uint32_t y) { return _sId[x] < _sId[y]; });
-			ParticleCell& pc = getCellReference(static_cast<int>(c));
-			pc.increaseMoleculeStorage(b - a);
-			for (size_t k = a; k < b; ++k) {
-				const size_t i = ord[k];
-				Molecule m = point ? Molecule(_sId[i], &comps[_sCid[i]], _sR[3 * i], _sR[3 * i + 1], _sR[3 * i + 2], _sV[3 * i], _sV[3 * i + 1], _sV[3 * i + 2],
-				                              1., 0., 0., 0., 0., 0., 0.)
-				                   : Molecule(_sId[i], &comps[_sCid[i]], _sR[3 * i], _sR[3 * i + 1], _sR[3 * i + 2], _sV[3 * i], _sV[3 * i + 1], _sV[3 * i + 2],
-				                              _sQ[4 * i], _sQ[4 * i + 1], _sQ[4 * i + 2], _sQ[4 * i + 3], _sL[3 * i], _sL[3 * i + 1], _sL[3 * i + 2]);
-				m.setF(&_sF[3 * i]);
-				m.setM(const_cast<double*>(point ? zero3 : &_sM[3 * i]));
-				m.setVi(&_sVi[3 * i]);
-				pc.addParticle(m);
-			}
-		}
-		_tFill += wall() - tf;
+		++first[hc[i] + 1];
 	}
+	for (size_t c = 0; c < _numCells; ++c) first[c + 1] += first[c];
+#if defined(_OPENMP)
+#pragma omp parallel for schedule(static)
+#endif
+	for (long i = 0; i < static_cast<long>(n); ++i) {
+		uint32_t k;
+#if defined(_OPENMP)
+#pragma omp atomic capture
+#endif
+		k = fill[hc[i]]++;
+		ord[first[hc[i]] + k] = static_cast<uint32_t>(i);
+	}
+#if defined(_OPENMP)
+#pragma omp parallel for schedule(dynamic, 256)
+#endif
+	for (long c = 0; c < static_cast<long>(_numCells); ++c) {
+		const size_t a = first[c], b = first[c + 1];
+		if (a == b) continue;
+		std::sort(ord.begin() + a, ord.begin() + b, [&](uint32_t x, uint32_t y) { return _sId[x] < _sId[y]; });
+		ParticleCell& pc = getCellReference(static_cast<int>(c));
+		pc.increaseMoleculeStorage(b - a);
+		for (size_t k = a; k < b; ++k) {
+			const size_t i = ord[k];
+			Molecule m = point ? Molecule(_sId[i], &comps[_sCid[i]], _sR[3 * i], _sR[3 * i + 1], _sR[3 * i + 2], _sV[3 * i], _sV[3 * i + 1], _sV[3 * i + 2],
+			                              1., 0., 0., 0., 0., 0., 0.)
+			                   : Molecule(_sId[i], &comps[_sCid[i]], _sR[3 * i], _sR[3 * i + 1], _sR[3 * i + 2], _sV[3 * i], _sV[3 * i + 1], _sV[3 * i + 2],
+			                              _sQ[4 * i], _sQ[4 * i + 1], _sQ[4 * i + 2], _sQ[4 * i + 3], _sL[3 * i], _sL[3 * i + 1], _sL[3 * i + 2]);
+			m.setF(&_sF[3 * i]);
+			m.setM(const_cast<double*>(point ? zero3 : &_sM[3 * i]));
+			m.setVi(&_sVi[3 * i]);
+			pc.addParticle(m);
+		}
+	}
+	_tFill += wall() - tf;
 	_mirrorValid = true;
 	++_mirrors;
 	_tMirror += wall() - t0 - tStageAll;

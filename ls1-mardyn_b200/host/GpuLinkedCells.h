@@ -78,7 +78,7 @@ private:
 	void ensureContext();
 	void uploadComponents();
 	void uploadFromHost();
-	void uploadBlocks(size_t n);
+	void uploadBlocks(const std::vector<size_t>& start);
 	void downloadMirrorBlocks();
 	int blockOf(const double* r) const;
 	double ensureStaging(size_t molecules);
