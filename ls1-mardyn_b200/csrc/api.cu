@@ -184,10 +184,10 @@ extern "C" int ls1g_create(const ls1g_config* cfg, ls1g_ctx** out) {
 	c->bgrid = c->grid;
 	{ const char* e = getenv("LS1G_VI_EVERY_STEP"); c->vi_every_step = e && atoi(e) != 0; }
 	{ const char* lr = getenv("LS1G_LIST_ROWS"); c->list_R = lr && atoi(lr) == 1 ? 1 : 4; }
-	// bank-aware list order (lists.cuh: nl_permute_kernel): 0 never, 1 always, 2 (default) when the previous lists lived >= 32 steps -
-	// the pass costs ~6 ms per build at 10^7 molecules and saves ~0.19 ms per step, so it pays for lattices and cold systems, not for a
-	// liquid whose lists expire every ~18 steps (profiles/r02c_permute_tradeoff.json)
-	{ const char* lp = getenv("LS1G_LIST_PERMUTE"); c->list_permute = lp ? (atoi(lp) == 0 ? 0 : 1) : 2; }
+	// bank-aware list order: 1 (default) the build kernel orders every 16-entry chunk of a list as it writes it (lists.cuh: emit);
+	// 0 tile order; 2 tile order + the separate whole-list pass nl_permute_kernel (measurement only: 5.6 ms per build at 10^7 molecules,
+	// profiles/r02c_permute_tradeoff.json)
+	{ const char* lp = getenv("LS1G_LIST_PERMUTE"); c->list_permute = lp ? atoi(lp) : 1; if (c->list_permute < 0 || c->list_permute > 2) c->list_permute = 1; }
 	{ const char* lm = getenv("LS1G_LIST_MULTISITE"); c->list_multisite = lm && atoi(lm) == 0 ? 0 : 1; }
 	{ const char* sk = getenv("LS1G_SKIN"); c->skin = sk ? atof(sk) : 0.12 * c->cfg.cutoff; if (c->skin < 0.) c->skin = 0.; }
 	c->rc2 = c->cfg.cutoff * c->cfg.cutoff;

@@ -36,6 +36,7 @@ static NLArgs nl_args(ls1g_ctx* c) {
 	a.g = c->bgrid; a.pos = c->cur.pos; a.cell = c->cur.cell; a.cell_start = c->cell_start;
 	a.lists = c->lists; a.lcount = c->lcount; a.plans = (NLPlan*)c->plans; a.flags = c->d_flags; a.bpr = c->list_bpr; a.nyi = c->bgrid.cpd[1] - 2; a.lcap4 = c->list_lcap / 4; a.btcap = c->build_tcap;
 	a.nzi = c->bgrid.cpd[2] - 2; a.nyg = (a.nyi + 1) / 2;
+	a.order = c->list_permute == 1;
 	a.tcap = NL_TCAP;
 	const double rl = std::max(c->cfg.lj_cutoff, c->cfg.cutoff) + c->skin;
 	// FP32 filter: coordinates relative to the block centre are < 8 cell lengths: relative error on r^2 near rl^2 < 2e-5;
@@ -183,7 +184,7 @@ int k_list_build(ls1g_ctx* c) {
 	if (c->list_R == 4) nl_build_kernel<4><<<(unsigned)nb, NLGeom<4>::BT, NL_BUILD_SMEM(4, a.btcap), c->stream>>>(a);
 	else nl_build_kernel<1><<<(unsigned)nb, NLGeom<1>::BT, NL_BUILD_SMEM(1, a.btcap), c->stream>>>(a);
 	CUDA_TRY(cudaGetLastError());
-	const bool permute = c->list_permute == 1 || (c->list_permute == 2 && c->list_life >= 32);
+	const bool permute = c->list_permute == 2;      // the separate whole-list pass (measurement only; the build kernel orders its chunks itself)
 	if (permute) {      // bank-aware order of every list (lists.cuh: nl_permute_kernel)
 		const size_t lanes = nb * nl_bt(c);
 		const int bt = (int)nl_bt(c);

@@ -31,7 +31,8 @@
 //                     0..NL_DUMMY-1 hold a far-away dummy position (r^2 = 3e300 fails the cutoff test), so padding needs no
 //                     special case.  lists[((blk*(LCAP/4) + t/4)*BT + thread)*4 + t%4]: one 8-byte load = 4 entries, padded
 //                     to a multiple of 4 with entry 0.  The molecule itself is not in its list.  Order: tile rows in staging
-//                     order, x ascending.  lcount = quads of the molecule | quads that lie entirely in batch A << 16
+//                     order, x ascending, then every chunk of 16 list positions re-ordered for the shared-memory banks (see the
+//                     build kernel's emit).  lcount = quads of the molecule | quads that lie entirely in batch A << 16
 #pragma once
 
 #define NL_BT 128          // owned slots per cell row and block
@@ -64,6 +65,7 @@ struct NLArgs {
 	unsigned long long* flags;  // [1] |= NL_OVF_*
 	int bpr;                    // blocks per row (R = 4: per row bundle)
 	int lcap4;                  // list capacity per molecule in units of 4 entries
+	int order;                  // 1: bank-aware order of every list chunk (build kernel), 0: tile order
 	int btcap;                  // capacity of the build kernel's tile (NL_TCAP0 or NL_TCAP)
 	int nyi, nzi;               // owned rows per dimension
 	int nyg;                    // R = 4: row bundles in y = ceil(nyi / 2)
@@ -262,28 +264,62 @@ __global__ void __launch_bounds__(NLGeom<R>::BT) nl_build_kernel(NLArgs a) {
 	int nA4 = 0;                           // quads that only hold entries of staging batch A
 	float rmin = 1e30f;                    // a partner closer than 1e-4 (possibly coincident): the force kernel keeps its r2 == 0 test
 	const float rl2 = a.rl2f;
-	// queue -> list: complete quads go out as packed 8-byte stores; a flush in between (queue full) keeps the 0..3 left-over
-	// entries at the front of the queue, the final flush pads them with the dummy entry
+	// queue -> list, in CHUNKS of up to 16 entries = 16 consecutive list positions, and in a bank-aware order.  The force kernel reads
+	// one tile entry per lane and list position: a random 8-byte (Z) and 16-byte (XY) shared-memory read per lane, ~13 wavefronts
+	// per warp and position in tile order against 6 without conflicts - more than the FP64 pipe needs for the same position.  The
+	// ORDER of a molecule's list is free, so lane l wants at list position t an entry whose tile index is = (l + t) mod 16: then the
+	// 16 lanes of a half-warp hit 16 different 8-byte banks of Z and the 8 lanes of a quarter-warp 8 different 16-byte banks of XY.
+	// The 16 positions of a chunk want every residue once, so a chunk is a 16-slot hash table (rows 0..15 of the lane's queue
+	// column, the chunk's entries wait in registers, a 16-bit mask tracks the free slots): an entry goes to the slot that wants its
+	// residue, else to the slot 8 further (keeps XY conflict-free), else to the first free slot.  A fixed function of the build: runs stay bitwise reproducible.
+	// The whole warp flushes together (mode 0: some lane's queue is nearly full -> every lane with >= 16 entries emits one chunk;
+	// mode 1: end of staging batch A -> all complete quads; mode 2: end of the list -> everything, padded with the dummy entry 0).
 	// (the appends are asm statements without a memory clobber, so that the scan loop keeps its addresses in registers; the clobbers
 	// here order them against the queue reads and writes of the flush)
-	auto flush = [&](bool final) {
+	const int order = a.order;
+	auto emit = [&](const int n) {       // n <= 16 entries from the queue front -> (n + 3) / 4 quads of the list
+		const int n4 = (n + 3) >> 2, np = 4 * n4;
+		if (done4 + n4 > a.lcap4) { ovf = true; return; }
+		uint32_t e[16];
+#pragma unroll
+		for (int j = 0; j < 16; ++j) e[j] = j < n ? (uint32_t)q0[j * BT] : 0u;
+		const uint32_t base = (uint32_t)(tid + 4 * done4);      // lane + list position of slot 0
+		uint32_t free_slots = np >= 16 ? 0xffffu : (1u << np) - 1u;            // bit s: slot s of the chunk is still empty
+#pragma unroll
+		for (int j = 0; j < 16; ++j) {
+			if (j < n) {
+				uint32_t s = ((e[j] >> 3) - base) & 15u;
+				if (!(free_slots >> s & 1u)) s ^= 8u;
+				if (!order || !(free_slots >> s & 1u)) s = (uint32_t)__ffs((int)free_slots) - 1u;
+				free_slots &= ~(1u << s);
+				q0[s * BT] = (unsigned short)e[j];
+			}
+		}
+		while (free_slots) { q0[(__ffs((int)free_slots) - 1) * BT] = 0; free_slots &= free_slots - 1u; }      // final chunk: the pad entries
+		for (int t = 0; t < n4; ++t) {
+			const unsigned short* w4 = q0 + 4 * t * BT;
+			uint2 w;
+			w.x = (uint32_t)w4[0] | ((uint32_t)w4[BT] << 16);
+			w.y = (uint32_t)w4[2 * BT] | ((uint32_t)w4[3 * BT] << 16);
+			my[(size_t)(done4 + t) * BT] = w;
+		}
+		done4 += n4;
+	};
+	auto flush = [&](const int mode) {
 		asm volatile("" ::: "memory");
 		int cnt = (int)(qa - qa0) / (BT * 2);
-		if (final) while (cnt & 3) { q0[cnt * BT] = 0; ++cnt; }
-		const int n4 = cnt >> 2, rem = cnt & 3;
-		if (done4 + n4 > a.lcap4) ovf = true;
-		else {
-			for (int t = 0; t < n4; ++t) {
-				const unsigned short* e = q0 + 4 * t * BT;
-				uint2 w;
-				w.x = (uint32_t)e[0] | ((uint32_t)e[BT] << 16);
-				w.y = (uint32_t)e[2 * BT] | ((uint32_t)e[3 * BT] << 16);
-				my[(size_t)(done4 + t) * BT] = w;
+		for (;;) {
+			const int n = cnt >= 16 ? 16 : (mode == 0 ? 0 : (mode == 1 ? (cnt & ~3) : cnt));
+			if (!__any_sync(0xffffffffu, n > 0)) break;
+			if (n > 0) {
+				emit(n);
+				const int rem = cnt - n;
+				for (int j = 0; j < rem; ++j) q0[j * BT] = q0[(n + j) * BT];
+				cnt = rem;
 			}
-			done4 += n4;
+			if (mode == 0) break;
 		}
-		for (int t = 0; t < rem; ++t) q0[t * BT] = q0[(4 * n4 + t) * BT];
-		qa = qa0 + rem * (BT * 2);
+		qa = qa0 + cnt * (BT * 2);
 		asm volatile("" ::: "memory");
 	};
 	const int gy = R == 1 ? P.ty[0] : (P.ty[0] - 1) / 2, gz = R == 1 ? P.tz[0] : (P.tz[0] - 1) / 2;
@@ -333,15 +369,18 @@ __global__ void __launch_bounds__(NLGeom<R>::BT) nl_build_kernel(NLArgs a) {
 							if (r2a[u] < rl2) { asm volatile("st.shared.u16 [%0], %1;" :: "r"(qa), "h"((unsigned short)(val + 8 * u))); qa += BT * 2; }
 						}
 						rmin = fminf(fminf(rmin, r2a[0]), fminf(fminf(r2a[1], r2a[2]), r2a[3]));
-						if (qa > qalim) flush(false);
+						if (__any_sync(0xffffffffu, qa > qalim)) flush(0);
 					}
 				};
 				if (own) scan(std::true_type{}); else scan(std::false_type{});
 			}
-			if (p + 1 == NLGeom<R>::ROWS_A && mine) nA4 = done4 + (int)(qa - qa0) / (BT * 2 * 4);      // everything listed so far lies in batch A
+			if (p + 1 == NLGeom<R>::ROWS_A) {      // everything listed so far lies in batch A: its complete quads go out now
+				flush(1);
+				if (mine) nA4 = done4;
+			}
 		}
 	}
-	flush(true);
+	flush(2);
 	if (active) a.lcount[(size_t)blockIdx.x * BT + tid] = (uint32_t)done4 | ((uint32_t)nA4 << 16);
 	if (ovf && active) atomicOr(a.flags + 1, (unsigned long long)NL_OVF_LIST);
 	if (rmin < 1e-8f && active) a.flags[6] = 1ull;

@@ -126,7 +126,7 @@ struct ls1g_ctx {
 	uint64_t list_rebuilds;                 // list builds since the context was created (ls1g_list_stats)
 	int      list_R;                        // cell rows per block of the list kernels: 4 (2 x 2 bundle) or 1 (lists.cuh)
 	int      list_multisite;                // rigid multi-site systems take the list loop too (LS1G_LIST_MULTISITE=0: per-step cell scan)
-	int      list_permute;                  // bank-aware list order after a build: 0 never, 1 always, 2 when the last lists lived >= 32 steps
+	int      list_permute;                  // bank-aware list order: 1 in the build kernel (default), 0 none, 2 separate whole-list pass (LS1G_LIST_PERMUTE)
 	uint64_t list_steps;                    // list steps completed since the context was created
 	uint64_t list_steps_at_build, list_life;   // ... at the last build; lifetime (steps) of the lists that build replaced
 	int      list_zchk;                     // the last build saw a (nearly) coincident pair: force kernels keep the r2 == 0 test
