@@ -306,6 +306,8 @@ int k_forces_list_post(ls1g_ctx* c, double dt, int vi) {
 // numbering (a build block of 128 or 512 lanes is a whole number of these blocks).  Same pair functions and calcFM epilogue as
 // force_generic_kernel (pair_body.cuh); per-block partials [5] as there.
 #define NLM_THREADS 128
+#define NLM_QCAP 80        // queue entries per lane (partners inside the cutoff waiting for their site loops)
+#define NLM_CHUNK4 4       // list quads scanned between two "queue nearly full?" votes
 #ifndef NLM_MINB
 #define NLM_MINB 3         // resident blocks per SM the register allocation aims at
 #endif
@@ -322,6 +324,7 @@ __global__ void __launch_bounds__(NLM_THREADS, NLM_MINB) nl_force_ms_kernel(Forc
 	constexpr int NS = FIXED ? NLJ + NCH + 2 * NDI + 2 * NQU : 1;
 	__shared__ double red[5 * 32];
 	__shared__ NLPlan P;
+	__shared__ uint32_t queue[NLM_QCAP * NLM_THREADS];
 	if (m.guard && *m.guard > m.guard_thr) return;      // speculatively enqueued step, lists expired (see run_list_steps)
 	const int tid = threadIdx.x;
 	const size_t gl = (size_t)blockIdx.x * NLM_THREADS + tid;
@@ -335,50 +338,82 @@ __global__ void __launch_bounds__(NLM_THREADS, NLM_MINB) nl_force_ms_kernel(Forc
 	if (m.R == 4) q = (t >= P.o[1]) + (t >= P.o[2]) + (t >= P.o[3]);
 	const bool owned = P.live && t < P.o[m.R];
 	const size_t i = (size_t)P.s0[q] + (size_t)(t - P.o[q]);
-	if (owned) {
-		const double4 Pi = a.pos[i];
-		const V3 Ri = ld3(Pi);
-		CompDev ci; ci.n_lj = ci.n_ch = ci.n_di = ci.n_qu = 0;
-		ci = a.comps[pos_cid(Pi)];
-		const double4* si = a.cache + i * (size_t)a.stride;
-		const int i_ch0 = ci.n_lj, i_di0 = ci.n_lj + ci.n_ch, i_qu0 = i_di0 + 2 * ci.n_di;
-		double4 sir[NS];
-		if (FIXED) {
+	double4 Pi = make_double4(0., 0., 0., 0.);
+	if (owned) Pi = a.pos[i];
+	const V3 Ri = ld3(Pi);
+	CompDev ci; ci.n_lj = ci.n_ch = ci.n_di = ci.n_qu = 0;
+	if (owned) ci = a.comps[pos_cid(Pi)];
+	const double4* si = a.cache + i * (size_t)a.stride;
+	const int i_ch0 = ci.n_lj, i_di0 = ci.n_lj + ci.n_ch, i_qu0 = i_di0 + 2 * ci.n_di;
+	double4 sir[NS];
+	if (FIXED && owned) {
 #pragma unroll
-			for (int k = 0; k < NS; ++k) sir[k] = si[k];
-		}
-		MolAcc A_; A_.F = v3(0, 0, 0); A_.M = v3(0, 0, 0); A_.V = v3(0, 0, 0); A_.u6 = 0.; A_.uX = 0.; A_.rf = 0.; A_.np = 0;
-		const uint32_t cnt = m.lcount[gl];
-		const int n4 = (int)(cnt & 0xffffu);
-		const uint2* my = (const uint2*)(m.lists + ((size_t)blk * m.lcap4 * m.BT + t) * 4);
-		for (int o = 0; o < n4; ++o) {
-			const uint2 w = my[(size_t)o * m.BT];
-			const uint32_t ee[4] = {w.x & 0xffffu, w.x >> 16, w.y & 0xffffu, w.y >> 16};
-#pragma unroll 1
-			for (int u = 0; u < 4; ++u) {
-				if (!ee[u]) continue;                               // pad entry
-				const int k = (int)(ee[u] >> 3) - NL_DUMMY;         // tile index
-				int r = 0;
-				while (r + 1 < NR && k >= P.off[r + 1]) ++r;
-				const uint32_t jj = P.beg[r] + (uint32_t)(k - P.off[r]);
-				const double4 Pj = a.pos[jj];
-				const V3 mm = v3(Ri.x - Pj.x, Ri.y - Pj.y, Ri.z - Pj.z);
-				const double m2 = dot(mm, mm);
-				const bool in_lj = m2 < a.rclj2, in_rc = m2 < a.rc2;
-				// coincident centres lie in the same cell: the reference's SingleCellPolicy_ mask skips them (Helpers.h:367-376)
-				if (!(in_lj || in_rc) || m2 == 0.0) continue;
-				++A_.np;
-				if constexpr (FIXED) {
-					double4 sjr[NS];
-					const double4* sj = a.cache + (size_t)jj * a.stride;
+		for (int k = 0; k < NS; ++k) sir[k] = si[k];
+	}
+	MolAcc A_; A_.F = v3(0, 0, 0); A_.M = v3(0, 0, 0); A_.V = v3(0, 0, 0); A_.u6 = 0.; A_.uX = 0.; A_.rf = 0.; A_.np = 0;
+	// Two alternating phases, as in force_generic_kernel: every lane SCANS its list (slot of the entry, centre distance, both cutoffs:
+	// ~30 % of the listed partners are in the skin) and queues the survivors in its shared-memory column; when some lane's queue is
+	// nearly full all lanes DRAIN the same number of entries - the smallest backlog in the warp, so every lane is busy in the long site
+	// loops; only the last round empties the queues.
+	uint32_t* qq = queue + tid;
+	int cnt = 0, o = 0;
+	const int n4 = owned ? (int)(m.lcount[gl] & 0xffffu) : 0;
+	const uint2* my = (const uint2*)(m.lists + ((size_t)blk * m.lcap4 * m.BT + t) * 4);
+	for (;;) {
+		for (;;) {
+			const int oe = min(n4, o + NLM_CHUNK4);
+			for (; o < oe; ++o) {
+				const uint2 w = my[(size_t)o * m.BT];
+				const uint32_t ee[4] = {w.x & 0xffffu, w.x >> 16, w.y & 0xffffu, w.y >> 16};
 #pragma unroll
-					for (int kk = 0; kk < NS; ++kk) sjr[kk] = sj[kk];
-					pair_body_fixed<NLJ, NCH, NDI, NQU>(a, Ri, sir, sjr, mm, in_lj, in_rc, A_);
-				} else {
-					pair_body(a, Ri, ci, si, i_ch0, i_di0, i_qu0, jj, Pj, mm, in_lj, in_rc, A_);
+				for (int u = 0; u < 4; ++u) {
+					const int k = (int)(ee[u] >> 3) - NL_DUMMY;         // tile index; pad entries give k < 0
+					int r = 0;
+					while (r + 1 < NR && k >= P.off[r + 1]) ++r;
+					const uint32_t jj = P.beg[r] + (uint32_t)(k - P.off[r]);
+					bool take = false;
+					if (ee[u]) {
+						const double4 Pj = a.pos[jj];
+						const double mx = Ri.x - Pj.x, my_ = Ri.y - Pj.y, mz = Ri.z - Pj.z;
+						const double m2 = mx * mx + my_ * my_ + mz * mz;
+						// coincident centres lie in the same cell: the reference's SingleCellPolicy_ mask skips them (Helpers.h:367-376)
+						take = (m2 < a.rclj2 || m2 < a.rc2) && m2 != 0.0;
+					}
+					if (take) { qq[cnt * NLM_THREADS] = jj; ++cnt; }
 				}
 			}
+			const bool any_full = __any_sync(0xffffffffu, cnt > NLM_QCAP - 4 * NLM_CHUNK4);
+			const bool any_more = __any_sync(0xffffffffu, o < n4);
+			if (any_full || !any_more) break;
 		}
+		const bool last_round = !__any_sync(0xffffffffu, o < n4);
+		int D = NLM_QCAP;
+		if (!last_round) {
+			const int mn = __reduce_min_sync(0xffffffffu, owned && (o < n4 || cnt > 0) ? cnt : NLM_QCAP);
+			const int mx = __reduce_max_sync(0xffffffffu, cnt);
+			D = max(mn, mx - (NLM_QCAP - 4 * NLM_CHUNK4));
+		}
+		const int take_n = min(cnt, D);
+		for (int tt = 0; tt < take_n; ++tt) {
+			const uint32_t jj = qq[(cnt - 1 - tt) * NLM_THREADS];
+			const double4 Pj = a.pos[jj];
+			const V3 mm = v3(Ri.x - Pj.x, Ri.y - Pj.y, Ri.z - Pj.z);
+			const double m2 = dot(mm, mm);
+			++A_.np;
+			if constexpr (FIXED) {
+				double4 sjr[NS];
+				const double4* sj = a.cache + (size_t)jj * a.stride;
+#pragma unroll
+				for (int kk = 0; kk < NS; ++kk) sjr[kk] = sj[kk];
+				pair_body_fixed<NLJ, NCH, NDI, NQU>(a, Ri, sir, sjr, mm, m2 < a.rclj2, m2 < a.rc2, A_);
+			} else {
+				pair_body(a, Ri, ci, si, i_ch0, i_di0, i_qu0, jj, Pj, mm, m2 < a.rclj2, m2 < a.rc2, A_);
+			}
+		}
+		cnt -= take_n;
+		if (last_round) break;
+	}
+	if (owned) {
 		a.F[3 * i] = A_.F.x; a.F[3 * i + 1] = A_.F.y; a.F[3 * i + 2] = A_.F.z;
 		a.M[3 * i] = A_.M.x; a.M[3 * i + 1] = A_.M.y; a.M[3 * i + 2] = A_.M.z;
 		a.Vi[3 * i] = 0.5 * A_.V.x; a.Vi[3 * i + 1] = 0.5 * A_.V.y; a.Vi[3 * i + 2] = 0.5 * A_.V.z;
