@@ -73,6 +73,9 @@ __global__ void __launch_bounds__(FORCE_THREADS) force_generic_kernel(ForceArgs 
 	constexpr int NS = FIXED ? NLJ + NCH + 2 * NDI + 2 * NQU : 1;      // site-cache rows per molecule
 	__shared__ double red[5 * 32];
 	__shared__ uint32_t queue[GQ_CAP * FORCE_THREADS];
+	__shared__ double ljtab[FIXED ? 1 : 3 * LJ_TAB_MAX];      // mixtures: the LJ tables in shared memory
+	LJTab lj; lj.eps24 = lj.sig2 = lj.shift6 = nullptr;
+	if constexpr (!FIXED) lj = lj_tables(a, ljtab);
 	// block (row, b) = 128 consecutive OWNED slots of one cell row (y, z): the owned cells of a row are contiguous in the
 	// cell-sorted arrays, so no lane is spent on a halo slot
 	const Grid& g = a.g;
@@ -157,7 +160,7 @@ __global__ void __launch_bounds__(FORCE_THREADS) force_generic_kernel(ForceArgs 
 				for (int k = 0; k < NS; ++k) sjr[k] = sj[k];
 				pair_body_fixed<NLJ, NCH, NDI, NQU>(a, Ri, sir, sjr, m, m2 < a.rclj2, m2 < a.rc2, A_);
 			} else {
-				pair_body(a, Ri, ci, si, i_ch0, i_di0, i_qu0, jj, Pj, m, m2 < a.rclj2, m2 < a.rc2, A_);
+				pair_body(a, lj, Ri, ci, si, i_ch0, i_di0, i_qu0, jj, Pj, m, m2 < a.rclj2, m2 < a.rc2, A_);
 			}
 		}
 		cnt -= take;

@@ -325,7 +325,10 @@ __global__ void __launch_bounds__(NLM_THREADS, NLM_MINB) nl_force_ms_kernel(Forc
 	__shared__ double red[5 * 32];
 	__shared__ NLPlan P;
 	__shared__ uint32_t queue[NLM_QCAP * NLM_THREADS];
+	__shared__ double ljtab[FIXED ? 1 : 3 * LJ_TAB_MAX];      // mixtures: the LJ tables in shared memory
 	if (m.guard && *m.guard > m.guard_thr) return;      // speculatively enqueued step, lists expired (see run_list_steps)
+	LJTab lj; lj.eps24 = lj.sig2 = lj.shift6 = nullptr;
+	if constexpr (!FIXED) lj = lj_tables(a, ljtab);
 	const int tid = threadIdx.x;
 	const size_t gl = (size_t)blockIdx.x * NLM_THREADS + tid;
 	const size_t blk = ((size_t)blockIdx.x * NLM_THREADS) / (size_t)m.BT;      // the same for the whole block
@@ -407,7 +410,7 @@ __global__ void __launch_bounds__(NLM_THREADS, NLM_MINB) nl_force_ms_kernel(Forc
 				for (int kk = 0; kk < NS; ++kk) sjr[kk] = sj[kk];
 				pair_body_fixed<NLJ, NCH, NDI, NQU>(a, Ri, sir, sjr, mm, m2 < a.rclj2, m2 < a.rc2, A_);
 			} else {
-				pair_body(a, Ri, ci, si, i_ch0, i_di0, i_qu0, jj, Pj, mm, m2 < a.rclj2, m2 < a.rc2, A_);
+				pair_body(a, lj, Ri, ci, si, i_ch0, i_di0, i_qu0, jj, Pj, mm, m2 < a.rclj2, m2 < a.rc2, A_);
 			}
 		}
 		cnt -= take_n;

@@ -30,7 +30,22 @@ struct MolAcc {
 // All site-site interactions of the molecule pair (i, j): the ten ordered loops of _calculatePairs
 // (VectorizedCellProcessor.cpp:1031-2720) seen from molecule i; m = R_i - R_j (molecule centres), in_lj / in_rc the two
 // molecule-centre cutoff decisions (:1013-1024).
-__device__ __forceinline__ void pair_body(const ForceArgs& a, const V3& Ri, const CompDev& ci, const double4* __restrict__ si,
+// lj = the LJ parameter tables [3][LJ_TAB_STRIDE or S * S]: eps24 | sig2 | shift6, in shared memory when they fit (lj_tables)
+#define LJ_TAB_MAX 64       // S * S entries per table that the shared-memory copy holds (S <= 8 LJ site types; static shared memory is 48 KB)
+struct LJTab { const double *eps24, *sig2, *shift6; };
+// mixtures: every block copies the tables into shared memory once (tab = 3 * LJ_TAB_MAX doubles); larger tables stay in global memory
+__device__ __forceinline__ LJTab lj_tables(const ForceArgs& a, double* tab) {
+	LJTab t; t.eps24 = a.eps24; t.sig2 = a.sig2; t.shift6 = a.shift6;
+	const int n = a.S * a.S;
+	if (n <= LJ_TAB_MAX) {
+		for (int k = threadIdx.x; k < n; k += blockDim.x) { tab[k] = a.eps24[k]; tab[LJ_TAB_MAX + k] = a.sig2[k]; tab[2 * LJ_TAB_MAX + k] = a.shift6[k]; }
+		__syncthreads();
+		t.eps24 = tab; t.sig2 = tab + LJ_TAB_MAX; t.shift6 = tab + 2 * LJ_TAB_MAX;
+	}
+	return t;
+}
+
+__device__ __forceinline__ void pair_body(const ForceArgs& a, const LJTab& lj, const V3& Ri, const CompDev& ci, const double4* __restrict__ si,
                                           const int i_ch0, const int i_di0, const int i_qu0,
                                           const uint32_t j, const double4& Pj, const V3& m, const bool in_lj, const bool in_rc, MolAcc& A_) {
 	V3& F = A_.F; V3& M = A_.M; V3& V = A_.V; double& u6 = A_.u6; double& uX = A_.uX; double& rf = A_.rf;
@@ -48,7 +63,7 @@ __device__ __forceinline__ void pair_body(const ForceArgs& a, const V3& Ri, cons
 					const double4 B = sj[s2];
 					const int k = ida * a.S + (int)__double_as_longlong(B.w);
 					V3 f; double u;
-					pot_lj(v3(A.x - B.x, A.y - B.y, A.z - B.z), a.eps24[k], a.sig2[k], a.shift6[k], f, u);
+					pot_lj(v3(A.x - B.x, A.y - B.y, A.z - B.z), lj.eps24[k], lj.sig2[k], lj.shift6[k], f, u);
 					fa.x += f.x; fa.y += f.y; fa.z += f.z; u6 += u;
 				}
 				F.x += fa.x; F.y += fa.y; F.z += fa.z;

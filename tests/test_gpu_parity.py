@@ -94,6 +94,30 @@ def test_forces_match_reference(name):
     assert scalar_close(virial, w, tol, 1e-3 if name == "vcp_F0" else 1e-300)
 
 
+@pytest.mark.parametrize("name", golden_cases("ex_"))
+def test_list_force_kernels_match_reference_at_t0(name):
+    """The kernels of the device-resident loop - nl_force_kernel (1CLJ) and nl_force_ms_kernel (multi-site), reading the frozen
+    neighbour-list layout - pinned to the REFERENCE's own F, M, Vi, upot, virial at the same bar as the per-step kernels: one
+    ls1g_run step with dt = 0 leaves every molecule where the fixture has it, builds the lists and runs the list force pass."""
+    d = load(name)
+    tol = FORCE_TOL.get(name, 1e-10)
+    with container_of(d) as c:
+        _load_into(c, d, True)
+        c.traverse_cells()
+        rec = c.run(1, 0.0)
+        stats = c.list_stats()
+        out = by_id(c.download(("id", "r", "F", "M", "Vi")))
+    assert stats["rebuilds"] == 1, "the step did not run in the list layout"
+    own = d["f_owned"].astype(bool)
+    order = np.argsort(d["f_id"][own])
+    ref = {k: d["f_" + k][own][order] for k in ("id", "r", "F", "M", "Vi")}
+    assert np.array_equal(out["id"], ref["id"].astype(np.uint64)) and np.array_equal(out["r"], ref["r"])
+    for k in ("F", "M", "Vi"):
+        assert vec_rel_err(out[k], ref[k]) < tol, (k, vec_rel_err(out[k], ref[k]))
+    u, w = d["upot_virial"]
+    assert scalar_close(rec[0, 0], u, tol, 1e-12) and scalar_close(rec[0, 1], w, tol, 1e-300)
+
+
 @pytest.mark.parametrize("name", FORCE_CASES)
 def test_flop_count_matches_reference(name):
     """ls1g_flop_count (the reference's FlopCounter as a device cell processor, adapter/FlopCounter.cpp:196-421) against the
