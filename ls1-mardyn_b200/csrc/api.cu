@@ -106,6 +106,8 @@ static void free_molecules(ls1g_ctx* c) {
 	cudaFree(c->slot_src); cudaFree(c->slot_code); cudaFree(c->slot_key); cudaFree(c->slot_cell);
 	cudaFree(c->stage); c->stage = nullptr; c->stage_bytes = 0;
 	cudaFree(c->halo_src); cudaFree(c->halo_code); cudaFree(c->slot_dst); cudaFree(c->pos_build); cudaFree(c->lists); cudaFree(c->lcount);
+	cudaFree(c->pos_prune); cudaFree(c->lists_in); cudaFree(c->lcount_in);
+	c->pos_prune = nullptr; c->lists_in = nullptr; c->lcount_in = nullptr; c->lists_in_cap = c->lcount_in_cap = 0; c->inner_valid = 0;
 	c->halo_src = nullptr; c->halo_code = nullptr; c->slot_dst = nullptr; c->pos_build = nullptr; c->lists = nullptr; c->lcount = nullptr;
 	c->lists_cap = c->lcount_cap = 0;
 	c->F = c->M = c->Vi = c->F_alt = c->M_alt = nullptr; c->site_cache = nullptr;
@@ -189,7 +191,11 @@ extern "C" int ls1g_create(const ls1g_config* cfg, ls1g_ctx** out) {
 	// profiles/r02c_permute_tradeoff.json)
 	{ const char* lp = getenv("LS1G_LIST_PERMUTE"); c->list_permute = lp ? atoi(lp) : 1; if (c->list_permute < 0 || c->list_permute > 2) c->list_permute = 1; }
 	{ const char* lm = getenv("LS1G_LIST_MULTISITE"); c->list_multisite = lm && atoi(lm) == 0 ? 0 : 1; }
-	{ const char* sk = getenv("LS1G_SKIN"); c->skin = sk ? atof(sk) : 0.12 * c->cfg.cutoff; if (c->skin < 0.) c->skin = 0.; }
+	// skin: LS1G_SKIN, else 0.12 cutoff.  LS1G_SKIN_INNER > 0 (default 0 = off) adds pruned inner lists for single-centre systems
+	// (lists.cuh: nl_prune_kernel); the outer skin then defaults to 0.2 cutoff (ls1g_set_components).  Measured at 10^7 molecules:
+	// no gain - the pruned lists lose the bank-aware order of the build, DESIGN.md section 3
+	{ const char* sk = getenv("LS1G_SKIN"); c->skin_user = sk != nullptr; c->skin = sk ? atof(sk) : 0.12 * c->cfg.cutoff; if (c->skin < 0.) c->skin = 0.; }
+	{ const char* si = getenv("LS1G_SKIN_INNER"); c->skin_in = si ? atof(si) : 0.; if (c->skin_in < 0.) c->skin_in = 0.; }
 	c->rc2 = c->cfg.cutoff * c->cfg.cutoff;
 	c->rclj2 = c->cfg.lj_cutoff * c->cfg.lj_cutoff;
 	// VectorizedCellProcessor.cpp:24
@@ -219,8 +225,8 @@ extern "C" int ls1g_create(const ls1g_config* cfg, ls1g_ctx** out) {
 	CUDA_TRY(cudaMallocHost((void**)&c->h_scalars, 16 * sizeof(double)));
 	CUDA_TRY(cudaMalloc((void**)&c->d_flags, 16 * sizeof(unsigned long long)));
 	CUDA_TRY(cudaMemset(c->d_flags, 0, 16 * sizeof(unsigned long long)));
-	CUDA_TRY(cudaMallocHost((void**)&c->h_flags, 32 * sizeof(unsigned long long)));
-	memset(c->h_flags, 0, 32 * sizeof(unsigned long long));
+	CUDA_TRY(cudaMallocHost((void**)&c->h_flags, 48 * sizeof(unsigned long long)));
+	memset(c->h_flags, 0, 48 * sizeof(unsigned long long));
 	for (int k = 0; k < 16; ++k) CUDA_TRY(cudaEventCreateWithFlags(&c->disp_ev[k], cudaEventDisableTiming));
 	*out = c;
 	return 0;
@@ -327,6 +333,9 @@ extern "C" int ls1g_set_components(ls1g_ctx* c, int nc, const ls1g_component* co
 	c->simple_1clj = (nc == 1 && c0.n_lj == 1 && c0.n_ch == 0 && c0.n_di == 0 && c0.n_qu == 0 && c0.rot_dof == 0 &&
 	                  s0->d[0] == 0. && s0->d[1] == 0. && s0->d[2] == 0.);
 	c->has_rot = !c->simple_1clj;
+	// single-centre systems run on pruned inner lists (lists.cuh: nl_prune_kernel): the outer lists can afford the larger skin
+	if (!c->skin_user) c->skin = (c->simple_1clj && c->skin_in > 0.) ? 0.2 * c->cfg.cutoff : 0.12 * c->cfg.cutoff;
+	if (c->skin_in >= 0.5 * c->skin) c->skin_in = 0.;      // no room between the two radii: inner lists off
 	cudaFree(c->comps); cudaFree(c->sites); cudaFree(c->eps24); cudaFree(c->sig2); cudaFree(c->shift6);
 	CUDA_TRY(cudaMalloc((void**)&c->comps, nc * sizeof(CompDev)));
 	CUDA_TRY(cudaMalloc((void**)&c->sites, std::max<size_t>(1, c->sites_h.size()) * sizeof(SiteDev)));

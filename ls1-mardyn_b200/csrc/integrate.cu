@@ -33,7 +33,8 @@ struct IntArgs {
 	double dt_half;        // post
 	const double* betas;   // device [2] beta_trans, beta_rot; nullptr = no scaling
 	const double4* pos_build;          // neighbour-list mode: positions at the last list build (nullptr = not tracked)
-	unsigned long long* maxdisp;       // max |r - r_build|^2 as double bits (atomicMax)
+	const double4* pos_prune;          // ... at the last prune of the inner lists (nullptr = no inner lists)
+	unsigned long long* maxdisp;       // [0] max |r - r_build|^2, [1] max |r - r_prune|^2 as double bits (atomicMax)
 	double* partials;      // [gridDim.x][4]
 	const unsigned long long* guard; unsigned long long guard_thr;   // skip when *guard > guard_thr (see run_list_steps)
 };
@@ -44,7 +45,7 @@ __global__ void __launch_bounds__(INT_THREADS) integrate_kernel(IntArgs a) {
 	if (a.guard && *a.guard > a.guard_thr) return;
 	size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
 	double acc[4] = {0., 0., 0., 0.};   // summv2, sumIw2, N, rotDOF
-	double disp2 = 0.;
+	double disp2 = 0., disp2i = 0.;
 	bool active = i < a.n && !(a.cell[i] & HALO_FLAG);
 	if (active) {
 		double4 p = a.pos[i];
@@ -88,6 +89,7 @@ __global__ void __launch_bounds__(INT_THREADS) integrate_kernel(IntArgs a) {
 			p.x = r[0]; p.y = r[1]; p.z = r[2];
 			a.pos[i] = p;
 			if (a.pos_build) { const double4 b = a.pos_build[i]; const double ex = p.x - b.x, ey = p.y - b.y, ez = p.z - b.z; disp2 = ex * ex + ey * ey + ez * ez; }
+			if (a.pos_build && a.pos_prune) { const double4 b = a.pos_prune[i]; const double ex = p.x - b.x, ey = p.y - b.y, ez = p.z - b.z; disp2i = ex * ex + ey * ey + ez * ez; }
 			if (ROT) {
 				double w[3];
 				quat_rotateinv(q, L, w);
@@ -117,6 +119,12 @@ __global__ void __launch_bounds__(INT_THREADS) integrate_kernel(IntArgs a) {
 		for (int o = 16; o > 0; o >>= 1) disp2 = fmax(disp2, __shfl_xor_sync(0xffffffffu, disp2, o));
 		const unsigned long long bits = (unsigned long long)__double_as_longlong(disp2);
 		if ((threadIdx.x & 31) == 0 && bits > *(volatile unsigned long long*)a.maxdisp) atomicMax(a.maxdisp, bits);
+		if (a.pos_prune) {
+#pragma unroll
+			for (int o = 16; o > 0; o >>= 1) disp2i = fmax(disp2i, __shfl_xor_sync(0xffffffffu, disp2i, o));
+			const unsigned long long bi = (unsigned long long)__double_as_longlong(disp2i);
+			if ((threadIdx.x & 31) == 0 && bi > *(volatile unsigned long long*)(a.maxdisp + 1)) atomicMax(a.maxdisp + 1, bi);
+		}
 	}
 	if (POST) {
 		block_sum<4>(acc, red);
@@ -200,7 +208,8 @@ static IntArgs make_args(ls1g_ctx* c) {
 	a.F = c->F; a.M = c->M; a.cell = c->cur.cell; a.comps = c->comps;
 	a.dt = 0.; a.dt_half = 0.; a.betas = nullptr; a.partials = c->partials;
 	a.pos_build = c->track_disp ? c->pos_build : nullptr; a.maxdisp = c->d_flags;
-	a.guard = c->guard_on ? c->d_flags + 3 : nullptr; a.guard_thr = (unsigned long long)host_double_bits(c->disp_thr2);
+	a.pos_prune = c->track_disp && c->inner_valid ? c->pos_prune : nullptr;
+	a.guard = nl_guard_ptr(c); a.guard_thr = nl_guard_thr(c);
 	return a;
 }
 

@@ -44,7 +44,10 @@ static NLArgs nl_args(ls1g_ctx* c) {
 	a.rl2f = (float)(rl * rl * (1.0 + 3e-4));
 	a.eps24 = c->eps24_h[0]; a.sig2 = c->sig2_h[0]; a.shift6 = c->shift6_h[0]; a.rclj2 = c->rclj2;
 	a.F = c->F; a.Vi = c->Vi; a.partials = c->partials;
-	a.guard = c->guard_on ? c->d_flags + 3 : nullptr; a.guard_thr = (unsigned long long)host_double_bits(c->disp_thr2);
+	a.guard = nl_guard_ptr(c); a.guard_thr = nl_guard_thr(c);
+	if (c->inner_valid) { a.lists = c->lists_in; a.lcount = c->lcount_in; }      // the force kernels read the pruned lists
+	a.pos_prune = c->inner_valid ? c->pos_prune : nullptr;
+	a.lists_out = nullptr; a.lcount_out = nullptr; a.pos_prune_out = nullptr; a.rin2 = 0.;
 	a.bmap = c->bmap; a.bflag = c->bflag; a.phase = 0;
 	return a;
 }
@@ -71,6 +74,8 @@ static int nl_force_attrs(const ls1g_ctx* c) {
 	static unsigned long long done_mask = 0;       // bit d: attributes set on device d (ordinals < 64)
 	const int d = c->cfg.device;
 	if (d < 64 && (done_mask >> d & 1ull)) return 0;
+	CUDA_TRY(cudaFuncSetAttribute(nl_prune_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, NL_FORCE_SMEM_MAX));
+	CUDA_TRY(cudaFuncSetAttribute(nl_prune_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, NL_FORCE_SMEM_MAX));
 	CUDA_TRY(cudaFuncSetAttribute(nl_build_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, NL_BUILD_SMEM(1, NL_TCAP)));
 	CUDA_TRY(cudaFuncSetAttribute(nl_build_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, NL_BUILD_SMEM(4, NL_TCAP)));
 	CUDA_TRY((cudaFuncSetAttribute(nl_permute_kernel<128, 128>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)NL_PERM_SMEM(128, 128))));
@@ -101,6 +106,9 @@ static void nl_launch(const ls1g_ctx* c, const NLArgs& a, size_t grid) {
 	}
 }
 
+// inner lists: single-centre systems only (the multi-site kernel reads the outer lists), LS1G_SKIN_INNER=0 switches them off
+bool nl_inner_wanted(const ls1g_ctx* c) { return c->simple_1clj && c->skin_in > 0. && c->skin_in < 0.5 * c->skin; }
+
 // buffers of the list loop for nb blocks (grown, never shrunk)
 static int nl_ensure_buffers(ls1g_ctx* c, size_t nb) {
 	const size_t want_l = nb * (size_t)c->list_lcap * nl_bt(c), want_c = nb * nl_bt(c);
@@ -115,6 +123,19 @@ static int nl_ensure_buffers(ls1g_ctx* c, size_t nb) {
 		c->lcount_cap = want_c;
 	}
 	if (!c->pos_build) CUDA_TRY(cudaMalloc((void**)&c->pos_build, c->cap * sizeof(double4)));
+	if (nl_inner_wanted(c)) {      // the pruned copy of the lists (nl_prune_kernel)
+		if (want_l > c->lists_in_cap) {
+			cudaFree(c->lists_in); c->lists_in = nullptr; c->lists_in_cap = 0;
+			CUDA_TRY(cudaMalloc((void**)&c->lists_in, want_l * sizeof(unsigned short)));
+			c->lists_in_cap = want_l;
+		}
+		if (want_c > c->lcount_in_cap) {
+			cudaFree(c->lcount_in); c->lcount_in = nullptr; c->lcount_in_cap = 0;
+			CUDA_TRY(cudaMalloc((void**)&c->lcount_in, want_c * sizeof(uint32_t)));
+			c->lcount_in_cap = want_c;
+		}
+		if (!c->pos_prune) CUDA_TRY(cudaMalloc((void**)&c->pos_prune, c->cap * sizeof(double4)));
+	}
 	if (nb > c->bmap_cap) {
 		cudaFree(c->plans); c->plans = nullptr;
 		CUDA_TRY(cudaMalloc((void**)&c->plans, nb * sizeof(NLPlan)));
@@ -174,8 +195,9 @@ int k_list_build(ls1g_ctx* c) {
 	const size_t nb = nl_blocks(c);
 	if (nl_ensure_buffers(c, nb)) return 1;
 	timer_start(c, LS1G_T_SORT);
-	CUDA_TRY(cudaMemsetAsync(c->d_flags, 0, 3 * sizeof(unsigned long long), c->stream));
-	CUDA_TRY(cudaMemsetAsync(c->d_flags + 5, 0, 2 * sizeof(unsigned long long), c->stream));      // boundary-block count, near-pair flag
+	c->inner_valid = 0;                                                                            // the build replaces the outer lists
+	CUDA_TRY(cudaMemsetAsync(c->d_flags, 0, 3 * sizeof(unsigned long long), c->stream));           // displacement (build, prune), max tile
+	CUDA_TRY(cudaMemsetAsync(c->d_flags + 5, 0, 3 * sizeof(unsigned long long), c->stream));       // boundary-block count, near-pair flag, overflow bits
 	CUDA_TRY(cudaMemcpyAsync(c->pos_build, c->cur.pos, c->n_slots * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));
 	CUDA_TRY(cudaMemcpyAsync(c->alt.pos, c->cur.pos, c->n_slots * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));   // fused steps ping-pong cur.pos / alt.pos
 	NLArgs a = nl_args(c);
@@ -195,9 +217,47 @@ int k_list_build(ls1g_ctx* c) {
 		CUDA_TRY(cudaGetLastError());
 	}
 	CUDA_TRY(cudaMemcpyAsync(c->h_flags, c->d_flags, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+	CUDA_TRY(cudaMemcpyAsync(c->h_flags + 1, c->d_flags + NL_F_OVF, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));   // overflow bits
 	CUDA_TRY(cudaMemcpyAsync(c->h_flags + 3, c->d_flags + 5, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));   // read by the caller after its sync
 	CUDA_TRY(cudaMemcpyAsync(c->h_flags + 4, c->d_flags + 6, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));   // near-pair flag
 	timer_stop(c, LS1G_T_SORT, 2 + (permute ? 1 : 0));
+	return 0;
+}
+
+// outer lists -> inner lists at the current positions (lists.cuh: nl_prune_kernel); from the next force pass on the kernels read the
+// inner lists and are guarded by the displacement since THIS prune.  Halo positions must be current (after the refresh of the step).
+// guarded: a prune the host enqueues ahead of its knowledge (it does nothing when the lists turn out expired, like the step it
+// precedes); unguarded: right after a build, or after the host has seen the inner lists expire.
+int k_list_prune(ls1g_ctx* c, int guarded) {
+	const size_t nb = nl_blocks(c);
+	if (nl_force_attrs(c)) return 1;
+	c->inner_valid = 0;                     // nl_args: read the OUTER lists
+	const int keep_guard = c->guard_on;
+	c->guard_on = guarded;
+	NLArgs a = nl_args(c);
+	c->guard_on = keep_guard;
+	a.tcap = c->list_tcap;
+	a.lists_out = c->lists_in; a.lcount_out = c->lcount_in; a.pos_prune_out = c->pos_prune;
+	const double rin = std::max(c->cfg.lj_cutoff, c->cfg.cutoff) + c->skin_in;
+	a.rin2 = rin * rin;
+	timer_start(c, LS1G_T_SORT);
+	const size_t sm = (size_t)3 * a.tcap * 8;
+	if (nb) {
+		if (c->list_R == 4) nl_prune_kernel<4><<<(unsigned)nb, NLGeom<4>::BT, sm, c->stream>>>(a);
+		else nl_prune_kernel<1><<<(unsigned)nb, NLGeom<1>::BT, sm, c->stream>>>(a);
+	}
+	nl_prune_commit_kernel<<<1, 1, 0, c->stream>>>(c->d_flags, a.guard, a.guard_thr);
+	timer_stop(c, LS1G_T_SORT, 2);
+	CUDA_TRY(cudaGetLastError());
+	c->inner_valid = 1;
+	++c->list_prunes;
+	return 0;
+}
+
+// the guard word of the next step from the displacement flags (after the all-reduce of a multi-rank step)
+int k_list_guard(ls1g_ctx* c) {
+	nl_guard_kernel<<<1, 1, 0, c->stream>>>(c->d_flags, c->disp_thr2, c->thr_in2, c->inner_valid);
+	CUDA_TRY(cudaGetLastError());
 	return 0;
 }
 
@@ -447,7 +507,7 @@ int k_forces_list_ms(ls1g_ctx* c) {
 	NLMArgs m;
 	m.lists = c->lists; m.lcount = c->lcount; m.plans = (const NLPlan*)c->plans; m.lcap4 = c->list_lcap / 4; m.BT = (int)nl_bt(c); m.R = c->list_R;
 	m.n_lanes = lanes;
-	m.guard = c->guard_on ? c->d_flags + 3 : nullptr; m.guard_thr = (unsigned long long)host_double_bits(c->disp_thr2);
+	m.guard = nl_guard_ptr(c); m.guard_thr = nl_guard_thr(c);
 	const CompDev& c0 = c->comps_h[0];
 	const int key = c->n_comp == 1 && c->S_lj <= 4 ? c0.n_lj * 1000 + c0.n_ch * 100 + c0.n_di * 10 + c0.n_qu : -1;
 	if (key >= 0)

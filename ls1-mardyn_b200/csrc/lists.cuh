@@ -42,6 +42,7 @@
 #define NL_LCAP_MAX 1020   // lcount packs quad counts in 16 bits
 #define NL_DUMMY 4         // dummy entries at the start of the tile (keeps real entries 4-aligned)
 #define NL_MAXROWS 16
+#define NL_F_OVF 7         // d_flags word that collects the overflow bits of a build (ls1g_internal.cuh: d_flags)
 #ifndef NL_R4_BT
 #define NL_R4_BT 512       // R = 4: threads per block
 #endif
@@ -80,6 +81,10 @@ struct NLArgs {
 	double* vel;                // [slots][3], updated in place
 	double4* pos_out;           // the OTHER position buffer: new positions of the owned molecules (tiles still read pos)
 	const double4* pos_build;   // positions at the last list build
+	const double4* pos_prune;   // positions at the last prune of the inner lists (nullptr: no inner lists); tracked into flags[1]
+	// nl_prune_kernel: outer lists (lists, lcount) -> inner lists
+	unsigned short* lists_out; uint32_t* lcount_out; double4* pos_prune_out;
+	double rin2;                // (cutoff + inner skin)^2
 	// multi-rank overlap of the halo exchange with the force pass: blocks whose tile touches no halo cell ("inner") need no
 	// received data.  The build kernel classifies every block once per build; the force kernel runs as two launches:
 	// phase 1 = all blocks, boundary blocks return at once; phase 2 = a compact grid over bmap (the boundary blocks).  phase 0 = one launch.
@@ -124,7 +129,7 @@ __device__ __forceinline__ void nl_plan(const NLArgs& a, NLPlan& P, const unsign
 			const int crow = (cz * ny + cy) * nx;
 			const uint32_t rs = a.cell_start[crow + 1], re = a.cell_start[crow + nx - 1];
 			s0 = rs + (uint32_t)bi * NL_BT; s1 = min(s0 + NL_BT, re);
-			if (bi == a.bpr - 1 && s0 + NL_BT < re) atomicOr(a.flags + 1, (unsigned long long)NL_OVF_ROW);
+			if (bi == a.bpr - 1 && s0 + NL_BT < re) atomicOr(a.flags + NL_F_OVF, (unsigned long long)NL_OVF_ROW);
 			if (s0 >= re) s1 = s0;
 		} else {
 			// every thread q sums the whole bundle (4 x 2 loads) so that no barrier separates M from the cut
@@ -143,7 +148,7 @@ __device__ __forceinline__ void nl_plan(const NLArgs& a, NLPlan& P, const unsign
 				s0 = rs + (uint32_t)((unsigned long long)bi * n / nbk);
 				s1 = rs + (uint32_t)((unsigned long long)(bi + 1) * n / nbk);
 			}
-			if (q == 0 && nbk > (uint32_t)a.bpr) atomicOr(a.flags + 1, (unsigned long long)NL_OVF_ROW);
+			if (q == 0 && nbk > (uint32_t)a.bpr) atomicOr(a.flags + NL_F_OVF, (unsigned long long)NL_OVF_ROW);
 		}
 		if (s0 < s1) {
 			xf = (int)((a.cell[s0] & ~HALO_FLAG) % (uint32_t)nx);
@@ -182,7 +187,7 @@ __device__ __forceinline__ void nl_plan(const NLArgs& a, NLPlan& P, const unsign
 		P.o[0] = 0;
 		for (int q = 0; q < R; ++q) P.o[q + 1] = P.o[q] + (int)(P.s1[q] - P.s0[q]);
 		bool lv = live;
-		if (lv && off > a.btcap) { atomicOr(a.flags + 1, (unsigned long long)NL_OVF_TILE); lv = false; }
+		if (lv && off > a.btcap) { atomicOr(a.flags + NL_F_OVF, (unsigned long long)NL_OVF_TILE); lv = false; }
 		P.live = lv ? 1 : 0;
 		// a block is "boundary" when its tile reaches into a halo cell (the positions there arrive with the halo refresh)
 		const int ylo = R == 1 ? gy - 1 : 2 * gy, yhi = R == 1 ? gy + 1 : min(2 * gy + 3, ny - 1);
@@ -382,7 +387,7 @@ __global__ void __launch_bounds__(NLGeom<R>::BT) nl_build_kernel(NLArgs a) {
 	}
 	flush(2);
 	if (active) a.lcount[(size_t)blockIdx.x * BT + tid] = (uint32_t)done4 | ((uint32_t)nA4 << 16);
-	if (ovf && active) atomicOr(a.flags + 1, (unsigned long long)NL_OVF_LIST);
+	if (ovf && active) atomicOr(a.flags + NL_F_OVF, (unsigned long long)NL_OVF_LIST);
 	if (rmin < 1e-8f && active) a.flags[6] = 1ull;
 }
 
@@ -547,6 +552,86 @@ __device__ __forceinline__ double nl_rcp3(double a) {
 	return fma(x, t, x);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// prune: outer lists (radius rc + skin) -> inner lists (radius rc + skin_in), every few steps
+// ---------------------------------------------------------------------------------------------------------------
+// The force pass costs one shared-memory read and ~25 FP64 operations per LISTED partner, inside the cutoff or not; with the skin that
+// makes the lists live 18 steps, 40 % of the listed partners are outside.  So the force kernels read a second, short-lived list: the
+// partners of the outer list that are closer than rc + skin_in NOW.  Exactness: a pair inside rc at a later step t was inside
+// rc + skin_in at the prune as long as no molecule moved more than skin_in / 2 since the prune (tracked against pos_prune into
+// flags[1], the same mechanism as for the build); and it was in the outer list at the prune as long as no molecule had moved more
+// than (skin - skin_in) / 2 since the build - which is why, with inner lists, the OUTER lists count as expired at that displacement
+// already (step.cu: one guard word covers both conditions, so a prune is possible at every step that may run).  Same block decomposition, tile staging and list layout as the force kernel; entries keep their order, batch-A
+// quads stay in front; one lane = one molecule, no interaction between lanes.
+template <int R>
+__global__ void __launch_bounds__(NLGeom<R>::BT, R == 1 ? 6 : 1024 / NLGeom<R>::BT) nl_prune_kernel(NLArgs a) {
+	constexpr int BT = NLGeom<R>::BT;
+	extern __shared__ __align__(16) unsigned char nl_tile[];
+	double* Z = (double*)nl_tile;
+	double2* XY = (double2*)(nl_tile + (size_t)a.tcap * 8);
+	__shared__ NLPlan P;
+	__shared__ __align__(8) uint64_t mbar[2];
+	const int tid = threadIdx.x;
+	const unsigned blk = blockIdx.x;
+	if (a.guard && *a.guard > a.guard_thr) return;      // a prune enqueued ahead of the host's knowledge, lists already expired: like the step it belongs to, it does nothing
+	if (tid == 0) { nl_mbar_init(mbar, BT); nl_mbar_init(mbar + 1, BT); }
+	if (tid < NL_DUMMY) { Z[tid] = 1e150; XY[tid] = make_double2(1e150, 1e150); }
+	if (tid < (int)(sizeof(NLPlan) / 4)) ((uint32_t*)&P)[tid] = ((const uint32_t*)(a.plans + blk))[tid];
+	__syncthreads();
+	int qr; uint32_t i; bool has;
+	nl_my_slot<R>(P, tid, qr, i, has);
+	const bool active = P.live && has;
+	if (!active) a.lcount_out[(size_t)blk * BT + tid] = 0u;
+	if (!P.live) return;
+	nl_stage_tile<R>(a, P, Z, XY, mbar);
+	double4 Pi = make_double4(0., 0., 0., 0.);
+	uint32_t cnt = 0;
+	if (active) { Pi = a.pos[i]; cnt = a.lcount[(size_t)blk * BT + tid]; a.pos_prune_out[i] = Pi; }
+	const uint2* my = (const uint2*)(a.lists + ((size_t)blk * a.lcap4 * BT + tid) * 4);
+	uint2* out = (uint2*)(a.lists_out + ((size_t)blk * a.lcap4 * BT + tid) * 4);
+	const int n4 = (int)(cnt & 0xffffu), nA4 = min((int)(cnt >> 16), n4);
+	const unsigned long long rin2b = (unsigned long long)__double_as_longlong(a.rin2);
+	const char* const Zb = (const char*)Z; const char* const XYb = (const char*)XY;
+	nl_mbar_wait(mbar, 0);
+	nl_mbar_wait(mbar + 1, 0);
+	unsigned long long w64 = 0ull;      // the quad being filled
+	int nw = 0, o4 = 0, oA4 = 0;
+	for (int o = 0; o < n4; ++o) {
+		if (o == nA4) oA4 = o4;          // complete quads so far hold batch-A entries only
+		const uint2 w = my[(size_t)o * BT];
+		const uint32_t ee[4] = {w.x & 0xffffu, w.x >> 16, w.y & 0xffffu, w.y >> 16};
+#pragma unroll
+		for (int u = 0; u < 4; ++u) {
+			const uint32_t e = ee[u];
+			const double zk = *(const double*)(Zb + e);
+			const double2 xyk = *(const double2*)(XYb + (e + e));
+			const double dx = Pi.x - xyk.x, dy = Pi.y - xyk.y, dz = Pi.z - zk;
+			const double r2 = dx * dx + dy * dy + dz * dz;
+			if (e != 0u && (unsigned long long)__double_as_longlong(r2) < rin2b) {
+				w64 |= (unsigned long long)e << (16 * nw);
+				if (++nw == 4) { out[(size_t)o4 * BT] = make_uint2((uint32_t)w64, (uint32_t)(w64 >> 32)); ++o4; w64 = 0ull; nw = 0; }
+			}
+		}
+	}
+	if (n4 <= nA4) oA4 = o4;
+	if (nw) { out[(size_t)o4 * BT] = make_uint2((uint32_t)w64, (uint32_t)(w64 >> 32)); ++o4; }      // missing entries are 0 = the dummy
+	if (active) a.lcount_out[(size_t)blk * BT + tid] = (uint32_t)o4 | ((uint32_t)oA4 << 16);
+}
+
+// after nl_prune_kernel (all its blocks have read the guard): the displacement since the prune starts at zero
+__global__ void nl_prune_commit_kernel(unsigned long long* flags, const unsigned long long* guard, unsigned long long guard_thr) {
+	if (guard && *guard > guard_thr) return;
+	flags[1] = 0ull;
+}
+
+// the guard word of the next step (flags[3]; kernels return at once when it exceeds the bits of 1.0): expired = the outer lists moved
+// beyond thr_o2, or the inner lists (if in use) beyond thr_i2.  Runs after the step's integrator (and the all-reduce of flags[0..1]).
+__global__ void nl_guard_kernel(unsigned long long* flags, double thr_o2, double thr_i2, int inner) {
+	const double dO = __longlong_as_double((long long)flags[0]), dI = __longlong_as_double((long long)flags[1]);
+	const bool expired = dO > thr_o2 || (inner && dI > thr_i2);
+	flags[3] = (unsigned long long)__double_as_longlong(expired ? 2.0 : 0.0);
+}
+
 template <bool COUNT, bool VI, int FUSE, bool ZCHK, int R>
 __global__ void __launch_bounds__(NLGeom<R>::BT, R == 1 ? 6 : 1024 / NLGeom<R>::BT) nl_force_kernel(NLArgs a) {
 	constexpr int BT = NLGeom<R>::BT;
@@ -571,6 +656,7 @@ __global__ void __launch_bounds__(NLGeom<R>::BT, R == 1 ? 6 : 1024 / NLGeom<R>::
 	if (FUSE && has) {      // the epilogue's inputs: bring their lines into L2 now (no registers held)
 		asm volatile("prefetch.global.L2 [%0];" :: "l"(a.vel + 3 * (size_t)i));
 		if (FUSE == 1) asm volatile("prefetch.global.L2 [%0];" :: "l"(a.pos_build + i));
+		if (FUSE == 1 && a.pos_prune) asm volatile("prefetch.global.L2 [%0];" :: "l"(a.pos_prune + i));
 	}
 	const bool active = P.live && has;
 	if (FUSE == 1 && a.guard && *a.guard > a.guard_thr) {      // the host swaps the two position buffers after every fused launch: carry the positions over
@@ -581,7 +667,7 @@ __global__ void __launch_bounds__(NLGeom<R>::BT, R == 1 ? 6 : 1024 / NLGeom<R>::
 	double acc[NV];
 #pragma unroll
 	for (int k = 0; k < NV; ++k) acc[k] = 0.;
-	double disp2 = 0.;
+	double disp2 = 0., disp2i = 0.;
 	if (P.live) {
 		nl_stage_tile<R>(a, P, Z, XY, mbar);
 		double4 Pi = make_double4(0., 0., 0., 0.);
@@ -700,6 +786,11 @@ __global__ void __launch_bounds__(NLGeom<R>::BT, R == 1 ? 6 : 1024 / NLGeom<R>::
 				const double4 bp = a.pos_build[i];
 				const double ex = Pi.x - bp.x, ey = Pi.y - bp.y, ez = Pi.z - bp.z;
 				disp2 = ex * ex + ey * ey + ez * ez;
+				if (a.pos_prune) {
+					const double4 pp = a.pos_prune[i];
+					const double gx = Pi.x - pp.x, gy = Pi.y - pp.y, gz = Pi.z - pp.z;
+					disp2i = gx * gx + gy * gy + gz * gz;
+				}
 			} else {
 				double* Fp = a.F + 3 * (size_t)i;
 				Fp[0] = Fx; Fp[1] = Fy; Fp[2] = Fz;
@@ -713,6 +804,12 @@ __global__ void __launch_bounds__(NLGeom<R>::BT, R == 1 ? 6 : 1024 / NLGeom<R>::
 		for (int o = 16; o > 0; o >>= 1) disp2 = fmax(disp2, __shfl_xor_sync(0xffffffffu, disp2, o));
 		const unsigned long long bits = (unsigned long long)__double_as_longlong(disp2);
 		if ((tid & 31) == 0 && bits > *(volatile unsigned long long*)a.flags) atomicMax(a.flags, bits);
+		if (a.pos_prune) {
+#pragma unroll
+			for (int o = 16; o > 0; o >>= 1) disp2i = fmax(disp2i, __shfl_xor_sync(0xffffffffu, disp2i, o));
+			const unsigned long long bi = (unsigned long long)__double_as_longlong(disp2i);
+			if ((tid & 31) == 0 && bi > *(volatile unsigned long long*)(a.flags + 1)) atomicMax(a.flags + 1, bi);
+		}
 	}
 	block_sum<NV>(acc, red);
 	if (tid == 0) {

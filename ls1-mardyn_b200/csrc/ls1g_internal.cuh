@@ -134,13 +134,27 @@ struct ls1g_ctx {
 	int      list_bpr;                      // blocks per cell row
 	int      build_tcap;                    // 9-row tile capacity of the build kernel, raised once on overflow
 	int      list_lcap;                     // list entries per molecule (multiple of 4), grown on overflow
-	unsigned long long* d_flags;            // [16]: 0 max displacement^2 bits | 1 overflow bits | 2 max tile | 3 snapshot of [0] (kernel guard) |
-	                                        //       5 boundary blocks | 6 near-pair flag of the last build
+	unsigned long long* d_flags;            // [16]: 0 max displacement^2 since the BUILD (bits) | 1 the same since the last PRUNE | 2 max tile |
+	                                        //       3 guard word of the next step: bits of 0.0 = go, 2.0 = lists expired (nl_guard_kernel) |
+	                                        //       5 boundary blocks | 6 near-pair flag of the last build | 7 overflow bits of the last build (NL_F_OVF)
+	// inner lists (lists.cuh: nl_prune_kernel): the outer lists (radius cutoff + skin) are pruned every few steps to cutoff + skin_in;
+	// the force kernels read the pruned copy.  1CLJ only; skin_in = 0 disables them.
+	double   skin_in;                       // inner skin
+	int      skin_user;                     // LS1G_SKIN given: the outer skin is not adapted to the kind of system
+	unsigned short* lists_in; size_t lists_in_cap;
+	uint32_t* lcount_in; size_t lcount_in_cap;
+	double4* pos_prune;                     // [cap] positions at the last prune (displacement criterion of the inner lists)
+	int      inner_valid;                   // the force kernels read lists_in / lcount_in; the guard also covers the displacement since the prune
+	double   thr_in2;                       // (0.4995 skin_in)^2: the inner lists are exact while max |r - r_prune|^2 <= this
+	uint64_t list_prunes;
+	int      inner_life, since_prune;       // steps the inner lists lived when they last expired (0 = unknown); steps since the last prune
+	int      inner_streak;                  // proactive prunes since the last expiry (the expected lifetime is raised again after 16)
 	int      vi_every_step;                 // LS1G_VI_EVERY_STEP=1: per-molecule virial on every list step, not only the last of a run
 	int      guard_on;                      // force / integrate kernels return at once when d_flags[3] > disp_thr2 (lists expired)
 	double   disp_thr2;                     // (0.4995 skin)^2: the lists are exact while max |r - r_build|^2 <= this
 	cudaEvent_t disp_ev[16];                // completion of the per-step copy of d_flags[0] into h_flags[8 + step % 16]
-	unsigned long long* h_flags;            // pinned [32]: 0-2 build flags, 3 boundary blocks, 4 near-pair flag, 8.. ring of displacement flags      // device staging area of the host<->device transfers (transfer.cu)
+	unsigned long long* h_flags;            // pinned [48]: 0, 2 build flags, 1 overflow bits, 3 boundary blocks, 4 near-pair flag, 8..23 ring of the
+	                                        // displacement flags (since the build), 24..39 the same since the last prune      // device staging area of the host<->device transfers (transfer.cu)
 
 	// cells / sort scratch
 	uint32_t *cell_count, *cell_fill, *cell_start;   // [n_cells+1]
@@ -218,6 +232,13 @@ int  comm_exchange_build(const Group& G);      // list mode: migrate leavers, th
 int  comm_refresh(const Group& G);             // list mode: refresh halo positions along the persistent lists (asynchronous)
 enum { COMM_SUM = 0, COMM_MAX = 2 };
 enum { COMM_SCALARS = 0, COMM_FLAGS = 1 };
+// guard of the speculatively enqueued list steps: kernels return at once when *ptr > thr (lists.cuh).  With inner lists the
+// criterion is the displacement since the last prune, else since the build.
+static inline unsigned long long ls1g_double_bits(double x) { unsigned long long b; memcpy(&b, &x, sizeof(b)); return b; }
+static inline const unsigned long long* nl_guard_ptr(const ls1g_ctx* c) { return c->guard_on ? c->d_flags + 3 : nullptr; }
+static inline unsigned long long nl_guard_thr(const ls1g_ctx*) { return ls1g_double_bits(1.0); }      // d_flags[3] holds 0.0 (go) or 2.0 (expired), lists.cuh: nl_guard_kernel
+bool nl_inner_wanted(const ls1g_ctx* c);      // lists.cu
+int  k_list_prune(ls1g_ctx* c, int guarded);   // lists.cu
 // all-reduce of n <= 8 doubles at d_scalars + off (COMM_SCALARS) or d_flags + off (COMM_FLAGS) of every rank, in place, asynchronous
 int  comm_allreduce(const Group& G, int which, int off, int n, int op);
 void comm_destroy(ls1g_ctx* c);

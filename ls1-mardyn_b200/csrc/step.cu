@@ -174,11 +174,14 @@ static int g_post_pre(const Group& G, double dt, int do_post, int do_pre, int th
 #define NL_LCAP_MAX_H 1020        // lists.cuh: NL_LCAP_MAX
 #define NL_AHEAD 8      // steps the host may enqueue beyond the last displacement flag it has read (absorbs ~15 ms of host jitter)
 #define NL_RING 16      // pinned flag copies / events in flight (> NL_AHEAD)
+int k_list_guard(ls1g_ctx* c);      // lists.cu
 static int flag_snapshot(const Group& G, int ring) {
-	if (G.multi() && comm_allreduce(G, COMM_FLAGS, 0, 1, COMM_MAX)) return 1;      // non-negative doubles: bit order == value order
+	// displacement since the build and since the last prune: non-negative doubles, bit order == value order
+	if (G.multi() && comm_allreduce(G, COMM_FLAGS, 0, 2, COMM_MAX)) return 1;
 	FOR_G(G, c) {
-		CUDA_TRY(cudaMemcpyAsync(c->d_flags + 3, c->d_flags, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, c->stream));
+		if (k_list_guard(c)) return 1;       // d_flags[3]: may the next step run?
 		CUDA_TRY(cudaMemcpyAsync(c->h_flags + 8 + ring, c->d_flags, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
+		CUDA_TRY(cudaMemcpyAsync(c->h_flags + 24 + ring, c->d_flags + 1, sizeof(unsigned long long), cudaMemcpyDeviceToHost, c->stream));
 		CUDA_TRY(cudaEventRecord(c->disp_ev[ring], c->stream));
 	}
 	return 0;
@@ -189,8 +192,13 @@ static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, do
 	bool need_build = true;
 	int rc = 0, s = 0;
 	ls1g_ctx* c0 = G.c[0];
+	const bool inner = nl_inner_wanted(c0);       // the force kernels read pruned inner lists (lists.cuh: nl_prune_kernel)
 	for (int r = 0; r < G.n; ++r) {
-		G.c[r]->disp_thr2 = (0.4995 * c0->skin) * (0.4995 * c0->skin);    // lists stay exact while no molecule moved more than skin/2
+		// the lists stay exact while no molecule moved more than skin/2; with inner lists the outer ones must also still be prunable,
+		// i.e. (skin - skin_in)/2, and the inner ones are exact within skin_in/2 of the prune
+		const double so = inner ? c0->skin - c0->skin_in : c0->skin;
+		G.c[r]->disp_thr2 = (0.4995 * so) * (0.4995 * so);
+		G.c[r]->thr_in2 = (0.4995 * c0->skin_in) * (0.4995 * c0->skin_in);
 		G.c[r]->guard_on = 0;
 	}
 	const bool dbg = getenv("LS1G_DEBUG") != nullptr;
@@ -202,19 +210,28 @@ static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, do
 	// several ranks: overlap the halo refresh with the inner blocks of the force pass (LS1G_OVERLAP=0: exchange first, then one launch)
 	const char* oe = getenv("LS1G_OVERLAP");
 	const bool overlap = G.multi() && !(oe && atoi(oe) == 0);
-	auto expired = [&](int ring) { double d2; memcpy(&d2, c0->h_flags + 8 + ring, sizeof(double)); return d2 > c0->disp_thr2; };      // all ranks hold the same value
+	// what the flags of a finished step say about the next one (all ranks hold the same values): 0 = go, 1 = the inner lists expired
+	// (prune again), 2 = the outer lists expired (build).  The same comparisons as nl_guard_kernel, on the same bits.
+	auto expired = [&](int ring) {
+		double dO, dI;
+		memcpy(&dO, c0->h_flags + 8 + ring, sizeof(double)); memcpy(&dI, c0->h_flags + 24 + ring, sizeof(double));
+		if (dO > c0->disp_thr2) return 2;
+		return (c0->inner_valid && dI > c0->thr_in2) ? 1 : 0;
+	};
+	bool need_prune = false;
 	auto fail = [&]() { FOR_G(G, c) { c->track_disp = 0; c->in_list_mode = 0; c->guard_on = 0; nl_set_bin_grid(c, 0); cudaStreamSynchronize(c->stream); cudaStreamSynchronize(c->stream_comm); } return 1; };
 	bool cont = true;
 	for (int r = 0; r < G.n; ++r) cont = cont && G.c[r]->in_list_mode;
 	if (cont) {       // continuing the previous ls1g_run: the pre-kick above was tracked; rebuild only if the lists expired
 		if (flag_snapshot(G, 0)) return fail();
 		FOR_G(G, c) if (sync_check(c, "ls1g_run (displacement)")) return fail();
-		need_build = expired(0);
+		const int st = expired(0);
+		need_build = st == 2; need_prune = st == 1;
 	} else {
 		FOR_G(G, c) if (nl_set_bin_grid(c, 1)) return fail();
 	}
 	for (int r = 0; r < G.n; ++r) G.c[r]->in_list_mode = 1;
-	int rebuilds = 0, repeats = 0, regrow = 0;
+	int rebuilds = 0, repeats = 0, regrow = 0, prunes = 0;
 	double t_build = 0., t_wait = 0., t_enq = 0., t_max_wait = 0., t_max_enq = 0.;     // host wall clock, LS1G_DEBUG only
 	auto now = [&]() { if (!dbg) return 0.; struct timespec ts; clock_gettime(CLOCK_MONOTONIC, &ts); return ts.tv_sec * 1e3 + ts.tv_nsec * 1e-6; };
 	auto rec_copy = [&](ls1g_ctx* c, int step, int off, int n) {
@@ -228,6 +245,7 @@ static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, do
 		if (s < n_steps && s - chk < NL_AHEAD) {
 			const bool built = need_build;
 			bool overlapped = false;
+			const bool prune_now = !need_build && inner && c0->inner_valid && (need_prune || (c0->inner_life > 1 && c0->since_prune >= c0->inner_life - 1));
 			const double t0 = now();
 			if (need_build) {
 				// lifetime of the lists being replaced: steps [0, s) of this call have run with them (plus those of earlier calls)
@@ -286,8 +304,13 @@ static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, do
 				}
 				if (dbg) fprintf(stderr, "ls1g: list build at step %d: max tile %llu, rows per block %d, bpr %d, slots %zu, bin grid %d %d %d\n", s, c0->h_flags[2], c0->list_R, c0->list_bpr, c0->n_slots, c0->bgrid.cpd[0], c0->bgrid.cpd[1], c0->bgrid.cpd[2]);
 				need_build = false; ++rebuilds;
+				if (inner) {       // the first inner lists of these outer lists, at the build positions
+					FOR_G(G, c) { if (!rc) rc = k_list_prune(c, 0); c->since_prune = 0; }
+					FOR_G(G, c) if (!rc) rc = k_list_guard(c);
+					need_prune = false;
+				}
 				t_build += now() - t0;
-			} else if (overlap && fuse_nve && s + 1 < n_steps) {
+			} else if (overlap && fuse_nve && s + 1 < n_steps && !prune_now) {
 				// several ranks, NVE step: the halo positions travel on the communication stream while the inner blocks run
 				overlapped = true;
 				FOR_G(G, c) {
@@ -303,6 +326,20 @@ static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, do
 			} else {
 				if (G.multi()) rc = comm_refresh(G);
 				FOR_G(G, c) if (!rc) rc = k_halo_refresh(c);
+				if (prune_now) {
+					// recovery (the host has seen the inner lists expire: the guard word says "expired", so the prune runs unguarded and
+					// the word is recomputed) or proactive (one step before the inner lists are expected to expire: guarded like the step)
+					const int guarded = need_prune ? 0 : 1;
+					FOR_G(G, c) {
+						c->guard_on = guarded;
+						if (!rc) rc = k_list_prune(c, guarded);
+						c->guard_on = 0;
+						c->since_prune = 0;
+						if (!rc && !guarded) rc = k_list_guard(c);
+						if (guarded && ++c->inner_streak >= 16) { ++c->inner_life; c->inner_streak = 0; }      // no expiry for a while: try longer
+					}
+					need_prune = false; ++prunes;
+				}
 			}
 			const double t1 = now();
 			FOR_G(G, c) {
@@ -329,7 +366,7 @@ static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, do
 				rc = g_post_pre(G, dt, 1, s + 1 < n_steps, thermo, target_T);
 				FOR_G(G, c) if (!rc) rc = rec_copy(c, s, 4, 4);
 			}
-			FOR_G(G, c) c->guard_on = 0;
+			FOR_G(G, c) { c->guard_on = 0; ++c->since_prune; }
 			if (!rc && s + 1 < n_steps) rc = flag_snapshot(G, s % NL_RING);      // decides step s + 1
 			const double t2 = now();
 			t_enq += t2 - t1; if (t2 - t1 > t_max_enq) t_max_enq = t2 - t1;
@@ -341,9 +378,15 @@ static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, do
 			if (rc) break;
 			const double t3 = now();
 			t_wait += t3 - t2; if (t3 - t2 > t_max_wait) t_max_wait = t3 - t2;
-			if (expired(chk % NL_RING)) {      // steps chk + 1 .. s - 1 were skipped on the device: rebuild and enqueue them again
+			const int st = expired(chk % NL_RING);
+			if (st) {      // steps chk + 1 .. s - 1 were skipped on the device: rebuild (or prune again) and enqueue them again
 				repeats += s - (chk + 1);
-				s = chk + 1; need_build = true;
+				FOR_G(G, c) c->since_prune -= s - (chk + 1);
+				if (st == 1) {     // lifetime of the inner lists that just expired: the next ones are replaced one step earlier
+					FOR_G(G, c) { c->inner_life = c->since_prune > 1 ? c->since_prune : 1; c->inner_streak = 0; }
+					need_prune = true;
+				} else need_build = true;
+				s = chk + 1;
 			}
 			++chk;
 		} else break;
@@ -351,6 +394,7 @@ static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, do
 	FOR_G(G, c) c->guard_on = 0;
 	FOR_G(G, c) if (!rc && sync_check(c, "ls1g_run (list steps)")) rc = 1;
 	if (rc) return fail();
+	if (dbg) fprintf(stderr, "ls1g: inner lists %s, %d prunes, expected lifetime %d steps\n", inner ? "on" : "off", prunes, c0->inner_life);
 	if (dbg) fprintf(stderr, "ls1g: %d list steps, %d rebuilds, %d repeated steps; host ms: build %.2f, enqueue %.2f (max %.2f), wait %.2f (max %.2f)\n",
 	                 n_steps, rebuilds, repeats, t_build, t_enq, t_max_enq, t_wait, t_max_wait);
 	FOR_G(G, c) { c->list_rebuilds += (uint64_t)rebuilds; c->list_steps += (uint64_t)n_steps; }
