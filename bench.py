@@ -549,7 +549,7 @@ def main_b200(args):
     # pair-kernel time PER STEP (the overlapped multi-rank step launches the kernel twice: inner blocks, then boundary blocks)
     force_ms = tm["force"]["ms"] / max(args.steps, 1)
     traffic, traffic_src = None, None
-    prof = os.path.join(ROOT, "profiles", "r02b_ncu_nl_force_permuted_10M_summary.csv")
+    prof = os.path.join(ROOT, "profiles", "r02h_ncu_nl_force_10M_summary.csv")
     if os.path.exists(prof) and args.cells == CELLS_PER_GPU:      # dram bytes of ONE launch from the committed ncu --set full capture
         vals = {}
         for ln in open(prof):
@@ -557,7 +557,7 @@ def main_b200(args):
             if len(f) >= 3 and f[0].startswith("dram__bytes_"):
                 vals[f[0]] = float(f[1]) * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}.get(f[2], 1.0)
         if len(vals) == 2:
-            traffic, traffic_src = sum(vals.values()), "profiles/r02b_ncu_nl_force_permuted_10M_summary.csv (ncu --set full, one launch, same workload)"
+            traffic, traffic_src = sum(vals.values()), "profiles/r02h_ncu_nl_force_10M_summary.csv (ncu --set full, one launch, same workload)"
     peak = ls1g.fp64_peak_tflops(local) if rank == 0 else 0.0
     achieved = flops / (force_ms * 1e-3) / 1e12 if force_ms > 0 else 0.0
     launches = sum(sum(t["launches"] for t in w["tm"].values()) for w in windows)      # all timed windows
@@ -653,7 +653,7 @@ def main_b200(args):
                                                      "it visits a pair across the periodic boundary from both images, so its total lies a few % above the Newton-3 count "
                                                      "(every pair once) that flops_per_launch and frac are quoted on"},
                              "model": "FlopCounter: 8*N_dist + 41*N_pairs with per-molecule virial (last step of the run), 8*N_dist + 35*N_pairs without (the other steps; the reference's own count for that case); Newton-3 counts, the owner-computes kernel executes ~2x these",
-                             "note": "bound is the FP64 FMA pipe (SURVEY 8d), not HBM/tensor: ncu sm__pipe_fp64_cycles_active 57 % of this owner-computes kernel (it executes 2x the Newton-3 flops the fraction is quoted on), shared-memory pipe 69 %, DRAM 1.9 TB/s = 29 % of the copy peak (profiles/r02b_ncu_nl_force_permuted_10M_summary.csv)"},
+                             "note": "bound named by SURVEY 8d is the FP64 FMA pipe, not HBM/tensor.  ncu of this owner-computes kernel (it executes 2x the Newton-3 flops the fraction is quoted on): sm__pipe_fp64_cycles_active 55 %, shared-memory wavefronts 79 % of peak (the random 8 + 16 byte tile reads per listed partner, half of them bank-conflict replays), DRAM 3.3 GB per launch = 1.9 TB/s = 29 % of the copy peak (profiles/r02h_ncu_nl_force_10M_summary.csv)"},
                 "timed_windows": {"n": len(windows), "value_is": "median window", "ms": [round(w["ms"], 3) for w in windows],
                                   "list_rebuilds": [int(w["rebuilds"]) for w in windows],
                                   "spread_rel": round((max(w["ms"] for w in windows) - min(w["ms"] for w in windows)) / ms_max, 4),
