@@ -187,7 +187,10 @@ int ls1g_selective_thermostat(ls1g_ctx* ctx, double limit_trans_energy, double t
  * integrate_post, [thermostat] } in the order of Simulation::simulate (Simulation.cpp:979-1177).
  * target_temperature <= 0 : NVE (Domain::thermostatOff); else Domain::calculateGlobalValues betas
  * (Domain.cpp:226-247) are applied each step.  records may be NULL, else [n_steps].
- * Requires forces from a previous ls1g_traverse (as prepare_start does, Simulation.cpp:813-844). */
+ * Requires forces from a previous ls1g_traverse (as prepare_start does, Simulation.cpp:813-844).
+ * NOT reproduced here: the "explosion heuristics" branch of calculateGlobalValues (Domain.cpp:254-311, a beta below MIN_BETA) -
+ * the device thermostat of this loop always applies the raw betas.  The host-driven ls1g_step, which takes the Domain's own
+ * betas, together with ls1g_selective_thermostat reproduces that branch (GpuLinkedCells does; examples/EOX exercises it). */
 int ls1g_run(ls1g_ctx* ctx, int n_steps, double dt, double target_temperature, ls1g_step_record* records);
 
 /* One time step for a HOST-DRIVEN loop (the reference's Simulation::simulate calling the container once per step,

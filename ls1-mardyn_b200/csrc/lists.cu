@@ -18,6 +18,10 @@ static inline unsigned nblk(size_t n, unsigned t) { return (unsigned)((n + t - 1
 // list mode applies to: single-centre LJ and (LS1G_LIST_MULTISITE=0 switches that off) rigid multi-site systems, default kernels, skin > 0, not disabled by an earlier overflow; one rank or several with
 // either transport (NCCL, in-process group)
 int nl_applicable(const ls1g_ctx* c) {
+	// a block shorter than the list radius in some dimension would get ONE bin of less than that radius (grid_init_cut, as
+	// LinkedCells.cpp:56-58 does for its cells): partners two periodic images away would be missed, so such boxes stay on the per-step path
+	const double rl = std::max(c->cfg.cutoff, c->cfg.lj_cutoff) + c->skin;
+	for (int d = 0; d < 3; ++d) if (c->cfg.box_max[d] - c->cfg.box_min[d] < rl) return 0;
 	return (c->simple_1clj || c->list_multisite) && (c->n_ranks == 1 || c->comm_mode == 1 || c->comm_mode == 2) && c->force_variant == 0 && c->skin > 0. && !c->list_disabled;
 }
 
