@@ -443,6 +443,7 @@ void GpuLinkedCells::uploadFromHost() {
 		nt = omp_get_max_threads();
 #endif
 		std::vector<size_t> cursor(static_cast<size_t>(nt) * nb, 0);
+		std::vector<int> cellBlock(static_cast<size_t>(nc), -1);
 		blockStart.assign(static_cast<size_t>(nb) + 1, 0);
 #if defined(_OPENMP)
 #pragma omp parallel num_threads(nt)
@@ -454,9 +455,14 @@ void GpuLinkedCells::uploadFromHost() {
 #endif
 			const long c0 = nc * t / nt, c1 = nc * (t + 1) / nt;
 			size_t* mine = cursor.data() + static_cast<size_t>(t) * nb;
+			// a host cell that lies inside one block (all of them when the block faces fall on cell faces) is counted without
+			// touching its molecules; only a cell cut by a block face is walked molecule by molecule
 			for (long c = c0; c < c1; ++c) {
 				if (first[c + 1] == first[c]) continue;
 				ParticleCell& pc = getCellReference(static_cast<int>(c));
+				const int whole = blockOfCell(pc);
+				cellBlock[c] = whole;
+				if (whole >= 0) { mine[whole] += first[c + 1] - first[c]; continue; }
 				for (auto m = pc.iterator(); m.isValid(); ++m) ++mine[blockOf(m->r_arr().data())];
 			}
 #if defined(_OPENMP)
@@ -478,7 +484,9 @@ void GpuLinkedCells::uploadFromHost() {
 			for (long c = c0; c < c1; ++c) {
 				if (first[c + 1] == first[c]) continue;
 				ParticleCell& pc = getCellReference(static_cast<int>(c));
-				for (auto m = pc.iterator(); m.isValid(); ++m) put(*m, mine[blockOf(m->r_arr().data())]++);
+				const int whole = cellBlock[c];
+				if (whole >= 0) { for (auto m = pc.iterator(); m.isValid(); ++m) put(*m, mine[whole]++); }
+				else { for (auto m = pc.iterator(); m.isValid(); ++m) put(*m, mine[blockOf(m->r_arr().data())]++); }
 			}
 		}
 	}
@@ -503,6 +511,22 @@ int GpuLinkedCells::blockOf(const double* r) const {
 		k = std::max(0, std::min(g - 1, k));
 		while (k > 0 && r[d] < lo[k]) --k;
 		while (k + 1 < g && r[d] >= lo[k + 1]) ++k;
+		co[d] = k;
+	}
+	return (co[0] * _blockGrid[1] + co[1]) * _blockGrid[2] + co[2];
+}
+
+// the block that holds the whole host cell, or -1 when a block face cuts through it (its molecules are then assigned one by one).
+// A molecule exactly on the cell's upper face belongs to the next cell, so [min, max) inside [lo, hi) is the test.
+int GpuLinkedCells::blockOfCell(const ParticleCell& pc) const {
+	int co[3];
+	for (int d = 0; d < 3; ++d) {
+		const std::vector<double>& lo = _blockLo[d];
+		const int g = _blockGrid[d];
+		const double a = pc.getBoxMin(d), b = pc.getBoxMax(d);
+		int k = 0;
+		while (k + 1 < g && a >= lo[k + 1]) ++k;
+		if (k + 1 < g && b > lo[k + 1]) return -1;
 		co[d] = k;
 	}
 	return (co[0] * _blockGrid[1] + co[1]) * _blockGrid[2] + co[2];

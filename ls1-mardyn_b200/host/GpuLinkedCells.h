@@ -79,6 +79,7 @@ private:
 	void uploadComponents();
 	void uploadFromHost();
 	void uploadBlocks(const std::vector<size_t>& start);
+	int blockOfCell(const ParticleCell& pc) const;
 	void downloadMirrorBlocks();
 	int blockOf(const double* r) const;
 	double ensureStaging(size_t molecules);
