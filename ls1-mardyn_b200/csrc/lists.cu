@@ -301,25 +301,31 @@ __global__ void __launch_bounds__(256) fused_finalize_kernel(const double* __res
 
 // One NVE step of the list loop in ONE pass: forces, post(n), pre(n+1) (nl_force_kernel<.., FUSE>).  Reads c->cur.pos, writes
 // the new owned positions to c->alt.pos (free between sorts) and swaps the two pointers.
-// phase: 0 = one launch; 1 = inner blocks only (no finalize, no swap); 2 = boundary blocks, then finalize + swap (see NLArgs::phase)
+// phase: 0 = one launch; 1 = inner blocks only (no finalize, no swap); 2 = boundary blocks, then finalize + swap (see NLArgs::phase);
+//        3 = boundary blocks only (launched on the communication stream, next to the inner blocks); 4 = finalize + swap only
 int k_forces_list_fused(ls1g_ctx* c, double dt, int phase) {
 	const size_t nb = nl_blocks(c);
 	if (ls1g_ensure_partials(c, nb ? nb : 1, 8)) return 1;
 	if (nl_force_attrs(c)) return 1;
-	NLArgs a = nl_args(c);
-	a.tcap = c->list_tcap;
-	a.dt = dt; a.dt_half = 0.5 * dt; a.mass = c->comps_h[0].mass;
-	a.vel = c->cur.vel; a.pos_out = c->alt.pos; a.pos_build = c->pos_build;
-	a.phase = phase;
-	const size_t grid = phase == 2 ? (size_t)c->n_boundary_blocks : nb;
-	timer_start(c, LS1G_T_FORCE);
-	if (grid) {
-		if (c->shift6_h[0] != 0.) nl_launch<true, false, 1>(c, a, grid);
-		else nl_launch<false, false, 1>(c, a, grid);
+	if (phase != 4) {
+		NLArgs a = nl_args(c);
+		a.tcap = c->list_tcap;
+		a.dt = dt; a.dt_half = 0.5 * dt; a.mass = c->comps_h[0].mass;
+		a.vel = c->cur.vel; a.pos_out = c->alt.pos; a.pos_build = c->pos_build;
+		a.phase = phase == 3 ? 2 : phase;
+		const size_t grid = a.phase == 2 ? (size_t)c->n_boundary_blocks : nb;
+		// force_span (phases 1 + 3 run side by side on two streams): ONE timer interval on the main stream, from the start of the
+		// inner blocks to the completion of both kernels (phase 4) - the sum of two overlapping durations would count time twice
+		if (!(c->force_span && phase == 3)) timer_start(c, LS1G_T_FORCE);
+		if (grid) {
+			if (c->shift6_h[0] != 0.) nl_launch<true, false, 1>(c, a, grid);
+			else nl_launch<false, false, 1>(c, a, grid);
+		}
+		if (!c->force_span) timer_stop(c, LS1G_T_FORCE, grid ? 1 : 0);
+		CUDA_TRY(cudaGetLastError());
 	}
-	timer_stop(c, LS1G_T_FORCE, grid ? 1 : 0);
-	CUDA_TRY(cudaGetLastError());
-	if (phase == 1) return 0;
+	if (phase == 1 || phase == 3) return 0;
+	if (phase == 4 && c->force_span) timer_stop(c, LS1G_T_FORCE, 2);
 	std::swap(c->cur.pos, c->alt.pos);
 	timer_start(c, LS1G_T_AUX);
 	size_t nbr = nb; const double* base;

@@ -120,6 +120,7 @@ struct ls1g_ctx {
 	void* plans;                            // [blocks] NLPlan of every block of the last build (lists.cuh), sized with bmap
 	uint32_t* bmap; unsigned char* bflag; size_t bmap_cap;   // boundary blocks of the last build (lists.cuh: NLArgs::bmap)
 	uint32_t n_boundary_blocks;
+	int      force_span;                    // the two launches of an overlapped step run side by side: time them as one interval (lists.cu)
 	cudaStream_t stream_comm;               // high-priority stream of the overlapped halo refresh (multi-rank list steps)
 	cudaEvent_t ev_pos, ev_halo;
 	int      track_disp;                    // integrate kernels track max |r - pos_build|^2 into d_flags[0]

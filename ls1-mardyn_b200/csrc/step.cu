@@ -208,8 +208,11 @@ static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, do
 	const bool fuse_nve = !ms && !thermo && !c0->vi_every_step && !(fe && atoi(fe) == 0);
 	const bool post_fuse = !ms && !thermo && c0->n_ranks == 1 && !(fe && atoi(fe) == 0);      // single rank: the kinetic sums need no all-reduce
 	// several ranks: overlap the halo refresh with the inner blocks of the force pass (LS1G_OVERLAP=0: exchange first, then one launch)
+	// (LS1G_OVERLAP=1: the boundary blocks wait on the main stream; default: they run on the communication stream right behind the
+	// refresh, next to the inner blocks - one kernel tail and one stream hand-over less per step)
 	const char* oe = getenv("LS1G_OVERLAP");
 	const bool overlap = G.multi() && !(oe && atoi(oe) == 0);
+	const bool overlap_concurrent = overlap && !(oe && atoi(oe) == 1);
 	// what the flags of a finished step say about the next one (all ranks hold the same values): 0 = go, 1 = the inner lists expired
 	// (prune again), 2 = the outer lists expired (build).  The same comparisons as nl_guard_kernel, on the same bits.
 	auto expired = [&](int ring) {
@@ -320,6 +323,11 @@ static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, do
 				if (!rc) rc = comm_refresh(G);
 				FOR_G(G, c) {
 					if (!rc) rc = k_halo_refresh(c);
+					if (overlap_concurrent) {      // boundary blocks: same stream, right behind the data they wait for
+						c->guard_on = 1; c->force_span = 1;
+						if (!rc) rc = k_forces_list_fused(c, dt, 3);
+						c->guard_on = 0;
+					}
 					std::swap(c->stream, c->stream_comm);
 					if (!rc && CU(cudaEventRecord(c->ev_halo, c->stream_comm))) rc = 1;
 				}
@@ -347,7 +355,8 @@ static int run_list_steps(const Group& G, int n_steps, double dt, int thermo, do
 				if (overlapped) {
 					if (!rc) rc = k_forces_list_fused(c, dt, 1);
 					if (!rc && CU(cudaStreamWaitEvent(c->stream, c->ev_halo, 0))) rc = 1;
-					if (!rc) rc = k_forces_list_fused(c, dt, 2);
+					if (!rc) rc = k_forces_list_fused(c, dt, overlap_concurrent ? 4 : 2);
+					c->force_span = 0;
 					if (!rc) rc = rec_copy(c, s, 0, 8);
 				} else if (fuse_nve && s + 1 < n_steps) {
 					// NVE step that is not the last of the run: forces + post(s) + pre(s + 1) in one kernel

@@ -686,7 +686,7 @@ def test_group_list_loop_matches_oracle(n_ranks, monkeypatch):
     f0 = _oracle_forces(sysm, g, box, cid, r, q)
     ref = O.run(sysm, g, box, cid, r, v, q, np.zeros((n, 3)), f0["F"], np.zeros((n, 3)), steps, dt)
     out = {}
-    for overlap in ("1", "0"):
+    for overlap in ("2", "1", "0"):      # boundary blocks next to the inner ones (default) / after them on the main stream / no overlap
         monkeypatch.setenv("LS1G_OVERLAP", overlap)
         out[overlap] = _run_group_case(n_ranks, box, rc, ids, r, v, steps, dt)
     rec, st, stats = out["1"]
@@ -699,10 +699,11 @@ def test_group_list_loop_matches_oracle(n_ranks, monkeypatch):
     dr = np.minimum(dr, np.abs(dr - np.asarray(box)))                 # a molecule exactly on the periodic boundary may sit on either side
     assert dr.max() < 1e-9 and np.abs(st["v"] - ref["v"][order]).max() < 1e-8
     assert vec_rel_err(st["F"], ref["F"][order]) < 1e-6                # trajectory divergence over 72 steps, not arithmetic
-    rec0, st0, _ = out["0"]
-    assert np.array_equal(rec, rec0)
-    for k in ("id", "r", "v", "F"):
-        assert np.array_equal(st[k], st0[k]), k
+    for other in ("0", "2"):      # every block owns its outputs and partial sums: the three launch schemes are bitwise equal
+        rec0, st0, _ = out[other]
+        assert np.array_equal(rec, rec0), other
+        for k in ("id", "r", "v", "F"):
+            assert np.array_equal(st[k], st0[k]), (other, k)
 
 
 @pytest.mark.parametrize("skin", ["0.04", "0.11", "0.3+0.05"])
