@@ -35,6 +35,7 @@ int nl_set_bin_grid(ls1g_ctx* c, int list_mode) {
 	return 0;
 }
 
+static size_t nl_blocks(const ls1g_ctx* c);
 static NLArgs nl_args(ls1g_ctx* c) {
 	NLArgs a;
 	a.g = c->bgrid; a.pos = c->cur.pos; a.cell = c->cur.cell; a.cell_start = c->cell_start;
@@ -52,7 +53,7 @@ static NLArgs nl_args(ls1g_ctx* c) {
 	if (c->inner_valid) { a.lists = c->lists_in; a.lcount = c->lcount_in; }      // the force kernels read the pruned lists
 	a.pos_prune = c->inner_valid ? c->pos_prune : nullptr;
 	a.lists_out = nullptr; a.lcount_out = nullptr; a.pos_prune_out = nullptr; a.rin2 = 0.;
-	a.bmap = c->bmap; a.bflag = c->bflag; a.phase = 0;
+	a.bmap = c->bmap; a.bflag = c->bflag; a.phase = 0; a.nb_total = (unsigned)nl_blocks(c);
 	return a;
 }
 
@@ -201,7 +202,7 @@ int k_list_build(ls1g_ctx* c) {
 	timer_start(c, LS1G_T_SORT);
 	c->inner_valid = 0;                                                                            // the build replaces the outer lists
 	CUDA_TRY(cudaMemsetAsync(c->d_flags, 0, 3 * sizeof(unsigned long long), c->stream));           // displacement (build, prune), max tile
-	CUDA_TRY(cudaMemsetAsync(c->d_flags + 5, 0, 3 * sizeof(unsigned long long), c->stream));       // boundary-block count, near-pair flag, overflow bits
+	CUDA_TRY(cudaMemsetAsync(c->d_flags + 4, 0, 4 * sizeof(unsigned long long), c->stream));       // inner- and boundary-block count, near-pair flag, overflow bits
 	CUDA_TRY(cudaMemcpyAsync(c->pos_build, c->cur.pos, c->n_slots * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));
 	CUDA_TRY(cudaMemcpyAsync(c->alt.pos, c->cur.pos, c->n_slots * sizeof(double4), cudaMemcpyDeviceToDevice, c->stream));   // fused steps ping-pong cur.pos / alt.pos
 	NLArgs a = nl_args(c);
@@ -313,7 +314,7 @@ int k_forces_list_fused(ls1g_ctx* c, double dt, int phase) {
 		a.dt = dt; a.dt_half = 0.5 * dt; a.mass = c->comps_h[0].mass;
 		a.vel = c->cur.vel; a.pos_out = c->alt.pos; a.pos_build = c->pos_build;
 		a.phase = phase == 3 ? 2 : phase;
-		const size_t grid = a.phase == 2 ? (size_t)c->n_boundary_blocks : nb;
+		const size_t grid = a.phase == 2 ? (size_t)c->n_boundary_blocks : (a.phase == 1 ? nb - (size_t)c->n_boundary_blocks : nb);
 		// force_span (phases 1 + 3 run side by side on two streams): ONE timer interval on the main stream, from the start of the
 		// inner blocks to the completion of both kernels (phase 4) - the sum of two overlapping durations would count time twice
 		if (!(c->force_span && phase == 3)) timer_start(c, LS1G_T_FORCE);

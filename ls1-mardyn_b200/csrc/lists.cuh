@@ -87,8 +87,10 @@ struct NLArgs {
 	double rin2;                // (cutoff + inner skin)^2
 	// multi-rank overlap of the halo exchange with the force pass: blocks whose tile touches no halo cell ("inner") need no
 	// received data.  The build kernel classifies every block once per build; the force kernel runs as two launches:
-	// phase 1 = all blocks, boundary blocks return at once; phase 2 = a compact grid over bmap (the boundary blocks).  phase 0 = one launch.
-	uint32_t* bmap;             // [n_boundary] block ids of the boundary blocks (order irrelevant: every block owns its outputs)
+	// phase 1 = a compact grid over the inner blocks; phase 2 = a compact grid over the boundary blocks.  phase 0 = one launch over all.
+	uint32_t* bmap;             // [blocks] block ids: the boundary blocks from the front, the inner ones from the back (order irrelevant:
+	                            // every block owns its outputs)
+	unsigned nb_total;          // blocks of the build
 	unsigned char* bflag;       // [blocks] 1 = boundary
 	int phase;
 };
@@ -226,7 +228,9 @@ __global__ void __launch_bounds__(NLGeom<R>::BT) nl_build_kernel(NLArgs a) {
 	nl_plan<R>(a, P, blockIdx.x);
 	if (tid == 0 && a.bflag) {      // inner / boundary classification for the overlapped multi-rank force pass (see NLArgs)
 		a.bflag[blockIdx.x] = P.boundary ? 1 : 0;
+		// boundary blocks fill bmap from the front, the others from the back: two compact grids out of one array
 		if (P.boundary) a.bmap[atomicAdd(a.flags + 5, 1ull)] = blockIdx.x;
+		else a.bmap[gridDim.x - 1 - (unsigned)atomicAdd(a.flags + 4, 1ull)] = blockIdx.x;
 	}
 	// the force kernel loads the plan instead of re-deriving it (three dependent global loads behind three barriers)
 	if (tid < (int)(sizeof(NLPlan) / 4)) ((uint32_t*)(a.plans + blockIdx.x))[tid] = ((const uint32_t*)&P)[tid];
@@ -642,8 +646,8 @@ __global__ void __launch_bounds__(NLGeom<R>::BT, R == 1 ? 6 : 1024 / NLGeom<R>::
 	__shared__ double red[(FUSE ? 8 : 5) * 32];
 	__shared__ __align__(8) uint64_t mbar[2];
 	const int tid = threadIdx.x;
-	const unsigned blk = a.phase == 2 ? a.bmap[blockIdx.x] : blockIdx.x;
-	if (a.phase == 1 && a.bflag[blk]) return;         // boundary block: runs in phase 2, after the halo positions arrived
+	// phase 2: the boundary blocks (they wait for the halo positions); phase 1: all the others; phase 0: every block
+	const unsigned blk = a.phase == 2 ? a.bmap[blockIdx.x] : (a.phase == 1 ? a.bmap[a.nb_total - 1 - blockIdx.x] : blockIdx.x);
 	// speculatively enqueued step whose lists turned out expired: nothing is computed, the host rebuilds and repeats it
 	if (FUSE != 1 && a.guard && *a.guard > a.guard_thr) return;
 	if (tid == 0) { nl_mbar_init(mbar, BT); nl_mbar_init(mbar + 1, BT); }
