@@ -141,6 +141,28 @@ int ls1g_upload(ls1g_ctx* ctx, size_t n, const uint64_t* id, const uint32_t* cid
  * of the molecules of the directly preceding ls1g_upload, same order.  Makes ls1g_run callable without a
  * fresh ls1g_traverse (the first half-kick of Leapfrog::transition1to2 needs F(t), Leapfrog.cpp:48-68). */
 int ls1g_upload_forces(ls1g_ctx* ctx, size_t n, const double* F, const double* M);
+/* --- binary phase-space records ---------------------------------------------
+ * The PACKED records of the reference's binary checkpoint, taken and produced by the device as they stand in the file: the
+ * host copies bytes and never looks inside a record (no per-molecule host loop, no host Molecule objects).
+ *   LS1G_REC_ICRVQD  id u64 | component id u32, 1-based | r[3] v[3] q[4] = (w x y z) D[3]   = 116 bytes
+ *   LS1G_REC_ICRV    id u64 | component id u32, 1-based | r[3] v[3]                         =  60 bytes  (q = 1 0 0 0, D = 0)
+ *   LS1G_REC_IRV     id u64 | r[3] v[3]                                                      =  56 bytes  (component 1)
+ * replaces: <format type="ICRVQD|ICRV|IRV"/> of BinaryReader::readPhaseSpaceHeader (io/BinaryReader.cpp:102-112) */
+enum { LS1G_REC_ICRVQD = 0, LS1G_REC_ICRV = 1, LS1G_REC_IRV = 2 };
+int ls1g_record_size(int format, size_t* bytes);
+/* replaces: the record loop of BinaryReader::readPhaseSpace (io/BinaryReader.cpp:171-287).  Replaces the content of the context by
+ * the records that lie inside its bounding box (ParticleContainer::isInBoundingBox, ParticleContainer.cpp:37-44: min <= r < max, as
+ * the reader's "if (isInBoundingBox) addParticle" :271-273 - every rank of a decomposed run is handed the whole file and keeps its
+ * own part), in file order.  *n_kept = their number, *max_id = the highest id of ALL n records (the reader's return value, :281-282);
+ * both may be NULL.  A component id of 0 or above the component count is an error (:222-228) and leaves the context empty.
+ * With every record inside the box the state equals that after ls1g_upload of the same molecules (ls1g_upload_forces may follow).
+ * `records` may be any host memory; from ls1g_host_alloc memory the copy runs at the full PCIe rate. */
+int ls1g_upload_records(ls1g_ctx* ctx, size_t n, const void* records, int format, uint64_t* n_kept, uint64_t* max_id);
+/* replaces: DomainDecompBase::writeMoleculesToFile -> FullMolecule::writeBinary over the owned molecules
+ * (parallel/DomainDecompBase.cpp:505-540, molecules/FullMolecule.cpp:451-474): ICRVQD records of the owned molecules in the order
+ * ls1g_download returns them (cell by cell), *n_out = their number; records == NULL only reports the number.  A context that keeps
+ * no orientations (exactly one component with one LJ centre at the origin) writes q = (1 0 0 0), D = 0. */
+int ls1g_download_records(ls1g_ctx* ctx, size_t capacity, void* records, size_t* n_out);
 /* number of molecules held: owned (non-halo cells) and halo copies */
 int ls1g_count(ls1g_ctx* ctx, uint64_t* n_owned, uint64_t* n_halo);
 /* replaces: ParticleIterator over ALL_CELLS / ONLY_INNER_AND_BOUNDARY + Molecule getters.

@@ -21,6 +21,7 @@ EXPORTS = [
     "ls1g_comm_unique_id", "ls1g_comm_init", "ls1g_allreduce_sum", "ls1g_comm_init_local", "ls1g_exchange_group",
     "ls1g_timers", "ls1g_measure_fp64_peak", "ls1g_last_pair_count", "ls1g_flop_count", "ls1g_rdf", "ls1g_reserve", "ls1g_download_range", "ls1g_slot_count",
     "ls1g_run_group", "ls1g_step_group", "ls1g_list_stats", "ls1g_cell_index_of_points_noalloc", "ls1g_device_count",
+    "ls1g_record_size", "ls1g_upload_records", "ls1g_download_records",
 ]
 
 FIELDS = dict(id=1, cid=2, r=4, v=8, q=16, L=32, F=64, M=128, Vi=256, cell=512)
@@ -285,6 +286,41 @@ class Container:
         q = None if q is None else np.ascontiguousarray(q, dtype=np.float64).reshape(n, 4)
         L = None if L is None else np.ascontiguousarray(L, dtype=np.float64).reshape(n, 3)
         _chk(lib().ls1g_upload(self._ctx, C.c_size_t(n), _p(id), _p(cid), _p(r), _p(v), _p(q), _p(L)))
+
+    RECORD_FORMATS = dict(ICRVQD=0, ICRV=1, IRV=2)      # LS1G_REC_*
+
+    @staticmethod
+    def record_size(fmt="ICRVQD"):
+        n = C.c_size_t()
+        _chk(lib().ls1g_record_size(Container.RECORD_FORMATS[fmt] if isinstance(fmt, str) else int(fmt), C.byref(n)))
+        return n.value
+
+    def add_records(self, records, fmt="ICRVQD"):
+        """ls1g_upload_records: the packed records of a binary checkpoint (bytes / uint8 array / structured array, as they stand in the
+        .dat file) replace the content; the device unpacks them and keeps those inside this context's bounding box
+        (BinaryReader::readPhaseSpace).  Returns (molecules kept, highest id of all records)."""
+        buf = np.frombuffer(records, dtype=np.uint8) if isinstance(records, (bytes, bytearray, memoryview)) else np.ascontiguousarray(records).view(np.uint8).reshape(-1)
+        size = self.record_size(fmt)
+        if buf.size % size:
+            raise Ls1gError("add_records: %d bytes are not a whole number of %d-byte records" % (buf.size, size))
+        kept, mx = C.c_uint64(), C.c_uint64()
+        _chk(lib().ls1g_upload_records(self._ctx, C.c_size_t(buf.size // size), _p(buf) if buf.size else None, self.RECORD_FORMATS[fmt], C.byref(kept), C.byref(mx)))
+        return kept.value, mx.value
+
+    def download_records(self, out=None):
+        """ls1g_download_records: the owned molecules as ICRVQD records (uint8 array [n][116]), cell by cell - the bytes
+        DomainDecompBase::writeMoleculesToFile(binary) appends to the .dat file.  out: optional preallocated (e.g. pinned) uint8 buffer"""
+        n = C.c_size_t()
+        _chk(lib().ls1g_download_records(self._ctx, C.c_size_t(0), None, C.byref(n)))
+        if out is not None:
+            if out.dtype != np.uint8 or out.size < n.value * 116 or not out.flags.c_contiguous:
+                raise Ls1gError("download_records: out must be a contiguous uint8 buffer of at least %d bytes" % (n.value * 116))
+            out = out.reshape(-1)[:n.value * 116].reshape(n.value, 116)
+        else:
+            out = np.empty((n.value, 116), dtype=np.uint8)
+        if n.value:
+            _chk(lib().ls1g_download_records(self._ctx, C.c_size_t(n.value), _p(out), C.byref(n)))
+        return out
 
     def set_forces(self, F, M=None):
         """Molecule::setF/setM for the molecules of the directly preceding add_particles (same order)"""

@@ -442,6 +442,53 @@ extern "C" int ls1g_upload(ls1g_ctx* c, size_t n, const uint64_t* id, const uint
 	return 0;
 }
 
+// --- binary phase-space records (records.cu) ---------------------------------------------------------
+int k_upload_records(ls1g_ctx* c, size_t n, const void* records, int format, uint64_t* n_kept, uint64_t* max_id);
+int k_download_records(ls1g_ctx* c, size_t n_ret, void* records);
+
+extern "C" int ls1g_record_size(int format, size_t* bytes) {
+	if (!bytes) LS1G_FAIL("null argument");
+	if (format < LS1G_REC_ICRVQD || format > LS1G_REC_IRV) LS1G_FAIL("Not a valid molecule format");      // BinaryReader.cpp:109-112
+	*bytes = format == LS1G_REC_ICRVQD ? 116 : format == LS1G_REC_ICRV ? 60 : 56;
+	return 0;
+}
+
+extern "C" int ls1g_upload_records(ls1g_ctx* c, size_t n, const void* records, int format, uint64_t* n_kept, uint64_t* max_id) {
+	if (!c) LS1G_FAIL("null context");
+	if (c->n_comp == 0) LS1G_FAIL("ls1g_upload_records: call ls1g_set_components first");
+	if (format < LS1G_REC_ICRVQD || format > LS1G_REC_IRV) LS1G_FAIL("Not a valid molecule format");
+	if (n && !records) LS1G_FAIL("ls1g_upload_records: records is required");
+	CUDA_TRY(cudaSetDevice(c->cfg.device));
+	// room: the configured capacity; else, on a rank that owns the whole box, the estimate for all n records as in ls1g_upload; on one
+	// rank of several (most records fall outside its box) what an earlier ls1g_reserve left, and the estimate for n only without one
+	const bool whole_box = c->cfg.rank_grid[0] * c->cfg.rank_grid[1] * c->cfg.rank_grid[2] <= 1;
+	if (c->cap == 0 || (!c->cfg.capacity && whole_box && c->cap < default_capacity(c, n))) {
+		const size_t want = c->cfg.capacity ? (size_t)c->cfg.capacity : default_capacity(c, n);
+		if (alloc_molecules(c, std::max<size_t>(want, 1))) return 1;
+	}
+	if (c->in_list_mode) { c->in_list_mode = 0; c->track_disp = 0; c->bgrid = c->grid; }     // the content is replaced
+	c->n_uploaded = 0; c->n_slots = c->n_owned = 0; c->n_halo = 0; c->sorted = 0; c->forces_valid = 0;
+	uint64_t kept = 0, mx = 0;
+	if (k_upload_records(c, n, records, format, &kept, &mx)) return 1;
+	c->n_uploaded = (size_t)kept;
+	c->n_slots = c->n_owned = (size_t)kept;
+	if (n_kept) *n_kept = kept;
+	if (max_id) *max_id = mx;
+	return 0;
+}
+
+extern "C" int ls1g_download_records(ls1g_ctx* c, size_t capacity, void* records, size_t* n_out) {
+	if (!c || !n_out) LS1G_FAIL("null argument");
+	CUDA_TRY(cudaSetDevice(c->cfg.device));
+	if (c->in_list_mode && ls1g_nl_leave(c)) return 1;
+	const size_t n_ret = c->n_owned;
+	*n_out = n_ret;
+	if (!records) return 0;       // count query
+	if (capacity < n_ret) LS1G_FAIL("ls1g_download_records: capacity too small");
+	CUDA_TRY(cudaStreamSynchronize(c->stream));
+	return k_download_records(c, n_ret, records);
+}
+
 extern "C" int ls1g_count(ls1g_ctx* c, uint64_t* n_owned, uint64_t* n_halo) {
 	if (!c) LS1G_FAIL("null context");
 	if (n_owned) *n_owned = c->n_owned;

@@ -194,11 +194,13 @@ def read_binary(header_path, data_path, n_components=None):
 
 
 def write_binary(header_path, data_path, ps):
-    """Domain::writeCheckpointHeaderXML (Domain.cpp:575-595) + FullMolecule::writeBinary per molecule."""
+    """Domain::writeCheckpointHeaderXML (Domain.cpp:572-595; FORMAT_SCI_MAX_DIGITS_WIDTH_21 = %21.15e, utils/FileUtils.h:17, so the box
+    lengths keep 15 digits as in the reference) + FullMolecule::writeBinary per molecule.  Byte-identical to the reference's files
+    (tests/golden/cp_binary_MultiComponent.*)."""
     n = len(ps["id"])
     with open(header_path, "w") as f:
         f.write("<?xml version='1.0' encoding='UTF-8'?>\n<mardyn version=\"20100525\" >\n\t<headerinfo>\n")
-        f.write("\t\t<time>%21.14e</time>\n\t\t<length>\n\t\t\t<x>%.17e</x> <y>%.17e</y> <z>%.17e</z>\n\t\t</length>\n"
+        f.write("\t\t<time>%21.15e</time>\n\t\t<length>\n\t\t\t<x>%21.15e</x> <y>%21.15e</y> <z>%21.15e</z>\n\t\t</length>\n"
                 % ((ps.get("time", 0.0),) + tuple(ps["box"])))
         f.write("\t\t<number>%d</number>\n\t\t<format type=\"ICRVQD\"/>\n\t</headerinfo>\n</mardyn>\n" % n)
     rec = np.empty(n, dtype=BINARY_RECORD)
