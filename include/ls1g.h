@@ -161,8 +161,12 @@ int ls1g_upload_records(ls1g_ctx* ctx, size_t n, const void* records, int format
 /* replaces: DomainDecompBase::writeMoleculesToFile -> FullMolecule::writeBinary over the owned molecules
  * (parallel/DomainDecompBase.cpp:505-540, molecules/FullMolecule.cpp:451-474): ICRVQD records of the owned molecules in the order
  * ls1g_download returns them (cell by cell), *n_out = their number; records == NULL only reports the number.  A context that keeps
- * no orientations (exactly one component with one LJ centre at the origin) writes q = (1 0 0 0), D = 0. */
-int ls1g_download_records(ls1g_ctx* ctx, size_t capacity, void* records, size_t* n_out);
+ * no orientations (exactly one component with one LJ centre at the origin) writes q = (1 0 0 0), D = 0.
+ * scale_v, scale_D: the records carry v * scale_v and D * scale_D (scale_v / scale_D, molecules/MoleculeInterface.h:195-213: one multiplication per component;
+ * 1.0 leaves the bits as stored).  For a host loop that applies the velocity scaling of a step inside the NEXT step (ls1g_step's
+ * beta_trans / beta_rot) and writes a checkpoint in between: VelocityScalingThermostat::apply (VelocityScalingThermostat.cpp:45-80)
+ * has already run in the reference when its writer reads the molecules.  The device state is not changed. */
+int ls1g_download_records(ls1g_ctx* ctx, double scale_v, double scale_D, size_t capacity, void* records, size_t* n_out);
 /* number of molecules held: owned (non-halo cells) and halo copies */
 int ls1g_count(ls1g_ctx* ctx, uint64_t* n_owned, uint64_t* n_halo);
 /* replaces: ParticleIterator over ALL_CELLS / ONLY_INNER_AND_BOUNDARY + Molecule getters.

@@ -307,11 +307,12 @@ class Container:
         _chk(lib().ls1g_upload_records(self._ctx, C.c_size_t(buf.size // size), _p(buf) if buf.size else None, self.RECORD_FORMATS[fmt], C.byref(kept), C.byref(mx)))
         return kept.value, mx.value
 
-    def download_records(self, out=None):
+    def download_records(self, out=None, scale_v=1.0, scale_D=1.0):
         """ls1g_download_records: the owned molecules as ICRVQD records (uint8 array [n][116]), cell by cell - the bytes
-        DomainDecompBase::writeMoleculesToFile(binary) appends to the .dat file.  out: optional preallocated (e.g. pinned) uint8 buffer"""
+        DomainDecompBase::writeMoleculesToFile(binary) appends to the .dat file.  out: optional preallocated (e.g. pinned) uint8 buffer;
+        scale_v, scale_D: factors applied to v and D on the way out (a thermostat scaling the device has not applied yet)"""
         n = C.c_size_t()
-        _chk(lib().ls1g_download_records(self._ctx, C.c_size_t(0), None, C.byref(n)))
+        _chk(lib().ls1g_download_records(self._ctx, C.c_double(1.0), C.c_double(1.0), C.c_size_t(0), None, C.byref(n)))
         if out is not None:
             if out.dtype != np.uint8 or out.size < n.value * 116 or not out.flags.c_contiguous:
                 raise Ls1gError("download_records: out must be a contiguous uint8 buffer of at least %d bytes" % (n.value * 116))
@@ -319,7 +320,7 @@ class Container:
         else:
             out = np.empty((n.value, 116), dtype=np.uint8)
         if n.value:
-            _chk(lib().ls1g_download_records(self._ctx, C.c_size_t(n.value), _p(out), C.byref(n)))
+            _chk(lib().ls1g_download_records(self._ctx, C.c_double(scale_v), C.c_double(scale_D), C.c_size_t(n.value), _p(out), C.byref(n)))
         return out
 
     def set_forces(self, F, M=None):

@@ -444,7 +444,7 @@ extern "C" int ls1g_upload(ls1g_ctx* c, size_t n, const uint64_t* id, const uint
 
 // --- binary phase-space records (records.cu) ---------------------------------------------------------
 int k_upload_records(ls1g_ctx* c, size_t n, const void* records, int format, uint64_t* n_kept, uint64_t* max_id);
-int k_download_records(ls1g_ctx* c, size_t n_ret, void* records);
+int k_download_records(ls1g_ctx* c, double scale_v, double scale_D, size_t n_ret, void* records);
 
 extern "C" int ls1g_record_size(int format, size_t* bytes) {
 	if (!bytes) LS1G_FAIL("null argument");
@@ -477,7 +477,7 @@ extern "C" int ls1g_upload_records(ls1g_ctx* c, size_t n, const void* records, i
 	return 0;
 }
 
-extern "C" int ls1g_download_records(ls1g_ctx* c, size_t capacity, void* records, size_t* n_out) {
+extern "C" int ls1g_download_records(ls1g_ctx* c, double scale_v, double scale_D, size_t capacity, void* records, size_t* n_out) {
 	if (!c || !n_out) LS1G_FAIL("null argument");
 	CUDA_TRY(cudaSetDevice(c->cfg.device));
 	if (c->in_list_mode && ls1g_nl_leave(c)) return 1;
@@ -486,7 +486,7 @@ extern "C" int ls1g_download_records(ls1g_ctx* c, size_t capacity, void* records
 	if (!records) return 0;       // count query
 	if (capacity < n_ret) LS1G_FAIL("ls1g_download_records: capacity too small");
 	CUDA_TRY(cudaStreamSynchronize(c->stream));
-	return k_download_records(c, n_ret, records);
+	return k_download_records(c, scale_v, scale_D, n_ret, records);
 }
 
 extern "C" int ls1g_count(ls1g_ctx* c, uint64_t* n_owned, uint64_t* n_halo) {

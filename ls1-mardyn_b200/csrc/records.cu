@@ -212,7 +212,7 @@ __global__ void __launch_bounds__(256) rec_kept_kernel(Grid g, const uint32_t* _
 }
 
 // rows [row0, row0 + n) of the owned molecules in cell order -> ICRVQD records.  kept_before == nullptr: row == slot.
-__global__ void __launch_bounds__(REC_BLOCK) rec_pack_kernel(size_t row0, int n, MolBuf mol, int has_rot, const uint32_t* __restrict__ cell_start,
+__global__ void __launch_bounds__(REC_BLOCK) rec_pack_kernel(size_t row0, int n, MolBuf mol, int has_rot, double sv, double sd, const uint32_t* __restrict__ cell_start,
                                                              const uint32_t* __restrict__ kept_before, int n_cells, uint32_t* __restrict__ rec) {
 	__shared__ __align__(16) uint32_t sh[REC_BLOCK * 29];
 	const int first = blockIdx.x * REC_BLOCK;
@@ -234,11 +234,11 @@ __global__ void __launch_bounds__(REC_BLOCK) rec_pack_kernel(size_t row0, int n,
 		w[0] = (uint32_t)id; w[1] = (uint32_t)(id >> 32);
 		w[2] = pos_cid(p) + 1u;                       // FullMolecule::writeBinary: _component->ID() + 1
 		put(3, p.x); put(5, p.y); put(7, p.z);
-		put(9, mol.vel[3 * s]); put(11, mol.vel[3 * s + 1]); put(13, mol.vel[3 * s + 2]);
+		put(9, mol.vel[3 * s] * sv); put(11, mol.vel[3 * s + 1] * sv); put(13, mol.vel[3 * s + 2] * sv);      // Molecule::scale_v: v[d] *= s (1.0 is exact)
 		if (has_rot) {
 			const double4 q = mol.q[s];
 			put(15, q.x); put(17, q.y); put(19, q.z); put(21, q.w);
-			put(23, mol.L[3 * s]); put(25, mol.L[3 * s + 1]); put(27, mol.L[3 * s + 2]);
+			put(23, mol.L[3 * s] * sd); put(25, mol.L[3 * s + 1] * sd); put(27, mol.L[3 * s + 2] * sd);           // Molecule::scale_D
 		} else {
 			put(15, 1.); put(17, 0.); put(19, 0.); put(21, 0.); put(23, 0.); put(25, 0.); put(27, 0.);
 		}
@@ -252,7 +252,7 @@ __global__ void __launch_bounds__(REC_BLOCK) rec_pack_kernel(size_t row0, int n,
 	for (int i = (nq << 2) + t; i < n_words; i += REC_BLOCK) dst[i] = sh[i];
 }
 
-int k_download_records(ls1g_ctx* c, size_t n_ret, void* records) {
+int k_download_records(ls1g_ctx* c, double scale_v, double scale_D, size_t n_ret, void* records) {
 	if (n_ret == 0) return 0;
 	size_t chunk; RecCtl* ctl;
 	if (rec_stage(c, n_ret, 29, &chunk, &ctl)) return 1;
@@ -265,7 +265,7 @@ int k_download_records(ls1g_ctx* c, size_t n_ret, void* records) {
 	}
 	for (size_t k0 = 0; k0 < n_ret; k0 += chunk) {
 		const int m = (int)std::min(chunk, n_ret - k0);
-		rec_pack_kernel<<<nblk(m, REC_BLOCK), REC_BLOCK, 0, st>>>(k0, m, c->cur, c->has_rot, c->cell_start, kept, c->bgrid.n_cells, (uint32_t*)c->stage);
+		rec_pack_kernel<<<nblk(m, REC_BLOCK), REC_BLOCK, 0, st>>>(k0, m, c->cur, c->has_rot, scale_v, scale_D, c->cell_start, kept, c->bgrid.n_cells, (uint32_t*)c->stage);
 		CUDA_TRY(cudaMemcpyAsync((char*)records + k0 * 116, c->stage, (size_t)m * 116, cudaMemcpyDeviceToHost, st));
 	}
 	CUDA_TRY(cudaStreamSynchronize(st));

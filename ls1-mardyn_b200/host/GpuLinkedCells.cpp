@@ -26,6 +26,7 @@ extern "C" {
 #include <atomic>
 #include <chrono>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
 #include <memory>
 #include <numeric>
@@ -72,7 +73,8 @@ void GpuLinkedCells::printSummary() const {
 	                   << _tMirror << " s (" << _bytesDown << " B); context creation " << _tContext << " s; selective thermostat applied "
 	                   << _selective << " time(s); " << _rdfSamples << " RDF and " << _flopSamples << " FLOP sample(s) on the device; first steps [s] " << _tFirstSteps[0] << " " << _tFirstSteps[1] << " "
 	                   << _tFirstSteps[2] << " " << _tFirstSteps[3] << ", slowest step " << _tMaxStep
-	                   << "; upload = gather " << _tGather << " + copy " << _tH2D << ", mirror = copy " << _tD2H << " + fill " << _tFill << std::endl;
+	                   << "; upload = gather " << _tGather << " + copy " << _tH2D << ", mirror = copy " << _tD2H << " + fill " << _tFill
+	                   << "; " << _recordWrites << " record checkpoint(s) from the device took " << _tRecords << " s (" << _bytesRecords << " B)" << std::endl;
 }
 
 void GpuLinkedCells::fail(const char* what) const {
@@ -145,7 +147,8 @@ void GpuLinkedCells::readXML(XMLfileUnits& xmlconfig) {
 unsigned long GpuLinkedCells::mirrorFrequencyFromPlugins(XMLfileUnits& xmlconfig) const {
 	static const std::set<std::string> noMolecules = {"ResultWriter", "SysMonOutput", "TimerWriter", "LoadbalanceWriter",
 	                                                  "DecompWriter", "CommunicationPartnerWriter", "KDTreePrinter",
-	                                                  "RDF", "FlopRateWriter"};      // their traversals are counted on the device (sampleRDF, sampleFlops)
+	                                                  "RDF", "FlopRateWriter",       // their traversals are counted on the device (sampleRDF, sampleFlops)
+	                                                  "GpuCheckpointWriter"};        // takes the packed records from the device (writeBinaryRecords)
 	static const std::set<std::string> readers = {"CheckpointWriter", "MPICheckpointWriter", "XyzWriter", "MmpldWriter",
 	                                              "MmspdWriter", "MmspdBinWriter", "PovWriter", "VISWriter", "MaxWriter",
 	                                              "EnergyLogWriter"};
@@ -844,18 +847,7 @@ void GpuLinkedCells::integratePre(double dt, Domain* domain) {
 		// computed (Domain.cpp:226-247); nothing reads v in between
 		const double bt = domain->getGlobalBetaTrans();
 		const double br = domain->getGlobalBetaRot();
-		// "Explosion heuristics" (Domain.cpp:254-311): when a raw beta is below MIN_BETA, calculateGlobalValues caps the kinetic
-		// energy per molecule and replaces the betas by (1, beta_rot^0.0091).  Its molecule loop ran over the (empty) host
-		// cells; the same capping is done here on the device.  The raw betas are recomputed from the very sums handed to Domain.
-		const double Ti = _lastTfactor * domain->getTargetTemperature(0);
-		if (Ti > 0.0 && _n > 0) {
-			const double rawBt = std::pow(3.0 * _n * Ti / _summv2, 0.4);
-			const double rawBr = (_sumIw2 == 0.0 || _rotDOF == 0) ? 1.0 : std::pow(_rotDOF * Ti / _sumIw2, 0.4);
-			if ((rawBt < MIN_BETA || rawBr < MIN_BETA) && bt == 1.0 && std::fabs(br - std::pow(rawBr, 0.0091)) <= 1e-14) {
-				for (ls1g_ctx* cx : _ctxs) chk(ls1g_selective_thermostat(cx, KINLIMIT_PER_T * Ti, Ti), "ls1g_selective_thermostat");
-				++_selective;
-			}
-		}
+		applySelectiveThermostat(domain);
 		if (_mode == FUSED) {          // applied inside ls1g_step, fused into the pre-kick
 			_pendingBt = bt;
 			_pendingBr = br;
@@ -867,6 +859,66 @@ void GpuLinkedCells::integratePre(double dt, Domain* domain) {
 	_tDevice += wall() - t0;
 	_inStep = true;
 	_ranThisStep = false;
+}
+
+// "Explosion heuristics" (Domain.cpp:254-311): when a raw beta is below MIN_BETA, calculateGlobalValues caps the kinetic energy per
+// molecule and replaces the betas by (1, beta_rot^0.0091).  Its molecule loop ran over the (empty) host cells; the same capping is
+// done here on the device.  The raw betas are recomputed from the very sums handed to Domain.  Runs once per time step: either when a
+// checkpoint is taken from the device at the end of the step (writeBinaryRecords) or at the start of the next step (integratePre) -
+// nothing touches v, D in between.
+void GpuLinkedCells::applySelectiveThermostat(Domain* domain) {
+	if (_selectiveStep == _steps) return;
+	_selectiveStep = _steps;
+	const double bt = domain->getGlobalBetaTrans();
+	const double br = domain->getGlobalBetaRot();
+	const double Ti = _lastTfactor * domain->getTargetTemperature(0);
+	if (Ti > 0.0 && _n > 0) {
+		const double rawBt = std::pow(3.0 * _n * Ti / _summv2, 0.4);
+		const double rawBr = (_sumIw2 == 0.0 || _rotDOF == 0) ? 1.0 : std::pow(_rotDOF * Ti / _sumIw2, 0.4);
+		if ((rawBt < MIN_BETA || rawBr < MIN_BETA) && bt == 1.0 && std::fabs(br - std::pow(rawBr, 0.0091)) <= 1e-14) {
+			for (ls1g_ctx* cx : _ctxs) chk(ls1g_selective_thermostat(cx, KINLIMIT_PER_T * Ti, Ti), "ls1g_selective_thermostat");
+			++_selective;
+		}
+	}
+}
+
+uint64_t GpuLinkedCells::writeBinaryRecords(const std::string& datFile, Domain* domain) {
+	if (!deviceHoldsState()) {
+		global_log->error_always_output() << "GpuLinkedCells::writeBinaryRecords: the host cells hold the state" << std::endl;
+		Simulation::exit(1);
+	}
+	const double t0 = wall();
+	// the reference's writer runs after VelocityScalingThermostat::apply (Simulation.cpp:1108-1136, plugins' endStep :1150-1158);
+	// the device applies that scaling inside its next step, so it goes into the records here (same multiplication, same bits)
+	double bt = 1.0, br = 1.0;
+	if (_steps > 0 && !domain->NVE()) {
+		applySelectiveThermostat(domain);
+		bt = domain->getGlobalBetaTrans();
+		br = domain->getGlobalBetaRot();
+	}
+	std::FILE* f = std::fopen(datFile.c_str(), "wb");
+	if (f == nullptr) {
+		global_log->error_always_output() << "GpuLinkedCells::writeBinaryRecords: could not open " << datFile << std::endl;
+		Simulation::exit(1);
+	}
+	uint64_t total = 0;
+	for (ls1g_ctx* cx : _ctxs) {
+		size_t n = 0;
+		chk(ls1g_download_records(cx, 1.0, 1.0, 0, nullptr, &n), "ls1g_download_records");
+		if (n == 0) continue;
+		ensureStaging(n + n / 28 + 16);                // the staging block holds >= 112 bytes per molecule: room for 116-byte records
+		chk(ls1g_download_records(cx, bt, br, n, _stage, &n), "ls1g_download_records");
+		if (std::fwrite(_stage, 116, n, f) != n) {
+			global_log->error_always_output() << "GpuLinkedCells::writeBinaryRecords: short write to " << datFile << std::endl;
+			Simulation::exit(1);
+		}
+		total += n;
+	}
+	std::fclose(f);
+	++_recordWrites;
+	_bytesRecords += static_cast<size_t>(total) * 116;
+	_tRecords += wall() - t0;
+	return total;
 }
 
 // Leapfrog::eventForcesCalculated (Leapfrog.cpp:70-155)

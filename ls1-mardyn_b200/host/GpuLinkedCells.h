@@ -35,6 +35,7 @@
 #include "particleContainer/LinkedCells.h"
 
 #include <cstdint>
+#include <string>
 #include <vector>
 
 struct ls1g_ctx;
@@ -70,6 +71,13 @@ public:
 
 	/** refill the host cells from the device (r, v, q, D, F, M, Vi); they are dropped again at the next time step */
 	void downloadMirror();
+	/** true while the device, not the host cells, holds the current state (device phase, outside a time step, no mirror taken) */
+	bool deviceHoldsState() const { return _ctx != nullptr && _deviceLoaded && _devicePhase && !_mirrorValid && !_inStep; }
+	/** the owned molecules of all blocks as FullMolecule::writeBinary records (ICRVQD, 116 bytes) straight from the device into
+	 *  `datFile` (truncated first; block after block as DomainDecompBase::writeMoleculesToFile appends rank after rank), with the
+	 *  velocity scaling of the step that just ended applied on the way out as VelocityScalingThermostat::apply would have by now.
+	 *  Requires deviceHoldsState().  Returns the number of records written. */
+	uint64_t writeBinaryRecords(const std::string& datFile, Domain* domain);
 	ls1g_ctx* ctx() { return _ctx; }
 	int numDevices() const { return static_cast<int>(_ctxs.size()); }
 
@@ -91,6 +99,7 @@ private:
 	bool mirrorWanted() const;
 	unsigned long mirrorFrequencyFromPlugins(XMLfileUnits& xmlconfig) const;
 	void printSummary() const;
+	void applySelectiveThermostat(Domain* domain);
 	void sampleRDF();
 	void sampleFlops(FlopCounter& counter);
 	[[noreturn]] void fail(const char* what) const;
@@ -118,6 +127,10 @@ private:
 	bool _pointMolecules = false;  // one component, one LJ centre at the origin, no rotation: the device keeps no q / D / M
 	unsigned long _steps = 0, _mirrors = 0, _selective = 0, _rdfSamples = 0, _flopSamples = 0;
 	double _lastTfactor = 1.0;
+	unsigned long _selectiveStep = ~0ul;   // value of _steps for which the explosion heuristics have been looked at (once per step)
+	unsigned long _recordWrites = 0;
+	double _tRecords = 0.;
+	size_t _bytesRecords = 0;
 	size_t _bytesUp = 0, _bytesDown = 0, _numCells = 0;
 	double _pendingBt = 1.0, _pendingBr = 1.0;   // fused mode: betas of the previous step, applied inside the next ls1g_step
 	// page-locked staging block (ls1g_host_alloc): r v q L F M Vi id cid cell, 192 bytes per molecule

@@ -86,6 +86,66 @@ def test_checkpoints_written_during_the_run_match_the_reference(tmp_path):
             assert np.allclose(a[key][ia], b[key][ib], rtol=1e-7, atol=1e-9), (k, key)
 
 
+BIN_REF = ('<outputplugin name="CheckpointWriter"><type>binary</type><writefrequency>%d</writefrequency><outputprefix>cp</outputprefix>'
+           '</outputplugin>')
+BIN_GPU = '<outputplugin name="GpuCheckpointWriter"><writefrequency>%d</writefrequency><outputprefix>cp</outputprefix></outputplugin>'
+RECORD = np.dtype([("id", "<u8"), ("cid", "<u4"), ("r", "<f8", 3), ("v", "<f8", 3), ("q", "<f8", 4), ("D", "<f8", 3)])
+
+
+def records_by_id(path):
+    rec = np.fromfile(path, dtype=RECORD)
+    return rec[np.argsort(rec["id"])]
+
+
+@needs_binaries
+def test_device_checkpoint_plugin_equals_the_reference_writer_on_a_host_container(tmp_path):
+    """GpuCheckpointWriter with the reference's own LinkedCells (no device): same file names, same bytes as <CheckpointWriter
+    type=binary> of the unmodified reference - the plugin's registration, XML and naming, on CPU"""
+    cpu_dir, gpu_dir = tmp_path / "ref", tmp_path / "plugin"
+    cpu_dir.mkdir(), gpu_dir.mkdir()
+    M.run(M.REF_EXE, M.write_case(str(cpu_dir), "ex_CO2", 4, "cpu", output_plugins=BIN_REF % 2), 4, threads=1)
+    M.run(M.GPU_EXE, M.write_case(str(gpu_dir), "ex_CO2", 4, "cpu", output_plugins=BIN_GPU % 2), 4, threads=1)
+    names = sorted(f for f in os.listdir(cpu_dir) if f.startswith("cp-"))
+    assert names == ["cp-%d.restart.%s" % (k, e) for k in (0, 1, 2) for e in ("dat", "header.xml")]
+    for f in names:
+        assert open(cpu_dir / f, "rb").read() == open(gpu_dir / f, "rb").read(), f
+
+
+@pytest.mark.gpu
+@needs_binaries
+@pytest.mark.parametrize("name,variant,devices", [("ex_Argon", "fused", 1), ("ex_CO2", "fused", 1), ("ex_EOX", "fused", 1),
+                                                  ("ex_EOX", "operators", 1), ("ex_CO2", "fused", 2)])
+def test_checkpoints_taken_from_the_device_records(name, variant, devices, tmp_path):
+    """GpuCheckpointWriter every 3 steps of a 7-step NVT run: the packed records come straight from the device (no mirror step, no
+    host Molecule), with the step's velocity scaling - and for EOX the kinetic-energy limiter of Domain.cpp:254-311 - applied as the
+    reference has by the time its writer runs.  Held to (a) the CPU reference's binary CheckpointWriter files and (b) the SAME device
+    trajectory written through the reference's writer on mirror steps, which must give the same records to rounding."""
+    opts = "<devices>%d</devices>" % devices if devices > 1 else ""
+    dirs = {k: tmp_path / k for k in ("cpu", "records", "mirror")}
+    for d in dirs.values():
+        d.mkdir()
+    M.run(M.REF_EXE, M.write_case(str(dirs["cpu"]), name, 7, "cpu", output_plugins=BIN_REF % 3), 7)
+    rec = M.run(M.GPU_EXE, M.write_case(str(dirs["records"]), name, 7, variant, container_options=opts, output_plugins=BIN_GPU % 3), 7)
+    mir = M.run(M.GPU_EXE, M.write_case(str(dirs["mirror"]), name, 7, variant, container_options=opts, output_plugins=BIN_REF % 3), 7)
+    assert "mirror frequency 0 (from the plugins' write frequencies)" in rec["log"] and rec["gpu"]["mirrors"] == 1      # the final one only
+    assert "2 record checkpoint(s) from the device" in rec["log"] and mir["gpu"]["mirrors"] == 3
+    if name == "ex_EOX":
+        assert "selective thermostat applied 0 time(s)" not in rec["log"]
+        sel = lambda log: log.split("selective thermostat applied ")[1].split(" ")[0]
+        assert sel(rec["log"]) == sel(mir["log"])                                                 # once per step, whoever asks first
+    assert np.allclose(rec["res"], mir["res"], rtol=1e-12, atol=0)                               # taking checkpoints does not touch the trajectory
+    for k in (0, 1, 2):            # 0 = the start configuration, written from the host phase through the reference's writer
+        hdr = "cp-%d.restart.header.xml" % k
+        assert open(dirs["cpu"] / hdr, "rb").read() == open(dirs["records"] / hdr, "rb").read()
+        a, b, c = (records_by_id(str(dirs[w] / ("cp-%d.restart.dat" % k))) for w in ("cpu", "records", "mirror"))
+        assert len(a) == len(b) == len(c) > 0
+        assert np.array_equal(a["id"], b["id"]) and np.array_equal(a["cid"], b["cid"]) and np.array_equal(b["id"], c["id"])
+        for key in ("r", "v", "q", "D"):
+            assert np.allclose(a[key], b[key], rtol=1e-7, atol=1e-9), (k, key)                  # against the CPU reference (file-wide tolerance)
+            scale = max(np.abs(c[key]).max(), 1e-300)
+            assert np.abs(b[key] - c[key]).max() <= 1e-12 * scale, (k, key, np.abs(b[key] - c[key]).max() / scale)   # same trajectory, two ways out
+
+
 @needs_binaries
 @pytest.mark.parametrize("what,xml", [
     ("planar long-range correction", '<longrange type="planar"><slabs>10</slabs></longrange></algorithm>'),

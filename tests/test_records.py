@@ -95,6 +95,14 @@ def test_download_records_are_the_bytes_the_reference_wrote():
         assert np.array_equal(got[np.argsort(order)], raw[np.argsort(ids)])
         c.delete_outer_particles()
         assert np.array_equal(c.download_records(), got)
+        # a velocity scaling that the device has not applied yet goes into the records (Molecule::scale_v / scale_D: one
+        # multiplication per component), the device state stays as it is
+        scaled = c.download_records(scale_v=0.97, scale_D=1.03).view(P.BINARY_RECORD).ravel()
+        plain = got.view(P.BINARY_RECORD).ravel()
+        assert np.array_equal(scaled["v"], plain["v"] * 0.97) and np.array_equal(scaled["D"], plain["D"] * 1.03)
+        for k in ("id", "cid", "r", "q"):
+            assert np.array_equal(scaled[k], plain[k])
+        assert np.array_equal(c.download_records(), got)
 
 
 def synthetic_records(n, fmt, n_comp, box, rng, outside=0.03):
