@@ -7,9 +7,8 @@ import bench
 cells = int(sys.argv[1]) if len(sys.argv) > 1 else 136
 steps = int(sys.argv[2]) if len(sys.argv) > 2 else 50
 mode = sys.argv[3] if len(sys.argv) > 3 else "fused"
-L = cells * (4.0 / bench.RHO) ** (1.0 / 3.0)
 with tempfile.TemporaryDirectory() as td:
-    xml = bench.MARDYN_XML.format(dt=bench.DT, steps=steps, temp=bench.TEMP, L=repr(L), rho=bench.RHO, rc=bench.RC, integrator="GpuLeapfrog", container="GpuLinkedCells")
+    xml = bench.mardyn_xml(steps, cells, True)
     xml = xml.replace("<cellsInCutoffRadius>1</cellsInCutoffRadius>", "<cellsInCutoffRadius>1</cellsInCutoffRadius><mode>%s</mode>" % mode)
     open(os.path.join(td, "cfg.xml"), "w").write(xml)
     env = dict(os.environ, OMP_NUM_THREADS=str(bench.host_cores()), OMP_PROC_BIND="close", OMP_PLACES="cores")
