@@ -113,10 +113,11 @@ def test_device_checkpoint_plugin_equals_the_reference_writer_on_a_host_containe
 
 @pytest.mark.gpu
 @needs_binaries
-@pytest.mark.parametrize("name,variant,devices", [("ex_Argon", "fused", 1), ("ex_CO2", "fused", 1), ("ex_EOX", "fused", 1),
-                                                  ("ex_EOX", "operators", 1), ("ex_CO2", "fused", 2)])
-def test_checkpoints_taken_from_the_device_records(name, variant, devices, tmp_path):
-    """GpuCheckpointWriter every 3 steps of a 7-step NVT run: the packed records come straight from the device (no mirror step, no
+@pytest.mark.parametrize("name,variant,devices,steps", [("ex_Argon", "fused", 1, 7), ("ex_CO2", "fused", 1, 7), ("ex_EOX", "fused", 1, 7),
+                                                        ("ex_EOX", "operators", 1, 7), ("ex_CO2", "fused", 2, 7), ("ex_CO2", "fused", 1, 6)])
+def test_checkpoints_taken_from_the_device_records(name, variant, devices, steps, tmp_path):
+    """GpuCheckpointWriter every 3 steps of a 7-step NVT run (6 steps: the second checkpoint falls on the last step, whose state is
+    already mirrored into the host cells, and goes through the reference's writer): the packed records come straight from the device (no mirror step, no
     host Molecule), with the step's velocity scaling - and for EOX the kinetic-energy limiter of Domain.cpp:254-311 - applied as the
     reference has by the time its writer runs.  Held to (a) the CPU reference's binary CheckpointWriter files and (b) the SAME device
     trajectory written through the reference's writer on mirror steps, which must give the same records to rounding."""
@@ -124,11 +125,12 @@ def test_checkpoints_taken_from_the_device_records(name, variant, devices, tmp_p
     dirs = {k: tmp_path / k for k in ("cpu", "records", "mirror")}
     for d in dirs.values():
         d.mkdir()
-    M.run(M.REF_EXE, M.write_case(str(dirs["cpu"]), name, 7, "cpu", output_plugins=BIN_REF % 3), 7)
-    rec = M.run(M.GPU_EXE, M.write_case(str(dirs["records"]), name, 7, variant, container_options=opts, output_plugins=BIN_GPU % 3), 7)
-    mir = M.run(M.GPU_EXE, M.write_case(str(dirs["mirror"]), name, 7, variant, container_options=opts, output_plugins=BIN_REF % 3), 7)
+    M.run(M.REF_EXE, M.write_case(str(dirs["cpu"]), name, steps, "cpu", output_plugins=BIN_REF % 3), steps)
+    rec = M.run(M.GPU_EXE, M.write_case(str(dirs["records"]), name, steps, variant, container_options=opts, output_plugins=BIN_GPU % 3), steps)
+    mir = M.run(M.GPU_EXE, M.write_case(str(dirs["mirror"]), name, steps, variant, container_options=opts, output_plugins=BIN_REF % 3), steps)
     assert "mirror frequency 0 (from the plugins' write frequencies)" in rec["log"] and rec["gpu"]["mirrors"] == 1      # the final one only
-    assert "2 record checkpoint(s) from the device" in rec["log"] and mir["gpu"]["mirrors"] == 3
+    from_device = sum(1 for k in (3, 6) if k < steps)
+    assert "%d record checkpoint(s) from the device" % from_device in rec["log"] and mir["gpu"]["mirrors"] == len({3, 6, steps})
     if name == "ex_EOX":
         assert "selective thermostat applied 0 time(s)" not in rec["log"]
         sel = lambda log: log.split("selective thermostat applied ")[1].split(" ")[0]
