@@ -2,9 +2,10 @@
  * GpuCheckpointWriter — ls1-MarDyn output plugin: binary checkpoints written straight from the device.
  *
  *   <outputplugin name="GpuCheckpointWriter">
+ *     <type>binary|ASCII</type>                    default binary
  *     <writefrequency>INTEGER</writefrequency>     default 1
  *     <outputprefix>STRING</outputprefix>          default "mardyn"
- *     <incremental>INTEGER</incremental>           default 1: PREFIX-<number>.restart.{header.xml,dat}
+ *     <incremental>INTEGER</incremental>           default 1: PREFIX-<number>.restart.{header.xml,dat} (binary), PREFIX-<number>.restart.dat (ASCII)
  *   </outputplugin>
  *
  * Same files as the reference's <outputplugin name="CheckpointWriter"><type>binary</type> (io/CheckpointWriter.cpp:62-90 ->
@@ -12,7 +13,9 @@
  * .dat file holds one FullMolecule::writeBinary record (molecules/FullMolecule.cpp:451-474) per molecule.  The difference is where
  * the records come from: DomainDecompBase::writeMoleculesToFile (parallel/DomainDecompBase.cpp:505-540, not virtual) walks host
  * Molecule objects, which costs a GpuLinkedCells container a full mirror step; this plugin asks the container for the packed records
- * (GpuLinkedCells::writeBinaryRecords -> ls1g_download_records) and writes the bytes as they arrive - no host Molecule is touched.
+ * (GpuLinkedCells::writeRecords -> ls1g_download_records) and writes the bytes as they arrive - no host Molecule is touched.
+ * <type>ASCII</type> gives the files of <CheckpointWriter><type>ASCII</type>: the reference's Domain::writeCheckpointHeader, then one
+ * FullMolecule::write line per molecule, printed by the host threads from the packed records (RecordText.h).
  * The molecules come cell by cell as in the reference's file, inside a cell ordered by id.  With any other container, or while
  * the host cells hold the state, it falls back to Domain::writeCheckpoint(binary).
  *
@@ -39,6 +42,7 @@ private:
 	std::string _prefix = "mardyn";
 	unsigned long _every = 1;
 	bool _numbered = true;
+	bool _ascii = false;
 };
 
 #endif /* GPUCHECKPOINTWRITER_H_ */

@@ -3,6 +3,7 @@
  * only converts between the reference's host objects (Molecule, Component, Domain) and plain arrays.
  */
 #include "GpuLinkedCells.h"
+#include "RecordText.h"
 
 #include "Domain.h"
 #include "Simulation.h"
@@ -148,7 +149,7 @@ unsigned long GpuLinkedCells::mirrorFrequencyFromPlugins(XMLfileUnits& xmlconfig
 	static const std::set<std::string> noMolecules = {"ResultWriter", "SysMonOutput", "TimerWriter", "LoadbalanceWriter",
 	                                                  "DecompWriter", "CommunicationPartnerWriter", "KDTreePrinter",
 	                                                  "RDF", "FlopRateWriter",       // their traversals are counted on the device (sampleRDF, sampleFlops)
-	                                                  "GpuCheckpointWriter"};        // takes the packed records from the device (writeBinaryRecords)
+	                                                  "GpuCheckpointWriter"};        // takes the packed records from the device (writeRecords)
 	static const std::set<std::string> readers = {"CheckpointWriter", "MPICheckpointWriter", "XyzWriter", "MmpldWriter",
 	                                              "MmspdWriter", "MmspdBinWriter", "PovWriter", "VISWriter", "MaxWriter",
 	                                              "EnergyLogWriter"};
@@ -864,7 +865,7 @@ void GpuLinkedCells::integratePre(double dt, Domain* domain) {
 // "Explosion heuristics" (Domain.cpp:254-311): when a raw beta is below MIN_BETA, calculateGlobalValues caps the kinetic energy per
 // molecule and replaces the betas by (1, beta_rot^0.0091).  Its molecule loop ran over the (empty) host cells; the same capping is
 // done here on the device.  The raw betas are recomputed from the very sums handed to Domain.  Runs once per time step: either when a
-// checkpoint is taken from the device at the end of the step (writeBinaryRecords) or at the start of the next step (integratePre) -
+// checkpoint is taken from the device at the end of the step (writeRecords) or at the start of the next step (integratePre) -
 // nothing touches v, D in between.
 void GpuLinkedCells::applySelectiveThermostat(Domain* domain) {
 	if (_selectiveStep == _steps) return;
@@ -882,9 +883,9 @@ void GpuLinkedCells::applySelectiveThermostat(Domain* domain) {
 	}
 }
 
-uint64_t GpuLinkedCells::writeBinaryRecords(const std::string& datFile, Domain* domain) {
+uint64_t GpuLinkedCells::writeRecords(const std::string& file, Domain* domain, bool ascii) {
 	if (!deviceHoldsState()) {
-		global_log->error_always_output() << "GpuLinkedCells::writeBinaryRecords: the host cells hold the state" << std::endl;
+		global_log->error_always_output() << "GpuLinkedCells::writeRecords: the host cells hold the state" << std::endl;
 		Simulation::exit(1);
 	}
 	const double t0 = wall();
@@ -896,27 +897,57 @@ uint64_t GpuLinkedCells::writeBinaryRecords(const std::string& datFile, Domain* 
 		bt = domain->getGlobalBetaTrans();
 		br = domain->getGlobalBetaRot();
 	}
-	std::FILE* f = std::fopen(datFile.c_str(), "wb");
+	std::FILE* f = std::fopen(file.c_str(), ascii ? "ab" : "wb");
 	if (f == nullptr) {
-		global_log->error_always_output() << "GpuLinkedCells::writeBinaryRecords: could not open " << datFile << std::endl;
+		global_log->error_always_output() << "GpuLinkedCells::writeRecords: could not open " << file << std::endl;
 		Simulation::exit(1);
 	}
+	auto put = [&](const void* p, size_t bytes) {
+		if (bytes != 0 && std::fwrite(p, 1, bytes, f) != bytes) {
+			global_log->error_always_output() << "GpuLinkedCells::writeRecords: short write to " << file << std::endl;
+			Simulation::exit(1);
+		}
+	};
 	uint64_t total = 0;
+	size_t written = 0;
 	for (ls1g_ctx* cx : _ctxs) {
 		size_t n = 0;
 		chk(ls1g_download_records(cx, 1.0, 1.0, 0, nullptr, &n), "ls1g_download_records");
 		if (n == 0) continue;
 		ensureStaging(n + n / 28 + 16);                // the staging block holds >= 112 bytes per molecule: room for 116-byte records
 		chk(ls1g_download_records(cx, bt, br, n, _stage, &n), "ls1g_download_records");
-		if (std::fwrite(_stage, 116, n, f) != n) {
-			global_log->error_always_output() << "GpuLinkedCells::writeBinaryRecords: short write to " << datFile << std::endl;
-			Simulation::exit(1);
+		const unsigned char* rec = static_cast<const unsigned char*>(_stage);
+		if (!ascii) {
+			put(rec, n * ls1g_records::kRecordBytes);
+			written += n * ls1g_records::kRecordBytes;
+		} else {
+			// text in slabs of 2^20 molecules: every thread prints a contiguous share of the slab, the shares go to the file in order
+			int nt = 1;
+#if defined(_OPENMP)
+			nt = omp_get_max_threads();
+#endif
+			std::vector<std::string> part(nt);
+			const size_t slab = size_t(1) << 20;
+			for (size_t first = 0; first < n; first += slab) {
+				const size_t count = std::min(slab, n - first);
+#if defined(_OPENMP)
+#pragma omp parallel for schedule(static, 1)
+#endif
+				for (int t = 0; t < nt; ++t) {
+					part[t].clear();
+					ls1g_records::appendLines(rec, first + count * t / nt, first + count * (t + 1) / nt, part[t]);
+				}
+				for (int t = 0; t < nt; ++t) {
+					put(part[t].data(), part[t].size());
+					written += part[t].size();
+				}
+			}
 		}
 		total += n;
 	}
 	std::fclose(f);
 	++_recordWrites;
-	_bytesRecords += static_cast<size_t>(total) * 116;
+	_bytesRecords += written;
 	_tRecords += wall() - t0;
 	return total;
 }

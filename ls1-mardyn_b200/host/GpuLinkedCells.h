@@ -73,11 +73,14 @@ public:
 	void downloadMirror();
 	/** true while the device, not the host cells, holds the current state (device phase, outside a time step, no mirror taken) */
 	bool deviceHoldsState() const { return _ctx != nullptr && _deviceLoaded && _devicePhase && !_mirrorValid && !_inStep; }
-	/** the owned molecules of all blocks as FullMolecule::writeBinary records (ICRVQD, 116 bytes) straight from the device into
-	 *  `datFile` (truncated first; block after block as DomainDecompBase::writeMoleculesToFile appends rank after rank), with the
-	 *  velocity scaling of the step that just ended applied on the way out as VelocityScalingThermostat::apply would have by now.
-	 *  Requires deviceHoldsState().  Returns the number of records written. */
-	uint64_t writeBinaryRecords(const std::string& datFile, Domain* domain);
+	/** the owned molecules of all blocks straight from the device into `file`, block after block as
+	 *  DomainDecompBase::writeMoleculesToFile appends rank after rank, with the velocity scaling of the step that just ended applied
+	 *  on the way out as VelocityScalingThermostat::apply would have by now.
+	 *  ascii = false: FullMolecule::writeBinary records (ICRVQD, 116 bytes); the file is truncated first.
+	 *  ascii = true : FullMolecule::write lines at the writer's stream precision of 20 (RecordText.h), formatted by the host threads
+	 *                 from the packed records; appended to the file, which holds Domain::writeCheckpointHeader's header already.
+	 *  Requires deviceHoldsState().  Returns the number of molecules written. */
+	uint64_t writeRecords(const std::string& file, Domain* domain, bool ascii);
 	ls1g_ctx* ctx() { return _ctx; }
 	int numDevices() const { return static_cast<int>(_ctxs.size()); }
 

@@ -4,8 +4,9 @@ Runs the unmodified reference executable on the per_MultiComponentMultiPotential
 rotation) for one time step with its CheckpointWriter plugin in binary mode (io/CheckpointWriter.cpp:28-33 ->
 Domain::writeCheckpoint -> DomainDecompBase::writeMoleculesToFile -> FullMolecule::writeBinary) and keeps
     tests/golden/cp_binary_MultiComponent.dat / .header.xml   the binary checkpoint after that step, byte for byte
-    tests/golden/cp_binary_MultiComponent.npz                 the same state as the reference's ASCII writer printed it (final
-                                                              checkpoint, FullMolecule::write at 20 digits), parsed: id cid r v q D
+    tests/golden/cp_ascii_MultiComponent.restart.dat          the same state as the reference's ASCII writer printed it (final
+                                                              checkpoint, FullMolecule::write at 20 digits), molecules in the same order
+    tests/golden/cp_binary_MultiComponent.npz                 ... parsed: id cid r v q D
 so the two writers of the reference pin each other (the script checks that they agree exactly; the checkpoint of step 0 is
 checked against the fixture's input molecules).  The record layout of ls1g_upload_records / ls1g_download_records (and of phasespace.read_binary / write_binary) is pinned to
 these bytes: tests/test_records.py.
@@ -54,6 +55,12 @@ def main():
         for a in ("r", "v", "q", "D"):
             assert np.array_equal(rec[a][o], f[a]), a
         np.savez_compressed(os.path.join(out, "cp_binary_MultiComponent.npz"), **f)
+        # the ASCII checkpoint itself (header + one FullMolecule::write line per molecule, stream precision 20), same state, same order
+        asc = os.path.join(tmp, NAME + "_cpu.restart.dat")
+        lines = open(asc).read().split("\n")
+        k = next(i for i, l in enumerate(lines) if l.split()[:1] == ["MoleculeFormat"])
+        assert [int(l.split()[0]) for l in lines[k + 1:] if l] == rec["id"].tolist()
+        shutil.copy(asc, os.path.join(out, "cp_ascii_MultiComponent.restart.dat"))
         shutil.copy(dat, os.path.join(out, "cp_binary_MultiComponent.dat"))
         shutil.copy(hdr, os.path.join(out, "cp_binary_MultiComponent.header.xml"))
     print("wrote cp_binary_MultiComponent.{dat,header.xml}: %d records" % len(rec))

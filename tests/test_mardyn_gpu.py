@@ -111,6 +111,57 @@ def test_device_checkpoint_plugin_equals_the_reference_writer_on_a_host_containe
         assert open(cpu_dir / f, "rb").read() == open(gpu_dir / f, "rb").read(), f
 
 
+ASCII_REF = ('<outputplugin name="CheckpointWriter"><type>ASCII</type><writefrequency>%d</writefrequency><outputprefix>cp</outputprefix>'
+             '</outputplugin>')
+ASCII_GPU = ('<outputplugin name="GpuCheckpointWriter"><type>ASCII</type><writefrequency>%d</writefrequency><outputprefix>cp</outputprefix>'
+             '</outputplugin>')
+
+
+def ascii_header(path):
+    text = open(path, "rb").read()
+    return text[:text.index(b"\n", text.index(b"MoleculeFormat")) + 1]
+
+
+@needs_binaries
+def test_device_checkpoint_plugin_ascii_on_a_host_container(tmp_path):
+    """<type>ASCII</type> with the reference's own LinkedCells: the bytes of <CheckpointWriter type=ASCII>"""
+    cpu_dir, gpu_dir = tmp_path / "ref", tmp_path / "plugin"
+    cpu_dir.mkdir(), gpu_dir.mkdir()
+    M.run(M.REF_EXE, M.write_case(str(cpu_dir), "ex_EOX", 2, "cpu", output_plugins=ASCII_REF % 2), 2, threads=1)
+    M.run(M.GPU_EXE, M.write_case(str(gpu_dir), "ex_EOX", 2, "cpu", output_plugins=ASCII_GPU % 2), 2, threads=1)
+    names = sorted(f for f in os.listdir(cpu_dir) if f.startswith("cp-"))
+    assert names == ["cp-0.restart.dat", "cp-1.restart.dat"]
+    for f in names:
+        assert open(cpu_dir / f, "rb").read() == open(gpu_dir / f, "rb").read(), f
+
+
+@pytest.mark.gpu
+@needs_binaries
+@pytest.mark.parametrize("name,devices", [("ex_CO2", 1), ("ex_Argon", 2)])
+def test_ascii_checkpoints_taken_from_the_device_records(name, devices, tmp_path):
+    """GpuCheckpointWriter <type>ASCII</type>: the reference's header, then lines printed by the host threads from the device's packed
+    records (no mirror step).  Header equal to the CPU reference's byte for byte; molecules against the CPU reference (file-wide
+    tolerance) and against the same device trajectory written by the reference's ASCII writer on mirror steps (1e-12)"""
+    opts = "<devices>%d</devices>" % devices if devices > 1 else ""
+    dirs = {k: tmp_path / k for k in ("cpu", "records", "mirror")}
+    for d in dirs.values():
+        d.mkdir()
+    M.run(M.REF_EXE, M.write_case(str(dirs["cpu"]), name, 7, "cpu", output_plugins=ASCII_REF % 3), 7)
+    rec = M.run(M.GPU_EXE, M.write_case(str(dirs["records"]), name, 7, "fused", container_options=opts, output_plugins=ASCII_GPU % 3), 7)
+    M.run(M.GPU_EXE, M.write_case(str(dirs["mirror"]), name, 7, "fused", container_options=opts, output_plugins=ASCII_REF % 3), 7)
+    assert rec["gpu"]["mirrors"] == 1 and "2 record checkpoint(s) from the device" in rec["log"]
+    for k in (0, 1, 2):
+        f = "cp-%d.restart.dat" % k
+        assert ascii_header(str(dirs["cpu"] / f)) == ascii_header(str(dirs["records"] / f))
+        a, b, c = (M.read_checkpoint_molecules(str(dirs[w] / f)) for w in ("cpu", "records", "mirror"))
+        assert len(a["id"]) == len(b["id"]) == len(c["id"]) > 0
+        assert np.array_equal(a["id"], b["id"]) and np.array_equal(a["cid"], b["cid"]) and np.array_equal(b["id"], c["id"])
+        for key in ("r", "v", "q", "D"):
+            assert np.allclose(a[key], b[key], rtol=1e-7, atol=1e-9), (k, key)
+            scale = max(np.abs(c[key]).max(), 1e-300)
+            assert np.abs(b[key] - c[key]).max() <= 1e-12 * scale, (k, key)
+
+
 @pytest.mark.gpu
 @needs_binaries
 @pytest.mark.parametrize("name,variant,devices,steps", [("ex_Argon", "fused", 1, 7), ("ex_CO2", "fused", 1, 7), ("ex_EOX", "fused", 1, 7),

@@ -53,6 +53,21 @@ def test_python_reader_and_writer_reproduce_the_reference_files(tmp_path):
         P.read_binary(HDR, DAT, n_components=4)                                         # BinaryReader.cpp:222-228
 
 
+def test_ascii_lines_printed_from_the_packed_records_are_the_reference_writers(tmp_path):
+    """host/RecordText.h (what GpuLinkedCells::writeRecords prints for <type>ASCII</type>): the molecule lines of the reference's
+    ASCII checkpoint, byte for byte, from the reference's binary checkpoint of the same state"""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = str(tmp_path / "record_text_check")
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-I", os.path.join(root, "ls1-mardyn_b200", "host"),
+                           os.path.join(root, "tests", "record_text_check.cpp"), "-o", exe])
+    mine = subprocess.run([exe, DAT], capture_output=True, check=True).stdout
+    ref = open(os.path.join(GOLDEN, "cp_ascii_MultiComponent.restart.dat"), "rb").read()
+    k = ref.index(b"MoleculeFormat")
+    body = ref[ref.index(b"\n", k) + 1:]
+    assert mine == body and mine.count(b"\n") == 128
+
+
 def test_record_size_is_host_only():
     assert [ls1g.Container.record_size(f) for f in ("ICRVQD", "ICRV", "IRV")] == [116, 60, 56] == [FORMATS[f].itemsize for f in ("ICRVQD", "ICRV", "IRV")]
     with pytest.raises(ls1g.Ls1gError, match="Not a valid molecule format"):
