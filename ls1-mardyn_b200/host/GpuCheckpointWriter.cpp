@@ -46,7 +46,7 @@ void GpuCheckpointWriter::endStep(ParticleContainer* particleContainer, DomainDe
 	std::string name = _prefix;
 	if (_numbered) {
 		const unsigned long writes = _simulation.getNumTimesteps() / _every;
-		const int digits = static_cast<int>(std::ceil(std::log(static_cast<double>(writes)) / std::log(10.)));
+		const int digits = writes >= 1 ? static_cast<int>(std::ceil(std::log(static_cast<double>(writes)) / std::log(10.))) : 0;
 		name += "-" + aligned_number(static_cast<int>(simstep / _every), digits, '0');
 	}
 	name += _ascii ? ".restart.dat" : ".restart";
