@@ -68,6 +68,27 @@ def test_ascii_lines_printed_from_the_packed_records_are_the_reference_writers(t
     assert mine == body and mine.count(b"\n") == 128
 
 
+@pytest.mark.parametrize("n_ranks", [2, 4, 8, 6])
+def test_bounding_boxes_of_the_ranks_partition_a_file(n_ranks):
+    """ls1g_upload_records keeps min <= r < max of the rank's box (isInBoundingBox): with DomainDecomposition's boxes (ls1g_decomp_grid /
+    ls1g_decomp_box, host only) every record of a file lands on exactly one rank - also records exactly on the faces between ranks"""
+    rng = np.random.default_rng(n_ranks)
+    box = np.array([31.7, 25.3, 40.9])
+    r = rng.uniform(0.0, 1.0, size=(20000, 3)) * box
+    owners = np.zeros(len(r), dtype=np.int64)
+    faces = []
+    for rank in range(n_ranks):
+        grid, coords = ls1g.decomp_grid(n_ranks, rank)
+        bmin, bmax = ls1g.decomp_box(grid, coords, box)
+        faces.append(bmax)
+    r[:len(faces)] = np.minimum(np.array(faces), np.nextafter(box, 0.0))          # points ON the upper faces of the rank boxes
+    for rank in range(n_ranks):
+        grid, coords = ls1g.decomp_grid(n_ranks, rank)
+        bmin, bmax = ls1g.decomp_box(grid, coords, box)
+        owners += np.all((r >= bmin) & (r < bmax), axis=1)
+    assert np.all(owners == 1)
+
+
 def test_record_size_is_host_only():
     assert [ls1g.Container.record_size(f) for f in ("ICRVQD", "ICRV", "IRV")] == [116, 60, 56] == [FORMATS[f].itemsize for f in ("ICRVQD", "ICRV", "IRV")]
     with pytest.raises(ls1g.Ls1gError, match="Not a valid molecule format"):
